@@ -1,0 +1,64 @@
+// Internal (C++) launch wrappers of the irb200 kernels. All take channels-last activations with an explicit
+// row stride (ld, in elements) so that zero-copy concatenation / channel slicing works, and a cudaStream_t.
+// Return 0 on success; on failure the message is available through irb_last_error().
+#pragma once
+#include "common.cuh"
+#include <cuda.h>
+
+namespace irb {
+
+// ---- gemm_tc.cu : tcgen05 (bf16) -------------------------------------------------------------
+int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                   const uint32_t* box);
+int tc_gemm(const bf16* A, long long lda, int M, int K, int batch, long long a_batch_stride, const bf16* Wt, int ldw,
+            int N, int w_rows_total, int w_rows_per_batch, const Epi& epi, cudaStream_t stream);
+int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, const bf16* Wt, int kpad, int N,
+               int w_rows_total, const Epi& epi, cudaStream_t stream);
+
+// ---- gemm_simt.cu : fp32 FMA path (fp32 precision mode, and tiny-channel convolutions) ------
+// A element type a_dt (DT_F32/DT_BF16); weights always float [Nrows, taps*kpad].
+int simt_gemm(const void* A, int a_dt, long long lda, int M, int K, int batch, long long a_batch_stride,
+              const float* Wt, int ldw, int N, int w_rows_per_batch, const Epi& epi, cudaStream_t stream);
+int simt_conv3x3(const void* A, int a_dt, long long lda, int Nimg, int H, int W, int C, const float* Wt, int kpad,
+                 int N, const Epi& epi, cudaStream_t stream);
+
+// ---- pointwise.cu ----------------------------------------------------------------------------
+// LayerNorm over channels per pixel. mode 0: WithBias ((x-mu)*rstd*w+b), mode 1: BiasFree (x*rstd*w).
+int layernorm(const void* x, int x_dt, long long ldx, void* y, int y_dt, long long ldy, long long rows, int C,
+              const float* w, const float* b, int mode, float eps, cudaStream_t stream);
+// depthwise 3x3 (zero pad 1). wt is [9][C] float (tap-major). If sumsq != nullptr, accumulates per (image, channel)
+// sum of squares of the fp32 outputs for channels < sumsq_channels into sumsq[img*sumsq_channels + c].
+int dwconv3x3(const void* x, int dt, long long ldx, void* y, long long ldy, int Nimg, int H, int W, int C,
+              const float* wt, float* sumsq, int sumsq_channels, cudaStream_t stream);
+// GDFN gate: y[., c] = gelu(dw(x)[., c]) * dw(x)[., hp + c] for c < hp ; x has 2*hp channels, wt is [9][2*hp].
+int dwconv3x3_gate(const void* x, int dt, long long ldx, void* y, long long ldy, int Nimg, int H, int W, int hp,
+                   const float* wt, cudaStream_t stream);
+int nearest_up2(const void* x, int dt, long long ldx, void* y, long long ldy, int Nimg, int H, int W, int C,
+                cudaStream_t stream);
+
+// ---- mdta.cu ---------------------------------------------------------------------------------
+// Gram over pixels of channels-last q,k (inside a qkv tensor of row stride ld): G[b,h,i,j] += sum_p q[p,hc+i]*k[p,hc+j]
+int mdta_gram_tc(const bf16* qkv, long long ld, int Nimg, int P, int C, int heads, float* G, cudaStream_t stream);
+int mdta_gram_simt(const void* qkv, int dt, long long ld, int Nimg, int P, int C, int heads, float* G,
+                   cudaStream_t stream);
+// attn = softmax_j(G[i,j] / (max(|q_i|,eps) max(|k_j|,eps)) * temp[h]); Weff[b][o][h*c+j] = sum_i Wp[o][h*c+i] attn[i][j]
+int mdta_softmax_weff(const float* G, const float* sumsq /*[Nimg][2C]*/, const float* temperature, const float* Wp,
+                      int Nimg, int C, int heads, void* Weff, int w_dt, float* attn_out /*optional*/,
+                      cudaStream_t stream);
+
+// ---- tiles.cu --------------------------------------------------------------------------------
+// Gather tiles from a planar float image [c][h][w] into channels-last float tiles [n][t][t][c],
+// applying (x - mean[c]) * scale.
+int tiles_gather(const float* img, int c, int h, int w, const int* ys, const int* xs, int ny, int nx, int th, int tw,
+                 float* tiles, const float* mean, float scale, cudaStream_t stream);
+// Overlap blend (reference order h-major, w-minor), divide by the analytic count, crop, clamp, round-half-even.
+int tiles_stitch(const float* tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx, int h,
+                 int w, int crop_h, int crop_w, float* out_f32 /*[c][crop_h][crop_w] or null*/,
+                 uint8_t* out_u8 /*[crop_h][crop_w][c] or null*/, int u8_reverse_channels, cudaStream_t stream);
+// uint8 HWC (optionally BGR) -> planar float [c][h'][w'] in [0,1] with the reference's padding rule.
+// pad_mode 0: reflect (Restormer / F.pad 'reflect'), 1: symmetric flip-and-concat (SwinIR scripts).
+int image_prepare(const uint8_t* src, int h, int w, int c, int reverse_channels, float* dst, int hp, int wp,
+                  int pad_mode, cudaStream_t stream);
+int image_pad_f32(const float* src, int c, int h, int w, float* dst, int hp, int wp, int pad_mode, cudaStream_t stream);
+
+}  // namespace irb

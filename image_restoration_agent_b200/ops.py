@@ -1,0 +1,135 @@
+"""Single-kernel host wrappers (torch tensors in, C-ABI calls out). Used by the parity tests and ncu captures.
+
+Activations are channels-last: [rows, C] or [n, H, W, C] contiguous torch CUDA tensors (fp32 or bf16).
+torch is used only for device memory and the current stream.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import BF16, F32, check
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise TypeError(f"irb200 supports fp32 / bf16 activations, got {t.dtype}")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def layernorm(x, w, b=None, bias_free=False, eps=1e-5):
+    rows, C = x.numel() // x.shape[-1], x.shape[-1]
+    y = torch.empty_like(x)
+    check(_lib.load().irb_layernorm(x.data_ptr(), _dt(x), C, y.data_ptr(), C, rows, C, w.data_ptr(), _ptr(b),
+                                    int(bias_free), eps, _stream()))
+    return y
+
+
+def gemm1x1(x, w, bias=None, res=None, act=0, slope=0.0, batch=1, w_rows_per_batch=0, N=None):
+    """x [batch*M, K], w [rows, K] (same dtype) -> [batch*M, N]."""
+    K = x.shape[-1]
+    M = (x.numel() // K) // batch
+    N = N if N is not None else (w_rows_per_batch if w_rows_per_batch else w.shape[0])
+    y = torch.empty((batch * M, N), device=x.device, dtype=x.dtype)
+    check(_lib.load().irb_gemm1x1(x.data_ptr(), _dt(x), x.stride(-2), M, K, batch, w.data_ptr(), w.stride(0), N,
+                                  w.shape[0], w_rows_per_batch, _ptr(bias), _ptr(res), N if res is not None else 0,
+                                  act, slope, y.data_ptr(), N, _stream()))
+    return y
+
+
+def pack_conv3x3_weight(w: torch.Tensor, dtype, row_pad=16) -> tuple[torch.Tensor, int]:
+    """nn.Conv2d weight [N, C, 3, 3] -> [N_pad, 9*kpad] with K index = (ky*3+kx)*kpad + c (zero padded)."""
+    N, Cin = w.shape[0], w.shape[1]
+    kpad = (Cin + 63) // 64 * 64
+    npad = (N + row_pad - 1) // row_pad * row_pad
+    out = torch.zeros((npad, 9, kpad), device=w.device, dtype=torch.float32)
+    out[:N, :, :Cin] = w.float().permute(0, 2, 3, 1).reshape(N, 9, Cin)
+    return out.reshape(npad, 9 * kpad).to(dtype).contiguous(), kpad
+
+
+def conv3x3(x, w_packed, kpad, N, bias=None, res=None, act=0, slope=0.0, shuffle=0):
+    """x [n, H, W, C] -> [n, H, W, N] (or the (un)shuffled shape)."""
+    n, H, W, Cin = x.shape
+    if shuffle == 1:
+        y = torch.empty((n, 2 * H, 2 * W, N // 4), device=x.device, dtype=x.dtype)
+    elif shuffle == 2:
+        y = torch.empty((n, H // 2, W // 2, N * 4), device=x.device, dtype=x.dtype)
+    else:
+        y = torch.empty((n, H, W, N), device=x.device, dtype=x.dtype)
+    check(_lib.load().irb_conv3x3(x.data_ptr(), _dt(x), x.stride(-2), n, H, W, Cin, w_packed.data_ptr(), kpad, N,
+                                  w_packed.shape[0], _ptr(bias), _ptr(res), N if res is not None else 0, act, slope,
+                                  shuffle, y.data_ptr(), y.shape[-1], _stream()))
+    return y
+
+
+def pack_dw_weight(w: torch.Tensor) -> torch.Tensor:
+    """depthwise nn.Conv2d weight [C, 1, 3, 3] -> fp32 [9, C] tap-major."""
+    return w.float().reshape(w.shape[0], 9).t().contiguous()
+
+
+def dwconv3x3(x, w9c, sumsq_channels=0):
+    n, H, W, Cc = x.shape
+    y = torch.empty_like(x)
+    ss = torch.zeros((n, sumsq_channels), device=x.device, dtype=torch.float32) if sumsq_channels else None
+    check(_lib.load().irb_dwconv3x3(x.data_ptr(), _dt(x), Cc, y.data_ptr(), Cc, n, H, W, Cc, w9c.data_ptr(), _ptr(ss),
+                                    sumsq_channels, _stream()))
+    return (y, ss) if sumsq_channels else y
+
+
+def gdfn_dw_gate(x, w9c):
+    n, H, W, C2 = x.shape
+    hp = C2 // 2
+    y = torch.empty((n, H, W, hp), device=x.device, dtype=x.dtype)
+    check(_lib.load().irb_gdfn_dw_gate(x.data_ptr(), _dt(x), C2, y.data_ptr(), hp, n, H, W, hp, w9c.data_ptr(),
+                                       _stream()))
+    return y
+
+
+def mdta_gram(qkv, heads):
+    n, H, W, C3 = qkv.shape
+    Cc = C3 // 3
+    c = Cc // heads
+    G = torch.zeros((n, heads, c, c), device=qkv.device, dtype=torch.float32)
+    check(_lib.load().irb_mdta_gram(qkv.data_ptr(), _dt(qkv), C3, n, H * W, Cc, heads, G.data_ptr(), _stream()))
+    return G
+
+
+def mdta_attn(G, sumsq, temperature, wproj, out_dtype):
+    n, heads, c, _ = G.shape
+    Cc = heads * c
+    weff = torch.empty((n, Cc, Cc), device=G.device, dtype=out_dtype)
+    attn = torch.empty_like(G)
+    check(_lib.load().irb_mdta_attn(G.data_ptr(), sumsq.data_ptr(), temperature.data_ptr(), wproj.data_ptr(), n, Cc,
+                                    heads, weff.data_ptr(), BF16 if out_dtype == torch.bfloat16 else F32,
+                                    attn.data_ptr(), _stream()))
+    return weff, attn
+
+
+def stitch(tiles, ys, xs, sf, h, w, crop_h, crop_w, want_u8=True, reverse_channels=False):
+    nt, TH, TW, c = tiles.shape
+    th, tw = TH // sf, TW // sf
+    out = torch.empty((c, crop_h, crop_w), device=tiles.device, dtype=torch.float32)
+    u8 = torch.empty((crop_h, crop_w, c), device=tiles.device, dtype=torch.uint8) if want_u8 else None
+    check(_lib.load().irb_stitch(tiles.data_ptr(), c, th, tw, sf, _lib.int_array(ys), _lib.int_array(xs), len(ys),
+                                 len(xs), h, w, crop_h, crop_w, out.data_ptr(), _ptr(u8), int(reverse_channels),
+                                 _stream()))
+    return out, u8
+
+
+def window_attention(qkv, heads, window, shift, bias_table):
+    n, H, W, C3 = qkv.shape
+    Cc = C3 // 3
+    y = torch.empty((n, H, W, Cc), device=qkv.device, dtype=qkv.dtype)
+    check(_lib.load().irb_window_attention(qkv.data_ptr(), _dt(qkv), C3, y.data_ptr(), Cc, n, H, W, Cc, heads, window,
+                                           shift, bias_table.data_ptr(), _stream()))
+    return y

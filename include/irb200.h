@@ -1,0 +1,145 @@
+/* irb200 — C ABI of the B200-native tiled forward pass of the SwinIR / Restormer restoration tools.
+ *
+ * This is the drop-in boundary for the one hot path of blackbean001/Image-Restoration-Agent: everything a
+ * reference tool does between "image decoded" and "uint8 image ready to encode":
+ *     pad -> [tile loop: model(in_patch); E += out; W += 1] -> E/W -> crop -> clamp -> round -> uint8
+ * Reference call sites replaced (paths relative to the reference root):
+ *   AgenticIR/executor/denoising/tools/SwinIR/inference.py:69-90, 294-322          (main loop body, test())
+ *   AgenticIR/executor/defocus_deblurring/tools/Restormer/demo.py:118-161           (per-file loop body)
+ *   AgentApp/model_service/denoising/SwinIR/model_serving.py:131-175                (process_image)
+ *   AgentApp/model_service/motion_deblurring/Restormer/model_serving.py:157-208     (restore_image)
+ *   .../SwinIR/models/network_swinir.py:805-840  (SwinIR.forward)
+ *   .../Restormer/basicsr/models/archs/restormer_arch.py:245-284 (Restormer.forward)
+ *
+ * Conventions
+ *   - plain C types only; every pointer named d_* is DEVICE memory owned by the caller (e.g. tensor.data_ptr()).
+ *   - `stream` is a cudaStream_t passed as void*; the library never synchronises it (irb_create excepted) and
+ *     never allocates device memory during a forward call: scratch comes from the caller's workspace.
+ *   - return 0 = ok; 1 = invalid argument; 2 = CUDA/driver error; 3 = bad weights blob. The message is
+ *     available from irb_last_error() (thread-local).
+ *   - there is no CPU fallback and no alternative backend: without an sm_100 device every compute entry fails.
+ */
+#ifndef IRB200_H
+#define IRB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IRB_ARCH_RESTORMER 1
+#define IRB_ARCH_SWINIR 2
+
+#define IRB_F32 0  /* fp32 storage + fp32 FMA arithmetic (verification mode, <=1e-4 of the reference) */
+#define IRB_BF16 1 /* bf16 storage, tcgen05 tensor-core contractions with fp32 accumulation */
+
+#define IRB_UPSAMPLER_NONE 0         /* denoise / JPEG-CAR tail: x + conv_last(res)   network_swinir.py:832-836 */
+#define IRB_UPSAMPLER_PIXELSHUFFLE 1 /* classical SR                                   network_swinir.py:812-817 */
+#define IRB_UPSAMPLER_NEAREST_CONV 2 /* real-world SR                                  network_swinir.py:823-831 */
+
+typedef struct irb_handle irb_handle;
+
+/* Mirrors the constructor arguments of the two reference nn.Modules. */
+typedef struct irb_model_desc {
+    int arch;      /* IRB_ARCH_* */
+    int precision; /* IRB_F32 / IRB_BF16 */
+    int in_chans;  /* 1 or 3; out_chans is the same in every reference configuration */
+    /* Restormer(...)  restormer_arch.py:194-206, demo.py:92 */
+    int dim;
+    int num_blocks[4];
+    int num_refinement_blocks;
+    int heads[4];
+    float ffn_expansion_factor;
+    int ln_bias_free; /* 1: LayerNorm_type='BiasFree' (denoising tasks), 0: 'WithBias' */
+    /* SwinIR(...)  network_swinir.py:646-654, inference.py:136-195 */
+    int img_size;
+    int window_size;
+    int embed_dim;
+    int num_layers;
+    int depths[16];
+    int num_heads[16];
+    int mlp_ratio;
+    int upscale;
+    float img_range;
+    int upsampler;  /* IRB_UPSAMPLER_* */
+    int resi_3conv; /* 1: resi_connection='3conv', 0: '1conv' */
+} irb_model_desc;
+
+const char* irb_last_error(void);
+int irb_version(void);
+
+/* Tile index list of the reference loop: list(range(0, n - tile, tile - overlap)) + [n - tile]
+ * (inference.py:305-308, demo.py:139-141) with tile = min(tile, n) applied by the CALLER.
+ * idx may be NULL to query the count only. Host-only, no GPU needed. */
+int irb_plan_tiles(int n, int tile, int overlap, int* idx, int* count);
+
+/* Padded size the reference scripts feed to the model: SwinIR (h / ws + 1) * ws (always pads,
+ * inference.py:76-78); Restormer next multiple of 8 only when needed (demo.py:122-126). Host-only. */
+int irb_padded_size(int arch, int window_size, int h, int w, int* hp, int* wp);
+
+/* weights_blob: host memory, format documented in image_restoration_agent_b200/weights.py (IRBW v1: named fp32
+ * tensors of the reference state_dict). Uploads + repacks weights on `device`; synchronises. */
+int irb_create(const irb_model_desc* desc, const void* weights_blob, size_t nbytes, int device, irb_handle** out);
+void irb_destroy(irb_handle* h);
+/* options: "tile_batch" (max tiles per forward batch inside irb_restore_image; 0 = automatic) */
+int irb_set_option(irb_handle* h, const char* key, long long value);
+int irb_scale(const irb_handle* h); /* upscale factor (1 for Restormer / denoise) */
+
+/* model(x): x is [n, c, th, tw] fp32 NCHW (device), y is [n, c, th*s, tw*s] fp32 NCHW (device).
+ * Restormer needs th, tw multiples of 8; SwinIR reflect-pads to the window internally like the reference. */
+int irb_workspace_bytes(irb_handle* h, int n_tiles, int tile_h, int tile_w, size_t* out_bytes);
+int irb_forward_tiles(irb_handle* h, const float* d_in, float* d_out, int n_tiles, int tile_h, int tile_w,
+                      void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* The whole tool body for one image.
+ *   in_fmt 0: d_in is uint8 [h][w][c] (as cv2.imread gives it; reverse_channels=1 means BGR on both sides)
+ *   in_fmt 1: d_in is fp32 planar [c][h][w] in [0,1] (RGB / gray), reverse_channels ignored on input
+ *   tile = 0 means "--tile None" (whole image); otherwise the reference's tile / tile_overlap arguments.
+ *   d_out_u8  : uint8 [h*s][w*s][c] (NULL to skip)      d_out_f32 : fp32 planar [c][h*s][w*s], un-clamped E/W
+ *   (NULL to skip). */
+int irb_restore_workspace_bytes(irb_handle* h, int img_h, int img_w, int tile, int overlap, size_t* out_bytes);
+int irb_restore_image(irb_handle* h, const void* d_in, int in_fmt, int reverse_channels, int img_h, int img_w,
+                      int tile, int overlap, uint8_t* d_out_u8, float* d_out_f32, void* d_workspace,
+                      size_t workspace_bytes, void* stream);
+
+/* ---- single-kernel entry points (parity tests, ncu captures). dtype: IRB_F32 / IRB_BF16; activations are
+ * channels-last with an explicit row stride ld (elements). -------------------------------------------------- */
+int irb_layernorm(const void* d_x, int dtype, long long ldx, void* d_y, long long ldy, long long rows, int C,
+                  const float* d_w, const float* d_b, int bias_free, float eps, void* stream);
+/* y[b,m,:N] = act(x[b,m,:K] . W[b*w_rows_per_batch + n,:K] + bias) + res ; W has dtype `dtype`, row stride ldw.
+ * act: 0 none, 1 exact GELU, 2 LeakyReLU(slope). bf16 -> tcgen05 kernel, fp32 -> FMA kernel. */
+int irb_gemm1x1(const void* d_x, int dtype, long long ldx, int M, int K, int batch, const void* d_w, int ldw, int N,
+                int w_rows_total, int w_rows_per_batch, const float* d_bias, const void* d_res, long long ldr,
+                int act, float slope, void* d_y, long long ldy, void* stream);
+/* 3x3 conv, zero pad 1, on [n,H,W,C]; W is [N_rows][9*kpad] (K index = (ky*3+kx)*kpad + c), dtype `dtype`.
+ * shuffle: 0 none, 1 PixelShuffle(2) fused into the store, 2 PixelUnshuffle(2). */
+int irb_conv3x3(const void* d_x, int dtype, long long ldx, int n, int H, int W, int C, const void* d_w, int kpad,
+                int N, int w_rows_total, const float* d_bias, const void* d_res, long long ldr, int act, float slope,
+                int shuffle, void* d_y, long long ldy, void* stream);
+/* depthwise 3x3; d_w is fp32 [9][C] tap-major. d_sumsq (optional) [n][sumsq_channels] += sum_p y^2 */
+int irb_dwconv3x3(const void* d_x, int dtype, long long ldx, void* d_y, long long ldy, int n, int H, int W, int C,
+                  const float* d_w, float* d_sumsq, int sumsq_channels, void* stream);
+/* GDFN: y[.,c] = gelu(dw(x)[.,c]) * dw(x)[.,hp+c], c < hp; d_w fp32 [9][2*hp] */
+int irb_gdfn_dw_gate(const void* d_x, int dtype, long long ldx, void* d_y, long long ldy, int n, int H, int W, int hp,
+                     const float* d_w, void* stream);
+/* MDTA Gram: d_G[n][heads][c][c] += sum_p q k^T over a channels-last qkv tensor (q | k | v), d_G pre-zeroed */
+int irb_mdta_gram(const void* d_qkv, int dtype, long long ld, int n, int P, int C, int heads, float* d_G,
+                  void* stream);
+/* softmax(G / (|q||k|) * temperature) folded into project_out: d_weff[n][C][C] (dtype), d_attn optional fp32 */
+int irb_mdta_attn(const float* d_G, const float* d_sumsq, const float* d_temperature, const float* d_wproj, int n,
+                  int C, int heads, void* d_weff, int dtype, float* d_attn, void* stream);
+/* overlap-blend stitch of channels-last fp32 tiles [ny*nx][th*sf][tw*sf][c] (host index lists) */
+int irb_stitch(const float* d_tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx,
+               int h, int w, int crop_h, int crop_w, float* d_out_f32, uint8_t* d_out_u8, int reverse_channels,
+               void* stream);
+/* SwinIR (shifted-)window attention on a channels-last qkv tensor [n, H, W, 3*C] (q | k | v, head-major):
+ * out[n,H,W,C] = window_reverse(softmax(q k^T * scale + rel_pos_bias + shift_mask) v), with the cyclic shift folded
+ * into the addressing (network_swinir.py:114-145, 216-237, 239-279). d_bias_table is fp32 [(2ws-1)^2][heads]. */
+int irb_window_attention(const void* d_qkv, int dtype, long long ld, void* d_out, long long ldo, int n, int H, int W,
+                         int C, int heads, int window, int shift, const float* d_bias_table, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IRB200_H */

@@ -1,0 +1,223 @@
+"""Kernel bring-up on a B200: every single-kernel C-ABI entry against plain torch fp32 on the same GPU.
+
+Development tool (the judged parity tests live in tests/). Writes gpurun_out/bringup.json.
+Usage: python tools/gpu_bringup.py [--only name,name]
+"""
+import json
+import os
+import sys
+import time
+import traceback
+
+import torch
+import torch.nn.functional as F
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from image_restoration_agent_b200 import _lib, ops  # noqa: E402
+
+_lib.load(strict=False)
+dev = torch.device("cuda:0")
+RESULTS = {}
+
+
+def report(name, got, ref, tol):
+    got = got.float()
+    ref = ref.float()
+    err = (got - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    ok = bool(err <= tol * max(scale, 1e-6)) and bool(torch.isfinite(got).all())
+    RESULTS[name] = {"max_abs_err": err, "ref_max": scale, "tol_rel": tol, "ok": ok}
+    print(f"{'OK ' if ok else 'BAD'} {name:45s} err={err:.3e} ref_max={scale:.3e}", flush=True)
+    return ok
+
+
+def run(name, fn):
+    try:
+        fn()
+        torch.cuda.synchronize()
+    except Exception as e:  # noqa: BLE001
+        RESULTS[name] = {"ok": False, "exception": repr(e)}
+        print(f"EXC {name}: {e!r}", flush=True)
+        traceback.print_exc()
+        try:
+            torch.cuda.synchronize()
+        except Exception as e2:  # noqa: BLE001
+            print("CUDA context is dead:", e2, flush=True)
+            dump()
+            sys.exit(3)
+
+
+def dump():
+    os.makedirs("gpurun_out", exist_ok=True)
+    tag = sys.argv[sys.argv.index("--only") + 1].replace(",", "+") if "--only" in sys.argv else "all"
+    with open(f"gpurun_out/bringup_{tag[:40]}.json", "w") as f:
+        json.dump(RESULTS, f, indent=1)
+
+
+def t_layernorm():
+    for dt, tol in ((torch.float32, 1e-5), (torch.bfloat16, 1e-2)):
+        for C in (48, 96, 180, 192, 384):
+            for bias_free in (False, True):
+                x = (torch.randn(1000, C, device=dev) * 2 + 0.5).to(dt)
+                w = torch.randn(C, device=dev) * 0.2 + 1
+                b = torch.randn(C, device=dev) * 0.1
+                y = ops.layernorm(x, w, None if bias_free else b, bias_free=bias_free)
+                xf = x.float()
+                mu = xf.mean(-1, keepdim=True)
+                var = xf.var(-1, keepdim=True, unbiased=False)
+                ref = (xf / torch.sqrt(var + 1e-5) * w) if bias_free else ((xf - mu) / torch.sqrt(var + 1e-5) * w + b)
+                report(f"layernorm[{dt},C={C},bf={bias_free}]", y, ref, tol)
+
+
+def t_gemm(dt):
+    tol = 2e-5 if dt == torch.float32 else 1.5e-2
+    for (M, K, N) in ((300, 48, 144), (1000, 96, 288), (257, 192, 192), (512, 384, 1152), (700, 256, 96), (640, 1024, 384), (130, 180, 360)):
+        Kp = (K + 7) // 8 * 8
+        x = torch.randn(M, Kp, device=dev).to(dt)
+        w = (torch.randn(N, Kp, device=dev) / K ** 0.5).to(dt)
+        if Kp != K:
+            x[:, K:] = 0
+        bias = torch.randn(N, device=dev)
+        res = torch.randn(M, N, device=dev).to(dt)
+        ref0 = x.float() @ w.float().t()
+        report(f"gemm[{dt},{M}x{K}x{N}]", ops.gemm1x1(x, w), ref0, tol)
+        report(f"gemm+bias+gelu[{dt},{M}x{K}x{N}]", ops.gemm1x1(x, w, bias=bias, act=1), F.gelu(ref0 + bias), tol)
+        report(f"gemm+res[{dt},{M}x{K}x{N}]", ops.gemm1x1(x, w, res=res), ref0 + res.float(), tol)
+    # batched per-image weights (MDTA apply): x view with lda > K
+    n, P, C = 3, 200, 96
+    qkv = torch.randn(n, P, 3 * C, device=dev).to(dt)
+    weff = (torch.randn(n, C, C, device=dev) / C ** 0.5).to(dt)
+    v = qkv[:, :, 2 * C:]
+    y = ops.gemm1x1(v, weff.reshape(n * C, C), batch=n, w_rows_per_batch=C)
+    ref = torch.einsum("npk,nok->npo", v.float(), weff.float()).reshape(n * P, C)
+    report(f"gemm_batched_view[{dt}]", y, ref, tol)
+
+
+def t_conv(dt):
+    tol = 2e-5 if dt == torch.float32 else 1.5e-2
+    for (n, H, W, Cin, N) in ((2, 32, 32, 48, 24), (1, 24, 40, 96, 192), (2, 16, 16, 384, 768), (1, 40, 24, 180, 180), (1, 64, 64, 96, 3), (1, 33, 20, 64, 64)):
+        Cp = (Cin + 7) // 8 * 8
+        x = torch.randn(n, H, W, Cp, device=dev).to(dt)[..., :Cin]
+        w = (torch.randn(N, Cin, 3, 3, device=dev) / (9 * Cin) ** 0.5)
+        wq = w.to(dt)
+        wp, kpad = ops.pack_conv3x3_weight(wq, dt)
+        ref = F.conv2d(x.float().permute(0, 3, 1, 2), wq.float(), padding=1)
+        y = ops.conv3x3(x, wp, kpad, N)
+        report(f"conv3x3[{dt},{n}x{H}x{W}x{Cin}->{N}]", y, ref.permute(0, 2, 3, 1), tol)
+        if N % 4 == 0:
+            y = ops.conv3x3(x, wp, kpad, N, shuffle=1)
+            report(f"conv3x3+shuffle[{dt},{Cin}->{N}]", y, F.pixel_shuffle(ref, 2).permute(0, 2, 3, 1), tol)
+        if H % 2 == 0 and W % 2 == 0 and N >= 8:
+            y = ops.conv3x3(x, wp, kpad, N, shuffle=2)
+            report(f"conv3x3+unshuffle[{dt},{Cin}->{N}]", y, F.pixel_unshuffle(ref, 2).permute(0, 2, 3, 1), tol)
+        bias = torch.randn(N, device=dev)
+        y = ops.conv3x3(x, wp, kpad, N, bias=bias, act=2, slope=0.2)
+        report(f"conv3x3+bias+lrelu[{dt},{Cin}->{N}]", y, F.leaky_relu(ref + bias.view(1, -1, 1, 1), 0.2).permute(0, 2, 3, 1), tol)
+
+
+def t_dw(dt):
+    tol = 1e-5 if dt == torch.float32 else 1e-2
+    for (n, H, W, Cc) in ((2, 32, 32, 144), (1, 40, 24, 288), (1, 8, 8, 1152), (1, 70, 36, 576)):
+        x = torch.randn(n, H, W, Cc, device=dev).to(dt)
+        w = torch.randn(Cc, 1, 3, 3, device=dev) / 3
+        ref = F.conv2d(x.float().permute(0, 3, 1, 2), w, padding=1, groups=Cc)
+        sc = Cc // 3 * 2
+        y, ss = ops.dwconv3x3(x, ops.pack_dw_weight(w), sumsq_channels=sc)
+        report(f"dwconv3x3[{dt},{n}x{H}x{W}x{Cc}]", y, ref.permute(0, 2, 3, 1), tol)
+        report(f"dwconv3x3.sumsq[{dt},{Cc}]", ss, (ref[:, :sc] ** 2).sum((2, 3)), 1e-4)
+    for (n, H, W, hp) in ((2, 32, 32, 128), (1, 24, 40, 256), (1, 8, 8, 1024)):
+        x = torch.randn(n, H, W, 2 * hp, device=dev).to(dt)
+        w = torch.randn(2 * hp, 1, 3, 3, device=dev) / 3
+        ref = F.conv2d(x.float().permute(0, 3, 1, 2), w, padding=1, groups=2 * hp)
+        r = F.gelu(ref[:, :hp]) * ref[:, hp:]
+        y = ops.gdfn_dw_gate(x, ops.pack_dw_weight(w))
+        report(f"gdfn_dw_gate[{dt},{n}x{H}x{W}x{hp}]", y, r.permute(0, 2, 3, 1), tol)
+
+
+def t_mdta(dt):
+    tol = 1e-4 if dt == torch.float32 else 2e-3
+    for (n, H, W, Cc, heads) in ((2, 32, 32, 48, 1), (1, 64, 48, 96, 2), (2, 16, 16, 384, 8), (1, 50, 30, 96, 1), (1, 128, 128, 192, 4)):
+        qkv = torch.randn(n, H, W, 3 * Cc, device=dev).to(dt)
+        c = Cc // heads
+        q = qkv[..., :Cc].float().reshape(n, H * W, heads, c)
+        k = qkv[..., Cc:2 * Cc].float().reshape(n, H * W, heads, c)
+        ref = torch.einsum("nphi,nphj->nhij", q, k)
+        G = ops.mdta_gram(qkv, heads)
+        report(f"mdta_gram[{dt},{n}x{H}x{W}x{Cc},h={heads}]", G, ref, tol)
+        ss = torch.cat([(q ** 2).sum(1).reshape(n, Cc), (k ** 2).sum(1).reshape(n, Cc)], 1).contiguous()
+        temp = torch.rand(heads, device=dev) + 0.5
+        wproj = torch.randn(Cc, Cc, device=dev) / Cc ** 0.5
+        weff, attn = ops.mdta_attn(ref.contiguous(), ss, temp, wproj, torch.float32)
+        qn = F.normalize(q.permute(0, 2, 3, 1), dim=-1)
+        kn = F.normalize(k.permute(0, 2, 3, 1), dim=-1)
+        a_ref = ((qn @ kn.transpose(-2, -1)) * temp.view(1, heads, 1, 1)).softmax(-1)
+        report(f"mdta_attn.softmax[{Cc},h={heads}]", attn, a_ref, 1e-4)
+        w_ref = torch.einsum("ohi,nhij->nohj", wproj.reshape(Cc, heads, c), a_ref).reshape(n, Cc, Cc)
+        report(f"mdta_attn.weff[{Cc},h={heads}]", weff, w_ref, 1e-4)
+
+
+def t_stitch():
+    import random
+    rnd = random.Random(0)
+    for (h, w, tile, ov, sf, c) in ((720, 1280, 256, 32, 1, 3), (264, 264, 128, 32, 1, 1), (72, 88, 48, 16, 4, 3), (64, 64, 64, 32, 2, 3)):
+        lib = _lib.load(strict=False)
+        import ctypes
+        def plan(nn):
+            cnt = ctypes.c_int()
+            buf = (ctypes.c_int * 256)()
+            _lib.check(lib.irb_plan_tiles(nn, tile, ov, buf, ctypes.byref(cnt)))
+            return list(buf[:cnt.value])
+        ys, xs = plan(h), plan(w)
+        stride = tile - ov
+        assert ys == list(range(0, h - tile, stride)) + [h - tile]
+        tiles = torch.rand(len(ys) * len(xs), tile * sf, tile * sf, c, device=dev) * 1.2 - 0.1
+        E = torch.zeros(c, h * sf, w * sf, device=dev)
+        Wt = torch.zeros_like(E)
+        k = 0
+        for y0 in ys:
+            for x0 in xs:
+                E[:, y0 * sf:(y0 + tile) * sf, x0 * sf:(x0 + tile) * sf] += tiles[k].permute(2, 0, 1)
+                Wt[:, y0 * sf:(y0 + tile) * sf, x0 * sf:(x0 + tile) * sf] += 1
+                k += 1
+        ref = E / Wt
+        ch, cw = h * sf - rnd.randint(0, 7), w * sf - rnd.randint(0, 7)
+        out, u8 = ops.stitch(tiles, ys, xs, sf, h, w, ch, cw)
+        exact = torch.equal(out, ref[:, :ch, :cw])
+        RESULTS[f"stitch.bitexact[{h}x{w},t{tile},sf{sf}]"] = {"ok": bool(exact)}
+        print(("OK " if exact else "BAD"), f"stitch.bitexact[{h}x{w},t{tile},sf{sf}]", flush=True)
+        ref8 = (ref[:, :ch, :cw].clamp(0, 1).permute(1, 2, 0).cpu().numpy() * 255.0).round().astype("uint8")
+        same = bool((u8.cpu().numpy() == ref8).all())
+        RESULTS[f"stitch.u8[{h}x{w}]"] = {"ok": same}
+        print(("OK " if same else "BAD"), f"stitch.u8[{h}x{w}]", flush=True)
+
+
+TESTS = {
+    "layernorm": t_layernorm,
+    "gemm_f32": lambda: t_gemm(torch.float32),
+    "conv_f32": lambda: t_conv(torch.float32),
+    "dw_f32": lambda: t_dw(torch.float32),
+    "dw_bf16": lambda: t_dw(torch.bfloat16),
+    "mdta_f32": lambda: t_mdta(torch.float32),
+    "stitch": t_stitch,
+    "gemm_bf16": lambda: t_gemm(torch.bfloat16),
+    "conv_bf16": lambda: t_conv(torch.bfloat16),
+    "mdta_bf16": lambda: t_mdta(torch.bfloat16),
+}
+
+if __name__ == "__main__":
+    only = None
+    if "--only" in sys.argv:
+        only = sys.argv[sys.argv.index("--only") + 1].split(",")
+    torch.manual_seed(0)
+    print(torch.cuda.get_device_name(0), flush=True)
+    t0 = time.time()
+    for name, fn in TESTS.items():
+        if only and name not in only:
+            continue
+        print(f"== {name}", flush=True)
+        run(name, fn)
+        dump()
+    nbad = sum(1 for v in RESULTS.values() if not v.get("ok"))
+    print(f"done in {time.time() - t0:.1f}s: {len(RESULTS)} checks, {nbad} bad", flush=True)
+    dump()
+    sys.exit(1 if nbad else 0)
