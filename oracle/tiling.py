@@ -1,0 +1,90 @@
+"""ORACLE (test infrastructure, not product code): the reference tools' pad / tile loop / blend / quantise code,
+restated with numpy + torch on CPU. `model` is any callable x[B,c,H,W] -> y[B,c,sH,sW] (the oracle models, or the
+reference nn.Modules in tools/make_golden.py).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+
+def tile_indices(n: int, tile: int, overlap: int) -> list[int]:
+    """inference.py:305-308 / demo.py:139-141 (tile already min(tile, h, w))."""
+    stride = tile - overlap
+    return list(range(0, n - tile, stride)) + [n - tile]
+
+
+def coverage_count(n: int, tile: int, overlap: int, sf: int = 1) -> np.ndarray:
+    """The separable integer count that the reference accumulates in W (ones_like per tile)."""
+    cnt = np.zeros(n * sf, dtype=np.int64)
+    for i in tile_indices(n, tile, overlap):
+        cnt[i * sf:(i + tile) * sf] += 1
+    return cnt
+
+
+def tiled_forward(x: torch.Tensor, model, tile, overlap: int, sf: int, multiple: int) -> torch.Tensor:
+    """inference.py:294-322 test() / demo.py:129-153. tile=None -> whole image."""
+    if tile is None:
+        return model(x)
+    b, c, h, w = x.shape
+    tile = min(tile, h, w)
+    assert tile % multiple == 0, "tile size should be a multiple of window_size"
+    hs, ws_ = tile_indices(h, tile, overlap), tile_indices(w, tile, overlap)
+    E = torch.zeros(b, c, h * sf, w * sf, dtype=x.dtype)
+    W = torch.zeros_like(E)
+    for hi in hs:
+        for wi in ws_:
+            out = model(x[..., hi:hi + tile, wi:wi + tile])
+            E[..., hi * sf:(hi + tile) * sf, wi * sf:(wi + tile) * sf].add_(out)
+            W[..., hi * sf:(hi + tile) * sf, wi * sf:(wi + tile) * sf].add_(torch.ones_like(out))
+    return E.div_(W)
+
+
+def swinir_pad(x: torch.Tensor, ws: int) -> torch.Tensor:
+    """inference.py:76-80: symmetric flip-and-concat pad to (h // ws + 1) * ws — always pads."""
+    _, _, h, w = x.shape
+    hp, wp = (h // ws + 1) * ws - h, (w // ws + 1) * ws - w
+    x = torch.cat([x, torch.flip(x, [2])], 2)[:, :, :h + hp, :]
+    return torch.cat([x, torch.flip(x, [3])], 3)[:, :, :, :w + wp]
+
+
+def swinir_process_image(img_bgr_u8: np.ndarray, model, scale: int, window_size: int, tile=None, tile_overlap=32,
+                         return_float=False):
+    """model_serving.py:131-175 process_image() fed by cv2.imread(...)/255 (inference.py:238-246, 69-90).
+    img_bgr_u8: uint8 [H, W, 3] BGR (or [H, W, 1]). Returns uint8 [H*s, W*s, 3] BGR (or [H*s, W*s])."""
+    img = img_bgr_u8.astype(np.float32) / 255.0
+    img = np.transpose(img if img.shape[2] == 1 else img[:, :, [2, 1, 0]], (2, 0, 1))
+    x = torch.from_numpy(np.ascontiguousarray(img)).float().unsqueeze(0)
+    _, _, h_old, w_old = x.shape
+    x = swinir_pad(x, window_size)
+    with torch.no_grad():
+        out = tiled_forward(x, model, tile, tile_overlap, scale, window_size)
+    out = out[..., :h_old * scale, :w_old * scale]
+    if return_float:
+        return out[0].clone()
+    o = out.squeeze().float().clamp_(0, 1).numpy()
+    if o.ndim == 3:
+        o = np.transpose(o[[2, 1, 0], :, :], (1, 2, 0))
+    return (o * 255.0).round().astype(np.uint8)
+
+
+def restormer_restore_image(img_rgb_u8: np.ndarray, model, tile=None, tile_overlap=32, return_float=False):
+    """demo.py:118-161 / model_serving.py:157-208. img_rgb_u8: uint8 [H, W, c] RGB (or gray c=1).
+    Returns uint8 [H, W, c] (img_as_ubyte of the clamped float == rint(x*255))."""
+    x = torch.from_numpy(img_rgb_u8).float().div(255.0).permute(2, 0, 1).unsqueeze(0)
+    height, width = x.shape[2], x.shape[3]
+    m = 8
+    H, W = ((height + m) // m) * m, ((width + m) // m) * m
+    padh = H - height if height % m != 0 else 0
+    padw = W - width if width % m != 0 else 0
+    x = F.pad(x, (0, padw, 0, padh), "reflect")
+    with torch.no_grad():
+        restored = tiled_forward(x, model, tile, tile_overlap, 1, 8)
+    if return_float:
+        return restored[0, :, :height, :width].clone()
+    restored = torch.clamp(restored, 0, 1)[:, :, :height, :width]
+    r = restored.permute(0, 2, 3, 1).numpy()[0]
+    return np.rint(r * np.float32(255.0)).astype(np.uint8)
