@@ -1,0 +1,354 @@
+// Weights blob parsing, weight packing, Model plumbing, and the model-level C ABI (irb_create ... irb_restore_image).
+#include "model.h"
+#include <string.h>
+
+namespace irb {
+
+int Blob::parse(const void* p, size_t nbytes) {
+    const unsigned char* b = reinterpret_cast<const unsigned char*>(p);
+    if (!p || nbytes < 16 || memcmp(b, "IRBW", 4) != 0) {
+        set_error("weights blob: bad magic (expected IRBW)");
+        return 3;
+    }
+    uint32_t ver, n;
+    memcpy(&ver, b + 4, 4);
+    memcpy(&n, b + 8, 4);
+    if (ver != 1) {
+        set_error("weights blob: unsupported version");
+        return 3;
+    }
+    const size_t entry = 96 + 4 + 16 + 8 + 8;
+    if (16 + size_t(n) * entry > nbytes) {
+        set_error("weights blob: truncated table");
+        return 3;
+    }
+    for (uint32_t i = 0; i < n; ++i) {
+        const unsigned char* e = b + 16 + size_t(i) * entry;
+        char name[97];
+        memcpy(name, e, 96);
+        name[96] = 0;
+        uint32_t ndim, dims[4];
+        uint64_t off, numel;
+        memcpy(&ndim, e + 96, 4);
+        memcpy(dims, e + 100, 16);
+        memcpy(&off, e + 116, 8);
+        memcpy(&numel, e + 124, 8);
+        if (ndim > 4 || off % 4 != 0 || off + numel * 4 > nbytes) {
+            set_error(std::string("weights blob: bad entry ") + name);
+            return 3;
+        }
+        BlobTensor t{};
+        t.data = reinterpret_cast<const float*>(b + off);
+        t.ndim = int(ndim);
+        long long prod = 1;
+        for (int k = 0; k < 4; ++k) {
+            t.dims[k] = k < int(ndim) ? dims[k] : 1;
+            prod *= t.dims[k];
+        }
+        t.numel = (long long)numel;
+        if (prod != t.numel) {
+            set_error(std::string("weights blob: numel mismatch for ") + name);
+            return 3;
+        }
+        this->t[name] = t;
+    }
+    return 0;
+}
+
+int Blob::get(const std::string& name, BlobTensor& out, long long d0, long long d1, long long d2, long long d3) const {
+    auto it = t.find(name);
+    if (it == t.end()) {
+        set_error("weights blob: missing tensor " + name);
+        return 3;
+    }
+    // unspecified trailing dims must be 1 (dims beyond ndim are stored as 1)
+    const long long want[4] = {d0, d1 < 0 ? 1 : d1, d2 < 0 ? 1 : d2, d3 < 0 ? 1 : d3};
+    bool ok = true;
+    for (int k = 0; k < 4; ++k)
+        if (it->second.dims[k] != want[k]) ok = false;
+    if (!ok) {
+        char buf[256];
+        snprintf(buf, sizeof buf, "weights blob: tensor %s has shape [%lld,%lld,%lld,%lld], expected [%lld,%lld,%lld,%lld]",
+                 name.c_str(), it->second.dims[0], it->second.dims[1], it->second.dims[2], it->second.dims[3], d0, d1, d2, d3);
+        set_error(buf);
+        return 3;
+    }
+    out = it->second;
+    return 0;
+}
+
+Model::~Model() {
+    for (void* p : dev_allocs) cudaFree(p);
+}
+int Model::dev_alloc(size_t bytes, void** out) {
+    void* p = nullptr;
+    IRB_CHECK_CUDA(cudaMalloc(&p, bytes < 16 ? 16 : bytes));
+    dev_allocs.push_back(p);
+    *out = p;
+    return 0;
+}
+int Model::upload_f32(const float* host, size_t n, float** out) {
+    void* p;
+    IRB_TRY(dev_alloc(n * 4, &p));
+    IRB_CHECK_CUDA(cudaMemcpy(p, host, n * 4, cudaMemcpyHostToDevice));
+    *out = reinterpret_cast<float*>(p);
+    return 0;
+}
+int Model::upload_act(const float* host, size_t n, void** out) {
+    if (dt == DT_F32) {
+        float* f;
+        IRB_TRY(upload_f32(host, n, &f));
+        *out = f;
+        return 0;
+    }
+    std::vector<bf16> tmp(n);
+    for (size_t i = 0; i < n; ++i) tmp[i] = __float2bfloat16_rn(host[i]);
+    void* p;
+    IRB_TRY(dev_alloc(n * 2, &p));
+    IRB_CHECK_CUDA(cudaMemcpy(p, tmp.data(), n * 2, cudaMemcpyHostToDevice));
+    *out = p;
+    return 0;
+}
+
+std::vector<float> pack_conv3x3(const BlobTensor& w, int& kpad, int& npad) {
+    const int N = int(w.dims[0]), C = int(w.dims[1]);
+    kpad = (C + 63) / 64 * 64;
+    npad = (N + 15) / 16 * 16;
+    std::vector<float> o(size_t(npad) * 9 * kpad, 0.f);
+    for (int n = 0; n < N; ++n)
+        for (int c = 0; c < C; ++c)
+            for (int t = 0; t < 9; ++t) o[(size_t(n) * 9 + t) * kpad + c] = w.data[(size_t(n) * C + c) * 9 + t];
+    return o;
+}
+std::vector<float> pack_linear(const float* w, int N, int K, int& kpad, int& npad) {
+    kpad = (K + 7) / 8 * 8;
+    npad = (N + 15) / 16 * 16;
+    std::vector<float> o(size_t(npad) * kpad, 0.f);
+    for (int n = 0; n < N; ++n)
+        for (int k = 0; k < K; ++k) o[size_t(n) * kpad + k] = w[size_t(n) * K + k];
+    return o;
+}
+std::vector<float> pack_dw(const BlobTensor& w) {
+    const int C = int(w.dims[0]);
+    std::vector<float> o(size_t(9) * C);
+    for (int c = 0; c < C; ++c)
+        for (int t = 0; t < 9; ++t) o[size_t(t) * C + c] = w.data[size_t(c) * 9 + t];
+    return o;
+}
+
+__global__ void permute_f32_kernel(const float* __restrict__ in, float* __restrict__ out, int n, int c, long long hw,
+                                   int to_nhwc) {
+    const long long total = (long long)n * c * hw;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        // i indexes the OUTPUT
+        if (to_nhwc) {
+            const int ch = int(i % c);
+            const long long p = (i / c) % hw;
+            const long long b = i / (c * hw);
+            out[i] = in[(b * c + ch) * hw + p];
+        } else {
+            const long long p = i % hw;
+            const int ch = int((i / hw) % c);
+            const long long b = i / (hw * c);
+            out[i] = in[(b * hw + p) * c + ch];
+        }
+    }
+}
+static int permute_launch(const float* in, float* out, int n, int c, int h, int w, int to_nhwc, cudaStream_t s) {
+    const long long total = (long long)n * c * h * w;
+    const int blocks = int(ceil_div_ll(total, 256) > 148 * 16 ? 148 * 16 : ceil_div_ll(total, 256));
+    permute_f32_kernel<<<blocks, 256, 0, s>>>(in, out, n, c, (long long)h * w, to_nhwc);
+    IRB_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+int nchw_to_nhwc_f32(const float* in, float* out, int n, int c, int h, int w, cudaStream_t s) {
+    return permute_launch(in, out, n, c, h, w, 1, s);
+}
+int nhwc_to_nchw_f32(const float* in, float* out, int n, int c, int h, int w, cudaStream_t s) {
+    return permute_launch(in, out, n, c, h, w, 0, s);
+}
+
+}  // namespace irb
+
+using namespace irb;
+
+// ---------------------------------------------------------------------------------------------------------
+static int pick_batch(Model* m, int nt, int th, int tw) {
+    if (m->tile_batch > 0) return int(m->tile_batch < nt ? m->tile_batch : nt);
+    int nb = nt;
+    const size_t cap = size_t(40) << 30;
+    while (nb > 1 && m->forward_workspace(nb, th, tw) > cap) nb = (nb + 1) / 2;
+    return nb;
+}
+
+struct RestorePlan {
+    int hp, wp, th, tw, ny, nx, nb, sf, c;
+    int ys[128], xs[128];
+    // workspace pointers
+    float *padded, *tiles_in, *tiles_out;
+    void* model_ws;
+    size_t model_ws_bytes, total;
+};
+
+static int make_plan(Model* m, int img_h, int img_w, int tile, int overlap, void* ws, RestorePlan& P) {
+    IRB_REQUIRE(img_h > 0 && img_w > 0, "restore: empty image");
+    IRB_TRY(irb_padded_size(m->desc.arch, m->desc.window_size, img_h, img_w, &P.hp, &P.wp));
+    P.sf = m->scale;
+    P.c = m->cin;
+    if (tile <= 0) {
+        P.th = P.hp;
+        P.tw = P.wp;
+        P.ny = P.nx = 1;
+        P.ys[0] = P.xs[0] = 0;
+    } else {
+        int t = tile < P.hp ? tile : P.hp;
+        t = t < P.wp ? t : P.wp;
+        // inference.py:302 / demo.py:136
+        IRB_REQUIRE(t % m->tile_multiple() == 0, "tile size should be a multiple of window_size (SwinIR) / 8 (Restormer)");
+        IRB_REQUIRE(overlap >= 0 && overlap < t, "tile_overlap must be smaller than the tile");
+        P.th = P.tw = t;
+        IRB_REQUIRE((P.hp - t) / (t - overlap) + 2 <= 128 && (P.wp - t) / (t - overlap) + 2 <= 128,
+                    "too many tiles per axis (max 128)");
+        IRB_TRY(irb_plan_tiles(P.hp, t, overlap, P.ys, &P.ny));
+        IRB_TRY(irb_plan_tiles(P.wp, t, overlap, P.xs, &P.nx));
+    }
+    const int nt = P.ny * P.nx;
+    P.nb = pick_batch(m, nt, P.th, P.tw);
+    Bump b(ws);
+    P.padded = b.take<float>(size_t(P.c) * P.hp * P.wp * 4);
+    P.tiles_in = b.take<float>(size_t(nt) * P.th * P.tw * P.c * 4);
+    P.tiles_out = b.take<float>(size_t(nt) * P.th * P.tw * P.sf * P.sf * P.c * 4);
+    P.model_ws_bytes = m->forward_workspace(P.nb, P.th, P.tw);
+    P.model_ws = b.take<void>(P.model_ws_bytes);
+    P.total = b.off + 256;
+    return 0;
+}
+
+extern "C" {
+
+int irb_create(const irb_model_desc* desc, const void* weights_blob, size_t nbytes, int device, irb_handle** out) {
+    IRB_REQUIRE(desc && out, "irb_create: NULL argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        set_error("no CUDA device: irb200 has no CPU fallback");
+        return 2;
+    }
+    IRB_REQUIRE(device >= 0 && device < ndev, "irb_create: bad device index");
+    IRB_CHECK_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    IRB_CHECK_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        set_error("irb200 kernels are built for sm_100a only (device is sm_" + std::to_string(prop.major) +
+                  std::to_string(prop.minor) + ")");
+        return 2;
+    }
+    IRB_REQUIRE(desc->precision == IRB_F32 || desc->precision == IRB_BF16, "irb_create: bad precision");
+    Blob blob;
+    IRB_TRY(blob.parse(weights_blob, nbytes));
+    Model* m = nullptr;
+    int rc;
+    if (desc->arch == IRB_ARCH_RESTORMER)
+        rc = build_restormer(*desc, blob, device, &m);
+    else if (desc->arch == IRB_ARCH_SWINIR)
+        rc = build_swinir(*desc, blob, device, &m);
+    else {
+        set_error("irb_create: unknown arch");
+        return 1;
+    }
+    if (rc != 0) {
+        delete m;
+        return rc;
+    }
+    IRB_CHECK_CUDA(cudaDeviceSynchronize());
+    *out = new irb_handle{m};
+    return 0;
+}
+
+void irb_destroy(irb_handle* h) {
+    if (!h) return;
+    delete h->model;
+    delete h;
+}
+
+int irb_set_option(irb_handle* h, const char* key, long long value) {
+    IRB_REQUIRE(h && key, "irb_set_option: NULL argument");
+    if (strcmp(key, "tile_batch") == 0) {
+        IRB_REQUIRE(value >= 0, "tile_batch must be >= 0");
+        h->model->tile_batch = value;
+        return 0;
+    }
+    set_error(std::string("irb_set_option: unknown key ") + key);
+    return 1;
+}
+
+int irb_scale(const irb_handle* h) { return h ? h->model->scale : 0; }
+
+int irb_workspace_bytes(irb_handle* h, int n_tiles, int tile_h, int tile_w, size_t* out_bytes) {
+    IRB_REQUIRE(h && out_bytes && n_tiles > 0 && tile_h > 0 && tile_w > 0, "irb_workspace_bytes: bad arguments");
+    Model* m = h->model;
+    const size_t px = size_t(n_tiles) * tile_h * tile_w * m->cin * 4;
+    *out_bytes = m->forward_workspace(n_tiles, tile_h, tile_w) + px + px * m->scale * m->scale + 1024;
+    return 0;
+}
+
+int irb_forward_tiles(irb_handle* h, const float* d_in, float* d_out, int n_tiles, int tile_h, int tile_w,
+                      void* d_workspace, size_t workspace_bytes, void* stream) {
+    IRB_REQUIRE(h && d_in && d_out && d_workspace, "irb_forward_tiles: NULL argument");
+    Model* m = h->model;
+    size_t need;
+    IRB_TRY(irb_workspace_bytes(h, n_tiles, tile_h, tile_w, &need));
+    IRB_REQUIRE(workspace_bytes >= need, "irb_forward_tiles: workspace too small");
+    cudaStream_t s = (cudaStream_t)stream;
+    Bump b(d_workspace);
+    const size_t px = size_t(n_tiles) * tile_h * tile_w * m->cin * 4;
+    float* in_l = b.take<float>(px);
+    float* out_l = b.take<float>(px * m->scale * m->scale);
+    const size_t mws = m->forward_workspace(n_tiles, tile_h, tile_w);
+    void* mw = b.take<void>(mws);
+    IRB_TRY(nchw_to_nhwc_f32(d_in, in_l, n_tiles, m->cin, tile_h, tile_w, s));
+    IRB_TRY(m->forward(in_l, out_l, n_tiles, tile_h, tile_w, mw, mws, s));
+    IRB_TRY(nhwc_to_nchw_f32(out_l, d_out, n_tiles, m->cin, tile_h * m->scale, tile_w * m->scale, s));
+    return 0;
+}
+
+int irb_restore_workspace_bytes(irb_handle* h, int img_h, int img_w, int tile, int overlap, size_t* out_bytes) {
+    IRB_REQUIRE(h && out_bytes, "irb_restore_workspace_bytes: NULL argument");
+    RestorePlan P;
+    IRB_TRY(make_plan(h->model, img_h, img_w, tile, overlap, nullptr, P));
+    *out_bytes = P.total;
+    return 0;
+}
+
+int irb_restore_image(irb_handle* h, const void* d_in, int in_fmt, int reverse_channels, int img_h, int img_w,
+                      int tile, int overlap, uint8_t* d_out_u8, float* d_out_f32, void* d_workspace,
+                      size_t workspace_bytes, void* stream) {
+    IRB_REQUIRE(h && d_in && d_workspace, "irb_restore_image: NULL argument");
+    IRB_REQUIRE(d_out_u8 || d_out_f32, "irb_restore_image: no output requested");
+    IRB_REQUIRE(in_fmt == 0 || in_fmt == 1, "irb_restore_image: in_fmt must be 0 (u8 HWC) or 1 (f32 planar)");
+    Model* m = h->model;
+    RestorePlan P;
+    IRB_TRY(make_plan(m, img_h, img_w, tile, overlap, d_workspace, P));
+    IRB_REQUIRE(workspace_bytes >= P.total, "irb_restore_image: workspace too small");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int pad_mode = m->desc.arch == IRB_ARCH_SWINIR ? 1 : 0;
+    if (in_fmt == 0)
+        IRB_TRY(image_prepare(reinterpret_cast<const uint8_t*>(d_in), img_h, img_w, P.c, reverse_channels, P.padded,
+                              P.hp, P.wp, pad_mode, s));
+    else
+        IRB_TRY(image_pad_f32(reinterpret_cast<const float*>(d_in), P.c, img_h, img_w, P.padded, P.hp, P.wp, pad_mode, s));
+    IRB_TRY(tiles_gather(P.padded, P.c, P.hp, P.wp, P.ys, P.xs, P.ny, P.nx, P.th, P.tw, P.tiles_in, nullptr, 1.0f, s));
+    const int nt = P.ny * P.nx;
+    const size_t in_stride = size_t(P.th) * P.tw * P.c;
+    const size_t out_stride = in_stride * P.sf * P.sf;
+    for (int t0 = 0; t0 < nt; t0 += P.nb) {
+        const int nb = nt - t0 < P.nb ? nt - t0 : P.nb;
+        IRB_TRY(m->forward(P.tiles_in + t0 * in_stride, P.tiles_out + t0 * out_stride, nb, P.th, P.tw, P.model_ws,
+                           P.model_ws_bytes, s));
+    }
+    IRB_TRY(tiles_stitch(P.tiles_out, P.c, P.th, P.tw, P.sf, P.ys, P.xs, P.ny, P.nx, P.hp, P.wp, img_h * P.sf,
+                         img_w * P.sf, d_out_f32, d_out_u8, reverse_channels, s));
+    return 0;
+}
+
+}  // extern "C"

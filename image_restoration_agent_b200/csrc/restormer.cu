@@ -1,0 +1,336 @@
+// Restormer forward (restormer_arch.py:245-284) as a sequence of irb200 kernels on channels-last activations.
+//
+// Data layout in the caller's workspace (E = element size of the storage dtype):
+//   cat1 [P1, 2d]   decoder-level-1 stream; the encoder-level-1 stream lives in its channels [d, 2d)  (zero-copy cat)
+//   cat2 [P2, 4d]   channels [0,2d) <- up3_2 output, [2d,4d) = encoder-level-2 stream
+//   cat3 [P3, 8d]   channels [0,4d) <- up4_3 output, [4d,8d) = encoder-level-3 stream
+//   x2 [P2,2d], x3 [P3,4d], x4 [P4,8d]  decoder-2 / decoder-3 / latent streams
+//   scratch: ln [P,C], qkv_pre / qkv [P,3C], hidden [P,2hp], gated [P,hp], G [n,heads,c,c] + sumsq [n,2C] (fp32),
+//            weff [n,C,C]
+// where P1 = n*H*W, P2 = P1/4, ... and d = dim (48).
+#include "model.h"
+#include <algorithm>
+#include <string.h>
+
+namespace irb {
+
+struct RBlockW {
+    int C, heads, h, hp;
+    float *n1w, *n1b, *n2w, *n2b;
+    void* qkv_w;     // [3C][C]
+    float* qkv_dw;   // [9][3C]
+    float* temp;     // [heads]
+    float* proj_w;   // [C][C] fp32 (folded with the attention matrix per image)
+    void* pin_w;     // [2hp][C]   rows [0,h) = x1, [hp,hp+h) = x2, others zero
+    float* ffn_dw;   // [9][2hp]
+    void* pout_w;    // [C][hp]
+};
+
+struct ConvW {
+    void* w;       // storage dtype, [npad][9*kpad]
+    float* wf32;   // fp32 copy (SIMT path for tiny channel counts)
+    int kpad, npad, N, C;
+};
+
+struct Restormer : Model {
+    int dim;
+    std::vector<RBlockW> enc1, enc2, enc3, latent, dec3, dec2, dec1, refine;
+    ConvW patch, down12, down23, down34, up43, up32, up21, outc;
+    void *reduce3, *reduce2;
+
+    int tile_multiple() const override { return 8; }
+    size_t forward_workspace(int n, int H, int W) override;
+    int forward(const float* in, float* out, int n, int H, int W, void* ws, size_t ws_bytes,
+                cudaStream_t stream) override;
+
+    struct WS {
+        void *cat1, *cat2, *cat3, *x2, *x3, *x4, *ln, *qkv_pre, *qkv, *hidden, *gated, *weff;
+        float *G, *sumsq;
+        size_t gs_bytes;
+    };
+    void layout(Bump& b, int n, int H, int W, WS& w);
+    int load_block(const Blob& blob, const std::string& p, int C, int heads, RBlockW& o);
+    int load_conv(const Blob& blob, const std::string& name, int N, int C, ConvW& o);
+    int run_block(const RBlockW& w, void* x, long long ldx, int n, int H, int W, WS& ws, cudaStream_t s);
+    int run_conv(const ConvW& c, const void* x, int x_dt, long long ldx, int n, int H, int W, Epi e, cudaStream_t s);
+    int run_gemm(const void* A, long long lda, long long M, int K, const void* Wt, int ldw, int N, int wrows, Epi e,
+                 cudaStream_t s);
+    char* at(void* p, long long elems) { return reinterpret_cast<char*>(p) + elems * (long long)esize(); }
+};
+
+int Restormer::load_block(const Blob& blob, const std::string& p, int C, int heads, RBlockW& o) {
+    o.C = C;
+    o.heads = heads;
+    o.h = int(C * desc.ffn_expansion_factor);  // restormer_arch.py:80 int(dim*ffn_expansion_factor)
+    o.hp = (o.h + 63) / 64 * 64;
+    BlobTensor t;
+    IRB_TRY(blob.get(p + ".norm1.body.weight", t, C));
+    IRB_TRY(upload_f32(t.data, C, &o.n1w));
+    IRB_TRY(blob.get(p + ".norm2.body.weight", t, C));
+    IRB_TRY(upload_f32(t.data, C, &o.n2w));
+    o.n1b = o.n2b = nullptr;
+    if (!desc.ln_bias_free) {
+        IRB_TRY(blob.get(p + ".norm1.body.bias", t, C));
+        IRB_TRY(upload_f32(t.data, C, &o.n1b));
+        IRB_TRY(blob.get(p + ".norm2.body.bias", t, C));
+        IRB_TRY(upload_f32(t.data, C, &o.n2b));
+    }
+    IRB_TRY(blob.get(p + ".attn.temperature", t, heads, 1, 1));
+    IRB_TRY(upload_f32(t.data, heads, &o.temp));
+    IRB_TRY(blob.get(p + ".attn.qkv.weight", t, 3 * C, C, 1, 1));
+    IRB_TRY(upload_act(t.data, size_t(3) * C * C, &o.qkv_w));
+    IRB_TRY(blob.get(p + ".attn.qkv_dwconv.weight", t, 3 * C, 1, 3, 3));
+    {
+        std::vector<float> d = pack_dw(t);
+        IRB_TRY(upload_f32(d.data(), d.size(), &o.qkv_dw));
+    }
+    IRB_TRY(blob.get(p + ".attn.project_out.weight", t, C, C, 1, 1));
+    IRB_TRY(upload_f32(t.data, size_t(C) * C, &o.proj_w));
+    const int h = o.h, hp = o.hp;
+    IRB_TRY(blob.get(p + ".ffn.project_in.weight", t, 2 * h, C, 1, 1));
+    {
+        std::vector<float> w(size_t(2) * hp * C, 0.f);
+        for (int r = 0; r < 2 * h; ++r) {
+            const int dst = r < h ? r : hp + (r - h);
+            memcpy(&w[size_t(dst) * C], t.data + size_t(r) * C, size_t(C) * 4);
+        }
+        IRB_TRY(upload_act(w.data(), w.size(), &o.pin_w));
+    }
+    IRB_TRY(blob.get(p + ".ffn.dwconv.weight", t, 2 * h, 1, 3, 3));
+    {
+        std::vector<float> w(size_t(9) * 2 * hp, 0.f);
+        for (int r = 0; r < 2 * h; ++r) {
+            const int dst = r < h ? r : hp + (r - h);
+            for (int k = 0; k < 9; ++k) w[size_t(k) * 2 * hp + dst] = t.data[size_t(r) * 9 + k];
+        }
+        IRB_TRY(upload_f32(w.data(), w.size(), &o.ffn_dw));
+    }
+    IRB_TRY(blob.get(p + ".ffn.project_out.weight", t, C, h, 1, 1));
+    {
+        std::vector<float> w(size_t(C) * hp, 0.f);
+        for (int r = 0; r < C; ++r) memcpy(&w[size_t(r) * hp], t.data + size_t(r) * h, size_t(h) * 4);
+        IRB_TRY(upload_act(w.data(), w.size(), &o.pout_w));
+    }
+    return 0;
+}
+
+int Restormer::load_conv(const Blob& blob, const std::string& name, int N, int C, ConvW& o) {
+    BlobTensor t;
+    IRB_TRY(blob.get(name, t, N, C, 3, 3));
+    std::vector<float> w = pack_conv3x3(t, o.kpad, o.npad);
+    o.N = N;
+    o.C = C;
+    IRB_TRY(upload_act(w.data(), w.size(), &o.w));
+    o.wf32 = nullptr;
+    if (dt == DT_F32)
+        o.wf32 = reinterpret_cast<float*>(o.w);
+    else if (C < 16)
+        IRB_TRY(upload_f32(w.data(), w.size(), &o.wf32));
+    return 0;
+}
+
+int build_restormer(const irb_model_desc& d, const Blob& blob, int device, Model** out) {
+    Restormer* m = new Restormer();
+    *out = m;
+    m->desc = d;
+    m->dt = d.precision == IRB_BF16 ? DT_BF16 : DT_F32;
+    m->device = device;
+    m->cin = d.in_chans;
+    m->scale = 1;
+    m->dim = d.dim;
+    IRB_REQUIRE(d.dim > 0 && d.dim % 16 == 0, "Restormer: dim must be a positive multiple of 16");
+    IRB_REQUIRE(d.in_chans == 1 || d.in_chans == 3, "Restormer: in_chans must be 1 or 3");
+    for (int l = 0; l < 4; ++l)
+        IRB_REQUIRE(d.heads[l] > 0 && ((d.dim << l) % d.heads[l]) == 0 && (d.dim << l) / d.heads[l] <= 96,
+                    "Restormer: channels per head must divide and be <= 96");
+    IRB_REQUIRE((2 * d.dim) % d.heads[0] == 0 && (2 * d.dim) / d.heads[0] <= 96, "Restormer: decoder-1 head size");
+    const int dim = d.dim;
+    auto stage = [&](std::vector<RBlockW>& v, const char* name, int nblk, int C, int heads) -> int {
+        v.resize(nblk);
+        for (int i = 0; i < nblk; ++i) IRB_TRY(m->load_block(blob, std::string(name) + "." + std::to_string(i), C, heads, v[i]));
+        return 0;
+    };
+    IRB_TRY(m->load_conv(blob, "patch_embed.proj.weight", dim, d.in_chans, m->patch));
+    IRB_TRY(stage(m->enc1, "encoder_level1", d.num_blocks[0], dim, d.heads[0]));
+    IRB_TRY(m->load_conv(blob, "down1_2.body.0.weight", dim / 2, dim, m->down12));
+    IRB_TRY(stage(m->enc2, "encoder_level2", d.num_blocks[1], dim * 2, d.heads[1]));
+    IRB_TRY(m->load_conv(blob, "down2_3.body.0.weight", dim, dim * 2, m->down23));
+    IRB_TRY(stage(m->enc3, "encoder_level3", d.num_blocks[2], dim * 4, d.heads[2]));
+    IRB_TRY(m->load_conv(blob, "down3_4.body.0.weight", dim * 2, dim * 4, m->down34));
+    IRB_TRY(stage(m->latent, "latent", d.num_blocks[3], dim * 8, d.heads[3]));
+    IRB_TRY(m->load_conv(blob, "up4_3.body.0.weight", dim * 16, dim * 8, m->up43));
+    BlobTensor t;
+    IRB_TRY(blob.get("reduce_chan_level3.weight", t, dim * 4, dim * 8, 1, 1));
+    IRB_TRY(m->upload_act(t.data, size_t(dim) * 4 * dim * 8, &m->reduce3));
+    IRB_TRY(stage(m->dec3, "decoder_level3", d.num_blocks[2], dim * 4, d.heads[2]));
+    IRB_TRY(m->load_conv(blob, "up3_2.body.0.weight", dim * 8, dim * 4, m->up32));
+    IRB_TRY(blob.get("reduce_chan_level2.weight", t, dim * 2, dim * 4, 1, 1));
+    IRB_TRY(m->upload_act(t.data, size_t(dim) * 2 * dim * 4, &m->reduce2));
+    IRB_TRY(stage(m->dec2, "decoder_level2", d.num_blocks[1], dim * 2, d.heads[1]));
+    IRB_TRY(m->load_conv(blob, "up2_1.body.0.weight", dim * 4, dim * 2, m->up21));
+    IRB_TRY(stage(m->dec1, "decoder_level1", d.num_blocks[0], dim * 2, d.heads[0]));
+    IRB_TRY(stage(m->refine, "refinement", d.num_refinement_blocks, dim * 2, d.heads[0]));
+    IRB_TRY(m->load_conv(blob, "output.weight", d.in_chans, dim * 2, m->outc));
+    return 0;
+}
+
+void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
+    const size_t E = esize();
+    const size_t P1 = size_t(n) * H * W, P2 = P1 / 4, P3 = P1 / 16, P4 = P1 / 64;
+    const int d = dim;
+    w.cat1 = b.take(P1 * 2 * d * E);
+    w.cat2 = b.take(P2 * 4 * d * E);
+    w.cat3 = b.take(P3 * 8 * d * E);
+    w.x2 = b.take(P2 * 2 * d * E);
+    w.x3 = b.take(P3 * 4 * d * E);
+    w.x4 = b.take(P4 * 8 * d * E);
+    // scratch sized by the worst level: per-pixel channel counts shrink 2x while pixels shrink 4x, so the
+    // full-resolution decoder level (C = 2d) dominates; take the max explicitly.
+    size_t ln = 0, qkv = 0, hid = 0, gat = 0, weff = 0, gs = 0;
+    const size_t Ps[4] = {P1, P2, P3, P4};
+    for (int l = 0; l < 4; ++l) {
+        const int Cs[2] = {d << l, l == 0 ? 2 * d : d << l};
+        for (int k = 0; k < 2; ++k) {
+            const int C = Cs[k];
+            const int heads = (k == 1 && l == 0) ? desc.heads[0] : desc.heads[l];
+            const int hp = (int(C * desc.ffn_expansion_factor) + 63) / 64 * 64;
+            ln = std::max(ln, Ps[l] * C * E);
+            qkv = std::max(qkv, Ps[l] * 3 * C * E);
+            hid = std::max(hid, Ps[l] * 2 * hp * E);
+            gat = std::max(gat, Ps[l] * hp * E);
+            weff = std::max(weff, size_t(n) * C * C * E);
+            gs = std::max(gs, (size_t(n) * C * (C / heads) + size_t(n) * 2 * C) * 4);
+        }
+    }
+    w.ln = b.take(ln);
+    w.qkv_pre = b.take(qkv);
+    w.qkv = b.take(qkv);
+    w.hidden = b.take(hid);
+    w.gated = b.take(gat);
+    w.weff = b.take(weff);
+    w.G = b.take<float>(gs);
+    w.gs_bytes = gs;
+    w.sumsq = nullptr;
+}
+
+size_t Restormer::forward_workspace(int n, int H, int W) {
+    Bump b(nullptr);
+    WS w;
+    layout(b, n, H, W, w);
+    return b.off + 256;
+}
+
+int Restormer::run_gemm(const void* A, long long lda, long long M, int K, const void* Wt, int ldw, int N, int wrows,
+                        Epi e, cudaStream_t s) {
+    IRB_REQUIRE(M < (1ll << 31), "Restormer: too many pixels in one batch (lower tile_batch)");
+    if (dt == DT_BF16)
+        return tc_gemm((const bf16*)A, lda, int(M), K, 1, 0, (const bf16*)Wt, ldw, N, wrows, 0, e, s);
+    return simt_gemm(A, DT_F32, lda, int(M), K, 1, 0, (const float*)Wt, ldw, N, 0, e, s);
+}
+
+int Restormer::run_conv(const ConvW& c, const void* x, int x_dt, long long ldx, int n, int H, int W, Epi e,
+                        cudaStream_t s) {
+    if (dt == DT_BF16 && x_dt == DT_BF16 && c.C >= 16)
+        return tc_conv3x3((const bf16*)x, ldx, n, H, W, c.C, (const bf16*)c.w, c.kpad, c.N, c.npad, e, s);
+    IRB_REQUIRE(c.wf32 != nullptr, "Restormer: missing fp32 conv weights");
+    return simt_conv3x3(x, x_dt, ldx, n, H, W, c.C, c.wf32, c.kpad, c.N, e, s);
+}
+
+// TransformerBlock.forward (restormer_arch.py:146-150) on the stream x [n*H*W, C] (row stride ldx), in place.
+int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H, int W, WS& ws, cudaStream_t s) {
+    const int C = w.C, heads = w.heads, c = C / heads;
+    const long long P = (long long)n * H * W;
+    const int mode = desc.ln_bias_free ? 1 : 0;
+    // --- x = x + project_out(attn(norm1(x))) ---
+    IRB_TRY(layernorm(x, dt, ldx, ws.ln, dt, C, P, C, w.n1w, w.n1b, mode, 1e-5f, s));
+    IRB_TRY(run_gemm(ws.ln, C, P, C, w.qkv_w, C, 3 * C, 3 * C, make_epi(ws.qkv_pre, 3 * C, dt), s));
+    const size_t g_floats = size_t(n) * heads * c * c;
+    float* G = ws.G;
+    float* sumsq = ws.G + g_floats;
+    IRB_CHECK_CUDA(cudaMemsetAsync(G, 0, (g_floats + size_t(n) * 2 * C) * 4, s));
+    IRB_TRY(dwconv3x3(ws.qkv_pre, dt, 3 * C, ws.qkv, 3 * C, n, H, W, 3 * C, w.qkv_dw, sumsq, 2 * C, s));
+    if (dt == DT_BF16)
+        IRB_TRY(mdta_gram_tc((const bf16*)ws.qkv, 3 * C, n, H * W, C, heads, G, s));
+    else
+        IRB_TRY(mdta_gram_simt(ws.qkv, DT_F32, 3 * C, n, H * W, C, heads, G, s));
+    IRB_TRY(mdta_softmax_weff(G, sumsq, w.temp, w.proj_w, n, C, heads, ws.weff, dt, nullptr, s));
+    {
+        Epi e = make_epi(x, ldx, dt);
+        e.res = x;
+        e.ldr = ldx;
+        e.res_dt = dt;
+        const void* v = at(ws.qkv, 2 * C);
+        if (dt == DT_BF16)
+            IRB_TRY(tc_gemm((const bf16*)v, 3 * C, H * W, C, n, 0, (const bf16*)ws.weff, C, C, n * C, C, e, s));
+        else
+            IRB_TRY(simt_gemm(v, DT_F32, 3 * C, H * W, C, n, 0, (const float*)ws.weff, C, C, C, e, s));
+    }
+    // --- x = x + project_out(gelu(dw(x1)) * dw(x2)) ---
+    IRB_TRY(layernorm(x, dt, ldx, ws.ln, dt, C, P, C, w.n2w, w.n2b, mode, 1e-5f, s));
+    IRB_TRY(run_gemm(ws.ln, C, P, C, w.pin_w, C, 2 * w.hp, 2 * w.hp, make_epi(ws.hidden, 2 * w.hp, dt), s));
+    IRB_TRY(dwconv3x3_gate(ws.hidden, dt, 2 * w.hp, ws.gated, w.hp, n, H, W, w.hp, w.ffn_dw, s));
+    {
+        Epi e = make_epi(x, ldx, dt);
+        e.res = x;
+        e.ldr = ldx;
+        e.res_dt = dt;
+        IRB_TRY(run_gemm(ws.gated, w.hp, P, w.hp, w.pout_w, w.hp, C, C, e, s));
+    }
+    return 0;
+}
+
+int Restormer::forward(const float* in, float* out, int n, int H, int W, void* wsp, size_t ws_bytes,
+                       cudaStream_t s) {
+    IRB_REQUIRE(H % 8 == 0 && W % 8 == 0, "Restormer: tile height/width must be multiples of 8");
+    IRB_REQUIRE(ws_bytes >= forward_workspace(n, H, W), "Restormer: workspace too small");
+    IRB_REQUIRE((long long)H * W < (1ll << 31) / 8, "Restormer: tile too large");
+    Bump b(wsp);
+    WS ws;
+    layout(b, n, H, W, ws);
+    const int d = dim;
+    auto blocks = [&](std::vector<RBlockW>& v, void* x, long long ldx, int h, int w) -> int {
+        for (auto& blk : v) IRB_TRY(run_block(blk, x, ldx, n, h, w, ws, s));
+        return 0;
+    };
+    auto shuffle_epi = [&](void* o, long long ldo, int ps, int h, int w) {
+        Epi e = make_epi(o, ldo, dt);
+        e.ps = ps;
+        e.ps_h = h;
+        e.ps_w = w;
+        return e;
+    };
+    void* e1 = at(ws.cat1, d);       // encoder-1 stream: channels [d,2d) of cat1
+    void* e2 = at(ws.cat2, 2 * d);   // encoder-2 stream: channels [2d,4d) of cat2
+    void* e3 = at(ws.cat3, 4 * d);   // encoder-3 stream: channels [4d,8d) of cat3
+    const int H2 = H / 2, W2 = W / 2, H3 = H / 4, W3 = W / 4, H4 = H / 8, W4 = W / 8;
+
+    IRB_TRY(run_conv(patch, in, DT_F32, cin, n, H, W, make_epi(e1, 2 * d, dt), s));               // :247
+    IRB_TRY(blocks(enc1, e1, 2 * d, H, W));                                                        // :248
+    IRB_TRY(run_conv(down12, e1, dt, 2 * d, n, H, W, shuffle_epi(e2, 4 * d, 2, H, W), s));         // :250
+    IRB_TRY(blocks(enc2, e2, 4 * d, H2, W2));                                                      // :251
+    IRB_TRY(run_conv(down23, e2, dt, 4 * d, n, H2, W2, shuffle_epi(e3, 8 * d, 2, H2, W2), s));     // :253
+    IRB_TRY(blocks(enc3, e3, 8 * d, H3, W3));                                                      // :254
+    IRB_TRY(run_conv(down34, e3, dt, 8 * d, n, H3, W3, shuffle_epi(ws.x4, 8 * d, 2, H3, W3), s));  // :256
+    IRB_TRY(blocks(latent, ws.x4, 8 * d, H4, W4));                                                 // :257
+    IRB_TRY(run_conv(up43, ws.x4, dt, 8 * d, n, H4, W4, shuffle_epi(ws.cat3, 8 * d, 1, H4, W4), s));  // :259-260
+    IRB_TRY(run_gemm(ws.cat3, 8 * d, (long long)n * H3 * W3, 8 * d, reduce3, 8 * d, 4 * d, 4 * d,
+                     make_epi(ws.x3, 4 * d, dt), s));                                              // :261
+    IRB_TRY(blocks(dec3, ws.x3, 4 * d, H3, W3));                                                   // :262
+    IRB_TRY(run_conv(up32, ws.x3, dt, 4 * d, n, H3, W3, shuffle_epi(ws.cat2, 4 * d, 1, H3, W3), s));  // :264-265
+    IRB_TRY(run_gemm(ws.cat2, 4 * d, (long long)n * H2 * W2, 4 * d, reduce2, 4 * d, 2 * d, 2 * d,
+                     make_epi(ws.x2, 2 * d, dt), s));                                              // :266
+    IRB_TRY(blocks(dec2, ws.x2, 2 * d, H2, W2));                                                   // :267
+    IRB_TRY(run_conv(up21, ws.x2, dt, 2 * d, n, H2, W2, shuffle_epi(ws.cat1, 2 * d, 1, H2, W2), s));  // :269-270
+    IRB_TRY(blocks(dec1, ws.cat1, 2 * d, H, W));                                                   // :271
+    IRB_TRY(blocks(refine, ws.cat1, 2 * d, H, W));                                                 // :273
+    {
+        Epi e = make_epi(out, cin, DT_F32);  // output conv + inp_img (:281), fp32 out
+        e.res = in;
+        e.ldr = cin;
+        e.res_dt = DT_F32;
+        IRB_TRY(run_conv(outc, ws.cat1, dt, 2 * d, n, H, W, e, s));
+    }
+    return 0;
+}
+
+}  // namespace irb
