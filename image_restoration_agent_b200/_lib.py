@@ -53,7 +53,7 @@ PROTOTYPES = {
     "irb_mdta_gram": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _vp]),
     "irb_mdta_attn": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp]),
     "irb_stitch": (_i, [_vp, _i, _i, _i, _i, _ip, _ip, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
-    "irb_window_attention": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "irb_window_attention": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
 }
 
 _lib = None

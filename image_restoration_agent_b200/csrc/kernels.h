@@ -46,6 +46,10 @@ int mdta_softmax_weff(const float* G, const float* sumsq /*[Nimg][2C]*/, const f
                       int Nimg, int C, int heads, void* Weff, int w_dt, float* attn_out /*optional*/,
                       cudaStream_t stream);
 
+// ---- swin_attn.cu ----------------------------------------------------------------------------
+int window_attention(const void* qkv, int dt, long long ld, void* out, long long ldo, int n, int H, int W, int C,
+                     int heads, int dstride, int ws, int shift, const float* bias_table, cudaStream_t stream);
+
 // ---- tiles.cu --------------------------------------------------------------------------------
 // Gather tiles from a planar float image [c][h][w] into channels-last float tiles [n][t][t][c],
 // applying (x - mean[c]) * scale.

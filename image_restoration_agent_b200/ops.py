@@ -126,10 +126,11 @@ def stitch(tiles, ys, xs, sf, h, w, crop_h, crop_w, want_u8=True, reverse_channe
     return out, u8
 
 
-def window_attention(qkv, heads, window, shift, bias_table):
+def window_attention(qkv, C, heads, window, shift, bias_table):
+    """qkv [n, H, W, 3*heads*dstride] (q pre-scaled) -> [n, H, W, C]."""
     n, H, W, C3 = qkv.shape
-    Cc = C3 // 3
-    y = torch.empty((n, H, W, Cc), device=qkv.device, dtype=qkv.dtype)
-    check(_lib.load().irb_window_attention(qkv.data_ptr(), _dt(qkv), C3, y.data_ptr(), Cc, n, H, W, Cc, heads, window,
-                                           shift, bias_table.data_ptr(), _stream()))
+    dstride = C3 // (3 * heads)
+    y = torch.zeros((n, H, W, C), device=qkv.device, dtype=qkv.dtype)
+    check(_lib.load().irb_window_attention(qkv.data_ptr(), _dt(qkv), C3, y.data_ptr(), C, n, H, W, C, heads, dstride,
+                                           window, shift, bias_table.data_ptr(), _stream()))
     return y

@@ -133,11 +133,13 @@ int irb_mdta_attn(const float* d_G, const float* d_sumsq, const float* d_tempera
 int irb_stitch(const float* d_tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx,
                int h, int w, int crop_h, int crop_w, float* d_out_f32, uint8_t* d_out_u8, int reverse_channels,
                void* stream);
-/* SwinIR (shifted-)window attention on a channels-last qkv tensor [n, H, W, 3*C] (q | k | v, head-major):
- * out[n,H,W,C] = window_reverse(softmax(q k^T * scale + rel_pos_bias + shift_mask) v), with the cyclic shift folded
- * into the addressing (network_swinir.py:114-145, 216-237, 239-279). d_bias_table is fp32 [(2ws-1)^2][heads]. */
+/* SwinIR (shifted-)window attention on a channels-last qkv tensor [n, H, W, 3*heads*dstride] (sections q | k | v,
+ * head-major, dstride >= C/heads channels per head, q pre-multiplied by head_dim^-0.5):
+ * out[n,H,W,C] = window_reverse(softmax(q k^T + rel_pos_bias + shift_mask) v), with the cyclic shift folded into
+ * the addressing (network_swinir.py:114-145, 216-237, 239-279). d_bias_table is fp32 [(2ws-1)^2][heads]. */
 int irb_window_attention(const void* d_qkv, int dtype, long long ld, void* d_out, long long ldo, int n, int H, int W,
-                         int C, int heads, int window, int shift, const float* d_bias_table, void* stream);
+                         int C, int heads, int dstride, int window, int shift, const float* d_bias_table,
+                         void* stream);
 
 #ifdef __cplusplus
 }
