@@ -259,3 +259,210 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
     }
     return 0;
 }
+
+void SwinIR::layout(Bump& b, int n, int H0, int W0, WS& w) {
+    int H, W;
+    padded(H0, W0, H, W);
+    const size_t E = esize();
+    const size_t P = size_t(n) * H * W;
+    const int s = scale;
+    w.xin = b.take<float>(P * cin * 4);
+    w.out_tmp = (H != H0 || W != W0) ? b.take<float>(P * s * s * cin * 4) : nullptr;
+    w.xa = b.take(P * ldC * E);
+    w.xb = b.take(P * ldC * E);
+    w.ffirst = b.take(P * ldC * E);
+    w.ln = b.take(P * ldC * E);
+    w.qkv = b.take(P * 3 * Cq * E);
+    w.attn = b.take(P * ldC * E);
+    w.hidden = b.take(P * hid * E);
+    w.q4a = w.q4b = nullptr;
+    if (desc.resi_3conv) {
+        w.q4a = b.take(P * 64 * E);
+        w.q4b = b.take(P * 64 * E);
+    }
+    w.t64 = w.u1 = w.u2 = w.u3 = nullptr;
+    if (desc.upsampler == IRB_UPSAMPLER_PIXELSHUFFLE) {
+        // ping-pong 64-channel maps: LR, then x2, x4, ... (largest = s*s*P)
+        w.t64 = b.take(P * 64 * E);
+        w.u1 = b.take(P * s * s * 64 * E);
+        w.u2 = b.take(P * (s * s / 4 > 0 ? s * s / 4 : 1) * 64 * E);
+    } else if (desc.upsampler == IRB_UPSAMPLER_NEAREST_CONV) {
+        w.t64 = b.take(P * 64 * E);
+        w.u1 = b.take(P * s * s * 64 * E);
+        w.u2 = b.take(P * s * s * 64 * E);
+    }
+}
+
+size_t SwinIR::forward_workspace(int n, int H, int W) {
+    Bump b(nullptr);
+    WS w;
+    layout(b, n, H, W, w);
+    return b.off + 256;
+}
+
+int SwinIR::gemm(const void* A, long long lda, long long M, const LinW& L, Epi e, cudaStream_t s) {
+    IRB_REQUIRE(M < (1ll << 31), "SwinIR: too many tokens in one batch (lower tile_batch)");
+    e.bias = L.b;
+    if (dt == DT_BF16)
+        return tc_gemm((const bf16*)A, lda, int(M), L.K, 1, 0, (const bf16*)L.w, L.kpad, L.N, L.npad, 0, e, s);
+    return simt_gemm(A, DT_F32, lda, int(M), L.K, 1, 0, (const float*)L.w, L.kpad, L.N, 0, e, s);
+}
+
+int SwinIR::conv(const Conv3W& c, const void* x, int x_dt, long long ldx, int n, int H, int W, Epi e,
+                 cudaStream_t s) {
+    e.bias = c.b;
+    if (dt == DT_BF16 && x_dt == DT_BF16 && c.C >= 16)
+        return tc_conv3x3((const bf16*)x, ldx, n, H, W, c.C, (const bf16*)c.w, c.kpad, c.N, c.npad, e, s);
+    IRB_REQUIRE(c.wf32 != nullptr, "SwinIR: missing fp32 conv weights");
+    return simt_conv3x3(x, x_dt, ldx, n, H, W, c.C, c.wf32, c.kpad, c.N, e, s);
+}
+
+// '1conv' / '3conv' residual convolution (:464-471, :728-736); `e` is the epilogue of the LAST convolution.
+int SwinIR::resi(const ResiW& r, const void* x, long long ldx, int n, int H, int W, Epi e, WS& w, cudaStream_t s) {
+    if (!desc.resi_3conv) return conv(r.c0, x, dt, ldx, n, H, W, e, s);
+    Epi e0 = make_epi(w.q4a, 64, dt);
+    e0.act = ACT_LRELU;
+    e0.slope = 0.2f;
+    IRB_TRY(conv(r.c0, x, dt, ldx, n, H, W, e0, s));
+    Epi e1 = make_epi(w.q4b, 64, dt);
+    e1.act = ACT_LRELU;
+    e1.slope = 0.2f;
+    IRB_TRY(gemm(w.q4a, 64, (long long)n * H * W, r.lin, e1, s));
+    return conv(r.c2, w.q4b, dt, 64, n, H, W, e, s);
+}
+
+// SwinTransformerBlock.forward (:239-279): xout = xin + attn(LN1(xin)); xout += mlp(LN2(xout))
+int SwinIR::stl(const STLW& L, const void* xin, void* xout, int n, int H, int W, WS& w, cudaStream_t s) {
+    const long long P = (long long)n * H * W;
+    IRB_TRY(layernorm(xin, dt, ldC, w.ln, dt, ldC, P, C, L.n1w, L.n1b, 0, 1e-5f, s));
+    IRB_TRY(gemm(w.ln, ldC, P, L.qkv, make_epi(w.qkv, 3 * Cq, dt), s));
+    IRB_TRY(window_attention(w.qkv, dt, 3 * Cq, w.attn, ldC, n, H, W, C, L.heads, dp, ws_eff, L.shift, L.bias_table, s));
+    {
+        Epi e = make_epi(xout, ldC, dt);
+        e.res = xin;
+        e.ldr = ldC;
+        e.res_dt = dt;
+        IRB_TRY(gemm(w.attn, ldC, P, L.proj, e, s));
+    }
+    IRB_TRY(layernorm(xout, dt, ldC, w.ln, dt, ldC, P, C, L.n2w, L.n2b, 0, 1e-5f, s));
+    {
+        Epi e = make_epi(w.hidden, hid, dt);
+        e.act = ACT_GELU;
+        IRB_TRY(gemm(w.ln, ldC, P, L.fc1, e, s));
+    }
+    {
+        Epi e = make_epi(xout, ldC, dt);
+        e.res = xout;
+        e.ldr = ldC;
+        e.res_dt = dt;
+        IRB_TRY(gemm(w.hidden, hid, P, L.fc2, e, s));
+    }
+    return 0;
+}
+
+int SwinIR::forward(const float* in, float* out, int n, int H0, int W0, void* wsp, size_t ws_bytes, cudaStream_t s) {
+    IRB_REQUIRE(ws_bytes >= forward_workspace(n, H0, W0), "SwinIR: workspace too small");
+    int H, W;
+    padded(H0, W0, H, W);
+    IRB_REQUIRE(H - H0 < H0 && W - W0 < W0, "SwinIR: image smaller than the reflect padding");
+    IRB_REQUIRE(H % ws_eff == 0 && W % ws_eff == 0, "SwinIR: padded size must be a multiple of the window");
+    if (desc.resi_3conv) IRB_REQUIRE(C / 4 <= 64, "SwinIR: 3conv supports embed_dim <= 256");
+    Bump b(wsp);
+    WS w;
+    layout(b, n, H0, W0, w);
+    const long long P = (long long)n * H * W;
+    const int sc = scale;
+    // (x - mean) * img_range on the reflect-padded tile (:806-810)
+    swin_prep_kernel<<<grid_for(P), 256, 0, s>>>(in, w.xin, n, H0, W0, H, W, cin, mean[0], mean[1], mean[2],
+                                                 desc.img_range);
+    IRB_CHECK_CUDA(cudaGetLastError());
+    IRB_TRY(conv(conv_first, w.xin, DT_F32, cin, n, H, W, make_epi(w.ffirst, ldC, dt), s));  // :813 / :833
+    // forward_features (:790-803)
+    IRB_TRY(layernorm(w.ffirst, dt, ldC, w.xa, dt, ldC, P, C, pen_w, pen_b, 0, 1e-5f, s));  // patch_embed.norm
+    for (size_t r = 0; r < layers.size(); ++r) {
+        // RSTB (:481-482): xa = conv(blocks(xa)) + xa ; the blocks run in xb
+        const void* src = w.xa;
+        for (auto& L : layers[r]) {
+            IRB_TRY(stl(L, src, w.xb, n, H, W, w, s));
+            src = w.xb;
+        }
+        Epi e = make_epi(w.xa, ldC, dt);
+        e.res = w.xa;
+        e.ldr = ldC;
+        e.res_dt = dt;
+        IRB_TRY(resi(layer_conv[r], w.xb, ldC, n, H, W, e, w, s));
+    }
+    IRB_TRY(layernorm(w.xa, dt, ldC, w.ln, dt, ldC, P, C, norm_w, norm_b, 0, 1e-5f, s));  // :800
+    {
+        // conv_after_body(forward_features(x)) + x  -> xb
+        Epi e = make_epi(w.xb, ldC, dt);
+        e.res = w.ffirst;
+        e.ldr = ldC;
+        e.res_dt = dt;
+        IRB_TRY(resi(conv_after_body, w.ln, ldC, n, H, W, e, w, s));
+    }
+    const bool crop = (H != H0) || (W != W0);
+    float* dst = crop ? w.out_tmp : out;
+    auto last_epi = [&]() {
+        Epi e = make_epi(dst, cin, DT_F32);  // x / img_range + mean (:838)
+        e.post_scale = 1.0f / desc.img_range;
+        e.post_shift = d_mean;
+        return e;
+    };
+    auto lrelu_epi = [&](void* o, float slope) {
+        Epi e = make_epi(o, 64, dt);
+        e.act = ACT_LRELU;
+        e.slope = slope;
+        return e;
+    };
+    if (desc.upsampler == IRB_UPSAMPLER_NONE) {
+        Epi e = last_epi();  // x + conv_last(res) on the normalised input (:834-836)
+        e.res = w.xin;
+        e.ldr = cin;
+        e.res_dt = DT_F32;
+        IRB_TRY(conv(conv_last, w.xb, dt, ldC, n, H, W, e, s));
+    } else if (desc.upsampler == IRB_UPSAMPLER_PIXELSHUFFLE) {
+        IRB_TRY(conv(conv_before_up, w.xb, dt, ldC, n, H, W, lrelu_epi(w.t64, 0.01f), s));  // nn.LeakyReLU() :742-743
+        const void* cur = w.t64;
+        int h = H, wd = W;
+        void* bufs[2] = {w.u1, w.u2};
+        // keep the LAST stage in u1 (the largest buffer)
+        int which = (upsample.size() % 2 == 1) ? 0 : 1;
+        for (size_t i = 0; i < upsample.size(); ++i) {
+            Epi e = make_epi(bufs[which], 64, dt);  // conv 64->256 + PixelShuffle(2) fused into the store (:572-591)
+            e.ps = 1;
+            e.ps_h = h;
+            e.ps_w = wd;
+            IRB_TRY(conv(upsample[i], cur, dt, 64, n, h, wd, e, s));
+            cur = bufs[which];
+            which ^= 1;
+            h *= 2;
+            wd *= 2;
+        }
+        IRB_TRY(conv(conv_last, cur, dt, 64, n, h, wd, last_epi(), s));
+    } else {
+        IRB_TRY(conv(conv_before_up, w.xb, dt, ldC, n, H, W, lrelu_epi(w.t64, 0.01f), s));
+        // lrelu(conv_up1(nearest x2)) [, lrelu(conv_up2(nearest x2))], conv_last(lrelu(conv_hr(x)))  (:826-831)
+        IRB_TRY(nearest_up2(w.t64, dt, 64, w.u1, 64, n, H, W, 64, s));
+        IRB_TRY(conv(conv_up1, w.u1, dt, 64, n, 2 * H, 2 * W, lrelu_epi(w.u2, 0.2f), s));
+        int h = 2 * H, wd = 2 * W;
+        void* cur = w.u2;
+        void* other = w.u1;
+        if (sc == 4) {
+            IRB_TRY(nearest_up2(w.u2, dt, 64, w.u1, 64, n, h, wd, 64, s));
+            h *= 2;
+            wd *= 2;
+            IRB_TRY(conv(conv_up2, w.u1, dt, 64, n, h, wd, lrelu_epi(w.u2, 0.2f), s));
+        }
+        IRB_TRY(conv(conv_hr, cur, dt, 64, n, h, wd, lrelu_epi(other, 0.2f), s));
+        IRB_TRY(conv(conv_last, other, dt, 64, n, h, wd, last_epi(), s));
+    }
+    if (crop) {
+        const long long total = (long long)n * H0 * sc * W0 * sc * cin;
+        crop_nhwc_kernel<<<grid_for(total), 256, 0, s>>>(w.out_tmp, out, n, H * sc, W * sc, H0 * sc, W0 * sc, cin);
+        IRB_CHECK_CUDA(cudaGetLastError());
+    }
+    return 0;
+}
+
+}  // namespace irb
