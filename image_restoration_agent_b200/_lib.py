@@ -45,6 +45,9 @@ PROTOTYPES = {
     "irb_forward_tiles": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "irb_restore_workspace_bytes": (_i, [_vp, _i, _i, _i, _i, C.POINTER(_sz)]),
     "irb_restore_image": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),
+    "irb_restore_plan": (_i, [_vp, _i, _i, _i, _i, _ip, _ip, _ip, _ip, _ip, _ip, _ip, _ip]),
+    "irb_tiles_prepare": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "irb_forward_tiles_cl": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "irb_layernorm": (_i, [_vp, _i, _ll, _vp, _ll, _ll, _i, _vp, _vp, _i, _f, _vp]),
     "irb_gemm1x1": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _i, _i, _i, _i, _vp, _vp, _ll, _i, _f, _vp, _ll, _vp]),
     "irb_conv3x3": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _i, _i, _i, _vp, _vp, _ll, _i, _f, _i, _vp, _ll, _vp]),

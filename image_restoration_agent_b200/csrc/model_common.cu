@@ -351,4 +351,46 @@ int irb_restore_image(irb_handle* h, const void* d_in, int in_fmt, int reverse_c
     return 0;
 }
 
+// ---- building blocks of irb_restore_image, exposed so that tiles can be sharded across ranks -------------------
+int irb_restore_plan(irb_handle* h, int img_h, int img_w, int tile, int overlap, int* hp, int* wp, int* th, int* tw,
+                     int* ys, int* ny, int* xs, int* nx) {
+    IRB_REQUIRE(h && hp && wp && th && tw && ys && ny && xs && nx, "irb_restore_plan: NULL argument");
+    RestorePlan P;
+    IRB_TRY(make_plan(h->model, img_h, img_w, tile, overlap, nullptr, P));
+    *hp = P.hp;
+    *wp = P.wp;
+    *th = P.th;
+    *tw = P.tw;
+    *ny = P.ny;
+    *nx = P.nx;
+    for (int i = 0; i < P.ny; ++i) ys[i] = P.ys[i];
+    for (int i = 0; i < P.nx; ++i) xs[i] = P.xs[i];
+    return 0;
+}
+
+int irb_tiles_prepare(irb_handle* h, const void* d_in, int in_fmt, int reverse_channels, int img_h, int img_w,
+                      int tile, int overlap, float* d_padded, float* d_tiles, void* stream) {
+    IRB_REQUIRE(h && d_in && d_padded && d_tiles, "irb_tiles_prepare: NULL argument");
+    Model* m = h->model;
+    RestorePlan P;
+    IRB_TRY(make_plan(m, img_h, img_w, tile, overlap, nullptr, P));
+    cudaStream_t s = (cudaStream_t)stream;
+    const int pad_mode = m->desc.arch == IRB_ARCH_SWINIR ? 1 : 0;
+    if (in_fmt == 0)
+        IRB_TRY(image_prepare(reinterpret_cast<const uint8_t*>(d_in), img_h, img_w, P.c, reverse_channels, d_padded,
+                              P.hp, P.wp, pad_mode, s));
+    else
+        IRB_TRY(image_pad_f32(reinterpret_cast<const float*>(d_in), P.c, img_h, img_w, d_padded, P.hp, P.wp, pad_mode, s));
+    return tiles_gather(d_padded, P.c, P.hp, P.wp, P.ys, P.xs, P.ny, P.nx, P.th, P.tw, d_tiles, nullptr, 1.0f, s);
+}
+
+int irb_forward_tiles_cl(irb_handle* h, const float* d_in, float* d_out, int n_tiles, int tile_h, int tile_w,
+                         void* d_workspace, size_t workspace_bytes, void* stream) {
+    IRB_REQUIRE(h && d_in && d_out && d_workspace && n_tiles > 0, "irb_forward_tiles_cl: bad argument");
+    Model* m = h->model;
+    const size_t need = m->forward_workspace(n_tiles, tile_h, tile_w);
+    IRB_REQUIRE(workspace_bytes >= need, "irb_forward_tiles_cl: workspace too small");
+    return m->forward(d_in, d_out, n_tiles, tile_h, tile_w, d_workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
 }  // extern "C"

@@ -135,6 +135,51 @@ class Engine:
                                              torch.cuda.current_stream().cuda_stream))
         return u8, f32
 
+    # ---- the stages of restore_device, for sharding tiles across ranks (parallel.py) ----
+    def plan(self, h: int, w: int, tile=None, tile_overlap: int = 32) -> dict:
+        ys, xs = (C.c_int * 128)(), (C.c_int * 128)()
+        v = [C.c_int() for _ in range(6)]
+        hp, wp, th, tw, ny, nx = v
+        check(self.lib.irb_restore_plan(self._h, h, w, 0 if tile is None else int(tile), tile_overlap, C.byref(hp),
+                                        C.byref(wp), C.byref(th), C.byref(tw), ys, C.byref(ny), xs, C.byref(nx)))
+        return dict(hp=hp.value, wp=wp.value, th=th.value, tw=tw.value, ys=list(ys[:ny.value]),
+                    xs=list(xs[:nx.value]), scale=self.scale, c=self.channels, h=h, w=w)
+
+    def prepare_tiles(self, img: torch.Tensor, plan: dict, tile=None, tile_overlap: int = 32, bgr: bool = False):
+        """-> fp32 channels-last tiles [ny*nx, th, tw, c] of the padded image (pad rule of the reference tool)."""
+        fmt = 0 if img.dtype == torch.uint8 else 1
+        img = img.contiguous()
+        c = self.channels
+        padded = torch.empty((c, plan["hp"], plan["wp"]), dtype=torch.float32, device=img.device)
+        nt = len(plan["ys"]) * len(plan["xs"])
+        tiles = torch.empty((nt, plan["th"], plan["tw"], c), dtype=torch.float32, device=img.device)
+        check(self.lib.irb_tiles_prepare(self._h, img.data_ptr(), fmt, int(bgr), plan["h"], plan["w"],
+                                         0 if tile is None else int(tile), tile_overlap, padded.data_ptr(),
+                                         tiles.data_ptr(), torch.cuda.current_stream().cuda_stream))
+        return tiles
+
+    def forward_cl(self, tiles: torch.Tensor) -> torch.Tensor:
+        """model(x) on channels-last fp32 tiles [n, th, tw, c] -> [n, th*s, tw*s, c]."""
+        n, th, tw, c = tiles.shape
+        s = self.scale
+        out = torch.empty((n, th * s, tw * s, c), dtype=torch.float32, device=tiles.device)
+        if n == 0:
+            return out
+        need = C.c_size_t()
+        with self._lock:
+            check(self.lib.irb_workspace_bytes(self._h, n, th, tw, C.byref(need)))
+            ws = self._workspace(need.value)
+            check(self.lib.irb_forward_tiles_cl(self._h, tiles.data_ptr(), out.data_ptr(), n, th, tw, ws.data_ptr(),
+                                                ws.numel(), torch.cuda.current_stream().cuda_stream))
+        return out
+
+    def stitch(self, tiles_out: torch.Tensor, plan: dict, bgr: bool = False, want_u8=True, want_f32=False):
+        from . import ops
+        s = plan["scale"]
+        f32, u8 = ops.stitch(tiles_out, plan["ys"], plan["xs"], s, plan["hp"], plan["wp"], plan["h"] * s,
+                             plan["w"] * s, want_u8=want_u8, reverse_channels=bgr)
+        return u8, (f32 if want_f32 else None)
+
     def restore(self, img_u8: np.ndarray, tile=None, tile_overlap: int = 32, bgr: bool = False) -> np.ndarray:
         """Host uint8 [H,W,c] (or [H,W]) in -> host uint8 out; H2D and D2H included."""
         squeeze = img_u8.ndim == 2

@@ -103,6 +103,18 @@ int irb_restore_image(irb_handle* h, const void* d_in, int in_fmt, int reverse_c
                       int tile, int overlap, uint8_t* d_out_u8, float* d_out_f32, void* d_workspace,
                       size_t workspace_bytes, void* stream);
 
+/* ---- the stages of irb_restore_image, exposed so that tiles can be sharded across ranks (one process per GPU):
+ * plan (host) -> tiles_prepare -> forward_tiles_cl on this rank's tile range -> [NCCL gather] -> irb_stitch. ------
+ * ys/xs must hold 128 ints each. d_padded: fp32 [c][hp][wp]; d_tiles: fp32 channels-last [ny*nx][th][tw][c]. */
+int irb_restore_plan(irb_handle* h, int img_h, int img_w, int tile, int overlap, int* hp, int* wp, int* th, int* tw,
+                     int* ys, int* ny, int* xs, int* nx);
+int irb_tiles_prepare(irb_handle* h, const void* d_in, int in_fmt, int reverse_channels, int img_h, int img_w,
+                      int tile, int overlap, float* d_padded, float* d_tiles, void* stream);
+/* channels-last variant of irb_forward_tiles: in [n][th][tw][c] -> out [n][th*s][tw*s][c]; workspace size =
+ * irb_workspace_bytes(). */
+int irb_forward_tiles_cl(irb_handle* h, const float* d_in, float* d_out, int n_tiles, int tile_h, int tile_w,
+                         void* d_workspace, size_t workspace_bytes, void* stream);
+
 /* ---- single-kernel entry points (parity tests, ncu captures). dtype: IRB_F32 / IRB_BF16; activations are
  * channels-last with an explicit row stride ld (elements). -------------------------------------------------- */
 int irb_layernorm(const void* d_x, int dtype, long long ldx, void* d_y, long long ldy, long long rows, int C,

@@ -1,0 +1,157 @@
+"""GPU (-m gpu): the CUDA path behind the C ABI against the reference outputs in tests/golden/ and against the oracle.
+
+Tolerances (north_star): fp32 mode <= 1e-4 max-abs on the [0,1] scale; bf16 mode <= 2e-2 max-abs and PSNR >= 45 dB;
+tile indexing / blend weights bit-exact; uint8 within 1 LSB of the reference in fp32 mode, and within
+1 + ceil(255 * max_abs_float_error) LSB in bf16 mode (a 2e-2 float budget cannot guarantee 1 LSB after quantisation).
+"""
+import glob
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from image_restoration_agent_b200 import configs, synth
+
+from cases import R_CASES, S_CASES, tool_case
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp32": 1e-4, "bf16": 2e-2}
+
+
+def psnr(a, b):
+    mse = float(((a.astype(np.float64) - b) ** 2).mean())
+    return 200.0 if mse == 0 else 10 * math.log10(1.0 / mse)
+
+
+def _engine(arch, cfg, sd, prec):
+    from image_restoration_agent_b200.engine import Engine
+    return Engine(arch, cfg, sd, precision=prec)
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", sorted(R_CASES))
+def test_restormer_forward_matches_reference(name, prec, golden_dir):
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    cfg = R_CASES[name]()
+    eng = _engine("restormer", cfg, synth.restormer_state_dict(cfg, seed=int(g["seed"])), prec)
+    y = eng(torch.from_numpy(g["x"]).cuda()).cpu().numpy()
+    assert np.isfinite(y).all()
+    assert np.abs(y - g["y"]).max() <= TOL[prec]
+    if prec == "bf16":
+        assert psnr(y, g["y"]) >= 45.0
+    eng.close()
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", sorted(S_CASES))
+def test_swinir_forward_matches_reference(name, prec, golden_dir):
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    cfg = S_CASES[name]()
+    eng = _engine("swinir", cfg, synth.swinir_state_dict(cfg, seed=int(g["seed"])), prec)
+    y = eng(torch.from_numpy(g["x"]).cuda()).cpu().numpy()
+    assert y.shape == g["y"].shape and np.isfinite(y).all()
+    assert np.abs(y - g["y"]).max() <= TOL[prec]
+    if prec == "bf16":
+        assert psnr(y, g["y"]) >= 45.0
+    eng.close()
+
+
+_TOOLS = sorted(os.path.basename(p)[:-4] for p in
+                glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*_tool_*.npz")))
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", _TOOLS)
+def test_tool_body_matches_reference(name, prec, golden_dir):
+    """pad -> tiles -> model -> blend -> crop -> clamp -> round, whole-image and tiled, both tools."""
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    arch, cfg, sd, tile, overlap, scale = tool_case(name, g)
+    eng = _engine(arch, cfg, sd, prec)
+    u8, f32 = eng.restore_device(torch.from_numpy(g["img"]).cuda(), tile, overlap, bgr=(arch == "swinir"),
+                                 want_f32=True)
+    f = f32.cpu().numpy()
+    err = float(np.abs(f - g["out_f32"]).max())
+    assert err <= TOL[prec]
+    lsb = int(np.abs(u8.cpu().numpy().astype(int) - g["out_u8"].astype(int)).max())
+    assert lsb <= (1 if prec == "fp32" else 1 + math.ceil(255 * err))
+    # host API (H2D + D2H inside) gives the same bytes
+    assert np.array_equal(eng.restore(g["img"], tile, overlap, bgr=(arch == "swinir")), u8.cpu().numpy())
+    eng.close()
+
+
+def test_restormer_against_oracle_on_fresh_input():
+    """Not a stored fixture: seeded input, oracle run here on CPU (small config, finishes in seconds)."""
+    from oracle import restormer_ref
+    cfg = configs.small_restormer_config("BiasFree", 3)
+    sd = synth.restormer_state_dict(cfg, seed=11)
+    x = torch.rand(2, 3, 40, 24, generator=torch.Generator().manual_seed(5))
+    want = restormer_ref.Model(sd, cfg)(x).numpy()
+    for prec in ("fp32", "bf16"):
+        eng = _engine("restormer", cfg, sd, prec)
+        got = eng(x.cuda()).cpu().numpy()
+        assert np.abs(got - want).max() <= TOL[prec]
+        eng.close()
+
+
+def test_batched_tiles_equal_single_tiles():
+    """model(x) on a batch of tiles == model on each tile alone (MDTA statistics are per tile)."""
+    cfg = configs.small_restormer_config()
+    eng = _engine("restormer", cfg, synth.restormer_state_dict(cfg, 3), "fp32")
+    x = torch.rand(3, 3, 32, 32, generator=torch.Generator().manual_seed(1)).cuda()
+    yb = eng(x)
+    for i in range(3):
+        assert (eng(x[i:i + 1]) - yb[i:i + 1]).abs().max().item() <= 2e-6
+    eng.close()
+
+
+def test_restormer_cfg2_full_size_properties():
+    """BASELINE config 2 at full size (1280x720, tile 256 / overlap 32, bf16): size-independent properties."""
+    cfg = configs.restormer_config("Motion_Deblurring")
+    eng = _engine("restormer", cfg, synth.restormer_state_dict(cfg, 0), "bf16")
+    img = torch.from_numpy(synth.synthetic_image_u8(720, 1280, 3, seed=0)).cuda()
+    u8, f32 = eng.restore_device(img, 256, 32, want_f32=True)
+    assert u8.shape == (720, 1280, 3) and torch.isfinite(f32).all()
+    # (1) determinism / idempotence of the pipeline
+    u8b, f32b = eng.restore_device(img, 256, 32, want_f32=True)
+    assert torch.equal(u8, u8b)
+    # (2) tile_batch does not change the result beyond split-K atomics order
+    eng.set_tile_batch(5)
+    _, f32c = eng.restore_device(img, 256, 32, want_f32=True)
+    assert (f32c - f32).abs().max().item() <= 2e-3
+    eng.set_tile_batch(0)
+    # (3) the staged path (plan -> prepare -> forward_cl -> stitch) reproduces restore_device, and the tile list is
+    #     the reference's: h [0,224,448,464], w [0,224,448,672,896,1024]
+    plan = eng.plan(720, 1280, 256, 32)
+    assert plan["ys"] == [0, 224, 448, 464] and plan["xs"] == [0, 224, 448, 672, 896, 1024]
+    tiles = eng.prepare_tiles(img, plan, 256, 32)
+    u8s, f32s = eng.stitch(eng.forward_cl(tiles), plan, want_f32=True)
+    assert (f32s - f32).abs().max().item() <= 2e-3
+    # (4) uint8 equals clamp/rint of the float output exactly
+    want = torch.round(f32.clamp(0, 1) * 255.0).to(torch.uint8).permute(1, 2, 0)
+    assert torch.equal(want, u8)
+    # (5) a tile of the big image restored alone equals model(tile) (no cross-tile leakage)
+    y = eng(tiles[7:8].permute(0, 3, 1, 2).contiguous())
+    yb = eng.forward_cl(tiles[6:9])[1:2].permute(0, 3, 1, 2)
+    assert (y - yb).abs().max().item() <= 2e-3
+    eng.close()
+
+
+def test_invalid_arguments_raise():
+    cfg = configs.small_restormer_config()
+    eng = _engine("restormer", cfg, synth.restormer_state_dict(cfg, 3), "bf16")
+    img = torch.zeros(64, 64, 3, dtype=torch.uint8, device="cuda")
+    with pytest.raises(ValueError):  # demo.py:136 assert tile % 8 == 0
+        eng.restore_device(img, 20, 4)
+    with pytest.raises(ValueError):
+        eng.restore_device(img, 32, 32)
+    with pytest.raises(ValueError):
+        eng(torch.zeros(1, 3, 30, 32, device="cuda"))
+    eng.close()
+    scfg = configs.small_swinir_config("color_dn")
+    seng = _engine("swinir", scfg, synth.swinir_state_dict(scfg, 0), "bf16")
+    with pytest.raises(ValueError):  # inference.py:302 assert tile % window_size == 0
+        seng.restore_device(img, 20, 4)
+    seng.close()
