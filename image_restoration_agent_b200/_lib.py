@@ -56,6 +56,11 @@ PROTOTYPES = {
     "irb_mdta_gram": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _vp]),
     "irb_mdta_attn": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp]),
     "irb_stitch": (_i, [_vp, _i, _i, _i, _i, _ip, _ip, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "irb_profile_begin": (_i, [_vp]),
+    "irb_profile_end": (_i, [_vp]),
+    "irb_profile_count": (_i, []),
+    "irb_profile_entry": (_i, [_i, C.c_char_p, _ip, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                               C.POINTER(C.c_double)]),
     "irb_window_attention": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
 }
 

@@ -3,10 +3,48 @@
 #include "common.cuh"
 #include "kernels.h"
 #include <string.h>
+#include <vector>
 
 namespace irb {
 static thread_local std::string g_last_error;
 void set_error(const std::string& msg) { g_last_error = msg; }
+
+// ---- per-launch profiler -----------------------------------------------------------------------------
+bool g_prof_on = false;
+struct ProfRec {
+    char name[56];
+    double flops, bytes;
+    cudaEvent_t ev;
+};
+struct ProfAgg {
+    char name[56];
+    int launches;
+    double ms, flops, bytes;
+};
+static std::vector<ProfRec> g_prof_recs;
+static std::vector<cudaEvent_t> g_prof_pool;
+static std::vector<ProfAgg> g_prof_agg;
+static cudaEvent_t g_prof_start = nullptr;
+static size_t g_prof_pool_used = 0;
+
+static cudaEvent_t prof_event() {
+    if (g_prof_pool_used == g_prof_pool.size()) {
+        cudaEvent_t e = nullptr;
+        cudaEventCreate(&e);
+        g_prof_pool.push_back(e);
+    }
+    return g_prof_pool[g_prof_pool_used++];
+}
+
+void prof_mark_slow(const char* name, int p0, int p1, double flops, double bytes, cudaStream_t s) {
+    ProfRec r{};
+    snprintf(r.name, sizeof r.name, "%s[%d,%d]", name, p0, p1);
+    r.flops = flops;
+    r.bytes = bytes;
+    r.ev = prof_event();
+    cudaEventRecord(r.ev, s);
+    g_prof_recs.push_back(r);
+}
 }  // namespace irb
 
 using namespace irb;
@@ -46,6 +84,56 @@ int irb_padded_size(int arch, int window_size, int h, int w, int* hp, int* wp) {
         set_error("irb_padded_size: unknown arch");
         return 1;
     }
+    return 0;
+}
+
+// ---- profiler API: begin -> run any irb_* calls on `stream` -> end (synchronises) -> read entries ---------
+int irb_profile_begin(void* stream) {
+    g_prof_recs.clear();
+    g_prof_agg.clear();
+    g_prof_pool_used = 0;
+    g_prof_start = prof_event();
+    IRB_CHECK_CUDA(cudaEventRecord(g_prof_start, (cudaStream_t)stream));
+    g_prof_on = true;
+    return 0;
+}
+
+int irb_profile_end(void* stream) {
+    g_prof_on = false;
+    IRB_CHECK_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    cudaEvent_t prev = g_prof_start;
+    for (const ProfRec& r : g_prof_recs) {
+        float ms = 0.f;
+        IRB_CHECK_CUDA(cudaEventElapsedTime(&ms, prev, r.ev));
+        prev = r.ev;
+        ProfAgg* a = nullptr;
+        for (ProfAgg& x : g_prof_agg)
+            if (strcmp(x.name, r.name) == 0) a = &x;
+        if (!a) {
+            ProfAgg n{};
+            memcpy(n.name, r.name, sizeof n.name);
+            g_prof_agg.push_back(n);
+            a = &g_prof_agg.back();
+        }
+        a->launches += 1;
+        a->ms += ms;
+        a->flops += r.flops;
+        a->bytes += r.bytes;
+    }
+    return 0;
+}
+
+int irb_profile_count(void) { return int(g_prof_agg.size()); }
+
+int irb_profile_entry(int i, char* name56, int* launches, double* ms, double* flops, double* bytes) {
+    IRB_REQUIRE(i >= 0 && i < int(g_prof_agg.size()) && name56 && launches && ms && flops && bytes,
+                "irb_profile_entry: bad arguments");
+    const ProfAgg& a = g_prof_agg[i];
+    memcpy(name56, a.name, sizeof a.name);
+    *launches = a.launches;
+    *ms = a.ms;
+    *flops = a.flops;
+    *bytes = a.bytes;
     return 0;
 }
 

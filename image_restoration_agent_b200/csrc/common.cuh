@@ -37,6 +37,17 @@ void set_error(const std::string& msg);
         if (_rc != 0) return _rc; \
     } while (0)
 
+// ---- optional per-launch profiling (irb_profile_begin/end; bench.py's live roofline) ---------------
+// Every launch wrapper calls prof_mark() right after its kernel launch. When profiling is off this is one
+// predictable branch; when on, a CUDA event is recorded on the launching stream, so the device time between
+// two consecutive marks is the duration of the kernel in between. flops / bytes are the ALGORITHMIC work of
+// the launch (each operand read once, each result written once).
+extern bool g_prof_on;
+void prof_mark_slow(const char* name, int p0, int p1, double flops, double bytes, cudaStream_t s);
+static inline void prof_mark(const char* name, int p0, int p1, double flops, double bytes, cudaStream_t s) {
+    if (g_prof_on) prof_mark_slow(name, p0, p1, flops, bytes, s);
+}
+
 // ---- fused epilogue of every GEMM / implicit-GEMM convolution ---------------------------------
 //   y = post_scale * ( act(acc + bias[col]) + res[row, col] ) + post_shift[col]
 // `row` is the global output pixel/token index, `col` the output channel.
@@ -180,6 +191,12 @@ static inline Epi make_epi(void* out, long long ldo, int out_dt) {
     e.out_dt = out_dt;
     e.post_scale = 1.0f;
     return e;
+}
+
+// algorithmic bytes of an epilogue: result written once (+ residual read once) for `rows` x `cols`
+static inline double epi_bytes(const Epi& e, double rows, double cols) {
+    const double eo = e.out_dt == DT_BF16 ? 2 : 4, er = e.res_dt == DT_BF16 ? 2 : 4;
+    return rows * cols * (eo + (e.res ? er : 0));
 }
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

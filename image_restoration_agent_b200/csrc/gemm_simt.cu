@@ -113,6 +113,10 @@ int simt_gemm(const void* A, int a_dt, long long lda, int M, int K, int batch, l
     dim3 grid(ceil_div(M, 64), ceil_div(N, 64), batch);
     simt_gemm_kernel<1><<<grid, 256, 0, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
+    {
+        const double rows = double(M) * batch, ea = a_dt == DT_BF16 ? 2 : 4;
+        prof_mark("simt_gemm", K, N, 2.0 * rows * K * N, rows * K * ea + double(N) * K * 4 + epi_bytes(epi, rows, N), stream);
+    }
     return 0;
 }
 
@@ -138,6 +142,10 @@ int simt_conv3x3(const void* A, int a_dt, long long lda, int Nimg, int H, int W,
     dim3 grid(ceil_div(H * W, 64), ceil_div(N, 64), Nimg);
     simt_gemm_kernel<9><<<grid, 256, 0, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
+    {
+        const double rows = double(H) * W * Nimg, ea = a_dt == DT_BF16 ? 2 : 4;
+        prof_mark("simt_conv3x3", C, N, 18.0 * rows * C * N, rows * C * ea + 9.0 * N * C * 4 + epi_bytes(epi, rows, N), stream);
+    }
     return 0;
 }
 

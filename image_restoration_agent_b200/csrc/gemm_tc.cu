@@ -272,7 +272,13 @@ int tc_gemm(const bf16* A, long long lda, int M, int K, int batch, long long a_b
     }
     p.epi = epi;
     dim3 grid(ceil_div(M, kTileM), ceil_div(N, p.BN), batch);
-    return launch_tc(p, grid, stream);
+    IRB_TRY(launch_tc(p, grid, stream));
+    {
+        const double rows = double(M) * batch;
+        const double wrows = w_rows_per_batch ? double(N) * batch : double(N);
+        prof_mark("tc_gemm", K, N, 2.0 * rows * K * N, rows * K * 2 + wrows * K * 2 + epi_bytes(epi, rows, N), stream);
+    }
+    return 0;
 }
 
 // 3x3 convolution, stride 1, zero pad 1, channels-last. Wt is [Nrows, 9*kpad] with K index = tap*kpad + c.
@@ -314,7 +320,12 @@ int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, cons
     }
     p.epi = epi;
     dim3 grid(p.tiles_x * ceil_div(H, BH), ceil_div(N, p.BN), Nimg);
-    return launch_tc(p, grid, stream);
+    IRB_TRY(launch_tc(p, grid, stream));
+    {
+        const double rows = double(H) * W * Nimg;
+        prof_mark("tc_conv3x3", C, N, 18.0 * rows * C * N, rows * C * 2 + 9.0 * N * C * 2 + epi_bytes(epi, rows, N), stream);
+    }
+    return 0;
 }
 
 }  // namespace irb

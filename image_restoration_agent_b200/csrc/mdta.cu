@@ -146,6 +146,7 @@ int mdta_gram_tc(const bf16* qkv, long long ld, int Nimg, int P, int C, int head
     dim3 grid(ceil_div(P, chunk), heads, Nimg);
     mdta_gram_tc_kernel<<<grid, 192, smem, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("mdta_gram_tc", C, heads, 2.0 * Nimg * P * C * c, double(Nimg) * P * 2 * C * 2 + double(Nimg) * C * c * 4, stream);
     return 0;
 }
 
@@ -211,6 +212,7 @@ int mdta_gram_simt(const void* qkv, int dt, long long ld, int Nimg, int P, int C
     else
         mdta_gram_simt_kernel<bf16><<<grid, 256, smem, stream>>>((const bf16*)qkv, ld, P, C, c, heads, chunk, G);
     IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("mdta_gram_simt", C, heads, 2.0 * Nimg * P * C * c, double(Nimg) * P * 2 * C * (dt == DT_F32 ? 4 : 2) + double(Nimg) * C * c * 4, stream);
     return 0;
 }
 
@@ -274,6 +276,7 @@ int mdta_softmax_weff(const float* G, const float* sumsq, const float* temperatu
     dim3 grid(heads, Nimg);
     mdta_softmax_weff_kernel<<<grid, 256, smem, stream>>>(G, sumsq, temperature, Wp, C, heads, Weff, w_dt, attn_out);
     IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("mdta_softmax_weff", C, heads, 2.0 * Nimg * C * C * c, double(Nimg) * (C * c * 4.0 + C * C * (w_dt == DT_BF16 ? 2 : 4)) + C * C * 4.0, stream);
     return 0;
 }
 

@@ -160,6 +160,7 @@ static int permute_launch(const float* in, float* out, int n, int c, int h, int 
     const int blocks = int(ceil_div_ll(total, 256) > 148 * 16 ? 148 * 16 : ceil_div_ll(total, 256));
     permute_f32_kernel<<<blocks, 256, 0, s>>>(in, out, n, c, (long long)h * w, to_nhwc);
     IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("permute_f32", c, to_nhwc, 0.0, 8.0 * total, s);
     return 0;
 }
 int nchw_to_nhwc_f32(const float* in, float* out, int n, int c, int h, int w, cudaStream_t s) {

@@ -114,6 +114,7 @@ static int layernorm_launch(const void* x, long long ldx, void* y, long long ldy
     else
         layernorm_kernel<TI, TO, 32><<<blocks, 256, 0, stream>>>(xi, ldx, yo, ldy, rows, C, w, b, mode, eps);
     IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("layernorm", C, int(sizeof(TI)), 8.0 * rows * C, double(rows) * C * (sizeof(TI) + sizeof(TO)), stream);
     return 0;
 }
 
@@ -248,6 +249,10 @@ static int dwconv_launch(bool gate, const void* x, long long ldx, void* y, long 
     else
         dwconv3x3_kernel<T, false><<<grid, 256, smem, stream>>>(xi, ldx, yo, ldy, H, W, Cout, 0, wt, wt_ld, RY, sumsq, sumsq_channels);
     IRB_CHECK_CUDA(cudaGetLastError());
+    {
+        const double px = double(Nimg) * H * W, cin = gate ? 2.0 * Cout : double(Cout);
+        prof_mark(gate ? "dwconv3x3_gate" : "dwconv3x3", Cout, int(sizeof(T)), 18.0 * px * cin, px * (cin + Cout) * sizeof(T) + 36.0 * cin, stream);
+    }
     return 0;
 }
 
@@ -297,6 +302,7 @@ int nearest_up2(const void* x, int dt, long long ldx, void* y, long long ldy, in
     else
         nearest_up2_kernel<bf16><<<blocks, 256, 0, stream>>>((const bf16*)x, ldx, (bf16*)y, ldy, Nimg, H, W, C / 4);
     IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("nearest_up2", C, dt, 0.0, double(Nimg) * H * W * C * 5.0 * (dt == DT_F32 ? 4 : 2), stream);
     return 0;
 }
 

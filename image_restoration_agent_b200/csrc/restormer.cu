@@ -248,6 +248,7 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
     float* G = ws.G;
     float* sumsq = ws.G + g_floats;
     IRB_CHECK_CUDA(cudaMemsetAsync(G, 0, (g_floats + size_t(n) * 2 * C) * 4, s));
+    prof_mark("memset_gram", C, heads, 0.0, (g_floats + double(n) * 2 * C) * 4, s);
     IRB_TRY(dwconv3x3(ws.qkv_pre, dt, 3 * C, ws.qkv, 3 * C, n, H, W, 3 * C, w.qkv_dw, sumsq, 2 * C, s));
     if (dt == DT_BF16)
         IRB_TRY(mdta_gram_tc((const bf16*)ws.qkv, 3 * C, n, H * W, C, heads, G, s));

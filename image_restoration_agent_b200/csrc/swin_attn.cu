@@ -138,6 +138,10 @@ int window_attention_simt(const void* qkv, int dt, long long ld, void* out, long
     dim3 grid((H / ws) * (W / ws), heads, n);
     window_attention_simt_kernel<<<grid, 256, 0, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
+    {
+        const double px = double(n) * H * W, e = dt == DT_F32 ? 4 : 2;
+        prof_mark("window_attention_simt", C, shift, 4.0 * px * ws * ws * C, px * 4.0 * C * e, stream);
+    }
     return 0;
 }
 

@@ -376,6 +376,7 @@ int SwinIR::forward(const float* in, float* out, int n, int H0, int W0, void* ws
     swin_prep_kernel<<<grid_for(P), 256, 0, s>>>(in, w.xin, n, H0, W0, H, W, cin, mean[0], mean[1], mean[2],
                                                  desc.img_range);
     IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("swin_prep", cin, 0, 0.0, 8.0 * P * cin, s);
     IRB_TRY(conv(conv_first, w.xin, DT_F32, cin, n, H, W, make_epi(w.ffirst, ldC, dt), s));  // :813 / :833
     // forward_features (:790-803)
     IRB_TRY(layernorm(w.ffirst, dt, ldC, w.xa, dt, ldC, P, C, pen_w, pen_b, 0, 1e-5f, s));  // patch_embed.norm
@@ -461,6 +462,7 @@ int SwinIR::forward(const float* in, float* out, int n, int H0, int W0, void* ws
         const long long total = (long long)n * H0 * sc * W0 * sc * cin;
         crop_nhwc_kernel<<<grid_for(total), 256, 0, s>>>(w.out_tmp, out, n, H * sc, W * sc, H0 * sc, W0 * sc, cin);
         IRB_CHECK_CUDA(cudaGetLastError());
+        prof_mark("crop_nhwc", cin, 0, 0.0, 8.0 * total, s);
     }
     return 0;
 }

@@ -51,6 +51,7 @@ int image_prepare(const uint8_t* src, int h, int w, int c, int reverse_channels,
     const int blocks = int(ceil_div_ll(total, 256) > 148 * 16 ? 148 * 16 : ceil_div_ll(total, 256));
     image_prepare_kernel<<<blocks, 256, 0, stream>>>(src, h, w, c, reverse_channels, dst, hp, wp, pad_mode);
     IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("image_prepare", c, pad_mode, 0.0, 5.0 * total * c, stream);
     return 0;
 }
 
@@ -75,6 +76,7 @@ int image_pad_f32(const float* src, int c, int h, int w, float* dst, int hp, int
     const int blocks = int(ceil_div_ll(total, 256) > 148 * 16 ? 148 * 16 : ceil_div_ll(total, 256));
     image_pad_kernel<<<blocks, 256, 0, stream>>>(src, c, h, w, dst, hp, wp, pad_mode);
     IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("image_pad", c, pad_mode, 0.0, 8.0 * total, stream);
     return 0;
 }
 
@@ -109,6 +111,7 @@ int tiles_gather(const float* img, int c, int h, int w, const int* ys, const int
                                                     (mean && c > 1) ? mean[1] : 0.f, (mean && c > 2) ? mean[2] : 0.f,
                                                     scale);
     IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("tiles_gather", c, ny * nx, 0.0, 8.0 * total * c, stream);
     return 0;
 }
 
@@ -159,6 +162,8 @@ int tiles_stitch(const float* tiles, int c, int th, int tw, int sf, const int* y
     tiles_stitch_kernel<<<blocks, 256, 0, stream>>>(tiles, c, th, tw, sf, L, h, w, crop_h, crop_w, out_f32, out_u8,
                                                     u8_reverse_channels);
     IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("tiles_stitch", c, ny * nx, 0.0,
+              4.0 * ny * nx * th * tw * sf * sf * c + double(total) * c * ((out_f32 ? 4 : 0) + (out_u8 ? 1 : 0)), stream);
     return 0;
 }
 

@@ -153,6 +153,14 @@ int irb_window_attention(const void* d_qkv, int dtype, long long ld, void* d_out
                          int C, int heads, int dstride, int window, int shift, const float* d_bias_table,
                          void* stream);
 
+/* ---- per-launch profiler (bench.py's live roofline): between begin and end every kernel launched by this
+ * library on `stream` is bracketed by CUDA events; end synchronises the stream and aggregates by kernel name +
+ * shape class. flops / bytes are ALGORITHMIC (operands read once, results written once). Not thread-safe. ---- */
+int irb_profile_begin(void* stream);
+int irb_profile_end(void* stream);
+int irb_profile_count(void);
+int irb_profile_entry(int i, char* name56, int* launches, double* ms, double* flops, double* bytes);
+
 #ifdef __cplusplus
 }
 #endif
