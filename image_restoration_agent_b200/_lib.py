@@ -53,8 +53,9 @@ PROTOTYPES = {
     "irb_conv3x3": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _i, _i, _i, _vp, _vp, _ll, _i, _f, _i, _vp, _ll, _vp]),
     "irb_dwconv3x3": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "irb_gdfn_dw_gate": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _vp, _vp]),
-    "irb_mdta_gram": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _vp]),
-    "irb_mdta_attn": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp]),
+    "irb_mdta_nchunks": (_i, [_i, _i, _i]),
+    "irb_mdta_gram": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "irb_mdta_attn": (_i, [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp]),
     "irb_stitch": (_i, [_vp, _i, _i, _i, _i, _ip, _ip, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "irb_profile_begin": (_i, [_vp]),
     "irb_profile_end": (_i, [_vp]),

@@ -205,17 +205,21 @@ int irb_gdfn_dw_gate(const void* d_x, int dtype, long long ldx, void* d_y, long 
     return dwconv3x3_gate(d_x, dtype, ldx, d_y, ldy, n, H, W, hp, d_w, (cudaStream_t)stream);
 }
 
-int irb_mdta_gram(const void* d_qkv, int dtype, long long ld, int n, int P, int C, int heads, float* d_G,
-                  void* stream) {
+int irb_mdta_nchunks(int P, int heads, int n) { return mdta_nchunks(P, heads, n); }
+
+int irb_mdta_gram(const void* d_qkv, int dtype, long long ld, int n, int P, int C, int heads, int nchunks,
+                  float* d_Gpart, float* d_ssq_part, void* stream) {
     IRB_TRY(require_device());
-    if (dtype == IRB_BF16) return mdta_gram_tc((const bf16*)d_qkv, ld, n, P, C, heads, d_G, (cudaStream_t)stream);
-    return mdta_gram_simt(d_qkv, DT_F32, ld, n, P, C, heads, d_G, (cudaStream_t)stream);
+    if (dtype == IRB_BF16)
+        return mdta_gram_tc((const bf16*)d_qkv, ld, n, P, C, heads, nchunks, d_Gpart, d_ssq_part, (cudaStream_t)stream);
+    return mdta_gram_simt(d_qkv, DT_F32, ld, n, P, C, heads, nchunks, d_Gpart, d_ssq_part, (cudaStream_t)stream);
 }
 
-int irb_mdta_attn(const float* d_G, const float* d_sumsq, const float* d_temperature, const float* d_wproj, int n,
-                  int C, int heads, void* d_weff, int dtype, float* d_attn, void* stream) {
+int irb_mdta_attn(const float* d_Gpart, const float* d_ssq_part, int nchunks, const float* d_temperature,
+                  const float* d_wproj, int n, int C, int heads, void* d_weff, int dtype, float* d_attn,
+                  void* stream) {
     IRB_TRY(require_device());
-    return mdta_softmax_weff(d_G, d_sumsq, d_temperature, d_wproj, n, C, heads, d_weff, dtype, d_attn,
+    return mdta_softmax_weff(d_Gpart, d_ssq_part, nchunks, d_temperature, d_wproj, n, C, heads, d_weff, dtype, d_attn,
                              (cudaStream_t)stream);
 }
 

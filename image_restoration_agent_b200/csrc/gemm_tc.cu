@@ -177,6 +177,12 @@ static PFN_encodeTiled get_encode() {
 // dims/strides innermost first; strides[i] is the byte stride of dim i+1.
 int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                    const uint32_t* box) {
+    return make_tmap_bf16_sw(m, base, rank, dims, strides_bytes, box, 128);
+}
+
+// swizzle_bytes: 128 (UMMA operand tiles) or 0 (plain row-major box, read by ordinary shared-memory loads)
+int make_tmap_bf16_sw(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box, int swizzle_bytes) {
     PFN_encodeTiled enc = get_encode();
     if (!enc) {
         set_error("cuTensorMapEncodeTiled entry point not available (driver too old?)");
@@ -191,7 +197,9 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* d
     }
     for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
     CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), d, s, b, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         char buf[256];

@@ -10,6 +10,8 @@ namespace irb {
 // ---- gemm_tc.cu : tcgen05 (bf16) -------------------------------------------------------------
 int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                    const uint32_t* box);
+int make_tmap_bf16_sw(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+                      const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
 int tc_gemm(const bf16* A, long long lda, int M, int K, int batch, long long a_batch_stride, const bf16* Wt, int ldw,
             int N, int w_rows_total, int w_rows_per_batch, const Epi& epi, cudaStream_t stream);
 int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, const bf16* Wt, int kpad, int N,
@@ -33,18 +35,28 @@ int dwconv3x3(const void* x, int dt, long long ldx, void* y, long long ldy, int 
 // GDFN gate: y[., c] = gelu(dw(x)[., c]) * dw(x)[., hp + c] for c < hp ; x has 2*hp channels, wt is [9][2*hp].
 int dwconv3x3_gate(const void* x, int dt, long long ldx, void* y, long long ldy, int Nimg, int H, int W, int hp,
                    const float* wt, cudaStream_t stream);
+// bf16 TMA-fed versions (dw_tma.cu); x rows must be 16-byte aligned
+int dwconv3x3_bf16_tma(const bf16* x, long long ldx, bf16* y, long long ldy, int Nimg, int H, int W, int C,
+                       const float* wt, cudaStream_t stream);
+int dwconv3x3_gate_bf16_tma(const bf16* x, long long ldx, bf16* y, long long ldy, int Nimg, int H, int W, int hp,
+                            const float* wt, cudaStream_t stream);
 int nearest_up2(const void* x, int dt, long long ldx, void* y, long long ldy, int Nimg, int H, int W, int C,
                 cudaStream_t stream);
 
 // ---- mdta.cu ---------------------------------------------------------------------------------
 // Gram over pixels of channels-last q,k (inside a qkv tensor of row stride ld): G[b,h,i,j] += sum_p q[p,hc+i]*k[p,hc+j]
-int mdta_gram_tc(const bf16* qkv, long long ld, int Nimg, int P, int C, int heads, float* G, cudaStream_t stream);
-int mdta_gram_simt(const void* qkv, int dt, long long ld, int Nimg, int P, int C, int heads, float* G,
-                   cudaStream_t stream);
-// attn = softmax_j(G[i,j] / (max(|q_i|,eps) max(|k_j|,eps)) * temp[h]); Weff[b][o][h*c+j] = sum_i Wp[o][h*c+i] attn[i][j]
-int mdta_softmax_weff(const float* G, const float* sumsq /*[Nimg][2C]*/, const float* temperature, const float* Wp,
-                      int Nimg, int C, int heads, void* Weff, int w_dt, float* attn_out /*optional*/,
-                      cudaStream_t stream);
+// The pixel axis is split into nchunks = mdta_nchunks(P, heads, Nimg) chunks; every chunk writes its own slot:
+//   Gpart [Nimg][heads][nchunks][c][c], ssq_part [Nimg][heads][nchunks][2][c] (|q_i|^2 then |k_j|^2). No atomics.
+int mdta_nchunks(int P, int heads, int Nimg);
+int mdta_gram_tc(const bf16* qkv, long long ld, int Nimg, int P, int C, int heads, int nchunks, float* Gpart,
+                 float* ssq_part, cudaStream_t stream);
+int mdta_gram_simt(const void* qkv, int dt, long long ld, int Nimg, int P, int C, int heads, int nchunks,
+                   float* Gpart, float* ssq_part, cudaStream_t stream);
+// sums the slots in order; attn = softmax_j(G[i,j] / (max(|q_i|,eps) max(|k_j|,eps)) * temp[h]);
+// Weff[b][o][h*c+j] = sum_i Wp[o][h*c+i] attn[i][j]
+int mdta_softmax_weff(const float* Gpart, const float* ssq_part, int nchunks, const float* temperature,
+                      const float* Wp, int Nimg, int C, int heads, void* Weff, int w_dt,
+                      float* attn_out /*optional*/, cudaStream_t stream);
 
 // ---- swin_attn.cu ----------------------------------------------------------------------------
 int window_attention(const void* qkv, int dt, long long ld, void* out, long long ldo, int n, int H, int W, int C,

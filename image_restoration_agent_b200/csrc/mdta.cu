@@ -1,7 +1,14 @@
 // Restormer MDTA (restormer_arch.py:111-132): channel-transposed attention.
-//   G[b,h,i,j] = sum_p q[b,p,hc+i] * k[b,p,hc+j]      (c x c Gram over K = H*W pixels, split-K over CTAs)
-//   attn       = softmax_j( G / (|q_i| |k_j|) * temperature[h] )
-//   Weff[b]    = Wp . blockdiag_h(attn[b,h])           (attn @ v followed by project_out is ONE per-image GEMM)
+//   G[b,h,i,j]  = sum_p q[b,p,hc+i] * k[b,p,hc+j]      (c x c Gram over K = H*W pixels)
+//   nq[i], nk[j] = sum_p q^2, sum_p k^2                 (the F.normalize denominators, :121-122)
+//   attn        = softmax_j( G / (max(|q_i|,1e-12) max(|k_j|,1e-12)) * temperature[h] )
+//   Weff[b]     = Wp . blockdiag_h(attn[b,h])           (attn @ v followed by project_out is ONE per-image GEMM)
+//
+// The pixel axis is split into `nchunks` chunks per image; every (chunk, head, image) CTA writes its partial
+// Gram AND the partial squared norms (the diagonals of q^T q and k^T k, computed by two more MMAs on the tiles that
+// are already in shared memory) to its own slot; the softmax kernel sums the slots in a fixed order. No atomics:
+// the result is bit-reproducible run to run.
+//
 // The Gram runs on tcgen05 with BOTH operands MN-major: q and k are channels-last, so the contraction index
 // (pixels) is the slow axis of the TMA box and the channel axis is the 128-byte swizzled row.
 #include "common.cuh"
@@ -12,23 +19,39 @@ namespace irb {
 
 static constexpr int kGramKP = 64;             // pixels per pipeline stage
 static constexpr int kGramBox = kGramKP * 128; // bytes of one [64 ch x KP px] box
+static constexpr int kGramStageBytes = 4 * kGramBox;  // q: 2 boxes (M = 128 rows), k: 2 boxes
+
+// Pixel chunks per image: about 2048 pixels each, at most 32 slots. A function of P ONLY, so that the summation
+// order (hence every output bit) does not depend on how many tiles are batched into one launch.
+int mdta_nchunks(int P, int heads, int Nimg) {
+    (void)heads;
+    (void)Nimg;
+    long long want = P / 2048;
+    if (want > 32) want = 32;
+    if (want < 1) want = 1;
+    const int chunk_px = int((((P + want - 1) / want) + kGramKP - 1) / kGramKP * kGramKP);
+    return (P + chunk_px - 1) / chunk_px;
+}
+static int chunk_px_for(int P, int nchunks) {
+    return ((P + nchunks - 1) / nchunks + kGramKP - 1) / kGramKP * kGramKP;
+}
 
 struct alignas(64) GramParams {
     CUtensorMap tm;   // {channels(3C), P, Nimg}, box {64, KP, 1}
     int C, c, heads, P;
     int chunk_px;     // pixels per CTA
-    int nB;           // 64-channel boxes of k per stage (1 for c<=64, 2 for c<=128)
     int ncols;        // UMMA N (c rounded up to 16)
+    int acc_stride;   // TMEM columns between the three accumulators (ncols rounded up to 32)
     int stages;
     int tmem_cols;
-    float* G;
+    float* Gpart;     // [Nimg][heads][nchunks][c][c]
+    float* ssq_part;  // [Nimg][heads][nchunks][2][c]
 };
 
 __global__ void __launch_bounds__(192) mdta_gram_tc_kernel(const __grid_constant__ GramParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    const int stage_bytes = (2 + p.nB) * kGramBox;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.stages * stage_bytes);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.stages * kGramStageBytes);
     uint64_t* empty_bar = full_bar + p.stages;
     uint64_t* accum_bar = empty_bar + p.stages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
@@ -64,13 +87,13 @@ __global__ void __launch_bounds__(192) mdta_gram_tc_kernel(const __grid_constant
             const int s = it % p.stages;
             const uint32_t ph = (it / p.stages) & 1;
             mbar_wait(&empty_bar[s], ph ^ 1);
-            uint8_t* sa = smem + s * stage_bytes;
-            mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
-            const int pp = px0 + it * kGramKP;
+            uint8_t* sa = smem + s * kGramStageBytes;
+            mbar_arrive_expect_tx(&full_bar[s], kGramStageBytes);
+            const int pp = px0 + it * kGramKP;  // pixels >= P are zero-filled by TMA: they add nothing
             tma_load_3d(sa, &p.tm, &full_bar[s], qc, pp, img);
             tma_load_3d(sa + kGramBox, &p.tm, &full_bar[s], qc + 64, pp, img);
-            for (int j = 0; j < p.nB; ++j)
-                tma_load_3d(sa + (2 + j) * kGramBox, &p.tm, &full_bar[s], kc + 64 * j, pp, img);
+            tma_load_3d(sa + 2 * kGramBox, &p.tm, &full_bar[s], kc, pp, img);
+            tma_load_3d(sa + 3 * kGramBox, &p.tm, &full_bar[s], kc + 64, pp, img);
         }
     } else if (warp == 1 && lane == 0) {
         const uint32_t idesc = make_idesc_bf16(128, p.ncols, 1, 1);  // both operands MN-major
@@ -79,14 +102,17 @@ __global__ void __launch_bounds__(192) mdta_gram_tc_kernel(const __grid_constant
             const uint32_t ph = (it / p.stages) & 1;
             mbar_wait(&full_bar[s], ph);
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(smem + s * stage_bytes);
-            const uint32_t b_addr = a_addr + 2 * kGramBox;
+            const uint32_t q_addr = smem_u32(smem + s * kGramStageBytes);
+            const uint32_t k_addr = q_addr + 2 * kGramBox;
 #pragma unroll
             for (int k = 0; k < kGramKP / 16; ++k) {
                 // 16 pixels = two 8-pixel groups (SBO = 1024 B apart); next 64 channels are one box (LBO) away
-                const uint64_t adesc = make_sdesc_sw128(a_addr + k * 2048, kGramBox, 1024);
-                const uint64_t bdesc = make_sdesc_sw128(b_addr + k * 2048, kGramBox, 1024);
-                umma_bf16(tmem_base, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+                const uint64_t qd = make_sdesc_sw128(q_addr + k * 2048, kGramBox, 1024);
+                const uint64_t kd = make_sdesc_sw128(k_addr + k * 2048, kGramBox, 1024);
+                const uint32_t acc = (it | k) != 0 ? 1u : 0u;
+                umma_bf16(tmem_base, qd, kd, idesc, acc);                // q^T k
+                umma_bf16(tmem_base + p.acc_stride, qd, qd, idesc, acc);      // q^T q (diagonal = |q_i|^2)
+                umma_bf16(tmem_base + 2 * p.acc_stride, kd, kd, idesc, acc);  // k^T k (diagonal = |k_j|^2)
             }
             umma_commit(&empty_bar[s]);
         }
@@ -95,16 +121,38 @@ __global__ void __launch_bounds__(192) mdta_gram_tc_kernel(const __grid_constant
         mbar_wait(accum_bar, 0);
         tc_fence_after();
         const int q = warp & 3;
-        const int i = q * 32 + lane;  // q channel within the head
+        const int i = q * 32 + lane;  // channel within the head (row of all three accumulators)
         const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16);
-        float* g = p.G + (((long long)img * p.heads + head) * p.c + i) * p.c;
+        const long long slot = ((long long)img * p.heads + head) * gridDim.x + blockIdx.x;
+        float* g = p.Gpart + (slot * p.c + i) * p.c;
         for (int cb = 0; cb < p.ncols; cb += 16) {
             float v[16];
             tmem_ld16(taddr + cb, v);
             if (i < p.c) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j)
-                    if (cb + j < p.c) atomicAdd(g + cb + j, v[j]);
+                for (int j = 0; j < 16; j += 4)
+                    if (cb + j < p.c)  // c % 8 == 0
+                        *reinterpret_cast<float4*>(g + cb + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            }
+        }
+        if (q * 32 < p.ncols) {  // warp-uniform: rows of this warp that can be < c
+            float d[2];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                float lo[16], hi[16];
+                tmem_ld16(taddr + (a + 1) * p.acc_stride + q * 32, lo);
+                tmem_ld16(taddr + (a + 1) * p.acc_stride + q * 32 + 16, hi);
+                float r = 0.f;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    r = (lane == j) ? lo[j] : r;
+                    r = (lane == j + 16) ? hi[j] : r;
+                }
+                d[a] = r;
+            }
+            if (i < p.c) {
+                p.ssq_part[(slot * 2 + 0) * p.c + i] = d[0];
+                p.ssq_part[(slot * 2 + 1) * p.c + i] = d[1];
             }
         }
     }
@@ -113,10 +161,12 @@ __global__ void __launch_bounds__(192) mdta_gram_tc_kernel(const __grid_constant
     if (warp == 0) tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
-int mdta_gram_tc(const bf16* qkv, long long ld, int Nimg, int P, int C, int heads, float* G, cudaStream_t stream) {
+int mdta_gram_tc(const bf16* qkv, long long ld, int Nimg, int P, int C, int heads, int nchunks, float* Gpart,
+                 float* ssq_part, cudaStream_t stream) {
     const int c = C / heads;
     IRB_REQUIRE(C % heads == 0 && c <= 128 && c % 8 == 0, "mdta_gram_tc: channels per head must be <=128 and %8");
     IRB_REQUIRE(ld % 8 == 0 && (reinterpret_cast<uintptr_t>(qkv) & 15) == 0, "mdta_gram_tc: alignment");
+    IRB_REQUIRE(nchunks >= 1 && nchunks <= 64, "mdta_gram_tc: 1..64 chunks");
     GramParams p{};
     uint64_t dims[3] = {uint64_t(3 * C), uint64_t(P), uint64_t(Nimg)};
     uint64_t str[2] = {uint64_t(ld) * 2, uint64_t(ld) * 2 * P};
@@ -126,34 +176,35 @@ int mdta_gram_tc(const bf16* qkv, long long ld, int Nimg, int P, int C, int head
     p.c = c;
     p.heads = heads;
     p.P = P;
-    p.nB = c <= 64 ? 1 : 2;
     p.ncols = (c + 15) / 16 * 16;
+    p.acc_stride = (p.ncols + 31) / 32 * 32;
     p.tmem_cols = 32;
-    while (p.tmem_cols < p.ncols) p.tmem_cols <<= 1;
-    // split-K: aim for >= 4 waves of CTAs but at least 512 pixels per CTA
-    int chunk = 2048;
-    while (chunk > 512 && (long long)ceil_div(P, chunk) * heads * Nimg < 4 * 148) chunk >>= 1;
-    p.chunk_px = chunk;
-    const int stage_bytes = (2 + p.nB) * kGramBox;
+    while (p.tmem_cols < 3 * p.acc_stride + 32) p.tmem_cols <<= 1;  // +32: the diagonal loads may run past the last column
+    IRB_REQUIRE(p.tmem_cols <= 512, "mdta_gram_tc: head too wide for TMEM");
+    p.chunk_px = chunk_px_for(P, nchunks);
+    IRB_REQUIRE((P + p.chunk_px - 1) / p.chunk_px == nchunks, "mdta_gram_tc: nchunks must come from mdta_nchunks()");
     p.stages = 4;
-    p.G = G;
-    const size_t smem = size_t(p.stages) * stage_bytes + 1024 + 256;
+    p.Gpart = Gpart;
+    p.ssq_part = ssq_part;
+    const size_t smem = size_t(p.stages) * kGramStageBytes + 1024 + 256;
     static bool attr_set = false;
     if (!attr_set) {
         IRB_CHECK_CUDA(cudaFuncSetAttribute(mdta_gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_set = true;
     }
-    dim3 grid(ceil_div(P, chunk), heads, Nimg);
+    dim3 grid(nchunks, heads, Nimg);
     mdta_gram_tc_kernel<<<grid, 192, smem, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
-    prof_mark("mdta_gram_tc", C, heads, 2.0 * Nimg * P * C * c, double(Nimg) * P * 2 * C * 2 + double(Nimg) * C * c * 4, stream);
+    prof_mark("mdta_gram_tc", C, heads, 2.0 * Nimg * P * C * c,
+              double(Nimg) * P * 2 * C * 2 + double(Nimg) * nchunks * (C * c + 2 * C) * 4, stream);
     return 0;
 }
 
 // ---- fp32 FMA Gram (fp32 precision mode) -----------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) mdta_gram_simt_kernel(const T* __restrict__ qkv, long long ld, int P, int C,
-                                                             int c, int heads, int chunk_px, float* __restrict__ G) {
+                                                             int c, int heads, int chunk_px, float* __restrict__ Gpart,
+                                                             float* __restrict__ ssq_part) {
     constexpr int TP = 16;
     extern __shared__ float sm[];  // qs[TP][c], ks[TP][c]
     float* qs = sm;
@@ -166,6 +217,7 @@ __global__ void __launch_bounds__(256) mdta_gram_simt_kernel(const T* __restrict
     float acc[MAXO];
 #pragma unroll
     for (int m = 0; m < MAXO; ++m) acc[m] = 0.f;
+    float sq = 0.f, sk = 0.f;  // thread t < c: |q_t|^2 and |k_t|^2
     for (int pp = px0; pp < px1; pp += TP) {
         for (int e = threadIdx.x; e < TP * c; e += 256) {
             const int r = e / c, ch = e % c;
@@ -190,55 +242,81 @@ __global__ void __launch_bounds__(256) mdta_gram_simt_kernel(const T* __restrict
                 acc[m] = a;
             }
         }
+        if (threadIdx.x < c) {
+#pragma unroll
+            for (int r = 0; r < TP; ++r) {
+                sq = fmaf(qs[r * c + threadIdx.x], qs[r * c + threadIdx.x], sq);
+                sk = fmaf(ks[r * c + threadIdx.x], ks[r * c + threadIdx.x], sk);
+            }
+        }
         __syncthreads();
     }
-    float* g = G + ((long long)img * heads + head) * nout;
+    const long long slot = ((long long)img * heads + head) * gridDim.x + blockIdx.x;
+    float* g = Gpart + slot * nout;
 #pragma unroll
     for (int m = 0; m < MAXO; ++m) {
         const int o = threadIdx.x + 256 * m;
-        if (o < nout) atomicAdd(g + o, acc[m]);
+        if (o < nout) g[o] = acc[m];
+    }
+    if (threadIdx.x < c) {
+        ssq_part[(slot * 2 + 0) * c + threadIdx.x] = sq;
+        ssq_part[(slot * 2 + 1) * c + threadIdx.x] = sk;
     }
 }
 
-int mdta_gram_simt(const void* qkv, int dt, long long ld, int Nimg, int P, int C, int heads, float* G,
-                   cudaStream_t stream) {
+int mdta_gram_simt(const void* qkv, int dt, long long ld, int Nimg, int P, int C, int heads, int nchunks,
+                   float* Gpart, float* ssq_part, cudaStream_t stream) {
     const int c = C / heads;
-    IRB_REQUIRE(C % heads == 0 && c * c <= 36 * 256, "mdta_gram_simt: channels per head must be <= 96");
-    int chunk = 1024;
-    dim3 grid(ceil_div(P, chunk), heads, Nimg);
+    IRB_REQUIRE(C % heads == 0 && c * c <= 36 * 256 && c <= 256, "mdta_gram_simt: channels per head must be <= 96");
+    IRB_REQUIRE(nchunks >= 1 && nchunks <= 64, "mdta_gram_simt: 1..64 chunks");
+    const int chunk = chunk_px_for(P, nchunks);
+    IRB_REQUIRE((P + chunk - 1) / chunk == nchunks, "mdta_gram_simt: nchunks must come from mdta_nchunks()");
+    dim3 grid(nchunks, heads, Nimg);
     const size_t smem = size_t(2) * 16 * c * sizeof(float);
     if (dt == DT_F32)
-        mdta_gram_simt_kernel<float><<<grid, 256, smem, stream>>>((const float*)qkv, ld, P, C, c, heads, chunk, G);
+        mdta_gram_simt_kernel<float><<<grid, 256, smem, stream>>>((const float*)qkv, ld, P, C, c, heads, chunk, Gpart, ssq_part);
     else
-        mdta_gram_simt_kernel<bf16><<<grid, 256, smem, stream>>>((const bf16*)qkv, ld, P, C, c, heads, chunk, G);
+        mdta_gram_simt_kernel<bf16><<<grid, 256, smem, stream>>>((const bf16*)qkv, ld, P, C, c, heads, chunk, Gpart, ssq_part);
     IRB_CHECK_CUDA(cudaGetLastError());
-    prof_mark("mdta_gram_simt", C, heads, 2.0 * Nimg * P * C * c, double(Nimg) * P * 2 * C * (dt == DT_F32 ? 4 : 2) + double(Nimg) * C * c * 4, stream);
+    prof_mark("mdta_gram_simt", C, heads, 2.0 * Nimg * P * C * c,
+              double(Nimg) * P * 2 * C * (dt == DT_F32 ? 4 : 2) + double(Nimg) * nchunks * (C * c + 2 * C) * 4, stream);
     return 0;
 }
 
-// ---- softmax + fold into project_out ----------------------------------------------------------
-__global__ void __launch_bounds__(256) mdta_softmax_weff_kernel(const float* __restrict__ G,
-                                                                const float* __restrict__ sumsq,
+// ---- fixed-order reduction of the partials + softmax + fold into project_out --------------------
+__global__ void __launch_bounds__(256) mdta_softmax_weff_kernel(const float* __restrict__ Gpart,
+                                                                const float* __restrict__ ssq_part, int nchunks,
                                                                 const float* __restrict__ temperature,
                                                                 const float* __restrict__ Wp, int C, int heads,
                                                                 void* __restrict__ Weff, int w_dt,
                                                                 float* __restrict__ attn_out) {
-    extern __shared__ float attn[];  // [c][c+1]
+    extern __shared__ float attn[];  // [c][c+1] then nrm[2c]
     const int c = C / heads;
     const int head = blockIdx.x, img = blockIdx.y;
     const int ldA = c + 1;
-    const float* g = G + ((long long)img * heads + head) * c * c;
-    const float* ssq = sumsq + (long long)img * 2 * C + head * c;
-    const float* ssk = ssq + C;
+    float* nrm = attn + c * ldA;
+    const long long slot0 = ((long long)img * heads + head) * nchunks;
+    const float* g = Gpart + slot0 * c * c;
+    const float* ss = ssq_part + slot0 * 2 * c;
+    for (int e = threadIdx.x; e < c * c; e += 256) {
+        float a = 0.f;
+        for (int k = 0; k < nchunks; ++k) a += g[(long long)k * c * c + e];
+        attn[(e / c) * ldA + (e % c)] = a;
+    }
+    // F.normalize(dim=-1) divides by max(||.||_2, 1e-12) (restormer_arch.py:121-122)
+    for (int v = threadIdx.x; v < 2 * c; v += 256) {
+        float a = 0.f;
+        for (int k = 0; k < nchunks; ++k) a += ss[(long long)k * 2 * c + v];
+        nrm[v] = fmaxf(sqrtf(a), 1e-12f);
+    }
+    __syncthreads();
     const float temp = __ldg(temperature + head);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // one warp per row i: F.normalize(dim=-1) divides by max(||.||_2, 1e-12) (restormer_arch.py:121-122)
-    for (int i = warp; i < c; i += 8) {
-        const float nq = fmaxf(sqrtf(ssq[i]), 1e-12f);
+    for (int i = warp; i < c; i += 8) {  // one warp per row i
+        const float nq = nrm[i];
         float mx = -INFINITY;
         for (int j = lane; j < c; j += 32) {
-            const float nk = fmaxf(sqrtf(ssk[j]), 1e-12f);
-            const float s = g[i * c + j] / (nq * nk) * temp;
+            const float s = attn[i * ldA + j] / (nq * nrm[c + j]) * temp;
             attn[i * ldA + j] = s;
             mx = fmaxf(mx, s);
         }
@@ -268,15 +346,19 @@ __global__ void __launch_bounds__(256) mdta_softmax_weff_kernel(const float* __r
     }
 }
 
-int mdta_softmax_weff(const float* G, const float* sumsq, const float* temperature, const float* Wp, int Nimg, int C,
-                      int heads, void* Weff, int w_dt, float* attn_out, cudaStream_t stream) {
+int mdta_softmax_weff(const float* Gpart, const float* ssq_part, int nchunks, const float* temperature,
+                      const float* Wp, int Nimg, int C, int heads, void* Weff, int w_dt, float* attn_out,
+                      cudaStream_t stream) {
     const int c = C / heads;
     IRB_REQUIRE(C % heads == 0 && c <= 104, "mdta_softmax_weff: channels per head too large");
-    const size_t smem = size_t(c) * (c + 1) * sizeof(float);
+    IRB_REQUIRE(nchunks >= 1, "mdta_softmax_weff: nchunks");
+    const size_t smem = (size_t(c) * (c + 1) + 2 * c) * sizeof(float);
     dim3 grid(heads, Nimg);
-    mdta_softmax_weff_kernel<<<grid, 256, smem, stream>>>(G, sumsq, temperature, Wp, C, heads, Weff, w_dt, attn_out);
+    mdta_softmax_weff_kernel<<<grid, 256, smem, stream>>>(Gpart, ssq_part, nchunks, temperature, Wp, C, heads, Weff,
+                                                          w_dt, attn_out);
     IRB_CHECK_CUDA(cudaGetLastError());
-    prof_mark("mdta_softmax_weff", C, heads, 2.0 * Nimg * C * C * c, double(Nimg) * (C * c * 4.0 + C * C * (w_dt == DT_BF16 ? 2 : 4)) + C * C * 4.0, stream);
+    prof_mark("mdta_softmax_weff", C, heads, 2.0 * Nimg * C * C * c,
+              double(Nimg) * (nchunks * (C * c + 2.0 * C) * 4.0 + C * C * (w_dt == DT_BF16 ? 2 : 4)) + C * C * 4.0, stream);
     return 0;
 }
 

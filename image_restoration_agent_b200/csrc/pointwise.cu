@@ -261,6 +261,8 @@ int dwconv3x3(const void* x, int dt, long long ldx, void* y, long long ldy, int 
     IRB_REQUIRE(C % 4 == 0 && ldx % 4 == 0 && ldy % 4 == 0, "dwconv3x3: C and strides must be multiples of 4");
     IRB_REQUIRE(sumsq_channels % 4 == 0 && sumsq_channels <= C && sumsq_channels <= 8192, "dwconv3x3: bad sumsq_channels");
     if (dt == DT_F32) return dwconv_launch<float>(false, x, ldx, y, ldy, Nimg, H, W, C, 0, wt, C, sumsq, sumsq_channels, stream);
+    if (!sumsq && ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0)
+        return dwconv3x3_bf16_tma((const bf16*)x, ldx, (bf16*)y, ldy, Nimg, H, W, C, wt, stream);
     return dwconv_launch<bf16>(false, x, ldx, y, ldy, Nimg, H, W, C, 0, wt, C, sumsq, sumsq_channels, stream);
 }
 
@@ -268,6 +270,8 @@ int dwconv3x3_gate(const void* x, int dt, long long ldx, void* y, long long ldy,
                    const float* wt, cudaStream_t stream) {
     IRB_REQUIRE(hp % 4 == 0 && ldx % 4 == 0 && ldy % 4 == 0, "dwconv3x3_gate: hp and strides must be multiples of 4");
     if (dt == DT_F32) return dwconv_launch<float>(true, x, ldx, y, ldy, Nimg, H, W, hp, hp, wt, 2 * hp, nullptr, 0, stream);
+    if (ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0)
+        return dwconv3x3_gate_bf16_tma((const bf16*)x, ldx, (bf16*)y, ldy, Nimg, H, W, hp, wt, stream);
     return dwconv_launch<bf16>(true, x, ldx, y, ldy, Nimg, H, W, hp, hp, wt, 2 * hp, nullptr, 0, stream);
 }
 

@@ -199,7 +199,8 @@ void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
             hid = std::max(hid, Ps[l] * 2 * hp * E);
             gat = std::max(gat, Ps[l] * hp * E);
             weff = std::max(weff, size_t(n) * C * C * E);
-            gs = std::max(gs, (size_t(n) * C * (C / heads) + size_t(n) * 2 * C) * 4);
+            const int P = int(Ps[l] / n);
+            gs = std::max(gs, size_t(n) * mdta_nchunks(P, heads, n) * (size_t(C) * (C / heads) + 2 * C) * 4);
         }
     }
     w.ln = b.take(ln);
@@ -244,17 +245,15 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
     // --- x = x + project_out(attn(norm1(x))) ---
     IRB_TRY(layernorm(x, dt, ldx, ws.ln, dt, C, P, C, w.n1w, w.n1b, mode, 1e-5f, s));
     IRB_TRY(run_gemm(ws.ln, C, P, C, w.qkv_w, C, 3 * C, 3 * C, make_epi(ws.qkv_pre, 3 * C, dt), s));
-    const size_t g_floats = size_t(n) * heads * c * c;
-    float* G = ws.G;
-    float* sumsq = ws.G + g_floats;
-    IRB_CHECK_CUDA(cudaMemsetAsync(G, 0, (g_floats + size_t(n) * 2 * C) * 4, s));
-    prof_mark("memset_gram", C, heads, 0.0, (g_floats + double(n) * 2 * C) * 4, s);
-    IRB_TRY(dwconv3x3(ws.qkv_pre, dt, 3 * C, ws.qkv, 3 * C, n, H, W, 3 * C, w.qkv_dw, sumsq, 2 * C, s));
+    const int nch = mdta_nchunks(H * W, heads, n);
+    float* G = ws.G;                                       // [n][heads][nch][c][c]
+    float* ssq = ws.G + size_t(n) * heads * nch * c * c;   // [n][heads][nch][2][c]
+    IRB_TRY(dwconv3x3(ws.qkv_pre, dt, 3 * C, ws.qkv, 3 * C, n, H, W, 3 * C, w.qkv_dw, nullptr, 0, s));
     if (dt == DT_BF16)
-        IRB_TRY(mdta_gram_tc((const bf16*)ws.qkv, 3 * C, n, H * W, C, heads, G, s));
+        IRB_TRY(mdta_gram_tc((const bf16*)ws.qkv, 3 * C, n, H * W, C, heads, nch, G, ssq, s));
     else
-        IRB_TRY(mdta_gram_simt(ws.qkv, DT_F32, 3 * C, n, H * W, C, heads, G, s));
-    IRB_TRY(mdta_softmax_weff(G, sumsq, w.temp, w.proj_w, n, C, heads, ws.weff, dt, nullptr, s));
+        IRB_TRY(mdta_gram_simt(ws.qkv, DT_F32, 3 * C, n, H * W, C, heads, nch, G, ssq, s));
+    IRB_TRY(mdta_softmax_weff(G, ssq, nch, w.temp, w.proj_w, n, C, heads, ws.weff, dt, nullptr, s));
     {
         Epi e = make_epi(x, ldx, dt);
         e.res = x;

@@ -79,9 +79,9 @@ def pack_dw_weight(w: torch.Tensor) -> torch.Tensor:
 
 def dwconv3x3(x, w9c, sumsq_channels=0):
     n, H, W, Cc = x.shape
-    y = torch.empty_like(x)
+    y = torch.empty((n, H, W, Cc), device=x.device, dtype=x.dtype)
     ss = torch.zeros((n, sumsq_channels), device=x.device, dtype=torch.float32) if sumsq_channels else None
-    check(_lib.load().irb_dwconv3x3(x.data_ptr(), _dt(x), Cc, y.data_ptr(), Cc, n, H, W, Cc, w9c.data_ptr(), _ptr(ss),
+    check(_lib.load().irb_dwconv3x3(x.data_ptr(), _dt(x), x.stride(-2), y.data_ptr(), Cc, n, H, W, Cc, w9c.data_ptr(), _ptr(ss),
                                     sumsq_channels, _stream()))
     return (y, ss) if sumsq_channels else y
 
@@ -96,22 +96,27 @@ def gdfn_dw_gate(x, w9c):
 
 
 def mdta_gram(qkv, heads):
+    """-> (Gpart [n, heads, nchunks, c, c], ssq_part [n, heads, nchunks, 2, c]): per-chunk partial sums."""
     n, H, W, C3 = qkv.shape
     Cc = C3 // 3
     c = Cc // heads
-    G = torch.zeros((n, heads, c, c), device=qkv.device, dtype=torch.float32)
-    check(_lib.load().irb_mdta_gram(qkv.data_ptr(), _dt(qkv), C3, n, H * W, Cc, heads, G.data_ptr(), _stream()))
-    return G
+    lib = _lib.load()
+    nch = lib.irb_mdta_nchunks(H * W, heads, n)
+    G = torch.full((n, heads, nch, c, c), float("nan"), device=qkv.device, dtype=torch.float32)
+    ss = torch.full((n, heads, nch, 2, c), float("nan"), device=qkv.device, dtype=torch.float32)
+    check(lib.irb_mdta_gram(qkv.data_ptr(), _dt(qkv), C3, n, H * W, Cc, heads, nch, G.data_ptr(), ss.data_ptr(),
+                            _stream()))
+    return G, ss
 
 
-def mdta_attn(G, sumsq, temperature, wproj, out_dtype):
-    n, heads, c, _ = G.shape
+def mdta_attn(Gpart, ssq_part, temperature, wproj, out_dtype):
+    n, heads, nch, c, _ = Gpart.shape
     Cc = heads * c
-    weff = torch.empty((n, Cc, Cc), device=G.device, dtype=out_dtype)
-    attn = torch.empty_like(G)
-    check(_lib.load().irb_mdta_attn(G.data_ptr(), sumsq.data_ptr(), temperature.data_ptr(), wproj.data_ptr(), n, Cc,
-                                    heads, weff.data_ptr(), BF16 if out_dtype == torch.bfloat16 else F32,
-                                    attn.data_ptr(), _stream()))
+    weff = torch.empty((n, Cc, Cc), device=Gpart.device, dtype=out_dtype)
+    attn = torch.empty((n, heads, c, c), device=Gpart.device, dtype=torch.float32)
+    check(_lib.load().irb_mdta_attn(Gpart.data_ptr(), ssq_part.data_ptr(), nch, temperature.data_ptr(),
+                                    wproj.data_ptr(), n, Cc, heads, weff.data_ptr(),
+                                    BF16 if out_dtype == torch.bfloat16 else F32, attn.data_ptr(), _stream()))
     return weff, attn
 
 

@@ -135,12 +135,18 @@ int irb_dwconv3x3(const void* d_x, int dtype, long long ldx, void* d_y, long lon
 /* GDFN: y[.,c] = gelu(dw(x)[.,c]) * dw(x)[.,hp+c], c < hp; d_w fp32 [9][2*hp] */
 int irb_gdfn_dw_gate(const void* d_x, int dtype, long long ldx, void* d_y, long long ldy, int n, int H, int W, int hp,
                      const float* d_w, void* stream);
-/* MDTA Gram: d_G[n][heads][c][c] += sum_p q k^T over a channels-last qkv tensor (q | k | v), d_G pre-zeroed */
-int irb_mdta_gram(const void* d_qkv, int dtype, long long ld, int n, int P, int C, int heads, float* d_G,
+/* MDTA Gram over a channels-last qkv tensor (q | k | v): the P pixels are split into nchunks =
+ * irb_mdta_nchunks(P, heads, n) chunks and every chunk writes its own slot (no atomics -> bit-reproducible):
+ *   d_Gpart   [n][heads][nchunks][c][c]   partial sum_p q k^T
+ *   d_ssq_part[n][heads][nchunks][2][c]   partial sum_p q^2 (then k^2): the F.normalize denominators */
+int irb_mdta_nchunks(int P, int heads, int n);
+int irb_mdta_gram(const void* d_qkv, int dtype, long long ld, int n, int P, int C, int heads, int nchunks,
+                  float* d_Gpart, float* d_ssq_part, void* stream);
+/* sums the slots in order, softmax(G / (|q||k|) * temperature), folded into project_out:
+ * d_weff[n][C][C] (dtype), d_attn optional fp32 [n][heads][c][c] */
+int irb_mdta_attn(const float* d_Gpart, const float* d_ssq_part, int nchunks, const float* d_temperature,
+                  const float* d_wproj, int n, int C, int heads, void* d_weff, int dtype, float* d_attn,
                   void* stream);
-/* softmax(G / (|q||k|) * temperature) folded into project_out: d_weff[n][C][C] (dtype), d_attn optional fp32 */
-int irb_mdta_attn(const float* d_G, const float* d_sumsq, const float* d_temperature, const float* d_wproj, int n,
-                  int C, int heads, void* d_weff, int dtype, float* d_attn, void* stream);
 /* overlap-blend stitch of channels-last fp32 tiles [ny*nx][th*sf][tw*sf][c] (host index lists) */
 int irb_stitch(const float* d_tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx,
                int h, int w, int crop_h, int crop_w, float* d_out_f32, uint8_t* d_out_u8, int reverse_channels,

@@ -99,6 +99,18 @@ def test_dwconv3x3_and_sumsq(dt, tol, n, H, W, Cc):
     y, ss = ops.dwconv3x3(x, ops.pack_dw_weight(w), sumsq_channels=sc)
     close(y, ref.permute(0, 2, 3, 1), tol)
     close(ss, (ref[:, :sc] ** 2).sum((2, 3)), 1e-4)
+    close(ops.dwconv3x3(x, ops.pack_dw_weight(w)), ref.permute(0, 2, 3, 1), tol)  # bf16: the TMA-fed kernel
+
+
+@pytest.mark.parametrize("n,H,W,Cc", [(3, 100, 70, 96), (2, 64, 64, 288), (1, 9, 33, 16), (2, 17, 31, 200)])
+def test_dwconv3x3_tma_ragged_tiles(n, H, W, Cc):
+    """bf16 TMA kernel on sizes that are not multiples of the 32x8 tile / 64-channel chunk, on a channel slice."""
+    from image_restoration_agent_b200 import ops
+    big = torch.randn(n, H, W, Cc + 8, device="cuda").bfloat16()
+    x = big[..., :Cc]  # row stride Cc + 8
+    w = torch.randn(Cc, 1, 3, 3, device="cuda") / 3
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w, padding=1, groups=Cc).permute(0, 2, 3, 1)
+    close(ops.dwconv3x3(x, ops.pack_dw_weight(w)), ref, 1e-2)
 
 
 @pytest.mark.parametrize("dt,tol", [(torch.float32, 1e-5), (torch.bfloat16, 1e-2)])
@@ -123,18 +135,23 @@ def test_mdta_gram_softmax_fold(dt, tol, n, H, W, Cc, heads):
     q = qkv[..., :Cc].float().reshape(n, H * W, heads, c)
     k = qkv[..., Cc:2 * Cc].float().reshape(n, H * W, heads, c)
     ref = torch.einsum("nphi,nphj->nhij", q, k)
-    close(ops.mdta_gram(qkv, heads), ref, tol)
-    ss = torch.cat([(q ** 2).sum(1).reshape(n, Cc), (k ** 2).sum(1).reshape(n, Cc)], 1).contiguous()
+    Gp, sp = ops.mdta_gram(qkv, heads)
+    close(Gp.sum(2), ref, tol)
+    ss = torch.stack([(q ** 2).sum(1), (k ** 2).sum(1)], 2).contiguous()  # [n, heads, 2, c]
+    close(sp.sum(2), ss, tol)
+    Gp2, sp2 = ops.mdta_gram(qkv, heads)
+    assert torch.equal(Gp, Gp2) and torch.equal(sp, sp2)  # no atomics: bit-reproducible
     temp = torch.rand(heads, device="cuda") * 3 + 0.5
     wproj = torch.randn(Cc, Cc, device="cuda") / Cc ** 0.5
-    weff, attn = ops.mdta_attn(ref.contiguous(), ss, temp, wproj, torch.float32)
+    ss = ss.unsqueeze(2).contiguous()                                        # one chunk
+    weff, attn = ops.mdta_attn(ref.unsqueeze(2).contiguous(), ss, temp, wproj, torch.float32)
     qn, kn = F.normalize(q.permute(0, 2, 3, 1), dim=-1), F.normalize(k.permute(0, 2, 3, 1), dim=-1)
     a_ref = ((qn @ kn.transpose(-2, -1)) * temp.view(1, heads, 1, 1)).softmax(-1)
     close(attn, a_ref, 1e-4)
     close(weff, torch.einsum("ohi,nhij->nohj", wproj.reshape(Cc, heads, c), a_ref).reshape(n, Cc, Cc), 1e-4)
     # all-zero q row: F.normalize's eps path (max(||q||, 1e-12)) must not produce NaN
     z = torch.zeros_like(ss)
-    weff0, attn0 = ops.mdta_attn(torch.zeros_like(ref), z, temp, wproj, torch.float32)
+    weff0, attn0 = ops.mdta_attn(torch.zeros_like(ref).unsqueeze(2).contiguous(), z, temp, wproj, torch.float32)
     assert torch.isfinite(attn0).all() and torch.allclose(attn0, torch.full_like(attn0, 1.0 / c))
 
 
