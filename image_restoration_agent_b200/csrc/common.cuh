@@ -68,9 +68,27 @@ struct Epi {
     // [B,H/2,W/2,4N]. ps_w / ps_h are the width / height the convolution runs at.
     int ps;
     int ps_h, ps_w;
+    // optional fused LayerNorm of the GEMM's A operand (weights pre-multiplied by the LN gain, see row_stats()):
+    //   acc <- rstd[row] * (acc - mu[row] * ln_colsum[col])      (WithBias / nn.LayerNorm; the LN bias is folded
+    //   acc <- rstd[row] * acc                                   (BiasFree: ln_colsum == nullptr)     into `bias`)
+    const float2* ln_stats;   // [rows] (mu, rstd) or nullptr
+    const float* ln_colsum;   // [N] sum_k W'[n,k] of the (rounded) folded weights
 };
 
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
+
+// exact-erf GELU with erf from Abramowitz-Stegun 7.1.26 (|abs err| <= 1.5e-7, i.e. fp32 round-off level)
+__device__ __forceinline__ float gelu_as(float x) {
+    const float z = fabsf(x) * 0.70710678118654752440f;
+    const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+    float poly = fmaf(1.061405429f, t, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    poly *= t;
+    const float e = 1.0f - poly * __expf(-z * z);  // erf(|x|/sqrt2)
+    return 0.5f * x + 0.5f * fabsf(x) * e;        // 0.5*x*(1 + sign(x)*erf(|x|/sqrt2))
+}
 
 __device__ __forceinline__ float epi_act(const Epi& e, float x) {
     if (e.act == ACT_GELU) return gelu_erf(x);
@@ -105,6 +123,13 @@ __device__ __forceinline__ void epi_apply_store(const Epi& e, long long row, int
                                                 int b = 0, int y = 0, int x = 0) {
     const int nvalid = min(NV, ncols_total - col0);
     if (nvalid <= 0) return;
+    if (e.ln_stats) {
+        const float2 st = __ldg(e.ln_stats + row);
+#pragma unroll
+        for (int i = 0; i < NV; ++i)
+            if (i < nvalid)
+                v[i] = e.ln_colsum ? st.y * (v[i] - st.x * __ldg(e.ln_colsum + col0 + i)) : st.y * v[i];
+    }
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
         if (i < nvalid) {

@@ -47,19 +47,6 @@ __device__ __forceinline__ void ffma2(f32x2& acc, f32x2 a, f32x2 b) {
     asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
 }
 
-// exact-erf GELU with erf from Abramowitz-Stegun 7.1.26 (|abs err| <= 1.5e-7, i.e. fp32 round-off level)
-__device__ __forceinline__ float gelu_as(float x) {
-    const float z = fabsf(x) * 0.70710678118654752440f;
-    const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
-    float poly = fmaf(1.061405429f, t, -1.453152027f);
-    poly = fmaf(poly, t, 1.421413741f);
-    poly = fmaf(poly, t, -0.284496736f);
-    poly = fmaf(poly, t, 0.254829592f);
-    poly *= t;
-    const float e = 1.0f - poly * __expf(-z * z);  // erf(|x|/sqrt2)
-    return 0.5f * x + 0.5f * fabsf(x) * e;        // 0.5*x*(1 + sign(x)*erf(|x|/sqrt2))
-}
-
 template <bool GATE>
 __global__ void __launch_bounds__(288, 1) dw3x3_tma_kernel(const __grid_constant__ DwParams p) {
     constexpr int NS = GATE ? 2 : 1;

@@ -27,28 +27,113 @@ static constexpr int kABytes = kTileM * 128;      // 16 KB
 struct alignas(64) TcGemmParams {
     CUtensorMap tmA;
     CUtensorMap tmB;
+    CUtensorMap tmC;  // output (bf16): mode 0 {N, M, batch} box {64, 32, 1}; mode 1 {N, W, H, Nimg} box {64, bw, 32/bw, 1}
+    int tma_store;    // 1: epilogue stages 32-row x 64-column blocks in shared memory and stores them with TMA
     int mode;
     int M;        // rows per batch (mode 0)
     int N;        // valid output columns
-    int BN;       // columns per CTA (multiple of 16, <= 256)
+    int BN;       // columns per tile (multiple of 16, <= 256)
     int ktiles;   // 64-wide K chunks per tap
     int taps;     // 1 or 9
     int kpad;     // K distance between taps inside Wt
     int H, W, BW, BH, tiles_x;
     int b_rows_per_batch;
     int stages;
-    int tmem_cols;
+    int tmem_cols;    // 2 accumulators of acc_stride columns
+    int acc_stride;
+    int tiles_m, tiles_n, total;  // work items: total = batch * tiles_m * tiles_n, n fastest
     Epi epi;
 };
 
-__global__ void __launch_bounds__(192) tc_gemm_kernel(const __grid_constant__ TcGemmParams p) {
+static constexpr int kGemmThreads = 320;  // warp 0: TMA, warp 1: MMA, warps 2..9: epilogue
+
+// Lean epilogue math for 16 columns of one row: the per-column vectors come from shared memory (staged once
+// per tile), the per-row LayerNorm fold is two FMAs per element:
+//   y = act(acc * a + (b * colsum[col] + bias[col])) + res         a = rstd (or 1), b = -mu * rstd (or 0)
+template <int ACT>
+__device__ __forceinline__ void epi_math16(const Epi& e, long long row, int col0, int res_cols, float* v,
+                                           const float* s_bias, const float* s_cs, float a, float b) {
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+        const float4 bi = *reinterpret_cast<const float4*>(s_bias + j);
+        const float4 cs = *reinterpret_cast<const float4*>(s_cs + j);
+        v[j + 0] = fmaf(v[j + 0], a, fmaf(b, cs.x, bi.x));
+        v[j + 1] = fmaf(v[j + 1], a, fmaf(b, cs.y, bi.y));
+        v[j + 2] = fmaf(v[j + 2], a, fmaf(b, cs.z, bi.z));
+        v[j + 3] = fmaf(v[j + 3], a, fmaf(b, cs.w, bi.w));
+    }
+    if (ACT == ACT_GELU) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = gelu_as(v[j]);  // bf16 output: 1.5e-7 abs error is invisible
+    } else if (ACT == ACT_LRELU) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = v[j] > 0.f ? v[j] : v[j] * e.slope;
+    }
+    if (res_cols > 0 && res_cols < 16) {  // ragged last group: element-wise
+        const long long rbase = row * e.ldr + col0;
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+            if (j < res_cols) v[j] += ld_as_float(e.res, rbase + j, e.res_dt);
+    } else if (res_cols >= 16) {
+        const long long rbase = row * e.ldr + col0;
+        if (e.res_dt == DT_BF16) {
+            const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.res) + rbase);
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const uint4 u = __ldg(rp + q);
+                float x0, x1;
+                unpack_bf16x2(u.x, x0, x1); v[q * 8 + 0] += x0; v[q * 8 + 1] += x1;
+                unpack_bf16x2(u.y, x0, x1); v[q * 8 + 2] += x0; v[q * 8 + 3] += x1;
+                unpack_bf16x2(u.z, x0, x1); v[q * 8 + 4] += x0; v[q * 8 + 5] += x1;
+                unpack_bf16x2(u.w, x0, x1); v[q * 8 + 6] += x0; v[q * 8 + 7] += x1;
+            }
+        } else {
+            const float4* rp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(e.res) + rbase);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float4 u = __ldg(rp + q);
+                v[q * 4 + 0] += u.x; v[q * 4 + 1] += u.y; v[q * 4 + 2] += u.z; v[q * 4 + 3] += u.w;
+            }
+        }
+    }
+}
+template <int ACT>
+__device__ __forceinline__ void epi_fast16(const Epi& e, long long row, int col0, float* v, const float* s_bias,
+                                           const float* s_cs, float a, float b) {
+    epi_math16<ACT>(e, row, col0, e.res != nullptr ? 16 : 0, v, s_bias, s_cs, a, b);
+    const long long obase = row * e.ldo + col0;
+    if (e.out_dt == DT_BF16) {
+        uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(e.out) + obase);
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            uint4 u;
+            u.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]);
+            u.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+            u.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]);
+            u.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+            op[q] = u;
+        }
+    } else {
+        float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + obase);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) op[q] = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+    }
+}
+
+// Persistent CTA: walks work items w = blockIdx.x, blockIdx.x + gridDim.x, ...  Two TMEM accumulators let the
+// epilogue of tile i overlap the MMAs of tile i+1; the shared-memory ring runs across tile boundaries.
+__global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_constant__ TcGemmParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int stage_bytes = kABytes + p.BN * 128;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.stages * stage_bytes);
     uint64_t* empty_bar = full_bar + p.stages;
-    uint64_t* accum_bar = empty_bar + p.stages;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+    uint64_t* tfull_bar = empty_bar + p.stages;   // [2] accumulator ready (MMA -> epilogue)
+    uint64_t* tempty_bar = tfull_bar + 2;         // [2] accumulator drained (epilogue -> MMA)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+    float* colvec = reinterpret_cast<float*>(tmem_slot + 4);  // [2 tiles][bias | colsum][256], 16-byte aligned
+    // 8 epilogue warps x 4 KB staging blocks for TMA stores ([32 rows][64 bf16], 128B-swizzled), 1024-aligned
+    uint8_t* staging = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(colvec + 1024) + 1023) & ~uintptr_t(1023));
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -57,11 +142,15 @@ __global__ void __launch_bounds__(192) tc_gemm_kernel(const __grid_constant__ Tc
         if (lane == 0) {
             tma_prefetch_desc(&p.tmA);
             tma_prefetch_desc(&p.tmB);
+            if (p.tma_store) tma_prefetch_desc(&p.tmC);
             for (int s = 0; s < p.stages; ++s) {
                 mbar_init(&full_bar[s], 1);
                 mbar_init(&empty_bar[s], 1);
             }
-            mbar_init(accum_bar, 1);
+            for (int a = 0; a < 2; ++a) {
+                mbar_init(&tfull_bar[a], 1);
+                mbar_init(&tempty_bar[a], 8);
+            }
             fence_mbar_init();
         }
         __syncwarp();
@@ -72,83 +161,193 @@ __global__ void __launch_bounds__(192) tc_gemm_kernel(const __grid_constant__ Tc
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-
-    const int n0 = blockIdx.y * p.BN;
     const int total_it = p.taps * p.ktiles;
-
-    // tile origin
-    int x0 = 0, y0 = 0;
-    if (p.mode == 1) {
-        const int ty = blockIdx.x / p.tiles_x, tx = blockIdx.x % p.tiles_x;
-        x0 = tx * p.BW;
-        y0 = ty * p.BH;
-    }
 
     if (warp == 0 && lane == 0) {
         // ===== TMA producer =====
         int it = 0;
-        for (int tap = 0; tap < p.taps; ++tap) {
-            const int dy = (p.taps == 9) ? tap / 3 - 1 : 0;
-            const int dx = (p.taps == 9) ? tap % 3 - 1 : 0;
-            for (int kc = 0; kc < p.ktiles; ++kc, ++it) {
-                const int s = it % p.stages;
-                const uint32_t ph = (it / p.stages) & 1;
-                mbar_wait(&empty_bar[s], ph ^ 1);
-                uint8_t* sa = smem + s * stage_bytes;
-                uint8_t* sb = sa + kABytes;
-                mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
-                if (p.mode == 0)
-                    tma_load_3d(sa, &p.tmA, &full_bar[s], kc * kTileK, blockIdx.x * kTileM, blockIdx.z);
-                else
-                    tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx, y0 + dy, blockIdx.z);
-                tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK,
-                            blockIdx.z * p.b_rows_per_batch + n0);
+        for (int w = blockIdx.x; w < p.total; w += gridDim.x) {
+            const int nt = w % p.tiles_n;
+            const int mt = (w / p.tiles_n) % p.tiles_m;
+            const int z = w / (p.tiles_n * p.tiles_m);
+            const int n0 = nt * p.BN;
+            int x0 = 0, y0 = 0;
+            if (p.mode == 1) {
+                x0 = (mt % p.tiles_x) * p.BW;
+                y0 = (mt / p.tiles_x) * p.BH;
+            }
+            for (int tap = 0; tap < p.taps; ++tap) {
+                const int dy = (p.taps == 9) ? tap / 3 - 1 : 0;
+                const int dx = (p.taps == 9) ? tap % 3 - 1 : 0;
+                for (int kc = 0; kc < p.ktiles; ++kc, ++it) {
+                    const int s = it % p.stages;
+                    const uint32_t ph = (it / p.stages) & 1;
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    uint8_t* sa = smem + s * stage_bytes;
+                    uint8_t* sb = sa + kABytes;
+                    mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
+                    if (p.mode == 0)
+                        tma_load_3d(sa, &p.tmA, &full_bar[s], kc * kTileK, mt * kTileM, z);
+                    else
+                        tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx, y0 + dy, z);
+                    tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK, z * p.b_rows_per_batch + n0);
+                }
             }
         }
     } else if (warp == 1 && lane == 0) {
         // ===== MMA issuer =====
         const uint32_t idesc = make_idesc_bf16(kTileM, p.BN, 0, 0);
-        for (int it = 0; it < total_it; ++it) {
-            const int s = it % p.stages;
-            const uint32_t ph = (it / p.stages) & 1;
-            mbar_wait(&full_bar[s], ph);
+        int it = 0, t = 0;
+        for (int w = blockIdx.x; w < p.total; w += gridDim.x, ++t) {
+            const int a = t & 1;
+            mbar_wait(&tempty_bar[a], ((t >> 1) & 1) ^ 1);
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(smem + s * stage_bytes);
-            const uint32_t b_addr = a_addr + kABytes;
+            const uint32_t tacc = tmem_base + a * p.acc_stride;
+            for (int i = 0; i < total_it; ++i, ++it) {
+                const int s = it % p.stages;
+                const uint32_t ph = (it / p.stages) & 1;
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(smem + s * stage_bytes);
+                const uint32_t b_addr = a_addr + kABytes;
 #pragma unroll
-            for (int k = 0; k < kTileK / 16; ++k) {
-                const uint64_t adesc = make_sdesc_sw128(a_addr + k * 32, 16, 1024);
-                const uint64_t bdesc = make_sdesc_sw128(b_addr + k * 32, 16, 1024);
-                umma_bf16(tmem_base, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+                for (int k = 0; k < kTileK / 16; ++k) {
+                    const uint64_t adesc = make_sdesc_sw128(a_addr + k * 32, 16, 1024);
+                    const uint64_t bdesc = make_sdesc_sw128(b_addr + k * 32, 16, 1024);
+                    umma_bf16(tacc, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
             }
-            umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
+            umma_commit(&tfull_bar[a]);  // accumulator complete
         }
-        umma_commit(accum_bar);  // accumulator complete
     } else if (warp >= 2) {
-        // ===== epilogue: TMEM -> registers -> global =====
-        mbar_wait(accum_bar, 0);
-        tc_fence_after();
-        const int q = warp & 3;  // TMEM lane quarter this warp may access
+        // ===== epilogue: TMEM -> registers -> global. Warp e owns TMEM lane quarter (warp & 3); the two warps of
+        // a quarter split the tile's columns. =====
+        const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
         const int r = q * 32 + lane;
-        long long grow;
-        bool valid;
-        int py = 0, px = 0;
-        if (p.mode == 0) {
-            const int m = blockIdx.x * kTileM + r;
-            valid = m < p.M;
-            grow = (long long)blockIdx.z * p.M + m;
-        } else {
-            py = y0 + r / p.BW;
-            px = x0 + r % p.BW;
-            valid = (py < p.H) && (px < p.W);
-            grow = ((long long)blockIdx.z * p.H + py) * p.W + px;
+        const int ncol16 = p.BN >> 4;                 // 16-column groups per tile
+        const int g0 = half ? (ncol16 + 1) / 2 : 0;   // this warp's groups [g0, g1)
+        const int g1 = half ? ncol16 : (ncol16 + 1) / 2;
+        const int et = threadIdx.x - 64;  // 0..255
+        // fast path: aligned vector access for 16-column groups, no pixel shuffle / post scale
+        const bool vec_ok = p.epi.ps == 0 && p.epi.post_scale == 1.0f && p.epi.post_shift == nullptr &&
+                            (p.epi.out_dt == DT_BF16 ? (p.epi.ldo % 8 == 0) : (p.epi.ldo % 4 == 0)) &&
+                            (reinterpret_cast<uintptr_t>(p.epi.out) % 16 == 0) &&
+                            (!p.epi.res || ((p.epi.res_dt == DT_BF16 ? (p.epi.ldr % 8 == 0) : (p.epi.ldr % 4 == 0)) &&
+                                            reinterpret_cast<uintptr_t>(p.epi.res) % 16 == 0));
+        int t = 0;
+        for (int w = blockIdx.x; w < p.total; w += gridDim.x, ++t) {
+            const int nt = w % p.tiles_n;
+            const int mt = (w / p.tiles_n) % p.tiles_m;
+            const int z = w / (p.tiles_n * p.tiles_m);
+            const int n0 = nt * p.BN;
+            const int a = t & 1;
+            // stage this tile's per-column vectors (double-buffered by tile parity; one barrier per tile)
+            float* s_bias = colvec + a * 512;
+            float* s_cs = s_bias + 256;
+            if (et < p.BN) {
+                const int col = n0 + et;
+                s_bias[et] = (p.epi.bias && col < p.N) ? __ldg(p.epi.bias + col) : 0.f;
+                s_cs[et] = (p.epi.ln_colsum && col < p.N) ? __ldg(p.epi.ln_colsum + col) : 0.f;
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            long long grow;
+            bool valid;
+            int py = 0, px = 0;
+            if (p.mode == 0) {
+                const int m = mt * kTileM + r;
+                valid = m < p.M;
+                grow = (long long)z * p.M + m;
+            } else {
+                py = (mt / p.tiles_x) * p.BH + r / p.BW;
+                px = (mt % p.tiles_x) * p.BW + r % p.BW;
+                valid = (py < p.H) && (px < p.W);
+                grow = ((long long)z * p.H + py) * p.W + px;
+            }
+            mbar_wait(&tfull_bar[a], (t >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + a * p.acc_stride + (uint32_t(q * 32) << 16);
+            float fa = 1.f, fb = 0.f;
+            if (p.epi.ln_stats && valid) {
+                const float2 st = __ldg(p.epi.ln_stats + grow);
+                fa = st.y;
+                fb = p.epi.ln_colsum ? -st.x * st.y : 0.f;
+            }
+            if (p.tma_store) {
+                // ---- 64-column blocks: TMEM -> registers (math) -> swizzled smem block -> TMA store ----
+                const int nblk = (p.BN + 63) >> 6;
+                const int b0 = half ? (nblk + 1) / 2 : 0, b1 = half ? nblk : (nblk + 1) / 2;
+                uint8_t* stg = staging + (warp - 2) * 4096;
+                const bool has_res = p.epi.res != nullptr && valid;
+                for (int blk = b0; blk < b1; ++blk) {
+                    const int cb = blk * 64;
+                    if (n0 + cb >= p.N) break;  // warp-uniform
+                    const int ng = min(4, (p.BN - cb) >> 4);
+                    uint32_t pk[32];
+#pragma unroll
+                    for (int gi = 0; gi < 4; ++gi) {
+                        if (gi < ng) {
+                            float v[16];
+                            tmem_ld16(taddr + cb + gi * 16, v);
+                            const int col0 = n0 + cb + gi * 16;
+                            const int lr = has_res ? min(16, p.N - col0) : 0;
+                            if (p.epi.act == ACT_GELU)
+                                epi_math16<ACT_GELU>(p.epi, grow, col0, lr, v, s_bias + cb + gi * 16, s_cs + cb + gi * 16, fa, fb);
+                            else if (p.epi.act == ACT_LRELU)
+                                epi_math16<ACT_LRELU>(p.epi, grow, col0, lr, v, s_bias + cb + gi * 16, s_cs + cb + gi * 16, fa, fb);
+                            else
+                                epi_math16<ACT_NONE>(p.epi, grow, col0, lr, v, s_bias + cb + gi * 16, s_cs + cb + gi * 16, fa, fb);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) pk[gi * 8 + j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+                        }
+                    }
+                    // the previous TMA store of this warp must have finished READING the staging block
+                    if (lane == 0) bulk_wait_read0();
+                    __syncwarp();
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        if (c < 2 * ng) {
+                            uint4 u = make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
+                            *reinterpret_cast<uint4*>(stg + lane * 128 + ((c ^ (lane & 7)) << 4)) = u;
+                        }
+                    }
+                    fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (p.mode == 0) {
+                            tma_store_3d(&p.tmC, stg, n0 + cb, mt * kTileM + q * 32, z);
+                        } else {
+                            const int r0 = q * 32;
+                            tma_store_4d(&p.tmC, stg, n0 + cb, (mt % p.tiles_x) * p.BW + r0 % p.BW,
+                                         (mt / p.tiles_x) * p.BH + r0 / p.BW, z);
+                        }
+                        bulk_commit();
+                    }
+                }
+            } else {
+            for (int g = g0; g < g1; ++g) {
+                float v[16];
+                tmem_ld16(taddr + g * 16, v);
+                const int col0 = n0 + g * 16;
+                if (!valid || col0 >= p.N) continue;
+                if (vec_ok && col0 + 16 <= p.N) {
+                    if (p.epi.act == ACT_GELU)
+                        epi_fast16<ACT_GELU>(p.epi, grow, col0, v, s_bias + g * 16, s_cs + g * 16, fa, fb);
+                    else if (p.epi.act == ACT_LRELU)
+                        epi_fast16<ACT_LRELU>(p.epi, grow, col0, v, s_bias + g * 16, s_cs + g * 16, fa, fb);
+                    else
+                        epi_fast16<ACT_NONE>(p.epi, grow, col0, v, s_bias + g * 16, s_cs + g * 16, fa, fb);
+                } else {
+                    epi_apply_store<16>(p.epi, grow, col0, p.N, v, z, py, px);
+                }
+            }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[a]);
         }
-        const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16);
-        for (int c = 0; c < p.BN; c += 16) {
-            float v[16];
-            tmem_ld16(taddr + c, v);
-            if (valid && n0 + c < p.N) epi_apply_store<16>(p.epi, grow, n0 + c, p.N, v, blockIdx.z, py, px);
-        }
+        if (p.tma_store && lane == 0) bulk_wait0();  // all bulk stores of this warp have landed before the CTA exits
     }
     tc_fence_before();
     __syncthreads();
@@ -215,13 +414,25 @@ int make_tmap_bf16_sw(CUtensorMap* m, const void* base, int rank, const uint64_t
 }
 
 static int pick_bn(int N) {
-    // largest multiple of 16 that is <= 256 and splits N (rounded up to 16) evenly
+    // one tile when N fits; otherwise a multiple of 64 (the TMA-store block width) with the least padded work
     const int n16 = (N + 15) / 16 * 16;
     if (n16 <= 256) return n16;
-    for (int parts = 2; parts <= 64; ++parts) {
-        if (n16 % (16 * parts) == 0 && n16 / parts <= 256) return n16 / parts;
+    int best = 256, best_pad = ceil_div(N, 256) * 256;
+    for (int bn : {192, 128}) {
+        const int pad = ceil_div(N, bn) * bn;
+        if (pad < best_pad) {
+            best = bn;
+            best_pad = pad;
+        }
     }
-    return 128;
+    return best;
+}
+
+static bool can_tma_store(const Epi& e) {
+    return e.out_dt == DT_BF16 && e.ps == 0 && e.post_scale == 1.0f && e.post_shift == nullptr && e.ldo % 8 == 0 &&
+           (reinterpret_cast<uintptr_t>(e.out) & 15) == 0 &&
+           (!e.res || ((e.res_dt == DT_BF16 ? e.ldr % 8 == 0 : e.ldr % 4 == 0) &&
+                       (reinterpret_cast<uintptr_t>(e.res) & 15) == 0));
 }
 
 static int tmem_cols_for(int bn) {
@@ -230,22 +441,38 @@ static int tmem_cols_for(int bn) {
     return c;
 }
 
-static int launch_tc(TcGemmParams& p, dim3 grid, cudaStream_t stream) {
+static int sm_count() {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+    }
+    return sms;
+}
+
+static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     const int stage_bytes = kABytes + p.BN * 128;
-    int stages = (100 * 1024) / stage_bytes;
-    const int total_it = p.taps * p.ktiles;
-    if (stages > 4) stages = 4;
-    if (stages > total_it) stages = total_it;
-    if (stages < 1) stages = 1;
+    int stages = (180 * 1024) / stage_bytes;
+    if (stages > 6) stages = 6;
+    if (stages < 2) stages = 2;
     p.stages = stages;
-    p.tmem_cols = tmem_cols_for(p.BN);
-    const size_t smem = size_t(stages) * stage_bytes + 1024 /*align*/ + 256 /*barriers*/;
+    p.acc_stride = (p.BN + 31) / 32 * 32;
+    p.tmem_cols = tmem_cols_for(2 * p.acc_stride);
+    p.tiles_n = ceil_div(p.N, p.BN);
+    const long long total = (long long)batch * p.tiles_m * p.tiles_n;
+    IRB_REQUIRE(total < (1ll << 31), "tc_gemm: too many tiles");
+    p.total = int(total);
+    const size_t smem = size_t(stages) * stage_bytes + 1024 /*align*/ + 256 /*barriers*/ + 4096 /*column vectors*/ +
+                        1024 + 8 * 4096 /*TMA-store staging*/;
     static bool attr_set = false;
     if (!attr_set) {
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        IRB_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         attr_set = true;
     }
-    tc_gemm_kernel<<<grid, 192, smem, stream>>>(p);
+    const int grid = int(total < sm_count() ? total : sm_count());
+    tc_gemm_kernel<<<grid, kGemmThreads, smem, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -279,8 +506,15 @@ int tc_gemm(const bf16* A, long long lda, int M, int K, int batch, long long a_b
         IRB_TRY(make_tmap_bf16(&p.tmB, Wt, 2, dims, str, box));
     }
     p.epi = epi;
-    dim3 grid(ceil_div(M, kTileM), ceil_div(N, p.BN), batch);
-    IRB_TRY(launch_tc(p, grid, stream));
+    p.tma_store = can_tma_store(epi) ? 1 : 0;
+    if (p.tma_store) {
+        uint64_t dims[3] = {uint64_t(N), uint64_t(M), uint64_t(batch)};
+        uint64_t str[2] = {uint64_t(epi.ldo) * 2, uint64_t(epi.ldo) * 2 * M};
+        uint32_t box[3] = {64, 32, 1};
+        IRB_TRY(make_tmap_bf16(&p.tmC, epi.out, 3, dims, str, box));
+    }
+    p.tiles_m = ceil_div(M, kTileM);
+    IRB_TRY(launch_tc(p, batch, stream));
     {
         const double rows = double(M) * batch;
         const double wrows = w_rows_per_batch ? double(N) * batch : double(N);
@@ -327,8 +561,16 @@ int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, cons
         IRB_TRY(make_tmap_bf16(&p.tmB, Wt, 2, dims, str, box));
     }
     p.epi = epi;
-    dim3 grid(p.tiles_x * ceil_div(H, BH), ceil_div(N, p.BN), Nimg);
-    IRB_TRY(launch_tc(p, grid, stream));
+    p.tma_store = can_tma_store(epi) ? 1 : 0;
+    if (p.tma_store) {
+        const int bw = BW < 32 ? BW : 32;
+        uint64_t dims[4] = {uint64_t(N), uint64_t(W), uint64_t(H), uint64_t(Nimg)};
+        uint64_t str[3] = {uint64_t(epi.ldo) * 2, uint64_t(epi.ldo) * 2 * W, uint64_t(epi.ldo) * 2 * W * H};
+        uint32_t box[4] = {64, uint32_t(bw), uint32_t(32 / bw), 1};
+        IRB_TRY(make_tmap_bf16(&p.tmC, epi.out, 4, dims, str, box));
+    }
+    p.tiles_m = p.tiles_x * ceil_div(H, BH);
+    IRB_TRY(launch_tc(p, Nimg, stream));
     {
         const double rows = double(H) * W * Nimg;
         prof_mark("tc_conv3x3", C, N, 18.0 * rows * C * N, rows * C * 2 + 9.0 * N * C * 2 + epi_bytes(epi, rows, N), stream);

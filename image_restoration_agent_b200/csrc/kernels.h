@@ -28,6 +28,9 @@ int simt_conv3x3(const void* A, int a_dt, long long lda, int Nimg, int H, int W,
 // LayerNorm over channels per pixel. mode 0: WithBias ((x-mu)*rstd*w+b), mode 1: BiasFree (x*rstd*w).
 int layernorm(const void* x, int x_dt, long long ldx, void* y, int y_dt, long long ldy, long long rows, int C,
               const float* w, const float* b, int mode, float eps, cudaStream_t stream);
+// (mu, rstd) per row for a LayerNorm folded into the next GEMM (Epi::ln_stats / ln_colsum).
+int row_stats(const void* x, int x_dt, long long ldx, float2* stats, long long rows, int C, float eps,
+              cudaStream_t stream);
 // depthwise 3x3 (zero pad 1). wt is [9][C] float (tap-major). If sumsq != nullptr, accumulates per (image, channel)
 // sum of squares of the fp32 outputs for channels < sumsq_channels into sumsq[img*sumsq_channels + c].
 int dwconv3x3(const void* x, int dt, long long ldx, void* y, long long ldy, int Nimg, int H, int W, int C,

@@ -131,6 +131,70 @@ int layernorm(const void* x, int x_dt, long long ldx, void* y, int y_dt, long lo
 }
 
 // ----------------------------------------------------------------------------------------------
+// Row statistics for the LayerNorm that is folded into the following GEMM (Epi::ln_stats): per pixel
+// (mu, 1/sqrt(var + eps)) with the population variance about mu, two-pass in registers like layernorm_kernel.
+// Reads x once (C*e bytes per row), writes 8 bytes per row.
+// ----------------------------------------------------------------------------------------------
+template <typename TI, int LPP>
+__global__ void __launch_bounds__(256) row_stats_kernel(const TI* __restrict__ x, long long ldx, float2* __restrict__ st,
+                                                        long long rows, int C, float eps) {
+    constexpr int MAXCH = 4;
+    const int lane = threadIdx.x % LPP;
+    const long long row = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / LPP;
+    const bool active = row < rows;
+    const int nch = C >> 2;
+    float v[MAXCH][4];
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < MAXCH; ++j) {
+        const int ch = lane + j * LPP;
+        if (active && ch < nch) {
+            Vec4<TI>::load(x + row * ldx + ch * 4, v[j]);
+            s += v[j][0] + v[j][1] + v[j][2] + v[j][3];
+        } else {
+            v[j][0] = v[j][1] = v[j][2] = v[j][3] = 0.f;
+        }
+    }
+#pragma unroll
+    for (int o = LPP / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o, LPP);
+    const float mu = s / float(C);
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < MAXCH; ++j) {
+        const int ch = lane + j * LPP;
+        if (ch < nch) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float d = v[j][i] - mu;
+                q += d * d;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = LPP / 2; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o, LPP);
+    if (active && lane == 0) st[row] = make_float2(mu, 1.0f / sqrtf(q / float(C) + eps));
+}
+
+int row_stats(const void* x, int x_dt, long long ldx, float2* stats, long long rows, int C, float eps,
+              cudaStream_t stream) {
+    IRB_REQUIRE(C % 4 == 0 && C <= 512 && C > 0 && ldx % 4 == 0, "row_stats: C must be a multiple of 4 and <= 512");
+    if (rows <= 0) return 0;
+    const int nch = C / 4;
+    const int lpp = nch <= 8 ? 8 : (nch <= 16 ? 16 : 32);
+    const int blocks = int(ceil_div_ll(rows * lpp, 256));
+#define IRB_RS(T, L) row_stats_kernel<T, L><<<blocks, 256, 0, stream>>>((const T*)x, ldx, stats, rows, C, eps)
+    if (x_dt == DT_BF16) {
+        if (lpp == 8) IRB_RS(bf16, 8); else if (lpp == 16) IRB_RS(bf16, 16); else IRB_RS(bf16, 32);
+    } else {
+        if (lpp == 8) IRB_RS(float, 8); else if (lpp == 16) IRB_RS(float, 16); else IRB_RS(float, 32);
+    }
+#undef IRB_RS
+    IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("row_stats", C, x_dt == DT_BF16 ? 2 : 4, 4.0 * rows * C, double(rows) * (C * (x_dt == DT_BF16 ? 2 : 4) + 8), stream);
+    return 0;
+}
+
+// ----------------------------------------------------------------------------------------------
 // Depthwise 3x3, zero pad 1 (restormer_arch.py:82,106 qkv_dwconv / ffn.dwconv, bias=False).
 // Thread = (x, 4-channel group); it walks RY rows with a 3x3 register window, so every input element is
 // loaded 3x from L1 and once from HBM. GATE: the GDFN gate gelu(dw(x1)) * dw(x2) (restormer_arch.py:90-91).

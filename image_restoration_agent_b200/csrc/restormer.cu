@@ -24,7 +24,28 @@ struct RBlockW {
     void* pin_w;     // [2hp][C]   rows [0,h) = x1, [hp,hp+h) = x2, others zero
     float* ffn_dw;   // [9][2hp]
     void* pout_w;    // [C][hp]
+    // bf16 mode: norm1 / norm2 are folded into qkv_w / pin_w (W' = W diag(gain)); the GEMM epilogue applies
+    // rstd * (acc - mu * colsum) + t with colsum[n] = sum_k W'[n,k], t[n] = sum_k W[n,k] * ln_bias[k]
+    float *qkv_cs, *qkv_t, *pin_cs, *pin_t;
 };
+
+// W [N][K] (row stride ldw) -> W' = W * diag(gain) in place; colsum of the bf16-ROUNDED W'; t = W . ln_bias
+static void fold_ln(std::vector<float>& w, int N, int K, int ldw, const float* gain, const float* ln_bias,
+                    std::vector<float>& colsum, std::vector<float>& t) {
+    colsum.assign(N, 0.f);
+    t.assign(N, 0.f);
+    for (int n = 0; n < N; ++n) {
+        double cs = 0.0, tt = 0.0;
+        for (int k = 0; k < K; ++k) {
+            float& e = w[size_t(n) * ldw + k];
+            if (ln_bias) tt += double(e) * ln_bias[k];
+            e *= gain[k];
+            cs += double(__bfloat162float(__float2bfloat16_rn(e)));
+        }
+        colsum[n] = float(cs);
+        t[n] = float(tt);
+    }
+}
 
 struct ConvW {
     void* w;       // storage dtype, [npad][9*kpad]
@@ -46,6 +67,7 @@ struct Restormer : Model {
     struct WS {
         void *cat1, *cat2, *cat3, *x2, *x3, *x4, *ln, *qkv_pre, *qkv, *hidden, *gated, *weff;
         float *G, *sumsq;
+        float2* stats;  // [P] (mu, rstd) of the LayerNorm folded into the next GEMM (bf16 mode)
         size_t gs_bytes;
     };
     void layout(Bump& b, int n, int H, int W, WS& w);
@@ -77,8 +99,27 @@ int Restormer::load_block(const Blob& blob, const std::string& p, int C, int hea
     }
     IRB_TRY(blob.get(p + ".attn.temperature", t, heads, 1, 1));
     IRB_TRY(upload_f32(t.data, heads, &o.temp));
+    const bool fold = dt == DT_BF16;
+    BlobTensor g1, b1, g2, b2;
+    IRB_TRY(blob.get(p + ".norm1.body.weight", g1, C));
+    IRB_TRY(blob.get(p + ".norm2.body.weight", g2, C));
+    if (!desc.ln_bias_free) {
+        IRB_TRY(blob.get(p + ".norm1.body.bias", b1, C));
+        IRB_TRY(blob.get(p + ".norm2.body.bias", b2, C));
+    }
+    o.qkv_cs = o.qkv_t = o.pin_cs = o.pin_t = nullptr;
     IRB_TRY(blob.get(p + ".attn.qkv.weight", t, 3 * C, C, 1, 1));
-    IRB_TRY(upload_act(t.data, size_t(3) * C * C, &o.qkv_w));
+    {
+        std::vector<float> w(t.data, t.data + size_t(3) * C * C), cs, tt;
+        if (fold) {
+            fold_ln(w, 3 * C, C, C, g1.data, desc.ln_bias_free ? nullptr : b1.data, cs, tt);
+            if (!desc.ln_bias_free) {
+                IRB_TRY(upload_f32(cs.data(), cs.size(), &o.qkv_cs));
+                IRB_TRY(upload_f32(tt.data(), tt.size(), &o.qkv_t));
+            }
+        }
+        IRB_TRY(upload_act(w.data(), w.size(), &o.qkv_w));
+    }
     IRB_TRY(blob.get(p + ".attn.qkv_dwconv.weight", t, 3 * C, 1, 3, 3));
     {
         std::vector<float> d = pack_dw(t);
@@ -93,6 +134,14 @@ int Restormer::load_block(const Blob& blob, const std::string& p, int C, int hea
         for (int r = 0; r < 2 * h; ++r) {
             const int dst = r < h ? r : hp + (r - h);
             memcpy(&w[size_t(dst) * C], t.data + size_t(r) * C, size_t(C) * 4);
+        }
+        if (fold) {
+            std::vector<float> cs, tt;
+            fold_ln(w, 2 * hp, C, C, g2.data, desc.ln_bias_free ? nullptr : b2.data, cs, tt);
+            if (!desc.ln_bias_free) {
+                IRB_TRY(upload_f32(cs.data(), cs.size(), &o.pin_cs));
+                IRB_TRY(upload_f32(tt.data(), tt.size(), &o.pin_t));
+            }
         }
         IRB_TRY(upload_act(w.data(), w.size(), &o.pin_w));
     }
@@ -209,6 +258,7 @@ void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
     w.hidden = b.take(hid);
     w.gated = b.take(gat);
     w.weff = b.take(weff);
+    w.stats = b.take<float2>(P1 * sizeof(float2));
     w.G = b.take<float>(gs);
     w.gs_bytes = gs;
     w.sumsq = nullptr;
@@ -243,8 +293,17 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
     const long long P = (long long)n * H * W;
     const int mode = desc.ln_bias_free ? 1 : 0;
     // --- x = x + project_out(attn(norm1(x))) ---
-    IRB_TRY(layernorm(x, dt, ldx, ws.ln, dt, C, P, C, w.n1w, w.n1b, mode, 1e-5f, s));
-    IRB_TRY(run_gemm(ws.ln, C, P, C, w.qkv_w, C, 3 * C, 3 * C, make_epi(ws.qkv_pre, 3 * C, dt), s));
+    if (dt == DT_BF16) {  // norm1 folded into the qkv GEMM
+        IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
+        Epi e = make_epi(ws.qkv_pre, 3 * C, dt);
+        e.ln_stats = ws.stats;
+        e.ln_colsum = w.qkv_cs;
+        e.bias = w.qkv_t;
+        IRB_TRY(run_gemm(x, ldx, P, C, w.qkv_w, C, 3 * C, 3 * C, e, s));
+    } else {
+        IRB_TRY(layernorm(x, dt, ldx, ws.ln, dt, C, P, C, w.n1w, w.n1b, mode, 1e-5f, s));
+        IRB_TRY(run_gemm(ws.ln, C, P, C, w.qkv_w, C, 3 * C, 3 * C, make_epi(ws.qkv_pre, 3 * C, dt), s));
+    }
     const int nch = mdta_nchunks(H * W, heads, n);
     float* G = ws.G;                                       // [n][heads][nch][c][c]
     float* ssq = ws.G + size_t(n) * heads * nch * c * c;   // [n][heads][nch][2][c]
@@ -266,8 +325,17 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
             IRB_TRY(simt_gemm(v, DT_F32, 3 * C, H * W, C, n, 0, (const float*)ws.weff, C, C, C, e, s));
     }
     // --- x = x + project_out(gelu(dw(x1)) * dw(x2)) ---
-    IRB_TRY(layernorm(x, dt, ldx, ws.ln, dt, C, P, C, w.n2w, w.n2b, mode, 1e-5f, s));
-    IRB_TRY(run_gemm(ws.ln, C, P, C, w.pin_w, C, 2 * w.hp, 2 * w.hp, make_epi(ws.hidden, 2 * w.hp, dt), s));
+    if (dt == DT_BF16) {  // norm2 folded into project_in
+        IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
+        Epi e = make_epi(ws.hidden, 2 * w.hp, dt);
+        e.ln_stats = ws.stats;
+        e.ln_colsum = w.pin_cs;
+        e.bias = w.pin_t;
+        IRB_TRY(run_gemm(x, ldx, P, C, w.pin_w, C, 2 * w.hp, 2 * w.hp, e, s));
+    } else {
+        IRB_TRY(layernorm(x, dt, ldx, ws.ln, dt, C, P, C, w.n2w, w.n2b, mode, 1e-5f, s));
+        IRB_TRY(run_gemm(ws.ln, C, P, C, w.pin_w, C, 2 * w.hp, 2 * w.hp, make_epi(ws.hidden, 2 * w.hp, dt), s));
+    }
     IRB_TRY(dwconv3x3_gate(ws.hidden, dt, 2 * w.hp, ws.gated, w.hp, n, H, W, w.hp, w.ffn_dw, s));
     {
         Epi e = make_epi(x, ldx, dt);

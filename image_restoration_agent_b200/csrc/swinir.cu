@@ -13,8 +13,26 @@ namespace irb {
 struct LinW {
     void* w;     // storage dtype [npad][kpad]
     float* b;    // [N] fp32 (nullptr = no bias)
+    float* cs;   // bf16 mode, LayerNorm folded in: colsum[n] = sum_k bf16(W[n,k] * gain[k]); b then holds b + W.ln_bias
     int N, K, kpad, npad;
 };
+
+// W [N][K] -> W * diag(gain) in place; colsum of the bf16-rounded result; bias += W . ln_bias
+static void fold_ln(std::vector<float>& w, std::vector<float>& bias, int N, int K, const float* gain,
+                    const float* ln_bias, std::vector<float>& colsum) {
+    colsum.assign(N, 0.f);
+    for (int n = 0; n < N; ++n) {
+        double cs = 0.0, tt = 0.0;
+        for (int k = 0; k < K; ++k) {
+            float& e = w[size_t(n) * K + k];
+            tt += double(e) * ln_bias[k];
+            e *= gain[k];
+            cs += double(__bfloat162float(__float2bfloat16_rn(e)));
+        }
+        colsum[n] = float(cs);
+        bias[n] += float(tt);
+    }
+}
 struct Conv3W {
     void* w;       // storage dtype [npad][9*kpad]
     float* wf32;   // fp32 copy when the FMA kernel runs it
@@ -84,6 +102,7 @@ struct SwinIR : Model {
     struct WS {
         float *xin, *out_tmp;
         void *xa, *xb, *ffirst, *ln, *qkv, *attn, *hidden, *q4a, *q4b, *t64, *u1, *u2, *u3;
+        float2* stats;
     };
     void layout(Bump& b, int n, int H0, int W0, WS& w);
     void padded(int H0, int W0, int& H, int& W) const {
@@ -91,10 +110,10 @@ struct SwinIR : Model {
         H = (H0 + m - 1) / m * m;
         W = (W0 + m - 1) / m * m;
     }
-    int load_lin(const Blob& blob, const std::string& name, int N, int K, LinW& o);
+    int load_lin(const Blob& blob, const std::string& name, int N, int K, LinW& o, const std::string& fold_norm = "");
     int load_conv(const Blob& blob, const std::string& name, int N, int Cin, Conv3W& o);
     int load_resi(const Blob& blob, const std::string& name, ResiW& o);
-    int load_qkv(const Blob& blob, const std::string& name, int heads, LinW& o);
+    int load_qkv(const Blob& blob, const std::string& name, int heads, LinW& o, const std::string& fold_norm);
     int load_norm(const Blob& blob, const std::string& name, float** w, float** b);
     int gemm(const void* A, long long lda, long long M, const LinW& L, Epi e, cudaStream_t s);
     int conv(const Conv3W& c, const void* x, int x_dt, long long ldx, int n, int H, int W, Epi e, cudaStream_t s);
@@ -111,24 +130,34 @@ int SwinIR::load_norm(const Blob& blob, const std::string& name, float** w, floa
     return 0;
 }
 
-int SwinIR::load_lin(const Blob& blob, const std::string& name, int N, int K, LinW& o) {
-    BlobTensor t;
+int SwinIR::load_lin(const Blob& blob, const std::string& name, int N, int K, LinW& o, const std::string& fold_norm) {
+    BlobTensor t, tb;
     const bool conv1x1 = blob.has(name + ".weight") && blob.t.at(name + ".weight").ndim == 4;
     if (conv1x1)
         IRB_TRY(blob.get(name + ".weight", t, N, K, 1, 1));
     else
         IRB_TRY(blob.get(name + ".weight", t, N, K));
-    std::vector<float> w = pack_linear(t.data, N, K, o.kpad, o.npad);
+    IRB_TRY(blob.get(name + ".bias", tb, N));
+    std::vector<float> w0(t.data, t.data + size_t(N) * K), b0(tb.data, tb.data + N);
+    o.cs = nullptr;
+    if (!fold_norm.empty() && dt == DT_BF16) {
+        BlobTensor g, lb;
+        IRB_TRY(blob.get(fold_norm + ".weight", g, K));
+        IRB_TRY(blob.get(fold_norm + ".bias", lb, K));
+        std::vector<float> cs;
+        fold_ln(w0, b0, N, K, g.data, lb.data, cs);
+        IRB_TRY(upload_f32(cs.data(), cs.size(), &o.cs));
+    }
+    std::vector<float> w = pack_linear(w0.data(), N, K, o.kpad, o.npad);
     IRB_TRY(upload_act(w.data(), w.size(), &o.w));
-    IRB_TRY(blob.get(name + ".bias", t, N));
-    IRB_TRY(upload_f32(t.data, N, &o.b));
+    IRB_TRY(upload_f32(b0.data(), N, &o.b));
     o.N = N;
     o.K = K;
     return 0;
 }
 
 // qkv Linear [3C][C] (rows [3][heads][d], network_swinir.py:121-122) -> rows [3][heads][dp], q rows * d^-0.5
-int SwinIR::load_qkv(const Blob& blob, const std::string& name, int heads, LinW& o) {
+int SwinIR::load_qkv(const Blob& blob, const std::string& name, int heads, LinW& o, const std::string& fold_norm) {
     BlobTensor tw, tb;
     IRB_TRY(blob.get(name + ".weight", tw, 3 * C, C));
     IRB_TRY(blob.get(name + ".bias", tb, 3 * C));
@@ -143,6 +172,15 @@ int SwinIR::load_qkv(const Blob& blob, const std::string& name, int heads, LinW&
                 for (int k = 0; k < C; ++k) w[size_t(dst) * C + k] = tw.data[size_t(src) * C + k] * s;
                 b[dst] = tb.data[src] * s;
             }
+    o.cs = nullptr;
+    if (dt == DT_BF16) {
+        BlobTensor g, lb;
+        IRB_TRY(blob.get(fold_norm + ".weight", g, C));
+        IRB_TRY(blob.get(fold_norm + ".bias", lb, C));
+        std::vector<float> cs;
+        fold_ln(w, b, 3 * Cq, C, g.data, lb.data, cs);
+        IRB_TRY(upload_f32(cs.data(), cs.size(), &o.cs));
+    }
     std::vector<float> wp = pack_linear(w.data(), 3 * Cq, C, o.kpad, o.npad);
     IRB_TRY(upload_act(wp.data(), wp.size(), &o.w));
     IRB_TRY(upload_f32(b.data(), b.size(), &o.b));
@@ -231,9 +269,9 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
             const int nb = (2 * m->ws_eff - 1) * (2 * m->ws_eff - 1);
             IRB_TRY(blob.get(p + ".attn.relative_position_bias_table", t, nb, L.heads));
             IRB_TRY(m->upload_f32(t.data, size_t(nb) * L.heads, &L.bias_table));
-            IRB_TRY(m->load_qkv(blob, p + ".attn.qkv", L.heads, L.qkv));
+            IRB_TRY(m->load_qkv(blob, p + ".attn.qkv", L.heads, L.qkv, p + ".norm1"));
             IRB_TRY(m->load_lin(blob, p + ".attn.proj", C, C, L.proj));
-            IRB_TRY(m->load_lin(blob, p + ".mlp.fc1", m->hid, C, L.fc1));
+            IRB_TRY(m->load_lin(blob, p + ".mlp.fc1", m->hid, C, L.fc1, p + ".norm2"));
             IRB_TRY(m->load_lin(blob, p + ".mlp.fc2", C, m->hid, L.fc2));
         }
         IRB_TRY(m->load_resi(blob, "layers." + std::to_string(r) + ".conv", m->layer_conv[r]));
@@ -272,6 +310,7 @@ void SwinIR::layout(Bump& b, int n, int H0, int W0, WS& w) {
     w.xb = b.take(P * ldC * E);
     w.ffirst = b.take(P * ldC * E);
     w.ln = b.take(P * ldC * E);
+    w.stats = b.take<float2>(P * sizeof(float2));
     w.qkv = b.take(P * 3 * Cq * E);
     w.attn = b.take(P * ldC * E);
     w.hidden = b.take(P * hid * E);
@@ -334,8 +373,16 @@ int SwinIR::resi(const ResiW& r, const void* x, long long ldx, int n, int H, int
 // SwinTransformerBlock.forward (:239-279): xout = xin + attn(LN1(xin)); xout += mlp(LN2(xout))
 int SwinIR::stl(const STLW& L, const void* xin, void* xout, int n, int H, int W, WS& w, cudaStream_t s) {
     const long long P = (long long)n * H * W;
-    IRB_TRY(layernorm(xin, dt, ldC, w.ln, dt, ldC, P, C, L.n1w, L.n1b, 0, 1e-5f, s));
-    IRB_TRY(gemm(w.ln, ldC, P, L.qkv, make_epi(w.qkv, 3 * Cq, dt), s));
+    if (dt == DT_BF16) {  // norm1 folded into the qkv GEMM
+        IRB_TRY(row_stats(xin, dt, ldC, w.stats, P, C, 1e-5f, s));
+        Epi e = make_epi(w.qkv, 3 * Cq, dt);
+        e.ln_stats = w.stats;
+        e.ln_colsum = L.qkv.cs;
+        IRB_TRY(gemm(xin, ldC, P, L.qkv, e, s));
+    } else {
+        IRB_TRY(layernorm(xin, dt, ldC, w.ln, dt, ldC, P, C, L.n1w, L.n1b, 0, 1e-5f, s));
+        IRB_TRY(gemm(w.ln, ldC, P, L.qkv, make_epi(w.qkv, 3 * Cq, dt), s));
+    }
     IRB_TRY(window_attention(w.qkv, dt, 3 * Cq, w.attn, ldC, n, H, W, C, L.heads, dp, ws_eff, L.shift, L.bias_table, s));
     {
         Epi e = make_epi(xout, ldC, dt);
@@ -344,8 +391,15 @@ int SwinIR::stl(const STLW& L, const void* xin, void* xout, int n, int H, int W,
         e.res_dt = dt;
         IRB_TRY(gemm(w.attn, ldC, P, L.proj, e, s));
     }
-    IRB_TRY(layernorm(xout, dt, ldC, w.ln, dt, ldC, P, C, L.n2w, L.n2b, 0, 1e-5f, s));
-    {
+    if (dt == DT_BF16) {  // norm2 folded into fc1
+        IRB_TRY(row_stats(xout, dt, ldC, w.stats, P, C, 1e-5f, s));
+        Epi e = make_epi(w.hidden, hid, dt);
+        e.act = ACT_GELU;
+        e.ln_stats = w.stats;
+        e.ln_colsum = L.fc1.cs;
+        IRB_TRY(gemm(xout, ldC, P, L.fc1, e, s));
+    } else {
+        IRB_TRY(layernorm(xout, dt, ldC, w.ln, dt, ldC, P, C, L.n2w, L.n2b, 0, 1e-5f, s));
         Epi e = make_epi(w.hidden, hid, dt);
         e.act = ACT_GELU;
         IRB_TRY(gemm(w.ln, ldC, P, L.fc1, e, s));
