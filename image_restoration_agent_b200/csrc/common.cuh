@@ -77,17 +77,30 @@ struct Epi {
 
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 
-// exact-erf GELU with erf from Abramowitz-Stegun 7.1.26 (|abs err| <= 1.5e-7, i.e. fp32 round-off level)
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// exact-erf GELU with erf from Abramowitz-Stegun 7.1.26 (|abs err| <= 1.5e-7 + MUFU round-off, i.e. far below a
+// bf16 ulp); used where the result is stored as bf16. One MUFU.RCP, one MUFU.EX2, 9 FMA-pipe instructions.
 __device__ __forceinline__ float gelu_as(float x) {
-    const float z = fabsf(x) * 0.70710678118654752440f;
-    const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
-    float poly = fmaf(1.061405429f, t, -1.453152027f);
-    poly = fmaf(poly, t, 1.421413741f);
-    poly = fmaf(poly, t, -0.284496736f);
-    poly = fmaf(poly, t, 0.254829592f);
-    poly *= t;
-    const float e = 1.0f - poly * __expf(-z * z);  // erf(|x|/sqrt2)
-    return 0.5f * x + 0.5f * fabsf(x) * e;        // 0.5*x*(1 + sign(x)*erf(|x|/sqrt2))
+    const float h = 0.5f * x;
+    const float t = rcp_approx(fmaf(0.3275911f * 1.41421356237f, fabsf(h), 1.0f));  // 1 / (1 + p |x| / sqrt2)
+    float poly = fmaf(-1.061405429f, t, 1.453152027f);
+    poly = fmaf(poly, t, -1.421413741f);
+    poly = fmaf(poly, t, 0.284496736f);
+    poly = fmaf(poly, t, -0.254829592f);
+    poly *= t;                                                   // -(a1 t + ... + a5 t^5)
+    const float ez = ex2_approx(h * h * -2.88539008178f);       // exp(-x^2 / 2) = 2^(-2 log2(e) h^2)
+    const float e = fmaf(poly, ez, 1.0f);                        // erf(|x| / sqrt2)
+    return fmaf(fabsf(h), e, h);                                 // 0.5 x (1 + sign(x) erf(|x| / sqrt2))
 }
 
 __device__ __forceinline__ float epi_act(const Epi& e, float x) {

@@ -4,10 +4,13 @@
 //
 // Work item = (image, 32x8 pixel tile, 64-channel chunk). A persistent CTA walks its items with a 2-stage
 // shared-memory ring: one producer thread issues a 4-D TMA box {64 ch, 34, 10, 1} per stream (the halo'd tile;
-// rows / columns outside the image are ZERO-FILLED by TMA, which is exactly the convolution's zero padding), 256
-// consumer threads compute from shared memory. Consumer thread = (4-channel group, column); it walks down the 8
-// rows of two columns with a 3-row register window, so every input element is read from shared memory 3 times
-// (8-byte conflict-free loads) and from HBM once (+ halo). Arithmetic is fp32 with packed FFMA2 (fma.rn.f32x2).
+// rows / columns outside the image are ZERO-FILLED by TMA, which is exactly the convolution's zero padding), 16
+// consumer warps compute from shared memory. Consumer warp = two adjacent output columns, lane = one channel PAIR
+// (a warp reads the 128 contiguous bytes of one pixel: conflict-free, one wavefront). The warp walks down the 10
+// halo rows; every input row is loaded and converted ONCE (4 columns) and scattered into the three output rows it
+// touches (input-stationary, 3 live accumulator rows), so each element costs one LDS.32 + two ALU ops per 2 output
+// columns. Arithmetic is fp32 with packed fma.rn.f32x2 (both channels of the pair in one instruction); the GELU is
+// evaluated packed as well (Abramowitz-Stegun 7.1.26, 2 MUFU per element).
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
@@ -19,6 +22,8 @@ static constexpr int kDwHW = kDwTW + 2, kDwHH = kDwTH + 2;     // halo'd tile
 static constexpr int kDwCh = 64;                               // channels per chunk = one 128-byte row
 static constexpr int kDwStreamBytes = kDwHH * kDwHW * kDwCh * 2;  // 43 520
 static constexpr int kDwStages = 2;
+static constexpr int kDwConsumerWarps = kDwTW / 2;             // 16
+static constexpr int kDwThreads = (kDwConsumerWarps + 1) * 32; // + producer warp
 
 struct alignas(64) DwParams {
     CUtensorMap tm;  // {Ctot, W, H, N}, box {64, 34, 10, 1}, no swizzle
@@ -46,27 +51,71 @@ __device__ __forceinline__ f32x2 bf16x2_to_f32x2(uint32_t u) {
 __device__ __forceinline__ void ffma2(f32x2& acc, f32x2 a, f32x2 b) {
     asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
 }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ f32x2 splat2(float v) { return pack2(v, v); }
 
+// gelu on both halves (same formula as gelu_as in common.cuh)
+__device__ __forceinline__ f32x2 gelu2(f32x2 x) {
+    const f32x2 h = mul2(x, splat2(0.5f));
+    float h0, h1;
+    unpack2(h, h0, h1);
+    const float t0 = rcp_approx(fmaf(0.3275911f * 1.41421356237f, fabsf(h0), 1.0f));
+    const float t1 = rcp_approx(fmaf(0.3275911f * 1.41421356237f, fabsf(h1), 1.0f));
+    const f32x2 t = pack2(t0, t1);
+    f32x2 poly = fma2(splat2(-1.061405429f), t, splat2(1.453152027f));
+    poly = fma2(poly, t, splat2(-1.421413741f));
+    poly = fma2(poly, t, splat2(0.284496736f));
+    poly = fma2(poly, t, splat2(-0.254829592f));
+    poly = mul2(poly, t);
+    const f32x2 s = mul2(mul2(h, h), splat2(-2.88539008178f));
+    float s0, s1;
+    unpack2(s, s0, s1);
+    const f32x2 e = fma2(poly, pack2(ex2_approx(s0), ex2_approx(s1)), splat2(1.0f));
+    float e0, e1;
+    unpack2(e, e0, e1);
+    return pack2(fmaf(fabsf(h0), e0, h0), fmaf(fabsf(h1), e1, h1));
+}
+
+// Work order: chunk slowest, then image, tile row, tile column, so that the items a CTA walks (w, w + grid, ...)
+// mostly share their channel chunk (weights stay in registers) and neighbouring tiles are in flight together
+// (halo reads hit L2). The producer decodes the item once and hands (img, ty, tx, chunk) to the consumers through
+// the stage's shared-memory slot, so the 16 consumer warps do no integer division.
 template <bool GATE>
-__global__ void __launch_bounds__(288, 1) dw3x3_tma_kernel(const __grid_constant__ DwParams p) {
+__global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_constant__ DwParams p) {
     constexpr int NS = GATE ? 2 : 1;
     constexpr int stage_bytes = NS * kDwStreamBytes;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + kDwStages * stage_bytes);
     uint64_t* empty = full + kDwStages;
+    int4* item = reinterpret_cast<int4*>(empty + kDwStages);  // [stages] (img, ty, tx, chunk)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         for (int s = 0; s < kDwStages; ++s) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], 8);
+            mbar_init(&empty[s], kDwConsumerWarps);
         }
         fence_mbar_init();
     }
     __syncthreads();
-    const int per_img = p.tiles_x * p.tiles_y * p.chunks;
+    const int per_chunk = p.total / p.chunks;  // images * tiles
+    const int per_img = p.tiles_x * p.tiles_y;
 
-    if (warp == 8) {
+    if (warp == kDwConsumerWarps) {
         if (lane == 0) {
             tma_prefetch_desc(&p.tm);
             int it = 0;
@@ -74,11 +123,12 @@ __global__ void __launch_bounds__(288, 1) dw3x3_tma_kernel(const __grid_constant
                 const int s = it % kDwStages;
                 const uint32_t ph = (it / kDwStages) & 1;
                 mbar_wait(&empty[s], ph ^ 1);
-                const int img = w / per_img;
-                int r = w % per_img;
-                const int chunk = r % p.chunks;
-                r /= p.chunks;
-                const int tx = r % p.tiles_x, ty = r / p.tiles_x;
+                const int chunk = w / per_chunk;
+                int r = w - chunk * per_chunk;
+                const int img = r / per_img;
+                r -= img * per_img;
+                const int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
+                item[s] = make_int4(img, ty, tx, chunk);  // ordered before the consumers' reads by the mbarrier
                 uint8_t* dst = smem + s * stage_bytes;
                 mbar_arrive_expect_tx(&full[s], stage_bytes);
                 tma_load_4d(dst, &p.tm, &full[s], chunk * kDwCh, tx * kDwTW - 1, ty * kDwTH - 1, img);
@@ -90,91 +140,88 @@ __global__ void __launch_bounds__(288, 1) dw3x3_tma_kernel(const __grid_constant
         return;
     }
 
-    // ---- consumers: thread = (4-channel group g, column cl and cl + 16) ----
-    const int g = tid & 15, cl = tid >> 4;
+    // ---- consumers: warp = output columns (2*warp, 2*warp + 1), lane = channel pair ----
+    const int col0 = warp * 2;
+    const uint32_t lane_off = smem_u32(smem) + (col0 * kDwCh + lane * 2) * 2;
+    const long long row_step = (long long)p.W * p.ldy;
+    int cur_chunk = -1;
+    bool cvalid = false;
+    f32x2 wr[NS][9];
     int it = 0;
     for (int w = blockIdx.x; w < p.total; w += gridDim.x, ++it) {
         const int s = it % kDwStages;
         const uint32_t ph = (it / kDwStages) & 1;
-        const int img = w / per_img;
-        int r = w % per_img;
-        const int chunk = r % p.chunks;
-        r /= p.chunks;
-        const int tx = r % p.tiles_x, ty = r / p.tiles_x;
-        const int c0 = chunk * kDwCh + g * 4;
-        const bool cvalid = c0 < p.Cout;
-        f32x2 wr[NS][9][2];
-#pragma unroll
-        for (int st = 0; st < NS; ++st)
-#pragma unroll
-            for (int t = 0; t < 9; ++t) {
-                float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (cvalid) w4 = __ldg(reinterpret_cast<const float4*>(p.wt + (long long)t * p.wt_ld + c0 + st * p.hp_off));
-                wr[st][t][0] = pack2(w4.x, w4.y);
-                wr[st][t][1] = pack2(w4.z, w4.w);
-            }
         mbar_wait(&full[s], ph);
-        const uint8_t* tile = smem + s * stage_bytes;
-#pragma unroll 1
-        for (int half = 0; half < 2; ++half) {
-            const int col = cl + 16 * half;           // output column inside the tile
-            const int gx = tx * kDwTW + col;
-            f32x2 win[NS][3][3][2];                   // [stream][row slot][dx][channel pair]
-            auto load_row = [&](int hr, int slot) {   // hr: halo row 0..9
+        const int4 id = item[s];
+        const int img = id.x, ty = id.y, tx = id.z, chunk = id.w;
+        const int c0 = chunk * kDwCh + lane * 2;
+        if (chunk != cur_chunk) {  // warp-uniform
+            cur_chunk = chunk;
+            cvalid = c0 < p.Cout;
+#pragma unroll
+            for (int st = 0; st < NS; ++st)
+#pragma unroll
+                for (int t = 0; t < 9; ++t) {
+                    float2 w2 = make_float2(0.f, 0.f);
+                    if (cvalid) w2 = __ldg(reinterpret_cast<const float2*>(p.wt + (long long)t * p.wt_ld + c0 + st * p.hp_off));
+                    wr[st][t] = pack2(w2.x, w2.y);
+                }
+        }
+        const uint32_t tile = lane_off + s * stage_bytes;
+        const int gx = tx * kDwTW + col0;
+        const int nrows = min(kDwTH, p.H - ty * kDwTH);
+        const bool ok0 = cvalid && gx < p.W, ok1 = cvalid && gx + 1 < p.W;
+        bf16* yp0 = p.y + (((long long)img * p.H + ty * kDwTH) * p.W + gx) * p.ldy + c0;
+        bf16* yp1 = yp0 + p.ldy;
+        const bool fast = ok1 && nrows == kDwTH;  // lane-varying only through cvalid (ragged last chunk)
+        f32x2 acc[3][2][NS];  // [output row mod 3][pixel][stream]
+#pragma unroll
+        for (int hr = 0; hr < kDwHH; ++hr) {
+            f32x2 in[NS][4];
+#pragma unroll
+            for (int st = 0; st < NS; ++st)
+#pragma unroll
+                for (int d = 0; d < 4; ++d)
+                    in[st][d] = bf16x2_to_f32x2(lds_u32(tile + st * kDwStreamBytes + (hr * kDwHW + d) * kDwCh * 2));
+            // halo row hr is tap row dr of output row hr - dr
+#pragma unroll
+            for (int dr = 0; dr < 3; ++dr) {
+                const int orow = hr - dr;
+                if (orow < 0 || orow >= kDwTH) continue;
+                const int sl = orow % 3;
 #pragma unroll
                 for (int st = 0; st < NS; ++st)
 #pragma unroll
-                    for (int d = 0; d < 3; ++d) {
-                        const uint2 u = *reinterpret_cast<const uint2*>(
-                            tile + st * kDwStreamBytes + ((hr * kDwHW + col + d) * kDwCh + g * 4) * 2);
-                        win[st][slot][d][0] = bf16x2_to_f32x2(u.x);
-                        win[st][slot][d][1] = bf16x2_to_f32x2(u.y);
+                    for (int px = 0; px < 2; ++px) {
+                        if (dr == 0)
+                            acc[sl][px][st] = mul2(in[st][px], wr[st][0]);
+                        else
+                            ffma2(acc[sl][px][st], in[st][px], wr[st][dr * 3]);
+                        ffma2(acc[sl][px][st], in[st][px + 1], wr[st][dr * 3 + 1]);
+                        ffma2(acc[sl][px][st], in[st][px + 2], wr[st][dr * 3 + 2]);
                     }
-            };
-            load_row(0, 0);
-            load_row(1, 1);
+            }
+            const int done = hr - 2;  // this output row is complete
+            if (done >= 0) {
+                const int sl = done % 3;
+                uint32_t pk[2];
 #pragma unroll
-            for (int ry = 0; ry < kDwTH; ++ry) {
-                load_row(ry + 2, 2);
-                f32x2 acc[NS][2];
-#pragma unroll
-                for (int st = 0; st < NS; ++st) {
-                    acc[st][0] = 0ull;
-                    acc[st][1] = 0ull;
-#pragma unroll
-                    for (int rr = 0; rr < 3; ++rr)
-#pragma unroll
-                        for (int d = 0; d < 3; ++d) {
-                            ffma2(acc[st][0], win[st][rr][d][0], wr[st][rr * 3 + d][0]);
-                            ffma2(acc[st][1], win[st][rr][d][1], wr[st][rr * 3 + d][1]);
-                        }
+                for (int px = 0; px < 2; ++px) {
+                    f32x2 o = acc[sl][px][0];
+                    if (GATE) o = mul2(gelu2(o), acc[sl][px][NS - 1]);
+                    float o0, o1;
+                    unpack2(o, o0, o1);
+                    pk[px] = pack_bf16x2(o0, o1);
                 }
-                float o[4];
-                unpack2(acc[0][0], o[0], o[1]);
-                unpack2(acc[0][1], o[2], o[3]);
-                if (GATE) {
-                    float q[4];
-                    unpack2(acc[NS - 1][0], q[0], q[1]);
-                    unpack2(acc[NS - 1][1], q[2], q[3]);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) o[i] = gelu_as(o[i]) * q[i];
+                if (fast) {
+                    *reinterpret_cast<uint32_t*>(yp0) = pk[0];
+                    *reinterpret_cast<uint32_t*>(yp1) = pk[1];
+                } else if (done < nrows) {
+                    if (ok0) *reinterpret_cast<uint32_t*>(yp0) = pk[0];
+                    if (ok1) *reinterpret_cast<uint32_t*>(yp1) = pk[1];
                 }
-                const int gy = ty * kDwTH + ry;
-                if (cvalid && gx < p.W && gy < p.H) {
-                    uint2 pk;
-                    pk.x = pack_bf16x2(o[0], o[1]);
-                    pk.y = pack_bf16x2(o[2], o[3]);
-                    *reinterpret_cast<uint2*>(p.y + (((long long)img * p.H + gy) * p.W + gx) * p.ldy + c0) = pk;
-                }
-#pragma unroll
-                for (int st = 0; st < NS; ++st)
-#pragma unroll
-                    for (int d = 0; d < 3; ++d)
-#pragma unroll
-                        for (int k = 0; k < 2; ++k) {
-                            win[st][0][d][k] = win[st][1][d][k];
-                            win[st][1][d][k] = win[st][2][d][k];
-                        }
+                yp0 += row_step;
+                yp1 += row_step;
             }
         }
         __syncwarp();
@@ -185,7 +232,7 @@ __global__ void __launch_bounds__(288, 1) dw3x3_tma_kernel(const __grid_constant
 static int dw_tma_launch(bool gate, const bf16* x, long long ldx, int Ctot, bf16* y, long long ldy, int Nimg, int H,
                          int W, int Cout, int hp_off, const float* wt, int wt_ld, cudaStream_t stream) {
     IRB_REQUIRE(ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0, "dw3x3: x must be 16-byte aligned rows");
-    IRB_REQUIRE(Cout % 4 == 0 && ldy % 4 == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0, "dw3x3: y alignment");
+    IRB_REQUIRE(Cout % 2 == 0 && ldy % 2 == 0 && (reinterpret_cast<uintptr_t>(y) & 3) == 0, "dw3x3: y alignment");
     DwParams p{};
     uint64_t dims[4] = {uint64_t(Ctot), uint64_t(W), uint64_t(H), uint64_t(Nimg)};
     uint64_t str[3] = {uint64_t(ldx) * 2, uint64_t(ldx) * 2 * W, uint64_t(ldx) * 2 * W * H};
@@ -209,7 +256,7 @@ static int dw_tma_launch(bool gate, const bf16* x, long long ldx, int Ctot, bf16
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int grid = int(total < sms ? total : sms);
-    const size_t smem = size_t(kDwStages) * (gate ? 2 : 1) * kDwStreamBytes + 128 + 64;
+    const size_t smem = size_t(kDwStages) * (gate ? 2 : 1) * kDwStreamBytes + 128 + 64 + kDwStages * 16;
     static bool attr_set = false;
     if (!attr_set) {
         IRB_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -217,9 +264,9 @@ static int dw_tma_launch(bool gate, const bf16* x, long long ldx, int Ctot, bf16
         attr_set = true;
     }
     if (gate)
-        dw3x3_tma_kernel<true><<<grid, 288, smem, stream>>>(p);
+        dw3x3_tma_kernel<true><<<grid, kDwThreads, smem, stream>>>(p);
     else
-        dw3x3_tma_kernel<false><<<grid, 288, smem, stream>>>(p);
+        dw3x3_tma_kernel<false><<<grid, kDwThreads, smem, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
     const double px = double(Nimg) * H * W, cin = gate ? 2.0 * Cout : double(Cout);
     prof_mark(gate ? "dw3x3_gate_tma" : "dw3x3_tma", Cout, 2, 18.0 * px * cin, px * (cin + Cout) * 2 + 36.0 * cin, stream);

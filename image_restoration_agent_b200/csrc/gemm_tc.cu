@@ -11,9 +11,10 @@
 //   2-D TMA map with a {64, BN} box. Both operands land in shared memory in the 128B-swizzled K-major layout
 //   that the UMMA descriptors below describe.
 //
-// One CTA = one 128 x BN output tile. Warp 0 lane 0: TMA producer; warp 1 lane 0: tcgen05.mma issuer;
-// warps 2..5: epilogue (TMEM -> registers -> fused bias/act/residual -> global). A ring of `stages`
-// shared-memory slots with full/empty mbarriers decouples TMA from the tensor core.
+// Persistent CTAs walk 128 x BN output tiles. Warp 0 lane 0: TMA producer; warp 1 lane 0: tcgen05.mma issuer;
+// warps 2..5 / 6..9: two epilogue sets, one per TMEM accumulator (TMEM -> registers -> fused LN-fold / bias / act /
+// residual -> swizzled smem -> TMA store). A ring of `stages` shared-memory slots with full/empty mbarriers
+// decouples TMA from the tensor core; tfull/tempty mbarriers hand accumulators between MMA and epilogue.
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
@@ -131,9 +132,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
     uint64_t* tfull_bar = empty_bar + p.stages;   // [2] accumulator ready (MMA -> epilogue)
     uint64_t* tempty_bar = tfull_bar + 2;         // [2] accumulator drained (epilogue -> MMA)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-    float* colvec = reinterpret_cast<float*>(tmem_slot + 4);  // [2 tiles][bias | colsum][256], 16-byte aligned
+    const int ncolv = p.tiles_n * p.BN;                        // padded column count
+    float* colvec = reinterpret_cast<float*>(tmem_slot + 4);  // [bias | colsum][ncolv], 16-byte aligned, staged once
     // 8 epilogue warps x 4 KB staging blocks for TMA stores ([32 rows][64 bf16], 128B-swizzled), 1024-aligned
-    uint8_t* staging = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(colvec + 1024) + 1023) & ~uintptr_t(1023));
+    uint8_t* staging = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(colvec + 2 * ncolv) + 1023) & ~uintptr_t(1023));
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -149,7 +151,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             }
             for (int a = 0; a < 2; ++a) {
                 mbar_init(&tfull_bar[a], 1);
-                mbar_init(&tempty_bar[a], 8);
+                mbar_init(&tempty_bar[a], 4);
             }
             fence_mbar_init();
         }
@@ -221,37 +223,35 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             umma_commit(&tfull_bar[a]);  // accumulator complete
         }
     } else if (warp >= 2) {
-        // ===== epilogue: TMEM -> registers -> global. Warp e owns TMEM lane quarter (warp & 3); the two warps of
-        // a quarter split the tile's columns. =====
+        // ===== epilogue: TMEM -> registers -> global. Two sets of 4 warps: set s drains accumulator s, i.e. the
+        // tiles t of this CTA with (t & 1) == s, so two tiles are in the epilogue at once and the sets never wait
+        // for each other. Warp (warp & 3) owns that TMEM lane quarter (rows q*32 .. q*32+31 of the tile). =====
         const int q = warp & 3;
-        const int half = (warp - 2) >> 2;
+        const int set = (warp - 2) >> 2;
         const int r = q * 32 + lane;
-        const int ncol16 = p.BN >> 4;                 // 16-column groups per tile
-        const int g0 = half ? (ncol16 + 1) / 2 : 0;   // this warp's groups [g0, g1)
-        const int g1 = half ? ncol16 : (ncol16 + 1) / 2;
+        const int ncol16 = p.BN >> 4;  // 16-column groups per tile
         const int et = threadIdx.x - 64;  // 0..255
+        float* s_bias_all = colvec;
+        float* s_cs_all = colvec + ncolv;
+        for (int i = et; i < ncolv; i += 256) {
+            s_bias_all[i] = (p.epi.bias && i < p.N) ? __ldg(p.epi.bias + i) : 0.f;
+            s_cs_all[i] = (p.epi.ln_colsum && i < p.N) ? __ldg(p.epi.ln_colsum + i) : 0.f;
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         // fast path: aligned vector access for 16-column groups, no pixel shuffle / post scale
         const bool vec_ok = p.epi.ps == 0 && p.epi.post_scale == 1.0f && p.epi.post_shift == nullptr &&
                             (p.epi.out_dt == DT_BF16 ? (p.epi.ldo % 8 == 0) : (p.epi.ldo % 4 == 0)) &&
                             (reinterpret_cast<uintptr_t>(p.epi.out) % 16 == 0) &&
                             (!p.epi.res || ((p.epi.res_dt == DT_BF16 ? (p.epi.ldr % 8 == 0) : (p.epi.ldr % 4 == 0)) &&
                                             reinterpret_cast<uintptr_t>(p.epi.res) % 16 == 0));
-        int t = 0;
-        for (int w = blockIdx.x; w < p.total; w += gridDim.x, ++t) {
+        int t = set;
+        for (int w = blockIdx.x + set * gridDim.x; w < p.total; w += 2 * gridDim.x, t += 2) {
             const int nt = w % p.tiles_n;
             const int mt = (w / p.tiles_n) % p.tiles_m;
             const int z = w / (p.tiles_n * p.tiles_m);
             const int n0 = nt * p.BN;
-            const int a = t & 1;
-            // stage this tile's per-column vectors (double-buffered by tile parity; one barrier per tile)
-            float* s_bias = colvec + a * 512;
-            float* s_cs = s_bias + 256;
-            if (et < p.BN) {
-                const int col = n0 + et;
-                s_bias[et] = (p.epi.bias && col < p.N) ? __ldg(p.epi.bias + col) : 0.f;
-                s_cs[et] = (p.epi.ln_colsum && col < p.N) ? __ldg(p.epi.ln_colsum + col) : 0.f;
-            }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            const float* s_bias = s_bias_all + n0;
+            const float* s_cs = s_cs_all + n0;
             long long grow;
             bool valid;
             int py = 0, px = 0;
@@ -265,22 +265,22 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 valid = (py < p.H) && (px < p.W);
                 grow = ((long long)z * p.H + py) * p.W + px;
             }
-            mbar_wait(&tfull_bar[a], (t >> 1) & 1);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + a * p.acc_stride + (uint32_t(q * 32) << 16);
+            // the row's LayerNorm statistics do not depend on the accumulator: fetch them before waiting for it
             float fa = 1.f, fb = 0.f;
             if (p.epi.ln_stats && valid) {
                 const float2 st = __ldg(p.epi.ln_stats + grow);
                 fa = st.y;
                 fb = p.epi.ln_colsum ? -st.x * st.y : 0.f;
             }
+            mbar_wait(&tfull_bar[set], (t >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + set * p.acc_stride + (uint32_t(q * 32) << 16);
             if (p.tma_store) {
                 // ---- 64-column blocks: TMEM -> registers (math) -> swizzled smem block -> TMA store ----
                 const int nblk = (p.BN + 63) >> 6;
-                const int b0 = half ? (nblk + 1) / 2 : 0, b1 = half ? nblk : (nblk + 1) / 2;
                 uint8_t* stg = staging + (warp - 2) * 4096;
                 const bool has_res = p.epi.res != nullptr && valid;
-                for (int blk = b0; blk < b1; ++blk) {
+                for (int blk = 0; blk < nblk; ++blk) {
                     const int cb = blk * 64;
                     if (n0 + cb >= p.N) break;  // warp-uniform
                     const int ng = min(4, (p.BN - cb) >> 4);
@@ -326,26 +326,26 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                     }
                 }
             } else {
-            for (int g = g0; g < g1; ++g) {
-                float v[16];
-                tmem_ld16(taddr + g * 16, v);
-                const int col0 = n0 + g * 16;
-                if (!valid || col0 >= p.N) continue;
-                if (vec_ok && col0 + 16 <= p.N) {
-                    if (p.epi.act == ACT_GELU)
-                        epi_fast16<ACT_GELU>(p.epi, grow, col0, v, s_bias + g * 16, s_cs + g * 16, fa, fb);
-                    else if (p.epi.act == ACT_LRELU)
-                        epi_fast16<ACT_LRELU>(p.epi, grow, col0, v, s_bias + g * 16, s_cs + g * 16, fa, fb);
-                    else
-                        epi_fast16<ACT_NONE>(p.epi, grow, col0, v, s_bias + g * 16, s_cs + g * 16, fa, fb);
-                } else {
-                    epi_apply_store<16>(p.epi, grow, col0, p.N, v, z, py, px);
+                for (int g = 0; g < ncol16; ++g) {
+                    float v[16];
+                    tmem_ld16(taddr + g * 16, v);
+                    const int col0 = n0 + g * 16;
+                    if (!valid || col0 >= p.N) continue;
+                    if (vec_ok && col0 + 16 <= p.N) {
+                        if (p.epi.act == ACT_GELU)
+                            epi_fast16<ACT_GELU>(p.epi, grow, col0, v, s_bias + g * 16, s_cs + g * 16, fa, fb);
+                        else if (p.epi.act == ACT_LRELU)
+                            epi_fast16<ACT_LRELU>(p.epi, grow, col0, v, s_bias + g * 16, s_cs + g * 16, fa, fb);
+                        else
+                            epi_fast16<ACT_NONE>(p.epi, grow, col0, v, s_bias + g * 16, s_cs + g * 16, fa, fb);
+                    } else {
+                        epi_apply_store<16>(p.epi, grow, col0, p.N, v, z, py, px);
+                    }
                 }
-            }
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty_bar[a]);
+            if (lane == 0) mbar_arrive(&tempty_bar[set]);
         }
         if (p.tma_store && lane == 0) bulk_wait0();  // all bulk stores of this warp have landed before the CTA exits
     }
@@ -454,21 +454,22 @@ static int sm_count() {
 
 static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     const int stage_bytes = kABytes + p.BN * 128;
-    int stages = (180 * 1024) / stage_bytes;
-    if (stages > 6) stages = 6;
-    if (stages < 2) stages = 2;
-    p.stages = stages;
     p.acc_stride = (p.BN + 31) / 32 * 32;
     p.tmem_cols = tmem_cols_for(2 * p.acc_stride);
     p.tiles_n = ceil_div(p.N, p.BN);
+    const size_t fixed = 1024 /*align*/ + 256 /*barriers*/ + size_t(2) * p.tiles_n * p.BN * 4 /*column vectors*/ +
+                         1024 + 8 * 4096 /*TMA-store staging*/;
+    IRB_REQUIRE(fixed + 2 * size_t(stage_bytes) <= 227 * 1024, "tc_gemm: N too large for the shared-memory column vectors");
+    int stages = int((227 * 1024 - fixed) / stage_bytes);
+    if (stages > 8) stages = 8;
+    p.stages = stages;
     const long long total = (long long)batch * p.tiles_m * p.tiles_n;
     IRB_REQUIRE(total < (1ll << 31), "tc_gemm: too many tiles");
     p.total = int(total);
-    const size_t smem = size_t(stages) * stage_bytes + 1024 /*align*/ + 256 /*barriers*/ + 4096 /*column vectors*/ +
-                        1024 + 8 * 4096 /*TMA-store staging*/;
+    const size_t smem = size_t(stages) * stage_bytes + fixed;
     static bool attr_set = false;
     if (!attr_set) {
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        IRB_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set = true;
     }
     const int grid = int(total < sm_count() ? total : sm_count());

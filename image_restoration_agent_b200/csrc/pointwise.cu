@@ -135,58 +135,76 @@ int layernorm(const void* x, int x_dt, long long ldx, void* y, int y_dt, long lo
 // (mu, 1/sqrt(var + eps)) with the population variance about mu, two-pass in registers like layernorm_kernel.
 // Reads x once (C*e bytes per row), writes 8 bytes per row.
 // ----------------------------------------------------------------------------------------------
-template <typename TI, int LPP>
+// 4 lanes cooperate on one row; every lane owns 16-byte chunks lane, lane+4, ... (8 bf16 / 4 fp32 channels), so a
+// warp has 8 rows and up to 8 x C x e bytes in flight. NCH = chunks per lane (compile-time upper bound).
+template <typename TI, int NCH>
 __global__ void __launch_bounds__(256) row_stats_kernel(const TI* __restrict__ x, long long ldx, float2* __restrict__ st,
                                                         long long rows, int C, float eps) {
-    constexpr int MAXCH = 4;
-    const int lane = threadIdx.x % LPP;
-    const long long row = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / LPP;
+    constexpr int EPC = 16 / sizeof(TI);  // elements per 16-byte chunk
+    const int lane = threadIdx.x & 3;
+    const long long row = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 2;
     const bool active = row < rows;
-    const int nch = C >> 2;
-    float v[MAXCH][4];
+    float v[NCH][EPC];
     float s = 0.f;
+    const TI* xr = x + (active ? row : 0) * ldx;
 #pragma unroll
-    for (int j = 0; j < MAXCH; ++j) {
-        const int ch = lane + j * LPP;
-        if (active && ch < nch) {
-            Vec4<TI>::load(x + row * ldx + ch * 4, v[j]);
-            s += v[j][0] + v[j][1] + v[j][2] + v[j][3];
+    for (int j = 0; j < NCH; ++j) {
+        const int c0 = (lane + j * 4) * EPC;
+        if (active && c0 < C) {
+            const uint4 u = __ldg(reinterpret_cast<const uint4*>(xr + c0));
+            if (sizeof(TI) == 2) {
+                unpack_bf16x2(u.x, v[j][0], v[j][1]);
+                unpack_bf16x2(u.y, v[j][2], v[j][3]);
+                unpack_bf16x2(u.z, v[j][4 % EPC], v[j][5 % EPC]);
+                unpack_bf16x2(u.w, v[j][6 % EPC], v[j][7 % EPC]);
+            } else {
+                v[j][0] = __uint_as_float(u.x); v[j][1] = __uint_as_float(u.y);
+                v[j][2] = __uint_as_float(u.z); v[j][3] = __uint_as_float(u.w);
+            }
+#pragma unroll
+            for (int i = 0; i < EPC; ++i) {
+                if (c0 + i >= C) v[j][i] = 0.f;  // ragged last chunk (C % EPC != 0): padding columns are not data
+                s += v[j][i];
+            }
         } else {
-            v[j][0] = v[j][1] = v[j][2] = v[j][3] = 0.f;
+#pragma unroll
+            for (int i = 0; i < EPC; ++i) v[j][i] = 0.f;
         }
     }
-#pragma unroll
-    for (int o = LPP / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o, LPP);
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
     const float mu = s / float(C);
     float q = 0.f;
 #pragma unroll
-    for (int j = 0; j < MAXCH; ++j) {
-        const int ch = lane + j * LPP;
-        if (ch < nch) {
+    for (int j = 0; j < NCH; ++j) {
+        const int c0 = (lane + j * 4) * EPC;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float d = v[j][i] - mu;
-                q += d * d;
-            }
+        for (int i = 0; i < EPC; ++i) {
+            const float d = (c0 + i < C) ? v[j][i] - mu : 0.f;
+            q = fmaf(d, d, q);
         }
     }
-#pragma unroll
-    for (int o = LPP / 2; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o, LPP);
+    q += __shfl_xor_sync(0xffffffffu, q, 1);
+    q += __shfl_xor_sync(0xffffffffu, q, 2);
     if (active && lane == 0) st[row] = make_float2(mu, 1.0f / sqrtf(q / float(C) + eps));
 }
 
 int row_stats(const void* x, int x_dt, long long ldx, float2* stats, long long rows, int C, float eps,
               cudaStream_t stream) {
-    IRB_REQUIRE(C % 4 == 0 && C <= 512 && C > 0 && ldx % 4 == 0, "row_stats: C must be a multiple of 4 and <= 512");
+    const int epc = x_dt == DT_BF16 ? 8 : 4;
+    IRB_REQUIRE(C % 4 == 0 && C <= 512 && C > 0 && ldx % epc == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
+                "row_stats: C must be a multiple of 4 and <= 512, rows 16-byte aligned");
+    IRB_REQUIRE(ldx >= ceil_div(C, epc) * epc, "row_stats: row stride must cover the last 16-byte chunk");
     if (rows <= 0) return 0;
-    const int nch = C / 4;
-    const int lpp = nch <= 8 ? 8 : (nch <= 16 ? 16 : 32);
-    const int blocks = int(ceil_div_ll(rows * lpp, 256));
+    const int nch = ceil_div(ceil_div(C, epc), 4);  // chunks per lane
+    const int blocks = int(ceil_div_ll(rows * 4, 256));
 #define IRB_RS(T, L) row_stats_kernel<T, L><<<blocks, 256, 0, stream>>>((const T*)x, ldx, stats, rows, C, eps)
     if (x_dt == DT_BF16) {
-        if (lpp == 8) IRB_RS(bf16, 8); else if (lpp == 16) IRB_RS(bf16, 16); else IRB_RS(bf16, 32);
+        if (nch <= 2) IRB_RS(bf16, 2); else if (nch <= 3) IRB_RS(bf16, 3); else if (nch <= 6) IRB_RS(bf16, 6);
+        else if (nch <= 8) IRB_RS(bf16, 8); else if (nch <= 12) IRB_RS(bf16, 12); else IRB_RS(bf16, 16);
     } else {
-        if (lpp == 8) IRB_RS(float, 8); else if (lpp == 16) IRB_RS(float, 16); else IRB_RS(float, 32);
+        if (nch <= 3) IRB_RS(float, 3); else if (nch <= 6) IRB_RS(float, 6); else if (nch <= 12) IRB_RS(float, 12);
+        else if (nch <= 16) IRB_RS(float, 16); else if (nch <= 24) IRB_RS(float, 24); else IRB_RS(float, 32);
     }
 #undef IRB_RS
     IRB_CHECK_CUDA(cudaGetLastError());
