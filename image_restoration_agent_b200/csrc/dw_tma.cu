@@ -21,7 +21,7 @@ static constexpr int kDwTW = 32, kDwTH = 8;                    // output tile (p
 static constexpr int kDwHW = kDwTW + 2, kDwHH = kDwTH + 2;     // halo'd tile
 static constexpr int kDwCh = 64;                               // channels per chunk = one 128-byte row
 static constexpr int kDwStreamBytes = kDwHH * kDwHW * kDwCh * 2;  // 43 520
-static constexpr int kDwStages = 2;
+static constexpr int kDwStagesGate = 2, kDwStagesPlain = 4;  // 2 x 87 KB / 4 x 43.5 KB of shared memory
 static constexpr int kDwConsumerWarps = kDwTW / 2;             // 16
 static constexpr int kDwThreads = (kDwConsumerWarps + 1) * 32; // + producer warp
 
@@ -35,69 +35,16 @@ struct alignas(64) DwParams {
     int tiles_x, tiles_y, chunks, total;
 };
 
-typedef unsigned long long f32x2;  // two packed fp32 (lo = even channel, hi = odd channel)
-
-__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
-    f32x2 r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-    return r;
-}
-__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-}
-__device__ __forceinline__ f32x2 bf16x2_to_f32x2(uint32_t u) {
-    return pack2(__uint_as_float(u << 16), __uint_as_float(u & 0xFFFF0000u));
-}
-__device__ __forceinline__ void ffma2(f32x2& acc, f32x2 a, f32x2 b) {
-    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
-}
-__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
-    f32x2 r;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-    return r;
-}
-__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
-    f32x2 r;
-    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
-__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
-    uint32_t v;
-    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
-    return v;
-}
-__device__ __forceinline__ f32x2 splat2(float v) { return pack2(v, v); }
-
-// gelu on both halves (same formula as gelu_as in common.cuh)
-__device__ __forceinline__ f32x2 gelu2(f32x2 x) {
-    const f32x2 h = mul2(x, splat2(0.5f));
-    float h0, h1;
-    unpack2(h, h0, h1);
-    const float t0 = rcp_approx(fmaf(0.3275911f * 1.41421356237f, fabsf(h0), 1.0f));
-    const float t1 = rcp_approx(fmaf(0.3275911f * 1.41421356237f, fabsf(h1), 1.0f));
-    const f32x2 t = pack2(t0, t1);
-    f32x2 poly = fma2(splat2(-1.061405429f), t, splat2(1.453152027f));
-    poly = fma2(poly, t, splat2(-1.421413741f));
-    poly = fma2(poly, t, splat2(0.284496736f));
-    poly = fma2(poly, t, splat2(-0.254829592f));
-    poly = mul2(poly, t);
-    const f32x2 s = mul2(mul2(h, h), splat2(-2.88539008178f));
-    float s0, s1;
-    unpack2(s, s0, s1);
-    const f32x2 e = fma2(poly, pack2(ex2_approx(s0), ex2_approx(s1)), splat2(1.0f));
-    float e0, e1;
-    unpack2(e, e0, e1);
-    return pack2(fmaf(fabsf(h0), e0, h0), fmaf(fabsf(h1), e1, h1));
-}
-
-// Work order: chunk slowest, then image, tile row, tile column, so that the items a CTA walks (w, w + grid, ...)
-// mostly share their channel chunk (weights stay in registers) and neighbouring tiles are in flight together
-// (halo reads hit L2). The producer decodes the item once and hands (img, ty, tx, chunk) to the consumers through
-// the stage's shared-memory slot, so the 16 consumer warps do no integer division.
+// Work order: CTA b owns channel chunk (b % chunks) for the whole launch (its 9 x 2 weight pairs stay in registers)
+// and walks the spatial tiles (image, tile row, tile column) b / chunks, + grid / chunks, ...; the grid is a
+// multiple of `chunks`, so at any moment the CTAs cover ALL chunks of one neighbourhood of tiles: DRAM rows are
+// consumed whole and halo re-reads hit L2. The producer decodes the tile once and hands (img, ty, tx) to the
+// consumers through the stage's shared-memory slot, so the 16 consumer warps do no integer division.
 template <bool GATE>
 __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_constant__ DwParams p) {
     constexpr int NS = GATE ? 2 : 1;
     constexpr int stage_bytes = NS * kDwStreamBytes;
+    constexpr int kDwStages = GATE ? kDwStagesGate : kDwStagesPlain;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + kDwStages * stage_bytes);
@@ -114,19 +61,19 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_c
     __syncthreads();
     const int per_chunk = p.total / p.chunks;  // images * tiles
     const int per_img = p.tiles_x * p.tiles_y;
+    const int chunk = blockIdx.x % p.chunks;
+    const int sp0 = blockIdx.x / p.chunks, sp_step = gridDim.x / p.chunks;
 
     if (warp == kDwConsumerWarps) {
         if (lane == 0) {
             tma_prefetch_desc(&p.tm);
             int it = 0;
-            for (int w = blockIdx.x; w < p.total; w += gridDim.x, ++it) {
+            for (int sp = sp0; sp < per_chunk; sp += sp_step, ++it) {
                 const int s = it % kDwStages;
                 const uint32_t ph = (it / kDwStages) & 1;
                 mbar_wait(&empty[s], ph ^ 1);
-                const int chunk = w / per_chunk;
-                int r = w - chunk * per_chunk;
-                const int img = r / per_img;
-                r -= img * per_img;
+                const int img = sp / per_img;
+                int r = sp - img * per_img;
                 const int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
                 item[s] = make_int4(img, ty, tx, chunk);  // ordered before the consumers' reads by the mbarrier
                 uint8_t* dst = smem + s * stage_bytes;
@@ -144,29 +91,24 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_c
     const int col0 = warp * 2;
     const uint32_t lane_off = smem_u32(smem) + (col0 * kDwCh + lane * 2) * 2;
     const long long row_step = (long long)p.W * p.ldy;
-    int cur_chunk = -1;
-    bool cvalid = false;
+    const int c0 = chunk * kDwCh + lane * 2;
+    const bool cvalid = c0 < p.Cout;
     f32x2 wr[NS][9];
+#pragma unroll
+    for (int st = 0; st < NS; ++st)
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+            float2 w2 = make_float2(0.f, 0.f);
+            if (cvalid) w2 = __ldg(reinterpret_cast<const float2*>(p.wt + (long long)t * p.wt_ld + c0 + st * p.hp_off));
+            wr[st][t] = pack2(w2.x, w2.y);
+        }
     int it = 0;
-    for (int w = blockIdx.x; w < p.total; w += gridDim.x, ++it) {
+    for (int sp = sp0; sp < per_chunk; sp += sp_step, ++it) {
         const int s = it % kDwStages;
         const uint32_t ph = (it / kDwStages) & 1;
         mbar_wait(&full[s], ph);
         const int4 id = item[s];
-        const int img = id.x, ty = id.y, tx = id.z, chunk = id.w;
-        const int c0 = chunk * kDwCh + lane * 2;
-        if (chunk != cur_chunk) {  // warp-uniform
-            cur_chunk = chunk;
-            cvalid = c0 < p.Cout;
-#pragma unroll
-            for (int st = 0; st < NS; ++st)
-#pragma unroll
-                for (int t = 0; t < 9; ++t) {
-                    float2 w2 = make_float2(0.f, 0.f);
-                    if (cvalid) w2 = __ldg(reinterpret_cast<const float2*>(p.wt + (long long)t * p.wt_ld + c0 + st * p.hp_off));
-                    wr[st][t] = pack2(w2.x, w2.y);
-                }
-        }
+        const int img = id.x, ty = id.y, tx = id.z;
         const uint32_t tile = lane_off + s * stage_bytes;
         const int gx = tx * kDwTW + col0;
         const int nrows = min(kDwTH, p.H - ty * kDwTH);
@@ -255,8 +197,12 @@ static int dw_tma_launch(bool gate, const bf16* x, long long ldx, int Ctot, bf16
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int grid = int(total < sms ? total : sms);
-    const size_t smem = size_t(kDwStages) * (gate ? 2 : 1) * kDwStreamBytes + 128 + 64 + kDwStages * 16;
+    IRB_REQUIRE(p.chunks <= sms, "dw3x3: too many channel chunks");
+    const int spatial = p.total / p.chunks;
+    const int groups = spatial < sms / p.chunks ? spatial : sms / p.chunks;  // CTAs per chunk
+    const int grid = groups * p.chunks;
+    const int nst = gate ? kDwStagesGate : kDwStagesPlain;
+    const size_t smem = size_t(nst) * (gate ? 2 : 1) * kDwStreamBytes + 128 + nst * 32;
     static bool attr_set = false;
     if (!attr_set) {
         IRB_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

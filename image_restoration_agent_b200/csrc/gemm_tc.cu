@@ -18,6 +18,7 @@
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
+#include <stdlib.h>
 
 namespace irb {
 
@@ -43,6 +44,7 @@ struct alignas(64) TcGemmParams {
     int tmem_cols;    // 2 accumulators of acc_stride columns
     int acc_stride;
     int tiles_m, tiles_n, total;  // work items: total = batch * tiles_m * tiles_n, n fastest
+    int m_outer;                  // 1: a CTA walks all n-tiles of its m-tile back to back
     Epi epi;
 };
 
@@ -121,11 +123,81 @@ __device__ __forceinline__ void epi_fast16(const Epi& e, long long row, int col0
     }
 }
 
-// Persistent CTA: walks work items w = blockIdx.x, blockIdx.x + gridDim.x, ...  Two TMEM accumulators let the
-// epilogue of tile i overlap the MMAs of tile i+1; the shared-memory ring runs across tile boundaries.
+// Vectorised epilogue math for one full 16-column group held as raw TMEM words: packed FFMA2 / FADD2, column
+// vectors read from shared memory as 16-byte loads, bf16 residual pre-fetched by the caller (r0: columns 0..7,
+// r1: 8..15). LN 0: y = acc; 1: y = acc * a + bias[col]; 2: y = acc * a + (b * colsum[col] + bias[col]).
+// Everything that selects a variant is a template parameter: the unrolled body has no branches.
+template <int ACT, int LN, bool RES>
+__device__ __forceinline__ void epi_group16(const uint32_t* acc, const float* sb, const float* scs, f32x2 a2, f32x2 b2,
+                                            float slope, const uint4& r0, const uint4& r1, uint32_t* pk) {
+#pragma unroll
+    for (int j4 = 0; j4 < 4; ++j4) {
+        f32x2 x0 = pack2(__uint_as_float(acc[4 * j4 + 0]), __uint_as_float(acc[4 * j4 + 1]));
+        f32x2 x1 = pack2(__uint_as_float(acc[4 * j4 + 2]), __uint_as_float(acc[4 * j4 + 3]));
+        if (LN != 0) {
+            const ulonglong2 bb = *reinterpret_cast<const ulonglong2*>(sb + j4 * 4);
+            f32x2 bi0 = bb.x, bi1 = bb.y;
+            if (LN == 2) {
+                const ulonglong2 cc = *reinterpret_cast<const ulonglong2*>(scs + j4 * 4);
+                bi0 = fma2(b2, cc.x, bi0);
+                bi1 = fma2(b2, cc.y, bi1);
+            }
+            x0 = fma2(x0, a2, bi0);
+            x1 = fma2(x1, a2, bi1);
+        }
+        if (ACT == ACT_GELU) {
+            x0 = gelu2(x0);
+            x1 = gelu2(x1);
+        } else if (ACT == ACT_LRELU) {
+            float t0, t1, t2, t3;
+            unpack2(x0, t0, t1);
+            unpack2(x1, t2, t3);
+            x0 = pack2(t0 > 0.f ? t0 : t0 * slope, t1 > 0.f ? t1 : t1 * slope);
+            x1 = pack2(t2 > 0.f ? t2 : t2 * slope, t3 > 0.f ? t3 : t3 * slope);
+        }
+        if (RES) {
+            const uint32_t rw0 = j4 == 0 ? r0.x : (j4 == 1 ? r0.z : (j4 == 2 ? r1.x : r1.z));
+            const uint32_t rw1 = j4 == 0 ? r0.y : (j4 == 1 ? r0.w : (j4 == 2 ? r1.y : r1.w));
+            x0 = add2(x0, bf16x2_to_f32x2(rw0));
+            x1 = add2(x1, bf16x2_to_f32x2(rw1));
+        }
+        pk[2 * j4] = f32x2_to_bf16x2(x0);
+        pk[2 * j4 + 1] = f32x2_to_bf16x2(x1);
+    }
+}
+
+// One 64-column block (ng <= 4 groups) of one row: math + the swizzled 16-byte stores into the staging block.
+template <int ACT, int LN, bool RES>
+__device__ __forceinline__ void epi_block(const uint32_t (*acc)[16], const uint4* rr, int ng, const float* sb,
+                                          const float* scs, f32x2 a2, f32x2 b2, float slope, uint8_t* stg_row,
+                                          int lane) {
+#pragma unroll
+    for (int gi = 0; gi < 4; ++gi) {
+        if (gi < ng) {
+            uint32_t pk[8];
+            epi_group16<ACT, LN, RES>(acc[gi], sb + gi * 16, scs + gi * 16, a2, b2, slope, rr[2 * gi], rr[2 * gi + 1], pk);
+#pragma unroll
+            for (int c = 0; c < 2; ++c)
+                *reinterpret_cast<uint4*>(stg_row + (((2 * gi + c) ^ (lane & 7)) << 4)) =
+                    make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
+        }
+    }
+}
+
+// Work item w = (z * tiles_m + mt) * tiles_n + nt. A CTA takes m-tiles blockIdx.x, + gridDim.x, ... and walks ALL
+// n-tiles of an m-tile back to back, so the A tile it re-reads for the next n-tile is still in L2.
+__device__ __forceinline__ int first_item(const TcGemmParams& p) {
+    return p.m_outer ? blockIdx.x * p.tiles_n : blockIdx.x;
+}
+__device__ __forceinline__ int next_item(int w, const TcGemmParams& p) {
+    if (!p.m_outer) return w + gridDim.x;
+    return ((w + 1) % p.tiles_n) ? w + 1 : w + 1 + (gridDim.x - 1) * p.tiles_n;
+}
+
 __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_constant__ TcGemmParams p) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    // pointer arithmetic on the __shared__ symbol (not an integer round trip) keeps the address space known: LDS/STS
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const int stage_bytes = kABytes + p.BN * 128;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.stages * stage_bytes);
     uint64_t* empty_bar = full_bar + p.stages;
@@ -134,8 +206,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
     const int ncolv = p.tiles_n * p.BN;                        // padded column count
     float* colvec = reinterpret_cast<float*>(tmem_slot + 4);  // [bias | colsum][ncolv], 16-byte aligned, staged once
-    // 8 epilogue warps x 4 KB staging blocks for TMA stores ([32 rows][64 bf16], 128B-swizzled), 1024-aligned
-    uint8_t* staging = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(colvec + 2 * ncolv) + 1023) & ~uintptr_t(1023));
+    // 8 epilogue warps x 2 x 4 KB staging blocks for TMA stores ([32 rows][64 bf16], 128B-swizzled), 1024-aligned;
+    // double-buffered so that a warp never waits for the store it has just issued (wait_group.read 1)
+    uint8_t* stg_lo = reinterpret_cast<uint8_t*>(colvec + 2 * ncolv);
+    uint8_t* staging = stg_lo + ((1024u - (smem_u32(stg_lo) & 1023u)) & 1023u);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -168,7 +242,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
     if (warp == 0 && lane == 0) {
         // ===== TMA producer =====
         int it = 0;
-        for (int w = blockIdx.x; w < p.total; w += gridDim.x) {
+        for (int w = first_item(p); w < p.total; w = next_item(w, p)) {
             const int nt = w % p.tiles_n;
             const int mt = (w / p.tiles_n) % p.tiles_m;
             const int z = w / (p.tiles_n * p.tiles_m);
@@ -200,7 +274,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
         // ===== MMA issuer =====
         const uint32_t idesc = make_idesc_bf16(kTileM, p.BN, 0, 0);
         int it = 0, t = 0;
-        for (int w = blockIdx.x; w < p.total; w += gridDim.x, ++t) {
+        for (int w = first_item(p); w < p.total; w = next_item(w, p), ++t) {
             const int a = t & 1;
             mbar_wait(&tempty_bar[a], ((t >> 1) & 1) ^ 1);
             tc_fence_after();
@@ -244,8 +318,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                             (reinterpret_cast<uintptr_t>(p.epi.out) % 16 == 0) &&
                             (!p.epi.res || ((p.epi.res_dt == DT_BF16 ? (p.epi.ldr % 8 == 0) : (p.epi.ldr % 4 == 0)) &&
                                             reinterpret_cast<uintptr_t>(p.epi.res) % 16 == 0));
-        int t = set;
-        for (int w = blockIdx.x + set * gridDim.x; w < p.total; w += 2 * gridDim.x, t += 2) {
+        const int lnmode = p.epi.ln_colsum ? 2 : ((p.epi.ln_stats || p.epi.bias) ? 1 : 0);
+        const bool res_bf16 = p.epi.res != nullptr && p.epi.res_dt == DT_BF16;
+        int t = 0;
+        uint32_t sblk = 0;  // staging-block parity of this warp
+        for (int w = first_item(p); w < p.total; w = next_item(w, p), ++t) {
+            if ((t & 1) != set) continue;
             const int nt = w % p.tiles_n;
             const int mt = (w / p.tiles_n) % p.tiles_m;
             const int z = w / (p.tiles_n * p.tiles_m);
@@ -278,38 +356,83 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             if (p.tma_store) {
                 // ---- 64-column blocks: TMEM -> registers (math) -> swizzled smem block -> TMA store ----
                 const int nblk = (p.BN + 63) >> 6;
-                uint8_t* stg = staging + (warp - 2) * 4096;
+                uint8_t* stg_base = staging + (warp - 2) * 8192;
                 const bool has_res = p.epi.res != nullptr && valid;
+                const bool has_res_any = p.epi.res != nullptr;  // warp-uniform (rows past M read row 0, are clipped)
                 for (int blk = 0; blk < nblk; ++blk) {
                     const int cb = blk * 64;
                     if (n0 + cb >= p.N) break;  // warp-uniform
                     const int ng = min(4, (p.BN - cb) >> 4);
-                    uint32_t pk[32];
+                    uint8_t* stg = stg_base + (sblk & 1) * 4096;
+                    ++sblk;
+                    // fast path: no residual or a bf16 residual whose 16-column groups are all complete
+                    const bool ragged_res = has_res_any && (n0 + cb + ng * 16 > p.N);
+                    if ((res_bf16 || p.epi.res == nullptr) && !ragged_res) {
+                        // all TMEM loads and residual loads of the block in flight before the first wait
+                        uint32_t acc[4][16];
+                        uint4 rr[8];
 #pragma unroll
-                    for (int gi = 0; gi < 4; ++gi) {
-                        if (gi < ng) {
-                            float v[16];
-                            tmem_ld16(taddr + cb + gi * 16, v);
-                            const int col0 = n0 + cb + gi * 16;
-                            const int lr = has_res ? min(16, p.N - col0) : 0;
-                            if (p.epi.act == ACT_GELU)
-                                epi_math16<ACT_GELU>(p.epi, grow, col0, lr, v, s_bias + cb + gi * 16, s_cs + cb + gi * 16, fa, fb);
-                            else if (p.epi.act == ACT_LRELU)
-                                epi_math16<ACT_LRELU>(p.epi, grow, col0, lr, v, s_bias + cb + gi * 16, s_cs + cb + gi * 16, fa, fb);
-                            else
-                                epi_math16<ACT_NONE>(p.epi, grow, col0, lr, v, s_bias + cb + gi * 16, s_cs + cb + gi * 16, fa, fb);
+                        for (int gi = 0; gi < 4; ++gi)
+                            if (gi < ng) tmem_ld16_nowait(taddr + cb + gi * 16, acc[gi]);
+                        if (has_res_any) {
+                            const bf16* rrow = reinterpret_cast<const bf16*>(p.epi.res) + (valid ? grow : 0) * p.epi.ldr + n0 + cb;
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) pk[gi * 8 + j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+                            for (int gi = 0; gi < 4; ++gi) {
+                                if (gi < ng) {
+                                    rr[2 * gi] = __ldg(reinterpret_cast<const uint4*>(rrow + gi * 16));
+                                    rr[2 * gi + 1] = __ldg(reinterpret_cast<const uint4*>(rrow + gi * 16 + 8));
+                                }
+                            }
                         }
-                    }
-                    // the previous TMA store of this warp must have finished READING the staging block
-                    if (lane == 0) bulk_wait_read0();
-                    __syncwarp();
+                        const f32x2 a2 = splat2(fa), b2 = splat2(fb);
+                        // the store issued two blocks ago (same staging buffer) must have finished READING it
+                        if (lane == 0) bulk_wait_read1();
+                        __syncwarp();
+                        tmem_ld_wait();
+                        const float* sb = s_bias + cb;
+                        const float* sc = s_cs + cb;
+                        uint8_t* srow = stg + lane * 128;
+#define IRB_EPI(A, L, R) epi_block<A, L, R>(acc, rr, ng, sb, sc, a2, b2, p.epi.slope, srow, lane)
+#define IRB_EPI_LR(A)                                                  \
+    switch (lnmode * 2 + (has_res_any ? 1 : 0)) {                      \
+        case 0: IRB_EPI(A, 0, false); break;                           \
+        case 1: IRB_EPI(A, 0, true); break;                            \
+        case 2: IRB_EPI(A, 1, false); break;                           \
+        case 3: IRB_EPI(A, 1, true); break;                            \
+        case 4: IRB_EPI(A, 2, false); break;                           \
+        default: IRB_EPI(A, 2, true); break;                           \
+    }
+                        if (p.epi.act == ACT_GELU) {
+                            IRB_EPI_LR(ACT_GELU)
+                        } else if (p.epi.act == ACT_LRELU) {
+                            IRB_EPI_LR(ACT_LRELU)
+                        } else {
+                            IRB_EPI_LR(ACT_NONE)
+                        }
+#undef IRB_EPI_LR
+#undef IRB_EPI
+                    } else {
+                        if (lane == 0) bulk_wait_read1();
+                        __syncwarp();
 #pragma unroll
-                    for (int c = 0; c < 8; ++c) {
-                        if (c < 2 * ng) {
-                            uint4 u = make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
-                            *reinterpret_cast<uint4*>(stg + lane * 128 + ((c ^ (lane & 7)) << 4)) = u;
+                        for (int gi = 0; gi < 4; ++gi) {
+                            if (gi < ng) {
+                                float v[16];
+                                tmem_ld16(taddr + cb + gi * 16, v);
+                                const int col0 = n0 + cb + gi * 16;
+                                const int lr = has_res ? min(16, p.N - col0) : 0;
+                                if (p.epi.act == ACT_GELU)
+                                    epi_math16<ACT_GELU>(p.epi, grow, col0, lr, v, s_bias + cb + gi * 16, s_cs + cb + gi * 16, fa, fb);
+                                else if (p.epi.act == ACT_LRELU)
+                                    epi_math16<ACT_LRELU>(p.epi, grow, col0, lr, v, s_bias + cb + gi * 16, s_cs + cb + gi * 16, fa, fb);
+                                else
+                                    epi_math16<ACT_NONE>(p.epi, grow, col0, lr, v, s_bias + cb + gi * 16, s_cs + cb + gi * 16, fa, fb);
+#pragma unroll
+                                for (int c = 0; c < 2; ++c)
+                                    *reinterpret_cast<uint4*>(stg + lane * 128 + (((2 * gi + c) ^ (lane & 7)) << 4)) =
+                                        make_uint4(pack_bf16x2(v[c * 8 + 0], v[c * 8 + 1]), pack_bf16x2(v[c * 8 + 2], v[c * 8 + 3]),
+                                                   pack_bf16x2(v[c * 8 + 4], v[c * 8 + 5]), pack_bf16x2(v[c * 8 + 6], v[c * 8 + 7]));
+                            }
                         }
                     }
                     fence_proxy_async();
@@ -458,7 +581,7 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     p.tmem_cols = tmem_cols_for(2 * p.acc_stride);
     p.tiles_n = ceil_div(p.N, p.BN);
     const size_t fixed = 1024 /*align*/ + 256 /*barriers*/ + size_t(2) * p.tiles_n * p.BN * 4 /*column vectors*/ +
-                         1024 + 8 * 4096 /*TMA-store staging*/;
+                         1024 + 8 * 8192 /*TMA-store staging*/;
     IRB_REQUIRE(fixed + 2 * size_t(stage_bytes) <= 227 * 1024, "tc_gemm: N too large for the shared-memory column vectors");
     int stages = int((227 * 1024 - fixed) / stage_bytes);
     if (stages > 8) stages = 8;
@@ -472,7 +595,14 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
         IRB_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set = true;
     }
-    const int grid = int(total < sm_count() ? total : sm_count());
+    static int order = -1;
+    if (order < 0) {
+        const char* e = getenv("IRB_GEMM_ORDER");
+        order = e ? atoi(e) : 1;
+    }
+    p.m_outer = order;
+    const long long units = p.m_outer ? (long long)batch * p.tiles_m : total;
+    const int grid = int(units < sm_count() ? units : sm_count());
     tc_gemm_kernel<<<grid, kGemmThreads, smem, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
     return 0;

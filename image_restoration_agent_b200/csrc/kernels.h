@@ -43,6 +43,8 @@ int dwconv3x3_bf16_tma(const bf16* x, long long ldx, bf16* y, long long ldy, int
                        const float* wt, cudaStream_t stream);
 int dwconv3x3_gate_bf16_tma(const bf16* x, long long ldx, bf16* y, long long ldy, int Nimg, int H, int W, int hp,
                             const float* wt, cudaStream_t stream);
+// fp32 [rows][cin] (cin <= 4) -> bf16 [rows][8]: channel c = bf16(x), channel cin + c = bf16(x - hi), rest zero
+int split_hi_lo_bf16(const float* x, int cin, bf16* y, long long rows, cudaStream_t stream);
 int nearest_up2(const void* x, int dt, long long ldx, void* y, long long ldy, int Nimg, int H, int W, int C,
                 cudaStream_t stream);
 
@@ -59,7 +61,7 @@ int mdta_gram_simt(const void* qkv, int dt, long long ld, int Nimg, int P, int C
 // Weff[b][o][h*c+j] = sum_i Wp[o][h*c+i] attn[i][j]
 int mdta_softmax_weff(const float* Gpart, const float* ssq_part, int nchunks, const float* temperature,
                       const float* Wp, int Nimg, int C, int heads, void* Weff, int w_dt,
-                      float* attn_out /*optional*/, cudaStream_t stream);
+                      float* attn /*[Nimg][heads][c][c], required*/, cudaStream_t stream);
 
 // ---- swin_attn.cu ----------------------------------------------------------------------------
 int window_attention(const void* qkv, int dt, long long ld, void* out, long long ldo, int n, int H, int W, int C,

@@ -283,82 +283,117 @@ int mdta_gram_simt(const void* qkv, int dt, long long ld, int Nimg, int P, int C
     return 0;
 }
 
-// ---- fixed-order reduction of the partials + softmax + fold into project_out --------------------
-__global__ void __launch_bounds__(256) mdta_softmax_weff_kernel(const float* __restrict__ Gpart,
-                                                                const float* __restrict__ ssq_part, int nchunks,
-                                                                const float* __restrict__ temperature,
-                                                                const float* __restrict__ Wp, int C, int heads,
-                                                                void* __restrict__ Weff, int w_dt,
-                                                                float* __restrict__ attn_out) {
-    extern __shared__ float attn[];  // [c][c+1] then nrm[2c]
-    const int c = C / heads;
-    const int head = blockIdx.x, img = blockIdx.y;
-    const int ldA = c + 1;
-    float* nrm = attn + c * ldA;
+// ---- fixed-order reduction of the partials + softmax, then the fold into project_out ------------
+// Kernel A: CTA = 8 attention rows of one (image, head); warp = one row. Sums the per-chunk Gram / sum-of-squares
+// slots in slot order (bit-reproducible), applies F.normalize's denominators and the temperature, softmax over
+// the row, writes attn [n][heads][c][c] fp32.
+__global__ void __launch_bounds__(256) mdta_softmax_kernel(const float* __restrict__ Gpart,
+                                                           const float* __restrict__ ssq_part, int nchunks,
+                                                           const float* __restrict__ temperature, int c, int heads,
+                                                           float* __restrict__ attn_out) {
+    __shared__ float nrm_k[128];
+    const int head = blockIdx.y, img = blockIdx.z;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long slot0 = ((long long)img * heads + head) * nchunks;
     const float* g = Gpart + slot0 * c * c;
     const float* ss = ssq_part + slot0 * 2 * c;
-    for (int e = threadIdx.x; e < c * c; e += 256) {
-        float a = 0.f;
-        for (int k = 0; k < nchunks; ++k) a += g[(long long)k * c * c + e];
-        attn[(e / c) * ldA + (e % c)] = a;
-    }
     // F.normalize(dim=-1) divides by max(||.||_2, 1e-12) (restormer_arch.py:121-122)
-    for (int v = threadIdx.x; v < 2 * c; v += 256) {
+    for (int v = threadIdx.x; v < c; v += 256) {
         float a = 0.f;
-        for (int k = 0; k < nchunks; ++k) a += ss[(long long)k * 2 * c + v];
-        nrm[v] = fmaxf(sqrtf(a), 1e-12f);
+        for (int k = 0; k < nchunks; ++k) a += ss[(long long)k * 2 * c + c + v];
+        nrm_k[v] = fmaxf(sqrtf(a), 1e-12f);
     }
     __syncthreads();
+    const int i = blockIdx.x * 8 + warp;
+    if (i >= c) return;
+    float nq = 0.f;
+    for (int k = 0; k < nchunks; ++k) nq += ss[(long long)k * 2 * c + i];
+    nq = fmaxf(sqrtf(nq), 1e-12f);
     const float temp = __ldg(temperature + head);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int i = warp; i < c; i += 8) {  // one warp per row i
-        const float nq = nrm[i];
-        float mx = -INFINITY;
-        for (int j = lane; j < c; j += 32) {
-            const float s = attn[i * ldA + j] / (nq * nrm[c + j]) * temp;
-            attn[i * ldA + j] = s;
-            mx = fmaxf(mx, s);
-        }
-        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-        float sum = 0.f;
-        for (int j = lane; j < c; j += 32) {
-            const float e = expf(attn[i * ldA + j] - mx);
-            attn[i * ldA + j] = e;
-            sum += e;
-        }
-        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        const float inv = 1.0f / sum;
-        for (int j = lane; j < c; j += 32) {
-            const float a = attn[i * ldA + j] * inv;
-            attn[i * ldA + j] = a;
-            if (attn_out) attn_out[(((long long)img * heads + head) * c + i) * c + j] = a;
+    float sv[4];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+        const int j = lane + jj * 32;
+        sv[jj] = -INFINITY;
+        if (j < c) {
+            float a = 0.f;
+            const float* gp = g + (long long)i * c + j;
+#pragma unroll 8
+            for (int k = 0; k < nchunks; ++k) a += gp[(long long)k * c * c];
+            sv[jj] = a / (nq * nrm_k[j]) * temp;
+            mx = fmaxf(mx, sv[jj]);
         }
     }
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.f;
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+        const int j = lane + jj * 32;
+        sv[jj] = j < c ? expf(sv[jj] - mx) : 0.f;
+        sum += sv[jj];
+    }
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float inv = 1.0f / sum;
+    float* arow = attn_out + (((long long)img * heads + head) * c + i) * c;
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+        const int j = lane + jj * 32;
+        if (j < c) arow[j] = sv[jj] * inv;
+    }
+}
+
+// Kernel B: Weff[img][o][head*c + j] = sum_i Wp[o][head*c + i] * attn[img][head][i][j]; CTA = 16 rows o.
+__global__ void __launch_bounds__(256) mdta_weff_kernel(const float* __restrict__ attn, const float* __restrict__ Wp,
+                                                        int C, int heads, void* __restrict__ Weff, int w_dt) {
+    extern __shared__ float sm[];  // attn [c][c] then Wp rows [16][c]
+    const int c = C / heads;
+    const int head = blockIdx.y, img = blockIdx.z;
+    const int o0 = blockIdx.x * 16;
+    float* s_attn = sm;
+    float* s_w = sm + c * c;
+    const float* a = attn + ((long long)img * heads + head) * c * c;
+    for (int e = threadIdx.x; e < c * c; e += 256) s_attn[e] = a[e];
+    for (int e = threadIdx.x; e < 16 * c; e += 256) {
+        const int r = e / c, i = e % c;
+        s_w[e] = (o0 + r < C) ? __ldg(Wp + (long long)(o0 + r) * C + head * c + i) : 0.f;
+    }
     __syncthreads();
-    // Weff[img][o][head*c + j] = sum_i Wp[o][head*c + i] * attn[i][j]
-    for (int e = threadIdx.x; e < C * c; e += 256) {
-        const int o = e / c, j = e % c;
-        const float* wrow = Wp + (long long)o * C + head * c;
+    for (int e = threadIdx.x; e < 16 * c; e += 256) {
+        const int r = e / c, j = e % c;
+        if (o0 + r >= C) continue;
         float acc = 0.f;
-        for (int i = 0; i < c; ++i) acc = fmaf(__ldg(wrow + i), attn[i * ldA + j], acc);
-        st_from_float(Weff, ((long long)img * C + o) * C + head * c + j, w_dt, acc);
+        for (int i = 0; i < c; ++i) acc = fmaf(s_w[r * c + i], s_attn[i * c + j], acc);
+        st_from_float(Weff, ((long long)img * C + o0 + r) * C + head * c + j, w_dt, acc);
     }
 }
 
 int mdta_softmax_weff(const float* Gpart, const float* ssq_part, int nchunks, const float* temperature,
-                      const float* Wp, int Nimg, int C, int heads, void* Weff, int w_dt, float* attn_out,
+                      const float* Wp, int Nimg, int C, int heads, void* Weff, int w_dt, float* attn,
                       cudaStream_t stream) {
     const int c = C / heads;
     IRB_REQUIRE(C % heads == 0 && c <= 104, "mdta_softmax_weff: channels per head too large");
     IRB_REQUIRE(nchunks >= 1, "mdta_softmax_weff: nchunks");
-    const size_t smem = (size_t(c) * (c + 1) + 2 * c) * sizeof(float);
-    dim3 grid(heads, Nimg);
-    mdta_softmax_weff_kernel<<<grid, 256, smem, stream>>>(Gpart, ssq_part, nchunks, temperature, Wp, C, heads, Weff,
-                                                          w_dt, attn_out);
-    IRB_CHECK_CUDA(cudaGetLastError());
-    prof_mark("mdta_softmax_weff", C, heads, 2.0 * Nimg * C * C * c,
-              double(Nimg) * (nchunks * (C * c + 2.0 * C) * 4.0 + C * C * (w_dt == DT_BF16 ? 2 : 4)) + C * C * 4.0, stream);
+    IRB_REQUIRE(attn != nullptr, "mdta_softmax_weff: the attn buffer [n][heads][c][c] is required");
+    {
+        dim3 grid(ceil_div(c, 8), heads, Nimg);
+        mdta_softmax_kernel<<<grid, 256, 0, stream>>>(Gpart, ssq_part, nchunks, temperature, c, heads, attn);
+        IRB_CHECK_CUDA(cudaGetLastError());
+        prof_mark("mdta_softmax", C, heads, 0.0, double(Nimg) * (nchunks * (C * c + 2.0 * C) + C * c) * 4.0, stream);
+    }
+    {
+        const size_t smem = (size_t(c) * c + 16 * c) * sizeof(float);
+        static bool attr_set = false;
+        if (!attr_set) {
+            IRB_CHECK_CUDA(cudaFuncSetAttribute(mdta_weff_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+            attr_set = true;
+        }
+        dim3 grid(ceil_div(C, 16), heads, Nimg);
+        mdta_weff_kernel<<<grid, 256, smem, stream>>>(attn, Wp, C, heads, Weff, w_dt);
+        IRB_CHECK_CUDA(cudaGetLastError());
+        prof_mark("mdta_weff", C, heads, 2.0 * Nimg * C * C * c,
+                  double(Nimg) * (C * c * 4.0 + C * C * (w_dt == DT_BF16 ? 2 : 4)) + C * C * 4.0, stream);
+    }
     return 0;
 }
 

@@ -120,6 +120,23 @@ std::vector<float> pack_conv3x3(const BlobTensor& w, int& kpad, int& npad) {
             for (int t = 0; t < 9; ++t) o[(size_t(n) * 9 + t) * kpad + c] = w.data[(size_t(n) * C + c) * 9 + t];
     return o;
 }
+// First-layer convolutions (1 or 3 input channels) run on the tensor core with the fp32 input split into two bf16
+// terms x = hi + lo (split_hi_lo_bf16, pointwise.cu): channel c holds hi, channel C + c holds lo, and both get the
+// same weight, so the input keeps ~16 mantissa bits at no cost (K is padded to 64 anyway).
+std::vector<float> pack_conv3x3_split(const BlobTensor& w, int& kpad, int& npad) {
+    const int N = int(w.dims[0]), C = int(w.dims[1]);
+    kpad = 64;
+    npad = (N + 15) / 16 * 16;
+    std::vector<float> o(size_t(npad) * 9 * kpad, 0.f);
+    for (int n = 0; n < N; ++n)
+        for (int c = 0; c < C; ++c)
+            for (int t = 0; t < 9; ++t) {
+                const float v = w.data[(size_t(n) * C + c) * 9 + t];
+                o[(size_t(n) * 9 + t) * kpad + c] = v;
+                o[(size_t(n) * 9 + t) * kpad + C + c] = v;
+            }
+    return o;
+}
 std::vector<float> pack_linear(const float* w, int N, int K, int& kpad, int& npad) {
     kpad = (K + 7) / 8 * 8;
     npad = (N + 15) / 16 * 16;

@@ -392,4 +392,39 @@ int nearest_up2(const void* x, int dt, long long ldx, void* y, long long ldy, in
     return 0;
 }
 
+// ----------------------------------------------------------------------------------------------
+// x = hi + lo split of the fp32 network input for the tensor-core first convolution (see pack_conv3x3_split).
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) split_hi_lo_kernel(const float* __restrict__ x, int cin, bf16* __restrict__ y,
+                                                          long long rows) {
+    const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= rows) return;
+    float hi[4] = {0.f, 0.f, 0.f, 0.f}, lo[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int c = 0; c < cin; ++c) {
+        const float v = x[r * cin + c];
+        hi[c] = __bfloat162float(__float2bfloat16_rn(v));
+        lo[c] = v - hi[c];
+    }
+    float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int c = 0; c < cin; ++c) {
+        o[c] = hi[c];
+        o[cin + c] = lo[c];
+    }
+    uint4 u;
+    u.x = pack_bf16x2(o[0], o[1]);
+    u.y = pack_bf16x2(o[2], o[3]);
+    u.z = pack_bf16x2(o[4], o[5]);
+    u.w = pack_bf16x2(o[6], o[7]);
+    *reinterpret_cast<uint4*>(y + r * 8) = u;
+}
+
+int split_hi_lo_bf16(const float* x, int cin, bf16* y, long long rows, cudaStream_t stream) {
+    IRB_REQUIRE(cin >= 1 && cin <= 4, "split_hi_lo_bf16: cin must be <= 4");
+    if (rows <= 0) return 0;
+    split_hi_lo_kernel<<<int(ceil_div_ll(rows, 256)), 256, 0, stream>>>(x, cin, y, rows);
+    IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("split_hi_lo", cin, 0, 0.0, double(rows) * (cin * 4 + 16), stream);
+    return 0;
+}
+
 }  // namespace irb

@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include "common.cuh"
 
 namespace irb {
 
@@ -92,6 +93,7 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* s
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // ----------------------------------------------------------------------------------------------
@@ -140,6 +142,90 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
     tmem_ld_wait();
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// 16 fp32 columns without the wait: issue several, then tmem_ld_wait() once.
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+
+// ----------------------------------------------------------------------------------------------
+// packed fp32 pairs (sm_100 FFMA2 / FMUL2 / FADD2): two IEEE fp32 operations per instruction
+// ----------------------------------------------------------------------------------------------
+typedef unsigned long long f32x2;  // lo = first element, hi = second element
+
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 bf16x2_to_f32x2(uint32_t u) {
+    return pack2(__uint_as_float(u << 16), __uint_as_float(u & 0xFFFF0000u));
+}
+__device__ __forceinline__ void ffma2(f32x2& acc, f32x2 a, f32x2 b) {
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 splat2(float v) { return pack2(v, v); }
+__device__ __forceinline__ uint32_t f32x2_to_bf16x2(f32x2 v) {
+    float lo, hi;
+    unpack2(v, lo, hi);
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+// two packed pairs (4 consecutive floats) from shared memory
+__device__ __forceinline__ void lds_f32x4(uint32_t addr, f32x2& a, f32x2& b) {
+    asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "r"(addr));
+}
+
+// exact-erf GELU on both halves (same formula as gelu_as in common.cuh: Abramowitz-Stegun 7.1.26, 2 MUFU per element)
+__device__ __forceinline__ f32x2 gelu2(f32x2 x) {
+    const f32x2 h = mul2(x, splat2(0.5f));
+    float h0, h1;
+    unpack2(h, h0, h1);
+    const float t0 = rcp_approx(fmaf(0.3275911f * 1.41421356237f, fabsf(h0), 1.0f));
+    const float t1 = rcp_approx(fmaf(0.3275911f * 1.41421356237f, fabsf(h1), 1.0f));
+    const f32x2 t = pack2(t0, t1);
+    f32x2 poly = fma2(splat2(-1.061405429f), t, splat2(1.453152027f));
+    poly = fma2(poly, t, splat2(-1.421413741f));
+    poly = fma2(poly, t, splat2(0.284496736f));
+    poly = fma2(poly, t, splat2(-0.254829592f));
+    poly = mul2(poly, t);
+    const f32x2 s = mul2(mul2(h, h), splat2(-2.88539008178f));
+    float s0, s1;
+    unpack2(s, s0, s1);
+    const f32x2 e = fma2(poly, pack2(ex2_approx(s0), ex2_approx(s1)), splat2(1.0f));
+    float e0, e1;
+    unpack2(e, e0, e1);
+    return pack2(fmaf(fabsf(h0), e0, h0), fmaf(fabsf(h1), e1, h1));
 }
 
 // UMMA instruction descriptor, kind::f16, A/B = bf16, D = fp32 (bit layout: cute/arch/mma_sm100_desc.hpp

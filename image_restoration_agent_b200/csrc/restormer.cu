@@ -50,6 +50,7 @@ static void fold_ln(std::vector<float>& w, int N, int K, int ldw, const float* g
 struct ConvW {
     void* w;       // storage dtype, [npad][9*kpad]
     float* wf32;   // fp32 copy (SIMT path for tiny channel counts)
+    void* wsplit;  // bf16 mode, C <= 4: [npad][9*64] weights for the hi/lo-split tensor-core first conv
     int kpad, npad, N, C;
 };
 
@@ -66,7 +67,8 @@ struct Restormer : Model {
 
     struct WS {
         void *cat1, *cat2, *cat3, *x2, *x3, *x4, *ln, *qkv_pre, *qkv, *hidden, *gated, *weff;
-        float *G, *sumsq;
+        float *G, *sumsq, *attn;
+        bf16* in8;      // [P1][8] hi/lo split of the fp32 input (bf16 mode)
         float2* stats;  // [P] (mu, rstd) of the LayerNorm folded into the next GEMM (bf16 mode)
         size_t gs_bytes;
     };
@@ -175,6 +177,12 @@ int Restormer::load_conv(const Blob& blob, const std::string& name, int N, int C
         o.wf32 = reinterpret_cast<float*>(o.w);
     else if (C < 16)
         IRB_TRY(upload_f32(w.data(), w.size(), &o.wf32));
+    o.wsplit = nullptr;
+    if (dt == DT_BF16 && C <= 4) {
+        int kp, np;
+        std::vector<float> ws = pack_conv3x3_split(t, kp, np);
+        IRB_TRY(upload_act(ws.data(), ws.size(), &o.wsplit));
+    }
     return 0;
 }
 
@@ -235,7 +243,7 @@ void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
     w.x4 = b.take(P4 * 8 * d * E);
     // scratch sized by the worst level: per-pixel channel counts shrink 2x while pixels shrink 4x, so the
     // full-resolution decoder level (C = 2d) dominates; take the max explicitly.
-    size_t ln = 0, qkv = 0, hid = 0, gat = 0, weff = 0, gs = 0;
+    size_t ln = 0, qkv = 0, hid = 0, gat = 0, weff = 0, gs = 0, at = 0;
     const size_t Ps[4] = {P1, P2, P3, P4};
     for (int l = 0; l < 4; ++l) {
         const int Cs[2] = {d << l, l == 0 ? 2 * d : d << l};
@@ -248,6 +256,7 @@ void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
             hid = std::max(hid, Ps[l] * 2 * hp * E);
             gat = std::max(gat, Ps[l] * hp * E);
             weff = std::max(weff, size_t(n) * C * C * E);
+            at = std::max(at, size_t(n) * C * (C / heads) * 4);
             const int P = int(Ps[l] / n);
             gs = std::max(gs, size_t(n) * mdta_nchunks(P, heads, n) * (size_t(C) * (C / heads) + 2 * C) * 4);
         }
@@ -259,8 +268,10 @@ void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
     w.gated = b.take(gat);
     w.weff = b.take(weff);
     w.stats = b.take<float2>(P1 * sizeof(float2));
+    w.in8 = b.take<bf16>(P1 * 8 * sizeof(bf16));
     w.G = b.take<float>(gs);
     w.gs_bytes = gs;
+    w.attn = b.take<float>(at);
     w.sumsq = nullptr;
 }
 
@@ -312,7 +323,7 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
         IRB_TRY(mdta_gram_tc((const bf16*)ws.qkv, 3 * C, n, H * W, C, heads, nch, G, ssq, s));
     else
         IRB_TRY(mdta_gram_simt(ws.qkv, DT_F32, 3 * C, n, H * W, C, heads, nch, G, ssq, s));
-    IRB_TRY(mdta_softmax_weff(G, ssq, nch, w.temp, w.proj_w, n, C, heads, ws.weff, dt, nullptr, s));
+    IRB_TRY(mdta_softmax_weff(G, ssq, nch, w.temp, w.proj_w, n, C, heads, ws.weff, dt, ws.attn, s));
     {
         Epi e = make_epi(x, ldx, dt);
         e.res = x;
@@ -372,7 +383,13 @@ int Restormer::forward(const float* in, float* out, int n, int H, int W, void* w
     void* e3 = at(ws.cat3, 4 * d);   // encoder-3 stream: channels [4d,8d) of cat3
     const int H2 = H / 2, W2 = W / 2, H3 = H / 4, W3 = W / 4, H4 = H / 8, W4 = W / 8;
 
-    IRB_TRY(run_conv(patch, in, DT_F32, cin, n, H, W, make_epi(e1, 2 * d, dt), s));               // :247
+    if (patch.wsplit) {  // :247 on the tensor core: x = hi + lo in bf16, both halves share the weights
+        IRB_TRY(split_hi_lo_bf16(in, cin, ws.in8, (long long)n * H * W, s));
+        IRB_TRY(tc_conv3x3(ws.in8, 8, n, H, W, 8, (const bf16*)patch.wsplit, 64, patch.N, patch.npad,
+                           make_epi(e1, 2 * d, dt), s));
+    } else {
+        IRB_TRY(run_conv(patch, in, DT_F32, cin, n, H, W, make_epi(e1, 2 * d, dt), s));           // :247
+    }
     IRB_TRY(blocks(enc1, e1, 2 * d, H, W));                                                        // :248
     IRB_TRY(run_conv(down12, e1, dt, 2 * d, n, H, W, shuffle_epi(e2, 4 * d, 2, H, W), s));         // :250
     IRB_TRY(blocks(enc2, e2, 4 * d, H2, W2));                                                      // :251

@@ -36,6 +36,7 @@ static void fold_ln(std::vector<float>& w, std::vector<float>& bias, int N, int 
 struct Conv3W {
     void* w;       // storage dtype [npad][9*kpad]
     float* wf32;   // fp32 copy when the FMA kernel runs it
+    void* wsplit;  // bf16 mode, C <= 4: weights of the hi/lo-split tensor-core first conv
     float* b;
     int N, C, kpad, npad;
 };
@@ -201,6 +202,12 @@ int SwinIR::load_conv(const Blob& blob, const std::string& name, int N, int Cin,
         o.wf32 = reinterpret_cast<float*>(o.w);
     else if (Cin < 16)
         IRB_TRY(upload_f32(w.data(), w.size(), &o.wf32));
+    o.wsplit = nullptr;
+    if (dt == DT_BF16 && Cin <= 4) {
+        int kp, np;
+        std::vector<float> wsp = pack_conv3x3_split(t, kp, np);
+        IRB_TRY(upload_act(wsp.data(), wsp.size(), &o.wsplit));
+    }
     IRB_TRY(blob.get(name + ".bias", t, N));
     IRB_TRY(upload_f32(t.data, N, &o.b));
     return 0;
@@ -431,7 +438,15 @@ int SwinIR::forward(const float* in, float* out, int n, int H0, int W0, void* ws
                                                  desc.img_range);
     IRB_CHECK_CUDA(cudaGetLastError());
     prof_mark("swin_prep", cin, 0, 0.0, 8.0 * P * cin, s);
-    IRB_TRY(conv(conv_first, w.xin, DT_F32, cin, n, H, W, make_epi(w.ffirst, ldC, dt), s));  // :813 / :833
+    if (conv_first.wsplit) {  // :813 / :833 on the tensor core: x = hi + lo in bf16 (w.hidden is free here)
+        IRB_TRY(split_hi_lo_bf16(w.xin, cin, (bf16*)w.hidden, P, s));
+        Epi e = make_epi(w.ffirst, ldC, dt);
+        e.bias = conv_first.b;
+        IRB_TRY(tc_conv3x3((const bf16*)w.hidden, 8, n, H, W, 8, (const bf16*)conv_first.wsplit, 64, conv_first.N,
+                           conv_first.npad, e, s));
+    } else {
+        IRB_TRY(conv(conv_first, w.xin, DT_F32, cin, n, H, W, make_epi(w.ffirst, ldC, dt), s));  // :813 / :833
+    }
     // forward_features (:790-803)
     IRB_TRY(layernorm(w.ffirst, dt, ldC, w.xa, dt, ldC, P, C, pen_w, pen_b, 0, 1e-5f, s));  // patch_embed.norm
     for (size_t r = 0; r < layers.size(); ++r) {

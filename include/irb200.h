@@ -143,7 +143,8 @@ int irb_mdta_nchunks(int P, int heads, int n);
 int irb_mdta_gram(const void* d_qkv, int dtype, long long ld, int n, int P, int C, int heads, int nchunks,
                   float* d_Gpart, float* d_ssq_part, void* stream);
 /* sums the slots in order, softmax(G / (|q||k|) * temperature), folded into project_out:
- * d_weff[n][C][C] (dtype), d_attn optional fp32 [n][heads][c][c] */
+ * d_weff[n][C][C] (dtype); d_attn fp32 [n][heads][c][c] receives the attention matrix (required: it is also the
+ * hand-off buffer between the softmax kernel and the fold kernel) */
 int irb_mdta_attn(const float* d_Gpart, const float* d_ssq_part, int nchunks, const float* d_temperature,
                   const float* d_wproj, int n, int C, int heads, void* d_weff, int dtype, float* d_attn,
                   void* stream);
