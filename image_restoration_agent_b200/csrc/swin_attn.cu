@@ -145,8 +145,17 @@ int window_attention_simt(const void* qkv, int dt, long long ld, void* out, long
     return 0;
 }
 
+// swin_attn_tc.cu
+bool window_attention_tc_ok(int dt, long long ld, long long ldo, int H, int W, int C, int heads, int dstride, int ws,
+                            int shift);
+int window_attention_tc(const bf16* qkv, long long ld, bf16* out, long long ldo, int n, int H, int W, int C, int heads,
+                        int shift, const float* bias_table, cudaStream_t stream);
+
 int window_attention(const void* qkv, int dt, long long ld, void* out, long long ldo, int n, int H, int W, int C,
                      int heads, int dstride, int ws, int shift, const float* bias_table, cudaStream_t stream) {
+    // bf16, 8x8 windows, head_dim <= 32 padded to 32: tcgen05 kernel; everything else (fp32 mode, window 7): FMA kernel
+    if (window_attention_tc_ok(dt, ld, ldo, H, W, C, heads, dstride, ws, shift))
+        return window_attention_tc((const bf16*)qkv, ld, (bf16*)out, ldo, n, H, W, C, heads, shift, bias_table, stream);
     return window_attention_simt(qkv, dt, ld, out, ldo, n, H, W, C, heads, dstride, ws, shift, bias_table, stream);
 }
 

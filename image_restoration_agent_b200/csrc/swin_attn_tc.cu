@@ -1,0 +1,337 @@
+// SwinIR (shifted-)window attention on tcgen05 for sm_100a (bf16 in, fp32 accumulate in TMEM).
+//   network_swinir.py:114-145 WindowAttention.forward, :216-237 calculate_mask, :239-279 roll / partition / reverse.
+//
+// Unit of work = a PAIR of 8x8 windows (128 tokens = the M of one UMMA); a persistent CTA walks its units and, per
+// unit, the heads two at a time (64 channels = one 128-byte swizzled row):
+//   loaders (4 warps)  : cp.async gather of the Q | K | V rows of the 128 tokens (the cyclic shift is plain address
+//                        arithmetic here, which is why this is not TMA) into the UMMA 128B-swizzled layout, 2 stages
+//   MMA (1 thread)     : S_h = Q_h K_h^T  (M 128, N 128, K 32; the two off-diagonal 64x64 blocks are ignored)
+//                        O_h = P_h V      (M 128, N 64 = both heads of the pair, K 128 keys; P is block diagonal)
+//   softmax (2 x 4 warps, one group per head of the pair, thread = token row):
+//                        S row from TMEM -> * log2(e) + rel-pos bias (+ shift mask) -> max / exp2 / sum in registers
+//                        -> unnormalised P row (bf16) into shared memory in the UMMA A layout -> after the PV MMA:
+//                        O row from TMEM * 1/sum -> bf16 -> per-warp transpose buffer -> coalesced global stores.
+// The relative-position bias is looked up from a shared-memory copy of the (2w-1)^2 x heads table with the index
+// (yi-yj+7)*15 + (xi-xj+7) folded into immediate offsets; the -100 mask is derived from the token coordinates of the
+// windows in the last window row / column of the shifted frame. Nothing is materialised in HBM.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "kernels.h"
+
+namespace irb {
+
+static constexpr int kWaThreads = 13 * 32;      // warp 0: MMA, 1..8: softmax groups A/B, 9..12: loaders
+static constexpr int kWaTile = 128 * 128;       // one [128 tokens][64 ch] bf16 operand tile (16 KB)
+static constexpr int kWaStage = 3 * kWaTile;    // Q | K | V
+static constexpr int kWaStages = 2;
+static constexpr int kWaPBytes = 2 * kWaTile;   // P of one head: 2 k-tiles of [128 rows][64 keys]
+static constexpr float kLog2e = 1.4426950408889634f;
+
+struct WaParams {
+    const bf16* qkv;
+    long long ld;
+    bf16* out;
+    long long ldo;
+    int n, H, W, heads, d, Cq, shift;
+    int nwx, nwy, total_windows, units;
+    const float* bias_table;  // [225][heads]
+};
+
+// bar[] layout (uint64 each)
+enum { WB_FULL = 0, WB_EMPTY = 2, WB_SFULL = 4, WB_SEMPTY = 6, WB_PFULL = 8, WB_OFULL = 10, WB_OEMPTY = 12, WB_COUNT = 14 };
+
+__device__ __forceinline__ long long wa_token_pixel(const WaParams& p, int unit, int r, bool& valid, int& masky, int& maskx) {
+    // row r of the unit -> window, token, original-frame pixel; masky / maskx: 0 none, 1: token in the first
+    // (ws - shift) rows/cols of a last-row/col window, 2: in the last `shift` rows/cols
+    const int gw = unit * 2 + (r >> 6);
+    valid = gw < p.total_windows;
+    const int per = p.nwx * p.nwy;
+    const int img = gw / per, wi = gw - img * per;
+    const int wy = wi / p.nwx, wx = wi - wy * p.nwx;
+    const int ty = (r & 63) >> 3, tx = r & 7;
+    const int sy = wy * 8 + ty, sx = wx * 8 + tx;
+    int oy = sy + p.shift, ox = sx + p.shift;
+    if (oy >= p.H) oy -= p.H;
+    if (ox >= p.W) ox -= p.W;
+    masky = (p.shift > 0 && wy == p.nwy - 1) ? (ty < 8 - p.shift ? 1 : 2) : 0;
+    maskx = (p.shift > 0 && wx == p.nwx - 1) ? (tx < 8 - p.shift ? 1 : 2) : 0;
+    return valid ? ((long long)img * p.H + oy) * p.W + ox : 0;
+}
+
+__global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(const WaParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t* stage_base = smem;                                   // [stages][Q|K|V]
+    uint8_t* p_base = smem + kWaStages * kWaStage;                // [2 groups][2 k-tiles][128][128 B]
+    uint32_t* tbuf = reinterpret_cast<uint32_t*>(p_base + 2 * kWaPBytes);  // [8 warps][32 rows][<= 17 words] output transpose
+    float* s_table = reinterpret_cast<float*>(tbuf + 8 * 32 * 17);  // [heads][225] bias * log2(e)
+    uint64_t* bar = reinterpret_cast<uint64_t*>(s_table + ((p.heads * 225 + 3) & ~3));
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + WB_COUNT);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // ---- one-time setup: zero the operand tiles (stale rows must be finite: 0 * NaN would poison valid rows),
+    // stage the bias table, init barriers, allocate TMEM ----
+    {
+        uint4* z = reinterpret_cast<uint4*>(smem);
+        const int n16 = (kWaStages * kWaStage + 2 * kWaPBytes) / 16;
+        for (int i = threadIdx.x; i < n16; i += kWaThreads) z[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = threadIdx.x; i < p.heads * 225; i += kWaThreads) {
+            const int h = i / 225, e = i - h * 225;
+            s_table[i] = __ldg(p.bias_table + e * p.heads + h) * kLog2e;
+        }
+    }
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int s = 0; s < 2; ++s) {
+                mbar_init(&bar[WB_FULL + s], 4);
+                mbar_init(&bar[WB_EMPTY + s], 1);
+                mbar_init(&bar[WB_SFULL + s], 1);
+                mbar_init(&bar[WB_SEMPTY + s], 4);
+                mbar_init(&bar[WB_PFULL + s], 4);
+                mbar_init(&bar[WB_OFULL + s], 1);
+                mbar_init(&bar[WB_OEMPTY + s], 4);
+            }
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int npairs = p.heads >> 1;
+    // TMEM columns: S of group g at g*128, O of group g at 256 + g*64
+
+    if (warp >= 9) {
+        // ===================== loaders: thread = token row r =====================
+        const int r = threadIdx.x - 9 * 32;
+        const uint32_t row_off = r * 128;
+        const int sw = r & 7;
+        int cnt = 0;
+        for (int u = blockIdx.x; u < p.units; u += gridDim.x) {
+            bool valid;
+            int my, mx;
+            const long long pix = wa_token_pixel(p, u, r, valid, my, mx);
+            const bf16* grow = p.qkv + pix * p.ld;
+            for (int hp = 0; hp < npairs; ++hp, ++cnt) {
+                const int s = cnt & 1;
+                if (lane == 0) mbar_wait(&bar[WB_EMPTY + s], ((cnt >> 1) & 1) ^ 1);
+                __syncwarp();
+                if (valid) {
+                    const uint32_t dst = smem_u32(stage_base + s * kWaStage) + row_off;
+#pragma unroll
+                    for (int t = 0; t < 3; ++t) {
+                        const bf16* src = grow + t * p.Cq + hp * 64;
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) cp_async16(dst + t * kWaTile + ((c ^ sw) << 4), src + c * 8);
+                    }
+                }
+                cp_async_commit();
+                cp_async_wait<0>();   // the other stage is being consumed meanwhile: the ring hides this latency
+                fence_proxy_async();  // generic-proxy writes -> visible to the tensor core's async-proxy reads
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bar[WB_FULL + s]);
+            }
+        }
+    } else if (warp == 0) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);  // Q, K both K-major
+            const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);   // P K-major, V MN-major
+            int my_pairs = 0;
+            for (int u = blockIdx.x; u < p.units; u += gridDim.x) my_pairs += npairs;
+            auto issue_s = [&](int cnt) {
+                const int s = cnt & 1;
+                mbar_wait(&bar[WB_FULL + s], (cnt >> 1) & 1);
+                tc_fence_after();
+                const uint32_t q_addr = smem_u32(stage_base + s * kWaStage);
+                const uint32_t k_addr = q_addr + kWaTile;
+                for (int g = 0; g < 2; ++g) {
+                    mbar_wait(&bar[WB_SEMPTY + g], (cnt & 1) ^ 1);
+                    tc_fence_after();
+#pragma unroll
+                    for (int ks = 0; ks < 2; ++ks) {
+                        const uint64_t ad = make_sdesc_sw128(q_addr + g * 64 + ks * 32, 16, 1024);
+                        const uint64_t bd = make_sdesc_sw128(k_addr + g * 64 + ks * 32, 16, 1024);
+                        umma_bf16(tmem_base + g * 128, ad, bd, idesc_s, ks);
+                    }
+                    umma_commit(&bar[WB_SFULL + g]);
+                }
+            };
+            if (my_pairs > 0) issue_s(0);
+            for (int cnt = 0; cnt < my_pairs; ++cnt) {
+                if (cnt + 1 < my_pairs) issue_s(cnt + 1);
+                const int s = cnt & 1;
+                const uint32_t v_addr = smem_u32(stage_base + s * kWaStage) + 2 * kWaTile;
+                for (int g = 0; g < 2; ++g) {
+                    mbar_wait(&bar[WB_PFULL + g], cnt & 1);
+                    mbar_wait(&bar[WB_OEMPTY + g], (cnt & 1) ^ 1);
+                    tc_fence_after();
+                    const uint32_t pa = smem_u32(p_base + g * kWaPBytes);
+#pragma unroll
+                    for (int ks = 0; ks < 8; ++ks) {
+                        const uint64_t ad = make_sdesc_sw128(pa + (ks >> 2) * kWaTile + (ks & 3) * 32, 16, 1024);
+                        const uint64_t bd = make_sdesc_sw128(v_addr + ks * 2048, kWaTile, 1024);
+                        umma_bf16(tmem_base + 256 + g * 64, ad, bd, idesc_o, ks);
+                    }
+                    umma_commit(&bar[WB_OFULL + g]);
+                }
+                umma_commit(&bar[WB_EMPTY + s]);  // Q, K, V of this stage are no longer read
+            }
+        }
+    } else {
+        // ===================== softmax + output groups: warps 1..4 (head 2*hp) and 5..8 (head 2*hp + 1) ==========
+        const int g = (warp - 1) >> 2;
+        const int q = warp & 3;                  // TMEM lane quarter this warp may read
+        const int r = q * 32 + lane;             // token row of the unit
+        const int win = r >> 6;
+        const int yi = (r & 63) >> 3, xi = r & 7;
+        const int d2 = p.d >> 1;                 // output words (bf16 pairs) per head
+        const int tstride = d2 | 1;              // odd stride: conflict-free transpose
+        uint32_t* tb = tbuf + (warp - 1) * 32 * 17;
+        uint8_t* prow = p_base + g * kWaPBytes + win * kWaTile + r * 128;
+        const int sw = r & 7;
+        const uint32_t lane_addr = uint32_t(q * 32) << 16;
+        uint32_t* out32 = reinterpret_cast<uint32_t*>(p.out);
+        const long long ldo2 = p.ldo >> 1;
+        int cnt = 0;
+        for (int u = blockIdx.x; u < p.units; u += gridDim.x) {
+            bool valid;
+            int my, mx;
+            const long long pix = wa_token_pixel(p, u, r, valid, my, mx);
+            const long long orow = valid ? pix * ldo2 : -1;
+            // additive mask per key quadrant (yj >= 4, xj >= 4), in log2 units (network_swinir.py:216-237: the
+            // region ids differ when the y parts or the x parts differ)
+            const bool ylo = my == 2, yhi = my == 1, xlo = mx == 2, xhi = mx == 1;  // which key halves are masked
+            const float NEG = -100.0f * kLog2e;
+            const float m00 = (ylo || xlo) ? NEG : 0.f, m01 = (ylo || xhi) ? NEG : 0.f;
+            const float m10 = (yhi || xlo) ? NEG : 0.f, m11 = (yhi || xhi) ? NEG : 0.f;
+            const bool any_mask = __any_sync(0xffffffffu, (my | mx) != 0);
+            for (int hp = 0; hp < npairs; ++hp, ++cnt) {
+                const int h = hp * 2 + g;
+                const float* tab = s_table + h * 225 + (yi + 7) * 15 + xi + 7;
+                mbar_wait(&bar[WB_SFULL + g], cnt & 1);
+                tc_fence_after();
+                uint32_t sr[64];
+                tmem_ld32_nowait(tmem_base + lane_addr + g * 128 + win * 64, sr);
+                tmem_ld32_nowait(tmem_base + lane_addr + g * 128 + win * 64 + 32, sr + 32);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bar[WB_SEMPTY + g]);
+                float t[64];
+                float mx_ = -INFINITY;
+#pragma unroll
+                for (int j = 0; j < 64; ++j) {
+                    const int yj = j >> 3, xj = j & 7;
+                    t[j] = fmaf(__uint_as_float(sr[j]), kLog2e, tab[-(yj * 15 + xj)]);
+                }
+                if (any_mask) {
+#pragma unroll
+                    for (int j = 0; j < 64; ++j) {
+                        const int yj = j >> 3, xj = j & 7;
+                        t[j] += (yj >= 4) ? ((xj >= 4) ? m11 : m10) : ((xj >= 4) ? m01 : m00);
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 64; ++j) mx_ = fmaxf(mx_, t[j]);
+                float sum = 0.f;
+                uint32_t pk[32];
+#pragma unroll
+                for (int j = 0; j < 64; j += 2) {
+                    const float e0 = ex2_approx(t[j] - mx_), e1 = ex2_approx(t[j + 1] - mx_);
+                    sum += e0 + e1;
+                    pk[j >> 1] = pack_bf16x2(e0, e1);
+                }
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    *reinterpret_cast<uint4*>(prow + ((c ^ sw) << 4)) =
+                        make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bar[WB_PFULL + g]);
+                const float inv = 1.0f / sum;
+                // ---- O = P V / sum ----
+                mbar_wait(&bar[WB_OFULL + g], cnt & 1);
+                tc_fence_after();
+                uint32_t orr[32];
+                tmem_ld32_nowait(tmem_base + lane_addr + 256 + g * 64 + g * 32, orr);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bar[WB_OEMPTY + g]);
+#pragma unroll
+                for (int k = 0; k < 16; ++k)
+                    if (k < d2)
+                        tb[lane * tstride + k] =
+                            pack_bf16x2(__uint_as_float(orr[2 * k]) * inv, __uint_as_float(orr[2 * k + 1]) * inv);
+                __syncwarp();
+                // coalesced: consecutive lanes write consecutive words of a token's head slice
+                const int nwords = 32 * d2;
+                for (int wi = lane; wi < nwords; wi += 32) {
+                    const int row = wi / d2, k = wi - row * d2;
+                    const uint32_t v = tb[row * tstride + k];
+                    const long long ob = __shfl_sync(0xffffffffu, orow, row);
+                    if (ob >= 0) out32[ob + h * d2 + k] = v;
+                }
+                __syncwarp();
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base, 512);
+}
+
+bool window_attention_tc_ok(int dt, long long ld, long long ldo, int H, int W, int C, int heads, int dstride, int ws,
+                            int shift) {
+    return dt == DT_BF16 && ws == 8 && dstride == 32 && heads >= 2 && heads % 2 == 0 && heads <= 8 &&
+           (C / heads) % 2 == 0 && C / heads <= 32 && (shift == 0 || shift == 4) && H % 8 == 0 && W % 8 == 0 &&
+           ld % 8 == 0 && ldo % 2 == 0;
+}
+
+int window_attention_tc(const bf16* qkv, long long ld, bf16* out, long long ldo, int n, int H, int W, int C, int heads,
+                        int shift, const float* bias_table, cudaStream_t stream) {
+    IRB_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 3) == 0,
+                "window_attention_tc: alignment");
+    WaParams p{};
+    p.qkv = qkv;
+    p.ld = ld;
+    p.out = out;
+    p.ldo = ldo;
+    p.n = n;
+    p.H = H;
+    p.W = W;
+    p.heads = heads;
+    p.d = C / heads;
+    p.Cq = heads * 32;
+    p.shift = shift;
+    p.nwx = W / 8;
+    p.nwy = H / 8;
+    const long long tw = (long long)n * p.nwx * p.nwy;
+    IRB_REQUIRE(tw < (1ll << 30), "window_attention_tc: too many windows");
+    p.total_windows = int(tw);
+    p.units = int((tw + 1) / 2);
+    p.bias_table = bias_table;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int grid = p.units < sms ? p.units : sms;
+    const size_t smem = 1024 + size_t(kWaStages) * kWaStage + 2 * kWaPBytes + 8 * 32 * 17 * 4 +
+                        ((heads * 225 + 3) & ~3) * 4 + WB_COUNT * 8 + 64;
+    static bool attr_set = false;
+    if (!attr_set) {
+        IRB_CHECK_CUDA(cudaFuncSetAttribute(window_attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_set = true;
+    }
+    window_attention_tc_kernel<<<grid, kWaThreads, smem, stream>>>(p);
+    IRB_CHECK_CUDA(cudaGetLastError());
+    const double px = double(n) * H * W;
+    prof_mark("window_attention_tc", C, shift, 4.0 * px * 64 * C, px * (3.0 * p.Cq + C) * 2, stream);
+    return 0;
+}
+
+}  // namespace irb
