@@ -72,6 +72,10 @@ struct Epi {
     //   acc <- rstd[row] * (acc - mu[row] * ln_colsum[col])      (WithBias / nn.LayerNorm; the LN bias is folded
     //   acc <- rstd[row] * acc                                   (BiasFree: ln_colsum == nullptr)     into `bias`)
     const float2* ln_stats;   // [rows] (mu, rstd) or nullptr
+    // optional: LayerNorm statistics of the OUTPUT rows (mu, 1/sqrt(var + stats_eps)) for the LayerNorm folded into
+    // the next GEMM; only the tcgen05 kernel with one n-tile (N <= 256), a bf16 residual and the TMA-store epilogue
+    float2* stats_out;
+    float stats_eps;
     const float* ln_colsum;   // [N] sum_k W'[n,k] of the (rounded) folded weights
 };
 

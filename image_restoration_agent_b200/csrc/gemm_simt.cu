@@ -96,6 +96,7 @@ __global__ void __launch_bounds__(256) simt_gemm_kernel(const SimtParams p) {
 int simt_gemm(const void* A, int a_dt, long long lda, int M, int K, int batch, long long a_batch_stride,
               const float* Wt, int ldw, int N, int w_rows_per_batch, const Epi& epi, cudaStream_t stream) {
     IRB_REQUIRE(M > 0 && K > 0 && N > 0 && batch > 0, "simt_gemm: empty problem");
+    IRB_REQUIRE(epi.stats_out == nullptr, "simt_gemm: Epi::stats_out is a tcgen05-epilogue feature");
     SimtParams p{};
     p.A = A;
     p.a_dt = a_dt;
@@ -123,6 +124,7 @@ int simt_gemm(const void* A, int a_dt, long long lda, int M, int K, int batch, l
 int simt_conv3x3(const void* A, int a_dt, long long lda, int Nimg, int H, int W, int C, const float* Wt, int kpad,
                  int N, const Epi& epi, cudaStream_t stream) {
     IRB_REQUIRE(Nimg > 0 && H > 0 && W > 0 && C > 0 && N > 0, "simt_conv3x3: empty problem");
+    IRB_REQUIRE(epi.stats_out == nullptr, "simt_conv3x3: Epi::stats_out is a tcgen05-epilogue feature");
     SimtParams p{};
     p.A = A;
     p.a_dt = a_dt;

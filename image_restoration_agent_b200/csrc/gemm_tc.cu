@@ -127,9 +127,10 @@ __device__ __forceinline__ void epi_fast16(const Epi& e, long long row, int col0
 // vectors read from shared memory as 16-byte loads, bf16 residual pre-fetched by the caller (r0: columns 0..7,
 // r1: 8..15). LN 0: y = acc; 1: y = acc * a + bias[col]; 2: y = acc * a + (b * colsum[col] + bias[col]).
 // Everything that selects a variant is a template parameter: the unrolled body has no branches.
-template <int ACT, int LN, bool RES>
+template <int ACT, int LN, bool RES, bool STATS>
 __device__ __forceinline__ void epi_group16(const uint32_t* acc, const float* sb, const float* scs, f32x2 a2, f32x2 b2,
-                                            float slope, const uint4& r0, const uint4& r1, uint32_t* pk) {
+                                            float slope, const uint4& r0, const uint4& r1, uint32_t* pk, f32x2& s1,
+                                            f32x2& s2, f32x2 nshift2) {
 #pragma unroll
     for (int j4 = 0; j4 < 4; ++j4) {
         f32x2 x0 = pack2(__uint_as_float(acc[4 * j4 + 0]), __uint_as_float(acc[4 * j4 + 1]));
@@ -161,21 +162,64 @@ __device__ __forceinline__ void epi_group16(const uint32_t* acc, const float* sb
             x0 = add2(x0, bf16x2_to_f32x2(rw0));
             x1 = add2(x1, bf16x2_to_f32x2(rw1));
         }
+        if (STATS) {  // shifted sums: sum (y - shift), sum (y - shift)^2
+            const f32x2 d0 = add2(x0, nshift2), d1 = add2(x1, nshift2);
+            s1 = add2(s1, add2(d0, d1));
+            s2 = fma2(d0, d0, s2);
+            s2 = fma2(d1, d1, s2);
+        }
         pk[2 * j4] = f32x2_to_bf16x2(x0);
         pk[2 * j4 + 1] = f32x2_to_bf16x2(x1);
     }
 }
 
-// One 64-column block (ng <= 4 groups) of one row: math + the swizzled 16-byte stores into the staging block.
-template <int ACT, int LN, bool RES>
-__device__ __forceinline__ void epi_block(const uint32_t (*acc)[16], const uint4* rr, int ng, const float* sb,
-                                          const float* scs, f32x2 a2, f32x2 b2, float slope, uint8_t* stg_row,
-                                          int lane) {
+// A group whose 16 columns are not all < N (ragged N such as SwinIR's 180): element-wise, columns >= N give 0.
+template <int ACT, int LN, bool RES, bool STATS>
+__device__ __forceinline__ void epi_group16_ragged(const uint32_t* acc, int nvalid, const float* sb, const float* scs,
+                                                   float fa, float fb, float slope, const bf16* res, uint32_t* pk,
+                                                   f32x2& s1, f32x2& s2, float shift) {
+    float v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        float y = __uint_as_float(acc[j]);
+        if (LN == 1) y = fmaf(y, fa, sb[j]);
+        if (LN == 2) y = fmaf(y, fa, fmaf(fb, scs[j], sb[j]));
+        if (ACT == ACT_GELU) y = gelu_as(y);
+        if (ACT == ACT_LRELU) y = y > 0.f ? y : y * slope;
+        if (j < nvalid) {
+            if (RES) y += __bfloat162float(res[j]);
+            if (STATS) {
+                const float d = y - shift;
+                s1 = add2(s1, pack2(d, 0.f));
+                s2 = fma2(pack2(d, 0.f), pack2(d, 0.f), s2);
+            }
+        } else {
+            y = 0.f;
+        }
+        v[j] = y;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+}
+
+// One 64-column block (ng <= 4 groups, nvalid columns < N) of one row: math + the swizzled 16-byte stores into the
+// staging block.
+template <int ACT, int LN, bool RES, bool STATS>
+__device__ __forceinline__ void epi_block(const uint32_t (*acc)[16], const uint4* rr, int ng, int nvalid,
+                                          const float* sb, const float* scs, float fa, float fb, float slope,
+                                          const bf16* res_row, uint8_t* stg_row, int lane, f32x2& s1, f32x2& s2,
+                                          float shift) {
+    const f32x2 a2 = splat2(fa), b2 = splat2(fb), nshift2 = splat2(-shift);
 #pragma unroll
     for (int gi = 0; gi < 4; ++gi) {
         if (gi < ng) {
             uint32_t pk[8];
-            epi_group16<ACT, LN, RES>(acc[gi], sb + gi * 16, scs + gi * 16, a2, b2, slope, rr[2 * gi], rr[2 * gi + 1], pk);
+            if (gi * 16 + 16 <= nvalid || !RES)
+                epi_group16<ACT, LN, RES, STATS>(acc[gi], sb + gi * 16, scs + gi * 16, a2, b2, slope, rr[2 * gi],
+                                                 rr[2 * gi + 1], pk, s1, s2, nshift2);
+            else
+                epi_group16_ragged<ACT, LN, RES, STATS>(acc[gi], nvalid - gi * 16, sb + gi * 16, scs + gi * 16, fa, fb,
+                                                        slope, res_row + gi * 16, pk, s1, s2, shift);
 #pragma unroll
             for (int c = 0; c < 2; ++c)
                 *reinterpret_cast<uint4*>(stg_row + (((2 * gi + c) ^ (lane & 7)) << 4)) =
@@ -320,6 +364,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                                             reinterpret_cast<uintptr_t>(p.epi.res) % 16 == 0));
         const int lnmode = p.epi.ln_colsum ? 2 : ((p.epi.ln_stats || p.epi.bias) ? 1 : 0);
         const bool res_bf16 = p.epi.res != nullptr && p.epi.res_dt == DT_BF16;
+        const bool do_stats = p.epi.stats_out != nullptr;
         int t = 0;
         uint32_t sblk = 0;  // staging-block parity of this warp
         for (int w = first_item(p); w < p.total; w = next_item(w, p), ++t) {
@@ -350,6 +395,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 fa = st.y;
                 fb = p.epi.ln_colsum ? -st.x * st.y : 0.f;
             }
+            f32x2 st_s1 = 0ull, st_s2 = 0ull;  // shifted sums for Epi::stats_out
+            float st_shift = 0.f;
             mbar_wait(&tfull_bar[set], (t >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem_base + set * p.acc_stride + (uint32_t(q * 32) << 16);
@@ -365,26 +412,26 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                     const int ng = min(4, (p.BN - cb) >> 4);
                     uint8_t* stg = stg_base + (sblk & 1) * 4096;
                     ++sblk;
-                    // fast path: no residual or a bf16 residual whose 16-column groups are all complete
-                    const bool ragged_res = has_res_any && (n0 + cb + ng * 16 > p.N);
-                    if ((res_bf16 || p.epi.res == nullptr) && !ragged_res) {
+                    // fast path: no residual or a bf16 residual
+                    if (res_bf16 || p.epi.res == nullptr) {
                         // all TMEM loads and residual loads of the block in flight before the first wait
                         uint32_t acc[4][16];
                         uint4 rr[8];
 #pragma unroll
                         for (int gi = 0; gi < 4; ++gi)
                             if (gi < ng) tmem_ld16_nowait(taddr + cb + gi * 16, acc[gi]);
+                        const int nvalid = min(64, p.N - (n0 + cb));
+                        const bf16* rrow = reinterpret_cast<const bf16*>(p.epi.res) + (valid ? grow : 0) * p.epi.ldr + n0 + cb;
                         if (has_res_any) {
-                            const bf16* rrow = reinterpret_cast<const bf16*>(p.epi.res) + (valid ? grow : 0) * p.epi.ldr + n0 + cb;
 #pragma unroll
                             for (int gi = 0; gi < 4; ++gi) {
-                                if (gi < ng) {
+                                if (gi < ng && gi * 16 + 16 <= nvalid) {
                                     rr[2 * gi] = __ldg(reinterpret_cast<const uint4*>(rrow + gi * 16));
                                     rr[2 * gi + 1] = __ldg(reinterpret_cast<const uint4*>(rrow + gi * 16 + 8));
                                 }
                             }
                         }
-                        const f32x2 a2 = splat2(fa), b2 = splat2(fb);
+                        if (do_stats && blk == 0) st_shift = __uint_as_float(rr[0].x << 16);  // x_old[row, 0]
                         // the store issued two blocks ago (same staging buffer) must have finished READING it
                         if (lane == 0) bulk_wait_read1();
                         __syncwarp();
@@ -392,17 +439,24 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                         const float* sb = s_bias + cb;
                         const float* sc = s_cs + cb;
                         uint8_t* srow = stg + lane * 128;
-#define IRB_EPI(A, L, R) epi_block<A, L, R>(acc, rr, ng, sb, sc, a2, b2, p.epi.slope, srow, lane)
+#define IRB_EPI(A, L, R, S) \
+    epi_block<A, L, R, S>(acc, rr, ng, nvalid, sb, sc, fa, fb, p.epi.slope, rrow, srow, lane, st_s1, st_s2, st_shift)
 #define IRB_EPI_LR(A)                                                  \
     switch (lnmode * 2 + (has_res_any ? 1 : 0)) {                      \
-        case 0: IRB_EPI(A, 0, false); break;                           \
-        case 1: IRB_EPI(A, 0, true); break;                            \
-        case 2: IRB_EPI(A, 1, false); break;                           \
-        case 3: IRB_EPI(A, 1, true); break;                            \
-        case 4: IRB_EPI(A, 2, false); break;                           \
-        default: IRB_EPI(A, 2, true); break;                           \
+        case 0: IRB_EPI(A, 0, false, false); break;                    \
+        case 1: IRB_EPI(A, 0, true, false); break;                     \
+        case 2: IRB_EPI(A, 1, false, false); break;                    \
+        case 3: IRB_EPI(A, 1, true, false); break;                     \
+        case 4: IRB_EPI(A, 2, false, false); break;                    \
+        default: IRB_EPI(A, 2, true, false); break;                    \
     }
-                        if (p.epi.act == ACT_GELU) {
+                        if (do_stats) {  // ACT_NONE + residual only (checked on the host)
+                            if (lnmode == 0) {
+                                IRB_EPI(ACT_NONE, 0, true, true);
+                            } else {
+                                IRB_EPI(ACT_NONE, 1, true, true);
+                            }
+                        } else if (p.epi.act == ACT_GELU) {
                             IRB_EPI_LR(ACT_GELU)
                         } else if (p.epi.act == ACT_LRELU) {
                             IRB_EPI_LR(ACT_LRELU)
@@ -465,6 +519,15 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                         epi_apply_store<16>(p.epi, grow, col0, p.N, v, z, py, px);
                     }
                 }
+            }
+            if (do_stats && valid) {
+                float a0, a1, q0, q1;
+                unpack2(st_s1, a0, a1);
+                unpack2(st_s2, q0, q1);
+                const float invn = 1.0f / float(p.N);
+                const float m = (a0 + a1) * invn;
+                const float var = fmaxf((q0 + q1) * invn - m * m, 0.f);
+                p.epi.stats_out[grow] = make_float2(st_shift + m, rsqrtf(var + p.epi.stats_eps));
             }
             tc_fence_before();
             __syncwarp();
@@ -558,6 +621,11 @@ static bool can_tma_store(const Epi& e) {
                        (reinterpret_cast<uintptr_t>(e.res) & 15) == 0));
 }
 
+bool tc_can_fuse_stats(int N, const Epi& e) {
+    return N <= 256 && can_tma_store(e) && e.res != nullptr && e.res_dt == DT_BF16 && e.act == ACT_NONE &&
+           e.ln_stats == nullptr;
+}
+
 static int tmem_cols_for(int bn) {
     int c = 32;
     while (c < bn) c <<= 1;
@@ -637,6 +705,7 @@ int tc_gemm(const bf16* A, long long lda, int M, int K, int batch, long long a_b
         IRB_TRY(make_tmap_bf16(&p.tmB, Wt, 2, dims, str, box));
     }
     p.epi = epi;
+    IRB_REQUIRE(!epi.stats_out || tc_can_fuse_stats(N, epi), "tc_gemm: stats_out needs N <= 256, bf16 residual, TMA-store epilogue");
     p.tma_store = can_tma_store(epi) ? 1 : 0;
     if (p.tma_store) {
         uint64_t dims[3] = {uint64_t(N), uint64_t(M), uint64_t(batch)};
@@ -692,6 +761,7 @@ int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, cons
         IRB_TRY(make_tmap_bf16(&p.tmB, Wt, 2, dims, str, box));
     }
     p.epi = epi;
+    IRB_REQUIRE(!epi.stats_out || tc_can_fuse_stats(N, epi), "tc_conv3x3: stats_out needs N <= 256, bf16 residual, TMA-store epilogue");
     p.tma_store = can_tma_store(epi) ? 1 : 0;
     if (p.tma_store) {
         const int bw = BW < 32 ? BW : 32;

@@ -12,6 +12,8 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* d
                    const uint32_t* box);
 int make_tmap_bf16_sw(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
                       const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
+// true when tc_gemm / tc_conv3x3 can also emit the LayerNorm statistics of their output rows (Epi::stats_out)
+bool tc_can_fuse_stats(int N, const Epi& epi);
 int tc_gemm(const bf16* A, long long lda, int M, int K, int batch, long long a_batch_stride, const bf16* Wt, int ldw,
             int N, int w_rows_total, int w_rows_per_batch, const Epi& epi, cudaStream_t stream);
 int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, const bf16* Wt, int kpad, int N,

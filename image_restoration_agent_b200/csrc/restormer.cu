@@ -71,6 +71,7 @@ struct Restormer : Model {
         bf16* in8;      // [P1][8] hi/lo split of the fp32 input (bf16 mode)
         float2* stats;  // [P] (mu, rstd) of the LayerNorm folded into the next GEMM (bf16 mode)
         size_t gs_bytes;
+        bool stats_valid;  // ws.stats already holds the LayerNorm statistics of the current stream (written by the producing GEMM)
     };
     void layout(Bump& b, int n, int H, int W, WS& w);
     int load_block(const Blob& blob, const std::string& p, int C, int heads, RBlockW& o);
@@ -305,7 +306,7 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
     const int mode = desc.ln_bias_free ? 1 : 0;
     // --- x = x + project_out(attn(norm1(x))) ---
     if (dt == DT_BF16) {  // norm1 folded into the qkv GEMM
-        IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
+        if (!ws.stats_valid) IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
         Epi e = make_epi(ws.qkv_pre, 3 * C, dt);
         e.ln_stats = ws.stats;
         e.ln_colsum = w.qkv_cs;
@@ -330,6 +331,12 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
         e.ldr = ldx;
         e.res_dt = dt;
         const void* v = at(ws.qkv, 2 * C);
+        ws.stats_valid = false;
+        if (dt == DT_BF16 && tc_can_fuse_stats(C, e)) {  // norm2's statistics come out of this GEMM's epilogue
+            e.stats_out = ws.stats;
+            e.stats_eps = 1e-5f;
+            ws.stats_valid = true;
+        }
         if (dt == DT_BF16)
             IRB_TRY(tc_gemm((const bf16*)v, 3 * C, H * W, C, n, 0, (const bf16*)ws.weff, C, C, n * C, C, e, s));
         else
@@ -337,7 +344,7 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
     }
     // --- x = x + project_out(gelu(dw(x1)) * dw(x2)) ---
     if (dt == DT_BF16) {  // norm2 folded into project_in
-        IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
+        if (!ws.stats_valid) IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
         Epi e = make_epi(ws.hidden, 2 * w.hp, dt);
         e.ln_stats = ws.stats;
         e.ln_colsum = w.pin_cs;
@@ -353,6 +360,12 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
         e.res = x;
         e.ldr = ldx;
         e.res_dt = dt;
+        ws.stats_valid = false;
+        if (dt == DT_BF16 && tc_can_fuse_stats(C, e)) {  // the next block's norm1 statistics
+            e.stats_out = ws.stats;
+            e.stats_eps = 1e-5f;
+            ws.stats_valid = true;
+        }
         IRB_TRY(run_gemm(ws.gated, w.hp, P, w.hp, w.pout_w, w.hp, C, C, e, s));
     }
     return 0;
@@ -368,6 +381,7 @@ int Restormer::forward(const float* in, float* out, int n, int H, int W, void* w
     layout(b, n, H, W, ws);
     const int d = dim;
     auto blocks = [&](std::vector<RBlockW>& v, void* x, long long ldx, int h, int w) -> int {
+        ws.stats_valid = false;  // the stream was just written by a convolution
         for (auto& blk : v) IRB_TRY(run_block(blk, x, ldx, n, h, w, ws, s));
         return 0;
     };

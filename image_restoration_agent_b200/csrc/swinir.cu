@@ -104,6 +104,7 @@ struct SwinIR : Model {
         float *xin, *out_tmp;
         void *xa, *xb, *ffirst, *ln, *qkv, *attn, *hidden, *q4a, *q4b, *t64, *u1, *u2, *u3;
         float2* stats;
+        bool stats_valid;  // stats already describe the stream the next block normalises (written by the producing GEMM)
     };
     void layout(Bump& b, int n, int H0, int W0, WS& w);
     void padded(int H0, int W0, int& H, int& W) const {
@@ -381,7 +382,7 @@ int SwinIR::resi(const ResiW& r, const void* x, long long ldx, int n, int H, int
 int SwinIR::stl(const STLW& L, const void* xin, void* xout, int n, int H, int W, WS& w, cudaStream_t s) {
     const long long P = (long long)n * H * W;
     if (dt == DT_BF16) {  // norm1 folded into the qkv GEMM
-        IRB_TRY(row_stats(xin, dt, ldC, w.stats, P, C, 1e-5f, s));
+        if (!w.stats_valid) IRB_TRY(row_stats(xin, dt, ldC, w.stats, P, C, 1e-5f, s));
         Epi e = make_epi(w.qkv, 3 * Cq, dt);
         e.ln_stats = w.stats;
         e.ln_colsum = L.qkv.cs;
@@ -396,10 +397,17 @@ int SwinIR::stl(const STLW& L, const void* xin, void* xout, int n, int H, int W,
         e.res = xin;
         e.ldr = ldC;
         e.res_dt = dt;
+        e.bias = L.proj.b;
+        w.stats_valid = false;
+        if (dt == DT_BF16 && tc_can_fuse_stats(C, e)) {  // norm2's statistics come out of this GEMM's epilogue
+            e.stats_out = w.stats;
+            e.stats_eps = 1e-5f;
+            w.stats_valid = true;
+        }
         IRB_TRY(gemm(w.attn, ldC, P, L.proj, e, s));
     }
     if (dt == DT_BF16) {  // norm2 folded into fc1
-        IRB_TRY(row_stats(xout, dt, ldC, w.stats, P, C, 1e-5f, s));
+        if (!w.stats_valid) IRB_TRY(row_stats(xout, dt, ldC, w.stats, P, C, 1e-5f, s));
         Epi e = make_epi(w.hidden, hid, dt);
         e.act = ACT_GELU;
         e.ln_stats = w.stats;
@@ -416,6 +424,13 @@ int SwinIR::stl(const STLW& L, const void* xin, void* xout, int n, int H, int W,
         e.res = xout;
         e.ldr = ldC;
         e.res_dt = dt;
+        e.bias = L.fc2.b;
+        w.stats_valid = false;
+        if (dt == DT_BF16 && tc_can_fuse_stats(C, e)) {  // the next block's norm1 statistics
+            e.stats_out = w.stats;
+            e.stats_eps = 1e-5f;
+            w.stats_valid = true;
+        }
         IRB_TRY(gemm(w.hidden, hid, P, L.fc2, e, s));
     }
     return 0;
@@ -449,6 +464,7 @@ int SwinIR::forward(const float* in, float* out, int n, int H0, int W0, void* ws
     }
     // forward_features (:790-803)
     IRB_TRY(layernorm(w.ffirst, dt, ldC, w.xa, dt, ldC, P, C, pen_w, pen_b, 0, 1e-5f, s));  // patch_embed.norm
+    w.stats_valid = false;
     for (size_t r = 0; r < layers.size(); ++r) {
         // RSTB (:481-482): xa = conv(blocks(xa)) + xa ; the blocks run in xb
         const void* src = w.xa;
@@ -460,6 +476,13 @@ int SwinIR::forward(const float* in, float* out, int n, int H0, int W0, void* ws
         e.res = w.xa;
         e.ldr = ldC;
         e.res_dt = dt;
+        w.stats_valid = false;
+        const int last_cin = desc.resi_3conv ? layer_conv[r].c2.C : layer_conv[r].c0.C;  // >= 16: tensor-core conv
+        if (dt == DT_BF16 && r + 1 < layers.size() && last_cin >= 16 && tc_can_fuse_stats(C, e)) {  // norm1 of the next RSTB's first block
+            e.stats_out = w.stats;
+            e.stats_eps = 1e-5f;
+            w.stats_valid = true;
+        }
         IRB_TRY(resi(layer_conv[r], w.xb, ldC, n, H, W, e, w, s));
     }
     IRB_TRY(layernorm(w.xa, dt, ldC, w.ln, dt, ldC, P, C, norm_w, norm_b, 0, 1e-5f, s));  // :800
