@@ -65,7 +65,9 @@ struct Epi {
     const float* post_shift;  // [N] or nullptr
     // optional fused PixelShuffle(2) store (ps=1): column n = c*4 + i*2 + j of LR pixel (y,x) goes to
     // channel c of HR pixel (2y+i, 2x+j); out is [B,2H,2W,N/4]. ps=2 is PixelUnshuffle(2): out is
-    // [B,H/2,W/2,4N]. ps_w / ps_h are the width / height the convolution runs at.
+    // [B,H/2,W/2,4N]. ps_w / ps_h are the width / height the convolution runs at. ps=3 is PixelShuffle(2) with the
+    // weight rows permuted sub-pixel major (column n = (i*2+j) * N/4 + c): every 64-column block is then one
+    // contiguous 128-byte run of an HR pixel and goes out as a strided 5-D TMA store.
     int ps;
     int ps_h, ps_w;
     // optional fused LayerNorm of the GEMM's A operand (weights pre-multiplied by the LN gain, see row_stats()):
@@ -188,6 +190,19 @@ __device__ __forceinline__ void epi_apply_store(const Epi& e, long long row, int
 #pragma unroll
         for (int i = 0; i < NV; ++i)
             if (i < nvalid) st_from_float(e.out, orow * e.ldo + (col0 + i) * 4 + sub, e.out_dt, v[i]);
+        return;
+    }
+    if (e.ps == 3) {
+        const int cout = ncols_total >> 2;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            if (i < nvalid) {
+                const int n = col0 + i;
+                const int sub = n / cout, c = n - sub * cout;
+                const long long orow = ((long long)b * (2 * e.ps_h) + (2 * y + (sub >> 1))) * (2 * e.ps_w) + (2 * x + (sub & 1));
+                st_from_float(e.out, orow * e.ldo + c, e.out_dt, v[i]);
+            }
+        }
         return;
     }
     if (e.ps == 1) {

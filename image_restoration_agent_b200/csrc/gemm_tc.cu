@@ -496,8 +496,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                             tma_store_3d(&p.tmC, stg, n0 + cb, mt * kTileM + q * 32, z);
                         } else {
                             const int r0 = q * 32;
-                            tma_store_4d(&p.tmC, stg, n0 + cb, (mt % p.tiles_x) * p.BW + r0 % p.BW,
-                                         (mt / p.tiles_x) * p.BH + r0 / p.BW, z);
+                            const int sx = (mt % p.tiles_x) * p.BW + r0 % p.BW, sy = (mt / p.tiles_x) * p.BH + r0 / p.BW;
+                            if (p.epi.ps == 3) {  // {c, j, x, 2y+i, image}: 32 LR pixels of one row -> every other HR pixel
+                                const int cout = p.N >> 2, ncol = n0 + cb;
+                                const int sub = ncol / cout;
+                                tma_store_5d(&p.tmC, stg, ncol - sub * cout, sub & 1, sx, 2 * sy + (sub >> 1), z);
+                            } else {
+                                tma_store_4d(&p.tmC, stg, n0 + cb, sx, sy, z);
+                            }
                         }
                         bulk_commit();
                     }
@@ -763,7 +769,20 @@ int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, cons
     p.epi = epi;
     IRB_REQUIRE(!epi.stats_out || tc_can_fuse_stats(N, epi), "tc_conv3x3: stats_out needs N <= 256, bf16 residual, TMA-store epilogue");
     p.tma_store = can_tma_store(epi) ? 1 : 0;
-    if (p.tma_store) {
+    if (epi.ps == 3) {
+        IRB_REQUIRE(N % 4 == 0, "tc_conv3x3: PixelShuffle needs N % 4 == 0");
+        Epi e0 = epi;
+        e0.ps = 0;
+        if (can_tma_store(e0) && BW >= 32 && (N / 4) % 64 == 0 && epi.res == nullptr) {
+            p.tma_store = 1;
+            const int cout = N / 4;
+            uint64_t dims[5] = {uint64_t(cout), 2, uint64_t(W), uint64_t(2 * H), uint64_t(Nimg)};
+            uint64_t str[4] = {uint64_t(epi.ldo) * 2, uint64_t(epi.ldo) * 4, uint64_t(epi.ldo) * 2 * 2 * W,
+                               uint64_t(epi.ldo) * 2 * 2 * W * 2 * H};
+            uint32_t box[5] = {64, 1, 32, 1, 1};
+            IRB_TRY(make_tmap_bf16(&p.tmC, epi.out, 5, dims, str, box));
+        }
+    } else if (p.tma_store) {
         const int bw = BW < 32 ? BW : 32;
         uint64_t dims[4] = {uint64_t(N), uint64_t(W), uint64_t(H), uint64_t(Nimg)};
         uint64_t str[3] = {uint64_t(epi.ldo) * 2, uint64_t(epi.ldo) * 2 * W, uint64_t(epi.ldo) * 2 * W * H};

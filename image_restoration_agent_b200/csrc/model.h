@@ -72,6 +72,7 @@ int nhwc_to_nchw_f32(const float* in, float* out, int n, int c, int h, int w, cu
 // conv weight [N][C][3][3] -> [Npad][9*kpad] (K index = tap*kpad + c), linear [N][K] -> [Npad][Kpad]
 std::vector<float> pack_conv3x3(const BlobTensor& w, int& kpad, int& npad);
 std::vector<float> pack_conv3x3_split(const BlobTensor& w, int& kpad, int& npad);  // C <= 4: hi/lo input split
+void permute_rows_ps_major(std::vector<float>& w, int N, int row_len, std::vector<float>* bias);
 std::vector<float> pack_linear(const float* w, int N, int K, int& kpad, int& npad);
 std::vector<float> pack_dw(const BlobTensor& w);  // [C][1][3][3] -> [9][C]
 

@@ -1,5 +1,6 @@
 // Weights blob parsing, weight packing, Model plumbing, and the model-level C ABI (irb_create ... irb_restore_image).
 #include "model.h"
+#include <algorithm>
 #include <string.h>
 
 namespace irb {
@@ -120,6 +121,25 @@ std::vector<float> pack_conv3x3(const BlobTensor& w, int& kpad, int& npad) {
             for (int t = 0; t < 9; ++t) o[(size_t(n) * 9 + t) * kpad + c] = w.data[(size_t(n) * C + c) * 9 + t];
     return o;
 }
+// PixelShuffle(2) convolutions: permute the packed weight rows (and the bias) sub-pixel major, row (i*2+j) * N/4 + c
+// <- row c*4 + i*2 + j, so that Epi::ps = 3 applies (common.cuh).
+void permute_rows_ps_major(std::vector<float>& w, int N, int row_len, std::vector<float>* bias) {
+    const int cout = N / 4;
+    std::vector<float> o(w.size(), 0.f);
+    for (int c = 0; c < cout; ++c)
+        for (int sub = 0; sub < 4; ++sub)
+            std::copy(w.begin() + size_t(c * 4 + sub) * row_len, w.begin() + size_t(c * 4 + sub + 1) * row_len,
+                      o.begin() + size_t(sub * cout + c) * row_len);
+    std::copy(w.begin() + size_t(N) * row_len, w.end(), o.begin() + size_t(N) * row_len);  // padding rows
+    w.swap(o);
+    if (bias) {
+        std::vector<float> b(bias->size());
+        for (int c = 0; c < cout; ++c)
+            for (int sub = 0; sub < 4; ++sub) b[sub * cout + c] = (*bias)[c * 4 + sub];
+        bias->swap(b);
+    }
+}
+
 // First-layer convolutions (1 or 3 input channels) run on the tensor core with the fp32 input split into two bf16
 // terms x = hi + lo (split_hi_lo_bf16, pointwise.cu): channel c holds hi, channel C + c holds lo, and both get the
 // same weight, so the input keeps ~16 mantissa bits at no cost (K is padded to 64 anyway).

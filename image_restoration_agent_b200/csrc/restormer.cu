@@ -52,6 +52,7 @@ struct ConvW {
     float* wf32;   // fp32 copy (SIMT path for tiny channel counts)
     void* wsplit;  // bf16 mode, C <= 4: [npad][9*64] weights for the hi/lo-split tensor-core first conv
     int kpad, npad, N, C;
+    int ps;        // PixelShuffle store mode when this conv is followed by PixelShuffle(2): 1 reference rows, 3 permuted
 };
 
 struct Restormer : Model {
@@ -75,7 +76,7 @@ struct Restormer : Model {
     };
     void layout(Bump& b, int n, int H, int W, WS& w);
     int load_block(const Blob& blob, const std::string& p, int C, int heads, RBlockW& o);
-    int load_conv(const Blob& blob, const std::string& name, int N, int C, ConvW& o);
+    int load_conv(const Blob& blob, const std::string& name, int N, int C, ConvW& o, bool pixelshuffle = false);
     int run_block(const RBlockW& w, void* x, long long ldx, int n, int H, int W, WS& ws, cudaStream_t s);
     int run_conv(const ConvW& c, const void* x, int x_dt, long long ldx, int n, int H, int W, Epi e, cudaStream_t s);
     int run_gemm(const void* A, long long lda, long long M, int K, const void* Wt, int ldw, int N, int wrows, Epi e,
@@ -166,12 +167,17 @@ int Restormer::load_block(const Blob& blob, const std::string& p, int C, int hea
     return 0;
 }
 
-int Restormer::load_conv(const Blob& blob, const std::string& name, int N, int C, ConvW& o) {
+int Restormer::load_conv(const Blob& blob, const std::string& name, int N, int C, ConvW& o, bool pixelshuffle) {
     BlobTensor t;
     IRB_TRY(blob.get(name, t, N, C, 3, 3));
     std::vector<float> w = pack_conv3x3(t, o.kpad, o.npad);
     o.N = N;
     o.C = C;
+    o.ps = pixelshuffle ? 1 : 0;
+    if (pixelshuffle && N % 4 == 0 && (N / 4) % 64 == 0) {
+        permute_rows_ps_major(w, N, 9 * o.kpad, nullptr);
+        o.ps = 3;
+    }
     IRB_TRY(upload_act(w.data(), w.size(), &o.w));
     o.wf32 = nullptr;
     if (dt == DT_F32)
@@ -216,16 +222,16 @@ int build_restormer(const irb_model_desc& d, const Blob& blob, int device, Model
     IRB_TRY(stage(m->enc3, "encoder_level3", d.num_blocks[2], dim * 4, d.heads[2]));
     IRB_TRY(m->load_conv(blob, "down3_4.body.0.weight", dim * 2, dim * 4, m->down34));
     IRB_TRY(stage(m->latent, "latent", d.num_blocks[3], dim * 8, d.heads[3]));
-    IRB_TRY(m->load_conv(blob, "up4_3.body.0.weight", dim * 16, dim * 8, m->up43));
+    IRB_TRY(m->load_conv(blob, "up4_3.body.0.weight", dim * 16, dim * 8, m->up43, true));
     BlobTensor t;
     IRB_TRY(blob.get("reduce_chan_level3.weight", t, dim * 4, dim * 8, 1, 1));
     IRB_TRY(m->upload_act(t.data, size_t(dim) * 4 * dim * 8, &m->reduce3));
     IRB_TRY(stage(m->dec3, "decoder_level3", d.num_blocks[2], dim * 4, d.heads[2]));
-    IRB_TRY(m->load_conv(blob, "up3_2.body.0.weight", dim * 8, dim * 4, m->up32));
+    IRB_TRY(m->load_conv(blob, "up3_2.body.0.weight", dim * 8, dim * 4, m->up32, true));
     IRB_TRY(blob.get("reduce_chan_level2.weight", t, dim * 2, dim * 4, 1, 1));
     IRB_TRY(m->upload_act(t.data, size_t(dim) * 2 * dim * 4, &m->reduce2));
     IRB_TRY(stage(m->dec2, "decoder_level2", d.num_blocks[1], dim * 2, d.heads[1]));
-    IRB_TRY(m->load_conv(blob, "up2_1.body.0.weight", dim * 4, dim * 2, m->up21));
+    IRB_TRY(m->load_conv(blob, "up2_1.body.0.weight", dim * 4, dim * 2, m->up21, true));
     IRB_TRY(stage(m->dec1, "decoder_level1", d.num_blocks[0], dim * 2, d.heads[0]));
     IRB_TRY(stage(m->refine, "refinement", d.num_refinement_blocks, dim * 2, d.heads[0]));
     IRB_TRY(m->load_conv(blob, "output.weight", d.in_chans, dim * 2, m->outc));
@@ -411,15 +417,15 @@ int Restormer::forward(const float* in, float* out, int n, int H, int W, void* w
     IRB_TRY(blocks(enc3, e3, 8 * d, H3, W3));                                                      // :254
     IRB_TRY(run_conv(down34, e3, dt, 8 * d, n, H3, W3, shuffle_epi(ws.x4, 8 * d, 2, H3, W3), s));  // :256
     IRB_TRY(blocks(latent, ws.x4, 8 * d, H4, W4));                                                 // :257
-    IRB_TRY(run_conv(up43, ws.x4, dt, 8 * d, n, H4, W4, shuffle_epi(ws.cat3, 8 * d, 1, H4, W4), s));  // :259-260
+    IRB_TRY(run_conv(up43, ws.x4, dt, 8 * d, n, H4, W4, shuffle_epi(ws.cat3, 8 * d, up43.ps, H4, W4), s));  // :259-260
     IRB_TRY(run_gemm(ws.cat3, 8 * d, (long long)n * H3 * W3, 8 * d, reduce3, 8 * d, 4 * d, 4 * d,
                      make_epi(ws.x3, 4 * d, dt), s));                                              // :261
     IRB_TRY(blocks(dec3, ws.x3, 4 * d, H3, W3));                                                   // :262
-    IRB_TRY(run_conv(up32, ws.x3, dt, 4 * d, n, H3, W3, shuffle_epi(ws.cat2, 4 * d, 1, H3, W3), s));  // :264-265
+    IRB_TRY(run_conv(up32, ws.x3, dt, 4 * d, n, H3, W3, shuffle_epi(ws.cat2, 4 * d, up32.ps, H3, W3), s));  // :264-265
     IRB_TRY(run_gemm(ws.cat2, 4 * d, (long long)n * H2 * W2, 4 * d, reduce2, 4 * d, 2 * d, 2 * d,
                      make_epi(ws.x2, 2 * d, dt), s));                                              // :266
     IRB_TRY(blocks(dec2, ws.x2, 2 * d, H2, W2));                                                   // :267
-    IRB_TRY(run_conv(up21, ws.x2, dt, 2 * d, n, H2, W2, shuffle_epi(ws.cat1, 2 * d, 1, H2, W2), s));  // :269-270
+    IRB_TRY(run_conv(up21, ws.x2, dt, 2 * d, n, H2, W2, shuffle_epi(ws.cat1, 2 * d, up21.ps, H2, W2), s));  // :269-270
     IRB_TRY(blocks(dec1, ws.cat1, 2 * d, H, W));                                                   // :271
     IRB_TRY(blocks(refine, ws.cat1, 2 * d, H, W));                                                 // :273
     {

@@ -39,6 +39,7 @@ struct Conv3W {
     void* wsplit;  // bf16 mode, C <= 4: weights of the hi/lo-split tensor-core first conv
     float* b;
     int N, C, kpad, npad;
+    int ps;        // PixelShuffle epilogue mode for this conv: 0 none, 1 reference row order, 3 sub-pixel-major rows
 };
 struct ResiW {  // '1conv' (c0 only) or '3conv' (c0 -> lrelu -> lin -> lrelu -> c2)
     Conv3W c0, c2;
@@ -113,7 +114,7 @@ struct SwinIR : Model {
         W = (W0 + m - 1) / m * m;
     }
     int load_lin(const Blob& blob, const std::string& name, int N, int K, LinW& o, const std::string& fold_norm = "");
-    int load_conv(const Blob& blob, const std::string& name, int N, int Cin, Conv3W& o);
+    int load_conv(const Blob& blob, const std::string& name, int N, int Cin, Conv3W& o, bool pixelshuffle = false);
     int load_resi(const Blob& blob, const std::string& name, ResiW& o);
     int load_qkv(const Blob& blob, const std::string& name, int heads, LinW& o, const std::string& fold_norm);
     int load_norm(const Blob& blob, const std::string& name, float** w, float** b);
@@ -191,12 +192,19 @@ int SwinIR::load_qkv(const Blob& blob, const std::string& name, int heads, LinW&
     return 0;
 }
 
-int SwinIR::load_conv(const Blob& blob, const std::string& name, int N, int Cin, Conv3W& o) {
-    BlobTensor t;
+int SwinIR::load_conv(const Blob& blob, const std::string& name, int N, int Cin, Conv3W& o, bool pixelshuffle) {
+    BlobTensor t, tb;
     IRB_TRY(blob.get(name + ".weight", t, N, Cin, 3, 3));
+    IRB_TRY(blob.get(name + ".bias", tb, N));
     std::vector<float> w = pack_conv3x3(t, o.kpad, o.npad);
+    std::vector<float> bias(tb.data, tb.data + N);
     o.N = N;
     o.C = Cin;
+    o.ps = pixelshuffle ? 1 : 0;
+    if (pixelshuffle && N % 4 == 0 && (N / 4) % 64 == 0) {
+        permute_rows_ps_major(w, N, 9 * o.kpad, &bias);
+        o.ps = 3;
+    }
     IRB_TRY(upload_act(w.data(), w.size(), &o.w));
     o.wf32 = nullptr;
     if (dt == DT_F32)
@@ -209,8 +217,7 @@ int SwinIR::load_conv(const Blob& blob, const std::string& name, int N, int Cin,
         std::vector<float> wsp = pack_conv3x3_split(t, kp, np);
         IRB_TRY(upload_act(wsp.data(), wsp.size(), &o.wsplit));
     }
-    IRB_TRY(blob.get(name + ".bias", t, N));
-    IRB_TRY(upload_f32(t.data, N, &o.b));
+    IRB_TRY(upload_f32(bias.data(), N, &o.b));
     return 0;
 }
 
@@ -292,7 +299,7 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
         for (int s = d.upscale; s > 1; s >>= 1) ++steps;
         m->upsample.resize(steps);
         for (int i = 0; i < steps; ++i)
-            IRB_TRY(m->load_conv(blob, "upsample." + std::to_string(2 * i), 256, 64, m->upsample[i]));
+            IRB_TRY(m->load_conv(blob, "upsample." + std::to_string(2 * i), 256, 64, m->upsample[i], true));
         IRB_TRY(m->load_conv(blob, "conv_last", d.in_chans, 64, m->conv_last));
     } else if (d.upsampler == IRB_UPSAMPLER_NEAREST_CONV) {
         IRB_TRY(m->load_conv(blob, "conv_before_upsample.0", 64, C, m->conv_before_up));
@@ -523,7 +530,7 @@ int SwinIR::forward(const float* in, float* out, int n, int H0, int W0, void* ws
         int which = (upsample.size() % 2 == 1) ? 0 : 1;
         for (size_t i = 0; i < upsample.size(); ++i) {
             Epi e = make_epi(bufs[which], 64, dt);  // conv 64->256 + PixelShuffle(2) fused into the store (:572-591)
-            e.ps = 1;
+            e.ps = upsample[i].ps;
             e.ps_h = h;
             e.ps_w = wd;
             IRB_TRY(conv(upsample[i], cur, dt, 64, n, h, wd, e, s));
