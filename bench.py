@@ -320,6 +320,15 @@ def run_b200(args):
             "peak_source": peaks["source"],
             "how": "CUDA events recorded by the library around every launch of one extra step after the timed region",
         }
+        # DRAM traffic of the dominant kernel: profiles/traffic.json holds, per kernel class, the ratio
+        # (dram__bytes_read.sum + dram__bytes_write.sum) / algorithmic bytes measured by one ncu --set full capture of a
+        # launch of that class (file and launch named there); traffic per launch = ratio x algorithmic bytes per launch.
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            tj = json.load(open(tpath)).get(top["kernel"])
+            if tj and top["bound"] == "hbm":
+                roofline["traffic"] = round(tj["dram_over_algorithmic"] * roofline["algorithmic_per_launch"]["bytes"])
+                roofline["traffic_source"] = tj["source"]
         tot_flops = sum(e["flops"] for e in prof.entries)
         tot_bytes = sum(e["bytes"] for e in prof.entries)
         line = {
