@@ -71,6 +71,7 @@ struct Restormer : Model {
         float *G, *sumsq, *attn;
         bf16* in8;      // [P1][8] hi/lo split of the fp32 input (bf16 mode)
         float2* stats;  // [P] (mu, rstd) of the LayerNorm folded into the next GEMM (bf16 mode)
+        float2* stats2; // [P] norm2 statistics of the attention output when the GDFN runs as one fused kernel
         size_t gs_bytes;
         bool stats_valid;  // ws.stats already holds the LayerNorm statistics of the current stream (written by the producing GEMM)
     };
@@ -275,6 +276,7 @@ void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
     w.gated = b.take(gat);
     w.weff = b.take(weff);
     w.stats = b.take<float2>(P1 * sizeof(float2));
+    w.stats2 = b.take<float2>(P1 * sizeof(float2));
     w.in8 = b.take<bf16>(P1 * 8 * sizeof(bf16));
     w.G = b.take<float>(gs);
     w.gs_bytes = gs;
@@ -331,15 +333,19 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
     else
         IRB_TRY(mdta_gram_simt(ws.qkv, DT_F32, 3 * C, n, H * W, C, heads, nch, G, ssq, s));
     IRB_TRY(mdta_softmax_weff(G, ssq, nch, w.temp, w.proj_w, n, C, heads, ws.weff, dt, ws.attn, s));
+    // bf16, C <= 96: the whole GDFN is one kernel that recomputes the hidden tensor with a halo, so it cannot run in
+    // place: the attention output goes to the scratch stream ws.ln and the GDFN writes x.
+    const bool fused_ffn = dt == DT_BF16 && gdfn_fused_supported(C, w.hp);
     {
-        Epi e = make_epi(x, ldx, dt);
+        Epi e = fused_ffn ? make_epi(ws.ln, C, dt) : make_epi(x, ldx, dt);
         e.res = x;
         e.ldr = ldx;
         e.res_dt = dt;
         const void* v = at(ws.qkv, 2 * C);
         ws.stats_valid = false;
+        float2* st = fused_ffn ? ws.stats2 : ws.stats;
         if (dt == DT_BF16 && tc_can_fuse_stats(C, e)) {  // norm2's statistics come out of this GEMM's epilogue
-            e.stats_out = ws.stats;
+            e.stats_out = st;
             e.stats_eps = 1e-5f;
             ws.stats_valid = true;
         }
@@ -347,6 +353,13 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
             IRB_TRY(tc_gemm((const bf16*)v, 3 * C, H * W, C, n, 0, (const bf16*)ws.weff, C, C, n * C, C, e, s));
         else
             IRB_TRY(simt_gemm(v, DT_F32, 3 * C, H * W, C, n, 0, (const float*)ws.weff, C, C, C, e, s));
+    }
+    if (fused_ffn) {
+        if (!ws.stats_valid) IRB_TRY(row_stats(ws.ln, dt, C, ws.stats2, P, C, 1e-5f, s));
+        IRB_TRY(gdfn_fused_bf16((const bf16*)ws.ln, C, ws.stats2, (bf16*)x, ldx, ws.stats, 1e-5f, n, H, W, C, w.hp,
+                                (const bf16*)w.pin_w, w.pin_cs, w.pin_t, w.ffn_dw, (const bf16*)w.pout_w, s));
+        ws.stats_valid = true;
+        return 0;
     }
     // --- x = x + project_out(gelu(dw(x1)) * dw(x2)) ---
     if (dt == DT_BF16) {  // norm2 folded into project_in

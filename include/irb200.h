@@ -135,6 +135,15 @@ int irb_dwconv3x3(const void* d_x, int dtype, long long ldx, void* d_y, long lon
 /* GDFN: y[.,c] = gelu(dw(x)[.,c]) * dw(x)[.,hp+c], c < hp; d_w fp32 [9][2*hp] */
 int irb_gdfn_dw_gate(const void* d_x, int dtype, long long ldx, void* d_y, long long ldy, int n, int H, int W, int hp,
                      const float* d_w, void* stream);
+/* The whole GDFN of a Restormer block (restormer_arch.py:88-93 with the block's norm2 and residual,
+ * :149-150) as ONE bf16 kernel: y = x + Wout . (gelu(dw(h1)) * dw(h2)), [h1 | h2] = Win' . LN(x).
+ * d_win bf16 [2*hp][C] = project_in with the LayerNorm gain folded in (rows [0,hp) = h1, [hp,2hp) = h2, zero padded),
+ * d_colsum / d_t fp32 [2*hp] = row sums of the (rounded) folded weights / Win . ln_bias (both NULL for BiasFree),
+ * d_dw fp32 [9][2*hp], d_wout bf16 [C][hp]. d_stats_in / d_stats_out: fp32 [n*H*W][2] scratch / output (mu, rstd) of
+ * the rows of x / y. C in {16..96} multiple of 16, hp in {64,128,192,256}; y must not alias x. */
+int irb_gdfn_fused(const void* d_x, long long ldx, void* d_y, long long ldy, int n, int H, int W, int C, int hp,
+                   const void* d_win, const float* d_colsum, const float* d_t, const float* d_dw, const void* d_wout,
+                   float* d_stats_in, float* d_stats_out, float eps, void* stream);
 /* MDTA Gram over a channels-last qkv tensor (q | k | v): the P pixels are split into nchunks =
  * irb_mdta_nchunks(P, heads, n) chunks and every chunk writes its own slot (no atomics -> bit-reproducible):
  *   d_Gpart   [n][heads][nchunks][c][c]   partial sum_p q k^T
