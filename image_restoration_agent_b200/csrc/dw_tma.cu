@@ -10,7 +10,7 @@
 // halo rows; every input row is loaded and converted ONCE (4 columns) and scattered into the three output rows it
 // touches (input-stationary, 3 live accumulator rows), so each element costs one LDS.32 + two ALU ops per 2 output
 // columns. Arithmetic is fp32 with packed fma.rn.f32x2 (both channels of the pair in one instruction); the GELU is
-// evaluated packed as well (Abramowitz-Stegun 7.1.26, 2 MUFU per element).
+// evaluated packed as well, in its sigmoid form (gelu2_fast: the kernel is bound by the FP32 pipe, 2 MUFU per element).
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_c
             for (int st = 0; st < NS; ++st)
 #pragma unroll
                 for (int d = 0; d < 4; ++d)
-                    in[st][d] = bf16x2_to_f32x2(lds_u32(tile + st * kDwStreamBytes + (hr * kDwHW + d) * kDwCh * 2));
+                    in[st][d] = bf16x2_to_f32x2_alu(lds_u32(tile + st * kDwStreamBytes + (hr * kDwHW + d) * kDwCh * 2));
             // halo row hr is tap row dr of output row hr - dr
 #pragma unroll
             for (int dr = 0; dr < 3; ++dr) {
@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_c
 #pragma unroll
                 for (int px = 0; px < 2; ++px) {
                     f32x2 o = acc[sl][px][0];
-                    if (GATE) o = mul2(gelu2(o), acc[sl][px][NS - 1]);
+                    if (GATE) o = mul2(gelu2_fast(o), acc[sl][px][NS - 1]);
                     float o0, o1;
                     unpack2(o, o0, o1);
                     pk[px] = pack_bf16x2(o0, o1);

@@ -34,8 +34,9 @@ static constexpr int kFfA1Slab = 256 * 128;     // one 64-channel K slab of the 
 static constexpr int kFfWinSlab = 64 * 128;     // 64 hidden rows x 64 K
 static constexpr int kFfA2Bytes = 128 * 128;    // 128 pixels x 64 gated channels (two chunks)
 static constexpr int kFfHidBytes = 26624;       // 204 x 128 B, rounded up to 1 KB
-static constexpr int kFfDwWarps = 16, kFfCvWarps = 4;
-static constexpr int kFfThreads = (kFfDwWarps + kFfCvWarps + 3) * 32;  // + TMA, MMA1, MMA2 warps = 736
+static constexpr int kFfDwWarps = 16, kFfCvWarps = 8;  // converter: one warpgroup per M-block of GEMM 1
+static constexpr int kFfCvActive = 7;  // converter warps that own halo rows (rows 224.. of M-block 1 do not exist)
+static constexpr int kFfThreads = (kFfDwWarps + kFfCvWarps + 3) * 32;  // + TMA, MMA1, MMA2 warps = 864
 static constexpr int kFfD2Col = 384;            // TMEM: D1 buffers at 0 / 128 / 256 (2 x 64 columns each), D2 at 384
 
 struct alignas(64) FfnParams {
@@ -62,10 +63,6 @@ struct FfnBars {
     uint32_t tmem_slot;
 };
 
-__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) {
-    asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
-}
-
 __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_constant__ FfnParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -87,7 +84,7 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
         for (int i = 0; i < 2; ++i) {
             mbar_init(&bars->win_full[i], 1);
             mbar_init(&bars->win_empty[i], 1);
-            mbar_init(&bars->hid_full[i], kFfCvWarps);
+            mbar_init(&bars->hid_full[i], kFfCvActive);
             mbar_init(&bars->hid_empty[i], kFfDwWarps);
             mbar_init(&bars->a2_empty[i], 1);
         }
@@ -95,11 +92,11 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
             mbar_init(&bars->wout_full[i], 1);
             mbar_init(&bars->wout_empty[i], 1);
             mbar_init(&bars->d1_full[i], 1);
-            mbar_init(&bars->d1_empty[i], kFfCvWarps);
+            mbar_init(&bars->d1_empty[i], kFfCvActive);
         }
         for (int i = 0; i < 4; ++i) mbar_init(&bars->a2_full[i], kFfDwWarps);
         mbar_init(&bars->d2_full, 1);
-        mbar_init(&bars->d2_empty, kFfCvWarps);
+        mbar_init(&bars->d2_empty, 4);
         fence_mbar_init();
     }
     if (warp == kFfDwWarps + kFfCvWarps) {
@@ -116,7 +113,11 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
         const int col0 = warp * 2, stream = lane >> 4, cp = lane & 15;
         const int in_chunk = stream * 4 + (cp >> 2);
         const uint32_t sub = (cp & 3) * 4;
-        const uint32_t hid_base = smem_u32(sHid), a2_base = smem_u32(sA2);
+        const uint8_t* hid_base = sHid + col0 * 128 + sub;  // plain shared-memory pointers: LDS / STS with immediates
+        // output word of this lane inside the A2 row of pixel (col0 + stream): 16-byte chunk (cp >> 2) of the chunk's
+        // 64-byte half, XOR-swizzled by the row index (rows of the tile are 32 apart, so only col0 + stream matters)
+        const int opx = col0 + stream;
+        const uint32_t out_off = opx * 128 + ((((cp >> 2) ^ (opx & 7)) << 4) | sub);
         int g = 0;
         for (int tile = blockIdx.x; tile < p.total; tile += gridDim.x) {
             for (int j = 0; j < NCH; ++j, ++g) {
@@ -128,20 +129,22 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
                     const float2 w2 = __ldg(reinterpret_cast<const float2*>(p.dww + (long long)t * 2 * p.hp + ch));
                     wr[t] = pack2(w2.x, w2.y);
                 }
+                // halo pixel (hr, col0 + d) is row hr * 34 + col0 + d of the hidden tile; its swizzle key is
+                // (2 * hr + d + col0) & 7, so 8 per-lane bases cover all 24 loads and the rest is an immediate offset
+                const uint8_t* hk[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    hk[k] = hid_base + hb * kFfHidBytes + ((in_chunk ^ ((col0 + k) & 7)) << 4);
                 mbar_wait(&bars->hid_full[hb], (g >> 1) & 1);
                 if (!(j & 1)) mbar_wait(&bars->a2_empty[(g >> 1) & 1], ((g >> 2) & 1) ^ 1);
-                const uint32_t hid = hid_base + hb * kFfHidBytes;
-                const uint32_t a2 = a2_base + ((g >> 1) & 1) * kFfA2Bytes;
-                const int out_chunk = (g & 1) * 4 + (cp >> 2);
+                uint8_t* a2 = sA2 + ((g >> 1) & 1) * kFfA2Bytes + (out_off ^ ((g & 1) << 6));
                 f32x2 acc[3][2];
 #pragma unroll
                 for (int hr = 0; hr < kFfHH; ++hr) {
                     f32x2 in[4];
 #pragma unroll
-                    for (int d = 0; d < 4; ++d) {
-                        const int row = hr * kFfHW + col0 + d;
-                        in[d] = bf16x2_to_f32x2(lds_u32(hid + row * 128 + ((in_chunk ^ (row & 7)) << 4) + sub));
-                    }
+                    for (int d = 0; d < 4; ++d)
+                        in[d] = bf16x2_to_f32x2_alu(*reinterpret_cast<const uint32_t*>(hk[(2 * hr + d) & 7] + (hr * kFfHW + d) * 128));
 #pragma unroll
                     for (int dr = 0; dr < 3; ++dr) {
                         const int orow = hr - dr;
@@ -166,9 +169,7 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
                         const f32x2 send = stream ? acc[sl][0] : acc[sl][1];
                         const f32x2 recv = __shfl_xor_sync(0xffffffffu, send, 16);
                         const f32x2 h1 = stream ? recv : keep, h2 = stream ? keep : recv;
-                        const uint32_t word = f32x2_to_bf16x2(mul2(gelu2(h1), h2));
-                        const int orow_px = done * kFfTW + col0 + stream;
-                        sts_u32(a2 + orow_px * 128 + ((out_chunk ^ (orow_px & 7)) << 4) + sub, word);
+                        *reinterpret_cast<uint32_t*>(a2 + done * kFfTW * 128) = f32x2_to_bf16x2(mul2(gelu2_fast(h1), h2));
                     }
                 }
                 fence_proxy_async();  // A2 is read by the tensor core (async proxy)
@@ -181,7 +182,9 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
         }
     } else if (warp < kFfDwWarps + kFfCvWarps) {
         // ================= converter (TMEM D1 -> hidden halo tile) + epilogue (D2 -> x_out) =================
-        const int q = warp & 3;
+        // warpgroup mb converts M-block mb (halo rows mb * 128 ..); warpgroup 1 has only 76 rows and also runs the
+        // output epilogue
+        const int q = warp & 3, mb = (warp - kFfDwWarps) >> 2;
         const int ct = threadIdx.x - kFfDwWarps * 32;
         float* s_cs = colvec;
         float* s_t = colvec + 2 * p.hp;
@@ -189,47 +192,66 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
             s_cs[i] = p.cs ? __ldg(p.cs + i) : 0.f;
             s_t[i] = p.t ? __ldg(p.t + i) : 0.f;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         const uint32_t tlane = tmem_base + (uint32_t(q * 32) << 16);
+        const int r = mb * 128 + q * 32 + lane;      // halo row of this thread
+        const bool warp_rows = mb * 128 + q * 32 < kFfRows;  // warp-uniform: this warp has rows to convert
+        const int hy = r / kFfHW, hx = r - hy * kFfHW;
 
+        // 16 output channels of this thread's pixel: + residual, shifted-sum statistics, bf16 store
+        auto epi16 = [&](const uint32_t* acc, const uint4& r0, const uint4& r1, f32x2 nshift2, f32x2& s1, f32x2& s2,
+                         bf16* dst, bool valid) {
+            const uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+            uint32_t pk[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                f32x2 y = pack2(__uint_as_float(acc[2 * i]), __uint_as_float(acc[2 * i + 1]));
+                y = add2(y, bf16x2_to_f32x2(rw[i]));
+                const f32x2 d = add2(y, nshift2);
+                s1 = add2(s1, d);
+                s2 = fma2(d, d, s2);
+                pk[i] = f32x2_to_bf16x2(y);
+            }
+            if (valid) {
+                *reinterpret_cast<uint4*>(dst) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                *reinterpret_cast<uint4*>(dst + 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            }
+        };
+        // The residual row (x_mid, an L2 hit ~700 cycles away) is fetched 32 channels at a time, one block ahead:
+        // the first block is requested before waiting for the accumulator, the next one before the current is used.
         auto epilogue = [&](int etile, int eti) {
             const int eimg = etile / per_img;
             const int er = etile - eimg * per_img;
             const int ety = er / p.tiles_x, etx = er - ety * p.tiles_x;
-            mbar_wait(&bars->d2_full, eti & 1);
-            tc_fence_after();
             const int gy = ety * kFfTH + q, gx = etx * kFfTW + lane;
             const bool valid = gy < p.H && gx < p.W;
             const long long pix = valid ? ((long long)eimg * p.H + gy) * p.W + gx : 0;
             const bf16* rrow = p.xmid + pix * p.ldm;
             bf16* orow = p.xout + pix * p.ldx;
+            uint4 rb[3][2];  // 16-channel groups of the residual row, two groups ahead of their use
+            rb[0][0] = __ldg(reinterpret_cast<const uint4*>(rrow));
+            rb[0][1] = __ldg(reinterpret_cast<const uint4*>(rrow + 8));
+            if (16 < p.C) {
+                rb[1][0] = __ldg(reinterpret_cast<const uint4*>(rrow + 16));
+                rb[1][1] = __ldg(reinterpret_cast<const uint4*>(rrow + 24));
+            }
+            mbar_wait(&bars->d2_full, eti & 1);
+            tc_fence_after();
             f32x2 s1 = 0ull, s2 = 0ull;
-            float shift = 0.f;
-            f32x2 nshift2 = 0ull;
-            for (int cb = 0; cb < p.C; cb += 16) {
-                uint32_t acc[16];
-                tmem_ld16_nowait(tlane + kFfD2Col + cb, acc);
-                const uint4 r0 = __ldg(reinterpret_cast<const uint4*>(rrow + cb));
-                const uint4 r1 = __ldg(reinterpret_cast<const uint4*>(rrow + cb + 8));
-                if (cb == 0) {
-                    shift = __uint_as_float(r0.x << 16);
-                    nshift2 = splat2(-shift);
-                }
-                tmem_ld_wait();
-                const uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
-                uint32_t pk[8];
+            const float shift = __uint_as_float(rb[0][0].x << 16);
+            const f32x2 nshift2 = splat2(-shift);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    f32x2 y = pack2(__uint_as_float(acc[2 * i]), __uint_as_float(acc[2 * i + 1]));
-                    y = add2(y, bf16x2_to_f32x2(rw[i]));
-                    const f32x2 d = add2(y, nshift2);
-                    s1 = add2(s1, d);
-                    s2 = fma2(d, d, s2);
-                    pk[i] = f32x2_to_bf16x2(y);
-                }
-                if (valid) {
-                    *reinterpret_cast<uint4*>(orow + cb) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                    *reinterpret_cast<uint4*>(orow + cb + 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            for (int gi = 0; gi < 6; ++gi) {
+                const int cb = gi * 16;
+                if (cb < p.C) {
+                    if (cb + 32 < p.C) {
+                        rb[(gi + 2) % 3][0] = __ldg(reinterpret_cast<const uint4*>(rrow + cb + 32));
+                        rb[(gi + 2) % 3][1] = __ldg(reinterpret_cast<const uint4*>(rrow + cb + 40));
+                    }
+                    uint32_t acc[16];
+                    tmem_ld16_nowait(tlane + kFfD2Col + cb, acc);
+                    tmem_ld_wait();
+                    epi16(acc, rb[gi % 3][0], rb[gi % 3][1], nshift2, s1, s2, orow + cb, valid);
                 }
             }
             if (valid && p.stats_out) {
@@ -246,38 +268,32 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
             if (lane == 0) mbar_arrive(&bars->d2_empty);
         };
 
-        int g = 0, ti = 0, prev_tile = -1;
-        for (int tile = blockIdx.x; tile < p.total; tile += gridDim.x, ++ti) {
+        // (mu, rstd) of this thread's halo pixel; fetched one tile ahead so that the L2 latency is off the critical path
+        auto tile_stats = [&](int tile, bool& in) -> float2 {
             const int img = tile / per_img;
             const int rr = tile - img * per_img;
             const int ty = rr / p.tiles_x, tx = rr - ty * p.tiles_x;
-            float fa[2], fb[2];
-            bool inimg[2];
-#pragma unroll
-            for (int mb = 0; mb < 2; ++mb) {
-                const int r = mb * 128 + q * 32 + lane;
-                const int hy = r / kFfHW, hx = r - hy * kFfHW;
-                const int gy = ty * kFfTH - 1 + hy, gx = tx * kFfTW - 1 + hx;
-                inimg[mb] = r < kFfRows && gy >= 0 && gy < p.H && gx >= 0 && gx < p.W;
-                fa[mb] = 0.f;
-                fb[mb] = 0.f;
-                if (inimg[mb]) {
-                    const float2 st = __ldg(p.stats_in + ((long long)img * p.H + gy) * p.W + gx);
-                    fa[mb] = st.y;
-                    fb[mb] = p.cs ? -st.x * st.y : 0.f;
-                }
-            }
+            const int gy = ty * kFfTH - 1 + hy, gx = tx * kFfTW - 1 + hx;
+            in = r < kFfRows && gy >= 0 && gy < p.H && gx >= 0 && gx < p.W;
+            return in ? __ldg(p.stats_in + ((long long)img * p.H + gy) * p.W + gx) : make_float2(0.f, 0.f);
+        };
+        int g = 0, ti = 0, prev_tile = -1;
+        bool in_next = false;
+        float2 st_next = make_float2(0.f, 0.f);
+        if (blockIdx.x < p.total) st_next = tile_stats(blockIdx.x, in_next);
+        for (int tile = blockIdx.x; tile < p.total; tile += gridDim.x, ++ti) {
+            const bool inimg = in_next;
+            const float fa = inimg ? st_next.y : 0.f;
+            const float fb = (inimg && p.cs) ? -st_next.x * st_next.y : 0.f;
+            if (tile + gridDim.x < p.total) st_next = tile_stats(tile + gridDim.x, in_next);
+            const f32x2 a2 = splat2(fa), b2 = splat2(fb);
             for (int j = 0; j < NCH; ++j, ++g) {
                 const int d = g % 3, hb = g & 1;
-                mbar_wait(&bars->d1_full[d], (g / 3) & 1);
-                tc_fence_after();
-                mbar_wait(&bars->hid_empty[hb], ((g >> 1) & 1) ^ 1);
-#pragma unroll
-                for (int mb = 0; mb < 2; ++mb) {
-                    if (mb * 128 + q * 32 >= kFfRows) continue;  // warp-uniform
-                    const int r = mb * 128 + q * 32 + lane;
+                if (warp_rows) {
+                    mbar_wait(&bars->d1_full[d], (g / 3) & 1);
+                    tc_fence_after();
+                    mbar_wait(&bars->hid_empty[hb], ((g >> 1) & 1) ^ 1);
                     uint8_t* hrow = sHid + hb * kFfHidBytes + r * 128;
-                    const f32x2 a2 = splat2(fa[mb]), b2 = splat2(fb[mb]);
 #pragma unroll
                     for (int half = 0; half < 2; ++half) {
                         uint32_t acc[32];
@@ -286,7 +302,7 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
                         const float* cs = s_cs + half * p.hp + j * 32;
                         const float* tt = s_t + half * p.hp + j * 32;
                         if (r < kFfRows) {
-                            if (inimg[mb]) {
+                            if (inimg) {
 #pragma unroll
                                 for (int i = 0; i < 4; ++i) {  // 16-byte chunk i of this half: 8 channels
                                     uint32_t pk[4];
@@ -311,18 +327,18 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
                             }
                         }
                     }
+                    tc_fence_before();
                 }
-                tc_fence_before();
                 __syncwarp();
-                if (lane == 0) {
+                if (warp_rows && lane == 0) {
                     mbar_arrive(&bars->d1_empty[d]);
                     mbar_arrive(&bars->hid_full[hb]);
                 }
-                if (j == 0 && ti > 0) epilogue(prev_tile, ti - 1);
+                if (mb == 1 && j == 1 && ti > 0) epilogue(prev_tile, ti - 1);
             }
             prev_tile = tile;
         }
-        if (ti > 0) epilogue(prev_tile, ti - 1);
+        if (mb == 1 && ti > 0) epilogue(prev_tile, ti - 1);
     } else if (warp == kFfDwWarps + kFfCvWarps) {
         // ================= TMA producer =================
         if (lane == 0) {
@@ -423,7 +439,7 @@ bool gdfn_fused_supported(int C, int hp) {
     static int enabled = -1;
     if (enabled < 0) {
         const char* e = getenv("IRB_FUSED_FFN");
-        enabled = e ? atoi(e) : 0;  // off by default until it beats the three-kernel path
+        enabled = e ? atoi(e) : 0;  // opt-in: at parity with the three-kernel path, see DESIGN.md
     }
     return enabled && C >= 16 && C <= 96 && C % 16 == 0 && hp >= 64 && hp <= 256 && hp % 64 == 0;
 }

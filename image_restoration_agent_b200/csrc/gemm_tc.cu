@@ -45,6 +45,9 @@ struct alignas(64) TcGemmParams {
     int acc_stride;
     int tiles_m, tiles_n, total;  // work items: total = batch * tiles_m * tiles_n, n fastest
     int m_outer;                  // 1: a CTA walks all n-tiles of its m-tile back to back
+    int b_resident;               // 1 (mode 0): the whole weight matrix stays in shared memory, the ring carries A only
+    int bres_bytes;
+    int dbg;                      // IRB_GEMM_DBG: 1 skip output stores, 2 skip LN-stats loads, 4 skip residual loads (diagnosis only)
     Epi epi;
 };
 
@@ -228,6 +231,17 @@ __device__ __forceinline__ void epi_block(const uint32_t (*acc)[16], const uint4
     }
 }
 
+// bf16 residual of one 64-column block of a row: whole 16-column groups only (ragged groups are read element-wise)
+__device__ __forceinline__ void load_res_block(const bf16* rb, int ng, int nvalid, uint4 (&dst)[8]) {
+#pragma unroll
+    for (int gi = 0; gi < 4; ++gi) {
+        if (gi < ng && gi * 16 + 16 <= nvalid) {
+            dst[2 * gi] = __ldg(reinterpret_cast<const uint4*>(rb + gi * 16));
+            dst[2 * gi + 1] = __ldg(reinterpret_cast<const uint4*>(rb + gi * 16 + 8));
+        }
+    }
+}
+
 // Work item w = (z * tiles_m + mt) * tiles_n + nt. A CTA takes m-tiles blockIdx.x, + gridDim.x, ... and walks ALL
 // n-tiles of an m-tile back to back, so the A tile it re-reads for the next n-tile is still in L2.
 __device__ __forceinline__ int first_item(const TcGemmParams& p) {
@@ -242,12 +256,16 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
     extern __shared__ uint8_t smem_raw[];
     // pointer arithmetic on the __shared__ symbol (not an integer round trip) keeps the address space known: LDS/STS
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    const int stage_bytes = kABytes + p.BN * 128;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.stages * stage_bytes);
+    // b_resident: [weights: tiles_n x ktiles slabs of BN x 128 B][ring of A tiles]; otherwise ring of (A, B) stages
+    const int stage_bytes = p.b_resident ? kABytes : kABytes + p.BN * 128;
+    uint8_t* ring = smem + p.bres_bytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + p.stages * stage_bytes);
     uint64_t* empty_bar = full_bar + p.stages;
     uint64_t* tfull_bar = empty_bar + p.stages;   // [2] accumulator ready (MMA -> epilogue)
     uint64_t* tempty_bar = tfull_bar + 2;         // [2] accumulator drained (epilogue -> MMA)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+    uint64_t* bres_full = tempty_bar + 2;         // resident weights loaded (TMA -> MMA)
+    uint64_t* bres_empty = bres_full + 1;         // all MMAs that read the resident weights are done (MMA -> TMA)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bres_empty + 1);
     const int ncolv = p.tiles_n * p.BN;                        // padded column count
     float* colvec = reinterpret_cast<float*>(tmem_slot + 4);  // [bias | colsum][ncolv], 16-byte aligned, staged once
     // 8 epilogue warps x 2 x 4 KB staging blocks for TMA stores ([32 rows][64 bf16], 128B-swizzled), 1024-aligned;
@@ -271,6 +289,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 mbar_init(&tfull_bar[a], 1);
                 mbar_init(&tempty_bar[a], 4);
             }
+            mbar_init(bres_full, 1);
+            mbar_init(bres_empty, 1);
             fence_mbar_init();
         }
         __syncwarp();
@@ -285,12 +305,23 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
 
     if (warp == 0 && lane == 0) {
         // ===== TMA producer =====
-        int it = 0;
+        int it = 0, nb = 0, cur_z = -1;
         for (int w = first_item(p); w < p.total; w = next_item(w, p)) {
             const int nt = w % p.tiles_n;
             const int mt = (w / p.tiles_n) % p.tiles_m;
             const int z = w / (p.tiles_n * p.tiles_m);
             const int n0 = nt * p.BN;
+            if (p.b_resident && (cur_z < 0 || (p.b_rows_per_batch != 0 && z != cur_z))) {
+                // (re)load the whole weight matrix; a new batch index only after the MMAs of the old one are done
+                if (nb > 0) mbar_wait(bres_empty, (nb - 1) & 1);
+                mbar_arrive_expect_tx(bres_full, p.bres_bytes);
+                for (int t = 0; t < p.tiles_n; ++t)
+                    for (int kc = 0; kc < p.ktiles; ++kc)
+                        tma_load_2d(smem + (t * p.ktiles + kc) * p.BN * 128, &p.tmB, bres_full, kc * kTileK,
+                                    z * p.b_rows_per_batch + t * p.BN);
+                cur_z = z;
+                ++nb;
+            }
             int x0 = 0, y0 = 0;
             if (p.mode == 1) {
                 x0 = (mt % p.tiles_x) * p.BW;
@@ -303,33 +334,44 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                     const int s = it % p.stages;
                     const uint32_t ph = (it / p.stages) & 1;
                     mbar_wait(&empty_bar[s], ph ^ 1);
-                    uint8_t* sa = smem + s * stage_bytes;
+                    uint8_t* sa = ring + s * stage_bytes;
                     uint8_t* sb = sa + kABytes;
                     mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
                     if (p.mode == 0)
                         tma_load_3d(sa, &p.tmA, &full_bar[s], kc * kTileK, mt * kTileM, z);
                     else
                         tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx, y0 + dy, z);
-                    tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK, z * p.b_rows_per_batch + n0);
+                    if (!p.b_resident)
+                        tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK, z * p.b_rows_per_batch + n0);
                 }
             }
         }
     } else if (warp == 1 && lane == 0) {
         // ===== MMA issuer =====
         const uint32_t idesc = make_idesc_bf16(kTileM, p.BN, 0, 0);
-        int it = 0, t = 0;
+        int it = 0, t = 0, nb = 0, cur_z = -1;
         for (int w = first_item(p); w < p.total; w = next_item(w, p), ++t) {
             const int a = t & 1;
+            if (p.b_resident) {
+                const int z = w / (p.tiles_n * p.tiles_m);
+                if (cur_z < 0 || (p.b_rows_per_batch != 0 && z != cur_z)) {
+                    if (nb > 0) umma_commit(bres_empty);  // every MMA issued so far has read the old weights
+                    mbar_wait(bres_full, nb & 1);
+                    cur_z = z;
+                    ++nb;
+                }
+            }
             mbar_wait(&tempty_bar[a], ((t >> 1) & 1) ^ 1);
             tc_fence_after();
             const uint32_t tacc = tmem_base + a * p.acc_stride;
+            const uint32_t bres_tile = smem_u32(smem) + (w % p.tiles_n) * p.ktiles * p.BN * 128;
             for (int i = 0; i < total_it; ++i, ++it) {
                 const int s = it % p.stages;
                 const uint32_t ph = (it / p.stages) & 1;
                 mbar_wait(&full_bar[s], ph);
                 tc_fence_after();
-                const uint32_t a_addr = smem_u32(smem + s * stage_bytes);
-                const uint32_t b_addr = a_addr + kABytes;
+                const uint32_t a_addr = smem_u32(ring + s * stage_bytes);
+                const uint32_t b_addr = p.b_resident ? bres_tile + i * p.BN * 128 : a_addr + kABytes;
 #pragma unroll
                 for (int k = 0; k < kTileK / 16; ++k) {
                     const uint64_t adesc = make_sdesc_sw128(a_addr + k * 32, 16, 1024);
@@ -388,9 +430,24 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 valid = (py < p.H) && (px < p.W);
                 grow = ((long long)z * p.H + py) * p.W + px;
             }
+            // The bf16 residual rows come from DRAM (the stream was written by the previous kernel) and their latency
+            // sits in front of every block's math: pull the rows of the tile this warp set handles NEXT into L2 now.
+            if (res_bf16 && p.mode == 0 && !(p.dbg & 8)) {
+                const int w2 = next_item(next_item(w, p), p);
+                if (w2 < p.total) {
+                    const int m2 = ((w2 / p.tiles_n) % p.tiles_m) * kTileM + r;
+                    if (m2 < p.M) {
+                        const bf16* pr = reinterpret_cast<const bf16*>(p.epi.res) +
+                                         ((long long)(w2 / (p.tiles_n * p.tiles_m)) * p.M + m2) * p.epi.ldr + (w2 % p.tiles_n) * p.BN;
+                        const int nb = min(p.BN, p.N - (w2 % p.tiles_n) * p.BN) * 2;
+                        for (int o = 0; o < nb; o += 128) prefetch_l2(reinterpret_cast<const uint8_t*>(pr) + o);
+                        prefetch_l2(reinterpret_cast<const uint8_t*>(pr) + nb - 2);
+                    }
+                }
+            }
             // the row's LayerNorm statistics do not depend on the accumulator: fetch them before waiting for it
             float fa = 1.f, fb = 0.f;
-            if (p.epi.ln_stats && valid) {
+            if (p.epi.ln_stats && valid && !(p.dbg & 2)) {
                 const float2 st = __ldg(p.epi.ln_stats + grow);
                 fa = st.y;
                 fb = p.epi.ln_colsum ? -st.x * st.y : 0.f;
@@ -416,21 +473,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                     if (res_bf16 || p.epi.res == nullptr) {
                         // all TMEM loads and residual loads of the block in flight before the first wait
                         uint32_t acc[4][16];
-                        uint4 rr[8];
 #pragma unroll
                         for (int gi = 0; gi < 4; ++gi)
                             if (gi < ng) tmem_ld16_nowait(taddr + cb + gi * 16, acc[gi]);
                         const int nvalid = min(64, p.N - (n0 + cb));
+                        uint4 rr[8];
                         const bf16* rrow = reinterpret_cast<const bf16*>(p.epi.res) + (valid ? grow : 0) * p.epi.ldr + n0 + cb;
-                        if (has_res_any) {
-#pragma unroll
-                            for (int gi = 0; gi < 4; ++gi) {
-                                if (gi < ng && gi * 16 + 16 <= nvalid) {
-                                    rr[2 * gi] = __ldg(reinterpret_cast<const uint4*>(rrow + gi * 16));
-                                    rr[2 * gi + 1] = __ldg(reinterpret_cast<const uint4*>(rrow + gi * 16 + 8));
-                                }
-                            }
-                        }
+                        if (has_res_any && !(p.dbg & 4)) load_res_block(rrow, ng, nvalid, rr);
                         if (do_stats && blk == 0) st_shift = __uint_as_float(rr[0].x << 16);  // x_old[row, 0]
                         // the store issued two blocks ago (same staging buffer) must have finished READING it
                         if (lane == 0) bulk_wait_read1();
@@ -493,7 +542,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                     __syncwarp();
                     if (lane == 0) {
                         if (p.mode == 0) {
-                            tma_store_3d(&p.tmC, stg, n0 + cb, mt * kTileM + q * 32, z);
+                            if (!(p.dbg & 1)) tma_store_3d(&p.tmC, stg, n0 + cb, mt * kTileM + q * 32, z);
                         } else {
                             const int r0 = q * 32;
                             const int sx = (mt % p.tiles_x) * p.BW + r0 % p.BW, sy = (mt / p.tiles_x) * p.BH + r0 / p.BW;
@@ -659,11 +708,37 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     IRB_REQUIRE(fixed + 2 * size_t(stage_bytes) <= 227 * 1024, "tc_gemm: N too large for the shared-memory column vectors");
     int stages = int((227 * 1024 - fixed) / stage_bytes);
     if (stages > 8) stages = 8;
+    // 1x1 GEMMs whose whole weight matrix fits next to >= 3 A stages keep it resident: otherwise every CTA re-reads
+    // the same N x K weights from L2 for each of its tiles (3x the A traffic at K = 96, all SMs on the same lines)
+    static int bres_on = -1;
+    if (bres_on < 0) {
+        const char* e = getenv("IRB_GEMM_BRES");
+        bres_on = e ? atoi(e) : 1;
+    }
+    static int dbg = -1;
+    if (dbg < 0) {
+        const char* e = getenv("IRB_GEMM_DBG");
+        dbg = e ? atoi(e) : 0;
+    }
+    p.dbg = dbg;
+    p.b_resident = 0;
+    p.bres_bytes = 0;
+    size_t ring_stage = stage_bytes;
+    if (bres_on && p.mode == 0) {
+        const size_t bres = size_t(p.tiles_n) * p.ktiles * p.BN * 128;
+        if (fixed + bres + 3 * size_t(kABytes) <= 227 * 1024) {
+            p.b_resident = 1;
+            p.bres_bytes = int(bres);
+            ring_stage = kABytes;
+            stages = int((227 * 1024 - fixed - bres) / kABytes);
+            if (stages > 8) stages = 8;
+        }
+    }
     p.stages = stages;
     const long long total = (long long)batch * p.tiles_m * p.tiles_n;
     IRB_REQUIRE(total < (1ll << 31), "tc_gemm: too many tiles");
     p.total = int(total);
-    const size_t smem = size_t(stages) * stage_bytes + fixed;
+    const size_t smem = size_t(stages) * ring_stage + p.bres_bytes + fixed;
     static bool attr_set = false;
     if (!attr_set) {
         IRB_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
