@@ -404,7 +404,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                             (reinterpret_cast<uintptr_t>(p.epi.out) % 16 == 0) &&
                             (!p.epi.res || ((p.epi.res_dt == DT_BF16 ? (p.epi.ldr % 8 == 0) : (p.epi.ldr % 4 == 0)) &&
                                             reinterpret_cast<uintptr_t>(p.epi.res) % 16 == 0));
-        const int lnmode = p.epi.ln_colsum ? 2 : ((p.epi.ln_stats || p.epi.bias) ? 1 : 0);
+        const int lnmode = (p.dbg & 16) ? 0 : (p.epi.ln_colsum ? 2 : ((p.epi.ln_stats || p.epi.bias) ? 1 : 0));
         const bool res_bf16 = p.epi.res != nullptr && p.epi.res_dt == DT_BF16;
         const bool do_stats = p.epi.stats_out != nullptr;
         int t = 0;
