@@ -209,7 +209,7 @@ int irb_gdfn_fused(const void* d_x, long long ldx, void* d_y, long long ldy, int
                    const void* d_win, const float* d_colsum, const float* d_t, const float* d_dw, const void* d_wout,
                    float* d_stats_in, float* d_stats_out, float eps, void* stream) {
     IRB_TRY(require_device());
-    IRB_REQUIRE(gdfn_fused_supported(C, hp), "irb_gdfn_fused: unsupported (C, hp) or disabled by IRB_FUSED_FFN=0");
+    IRB_REQUIRE(gdfn_fused_shape_ok(C, hp), "irb_gdfn_fused: unsupported (C, hp)");
     const long long P = (long long)n * H * W;
     IRB_TRY(row_stats(d_x, DT_BF16, ldx, reinterpret_cast<float2*>(d_stats_in), P, C, eps, (cudaStream_t)stream));
     return gdfn_fused_bf16((const bf16*)d_x, ldx, reinterpret_cast<const float2*>(d_stats_in), (bf16*)d_y, ldy,

@@ -435,13 +435,17 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
     if (warp == kFfDwWarps + kFfCvWarps) tmem_dealloc(tmem_base, 512);
 }
 
+bool gdfn_fused_shape_ok(int C, int hp) {
+    return C >= 16 && C <= 96 && C % 16 == 0 && hp >= 64 && hp <= 256 && hp % 64 == 0;
+}
+
 bool gdfn_fused_supported(int C, int hp) {
     static int enabled = -1;
     if (enabled < 0) {
         const char* e = getenv("IRB_FUSED_FFN");
         enabled = e ? atoi(e) : 0;  // opt-in: at parity with the three-kernel path, see DESIGN.md
     }
-    return enabled && C >= 16 && C <= 96 && C % 16 == 0 && hp >= 64 && hp <= 256 && hp % 64 == 0;
+    return enabled && gdfn_fused_shape_ok(C, hp);
 }
 
 int gdfn_fused_bf16(const bf16* xmid, long long ldm, const float2* stats_in, bf16* xout, long long ldx,

@@ -29,6 +29,7 @@ static constexpr int kABytes = kTileM * 128;      // 16 KB
 struct alignas(64) TcGemmParams {
     CUtensorMap tmA;
     CUtensorMap tmB;
+    CUtensorMap tmR;  // bf16 residual (mode 0, RES 2): same geometry and box as tmC
     CUtensorMap tmC;  // output (bf16): mode 0 {N, M, batch} box {64, 32, 1}; mode 1 {N, W, H, Nimg} box {64, bw, 32/bw, 1}
     int tma_store;    // 1: epilogue stages 32-row x 64-column blocks in shared memory and stores them with TMA
     int mode;
@@ -47,6 +48,8 @@ struct alignas(64) TcGemmParams {
     int m_outer;                  // 1: a CTA walks all n-tiles of its m-tile back to back
     int b_resident;               // 1 (mode 0): the whole weight matrix stays in shared memory, the ring carries A only
     int bres_bytes;
+    int res_tma;                  // 1: tmR is valid and the residual is TMA-staged (RES 2)
+    int stg_per_warp;             // 4 KB staging blocks per epilogue warp: 2, or 3 when the residual is TMA-staged
     int dbg;                      // IRB_GEMM_DBG: 1 skip output stores, 2 skip LN-stats loads, 4 skip residual loads (diagnosis only)
     Epi epi;
 };
@@ -252,6 +255,275 @@ __device__ __forceinline__ int next_item(int w, const TcGemmParams& p) {
     return ((w + 1) % p.tiles_n) ? w + 1 : w + 1 + (gridDim.x - 1) * p.tiles_n;
 }
 
+
+// ----------------------------------------------------------------------------------------------
+// Specialised epilogue (TMA-store path, no residual / bf16 residual). Every switch that selects the arithmetic is a
+// template parameter and the dispatch happens once per kernel, so the per-block code is one straight run of
+// LDTM / (LDS) / FFMA2 / F2FP / STS instead of a switch over inlined variants inside the tile loop.
+//   RES 0: no residual; 1: bf16 residual read by each thread from global memory (16-byte loads, mode 1);
+//   RES 2: bf16 residual rows TMA-loaded INTO the warp's staging block two blocks ahead (mode 0): the thread reads
+//          its 16-byte chunks from the swizzled block, adds, writes the result back in place, and the same block
+//          goes out as the TMA store, so no residual latency sits in front of the math.
+// ----------------------------------------------------------------------------------------------
+struct EpiCtx {
+    uint32_t tmem_base;
+    uint64_t* tfull_bar;
+    uint64_t* tempty_bar;
+    uint64_t* res_bar;   // [8 warps][3] residual-block barriers (RES 2)
+    const float* s_bias_all;
+    const float* s_cs_all;
+    uint8_t* staging;    // 8 warps x kStgPerWarp blocks of 4 KB
+    int stg_per_warp;    // 2, or 3 with RES 2
+};
+
+// rows of tile item w that this thread (row r of the tile) owns
+__device__ __forceinline__ void epi_row_of(const TcGemmParams& p, int w, int r, long long& grow, bool& valid) {
+    const int mt = (w / p.tiles_n) % p.tiles_m;
+    const int z = w / (p.tiles_n * p.tiles_m);
+    if (p.mode == 0) {
+        const int m = mt * kTileM + r;
+        valid = m < p.M;
+        grow = (long long)z * p.M + m;
+    } else {
+        const int py = (mt / p.tiles_x) * p.BH + r / p.BW;
+        const int px = (mt % p.tiles_x) * p.BW + r % p.BW;
+        valid = (py < p.H) && (px < p.W);
+        grow = ((long long)z * p.H + py) * p.W + px;
+    }
+}
+
+__device__ __forceinline__ float2 epi_load_stats(const TcGemmParams& p, int w, int r) {
+    float2 st = make_float2(0.f, 1.f);
+    if (w < p.total) {
+        long long grow;
+        bool valid;
+        epi_row_of(p, w, r, grow, valid);
+        if (valid) st = __ldg(p.epi.ln_stats + grow);
+    }
+    return st;
+}
+
+// NG full 16-column groups of one row. sx = shared address of the thread's staging row | ((lane & 7) << 4): chunk j of
+// the row lives at sx ^ (j << 4) (128-byte swizzle).
+template <int ACT, int LN, int RES, bool STATS, int NG>
+__device__ __forceinline__ void epi_block_full(uint32_t taddr_cb, const float* sb, const float* scs, f32x2 a2, f32x2 b2,
+                                               float slope, const bf16* rrow_cb, uint32_t sx, bool first_blk,
+                                               f32x2& s1, f32x2& s2, float& shift, bool wait_read, int lane) {
+    uint32_t acc[NG][16];
+#pragma unroll
+    for (int gi = 0; gi < NG; ++gi) tmem_ld16_nowait(taddr_cb + gi * 16, acc[gi]);
+    uint4 rr[RES == 1 ? 2 * NG : 1];
+    if (RES == 1) {
+#pragma unroll
+        for (int c = 0; c < 2 * NG; ++c) rr[c] = __ldg(reinterpret_cast<const uint4*>(rrow_cb + c * 8));
+    }
+    if (wait_read) {  // the store issued two blocks ago (same staging block) must have finished READING it
+        if (lane == 0) bulk_wait_read1();
+        __syncwarp();
+    }
+    if (STATS && first_blk)  // x_old[row, 0]
+        shift = __uint_as_float((RES == 2 ? lds_u32(sx) : rr[0].x) << 16);
+    const f32x2 nshift2 = splat2(-shift);
+    tmem_ld_wait();
+#pragma unroll
+    for (int gi = 0; gi < NG; ++gi) {
+        uint32_t pk[8];
+        uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
+        if (RES == 1) {
+            r0 = rr[2 * gi];
+            r1 = rr[2 * gi + 1];
+        } else if (RES == 2) {  // staged by TMA: short latency, read group by group
+            r0 = lds_v4(sx ^ ((2 * gi) << 4));
+            r1 = lds_v4(sx ^ ((2 * gi + 1) << 4));
+        }
+        epi_group16<ACT, LN, RES != 0, STATS>(acc[gi], sb + gi * 16, scs + gi * 16, a2, b2, slope, r0, r1, pk, s1, s2,
+                                              nshift2);
+        sts_v4(sx ^ ((2 * gi) << 4), pk[0], pk[1], pk[2], pk[3]);
+        sts_v4(sx ^ ((2 * gi + 1) << 4), pk[4], pk[5], pk[6], pk[7]);
+    }
+}
+
+template <int ACT, int LN, int RES, bool STATS>
+__device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCtx& c, int warp, int lane) {
+    const int q = warp & 3;
+    const int set = (warp - 2) >> 2;
+    const int r = q * 32 + lane;
+    const int nblk_max = (p.BN + 63) >> 6;
+    const uint32_t stg_warp = smem_u32(c.staging) + (warp - 2) * c.stg_per_warp * 4096;
+    uint8_t* stg_warp_p = c.staging + (warp - 2) * c.stg_per_warp * 4096;
+    const uint32_t row_off = lane * 128 + ((lane & 7) << 4);
+    uint64_t* rbar = c.res_bar + (warp - 2) * 3;
+    const float slope = p.epi.slope;
+
+    // first tile of this warp set
+    int w = first_item(p);
+    if (set == 1) w = next_item(w, p);
+    int t = set;
+    // software pipeline: LayerNorm statistics of the NEXT tile's row are fetched while this tile is processed
+    float2 st_next = make_float2(0.f, 1.f);
+    if (LN != 0 && p.epi.ln_stats) st_next = epi_load_stats(p, w, r);
+
+    // RES 2: residual prefetch iterator (pw, pblk), two blocks ahead of the consumer
+    int pw = w, pblk = 0;
+    uint32_t nissued = 0;
+    auto issue_res = [&]() {
+        if (pw >= p.total) return;
+        const int nt2 = pw % p.tiles_n, mt2 = (pw / p.tiles_n) % p.tiles_m, z2 = pw / (p.tiles_n * p.tiles_m);
+        const int col = nt2 * p.BN + pblk * 64;
+        const uint32_t b = nissued % 3;
+        if (lane == 0) {
+            mbar_arrive_expect_tx(&rbar[b], 4096);
+            tma_load_3d(stg_warp_p + b * 4096, &p.tmR, &rbar[b], col, mt2 * kTileM + q * 32, z2);
+        }
+        ++nissued;
+        ++pblk;
+        if (pblk >= nblk_max || nt2 * p.BN + pblk * 64 >= p.N) {
+            pblk = 0;
+            pw = next_item(next_item(pw, p), p);
+        }
+    };
+    if (RES == 2) {
+        issue_res();
+        issue_res();
+    }
+
+    uint32_t nb = 0;  // blocks consumed by this warp
+    for (; w < p.total; w = next_item(next_item(w, p), p), t += 2) {
+        const int nt = w % p.tiles_n;
+        const int mt = (w / p.tiles_n) % p.tiles_m;
+        const int z = w / (p.tiles_n * p.tiles_m);
+        const int n0 = nt * p.BN;
+        const float* s_bias = c.s_bias_all + n0;
+        const float* s_cs = c.s_cs_all + n0;
+        long long grow;
+        bool valid;
+        epi_row_of(p, w, r, grow, valid);
+        if (RES == 1 && p.mode == 0) {  // pull the residual rows of the NEXT tile of this set into L2
+            const int w2 = next_item(next_item(w, p), p);
+            if (w2 < p.total) {
+                const int m2 = ((w2 / p.tiles_n) % p.tiles_m) * kTileM + r;
+                if (m2 < p.M) {
+                    const bf16* pr = reinterpret_cast<const bf16*>(p.epi.res) +
+                                     ((long long)(w2 / (p.tiles_n * p.tiles_m)) * p.M + m2) * p.epi.ldr + (w2 % p.tiles_n) * p.BN;
+                    const int nbytes = min(p.BN, p.N - (w2 % p.tiles_n) * p.BN) * 2;
+                    for (int o = 0; o < nbytes; o += 128) prefetch_l2(reinterpret_cast<const uint8_t*>(pr) + o);
+                    prefetch_l2(reinterpret_cast<const uint8_t*>(pr) + nbytes - 2);
+                }
+            }
+        }
+        float fa = 1.f, fb = 0.f;
+        if (LN != 0 && p.epi.ln_stats) {
+            fa = st_next.y;
+            fb = (LN == 2) ? -st_next.x * st_next.y : 0.f;
+            st_next = epi_load_stats(p, next_item(next_item(w, p), p), r);
+        }
+        const f32x2 a2 = splat2(fa), b2 = splat2(fb);
+        f32x2 st_s1 = 0ull, st_s2 = 0ull;
+        float st_shift = 0.f;
+        const bf16* rrow = reinterpret_cast<const bf16*>(p.epi.res) + (valid ? grow : 0) * p.epi.ldr + n0;
+        mbar_wait(&c.tfull_bar[set], (t >> 1) & 1);
+        tc_fence_after();
+        const uint32_t taddr = c.tmem_base + set * p.acc_stride + (uint32_t(q * 32) << 16);
+        const int ncols = min(p.BN, p.N - n0);  // valid columns of this tile
+        for (int blk = 0; blk < nblk_max; ++blk) {
+            const int cb = blk * 64;
+            if (cb >= ncols) break;  // warp-uniform
+            const int nvalid = min(64, ncols - cb);
+            const uint32_t bsel = (RES == 2) ? nb % 3 : nb & 1;
+            const uint32_t stg = stg_warp + bsel * 4096;
+            const uint32_t sx = stg + row_off;
+            if (RES == 2) mbar_wait(&rbar[bsel], (nb / 3) & 1);
+            if (nvalid == 64 && RES == 1) {  // register-held residual: two halves keep the live set under the cap
+                epi_block_full<ACT, LN, RES, STATS, 2>(taddr + cb, s_bias + cb, s_cs + cb, a2, b2, slope, rrow + cb, sx,
+                                                       blk == 0, st_s1, st_s2, st_shift, true, lane);
+                epi_block_full<ACT, LN, RES, STATS, 2>(taddr + cb + 32, s_bias + cb + 32, s_cs + cb + 32, a2, b2, slope,
+                                                       rrow + cb + 32, sx ^ 64u, false, st_s1, st_s2, st_shift, false, lane);
+            } else if (nvalid == 64) {
+                epi_block_full<ACT, LN, RES, STATS, 4>(taddr + cb, s_bias + cb, s_cs + cb, a2, b2, slope, rrow + cb, sx,
+                                                       blk == 0, st_s1, st_s2, st_shift, RES != 2, lane);
+            } else if (nvalid == 32) {
+                epi_block_full<ACT, LN, RES, STATS, 2>(taddr + cb, s_bias + cb, s_cs + cb, a2, b2, slope, rrow + cb, sx,
+                                                       blk == 0, st_s1, st_s2, st_shift, RES != 2, lane);
+            } else {
+                // ragged block (N % 32 != 0): runtime group count, element-wise tail group
+                const int ng = min(4, (nvalid + 15) >> 4);
+                uint32_t acc[4][16];
+#pragma unroll
+                for (int gi = 0; gi < 4; ++gi)
+                    if (gi < ng) tmem_ld16_nowait(taddr + cb + gi * 16, acc[gi]);
+                uint4 rr[8];
+                if (RES == 1) load_res_block(rrow + cb, ng, nvalid, rr);
+                if (RES == 2) {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) rr[k] = lds_v4(sx ^ (k << 4));
+                }
+                if (STATS && blk == 0) st_shift = __uint_as_float(rr[0].x << 16);
+                if (RES != 2) {
+                    if (lane == 0) bulk_wait_read1();
+                    __syncwarp();
+                }
+                tmem_ld_wait();
+                const bf16* rrag = rrow + cb;
+                bf16 rtmp[16];
+                if (RES == 2) {  // the ragged group's residual as an array (columns >= nvalid are zero-filled by TMA)
+                    const int gl = nvalid >> 4;
+                    const uint4 u0 = gl == 0 ? rr[0] : (gl == 1 ? rr[2] : (gl == 2 ? rr[4] : rr[6]));
+                    const uint4 u1 = gl == 0 ? rr[1] : (gl == 1 ? rr[3] : (gl == 2 ? rr[5] : rr[7]));
+                    *reinterpret_cast<uint4*>(rtmp) = u0;
+                    *reinterpret_cast<uint4*>(rtmp + 8) = u1;
+                    rrag = rtmp - (nvalid >> 4) * 16;
+                }
+                epi_block<ACT, LN, RES != 0, STATS>(acc, rr, ng, nvalid, s_bias + cb, s_cs + cb, fa, fb, slope, rrag,
+                                                    stg_warp_p + bsel * 4096 + lane * 128, lane, st_s1, st_s2, st_shift);
+            }
+            const bool last = cb + 64 >= ncols;
+            if (last) {  // the accumulator is in registers / staged: hand it back to the MMA warp
+                tc_fence_before();
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+                if (last) mbar_arrive(&c.tempty_bar[set]);
+                if (!(p.dbg & 1)) {
+                    uint8_t* sp = stg_warp_p + bsel * 4096;
+                    if (p.mode == 0) {
+                        tma_store_3d(&p.tmC, sp, n0 + cb, mt * kTileM + q * 32, z);
+                    } else {
+                        const int r0 = q * 32;
+                        const int sx0 = (mt % p.tiles_x) * p.BW + r0 % p.BW, sy0 = (mt / p.tiles_x) * p.BH + r0 / p.BW;
+                        if (p.epi.ps == 3) {
+                            const int cout = p.N >> 2, ncol = n0 + cb;
+                            const int sub = ncol / cout;
+                            tma_store_5d(&p.tmC, sp, ncol - sub * cout, sub & 1, sx0, 2 * sy0 + (sub >> 1), z);
+                        } else {
+                            tma_store_4d(&p.tmC, sp, n0 + cb, sx0, sy0, z);
+                        }
+                    }
+                }
+                bulk_commit();
+            }
+            ++nb;
+            if (RES == 2) {
+                // block nb+1 goes into the staging block of block nb-2: its store must have finished reading
+                if (lane == 0) bulk_wait_read1();
+                __syncwarp();
+                issue_res();
+            }
+        }
+        if (STATS && valid) {
+            float a0, a1, q0, q1;
+            unpack2(st_s1, a0, a1);
+            unpack2(st_s2, q0, q1);
+            const float invn = 1.0f / float(p.N);
+            const float m = (a0 + a1) * invn;
+            const float var = fmaxf((q0 + q1) * invn - m * m, 0.f);
+            p.epi.stats_out[grow] = make_float2(st_shift + m, rsqrtf(var + p.epi.stats_eps));
+        }
+    }
+    if (lane == 0) bulk_wait0();  // all bulk stores of this warp have landed before the CTA exits
+}
+
+template <int VAR>
 __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_constant__ TcGemmParams p) {
     extern __shared__ uint8_t smem_raw[];
     // pointer arithmetic on the __shared__ symbol (not an integer round trip) keeps the address space known: LDS/STS
@@ -265,10 +537,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
     uint64_t* tempty_bar = tfull_bar + 2;         // [2] accumulator drained (epilogue -> MMA)
     uint64_t* bres_full = tempty_bar + 2;         // resident weights loaded (TMA -> MMA)
     uint64_t* bres_empty = bres_full + 1;         // all MMAs that read the resident weights are done (MMA -> TMA)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bres_empty + 1);
+    uint64_t* res_bar = bres_empty + 1;           // [8][3] residual blocks landed (TMA -> epilogue warp)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 24);
     const int ncolv = p.tiles_n * p.BN;                        // padded column count
     float* colvec = reinterpret_cast<float*>(tmem_slot + 4);  // [bias | colsum][ncolv], 16-byte aligned, staged once
-    // 8 epilogue warps x 2 x 4 KB staging blocks for TMA stores ([32 rows][64 bf16], 128B-swizzled), 1024-aligned;
+    // 8 epilogue warps x stg_per_warp x 4 KB staging blocks for TMA stores ([32 rows][64 bf16], 128B-swizzled), 1024-aligned;
     // double-buffered so that a warp never waits for the store it has just issued (wait_group.read 1)
     uint8_t* stg_lo = reinterpret_cast<uint8_t*>(colvec + 2 * ncolv);
     uint8_t* staging = stg_lo + ((1024u - (smem_u32(stg_lo) & 1023u)) & 1023u);
@@ -291,6 +564,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             }
             mbar_init(bres_full, 1);
             mbar_init(bres_empty, 1);
+            for (int i = 0; i < 24; ++i) mbar_init(&res_bar[i], 1);
+            if (VAR >= 0 && ((VAR >> 4) & 3) == 2) tma_prefetch_desc(&p.tmR);
             fence_mbar_init();
         }
         __syncwarp();
@@ -398,6 +673,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             s_cs_all[i] = (p.epi.ln_colsum && i < p.N) ? __ldg(p.epi.ln_colsum + i) : 0.f;
         }
         asm volatile("bar.sync 1, 256;" ::: "memory");
+        if constexpr (VAR >= 0) {
+            EpiCtx c{tmem_base, tfull_bar, tempty_bar, res_bar, s_bias_all, s_cs_all, staging, p.stg_per_warp};
+            epilogue_fast<VAR & 3, (VAR >> 2) & 3, (VAR >> 4) & 3, ((VAR >> 6) & 1) != 0>(p, c, warp, lane);
+        } else {
         // fast path: aligned vector access for 16-column groups, no pixel shuffle / post scale
         const bool vec_ok = p.epi.ps == 0 && p.epi.post_scale == 1.0f && p.epi.post_shift == nullptr &&
                             (p.epi.out_dt == DT_BF16 ? (p.epi.ldo % 8 == 0) : (p.epi.ldo % 4 == 0)) &&
@@ -460,7 +739,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             if (p.tma_store) {
                 // ---- 64-column blocks: TMEM -> registers (math) -> swizzled smem block -> TMA store ----
                 const int nblk = (p.BN + 63) >> 6;
-                uint8_t* stg_base = staging + (warp - 2) * 8192;
+                uint8_t* stg_base = staging + (warp - 2) * p.stg_per_warp * 4096;
                 const bool has_res = p.epi.res != nullptr && valid;
                 const bool has_res_any = p.epi.res != nullptr;  // warp-uniform (rows past M read row 0, are clipped)
                 for (int blk = 0; blk < nblk; ++blk) {
@@ -589,6 +868,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             if (lane == 0) mbar_arrive(&tempty_bar[set]);
         }
         if (p.tma_store && lane == 0) bulk_wait0();  // all bulk stores of this warp have landed before the CTA exits
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -698,13 +978,46 @@ static int sm_count() {
     return sms;
 }
 
+typedef void (*GemmKernelFn)(const TcGemmParams);
+
+// Specialised epilogue variants that exist (VAR = act | ln << 2 | res << 4 | stats << 6); anything else runs the
+// generic kernel (VAR -1), which also covers fp32 outputs / residuals, PixelShuffle(1) / PixelUnshuffle stores.
+#define IRB_GEMM_VARIANTS(X)                                                                                    \
+    X(0, 0, 0, 0) X(0, 1, 0, 0) X(0, 2, 0, 0) X(0, 0, 1, 0) X(0, 1, 1, 0) X(0, 2, 1, 0) X(0, 0, 2, 0) X(0, 1, 2, 0) \
+    X(0, 2, 2, 0) X(1, 0, 0, 0) X(1, 1, 0, 0) X(1, 2, 0, 0) X(2, 0, 0, 0) X(2, 1, 0, 0) X(0, 0, 1, 1) X(0, 1, 1, 1) \
+    X(0, 0, 2, 1) X(0, 1, 2, 1)
+
+static GemmKernelFn pick_gemm_kernel(int& var, int* slot) {
+    int i = 1;
+#define X(A, L, R, S)                                             \
+    if (var == ((A) | ((L) << 2) | ((R) << 4) | ((S) << 6))) {    \
+        *slot = i;                                                \
+        return tc_gemm_kernel<(A) | ((L) << 2) | ((R) << 4) | ((S) << 6)>; \
+    }                                                             \
+    ++i;
+    IRB_GEMM_VARIANTS(X)
+#undef X
+    var = -1;
+    *slot = 0;
+    return tc_gemm_kernel<-1>;
+}
+
+// does the (act, ln, TMA-staged residual, stats) combination of this epilogue have a specialised kernel?
+static bool gemm_variant_exists(const Epi& e) {
+    const int ln = e.ln_colsum ? 2 : ((e.ln_stats || e.bias) ? 1 : 0);
+    int var = e.act | (ln << 2) | (2 << 4) | (e.stats_out ? 64 : 0), slot = 0;
+    pick_gemm_kernel(var, &slot);
+    return var >= 0;
+}
+
 static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     const int stage_bytes = kABytes + p.BN * 128;
     p.acc_stride = (p.BN + 31) / 32 * 32;
     p.tmem_cols = tmem_cols_for(2 * p.acc_stride);
     p.tiles_n = ceil_div(p.N, p.BN);
-    const size_t fixed = 1024 /*align*/ + 256 /*barriers*/ + size_t(2) * p.tiles_n * p.BN * 4 /*column vectors*/ +
-                         1024 + 8 * 8192 /*TMA-store staging*/;
+    p.stg_per_warp = p.res_tma ? 3 : 2;
+    const size_t fixed = 1024 /*align*/ + 512 /*barriers*/ + size_t(2) * p.tiles_n * p.BN * 4 /*column vectors*/ +
+                         1024 + 8 * size_t(p.stg_per_warp) * 4096 /*TMA-store staging*/;
     IRB_REQUIRE(fixed + 2 * size_t(stage_bytes) <= 227 * 1024, "tc_gemm: N too large for the shared-memory column vectors");
     int stages = int((227 * 1024 - fixed) / stage_bytes);
     if (stages > 8) stages = 8;
@@ -739,10 +1052,27 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     IRB_REQUIRE(total < (1ll << 31), "tc_gemm: too many tiles");
     p.total = int(total);
     const size_t smem = size_t(stages) * ring_stage + p.bres_bytes + fixed;
-    static bool attr_set = false;
-    if (!attr_set) {
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set = true;
+    int var = -1;
+    static int spec_on = -1;
+    if (spec_on < 0) {
+        const char* e = getenv("IRB_GEMM_SPEC");
+        spec_on = e ? atoi(e) : 1;
+    }
+    const bool res_bf16 = p.epi.res != nullptr && p.epi.res_dt == DT_BF16;
+    if (spec_on && p.tma_store && (p.epi.res == nullptr || res_bf16)) {
+        const int ln = p.epi.ln_colsum ? 2 : ((p.epi.ln_stats || p.epi.bias) ? 1 : 0);
+        const int res = p.epi.res == nullptr ? 0 : (p.res_tma ? 2 : 1);
+        var = p.epi.act | (ln << 2) | (res << 4) | (p.epi.stats_out ? 64 : 0);
+    }
+    int slot = 0;
+    GemmKernelFn fn = pick_gemm_kernel(var, &slot);
+    if (var < 0 && p.res_tma) {  // generic kernel: no TMA-staged residual
+        IRB_REQUIRE(false, "tc_gemm: internal: res_tma without a specialised variant");
+    }
+    static bool attr_set[64] = {false};
+    if (!attr_set[slot]) {
+        IRB_CHECK_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_set[slot] = true;
     }
     static int order = -1;
     if (order < 0) {
@@ -752,7 +1082,7 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     p.m_outer = order;
     const long long units = p.m_outer ? (long long)batch * p.tiles_m : total;
     const int grid = int(units < sm_count() ? units : sm_count());
-    tc_gemm_kernel<<<grid, kGemmThreads, smem, stream>>>(p);
+    fn<<<grid, kGemmThreads, smem, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -793,6 +1123,16 @@ int tc_gemm(const bf16* A, long long lda, int M, int K, int batch, long long a_b
         uint64_t str[2] = {uint64_t(epi.ldo) * 2, uint64_t(epi.ldo) * 2 * M};
         uint32_t box[3] = {64, 32, 1};
         IRB_TRY(make_tmap_bf16(&p.tmC, epi.out, 3, dims, str, box));
+        static int restma_on = -1;
+        if (restma_on < 0) {
+            const char* e = getenv("IRB_GEMM_RESTMA");
+            restma_on = e ? atoi(e) : 1;
+        }
+        if (restma_on && epi.res != nullptr && epi.res_dt == DT_BF16 && gemm_variant_exists(epi)) {
+            uint64_t rstr[2] = {uint64_t(epi.ldr) * 2, uint64_t(epi.ldr) * 2 * M};
+            IRB_TRY(make_tmap_bf16(&p.tmR, epi.res, 3, dims, rstr, box));
+            p.res_tma = 1;
+        }
     }
     p.tiles_m = ceil_div(M, kTileM);
     IRB_TRY(launch_tc(p, batch, stream));

@@ -49,7 +49,8 @@ int dwconv3x3_gate_bf16_tma(const bf16* x, long long ldx, bf16* y, long long ldy
 // x_out = x_mid + Wout . (gelu(dw(h1)) * dw(h2)), [h1 | h2] = Win' . LN(x_mid); Win' is [2*hp][C] with the LayerNorm
 // gain folded in (rows [0,hp) = h1, [hp,2hp) = h2), cs / t as in Epi::ln_colsum / bias (nullptr for BiasFree),
 // stats_in = (mu, rstd) per pixel of x_mid, stats_out = the same for x_out. x_out must not alias x_mid.
-bool gdfn_fused_supported(int C, int hp);
+bool gdfn_fused_supported(int C, int hp);  // shape supported AND the model runners use it (IRB_FUSED_FFN=1)
+bool gdfn_fused_shape_ok(int C, int hp);
 int gdfn_fused_bf16(const bf16* xmid, long long ldm, const float2* stats_in, bf16* xout, long long ldx,
                     float2* stats_out, float stats_eps, int Nimg, int H, int W, int C, int hp, const bf16* win,
                     const float* cs, const float* t, const float* dww, const bf16* wout, cudaStream_t stream);
