@@ -48,6 +48,7 @@ struct alignas(64) TcGemmParams {
     int m_outer;                  // 1: a CTA walks all n-tiles of its m-tile back to back
     int b_resident;               // 1 (mode 0): the whole weight matrix stays in shared memory, the ring carries A only
     int bres_bytes;
+    int blk_cols;                 // columns per epilogue block: 64, or 48 (PixelShuffle with 48 | N/4, specialised kernels only)
     int res_tma;                  // 1: tmR is valid and the residual is TMA-staged (RES 2)
     int stg_per_warp;             // 4 KB staging blocks per epilogue warp: 2, or 3 when the residual is TMA-staged
     int dbg;                      // IRB_GEMM_DBG: 1 skip output stores, 2 skip LN-stats loads, 4 skip residual loads (diagnosis only)
@@ -348,7 +349,8 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
     const int q = warp & 3;
     const int set = (warp - 2) >> 2;
     const int r = q * 32 + lane;
-    const int nblk_max = (p.BN + 63) >> 6;
+    const int bcols = p.blk_cols;
+    const int nblk_max = (p.BN + bcols - 1) / bcols;
     const uint32_t stg_warp = smem_u32(c.staging) + (warp - 2) * c.stg_per_warp * 4096;
     uint8_t* stg_warp_p = c.staging + (warp - 2) * c.stg_per_warp * 4096;
     const uint32_t row_off = lane * 128 + ((lane & 7) << 4);
@@ -369,7 +371,7 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
     auto issue_res = [&]() {
         if (pw >= p.total) return;
         const int nt2 = pw % p.tiles_n, mt2 = (pw / p.tiles_n) % p.tiles_m, z2 = pw / (p.tiles_n * p.tiles_m);
-        const int col = nt2 * p.BN + pblk * 64;
+        const int col = nt2 * p.BN + pblk * bcols;
         const uint32_t b = nissued % 3;
         if (lane == 0) {
             mbar_arrive_expect_tx(&rbar[b], 4096);
@@ -377,7 +379,7 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
         }
         ++nissued;
         ++pblk;
-        if (pblk >= nblk_max || nt2 * p.BN + pblk * 64 >= p.N) {
+        if (pblk >= nblk_max || nt2 * p.BN + pblk * bcols >= p.N) {
             pblk = 0;
             pw = next_item(next_item(pw, p), p);
         }
@@ -426,9 +428,9 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
         const uint32_t taddr = c.tmem_base + set * p.acc_stride + (uint32_t(q * 32) << 16);
         const int ncols = min(p.BN, p.N - n0);  // valid columns of this tile
         for (int blk = 0; blk < nblk_max; ++blk) {
-            const int cb = blk * 64;
+            const int cb = blk * bcols;
             if (cb >= ncols) break;  // warp-uniform
-            const int nvalid = min(64, ncols - cb);
+            const int nvalid = min(bcols, ncols - cb);
             const uint32_t bsel = (RES == 2) ? nb % 3 : nb & 1;
             const uint32_t stg = stg_warp + bsel * 4096;
             const uint32_t sx = stg + row_off;
@@ -444,6 +446,9 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
             } else if (nvalid == 32) {
                 epi_block_full<ACT, LN, RES, STATS, 2>(taddr + cb, s_bias + cb, s_cs + cb, a2, b2, slope, rrow + cb, sx,
                                                        blk == 0, st_s1, st_s2, st_shift, RES != 2, lane);
+            } else if (nvalid == 48 && RES == 0) {
+                epi_block_full<ACT, LN, RES, STATS, 3>(taddr + cb, s_bias + cb, s_cs + cb, a2, b2, slope, rrow + cb, sx,
+                                                       blk == 0, st_s1, st_s2, st_shift, true, lane);
             } else {
                 // ragged block (N % 32 != 0): runtime group count, element-wise tail group
                 const int ng = min(4, (nvalid + 15) >> 4);
@@ -476,7 +481,7 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
                 epi_block<ACT, LN, RES != 0, STATS>(acc, rr, ng, nvalid, s_bias + cb, s_cs + cb, fa, fb, slope, rrag,
                                                     stg_warp_p + bsel * 4096 + lane * 128, lane, st_s1, st_s2, st_shift);
             }
-            const bool last = cb + 64 >= ncols;
+            const bool last = cb + bcols >= ncols;
             if (last) {  // the accumulator is in registers / staged: hand it back to the MMA warp
                 tc_fence_before();
             }
@@ -916,10 +921,24 @@ int make_tmap_bf16_sw(CUtensorMap* m, const void* base, int rank, const uint64_t
         b[i] = box[i];
     }
     for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
+    // L2 promotion widens every TMA read to whole 64/128/256-byte L2 requests. Measured on cfg2 (profiles/
+    // r01_s25_tma_promo.txt): 128 B and none are equal and ~1 % faster than 256 B, which drags neighbouring columns
+    // out of DRAM when a box covers a slice of each row (v of a qkv buffer: 192 of 576 bytes, 1.67x over-read in ncu).
+    // IRB_TMA_PROMO=0..3 forces none/64/128/256 (diagnosis).
+    static int promo_env = -2;
+    if (promo_env == -2) {
+        const char* e = getenv("IRB_TMA_PROMO");
+        promo_env = e ? atoi(e) : -1;
+    }
+    const int promo = promo_env >= 0 ? promo_env : 2;
+    const CUtensorMapL2promotion pr = promo == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE
+                                      : promo == 1 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+                                      : promo == 2 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B
+                                                   : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
     CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), d, s, b, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE,
                      swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
-                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     pr,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         char buf[256];
@@ -980,6 +999,15 @@ static int sm_count() {
 
 typedef void (*GemmKernelFn)(const TcGemmParams);
 
+static int gemm_spec_on() {  // IRB_GEMM_SPEC=0: generic kernel only (diagnosis)
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("IRB_GEMM_SPEC");
+        on = e ? atoi(e) : 1;
+    }
+    return on;
+}
+
 // Specialised epilogue variants that exist (VAR = act | ln << 2 | res << 4 | stats << 6); anything else runs the
 // generic kernel (VAR -1), which also covers fp32 outputs / residuals, PixelShuffle(1) / PixelUnshuffle stores.
 #define IRB_GEMM_VARIANTS(X)                                                                                    \
@@ -1004,6 +1032,7 @@ static GemmKernelFn pick_gemm_kernel(int& var, int* slot) {
 
 // does the (act, ln, TMA-staged residual, stats) combination of this epilogue have a specialised kernel?
 static bool gemm_variant_exists(const Epi& e) {
+    if (!gemm_spec_on()) return false;
     const int ln = e.ln_colsum ? 2 : ((e.ln_stats || e.bias) ? 1 : 0);
     int var = e.act | (ln << 2) | (2 << 4) | (e.stats_out ? 64 : 0), slot = 0;
     pick_gemm_kernel(var, &slot);
@@ -1016,6 +1045,7 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     p.tmem_cols = tmem_cols_for(2 * p.acc_stride);
     p.tiles_n = ceil_div(p.N, p.BN);
     p.stg_per_warp = p.res_tma ? 3 : 2;
+    if (p.blk_cols == 0) p.blk_cols = 64;
     const size_t fixed = 1024 /*align*/ + 512 /*barriers*/ + size_t(2) * p.tiles_n * p.BN * 4 /*column vectors*/ +
                          1024 + 8 * size_t(p.stg_per_warp) * 4096 /*TMA-store staging*/;
     IRB_REQUIRE(fixed + 2 * size_t(stage_bytes) <= 227 * 1024, "tc_gemm: N too large for the shared-memory column vectors");
@@ -1053,11 +1083,7 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     p.total = int(total);
     const size_t smem = size_t(stages) * ring_stage + p.bres_bytes + fixed;
     int var = -1;
-    static int spec_on = -1;
-    if (spec_on < 0) {
-        const char* e = getenv("IRB_GEMM_SPEC");
-        spec_on = e ? atoi(e) : 1;
-    }
+    const int spec_on = gemm_spec_on();
     const bool res_bf16 = p.epi.res != nullptr && p.epi.res_dt == DT_BF16;
     if (spec_on && p.tma_store && (p.epi.res == nullptr || res_bf16)) {
         const int ln = p.epi.ln_colsum ? 2 : ((p.epi.ln_stats || p.epi.bias) ? 1 : 0);
@@ -1066,9 +1092,7 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     }
     int slot = 0;
     GemmKernelFn fn = pick_gemm_kernel(var, &slot);
-    if (var < 0 && p.res_tma) {  // generic kernel: no TMA-staged residual
-        IRB_REQUIRE(false, "tc_gemm: internal: res_tma without a specialised variant");
-    }
+    IRB_REQUIRE(var >= 0 || (!p.res_tma && p.blk_cols == 64), "tc_gemm: internal: res_tma / 48-column blocks need a specialised variant");
     static bool attr_set[64] = {false};
     if (!attr_set[slot]) {
         IRB_CHECK_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -1188,9 +1212,14 @@ int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, cons
         IRB_REQUIRE(N % 4 == 0, "tc_conv3x3: PixelShuffle needs N % 4 == 0");
         Epi e0 = epi;
         e0.ps = 0;
-        if (can_tma_store(e0) && BW >= 32 && (N / 4) % 64 == 0 && epi.res == nullptr) {
+        // 64-column blocks must not straddle sub-pixels: N/4 a multiple of 64, or of 48 with 48-column blocks (the
+        // store box stays 64 wide; the map's channel extent N/4 clips columns 48..63 when N/4 == 48, and for
+        // N/4 == 96 the second block of a sub-pixel starts at channel 48 and is clipped at 96)
+        const int cout = N / 4;
+        const int bc = cout % 64 == 0 ? 64 : ((cout % 48 == 0 && p.BN % 48 == 0 && gemm_spec_on() && epi.act == ACT_NONE) ? 48 : 0);
+        if (can_tma_store(e0) && BW >= 32 && bc != 0 && epi.res == nullptr) {
             p.tma_store = 1;
-            const int cout = N / 4;
+            p.blk_cols = bc;
             uint64_t dims[5] = {uint64_t(cout), 2, uint64_t(W), uint64_t(2 * H), uint64_t(Nimg)};
             uint64_t str[4] = {uint64_t(epi.ldo) * 2, uint64_t(epi.ldo) * 4, uint64_t(epi.ldo) * 2 * 2 * W,
                                uint64_t(epi.ldo) * 2 * 2 * W * 2 * H};

@@ -175,7 +175,7 @@ int Restormer::load_conv(const Blob& blob, const std::string& name, int N, int C
     o.N = N;
     o.C = C;
     o.ps = pixelshuffle ? 1 : 0;
-    if (pixelshuffle && N % 4 == 0 && (N / 4) % 64 == 0) {
+    if (pixelshuffle && N % 4 == 0 && ((N / 4) % 64 == 0 || (N / 4) % 48 == 0)) {
         permute_rows_ps_major(w, N, 9 * o.kpad, nullptr);
         o.ps = 3;
     }

@@ -201,7 +201,7 @@ int SwinIR::load_conv(const Blob& blob, const std::string& name, int N, int Cin,
     o.N = N;
     o.C = Cin;
     o.ps = pixelshuffle ? 1 : 0;
-    if (pixelshuffle && N % 4 == 0 && (N / 4) % 64 == 0) {
+    if (pixelshuffle && N % 4 == 0 && ((N / 4) % 64 == 0 || (N / 4) % 48 == 0)) {
         permute_rows_ps_major(w, N, 9 * o.kpad, &bias);
         o.ps = 3;
     }
