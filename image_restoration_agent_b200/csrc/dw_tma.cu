@@ -14,6 +14,7 @@
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
+#include <stdlib.h>
 
 namespace irb {
 
@@ -40,11 +41,11 @@ struct alignas(64) DwParams {
 // multiple of `chunks`, so at any moment the CTAs cover ALL chunks of one neighbourhood of tiles: DRAM rows are
 // consumed whole and halo re-reads hit L2. The producer decodes the tile once and hands (img, ty, tx) to the
 // consumers through the stage's shared-memory slot, so the 16 consumer warps do no integer division.
-template <bool GATE>
+template <int GATE>  // 0: plain; 1: GELU gate, sigmoid form (ex2 + rcp); 2: GELU gate, tanh form (MUFU.TANH)
 __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_constant__ DwParams p) {
-    constexpr int NS = GATE ? 2 : 1;
+    constexpr int NS = GATE != 0 ? 2 : 1;
     constexpr int stage_bytes = NS * kDwStreamBytes;
-    constexpr int kDwStages = GATE ? kDwStagesGate : kDwStagesPlain;
+    constexpr int kDwStages = GATE != 0 ? kDwStagesGate : kDwStagesPlain;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + kDwStages * stage_bytes);
@@ -79,7 +80,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_c
                 uint8_t* dst = smem + s * stage_bytes;
                 mbar_arrive_expect_tx(&full[s], stage_bytes);
                 tma_load_4d(dst, &p.tm, &full[s], chunk * kDwCh, tx * kDwTW - 1, ty * kDwTH - 1, img);
-                if (GATE)
+                if (GATE != 0)
                     tma_load_4d(dst + kDwStreamBytes, &p.tm, &full[s], p.hp_off + chunk * kDwCh, tx * kDwTW - 1,
                                 ty * kDwTH - 1, img);
             }
@@ -150,7 +151,8 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_c
 #pragma unroll
                 for (int px = 0; px < 2; ++px) {
                     f32x2 o = acc[sl][px][0];
-                    if (GATE) o = mul2(gelu2_fast(o), acc[sl][px][NS - 1]);
+                    if (GATE == 1) o = mul2(gelu2_fast(o), acc[sl][px][NS - 1]);
+                    if (GATE == 2) o = mul2(gelu2_tanh(o), acc[sl][px][NS - 1]);
                     float o0, o1;
                     unpack2(o, o0, o1);
                     pk[px] = pack_bf16x2(o0, o1);
@@ -205,14 +207,24 @@ static int dw_tma_launch(bool gate, const bf16* x, long long ldx, int Ctot, bf16
     const size_t smem = size_t(nst) * (gate ? 2 : 1) * kDwStreamBytes + 128 + nst * 32;
     static bool attr_set = false;
     if (!attr_set) {
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        IRB_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        IRB_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        IRB_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_set = true;
     }
-    if (gate)
-        dw3x3_tma_kernel<true><<<grid, kDwThreads, smem, stream>>>(p);
+    static int gelu_tanh = -1;
+    if (gelu_tanh < 0) {
+        // measured equal to the sigmoid form here (6.07 vs 6.06 ms on cfg2: this kernel is not SFU-bound), so the
+        // default stays the more accurate sigmoid form
+        const char* e = getenv("IRB_DW_GELU_TANH");
+        gelu_tanh = e ? atoi(e) : 0;
+    }
+    if (gate && gelu_tanh)
+        dw3x3_tma_kernel<2><<<grid, kDwThreads, smem, stream>>>(p);
+    else if (gate)
+        dw3x3_tma_kernel<1><<<grid, kDwThreads, smem, stream>>>(p);
     else
-        dw3x3_tma_kernel<false><<<grid, kDwThreads, smem, stream>>>(p);
+        dw3x3_tma_kernel<0><<<grid, kDwThreads, smem, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
     const double px = double(Nimg) * H * W, cin = gate ? 2.0 * Cout : double(Cout);
     prof_mark(gate ? "dw3x3_gate_tma" : "dw3x3_tma", Cout, 2, 18.0 * px * cin, px * (cin + Cout) * 2 + 36.0 * cin, stream);

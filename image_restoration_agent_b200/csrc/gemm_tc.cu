@@ -55,6 +55,7 @@ struct alignas(64) TcGemmParams {
     Epi epi;
 };
 
+static constexpr int kActGeluTanh = 3;    // internal: ACT_GELU evaluated in its tanh form (bf16 outputs, see ptx.cuh)
 static constexpr int kGemmThreads = 320;  // warp 0: TMA, warp 1: MMA, warps 2..9: epilogue
 
 // Lean epilogue math for 16 columns of one row: the per-column vectors come from shared memory (staged once
@@ -156,6 +157,9 @@ __device__ __forceinline__ void epi_group16(const uint32_t* acc, const float* sb
         if (ACT == ACT_GELU) {
             x0 = gelu2(x0);
             x1 = gelu2(x1);
+        } else if (ACT == kActGeluTanh) {
+            x0 = gelu2_tanh(x0);
+            x1 = gelu2_tanh(x1);
         } else if (ACT == ACT_LRELU) {
             float t0, t1, t2, t3;
             unpack2(x0, t0, t1);
@@ -192,6 +196,10 @@ __device__ __forceinline__ void epi_group16_ragged(const uint32_t* acc, int nval
         if (LN == 1) y = fmaf(y, fa, sb[j]);
         if (LN == 2) y = fmaf(y, fa, fmaf(fb, scs[j], sb[j]));
         if (ACT == ACT_GELU) y = gelu_as(y);
+        if (ACT == kActGeluTanh) {
+            const float hy = 0.5f * y;
+            y = fmaf(hy, tanh_approx(y * fmaf(y * y, 0.7978845608f * 0.044715f, 0.7978845608f)), hy);
+        }
         if (ACT == ACT_LRELU) y = y > 0.f ? y : y * slope;
         if (j < nvalid) {
             if (RES) y += __bfloat162float(res[j]);
@@ -1013,7 +1021,7 @@ static int gemm_spec_on() {  // IRB_GEMM_SPEC=0: generic kernel only (diagnosis)
 #define IRB_GEMM_VARIANTS(X)                                                                                    \
     X(0, 0, 0, 0) X(0, 1, 0, 0) X(0, 2, 0, 0) X(0, 0, 1, 0) X(0, 1, 1, 0) X(0, 2, 1, 0) X(0, 0, 2, 0) X(0, 1, 2, 0) \
     X(0, 2, 2, 0) X(1, 0, 0, 0) X(1, 1, 0, 0) X(1, 2, 0, 0) X(2, 0, 0, 0) X(2, 1, 0, 0) X(0, 0, 1, 1) X(0, 1, 1, 1) \
-    X(0, 0, 2, 1) X(0, 1, 2, 1)
+    X(0, 0, 2, 1) X(0, 1, 2, 1) X(3, 0, 0, 0) X(3, 1, 0, 0) X(3, 2, 0, 0)
 
 static GemmKernelFn pick_gemm_kernel(int& var, int* slot) {
     int i = 1;
@@ -1088,7 +1096,13 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     if (spec_on && p.tma_store && (p.epi.res == nullptr || res_bf16)) {
         const int ln = p.epi.ln_colsum ? 2 : ((p.epi.ln_stats || p.epi.bias) ? 1 : 0);
         const int res = p.epi.res == nullptr ? 0 : (p.res_tma ? 2 : 1);
-        var = p.epi.act | (ln << 2) | (res << 4) | (p.epi.stats_out ? 64 : 0);
+        static int gelu_tanh = -1;
+        if (gelu_tanh < 0) {
+            const char* e = getenv("IRB_GELU_TANH");
+            gelu_tanh = e ? atoi(e) : 1;
+        }
+        const int act = (p.epi.act == ACT_GELU && gelu_tanh && p.epi.out_dt == DT_BF16) ? kActGeluTanh : p.epi.act;
+        var = act | (ln << 2) | (res << 4) | (p.epi.stats_out ? 64 : 0);
     }
     int slot = 0;
     GemmKernelFn fn = pick_gemm_kernel(var, &slot);

@@ -308,6 +308,24 @@ __device__ __forceinline__ f32x2 gelu2_fast(f32x2 x) {
     return mul2(x, pack2(rcp_approx(d0), rcp_approx(d1)));
 }
 
+// GELU in its tanh form 0.5 x (1 + tanh(k0 x + k1 x^3)) with the hardware tanh (MUFU.TANH, one SFU op per element
+// instead of the ex2 + rcp of the sigmoid form): 5 packed FP32-pipe instructions + 2 MUFU per channel pair. The tanh
+// form differs from the erf form by <= 4.8e-4, tanh.approx adds <= 2^-11 * |x| / 2: both below the bf16 rounding of
+// the value stored next. bf16 product mode only; the fp32 verification mode keeps the erf form.
+__device__ __forceinline__ float tanh_approx(float x) {
+    float r;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ f32x2 gelu2_tanh(f32x2 x) {
+    const f32x2 u = mul2(x, fma2(mul2(x, x), splat2(0.7978845608f * 0.044715f), splat2(0.7978845608f)));
+    float u0, u1;
+    unpack2(u, u0, u1);
+    const f32x2 t = pack2(tanh_approx(u0), tanh_approx(u1));
+    const f32x2 hx = mul2(x, splat2(0.5f));
+    return fma2(hx, t, hx);
+}
+
 // UMMA instruction descriptor, kind::f16, A/B = bf16, D = fp32 (bit layout: cute/arch/mma_sm100_desc.hpp
 // InstrDescriptor: c_format [4,6), a_format [7,10), b_format [10,13), a_major 15, b_major 16, N>>3 [17,23),
 // M>>4 [24,29)).

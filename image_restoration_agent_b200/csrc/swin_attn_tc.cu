@@ -58,6 +58,9 @@ __device__ __forceinline__ long long wa_token_pixel(const WaParams& p, int unit,
     return valid ? ((long long)img * p.H + oy) * p.W + ox : 0;
 }
 
+// D2T: compile-time head_dim / 2 (15: SwinIR-M / -L, 16), or 0 = runtime. With a constant the output loop below is
+// fully unrolled and its index arithmetic folds into constants (it was 31 % of the kernel's stall samples).
+template <int D2T>
 __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(const WaParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -106,27 +109,38 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
     // TMEM columns: S of group g at g*128, O of group g at 256 + g*64
 
     if (warp >= 9) {
-        // ===================== loaders: thread = token row r =====================
-        const int r = threadIdx.x - 9 * 32;
-        const uint32_t row_off = r * 128;
-        const int sw = r & 7;
+        // ===================== loaders: warp lw owns token rows lw*32 .. +31 =====================
+        // 8 consecutive lanes fetch the 8 16-byte chunks of ONE row's 128-byte line (4 rows per instruction), so a
+        // warp-wide cp.async touches 4 cache lines instead of 32: the L1 tag stage handles one line per cycle, and
+        // with lane = row it was the bottleneck of the kernel (3072 tag cycles per stage).
+        const int lw = warp - 9;
+        const int c = lane & 7;
+        const int sub = lane >> 3;
         int cnt = 0;
         for (int u = blockIdx.x; u < p.units; u += gridDim.x) {
-            bool valid;
-            int my, mx;
-            const long long pix = wa_token_pixel(p, u, r, valid, my, mx);
-            const bf16* grow = p.qkv + pix * p.ld;
+            long long poff[8];
+            uint32_t vmask = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                bool valid;
+                int my, mx;
+                const long long pix = wa_token_pixel(p, u, lw * 32 + i * 4 + sub, valid, my, mx);
+                poff[i] = pix * p.ld + c * 8;
+                vmask |= valid ? (1u << i) : 0u;
+            }
             for (int hp = 0; hp < npairs; ++hp, ++cnt) {
                 const int s = cnt & 1;
                 if (lane == 0) mbar_wait(&bar[WB_EMPTY + s], ((cnt >> 1) & 1) ^ 1);
                 __syncwarp();
-                if (valid) {
-                    const uint32_t dst = smem_u32(stage_base + s * kWaStage) + row_off;
+                const uint32_t dst0 = smem_u32(stage_base + s * kWaStage) + lw * 32 * 128;
 #pragma unroll
-                    for (int t = 0; t < 3; ++t) {
-                        const bf16* src = grow + t * p.Cq + hp * 64;
+                for (int i = 0; i < 8; ++i) {
+                    if (vmask & (1u << i)) {
+                        const int rl = i * 4 + sub;  // row inside the warp's 32
+                        const uint32_t dst = dst0 + rl * 128 + ((c ^ (rl & 7)) << 4);
+                        const bf16* src = p.qkv + poff[i] + hp * 64;
 #pragma unroll
-                        for (int c = 0; c < 8; ++c) cp_async16(dst + t * kWaTile + ((c ^ sw) << 4), src + c * 8);
+                        for (int t = 0; t < 3; ++t) cp_async16(dst + t * kWaTile, src + t * p.Cq);
                     }
                 }
                 cp_async_commit();
@@ -189,7 +203,7 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
         const int r = q * 32 + lane;             // token row of the unit
         const int win = r >> 6;
         const int yi = (r & 63) >> 3, xi = r & 7;
-        const int d2 = p.d >> 1;                 // output words (bf16 pairs) per head
+        const int d2 = D2T > 0 ? D2T : (p.d >> 1);  // output words (bf16 pairs) per head
         const int tstride = d2 | 1;              // odd stride: conflict-free transpose
         uint32_t* tb = tbuf + (warp - 1) * 32 * 17;
         uint8_t* prow = p_base + g * kWaPBytes + win * kWaTile + r * 128;
@@ -270,12 +284,29 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                             pack_bf16x2(__uint_as_float(orr[2 * k]) * inv, __uint_as_float(orr[2 * k + 1]) * inv);
                 __syncwarp();
                 // coalesced: consecutive lanes write consecutive words of a token's head slice
-                const int nwords = 32 * d2;
-                for (int wi = lane; wi < nwords; wi += 32) {
-                    const int row = wi / d2, k = wi - row * d2;
-                    const uint32_t v = tb[row * tstride + k];
-                    const long long ob = __shfl_sync(0xffffffffu, orow, row);
-                    if (ob >= 0) out32[ob + h * d2 + k] = v;
+                if (D2T > 0) {
+                    uint32_t v[D2T > 0 ? D2T : 1];
+                    int rows[D2T > 0 ? D2T : 1];
+#pragma unroll
+                    for (int it = 0; it < D2T; ++it) {
+                        const int wi = lane + 32 * it;
+                        rows[it] = wi / D2T;
+                        v[it] = tb[rows[it] * tstride + (wi - rows[it] * D2T)];
+                    }
+#pragma unroll
+                    for (int it = 0; it < D2T; ++it) {
+                        const int wi = lane + 32 * it;
+                        const long long ob = __shfl_sync(0xffffffffu, orow, rows[it]);
+                        if (ob >= 0) out32[ob + h * D2T + (wi - rows[it] * D2T)] = v[it];
+                    }
+                } else {
+                    const int nwords = 32 * d2;
+                    for (int wi = lane; wi < nwords; wi += 32) {
+                        const int row = wi / d2, k = wi - row * d2;
+                        const uint32_t v = tb[row * tstride + k];
+                        const long long ob = __shfl_sync(0xffffffffu, orow, row);
+                        if (ob >= 0) out32[ob + h * d2 + k] = v;
+                    }
                 }
                 __syncwarp();
             }
@@ -324,10 +355,17 @@ int window_attention_tc(const bf16* qkv, long long ld, bf16* out, long long ldo,
                         ((heads * 225 + 3) & ~3) * 4 + WB_COUNT * 8 + 64;
     static bool attr_set = false;
     if (!attr_set) {
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(window_attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        IRB_CHECK_CUDA(cudaFuncSetAttribute(window_attention_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        IRB_CHECK_CUDA(cudaFuncSetAttribute(window_attention_tc_kernel<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        IRB_CHECK_CUDA(cudaFuncSetAttribute(window_attention_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set = true;
     }
-    window_attention_tc_kernel<<<grid, kWaThreads, smem, stream>>>(p);
+    if (p.d == 30)
+        window_attention_tc_kernel<15><<<grid, kWaThreads, smem, stream>>>(p);
+    else if (p.d == 32)
+        window_attention_tc_kernel<16><<<grid, kWaThreads, smem, stream>>>(p);
+    else
+        window_attention_tc_kernel<0><<<grid, kWaThreads, smem, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
     const double px = double(n) * H * W;
     prof_mark("window_attention_tc", C, shift, 4.0 * px * 64 * C, px * (3.0 * p.Cq + C) * 2, stream);
