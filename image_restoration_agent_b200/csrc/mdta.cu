@@ -14,12 +14,15 @@
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
+#include <stdlib.h>
 
 namespace irb {
 
 static constexpr int kGramKP = 64;             // pixels per pipeline stage
 static constexpr int kGramBox = kGramKP * 128; // bytes of one [64 ch x KP px] box
-static constexpr int kGramStageBytes = 4 * kGramBox;  // q: 2 boxes (M = 128 rows), k: 2 boxes
+// A stage holds nbox 64-channel boxes of q and of k: 2 + 2 for heads wider than 64 channels, 1 + 1 otherwise (the UMMA
+// still runs at M = 128: its rows 64..127 alias rows 0..63 through a zero leading-dimension offset and are ignored),
+// which halves the shared-memory fill traffic of the 48-channel heads and lets 2-3 CTAs share an SM.
 
 // Pixel chunks per image: about 2048 pixels each, at most 32 slots. A function of P ONLY, so that the summation
 // order (hence every output bit) does not depend on how many tiles are batched into one launch.
@@ -43,6 +46,7 @@ struct alignas(64) GramParams {
     int ncols;        // UMMA N (c rounded up to 16)
     int acc_stride;   // TMEM columns between the three accumulators (ncols rounded up to 32)
     int stages;
+    int nbox;         // 64-channel boxes per operand and stage: 1 (c <= 64) or 2
     int tmem_cols;
     float* Gpart;     // [Nimg][heads][nchunks][c][c]
     float* ssq_part;  // [Nimg][heads][nchunks][2][c]
@@ -51,7 +55,8 @@ struct alignas(64) GramParams {
 __global__ void __launch_bounds__(192) mdta_gram_tc_kernel(const __grid_constant__ GramParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.stages * kGramStageBytes);
+    const int stage_bytes = 2 * p.nbox * kGramBox;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.stages * stage_bytes);
     uint64_t* empty_bar = full_bar + p.stages;
     uint64_t* accum_bar = empty_bar + p.stages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
@@ -87,13 +92,13 @@ __global__ void __launch_bounds__(192) mdta_gram_tc_kernel(const __grid_constant
             const int s = it % p.stages;
             const uint32_t ph = (it / p.stages) & 1;
             mbar_wait(&empty_bar[s], ph ^ 1);
-            uint8_t* sa = smem + s * kGramStageBytes;
-            mbar_arrive_expect_tx(&full_bar[s], kGramStageBytes);
+            uint8_t* sa = smem + s * stage_bytes;
+            mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
             const int pp = px0 + it * kGramKP;  // pixels >= P are zero-filled by TMA: they add nothing
             tma_load_3d(sa, &p.tm, &full_bar[s], qc, pp, img);
-            tma_load_3d(sa + kGramBox, &p.tm, &full_bar[s], qc + 64, pp, img);
-            tma_load_3d(sa + 2 * kGramBox, &p.tm, &full_bar[s], kc, pp, img);
-            tma_load_3d(sa + 3 * kGramBox, &p.tm, &full_bar[s], kc + 64, pp, img);
+            if (p.nbox == 2) tma_load_3d(sa + kGramBox, &p.tm, &full_bar[s], qc + 64, pp, img);
+            tma_load_3d(sa + p.nbox * kGramBox, &p.tm, &full_bar[s], kc, pp, img);
+            if (p.nbox == 2) tma_load_3d(sa + 3 * kGramBox, &p.tm, &full_bar[s], kc + 64, pp, img);
         }
     } else if (warp == 1 && lane == 0) {
         const uint32_t idesc = make_idesc_bf16(128, p.ncols, 1, 1);  // both operands MN-major
@@ -102,13 +107,14 @@ __global__ void __launch_bounds__(192) mdta_gram_tc_kernel(const __grid_constant
             const uint32_t ph = (it / p.stages) & 1;
             mbar_wait(&full_bar[s], ph);
             tc_fence_after();
-            const uint32_t q_addr = smem_u32(smem + s * kGramStageBytes);
-            const uint32_t k_addr = q_addr + 2 * kGramBox;
+            const uint32_t q_addr = smem_u32(smem + s * stage_bytes);
+            const uint32_t k_addr = q_addr + p.nbox * kGramBox;
+            const uint32_t lbo = p.nbox == 2 ? kGramBox : 0;
 #pragma unroll
             for (int k = 0; k < kGramKP / 16; ++k) {
                 // 16 pixels = two 8-pixel groups (SBO = 1024 B apart); next 64 channels are one box (LBO) away
-                const uint64_t qd = make_sdesc_sw128(q_addr + k * 2048, kGramBox, 1024);
-                const uint64_t kd = make_sdesc_sw128(k_addr + k * 2048, kGramBox, 1024);
+                const uint64_t qd = make_sdesc_sw128(q_addr + k * 2048, lbo, 1024);
+                const uint64_t kd = make_sdesc_sw128(k_addr + k * 2048, lbo, 1024);
                 const uint32_t acc = (it | k) != 0 ? 1u : 0u;
                 umma_bf16(tmem_base, qd, kd, idesc, acc);                // q^T k
                 umma_bf16(tmem_base + p.acc_stride, qd, qd, idesc, acc);      // q^T q (diagonal = |q_i|^2)
@@ -183,10 +189,16 @@ int mdta_gram_tc(const bf16* qkv, long long ld, int Nimg, int P, int C, int head
     IRB_REQUIRE(p.tmem_cols <= 512, "mdta_gram_tc: head too wide for TMEM");
     p.chunk_px = chunk_px_for(P, nchunks);
     IRB_REQUIRE((P + p.chunk_px - 1) / p.chunk_px == nchunks, "mdta_gram_tc: nchunks must come from mdta_nchunks()");
+    static int nbox1 = -1;
+    if (nbox1 < 0) {
+        const char* e = getenv("IRB_GRAM_NBOX1");
+        nbox1 = e ? atoi(e) : 1;
+    }
+    p.nbox = (c <= 64 && nbox1) ? 1 : 2;
     p.stages = 4;
     p.Gpart = Gpart;
     p.ssq_part = ssq_part;
-    const size_t smem = size_t(p.stages) * kGramStageBytes + 1024 + 256;
+    const size_t smem = size_t(p.stages) * 2 * p.nbox * kGramBox + 1024 + 256;
     static bool attr_set = false;
     if (!attr_set) {
         IRB_CHECK_CUDA(cudaFuncSetAttribute(mdta_gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

@@ -128,6 +128,20 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                 poff[i] = pix * p.ld + c * 8;
                 vmask |= valid ? (1u << i) : 0u;
             }
+            // The two-stage ring covers one head pair of look-ahead, less than the DRAM latency under load: pull the
+            // rows of this CTA's NEXT unit (all heads: 3 * Cq bf16 = whole 128-byte lines) into L2 now, a full unit
+            // (3 head pairs) ahead, so the cp.async gathers below only ever see L2 latency.
+            if (u + (int)gridDim.x < p.units) {
+                const int nlines = (3 * p.Cq) >> 6;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    bool valid;
+                    int my, mx;
+                    const long long pix = wa_token_pixel(p, u + gridDim.x, lw * 32 + i * 4 + sub, valid, my, mx);
+                    if (valid)
+                        for (int l = c; l < nlines; l += 8) prefetch_l2(p.qkv + pix * p.ld + l * 64);
+                }
+            }
             for (int hp = 0; hp < npairs; ++hp, ++cnt) {
                 const int s = cnt & 1;
                 if (lane == 0) mbar_wait(&bar[WB_EMPTY + s], ((cnt >> 1) & 1) ^ 1);
