@@ -188,7 +188,7 @@ int irb_conv3x3(const void* d_x, int dtype, long long ldx, int n, int H, int W, 
     if (shuffle == 1) IRB_REQUIRE(N % 4 == 0, "irb_conv3x3: PixelShuffle needs N % 4 == 0");
     if (shuffle == 2) IRB_REQUIRE(H % 2 == 0 && W % 2 == 0, "irb_conv3x3: PixelUnshuffle needs even H, W");
     if (dtype == IRB_BF16)
-        return tc_conv3x3((const bf16*)d_x, ldx, n, H, W, C, (const bf16*)d_w, kpad, N, w_rows_total, e,
+        return conv3x3_bf16((const bf16*)d_x, ldx, n, H, W, C, (const bf16*)d_w, kpad, N, w_rows_total, e,
                           (cudaStream_t)stream);
     return simt_conv3x3(d_x, DT_F32, ldx, n, H, W, C, (const float*)d_w, kpad, N, e, (cudaStream_t)stream);
 }

@@ -1,0 +1,214 @@
+// 3x3 convolution (stride 1, zero pad 1) with a handful of output channels (N <= 4): the reconstruction convolutions
+// that end both networks (Restormer `output` 96 -> 3, restormer_arch.py:281; SwinIR `conv_last` 64 / 180 -> 3,
+// network_swinir.py:836-838), bf16 channels-last in, generic fused epilogue (bias, fp32 residual image, post scale /
+// shift, fp32 or bf16 out).
+//
+// Why not the tcgen05 implicit GEMM: with N = 3 the tensor core has nothing to do, and the implicit GEMM re-reads
+// the activation once per tap (9 x 128-pixel boxes per tile through L2): tc_conv3x3[64,3] ran at 0.09 of HBM peak.
+// This is a memory-bound stencil: the halo tile is staged ONCE in shared memory (16-byte chunks, pixel stride padded
+// to an odd number of chunks so that a quarter-warp of consecutive pixels hits distinct banks), every thread owns PX
+// pixels of one column and walks taps x 8-channel chunks with packed FFMA2; the weights are read as broadcast
+// 16-byte shared loads and shared by the thread's PX pixels.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "kernels.h"
+#include <stdlib.h>
+
+namespace irb {
+
+static constexpr int kCsTW = 32;       // tile width  (= lanes of a warp)
+static constexpr int kCsWarps = 4;     // rows of threads
+static constexpr int kCsThreads = kCsTW * kCsWarps;
+
+struct ConvSmallParams {
+    const bf16* x;
+    long long ldx;
+    const bf16* wt;  // [npad][9 * kpad], K index = tap * kpad + channel
+    int kpad;
+    int Nimg, H, W, C, N;
+    int nchunk;      // ceil(C / 8)
+    int pstride;     // shared-memory pixel stride in 16-byte units (odd)
+    int tiles_x, tiles_y;
+    Epi epi;
+};
+
+template <int PX, int NOUT>
+__global__ void __launch_bounds__(kCsThreads) conv3x3_small_n_kernel(const ConvSmallParams p) {
+    constexpr int TH = PX * kCsWarps;
+    extern __shared__ uint4 cs_smem[];
+    uint4* halo = cs_smem;                                             // [(TH+2)][(TW+2)][pstride]
+    float* wsm = reinterpret_cast<float*>(cs_smem + (TH + 2) * (kCsTW + 2) * p.pstride);  // [9][nchunk][NOUT][8]
+    const int tid = threadIdx.x;
+    const int img = blockIdx.z;
+    const int x0 = blockIdx.x * kCsTW, y0 = blockIdx.y * TH;
+
+    // ---- weights: bf16 [n][tap * kpad + c] -> fp32 [tap][chunk][n][8], zero for c >= C ----
+    const int wtotal = 9 * p.nchunk * NOUT * 8;
+    for (int i = tid; i < wtotal; i += kCsThreads) {
+        const int k = i & 7;
+        const int n = (i >> 3) % NOUT;
+        const int tc = (i >> 3) / NOUT;  // tap * nchunk + chunk
+        const int tap = tc / p.nchunk, ch = (tc - tap * p.nchunk) * 8 + k;
+        float v = 0.f;
+        if (ch < p.C && n < p.N) v = __bfloat162float(p.wt[(long long)n * 9 * p.kpad + tap * p.kpad + ch]);
+        wsm[i] = v;
+    }
+    // ---- halo tile: (TH+2) x (TW+2) pixels x nchunk chunks; out-of-image pixels and channels >= C are zero ----
+    const int hw = kCsTW + 2;
+    const int total = (TH + 2) * hw * p.nchunk;
+    for (int i = tid; i < total; i += kCsThreads) {
+        const int ck = i % p.nchunk;
+        const int px = i / p.nchunk;
+        const int hy = px / hw, hx = px - hy * hw;
+        const int gy = y0 + hy - 1, gx = x0 + hx - 1;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (gy >= 0 && gy < p.H && gx >= 0 && gx < p.W) {
+            const bf16* src = p.x + (((long long)img * p.H + gy) * p.W + gx) * p.ldx + ck * 8;
+            if (ck * 8 + 8 <= p.C) {
+                v = __ldg(reinterpret_cast<const uint4*>(src));
+            } else {  // ragged last chunk (C % 8 != 0): element-wise, the rest stays zero
+                bf16 t[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) t[k] = (ck * 8 + k < p.C) ? src[k] : __float2bfloat16(0.f);
+                v = *reinterpret_cast<const uint4*>(t);
+            }
+        }
+        halo[px * p.pstride + ck] = v;
+    }
+    __syncthreads();
+
+    const int tx = tid & 31, ty = tid >> 5;
+    f32x2 acc[PX][NOUT];
+#pragma unroll
+    for (int i = 0; i < PX; ++i)
+#pragma unroll
+        for (int n = 0; n < NOUT; ++n) acc[i][n] = 0ull;
+
+    const uint32_t halo_s = smem_u32(halo);
+    const uint32_t w_s = smem_u32(wsm);
+#pragma unroll 1
+    for (int tap = 0; tap < 9; ++tap) {
+        const int dy = tap / 3, dx = tap - dy * 3;  // halo offsets (already +1)
+        // pixel i of this thread: output row ty + i * kCsWarps
+        uint32_t pa[PX];
+#pragma unroll
+        for (int i = 0; i < PX; ++i) pa[i] = halo_s + (((ty + i * kCsWarps + dy) * hw + tx + dx) * p.pstride) * 16;
+        uint32_t wa = w_s + tap * p.nchunk * NOUT * 32;
+#pragma unroll 2
+        for (int ck = 0; ck < p.nchunk; ++ck) {
+            f32x2 w[NOUT][4];
+#pragma unroll
+            for (int n = 0; n < NOUT; ++n) {
+                lds_f32x4(wa + n * 32, w[n][0], w[n][1]);
+                lds_f32x4(wa + n * 32 + 16, w[n][2], w[n][3]);
+            }
+            wa += NOUT * 32;
+#pragma unroll
+            for (int i = 0; i < PX; ++i) {
+                const uint4 d = lds_v4(pa[i] + ck * 16);
+                const f32x2 x0v = bf16x2_to_f32x2_alu(d.x), x1v = bf16x2_to_f32x2_alu(d.y);
+                const f32x2 x2v = bf16x2_to_f32x2_alu(d.z), x3v = bf16x2_to_f32x2_alu(d.w);
+#pragma unroll
+                for (int n = 0; n < NOUT; ++n) {
+                    ffma2(acc[i][n], x0v, w[n][0]);
+                    ffma2(acc[i][n], x1v, w[n][1]);
+                    ffma2(acc[i][n], x2v, w[n][2]);
+                    ffma2(acc[i][n], x3v, w[n][3]);
+                }
+            }
+        }
+    }
+    const int gx = x0 + tx;
+#pragma unroll
+    for (int i = 0; i < PX; ++i) {
+        const int gy = y0 + ty + i * kCsWarps;
+        if (gx < p.W && gy < p.H) {
+            float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int n = 0; n < NOUT; ++n) {
+                float lo, hi;
+                unpack2(acc[i][n], lo, hi);
+                v[n] = lo + hi;
+            }
+            const long long row = ((long long)img * p.H + gy) * p.W + gx;
+            epi_apply_store<4>(p.epi, row, 0, p.N, v, img, gy, gx);
+        }
+    }
+}
+
+bool conv3x3_small_n_ok(int C, int N, const Epi& e) {
+    if (!(N >= 1 && N <= 4 && C >= 16 && C <= 256 && e.ps == 0 && e.ln_stats == nullptr && e.stats_out == nullptr))
+        return false;
+    const int nchunk = (C + 7) / 8, pstride = nchunk | 1;
+    const size_t smem = size_t(2 * kCsWarps + 2) * (kCsTW + 2) * pstride * 16 + size_t(9) * nchunk * 4 * 32;
+    return smem <= 200 * 1024;
+}
+
+template <int PX, int NOUT>
+static int launch_cs(const ConvSmallParams& p, size_t smem, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        IRB_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_small_n_kernel<PX, NOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set = true;
+    }
+    dim3 grid(p.tiles_x, p.tiles_y, p.Nimg);
+    conv3x3_small_n_kernel<PX, NOUT><<<grid, kCsThreads, smem, stream>>>(p);
+    IRB_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int conv3x3_small_n(const bf16* x, long long ldx, int Nimg, int H, int W, int C, const bf16* Wt, int kpad, int N,
+                    const Epi& epi, cudaStream_t stream) {
+    IRB_REQUIRE(conv3x3_small_n_ok(C, N, epi), "conv3x3_small_n: unsupported shape / epilogue");
+    IRB_REQUIRE(ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0, "conv3x3_small_n: rows must be 16-byte aligned");
+    IRB_REQUIRE(Nimg <= 65535, "conv3x3_small_n: too many images in one launch");
+    ConvSmallParams p{};
+    p.x = x;
+    p.ldx = ldx;
+    p.wt = Wt;
+    p.kpad = kpad;
+    p.Nimg = Nimg;
+    p.H = H;
+    p.W = W;
+    p.C = C;
+    p.N = N;
+    p.nchunk = (C + 7) / 8;
+    p.pstride = p.nchunk | 1;
+    p.epi = epi;
+    // 4 pixels per thread (16-row tiles) when two CTAs of that size still fit an SM, else 2 (8-row tiles)
+    const size_t wbytes = size_t(9) * p.nchunk * (N <= 1 ? 1 : (N <= 3 ? 3 : 4)) * 32;
+    const size_t smem4 = size_t(4 * kCsWarps + 2) * (kCsTW + 2) * p.pstride * 16 + wbytes;
+    const size_t smem2 = size_t(2 * kCsWarps + 2) * (kCsTW + 2) * p.pstride * 16 + wbytes;
+    const bool px4 = smem4 <= 100 * 1024 && H >= 16;
+    const int TH = px4 ? 16 : 8;
+    p.tiles_x = ceil_div(W, kCsTW);
+    p.tiles_y = ceil_div(H, TH);
+    const size_t smem = px4 ? smem4 : smem2;
+    int rc;
+    if (N <= 1)
+        rc = px4 ? launch_cs<4, 1>(p, smem, stream) : launch_cs<2, 1>(p, smem, stream);
+    else if (N <= 3)
+        rc = px4 ? launch_cs<4, 3>(p, smem, stream) : launch_cs<2, 3>(p, smem, stream);
+    else
+        rc = px4 ? launch_cs<4, 4>(p, smem, stream) : launch_cs<2, 4>(p, smem, stream);
+    IRB_TRY(rc);
+    const double rows = double(H) * W * Nimg;
+    prof_mark("conv3x3_small_n", C, N, 18.0 * rows * C * N, rows * C * 2 + 9.0 * N * C * 2 + epi_bytes(epi, rows, N), stream);
+    return 0;
+}
+
+// bf16 3x3 convolution: the stencil kernel above for N <= 4 outputs, the tcgen05 implicit GEMM otherwise
+// (IRB_CONV_SMALLN=0 forces the implicit GEMM; diagnosis).
+int conv3x3_bf16(const bf16* x, long long ldx, int Nimg, int H, int W, int C, const bf16* Wt, int kpad, int N,
+                 int w_rows_total, const Epi& epi, cudaStream_t stream) {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("IRB_CONV_SMALLN");
+        on = e ? atoi(e) : 1;
+    }
+    if (on && conv3x3_small_n_ok(C, N, epi) && ldx % 8 == 0 && Nimg <= 65535)
+        return conv3x3_small_n(x, ldx, Nimg, H, W, C, Wt, kpad, N, epi, stream);
+    return tc_conv3x3(x, ldx, Nimg, H, W, C, Wt, kpad, N, w_rows_total, epi, stream);
+}
+
+}  // namespace irb

@@ -19,6 +19,14 @@ int tc_gemm(const bf16* A, long long lda, int M, int K, int batch, long long a_b
 int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, const bf16* Wt, int kpad, int N,
                int w_rows_total, const Epi& epi, cudaStream_t stream);
 
+// ---- conv_small.cu : 3x3 convolutions with N <= 4 output channels as a shared-memory stencil (the reconstruction
+// convolutions at the end of both networks); conv3x3_bf16 picks between it and tc_conv3x3 ----
+bool conv3x3_small_n_ok(int C, int N, const Epi& epi);
+int conv3x3_small_n(const bf16* x, long long ldx, int Nimg, int H, int W, int C, const bf16* Wt, int kpad, int N,
+                    const Epi& epi, cudaStream_t stream);
+int conv3x3_bf16(const bf16* x, long long ldx, int Nimg, int H, int W, int C, const bf16* Wt, int kpad, int N,
+                 int w_rows_total, const Epi& epi, cudaStream_t stream);
+
 // ---- gemm_simt.cu : fp32 FMA path (fp32 precision mode, and tiny-channel convolutions) ------
 // A element type a_dt (DT_F32/DT_BF16); weights always float [Nrows, taps*kpad].
 int simt_gemm(const void* A, int a_dt, long long lda, int M, int K, int batch, long long a_batch_stride,

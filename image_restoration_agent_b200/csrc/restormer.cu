@@ -302,7 +302,7 @@ int Restormer::run_gemm(const void* A, long long lda, long long M, int K, const 
 int Restormer::run_conv(const ConvW& c, const void* x, int x_dt, long long ldx, int n, int H, int W, Epi e,
                         cudaStream_t s) {
     if (dt == DT_BF16 && x_dt == DT_BF16 && c.C >= 16)
-        return tc_conv3x3((const bf16*)x, ldx, n, H, W, c.C, (const bf16*)c.w, c.kpad, c.N, c.npad, e, s);
+        return conv3x3_bf16((const bf16*)x, ldx, n, H, W, c.C, (const bf16*)c.w, c.kpad, c.N, c.npad, e, s);
     IRB_REQUIRE(c.wf32 != nullptr, "Restormer: missing fp32 conv weights");
     return simt_conv3x3(x, x_dt, ldx, n, H, W, c.C, c.wf32, c.kpad, c.N, e, s);
 }

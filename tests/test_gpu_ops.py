@@ -70,7 +70,9 @@ def test_gemm_batched_per_image_weights_on_a_channel_slice(dt, tol):
 @pytest.mark.parametrize("dt,tol", DT)
 @pytest.mark.parametrize("n,H,W,Cin,N", [(2, 32, 32, 48, 24), (1, 24, 40, 96, 192), (2, 16, 16, 384, 768),
                                          (1, 40, 24, 180, 180), (1, 64, 64, 96, 3), (1, 33, 20, 64, 64),
-                                         (1, 8, 8, 60, 240), (1, 136, 8, 64, 256)])
+                                         (1, 8, 8, 60, 240), (1, 136, 8, 64, 256),
+                                         # N <= 4: the shared-memory stencil kernel (conv_small.cu), ragged tiles / chunks
+                                         (2, 37, 45, 180, 3), (1, 9, 70, 64, 1), (1, 20, 33, 64, 4), (3, 16, 32, 96, 2)])
 def test_conv3x3_implicit_gemm(dt, tol, n, H, W, Cin, N):
     from image_restoration_agent_b200 import ops
     Cp = (Cin + 7) // 8 * 8
