@@ -28,6 +28,7 @@ struct ConvSmallParams {
     int Nimg, H, W, C, N;
     int nchunk;      // ceil(C / 8)
     int pstride;     // shared-memory pixel stride in 16-byte units (odd)
+    uint32_t nchunk_magic;  // ceil(2^32 / nchunk)
     int tiles_x, tiles_y;
     Epi epi;
 };
@@ -43,38 +44,50 @@ __global__ void __launch_bounds__(kCsThreads) conv3x3_small_n_kernel(const ConvS
     const int x0 = blockIdx.x * kCsTW, y0 = blockIdx.y * TH;
 
     // ---- weights: bf16 [n][tap * kpad + c] -> fp32 [tap][chunk][n][8], zero for c >= C ----
-    const int wtotal = 9 * p.nchunk * NOUT * 8;
-    for (int i = tid; i < wtotal; i += kCsThreads) {
-        const int k = i & 7;
-        const int n = (i >> 3) % NOUT;
-        const int tc = (i >> 3) / NOUT;  // tap * nchunk + chunk
-        const int tap = tc / p.nchunk, ch = (tc - tap * p.nchunk) * 8 + k;
-        float v = 0.f;
-        if (ch < p.C && n < p.N) v = __bfloat162float(p.wt[(long long)n * 9 * p.kpad + tap * p.kpad + ch]);
-        wsm[i] = v;
+    // one item = (tap, chunk, n): a 16-byte bf16 vector of the packed weights -> 8 floats (kpad % 8 == 0)
+    const int witems = 9 * p.nchunk * NOUT;
+    for (int i = tid; i < witems; i += kCsThreads) {
+        const int n = i % NOUT;
+        const int tc = i / NOUT;  // tap * nchunk + chunk
+        const int tap = tc / p.nchunk, ck = tc - tap * p.nchunk;
+        uint4 u = make_uint4(0u, 0u, 0u, 0u);
+        if (n < p.N) u = __ldg(reinterpret_cast<const uint4*>(p.wt + (long long)n * 9 * p.kpad + tap * p.kpad + ck * 8));
+        float4 lo, hi;  // channels >= C are zero in the packed weights (pack_conv3x3 pads K with zeros)
+        unpack_bf16x2(u.x, lo.x, lo.y);
+        unpack_bf16x2(u.y, lo.z, lo.w);
+        unpack_bf16x2(u.z, hi.x, hi.y);
+        unpack_bf16x2(u.w, hi.z, hi.w);
+        reinterpret_cast<float4*>(wsm)[2 * i] = lo;
+        reinterpret_cast<float4*>(wsm)[2 * i + 1] = hi;
     }
     // ---- halo tile: (TH+2) x (TW+2) pixels x nchunk chunks; out-of-image pixels and channels >= C are zero ----
     const int hw = kCsTW + 2;
     const int total = (TH + 2) * hw * p.nchunk;
+    // cp.async: every thread's ~30 chunk copies are in flight together (a load -> store loop was one DRAM latency per
+    // iteration: 32 us per CTA, slower than the implicit GEMM it replaces)
+    const uint32_t halo_s0 = smem_u32(halo);
     for (int i = tid; i < total; i += kCsThreads) {
-        const int ck = i % p.nchunk;
-        const int px = i / p.nchunk;
+        const int px = int(__umulhi(uint32_t(i), p.nchunk_magic));  // i / nchunk (exact for i < 2^16)
+        const int ck = i - px * p.nchunk;
         const int hy = px / hw, hx = px - hy * hw;
         const int gy = y0 + hy - 1, gx = x0 + hx - 1;
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if (gy >= 0 && gy < p.H && gx >= 0 && gx < p.W) {
-            const bf16* src = p.x + (((long long)img * p.H + gy) * p.W + gx) * p.ldx + ck * 8;
-            if (ck * 8 + 8 <= p.C) {
-                v = __ldg(reinterpret_cast<const uint4*>(src));
-            } else {  // ragged last chunk (C % 8 != 0): element-wise, the rest stays zero
+        const bool inside = gy >= 0 && gy < p.H && gx >= 0 && gx < p.W;
+        const bf16* src = p.x + (((long long)img * p.H + gy) * p.W + gx) * p.ldx + ck * 8;
+        if (inside && ck * 8 + 8 <= p.C) {
+            cp_async16(halo_s0 + (px * p.pstride + ck) * 16, src);
+        } else {
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            if (inside) {  // ragged last chunk (C % 8 != 0): element-wise, the rest stays zero
                 bf16 t[8];
 #pragma unroll
                 for (int k = 0; k < 8; ++k) t[k] = (ck * 8 + k < p.C) ? src[k] : __float2bfloat16(0.f);
                 v = *reinterpret_cast<const uint4*>(t);
             }
+            halo[px * p.pstride + ck] = v;
         }
-        halo[px * p.pstride + ck] = v;
     }
+    cp_async_commit();
+    cp_async_wait<0>();
     __syncthreads();
 
     const int tx = tid & 31, ty = tid >> 5;
@@ -94,7 +107,7 @@ __global__ void __launch_bounds__(kCsThreads) conv3x3_small_n_kernel(const ConvS
 #pragma unroll
         for (int i = 0; i < PX; ++i) pa[i] = halo_s + (((ty + i * kCsWarps + dy) * hw + tx + dx) * p.pstride) * 16;
         uint32_t wa = w_s + tap * p.nchunk * NOUT * 32;
-#pragma unroll 2
+#pragma unroll 4
         for (int ck = 0; ck < p.nchunk; ++ck) {
             f32x2 w[NOUT][4];
 #pragma unroll
@@ -162,6 +175,7 @@ int conv3x3_small_n(const bf16* x, long long ldx, int Nimg, int H, int W, int C,
     IRB_REQUIRE(conv3x3_small_n_ok(C, N, epi), "conv3x3_small_n: unsupported shape / epilogue");
     IRB_REQUIRE(ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0, "conv3x3_small_n: rows must be 16-byte aligned");
     IRB_REQUIRE(Nimg <= 65535, "conv3x3_small_n: too many images in one launch");
+    IRB_REQUIRE(kpad % 8 == 0 && kpad >= (C + 7) / 8 * 8 && (reinterpret_cast<uintptr_t>(Wt) & 15) == 0, "conv3x3_small_n: packed weights must be 16-byte aligned, K padded to 8");
     ConvSmallParams p{};
     p.x = x;
     p.ldx = ldx;
@@ -174,6 +188,7 @@ int conv3x3_small_n(const bf16* x, long long ldx, int Nimg, int H, int W, int C,
     p.N = N;
     p.nchunk = (C + 7) / 8;
     p.pstride = p.nchunk | 1;
+    p.nchunk_magic = uint32_t(((1ull << 32) + p.nchunk - 1) / p.nchunk);
     p.epi = epi;
     // 4 pixels per thread (16-row tiles) when two CTAs of that size still fit an SM, else 2 (8-row tiles)
     const size_t wbytes = size_t(9) * p.nchunk * (N <= 1 ? 1 : (N <= 3 ? 3 : 4)) * 32;
