@@ -26,6 +26,12 @@ static constexpr int kWaStage = 3 * kWaTile;    // Q | K | V
 static constexpr int kWaStages = 2;
 static constexpr int kWaPBytes = 2 * kWaTile;   // P of one head: 2 k-tiles of [128 rows][64 keys]
 static constexpr float kLog2e = 1.4426950408889634f;
+// The (2w-1)^2 = 15 x 15 bias table sits in shared memory with a row stride of 24 words: a warp's 32 tokens are 4
+// rows x 8 columns of a window, their lookups for one key are 4 runs of 8 consecutive words whose starts are then
+// 0 / 24 / 16 / 8 mod 32: conflict-free (with the natural stride 15 every lookup was a 2-way bank conflict, and the
+// kernel is shared-memory-bandwidth bound: 64 lookups per token row and head).
+static constexpr int kWaTabStride = 24;
+static constexpr int kWaTabSize = 15 * kWaTabStride;
 
 struct WaParams {
     const bf16* qkv;
@@ -67,8 +73,8 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
     uint8_t* stage_base = smem;                                   // [stages][Q|K|V]
     uint8_t* p_base = smem + kWaStages * kWaStage;                // [2 groups][2 k-tiles][128][128 B]
     uint32_t* tbuf = reinterpret_cast<uint32_t*>(p_base + 2 * kWaPBytes);  // [8 warps][32 rows][<= 17 words] output transpose
-    float* s_table = reinterpret_cast<float*>(tbuf + 8 * 32 * 17);  // [heads][225] bias * log2(e)
-    uint64_t* bar = reinterpret_cast<uint64_t*>(s_table + ((p.heads * 225 + 3) & ~3));
+    float* s_table = reinterpret_cast<float*>(tbuf + 8 * 32 * 17);  // [heads][15][24] bias * log2(e)
+    uint64_t* bar = reinterpret_cast<uint64_t*>(s_table + ((p.heads * kWaTabSize + 3) & ~3));
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + WB_COUNT);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -78,8 +84,14 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
         uint4* z = reinterpret_cast<uint4*>(smem);
         const int n16 = (kWaStages * kWaStage + 2 * kWaPBytes) / 16;
         for (int i = threadIdx.x; i < n16; i += kWaThreads) z[i] = make_uint4(0u, 0u, 0u, 0u);
-        for (int i = threadIdx.x; i < p.heads * 225; i += kWaThreads) {
-            const int h = i / 225, e = i - h * 225;
+        for (int i = threadIdx.x; i < p.heads * kWaTabSize; i += kWaThreads) {
+            const int h = i / kWaTabSize, e2 = i - h * kWaTabSize;
+            const int ey = e2 / kWaTabStride, ex = e2 - ey * kWaTabStride;
+            if (ex >= 15) {
+                s_table[i] = 0.f;
+                continue;
+            }
+            const int e = ey * 15 + ex;
             s_table[i] = __ldg(p.bias_table + e * p.heads + h) * kLog2e;
         }
     }
@@ -171,43 +183,69 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
             const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);   // P K-major, V MN-major
             int my_pairs = 0;
             for (int u = blockIdx.x; u < p.units; u += gridDim.x) my_pairs += npairs;
-            auto issue_s = [&](int cnt) {
-                const int s = cnt & 1;
-                mbar_wait(&bar[WB_FULL + s], (cnt >> 1) & 1);
-                tc_fence_after();
-                const uint32_t q_addr = smem_u32(stage_base + s * kWaStage);
-                const uint32_t k_addr = q_addr + kWaTile;
-                for (int g = 0; g < 2; ++g) {
-                    mbar_wait(&bar[WB_SEMPTY + g], (cnt & 1) ^ 1);
-                    tc_fence_after();
+            // Polling issue loop: S(cnt) needs its stage loaded and the group's S accumulator drained; P V(cnt) needs the
+            // group's P in shared memory and its O accumulator drained. Whichever is ready goes first: with blocking
+            // waits in program order, P V(cnt) sat behind the LOAD of cnt + 1 (which itself waits for P V(cnt - 1)),
+            // so every head pair paid a full gather latency.
+            int s_next = 0, pv_next = 0;
+            bool s_done[2] = {false, false}, pv_done[2] = {false, false};
+            bool s_loaded = false;
+            uint32_t spins = 0;
+            while (pv_next < my_pairs) {
+                bool progress = false;
+                if (s_next < my_pairs) {
+                    const int st = s_next & 1;
+                    if (!s_loaded && mbar_try_wait(&bar[WB_FULL + st], (s_next >> 1) & 1)) s_loaded = true;
+                    if (s_loaded) {
+                        const uint32_t q_addr = smem_u32(stage_base + st * kWaStage);
+                        const uint32_t k_addr = q_addr + kWaTile;
+                        for (int g = 0; g < 2; ++g) {
+                            if (s_done[g] || !mbar_try_wait(&bar[WB_SEMPTY + g], (s_next & 1) ^ 1)) continue;
+                            tc_fence_after();
 #pragma unroll
-                    for (int ks = 0; ks < 2; ++ks) {
-                        const uint64_t ad = make_sdesc_sw128(q_addr + g * 64 + ks * 32, 16, 1024);
-                        const uint64_t bd = make_sdesc_sw128(k_addr + g * 64 + ks * 32, 16, 1024);
-                        umma_bf16(tmem_base + g * 128, ad, bd, idesc_s, ks);
+                            for (int ks = 0; ks < 2; ++ks) {
+                                const uint64_t ad = make_sdesc_sw128(q_addr + g * 64 + ks * 32, 16, 1024);
+                                const uint64_t bd = make_sdesc_sw128(k_addr + g * 64 + ks * 32, 16, 1024);
+                                umma_bf16(tmem_base + g * 128, ad, bd, idesc_s, ks);
+                            }
+                            umma_commit(&bar[WB_SFULL + g]);
+                            s_done[g] = true;
+                            progress = true;
+                        }
+                        if (s_done[0] && s_done[1]) {
+                            s_done[0] = s_done[1] = false;
+                            s_loaded = false;
+                            ++s_next;
+                        }
                     }
-                    umma_commit(&bar[WB_SFULL + g]);
                 }
-            };
-            if (my_pairs > 0) issue_s(0);
-            for (int cnt = 0; cnt < my_pairs; ++cnt) {
-                if (cnt + 1 < my_pairs) issue_s(cnt + 1);
-                const int s = cnt & 1;
-                const uint32_t v_addr = smem_u32(stage_base + s * kWaStage) + 2 * kWaTile;
-                for (int g = 0; g < 2; ++g) {
-                    mbar_wait(&bar[WB_PFULL + g], cnt & 1);
-                    mbar_wait(&bar[WB_OEMPTY + g], (cnt & 1) ^ 1);
-                    tc_fence_after();
-                    const uint32_t pa = smem_u32(p_base + g * kWaPBytes);
+                if (pv_next < s_next) {
+                    const int st = pv_next & 1;
+                    const uint32_t v_addr = smem_u32(stage_base + st * kWaStage) + 2 * kWaTile;
+                    for (int g = 0; g < 2; ++g) {
+                        if (pv_done[g] || !mbar_try_wait(&bar[WB_PFULL + g], pv_next & 1) ||
+                            !mbar_try_wait(&bar[WB_OEMPTY + g], (pv_next & 1) ^ 1))
+                            continue;
+                        tc_fence_after();
+                        const uint32_t pa = smem_u32(p_base + g * kWaPBytes);
 #pragma unroll
-                    for (int ks = 0; ks < 8; ++ks) {
-                        const uint64_t ad = make_sdesc_sw128(pa + (ks >> 2) * kWaTile + (ks & 3) * 32, 16, 1024);
-                        const uint64_t bd = make_sdesc_sw128(v_addr + ks * 2048, kWaTile, 1024);
-                        umma_bf16(tmem_base + 256 + g * 64, ad, bd, idesc_o, ks);
+                        for (int ks = 0; ks < 8; ++ks) {
+                            const uint64_t ad = make_sdesc_sw128(pa + (ks >> 2) * kWaTile + (ks & 3) * 32, 16, 1024);
+                            const uint64_t bd = make_sdesc_sw128(v_addr + ks * 2048, kWaTile, 1024);
+                            umma_bf16(tmem_base + 256 + g * 64, ad, bd, idesc_o, ks);
+                        }
+                        umma_commit(&bar[WB_OFULL + g]);
+                        pv_done[g] = true;
+                        progress = true;
                     }
-                    umma_commit(&bar[WB_OFULL + g]);
+                    if (pv_done[0] && pv_done[1]) {
+                        umma_commit(&bar[WB_EMPTY + st]);  // Q, K, V of this stage are no longer read
+                        pv_done[0] = pv_done[1] = false;
+                        ++pv_next;
+                    }
                 }
-                umma_commit(&bar[WB_EMPTY + s]);  // Q, K, V of this stage are no longer read
+                if (progress) spins = 0;
+                else if (++spins > (1u << 26)) __trap();  // protocol bug: fail the launch instead of hanging
             }
         }
     } else {
@@ -225,105 +263,132 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
         const uint32_t lane_addr = uint32_t(q * 32) << 16;
         uint32_t* out32 = reinterpret_cast<uint32_t*>(p.out);
         const long long ldo2 = p.ldo >> 1;
-        int cnt = 0;
-        for (int u = blockIdx.x; u < p.units; u += gridDim.x) {
+        // Software pipeline over the CTA's (unit, head pair) sequence: P(cnt) is handed to the tensor core, then the
+        // softmax of cnt + 1 runs WHILE the P V product of cnt is in flight, and only then O(cnt) is drained. The
+        // S -> softmax -> P -> PV -> O chain of one head pair was fully serial before (ncu: the groups idled on the
+        // O barrier and the kernel sat at 0.3 of HBM with 35 % of the issue slots used).
+        const float NEG = -100.0f * kLog2e;
+        long long orow_s = -1;               // softmax-side unit state (cnt + 1 once the loop runs)
+        float m00 = 0.f, m01 = 0.f, m10 = 0.f, m11 = 0.f;
+        bool any_mask = false;
+        auto unit_info = [&](int u) {
             bool valid;
             int my, mx;
             const long long pix = wa_token_pixel(p, u, r, valid, my, mx);
-            const long long orow = valid ? pix * ldo2 : -1;
+            orow_s = valid ? pix * ldo2 : -1;
             // additive mask per key quadrant (yj >= 4, xj >= 4), in log2 units (network_swinir.py:216-237: the
             // region ids differ when the y parts or the x parts differ)
             const bool ylo = my == 2, yhi = my == 1, xlo = mx == 2, xhi = mx == 1;  // which key halves are masked
-            const float NEG = -100.0f * kLog2e;
-            const float m00 = (ylo || xlo) ? NEG : 0.f, m01 = (ylo || xhi) ? NEG : 0.f;
-            const float m10 = (yhi || xlo) ? NEG : 0.f, m11 = (yhi || xhi) ? NEG : 0.f;
-            const bool any_mask = __any_sync(0xffffffffu, (my | mx) != 0);
-            for (int hp = 0; hp < npairs; ++hp, ++cnt) {
-                const int h = hp * 2 + g;
-                const float* tab = s_table + h * 225 + (yi + 7) * 15 + xi + 7;
-                mbar_wait(&bar[WB_SFULL + g], cnt & 1);
-                tc_fence_after();
-                uint32_t sr[64];
-                tmem_ld32_nowait(tmem_base + lane_addr + g * 128 + win * 64, sr);
-                tmem_ld32_nowait(tmem_base + lane_addr + g * 128 + win * 64 + 32, sr + 32);
-                tmem_ld_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&bar[WB_SEMPTY + g]);
-                float t[64];
-                float mx_ = -INFINITY;
+            m00 = (ylo || xlo) ? NEG : 0.f;
+            m01 = (ylo || xhi) ? NEG : 0.f;
+            m10 = (yhi || xlo) ? NEG : 0.f;
+            m11 = (yhi || xhi) ? NEG : 0.f;
+            any_mask = __any_sync(0xffffffffu, (my | mx) != 0);
+        };
+        uint32_t pk[32];
+        float inv_s = 0.f;
+        // S(cnt) row from TMEM -> unnormalised probabilities (bf16 pairs) in pk, 1 / sum in inv_s
+        auto softmax_phase = [&](int cnt, int h) {
+            const float* tab = s_table + h * kWaTabSize + (yi + 7) * kWaTabStride + xi + 7;
+            mbar_wait(&bar[WB_SFULL + g], cnt & 1);
+            tc_fence_after();
+            uint32_t sr[64];
+            tmem_ld32_nowait(tmem_base + lane_addr + g * 128 + win * 64, sr);
+            tmem_ld32_nowait(tmem_base + lane_addr + g * 128 + win * 64 + 32, sr + 32);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar[WB_SEMPTY + g]);
+            float t[64];
+            float mx_ = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < 64; ++j) {
+                const int yj = j >> 3, xj = j & 7;
+                t[j] = fmaf(__uint_as_float(sr[j]), kLog2e, tab[-(yj * kWaTabStride + xj)]);
+            }
+            if (any_mask) {
 #pragma unroll
                 for (int j = 0; j < 64; ++j) {
                     const int yj = j >> 3, xj = j & 7;
-                    t[j] = fmaf(__uint_as_float(sr[j]), kLog2e, tab[-(yj * 15 + xj)]);
+                    t[j] += (yj >= 4) ? ((xj >= 4) ? m11 : m10) : ((xj >= 4) ? m01 : m00);
                 }
-                if (any_mask) {
-#pragma unroll
-                    for (int j = 0; j < 64; ++j) {
-                        const int yj = j >> 3, xj = j & 7;
-                        t[j] += (yj >= 4) ? ((xj >= 4) ? m11 : m10) : ((xj >= 4) ? m01 : m00);
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < 64; ++j) mx_ = fmaxf(mx_, t[j]);
-                float sum = 0.f;
-                uint32_t pk[32];
-#pragma unroll
-                for (int j = 0; j < 64; j += 2) {
-                    const float e0 = ex2_approx(t[j] - mx_), e1 = ex2_approx(t[j + 1] - mx_);
-                    sum += e0 + e1;
-                    pk[j >> 1] = pack_bf16x2(e0, e1);
-                }
-#pragma unroll
-                for (int c = 0; c < 8; ++c)
-                    *reinterpret_cast<uint4*>(prow + ((c ^ sw) << 4)) =
-                        make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
-                fence_proxy_async();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&bar[WB_PFULL + g]);
-                const float inv = 1.0f / sum;
-                // ---- O = P V / sum ----
-                mbar_wait(&bar[WB_OFULL + g], cnt & 1);
-                tc_fence_after();
-                uint32_t orr[32];
-                tmem_ld32_nowait(tmem_base + lane_addr + 256 + g * 64 + g * 32, orr);
-                tmem_ld_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&bar[WB_OEMPTY + g]);
-#pragma unroll
-                for (int k = 0; k < 16; ++k)
-                    if (k < d2)
-                        tb[lane * tstride + k] =
-                            pack_bf16x2(__uint_as_float(orr[2 * k]) * inv, __uint_as_float(orr[2 * k + 1]) * inv);
-                __syncwarp();
-                // coalesced: consecutive lanes write consecutive words of a token's head slice
-                if (D2T > 0) {
-                    uint32_t v[D2T > 0 ? D2T : 1];
-                    int rows[D2T > 0 ? D2T : 1];
-#pragma unroll
-                    for (int it = 0; it < D2T; ++it) {
-                        const int wi = lane + 32 * it;
-                        rows[it] = wi / D2T;
-                        v[it] = tb[rows[it] * tstride + (wi - rows[it] * D2T)];
-                    }
-#pragma unroll
-                    for (int it = 0; it < D2T; ++it) {
-                        const int wi = lane + 32 * it;
-                        const long long ob = __shfl_sync(0xffffffffu, orow, rows[it]);
-                        if (ob >= 0) out32[ob + h * D2T + (wi - rows[it] * D2T)] = v[it];
-                    }
-                } else {
-                    const int nwords = 32 * d2;
-                    for (int wi = lane; wi < nwords; wi += 32) {
-                        const int row = wi / d2, k = wi - row * d2;
-                        const uint32_t v = tb[row * tstride + k];
-                        const long long ob = __shfl_sync(0xffffffffu, orow, row);
-                        if (ob >= 0) out32[ob + h * d2 + k] = v;
-                    }
-                }
-                __syncwarp();
             }
+#pragma unroll
+            for (int j = 0; j < 64; ++j) mx_ = fmaxf(mx_, t[j]);
+            float sum = 0.f;
+#pragma unroll
+            for (int j = 0; j < 64; j += 2) {
+                const float e0 = ex2_approx(t[j] - mx_), e1 = ex2_approx(t[j + 1] - mx_);
+                sum += e0 + e1;
+                pk[j >> 1] = pack_bf16x2(e0, e1);
+            }
+            inv_s = 1.0f / sum;
+        };
+        int u_s = blockIdx.x, hp_s = 0;
+        if (u_s < p.units) {
+            unit_info(u_s);
+            softmax_phase(0, g);
+        }
+        for (int cnt = 0; u_s < p.units; ++cnt) {
+            // ---- P(cnt) -> shared memory (UMMA A layout) -> tensor core ----
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                *reinterpret_cast<uint4*>(prow + ((c ^ sw) << 4)) =
+                    make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar[WB_PFULL + g]);
+            const long long orow = orow_s;
+            const float inv = inv_s;
+            const int h = hp_s * 2 + g;
+            // ---- softmax of cnt + 1 while P V of cnt runs ----
+            if (++hp_s == npairs) {
+                hp_s = 0;
+                u_s += gridDim.x;
+                if (u_s < p.units) unit_info(u_s);
+            }
+            if (u_s < p.units) softmax_phase(cnt + 1, hp_s * 2 + g);
+            // ---- O(cnt) = P V / sum ----
+            mbar_wait(&bar[WB_OFULL + g], cnt & 1);
+            tc_fence_after();
+            uint32_t orr[32];
+            tmem_ld32_nowait(tmem_base + lane_addr + 256 + g * 64 + g * 32, orr);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar[WB_OEMPTY + g]);
+#pragma unroll
+            for (int k = 0; k < 16; ++k)
+                if (k < d2)
+                    tb[lane * tstride + k] =
+                        pack_bf16x2(__uint_as_float(orr[2 * k]) * inv, __uint_as_float(orr[2 * k + 1]) * inv);
+            __syncwarp();
+            // coalesced: consecutive lanes write consecutive words of a token's head slice
+            if (D2T > 0) {
+                uint32_t v[D2T > 0 ? D2T : 1];
+                int rows[D2T > 0 ? D2T : 1];
+#pragma unroll
+                for (int it = 0; it < D2T; ++it) {
+                    const int wi = lane + 32 * it;
+                    rows[it] = wi / D2T;
+                    v[it] = tb[rows[it] * tstride + (wi - rows[it] * D2T)];
+                }
+#pragma unroll
+                for (int it = 0; it < D2T; ++it) {
+                    const int wi = lane + 32 * it;
+                    const long long ob = __shfl_sync(0xffffffffu, orow, rows[it]);
+                    if (ob >= 0) out32[ob + h * D2T + (wi - rows[it] * D2T)] = v[it];
+                }
+            } else {
+                const int nwords = 32 * d2;
+                for (int wi = lane; wi < nwords; wi += 32) {
+                    const int row = wi / d2, k = wi - row * d2;
+                    const uint32_t v = tb[row * tstride + k];
+                    const long long ob = __shfl_sync(0xffffffffu, orow, row);
+                    if (ob >= 0) out32[ob + h * d2 + k] = v;
+                }
+            }
+            __syncwarp();
         }
     }
     tc_fence_before();
@@ -366,7 +431,7 @@ int window_attention_tc(const bf16* qkv, long long ld, bf16* out, long long ldo,
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int grid = p.units < sms ? p.units : sms;
     const size_t smem = 1024 + size_t(kWaStages) * kWaStage + 2 * kWaPBytes + 8 * 32 * 17 * 4 +
-                        ((heads * 225 + 3) & ~3) * 4 + WB_COUNT * 8 + 64;
+                        ((heads * kWaTabSize + 3) & ~3) * 4 + WB_COUNT * 8 + 64;
     static bool attr_set = false;
     if (!attr_set) {
         IRB_CHECK_CUDA(cudaFuncSetAttribute(window_attention_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
