@@ -965,6 +965,12 @@ static int pick_bn(int N) {
     // one tile when N fits; otherwise a multiple of 64 (the TMA-store block width) with the least padded work
     const int n16 = (N + 15) / 16 * 16;
     if (n16 <= 256) return n16;
+    static int force = -1;  // IRB_GEMM_BN: tile width for N > 256 (diagnosis)
+    if (force < 0) {
+        const char* e = getenv("IRB_GEMM_BN");
+        force = e ? atoi(e) : 0;
+    }
+    if (force >= 16 && force <= 256 && force % 16 == 0) return force;
     int best = 256, best_pad = ceil_div(N, 256) * 256;
     for (int bn : {192, 128}) {
         const int pad = ceil_div(N, bn) * bn;

@@ -355,28 +355,44 @@ __global__ void __launch_bounds__(256) mdta_softmax_kernel(const float* __restri
     }
 }
 
-// Kernel B: Weff[img][o][head*c + j] = sum_i Wp[o][head*c + i] * attn[img][head][i][j]; CTA = 16 rows o.
+// Kernel B: Weff[img][o][head*c + j] = sum_i Wp[o][head*c + i] * attn[img][head][i][j]; CTA = 64 rows o of one
+// (head, image): the c x c attention block is staged once per 64 rows (16 rows per CTA made the staging the whole
+// cost: 62 us for 340 MFLOP at level 4), each thread owns 4 rows x 1 column so that one attn load feeds 4 FMAs.
+// RPT rows per thread (16 * RPT rows per CTA): 4 when that still gives about two CTAs per SM, else 2 or 1.
+template <int RPT>
 __global__ void __launch_bounds__(256) mdta_weff_kernel(const float* __restrict__ attn, const float* __restrict__ Wp,
                                                         int C, int heads, void* __restrict__ Weff, int w_dt) {
-    extern __shared__ float sm[];  // attn [c][c] then Wp rows [16][c]
+    extern __shared__ float sm[];  // attn [c][c] then Wp rows [64][c + 1]
     const int c = C / heads;
     const int head = blockIdx.y, img = blockIdx.z;
-    const int o0 = blockIdx.x * 16;
+    constexpr int kWeffRows = 16 * RPT;
+    const int o0 = blockIdx.x * kWeffRows;
     float* s_attn = sm;
     float* s_w = sm + c * c;
+    const int wld = c + 1;  // odd-ish stride: the 4 rows of a thread and the row groups of a warp spread over banks
     const float* a = attn + ((long long)img * heads + head) * c * c;
     for (int e = threadIdx.x; e < c * c; e += 256) s_attn[e] = a[e];
-    for (int e = threadIdx.x; e < 16 * c; e += 256) {
-        const int r = e / c, i = e % c;
-        s_w[e] = (o0 + r < C) ? __ldg(Wp + (long long)(o0 + r) * C + head * c + i) : 0.f;
+    for (int e = threadIdx.x; e < kWeffRows * c; e += 256) {
+        const int r = e / c, i = e - r * c;
+        s_w[r * wld + i] = (o0 + r < C) ? __ldg(Wp + (long long)(o0 + r) * C + head * c + i) : 0.f;
     }
     __syncthreads();
     for (int e = threadIdx.x; e < 16 * c; e += 256) {
-        const int r = e / c, j = e % c;
-        if (o0 + r >= C) continue;
-        float acc = 0.f;
-        for (int i = 0; i < c; ++i) acc = fmaf(s_w[r * c + i], s_attn[i * c + j], acc);
-        st_from_float(Weff, ((long long)img * C + o0 + r) * C + head * c + j, w_dt, acc);
+        const int rq = e / c, j = e - rq * c;
+        float acc[RPT];
+#pragma unroll
+        for (int k = 0; k < RPT; ++k) acc[k] = 0.f;
+        const float* w0 = s_w + rq * wld;
+#pragma unroll 4
+        for (int i = 0; i < c; ++i) {
+            const float av = s_attn[i * c + j];
+#pragma unroll
+            for (int k = 0; k < RPT; ++k) acc[k] = fmaf(w0[k * 16 * wld + i], av, acc[k]);
+        }
+        const long long ob = ((long long)img * C + o0 + rq) * C + head * c + j;
+#pragma unroll
+        for (int k = 0; k < RPT; ++k)
+            if (o0 + rq + 16 * k < C) st_from_float(Weff, ob + (long long)(16 * k) * C, w_dt, acc[k]);
     }
 }
 
@@ -394,14 +410,23 @@ int mdta_softmax_weff(const float* Gpart, const float* ssq_part, int nchunks, co
         prof_mark("mdta_softmax", C, heads, 0.0, double(Nimg) * (nchunks * (C * c + 2.0 * C) + C * c) * 4.0, stream);
     }
     {
-        const size_t smem = (size_t(c) * c + 16 * c) * sizeof(float);
+        const long long per = (long long)heads * Nimg;
+        const int rpt = ceil_div(C, 64) * per >= 296 ? 4 : (ceil_div(C, 32) * per >= 296 ? 2 : 1);
+        const size_t smem = (size_t(c) * c + size_t(16 * rpt) * (c + 1)) * sizeof(float);
         static bool attr_set = false;
         if (!attr_set) {
-            IRB_CHECK_CUDA(cudaFuncSetAttribute(mdta_weff_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+            IRB_CHECK_CUDA(cudaFuncSetAttribute(mdta_weff_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+            IRB_CHECK_CUDA(cudaFuncSetAttribute(mdta_weff_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+            IRB_CHECK_CUDA(cudaFuncSetAttribute(mdta_weff_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
             attr_set = true;
         }
-        dim3 grid(ceil_div(C, 16), heads, Nimg);
-        mdta_weff_kernel<<<grid, 256, smem, stream>>>(attn, Wp, C, heads, Weff, w_dt);
+        dim3 grid(ceil_div(C, 16 * rpt), heads, Nimg);
+        if (rpt == 4)
+            mdta_weff_kernel<4><<<grid, 256, smem, stream>>>(attn, Wp, C, heads, Weff, w_dt);
+        else if (rpt == 2)
+            mdta_weff_kernel<2><<<grid, 256, smem, stream>>>(attn, Wp, C, heads, Weff, w_dt);
+        else
+            mdta_weff_kernel<1><<<grid, 256, smem, stream>>>(attn, Wp, C, heads, Weff, w_dt);
         IRB_CHECK_CUDA(cudaGetLastError());
         prof_mark("mdta_weff", C, heads, 2.0 * Nimg * C * C * c,
                   double(Nimg) * (C * c * 4.0 + C * C * (w_dt == DT_BF16 ? 2 : 4)) + C * C * 4.0, stream);
