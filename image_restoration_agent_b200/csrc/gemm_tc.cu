@@ -264,6 +264,44 @@ __device__ __forceinline__ int next_item(int w, const TcGemmParams& p) {
     return ((w + 1) % p.tiles_n) ? w + 1 : w + 1 + (gridDim.x - 1) * p.tiles_n;
 }
 
+// The same walk with the coordinates carried along: the single-thread producer / MMA loops and the epilogue warps paid
+// 8-12 integer divisions by run-time values per tile (each a ~30-instruction dependent chain: ~1 us per tile with
+// nothing else to do, measured with IRB_GEMM_DBG=224), now only additions and compares.
+struct TileIter {
+    int w, nt, mt, z;
+};
+__device__ __forceinline__ void tile_set(const TcGemmParams& p, TileIter& t, int w) {
+    t.w = w;
+    t.nt = w % p.tiles_n;
+    const int q = w / p.tiles_n;
+    t.z = q / p.tiles_m;
+    t.mt = q - t.z * p.tiles_m;
+}
+__device__ __forceinline__ void tile_first(const TcGemmParams& p, TileIter& t) { tile_set(p, t, first_item(p)); }
+__device__ __forceinline__ void tile_next(const TcGemmParams& p, TileIter& t) {
+    if (!p.m_outer) {
+        tile_set(p, t, t.w + gridDim.x);
+        return;
+    }
+    if (++t.nt < p.tiles_n) {
+        ++t.w;
+        return;
+    }
+    t.nt = 0;
+    t.w += 1 + (gridDim.x - 1) * p.tiles_n;
+    t.mt += gridDim.x;
+    if (t.mt >= p.tiles_m) {
+        if (t.mt - p.tiles_m < p.tiles_m) {
+            t.mt -= p.tiles_m;
+            ++t.z;
+        } else {
+            const int q = t.mt / p.tiles_m;
+            t.mt -= q * p.tiles_m;
+            t.z += q;
+        }
+    }
+}
+
 
 // ----------------------------------------------------------------------------------------------
 // Specialised epilogue (TMA-store path, no residual / bf16 residual). Every switch that selects the arithmetic is a
@@ -274,6 +312,13 @@ __device__ __forceinline__ int next_item(int w, const TcGemmParams& p) {
 //          its 16-byte chunks from the swizzled block, adds, writes the result back in place, and the same block
 //          goes out as the TMA store, so no residual latency sits in front of the math.
 // ----------------------------------------------------------------------------------------------
+// IRB_GEMM_DBG & 256: poll with mbarrier.test_wait instead of the suspending try_wait (handshake-latency diagnosis)
+#define GEMM_WAIT(bar, parity)                          \
+    do {                                                \
+        if (p.dbg & 256) mbar_wait_spin((bar), (parity)); \
+        else mbar_wait((bar), (parity));                \
+    } while (0)
+
 struct EpiCtx {
     uint32_t tmem_base;
     uint64_t* tfull_bar;
@@ -286,9 +331,9 @@ struct EpiCtx {
 };
 
 // rows of tile item w that this thread (row r of the tile) owns
-__device__ __forceinline__ void epi_row_of(const TcGemmParams& p, int w, int r, long long& grow, bool& valid) {
-    const int mt = (w / p.tiles_n) % p.tiles_m;
-    const int z = w / (p.tiles_n * p.tiles_m);
+__device__ __forceinline__ void epi_row_of(const TcGemmParams& p, const TileIter& ti, int r, long long& grow, bool& valid) {
+    const int mt = ti.mt;
+    const int z = ti.z;
     if (p.mode == 0) {
         const int m = mt * kTileM + r;
         valid = m < p.M;
@@ -301,12 +346,13 @@ __device__ __forceinline__ void epi_row_of(const TcGemmParams& p, int w, int r, 
     }
 }
 
-__device__ __forceinline__ float2 epi_load_stats(const TcGemmParams& p, int w, int r) {
+__device__ __forceinline__ float2 epi_load_stats(const TcGemmParams& p, const TileIter& ti, int r) {
+    const int w = ti.w;
     float2 st = make_float2(0.f, 1.f);
     if (w < p.total) {
         long long grow;
         bool valid;
-        epi_row_of(p, w, r, grow, valid);
+        epi_row_of(p, ti, r, grow, valid);
         if (valid) st = __ldg(p.epi.ln_stats + grow);
     }
     return st;
@@ -317,10 +363,12 @@ __device__ __forceinline__ float2 epi_load_stats(const TcGemmParams& p, int w, i
 template <int ACT, int LN, int RES, bool STATS, int NG>
 __device__ __forceinline__ void epi_block_full(uint32_t taddr_cb, const float* sb, const float* scs, f32x2 a2, f32x2 b2,
                                                float slope, const bf16* rrow_cb, uint32_t sx, bool first_blk,
-                                               f32x2& s1, f32x2& s2, float& shift, bool wait_read, int lane) {
-    uint32_t acc[NG][16];
-#pragma unroll
-    for (int gi = 0; gi < NG; ++gi) tmem_ld16_nowait(taddr_cb + gi * 16, acc[gi]);
+                                               f32x2& s1, f32x2& s2, float& shift, bool wait_read, int lane,
+                                               uint32_t (&accb)[2][16], bool preloaded, uint32_t next_taddr) {
+    // TMEM loads run one 16-column group ahead of the math (two register buffers): group gi + 1 is in flight while
+    // group gi is computed, and the block's last group fetches group 0 of the NEXT block of the tile (next_taddr != 0;
+    // NG even, so that it lands in buffer 0), which then enters with `preloaded`. Only the first load of a tile is exposed.
+    if (!preloaded) tmem_ld16_nowait(taddr_cb, accb[0]);
     uint4 rr[RES == 1 ? 2 * NG : 1];
     if (RES == 1) {
 #pragma unroll
@@ -333,9 +381,13 @@ __device__ __forceinline__ void epi_block_full(uint32_t taddr_cb, const float* s
     if (STATS && first_blk)  // x_old[row, 0]
         shift = __uint_as_float((RES == 2 ? lds_u32(sx) : rr[0].x) << 16);
     const f32x2 nshift2 = splat2(-shift);
-    tmem_ld_wait();
 #pragma unroll
     for (int gi = 0; gi < NG; ++gi) {
+        tmem_ld_wait();
+        if (gi + 1 < NG)
+            tmem_ld16_nowait(taddr_cb + (gi + 1) * 16, accb[(gi + 1) & 1]);
+        else if ((NG & 1) == 0 && next_taddr != 0)
+            tmem_ld16_nowait(next_taddr, accb[0]);
         uint32_t pk[8];
         uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
         if (RES == 1) {
@@ -345,8 +397,8 @@ __device__ __forceinline__ void epi_block_full(uint32_t taddr_cb, const float* s
             r0 = lds_v4(sx ^ ((2 * gi) << 4));
             r1 = lds_v4(sx ^ ((2 * gi + 1) << 4));
         }
-        epi_group16<ACT, LN, RES != 0, STATS>(acc[gi], sb + gi * 16, scs + gi * 16, a2, b2, slope, r0, r1, pk, s1, s2,
-                                              nshift2);
+        epi_group16<ACT, LN, RES != 0, STATS>(accb[gi & 1], sb + gi * 16, scs + gi * 16, a2, b2, slope, r0, r1, pk, s1,
+                                              s2, nshift2);
         sts_v4(sx ^ ((2 * gi) << 4), pk[0], pk[1], pk[2], pk[3]);
         sts_v4(sx ^ ((2 * gi + 1) << 4), pk[4], pk[5], pk[6], pk[7]);
     }
@@ -366,19 +418,24 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
     const float slope = p.epi.slope;
 
     // first tile of this warp set
-    int w = first_item(p);
-    if (set == 1) w = next_item(w, p);
+    TileIter ti;  // this set's current tile; tn = its next tile (two steps of the CTA's walk ahead)
+    tile_first(p, ti);
+    if (set == 1) tile_next(p, ti);
+    TileIter tn = ti;
+    tile_next(p, tn);
+    tile_next(p, tn);
     int t = set;
     // software pipeline: LayerNorm statistics of the NEXT tile's row are fetched while this tile is processed
     float2 st_next = make_float2(0.f, 1.f);
-    if (LN != 0 && p.epi.ln_stats) st_next = epi_load_stats(p, w, r);
+    if (LN != 0 && p.epi.ln_stats) st_next = epi_load_stats(p, ti, r);
 
-    // RES 2: residual prefetch iterator (pw, pblk), two blocks ahead of the consumer
-    int pw = w, pblk = 0;
+    // RES 2: residual prefetch iterator (tp, pblk), two blocks ahead of the consumer
+    TileIter tp = ti;
+    int pblk = 0;
     uint32_t nissued = 0;
     auto issue_res = [&]() {
-        if (pw >= p.total) return;
-        const int nt2 = pw % p.tiles_n, mt2 = (pw / p.tiles_n) % p.tiles_m, z2 = pw / (p.tiles_n * p.tiles_m);
+        if (tp.w >= p.total) return;
+        const int nt2 = tp.nt, mt2 = tp.mt, z2 = tp.z;
         const int col = nt2 * p.BN + pblk * bcols;
         const uint32_t b = nissued % 3;
         if (lane == 0) {
@@ -389,33 +446,38 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
         ++pblk;
         if (pblk >= nblk_max || nt2 * p.BN + pblk * bcols >= p.N) {
             pblk = 0;
-            pw = next_item(next_item(pw, p), p);
+            tile_next(p, tp);
+            tile_next(p, tp);
         }
     };
-    if (RES == 2) {
+    if (RES == 2 && !(p.dbg & 32)) {
         issue_res();
         issue_res();
     }
 
     uint32_t nb = 0;  // blocks consumed by this warp
-    for (; w < p.total; w = next_item(next_item(w, p), p), t += 2) {
-        const int nt = w % p.tiles_n;
-        const int mt = (w / p.tiles_n) % p.tiles_m;
-        const int z = w / (p.tiles_n * p.tiles_m);
+    for (; ti.w < p.total; t += 2) {
+        const int nt = ti.nt;
+        const int mt = ti.mt;
+        const int z = ti.z;
         const int n0 = nt * p.BN;
         const float* s_bias = c.s_bias_all + n0;
         const float* s_cs = c.s_cs_all + n0;
         long long grow;
         bool valid;
-        epi_row_of(p, w, r, grow, valid);
+        epi_row_of(p, ti, r, grow, valid);
+        const TileIter tcur = ti;  // (unused fields fold away) advance now: `continue` below must not skip it
+        ti = tn;
+        tile_next(p, tn);
+        tile_next(p, tn);
+        (void)tcur;
         if (RES == 1 && p.mode == 0) {  // pull the residual rows of the NEXT tile of this set into L2
-            const int w2 = next_item(next_item(w, p), p);
-            if (w2 < p.total) {
-                const int m2 = ((w2 / p.tiles_n) % p.tiles_m) * kTileM + r;
+            if (ti.w < p.total) {
+                const int m2 = ti.mt * kTileM + r;
                 if (m2 < p.M) {
                     const bf16* pr = reinterpret_cast<const bf16*>(p.epi.res) +
-                                     ((long long)(w2 / (p.tiles_n * p.tiles_m)) * p.M + m2) * p.epi.ldr + (w2 % p.tiles_n) * p.BN;
-                    const int nbytes = min(p.BN, p.N - (w2 % p.tiles_n) * p.BN) * 2;
+                                     ((long long)ti.z * p.M + m2) * p.epi.ldr + ti.nt * p.BN;
+                    const int nbytes = min(p.BN, p.N - ti.nt * p.BN) * 2;
                     for (int o = 0; o < nbytes; o += 128) prefetch_l2(reinterpret_cast<const uint8_t*>(pr) + o);
                     prefetch_l2(reinterpret_cast<const uint8_t*>(pr) + nbytes - 2);
                 }
@@ -425,16 +487,24 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
         if (LN != 0 && p.epi.ln_stats) {
             fa = st_next.y;
             fb = (LN == 2) ? -st_next.x * st_next.y : 0.f;
-            st_next = epi_load_stats(p, next_item(next_item(w, p), p), r);
+            st_next = epi_load_stats(p, ti, r);  // ti is already the next tile of this set
         }
         const f32x2 a2 = splat2(fa), b2 = splat2(fb);
         f32x2 st_s1 = 0ull, st_s2 = 0ull;
         float st_shift = 0.f;
         const bf16* rrow = reinterpret_cast<const bf16*>(p.epi.res) + (valid ? grow : 0) * p.epi.ldr + n0;
-        mbar_wait(&c.tfull_bar[set], (t >> 1) & 1);
+        GEMM_WAIT(&c.tfull_bar[set], (t >> 1) & 1);
         tc_fence_after();
         const uint32_t taddr = c.tmem_base + set * p.acc_stride + (uint32_t(q * 32) << 16);
+        if (p.dbg & 32) {  // diagnosis: no epilogue work at all (results are wrong on purpose)
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&c.tempty_bar[set]);
+            continue;
+        }
         const int ncols = min(p.BN, p.N - n0);  // valid columns of this tile
+        uint32_t accb[2][16];  // TMEM load double buffer (16 columns each)
+        bool pre = false;      // accb[0] already holds an in-flight load of this block's first group
         for (int blk = 0; blk < nblk_max; ++blk) {
             const int cb = blk * bcols;
             if (cb >= ncols) break;  // warp-uniform
@@ -442,23 +512,35 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
             const uint32_t bsel = (RES == 2) ? nb % 3 : nb & 1;
             const uint32_t stg = stg_warp + bsel * 4096;
             const uint32_t sx = stg + row_off;
-            if (RES == 2) mbar_wait(&rbar[bsel], (nb / 3) & 1);
+            if (RES == 2) GEMM_WAIT(&rbar[bsel], (nb / 3) & 1);
+            // does the next block of this tile take a pipelined path too (so that its first TMEM load can be issued
+            // from this block)?
+            const int nv_next = min(bcols, ncols - (cb + bcols));
+            const bool full_next = nv_next == 64 || nv_next == 32 || (nv_next == 48 && RES == 0);
+            const uint32_t next_t = full_next ? taddr + cb + bcols : 0u;
             if (nvalid == 64 && RES == 1) {  // register-held residual: two halves keep the live set under the cap
                 epi_block_full<ACT, LN, RES, STATS, 2>(taddr + cb, s_bias + cb, s_cs + cb, a2, b2, slope, rrow + cb, sx,
-                                                       blk == 0, st_s1, st_s2, st_shift, true, lane);
+                                                       blk == 0, st_s1, st_s2, st_shift, true, lane, accb, pre,
+                                                       taddr + cb + 32);
                 epi_block_full<ACT, LN, RES, STATS, 2>(taddr + cb + 32, s_bias + cb + 32, s_cs + cb + 32, a2, b2, slope,
-                                                       rrow + cb + 32, sx ^ 64u, false, st_s1, st_s2, st_shift, false, lane);
+                                                       rrow + cb + 32, sx ^ 64u, false, st_s1, st_s2, st_shift, false, lane,
+                                                       accb, true, next_t);
+                pre = full_next;
             } else if (nvalid == 64) {
                 epi_block_full<ACT, LN, RES, STATS, 4>(taddr + cb, s_bias + cb, s_cs + cb, a2, b2, slope, rrow + cb, sx,
-                                                       blk == 0, st_s1, st_s2, st_shift, RES != 2, lane);
+                                                       blk == 0, st_s1, st_s2, st_shift, RES != 2, lane, accb, pre, next_t);
+                pre = full_next;
             } else if (nvalid == 32) {
                 epi_block_full<ACT, LN, RES, STATS, 2>(taddr + cb, s_bias + cb, s_cs + cb, a2, b2, slope, rrow + cb, sx,
-                                                       blk == 0, st_s1, st_s2, st_shift, RES != 2, lane);
+                                                       blk == 0, st_s1, st_s2, st_shift, RES != 2, lane, accb, pre, next_t);
+                pre = full_next;
             } else if (nvalid == 48 && RES == 0) {
                 epi_block_full<ACT, LN, RES, STATS, 3>(taddr + cb, s_bias + cb, s_cs + cb, a2, b2, slope, rrow + cb, sx,
-                                                       blk == 0, st_s1, st_s2, st_shift, true, lane);
+                                                       blk == 0, st_s1, st_s2, st_shift, true, lane, accb, pre, 0u);
+                pre = false;
             } else {
                 // ragged block (N % 32 != 0): runtime group count, element-wise tail group
+                pre = false;
                 const int ng = min(4, (nvalid + 15) >> 4);
                 uint32_t acc[4][16];
 #pragma unroll
@@ -593,11 +675,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
 
     if (warp == 0 && lane == 0) {
         // ===== TMA producer =====
-        int it = 0, nb = 0, cur_z = -1;
-        for (int w = first_item(p); w < p.total; w = next_item(w, p)) {
-            const int nt = w % p.tiles_n;
-            const int mt = (w / p.tiles_n) % p.tiles_m;
-            const int z = w / (p.tiles_n * p.tiles_m);
+        int nb = 0, cur_z = -1;
+        int s = 0;         // ring slot and its phase, carried instead of it % stages, (it / stages) & 1
+        uint32_t ph = 0;
+        TileIter ti;
+        for (tile_first(p, ti); ti.w < p.total; tile_next(p, ti)) {
+            const int nt = ti.nt;
+            const int mt = ti.mt;
+            const int z = ti.z;
             const int n0 = nt * p.BN;
             if (p.b_resident && (cur_z < 0 || (p.b_rows_per_batch != 0 && z != cur_z))) {
                 // (re)load the whole weight matrix; a new batch index only after the MMAs of the old one are done
@@ -618,30 +703,39 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             for (int tap = 0; tap < p.taps; ++tap) {
                 const int dy = (p.taps == 9) ? tap / 3 - 1 : 0;
                 const int dx = (p.taps == 9) ? tap % 3 - 1 : 0;
-                for (int kc = 0; kc < p.ktiles; ++kc, ++it) {
-                    const int s = it % p.stages;
-                    const uint32_t ph = (it / p.stages) & 1;
-                    mbar_wait(&empty_bar[s], ph ^ 1);
+                for (int kc = 0; kc < p.ktiles; ++kc) {
+                    GEMM_WAIT(&empty_bar[s], ph ^ 1);
                     uint8_t* sa = ring + s * stage_bytes;
                     uint8_t* sb = sa + kABytes;
-                    mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
-                    if (p.mode == 0)
-                        tma_load_3d(sa, &p.tmA, &full_bar[s], kc * kTileK, mt * kTileM, z);
-                    else
-                        tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx, y0 + dy, z);
-                    if (!p.b_resident)
-                        tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK, z * p.b_rows_per_batch + n0);
+                    if (p.dbg & 128) {  // diagnosis: no operand loads
+                        mbar_arrive(&full_bar[s]);
+                    } else {
+                        mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
+                        if (p.mode == 0)
+                            tma_load_3d(sa, &p.tmA, &full_bar[s], kc * kTileK, mt * kTileM, z);
+                        else
+                            tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx, y0 + dy, z);
+                        if (!p.b_resident)
+                            tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK, z * p.b_rows_per_batch + n0);
+                    }
+                    if (++s == p.stages) {
+                        s = 0;
+                        ph ^= 1;
+                    }
                 }
             }
         }
     } else if (warp == 1 && lane == 0) {
         // ===== MMA issuer =====
         const uint32_t idesc = make_idesc_bf16(kTileM, p.BN, 0, 0);
-        int it = 0, t = 0, nb = 0, cur_z = -1;
-        for (int w = first_item(p); w < p.total; w = next_item(w, p), ++t) {
+        int t = 0, nb = 0, cur_z = -1;
+        int s = 0;
+        uint32_t ph = 0;
+        TileIter ti;
+        for (tile_first(p, ti); ti.w < p.total; tile_next(p, ti), ++t) {
             const int a = t & 1;
             if (p.b_resident) {
-                const int z = w / (p.tiles_n * p.tiles_m);
+                const int z = ti.z;
                 if (cur_z < 0 || (p.b_rows_per_batch != 0 && z != cur_z)) {
                     if (nb > 0) umma_commit(bres_empty);  // every MMA issued so far has read the old weights
                     mbar_wait(bres_full, nb & 1);
@@ -649,14 +743,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                     ++nb;
                 }
             }
-            mbar_wait(&tempty_bar[a], ((t >> 1) & 1) ^ 1);
+            GEMM_WAIT(&tempty_bar[a], ((t >> 1) & 1) ^ 1);
             tc_fence_after();
             const uint32_t tacc = tmem_base + a * p.acc_stride;
-            const uint32_t bres_tile = smem_u32(smem) + (w % p.tiles_n) * p.ktiles * p.BN * 128;
-            for (int i = 0; i < total_it; ++i, ++it) {
-                const int s = it % p.stages;
-                const uint32_t ph = (it / p.stages) & 1;
-                mbar_wait(&full_bar[s], ph);
+            const uint32_t bres_tile = smem_u32(smem) + ti.nt * p.ktiles * p.BN * 128;
+            for (int i = 0; i < total_it; ++i) {
+                GEMM_WAIT(&full_bar[s], ph);
                 tc_fence_after();
                 const uint32_t a_addr = smem_u32(ring + s * stage_bytes);
                 const uint32_t b_addr = p.b_resident ? bres_tile + i * p.BN * 128 : a_addr + kABytes;
@@ -664,9 +756,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 for (int k = 0; k < kTileK / 16; ++k) {
                     const uint64_t adesc = make_sdesc_sw128(a_addr + k * 32, 16, 1024);
                     const uint64_t bdesc = make_sdesc_sw128(b_addr + k * 32, 16, 1024);
-                    umma_bf16(tacc, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
+                    if (!(p.dbg & 64)) umma_bf16(tacc, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
                 }
                 umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
+                if (++s == p.stages) {
+                    s = 0;
+                    ph ^= 1;
+                }
             }
             umma_commit(&tfull_bar[a]);  // accumulator complete
         }

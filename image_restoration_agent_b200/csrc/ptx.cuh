@@ -51,6 +51,26 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
+// Non-blocking poll (mbarrier.test_wait) in a tight loop: no hardware suspend, so the waiter sees the phase flip as
+// soon as its next poll issues. Costs issue slots while waiting.
+__device__ __forceinline__ uint32_t mbar_test_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok;
+}
+__device__ __forceinline__ void mbar_wait_spin(uint64_t* bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_test_wait(bar, parity)) {
+        if (++spins > (1u << 28)) { __trap(); }
+    }
+}
+
 // Same, but every try suspends the thread in hardware for up to ~20 us (or until the phase completes) instead of
 // returning after a few hundred cycles: a waiting warp then costs no issue slots. For kernels whose warps wait on
 // each other while sharing the schedulers with the warps they wait for.
