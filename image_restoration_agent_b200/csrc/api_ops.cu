@@ -2,6 +2,7 @@
 #include "../../include/irb200.h"
 #include "common.cuh"
 #include "kernels.h"
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 
@@ -11,6 +12,15 @@ void set_error(const std::string& msg) { g_last_error = msg; }
 
 // ---- per-launch profiler -----------------------------------------------------------------------------
 bool g_prof_on = false;
+
+bool pdl_enabled() {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("IRB_PDL");
+        on = e ? atoi(e) : 1;
+    }
+    return on != 0;
+}
 struct ProfRec {
     char name[56];
     double flops, bytes;

@@ -1,5 +1,6 @@
 // Shared types for the irb200 kernels: storage dtypes, the fused GEMM/conv epilogue, error plumbing.
 #pragma once
+#include <utility>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -251,6 +252,24 @@ static inline Epi make_epi(void* out, long long ldo, int out_dt) {
 }
 
 // algorithmic bytes of an epilogue: result written once (+ residual read once) for `rows` x `cols`
+// Launch with the PDL attribute (see griddep_wait() in ptx.cuh); IRB_PDL=0 launches the ordinary way (diagnosis).
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                     Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 static inline double epi_bytes(const Epi& e, double rows, double cols) {
     const double eo = e.out_dt == DT_BF16 ? 2 : 4, er = e.res_dt == DT_BF16 ? 2 : 4;
     return rows * cols * (eo + (e.res ? er : 0));

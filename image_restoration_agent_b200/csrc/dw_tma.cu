@@ -60,6 +60,8 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_c
         fence_mbar_init();
     }
     __syncthreads();
+    griddep_wait();  // PDL: the barrier setup above overlapped the previous kernel's tail
+    griddep_launch();
     const int per_chunk = p.total / p.chunks;  // images * tiles
     const int per_img = p.tiles_x * p.tiles_y;
     const int chunk = blockIdx.x % p.chunks;
@@ -220,12 +222,11 @@ static int dw_tma_launch(bool gate, const bf16* x, long long ldx, int Ctot, bf16
         gelu_tanh = e ? atoi(e) : 0;
     }
     if (gate && gelu_tanh)
-        dw3x3_tma_kernel<2><<<grid, kDwThreads, smem, stream>>>(p);
+        IRB_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<2>, dim3(grid), dim3(kDwThreads), smem, stream, p));
     else if (gate)
-        dw3x3_tma_kernel<1><<<grid, kDwThreads, smem, stream>>>(p);
+        IRB_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<1>, dim3(grid), dim3(kDwThreads), smem, stream, p));
     else
-        dw3x3_tma_kernel<0><<<grid, kDwThreads, smem, stream>>>(p);
-    IRB_CHECK_CUDA(cudaGetLastError());
+        IRB_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<0>, dim3(grid), dim3(kDwThreads), smem, stream, p));
     const double px = double(Nimg) * H * W, cin = gate ? 2.0 * Cout : double(Cout);
     prof_mark(gate ? "dw3x3_gate_tma" : "dw3x3_tma", Cout, 2, 18.0 * px * cin, px * (cin + Cout) * 2 + 36.0 * cin, stream);
     return 0;

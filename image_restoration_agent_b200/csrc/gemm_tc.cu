@@ -672,6 +672,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const int total_it = p.taps * p.ktiles;
+    // PDL: everything above overlapped the previous kernel's tail; its results are visible from here on
+    griddep_wait();
+    griddep_launch();
 
     if (warp == 0 && lane == 0) {
         // ===== TMA producer =====
@@ -752,11 +755,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 tc_fence_after();
                 const uint32_t a_addr = smem_u32(ring + s * stage_bytes);
                 const uint32_t b_addr = p.b_resident ? bres_tile + i * p.BN * 128 : a_addr + kABytes;
+                // one descriptor per operand and stage; the 32-byte K steps only move the 16-byte-unit address field
+                const uint64_t adesc0 = make_sdesc_sw128(a_addr, 16, 1024);
+                const uint64_t bdesc0 = make_sdesc_sw128(b_addr, 16, 1024);
 #pragma unroll
                 for (int k = 0; k < kTileK / 16; ++k) {
-                    const uint64_t adesc = make_sdesc_sw128(a_addr + k * 32, 16, 1024);
-                    const uint64_t bdesc = make_sdesc_sw128(b_addr + k * 32, 16, 1024);
-                    if (!(p.dbg & 64)) umma_bf16(tacc, adesc, bdesc, idesc, (i | k) != 0 ? 1u : 0u);
+                    if (!(p.dbg & 64)) umma_bf16(tacc, adesc0 + uint64_t(k * 2), bdesc0 + uint64_t(k * 2), idesc, (i | k) != 0 ? 1u : 0u);
                 }
                 umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
                 if (++s == p.stages) {
@@ -1222,8 +1226,7 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     p.m_outer = order;
     const long long units = p.m_outer ? (long long)batch * p.tiles_m : total;
     const int grid = int(units < sm_count() ? units : sm_count());
-    fn<<<grid, kGemmThreads, smem, stream>>>(p);
-    IRB_CHECK_CUDA(cudaGetLastError());
+    IRB_CHECK_CUDA(launch_pdl(fn, dim3(grid), dim3(kGemmThreads), smem, stream, p));
     return 0;
 }
 

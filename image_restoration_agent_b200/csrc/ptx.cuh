@@ -288,6 +288,14 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
 __device__ __forceinline__ void sts_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+// Programmatic dependent launch (PDL). A kernel launched with the programmatic-stream-serialization attribute may
+// start while its predecessor in the stream is still running: everything it does before griddep_wait() (barrier init,
+// TMEM allocation, descriptor prefetch, staging of constants) overlaps the predecessor's tail and the grid launch
+// latency; griddep_wait() returns once the predecessor grid has completed and its memory is visible, so every global
+// read of produced data and every global write must come after it. griddep_launch() lets the successor be scheduled.
+// Both are no-ops for kernels launched the ordinary way.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 // two packed pairs (4 consecutive floats) from shared memory
 __device__ __forceinline__ void lds_f32x4(uint32_t addr, f32x2& a, f32x2& b) {
     asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "r"(addr));
