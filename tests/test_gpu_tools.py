@@ -89,3 +89,44 @@ def test_single_rank_sharded_restore_equals_plain():
     u8b, fb = parallel.restore_sharded(eng, img, 32, 8, want_f32=True)
     assert torch.equal(u8a, u8b) and (fa - fb).abs().max().item() <= 1e-6
     eng.close()
+
+
+def test_tool_chain_derain_denoise_sr(tmp_path):
+    """BASELINE config 4 (mixed-degradation chain): Restormer derain -> SwinIR denoise -> SwinIR x4 SR, each tool reading
+    the previous tool's output.png (AgenticIR/executor/tool.py:33-62). Every stage is checked against the oracle run
+    on the SAME input file the stage saw, so a 1-LSB difference of one stage cannot compound."""
+    import cv2
+    from image_restoration_agent_b200.tool_api import RestormerB200, SwinIRB200, clear_engines
+    from oracle import restormer_ref, swinir_ref, tiling
+    rcfg = configs.small_restormer_config()
+    rsd = synth.restormer_state_dict(rcfg, 3)
+    dcfg = configs.small_swinir_config("color_dn")
+    dsd = synth.swinir_state_dict(dcfg, 4)
+    scfg = configs.small_swinir_config("real_sr", scale=4, large_model=True)
+    ssd = synth.swinir_state_dict(scfg, 5)
+    img = synth.synthetic_image_u8(40, 56, 3, seed=11)
+    d0 = tmp_path / "s0"
+    d0.mkdir()
+    cv2.imwrite(str(d0 / "input.png"), img)
+    stages = [
+        (RestormerB200("deraining", state_dict=rsd, cfg=rcfg, precision="fp32"),
+         lambda bgr: cv2.cvtColor(tiling.restormer_restore_image(cv2.cvtColor(bgr, cv2.COLOR_BGR2RGB),
+                                                                 restormer_ref.Model(rsd, rcfg)), cv2.COLOR_RGB2BGR)),
+        (SwinIRB200("denoising", "15", state_dict=dsd, cfg=dcfg, precision="fp32"),
+         lambda bgr: tiling.swinir_process_image(bgr, swinir_ref.Model(dsd, dcfg), 1, 8)),
+        (SwinIRB200("super_resolution", "psnr", state_dict=ssd, cfg=scfg, precision="fp32"),
+         lambda bgr: tiling.swinir_process_image(bgr, swinir_ref.Model(ssd, scfg), 4, 8)),
+    ]
+    src = d0
+    for k, (tool, oracle_fn) in enumerate(stages):
+        dst = tmp_path / f"s{k + 1}"
+        dst.mkdir()
+        tool(src, dst, silent=True)
+        seen = cv2.imread(str(sorted(src.glob("*"))[0]), cv2.IMREAD_COLOR)
+        got = cv2.imread(str(dst / "output.png"), cv2.IMREAD_COLOR)
+        want = oracle_fn(seen)
+        assert got.shape == want.shape, (k, got.shape, want.shape)
+        assert np.abs(got.astype(int) - want.astype(int)).max() <= 1, k
+        src = dst
+    assert got.shape == (160, 224, 3)
+    clear_engines()
