@@ -1218,13 +1218,17 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
         IRB_CHECK_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set[slot] = true;
     }
-    static int order = -1;
-    if (order < 0) {
+    // Order 1 (a CTA walks all n-tiles of an m-tile) re-reads A from L2 back to back, but hands out whole m-tiles: with
+    // few m-tiles per CTA (the deep Restormer levels: 192 m-tiles on 148 SMs) a third of the SMs idle in the second
+    // wave. Then the (m, n) items are dealt round-robin instead (order 0). IRB_GEMM_ORDER=0/1 forces one.
+    static int order = -2;
+    if (order == -2) {
         const char* e = getenv("IRB_GEMM_ORDER");
-        order = e ? atoi(e) : 1;
+        order = e ? atoi(e) : -1;
     }
-    p.m_outer = order;
-    const long long units = p.m_outer ? (long long)batch * p.tiles_m : total;
+    const long long m_units = (long long)batch * p.tiles_m;
+    p.m_outer = order >= 0 ? order : ((p.tiles_n > 1 && m_units < 8ll * sm_count()) ? 0 : 1);
+    const long long units = p.m_outer ? m_units : total;
     const int grid = int(units < sm_count() ? units : sm_count());
     IRB_CHECK_CUDA(launch_pdl(fn, dim3(grid), dim3(kGemmThreads), smem, stream, p));
     return 0;
