@@ -66,6 +66,30 @@ __device__ __forceinline__ long long wa_token_pixel(const WaParams& p, int unit,
 
 // D2T: compile-time head_dim / 2 (15: SwinIR-M / -L, 16), or 0 = runtime. With a constant the output loop below is
 // fully unrolled and its index arithmetic folds into constants (it was 31 % of the kernel's stall samples).
+// The same split in two: the window of a row depends only on (unit, r >> 6), which is uniform per loader warp, so the
+// run-time divisions are done once per unit instead of once per row.
+struct WaWindow {
+    int img, wy, wx;
+    bool valid;
+};
+__device__ __forceinline__ WaWindow wa_window(const WaParams& p, int gw) {
+    WaWindow w;
+    w.valid = gw < p.total_windows;
+    const int per = p.nwx * p.nwy;
+    w.img = gw / per;
+    const int wi = gw - w.img * per;
+    w.wy = wi / p.nwx;
+    w.wx = wi - w.wy * p.nwx;
+    return w;
+}
+__device__ __forceinline__ long long wa_window_pixel(const WaParams& p, const WaWindow& w, int r) {
+    const int ty = (r & 63) >> 3, tx = r & 7;
+    int oy = w.wy * 8 + ty + p.shift, ox = w.wx * 8 + tx + p.shift;
+    if (oy >= p.H) oy -= p.H;
+    if (ox >= p.W) ox -= p.W;
+    return w.valid ? ((long long)w.img * p.H + oy) * p.W + ox : 0;
+}
+
 template <int D2T>
 __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(const WaParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -131,27 +155,22 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
         int cnt = 0;
         for (int u = blockIdx.x; u < p.units; u += gridDim.x) {
             long long poff[8];
-            uint32_t vmask = 0;
+            const WaWindow win = wa_window(p, u * 2 + (lw >> 1));  // the warp's 32 rows are half a window
+            const uint32_t vmask = win.valid ? 0xffu : 0u;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                bool valid;
-                int my, mx;
-                const long long pix = wa_token_pixel(p, u, lw * 32 + i * 4 + sub, valid, my, mx);
-                poff[i] = pix * p.ld + c * 8;
-                vmask |= valid ? (1u << i) : 0u;
-            }
+            for (int i = 0; i < 8; ++i) poff[i] = wa_window_pixel(p, win, lw * 32 + i * 4 + sub) * p.ld + c * 8;
             // The two-stage ring covers one head pair of look-ahead, less than the DRAM latency under load: pull the
             // rows of this CTA's NEXT unit (all heads: 3 * Cq bf16 = whole 128-byte lines) into L2 now, a full unit
             // (3 head pairs) ahead, so the cp.async gathers below only ever see L2 latency.
             if (u + (int)gridDim.x < p.units) {
                 const int nlines = (3 * p.Cq) >> 6;
+                const WaWindow wnx = wa_window(p, (u + (int)gridDim.x) * 2 + (lw >> 1));
+                if (wnx.valid) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    bool valid;
-                    int my, mx;
-                    const long long pix = wa_token_pixel(p, u + gridDim.x, lw * 32 + i * 4 + sub, valid, my, mx);
-                    if (valid)
+                    for (int i = 0; i < 8; ++i) {
+                        const long long pix = wa_window_pixel(p, wnx, lw * 32 + i * 4 + sub);
                         for (int l = c; l < nlines; l += 8) prefetch_l2(p.qkv + pix * p.ld + l * 64);
+                    }
                 }
             }
             for (int hp = 0; hp < npairs; ++hp, ++cnt) {
