@@ -263,8 +263,14 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                         ++pv_next;
                     }
                 }
-                if (progress) spins = 0;
-                else if (++spins > (1u << 26)) __trap();  // protocol bug: fail the launch instead of hanging
+                if (progress) {
+                    spins = 0;
+                } else {
+                    // back off: this thread shares its scheduler with softmax and loader warps, and the kernel is
+                    // sensitive to issue pressure
+                    __nanosleep(64);
+                    if (++spins > (1u << 24)) __trap();  // protocol bug: fail the launch instead of hanging
+                }
             }
         }
     } else {
