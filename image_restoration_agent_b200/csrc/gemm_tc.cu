@@ -45,6 +45,7 @@ struct alignas(64) TcGemmParams {
     int tmem_cols;    // 2 accumulators of acc_stride columns
     int acc_stride;
     int tiles_m, tiles_n, total;  // work items: total = batch * tiles_m * tiles_n, n fastest
+    int step_nt, step_units;      // order 0: divmod(grid, tiles_n)
     int m_outer;                  // 1: a CTA walks all n-tiles of its m-tile back to back
     int b_resident;               // 1 (mode 0): the whole weight matrix stays in shared memory, the ring carries A only
     int bres_bytes;
@@ -279,8 +280,25 @@ __device__ __forceinline__ void tile_set(const TcGemmParams& p, TileIter& t, int
 }
 __device__ __forceinline__ void tile_first(const TcGemmParams& p, TileIter& t) { tile_set(p, t, first_item(p)); }
 __device__ __forceinline__ void tile_next(const TcGemmParams& p, TileIter& t) {
-    if (!p.m_outer) {
-        tile_set(p, t, t.w + gridDim.x);
+    if (!p.m_outer) {  // w += grid: (step_units, step_nt) = divmod(grid, tiles_n), computed on the host
+        t.w += gridDim.x;
+        t.nt += p.step_nt;
+        int du = p.step_units;
+        if (t.nt >= p.tiles_n) {
+            t.nt -= p.tiles_n;
+            ++du;
+        }
+        t.mt += du;
+        if (t.mt >= p.tiles_m) {
+            if (t.mt - p.tiles_m < p.tiles_m) {
+                t.mt -= p.tiles_m;
+                ++t.z;
+            } else {
+                const int q = t.mt / p.tiles_m;
+                t.mt -= q * p.tiles_m;
+                t.z += q;
+            }
+        }
         return;
     }
     if (++t.nt < p.tiles_n) {
@@ -1230,6 +1248,8 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     p.m_outer = order >= 0 ? order : ((p.tiles_n > 1 && m_units < 8ll * sm_count()) ? 0 : 1);
     const long long units = p.m_outer ? m_units : total;
     const int grid = int(units < sm_count() ? units : sm_count());
+    p.step_nt = grid % p.tiles_n;
+    p.step_units = grid / p.tiles_n;
     IRB_CHECK_CUDA(launch_pdl(fn, dim3(grid), dim3(kGemmThreads), smem, stream, p));
     return 0;
 }
