@@ -694,8 +694,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
     griddep_wait();
     griddep_launch();
 
-    if (warp == 0 && lane == 0) {
-        // ===== TMA producer =====
+    if (warp == 0) {
+        // ===== TMA producer: the whole warp walks the tiles, the elected lane issues (ptxas then knows the issue
+        // is single-threaded and drops its per-instruction election loops) =====
+        const bool leader = elect_one() != 0;
         int nb = 0, cur_z = -1;
         int s = 0;         // ring slot and its phase, carried instead of it % stages, (it / stages) & 1
         uint32_t ph = 0;
@@ -708,11 +710,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             if (p.b_resident && (cur_z < 0 || (p.b_rows_per_batch != 0 && z != cur_z))) {
                 // (re)load the whole weight matrix; a new batch index only after the MMAs of the old one are done
                 if (nb > 0) mbar_wait(bres_empty, (nb - 1) & 1);
-                mbar_arrive_expect_tx(bres_full, p.bres_bytes);
-                for (int t = 0; t < p.tiles_n; ++t)
-                    for (int kc = 0; kc < p.ktiles; ++kc)
-                        tma_load_2d(smem + (t * p.ktiles + kc) * p.BN * 128, &p.tmB, bres_full, kc * kTileK,
-                                    z * p.b_rows_per_batch + t * p.BN);
+                if (leader) {
+                    mbar_arrive_expect_tx(bres_full, p.bres_bytes);
+                    for (int t = 0; t < p.tiles_n; ++t)
+                        for (int kc = 0; kc < p.ktiles; ++kc)
+                            tma_load_2d(smem + (t * p.ktiles + kc) * p.BN * 128, &p.tmB, bres_full, kc * kTileK,
+                                        z * p.b_rows_per_batch + t * p.BN);
+                }
+                __syncwarp();
                 cur_z = z;
                 ++nb;
             }
@@ -728,17 +733,20 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                     GEMM_WAIT(&empty_bar[s], ph ^ 1);
                     uint8_t* sa = ring + s * stage_bytes;
                     uint8_t* sb = sa + kABytes;
-                    if (p.dbg & 128) {  // diagnosis: no operand loads
-                        mbar_arrive(&full_bar[s]);
-                    } else {
-                        mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
-                        if (p.mode == 0)
-                            tma_load_3d(sa, &p.tmA, &full_bar[s], kc * kTileK, mt * kTileM, z);
-                        else
-                            tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx, y0 + dy, z);
-                        if (!p.b_resident)
-                            tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK, z * p.b_rows_per_batch + n0);
+                    if (leader) {
+                        if (p.dbg & 128) {  // diagnosis: no operand loads
+                            mbar_arrive(&full_bar[s]);
+                        } else {
+                            mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
+                            if (p.mode == 0)
+                                tma_load_3d(sa, &p.tmA, &full_bar[s], kc * kTileK, mt * kTileM, z);
+                            else
+                                tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx, y0 + dy, z);
+                            if (!p.b_resident)
+                                tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK, z * p.b_rows_per_batch + n0);
+                        }
                     }
+                    __syncwarp();
                     if (++s == p.stages) {
                         s = 0;
                         ph ^= 1;
@@ -746,8 +754,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 }
             }
         }
-    } else if (warp == 1 && lane == 0) {
-        // ===== MMA issuer =====
+    } else if (warp == 1) {
+        // ===== MMA issuer: the whole warp walks the tiles and polls the barriers (so the loop state and the
+        // descriptors stay warp-uniform), lane 0 alone issues the tcgen05 instructions =====
+        const bool leader = elect_one() != 0;  // elect.sync is deterministic for the full mask: always the same lane
         const uint32_t idesc = make_idesc_bf16(kTileM, p.BN, 0, 0);
         int t = 0, nb = 0, cur_z = -1;
         int s = 0;
@@ -758,7 +768,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             if (p.b_resident) {
                 const int z = ti.z;
                 if (cur_z < 0 || (p.b_rows_per_batch != 0 && z != cur_z)) {
-                    if (nb > 0) umma_commit(bres_empty);  // every MMA issued so far has read the old weights
+                    if (nb > 0 && leader) umma_commit(bres_empty);  // every MMA issued so far has read the old weights
+                    __syncwarp();
                     mbar_wait(bres_full, nb & 1);
                     cur_z = z;
                     ++nb;
@@ -776,17 +787,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 // one descriptor per operand and stage; the 32-byte K steps only move the 16-byte-unit address field
                 const uint64_t adesc0 = make_sdesc_sw128(a_addr, 16, 1024);
                 const uint64_t bdesc0 = make_sdesc_sw128(b_addr, 16, 1024);
+                if (leader) {
 #pragma unroll
-                for (int k = 0; k < kTileK / 16; ++k) {
-                    if (!(p.dbg & 64)) umma_bf16(tacc, adesc0 + uint64_t(k * 2), bdesc0 + uint64_t(k * 2), idesc, (i | k) != 0 ? 1u : 0u);
+                    for (int k = 0; k < kTileK / 16; ++k) {
+                        if (!(p.dbg & 64)) umma_bf16(tacc, adesc0 + uint64_t(k * 2), bdesc0 + uint64_t(k * 2), idesc, (i | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
                 }
-                umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
+                __syncwarp();
                 if (++s == p.stages) {
                     s = 0;
                     ph ^= 1;
                 }
             }
-            umma_commit(&tfull_bar[a]);  // accumulator complete
+            if (leader) umma_commit(&tfull_bar[a]);  // accumulator complete
+            __syncwarp();
         }
     } else if (warp >= 2) {
         // ===== epilogue: TMEM -> registers -> global. Two sets of 4 warps: set s drains accumulator s, i.e. the
