@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_c
     const int sp0 = blockIdx.x / p.chunks, sp_step = gridDim.x / p.chunks;
 
     if (warp == kDwConsumerWarps) {
-        if (lane == 0) {
+        if (elect_one()) {
             tma_prefetch_desc(&p.tm);
             int it = 0;
             for (int sp = sp0; sp < per_chunk; sp += sp_step, ++it) {

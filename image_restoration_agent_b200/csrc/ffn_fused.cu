@@ -341,7 +341,7 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
         if (mb == 1 && ti > 0) epilogue(prev_tile, ti - 1);
     } else if (warp == kFfDwWarps + kFfCvWarps) {
         // ================= TMA producer =================
-        if (lane == 0) {
+        if (elect_one()) {
             tma_prefetch_desc(&p.tmX);
             tma_prefetch_desc(&p.tmWin);
             tma_prefetch_desc(&p.tmWout);
@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
         }
     } else if (warp == kFfDwWarps + kFfCvWarps + 1) {
         // ================= MMA 1: project_in on the halo tile =================
-        if (lane == 0) {
+        if (elect_one()) {
             const uint32_t idesc = make_idesc_bf16(128, 64, 0, 0);
             const uint32_t a1 = smem_u32(sA1), win = smem_u32(sWin);
             int g = 0, ti = 0;
@@ -402,7 +402,7 @@ __global__ void __launch_bounds__(kFfThreads, 1) gdfn_fused_kernel(const __grid_
         }
     } else {
         // ================= MMA 2: project_out of the gated tile =================
-        if (lane == 0) {
+        if (elect_one()) {
             const uint32_t idesc = make_idesc_bf16(128, p.C, 0, 0);
             const uint32_t a2 = smem_u32(sA2), wout = smem_u32(sWout);
             int g = 0, pr = 0, ti = 0;

@@ -87,7 +87,8 @@ __global__ void __launch_bounds__(192) mdta_gram_tc_kernel(const __grid_constant
     const int qc = head * p.c;         // first q channel of this head
     const int kc = p.C + head * p.c;   // first k channel of this head
 
-    if (warp == 0 && lane == 0) {
+    // elect.sync leaders: ptxas then issues TMA / tcgen05 directly instead of through per-instruction election loops
+    if (warp == 0 && elect_one()) {
         for (int it = 0; it < total_it; ++it) {
             const int s = it % p.stages;
             const uint32_t ph = (it / p.stages) & 1;
@@ -100,7 +101,7 @@ __global__ void __launch_bounds__(192) mdta_gram_tc_kernel(const __grid_constant
             tma_load_3d(sa + p.nbox * kGramBox, &p.tm, &full_bar[s], kc, pp, img);
             if (p.nbox == 2) tma_load_3d(sa + 3 * kGramBox, &p.tm, &full_bar[s], kc + 64, pp, img);
         }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1 && elect_one()) {
         const uint32_t idesc = make_idesc_bf16(128, p.ncols, 1, 1);  // both operands MN-major
         for (int it = 0; it < total_it; ++it) {
             const int s = it % p.stages;

@@ -197,7 +197,9 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
         }
     } else if (warp == 0) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // elect.sync rather than lane == 0: ptxas then knows the region is single-threaded and issues the tcgen05
+        // instructions directly instead of wrapping each in an election loop
+        if (elect_one()) {
             const uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);  // Q, K both K-major
             const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);   // P K-major, V MN-major
             int my_pairs = 0;
