@@ -5,11 +5,12 @@ import sys, torch
 from image_restoration_agent_b200 import ops
 K = int(sys.argv[1]) if len(sys.argv) > 1 else 96
 N = int(sys.argv[2]) if len(sys.argv) > 2 else 96
-w = (torch.randn(N, K, device="cuda") / K ** 0.5).bfloat16()
+KP = (K + 63) // 64 * 64  # padded row strides (the C = 180 streams of SwinIR use 192)
+w = (torch.randn(N, KP, device="cuda") / K ** 0.5).bfloat16()[:, :K]
 res = []
 for t in (1, 2, 4, 8, 16, 32, 64):
     M = 148 * 128 * t
-    x = torch.randn(M, K, device="cuda").bfloat16()
+    x = torch.randn(M, (K + 15) // 16 * 16, device="cuda").bfloat16()[:, :K]
     for _ in range(3):
         ops.gemm1x1(x, w)
     torch.cuda.synchronize()
