@@ -393,7 +393,7 @@ __device__ __forceinline__ void epi_block_full(uint32_t taddr_cb, const float* s
         for (int c = 0; c < 2 * NG; ++c) rr[c] = __ldg(reinterpret_cast<const uint4*>(rrow_cb + c * 8));
     }
     if (wait_read) {  // the store issued two blocks ago (same staging block) must have finished READING it
-        if (lane == 0) bulk_wait_read1();
+        bulk_wait_read1();  // every lane: only the elected issuer has bulk groups, the others fall through
         __syncwarp();
     }
     if (STATS && first_blk)  // x_old[row, 0]
@@ -434,6 +434,10 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
     const uint32_t row_off = lane * 128 + ((lane & 7) << 4);
     uint64_t* rbar = c.res_bar + (warp - 2) * 3;
     const float slope = p.epi.slope;
+    // The lane that issues this warp's TMA loads / stores. elect.sync (deterministic for the full mask) instead of
+    // lane == 0 lets ptxas issue UTMASTG / UTMALDG / the commit without an election loop around each; the bulk-group
+    // waits are executed by all lanes because only the issuer's are non-trivial.
+    const bool leader = elect_one() != 0;
 
     // first tile of this warp set
     TileIter ti;  // this set's current tile; tn = its next tile (two steps of the CTA's walk ahead)
@@ -456,7 +460,7 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
         const int nt2 = tp.nt, mt2 = tp.mt, z2 = tp.z;
         const int col = nt2 * p.BN + pblk * bcols;
         const uint32_t b = nissued % 3;
-        if (lane == 0) {
+        if (leader) {
             mbar_arrive_expect_tx(&rbar[b], 4096);
             tma_load_3d(stg_warp_p + b * 4096, &p.tmR, &rbar[b], col, mt2 * kTileM + q * 32, z2);
         }
@@ -572,7 +576,7 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
                 }
                 if (STATS && blk == 0) st_shift = __uint_as_float(rr[0].x << 16);
                 if (RES != 2) {
-                    if (lane == 0) bulk_wait_read1();
+                    bulk_wait_read1();
                     __syncwarp();
                 }
                 tmem_ld_wait();
@@ -595,7 +599,7 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
             }
             fence_proxy_async();
             __syncwarp();
-            if (lane == 0) {
+            if (leader) {
                 if (last) mbar_arrive(&c.tempty_bar[set]);
                 if (!(p.dbg & 1)) {
                     uint8_t* sp = stg_warp_p + bsel * 4096;
@@ -618,7 +622,7 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
             ++nb;
             if (RES == 2) {
                 // block nb+1 goes into the staging block of block nb-2: its store must have finished reading
-                if (lane == 0) bulk_wait_read1();
+                bulk_wait_read1();
                 __syncwarp();
                 issue_res();
             }
@@ -633,7 +637,7 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
             p.epi.stats_out[grow] = make_float2(st_shift + m, rsqrtf(var + p.epi.stats_eps));
         }
     }
-    if (lane == 0) bulk_wait0();  // all bulk stores of this warp have landed before the CTA exits
+    bulk_wait0();  // all bulk stores of this warp have landed before the CTA exits
 }
 
 template <int VAR>
