@@ -37,6 +37,7 @@ struct alignas(64) TcGemmParams {
     int N;        // valid output columns
     int BN;       // columns per tile (multiple of 16, <= 256)
     int ktiles;   // 64-wide K chunks per tap
+    int klast;    // 16-wide K steps of the last chunk of a tap that hold data (1..4); the rest is TMA zero fill
     int taps;     // 1 or 9
     int kpad;     // K distance between taps inside Wt
     int H, W, BW, BH, tiles_x;
@@ -783,7 +784,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             tc_fence_after();
             const uint32_t tacc = tmem_base + a * p.acc_stride;
             const uint32_t bres_tile = smem_u32(smem) + ti.nt * p.ktiles * p.BN * 128;
+            int kc = 0;  // chunk within the tap
             for (int i = 0; i < total_it; ++i) {
+                const int ksteps = (kc == p.ktiles - 1) ? p.klast : kTileK / 16;
+                if (++kc == p.ktiles) kc = 0;
                 GEMM_WAIT(&full_bar[s], ph);
                 tc_fence_after();
                 const uint32_t a_addr = smem_u32(ring + s * stage_bytes);
@@ -794,7 +798,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 if (leader) {
 #pragma unroll
                     for (int k = 0; k < kTileK / 16; ++k) {
-                        if (!(p.dbg & 64)) umma_bf16(tacc, adesc0 + uint64_t(k * 2), bdesc0 + uint64_t(k * 2), idesc, (i | k) != 0 ? 1u : 0u);
+                        if (k < ksteps && !(p.dbg & 64))  // K steps past the data are zeros on both sides: skipped
+                            umma_bf16(tacc, adesc0 + uint64_t(k * 2), bdesc0 + uint64_t(k * 2), idesc, (i | k) != 0 ? 1u : 0u);
                     }
                     umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
                 }
@@ -1292,6 +1297,7 @@ int tc_gemm(const bf16* A, long long lda, int M, int K, int batch, long long a_b
     p.N = N;
     p.BN = pick_bn(N);
     p.ktiles = ceil_div(K, kTileK);
+    p.klast = ceil_div(K - (p.ktiles - 1) * kTileK, 16);
     p.taps = 1;
     p.kpad = 0;
     p.b_rows_per_batch = w_rows_per_batch;
@@ -1353,6 +1359,10 @@ int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, cons
     p.N = N;
     p.BN = pick_bn(N);
     p.ktiles = kpad / kTileK;
+    {
+        const int rem = C - (p.ktiles - 1) * kTileK;  // channels in the last chunk of a tap
+        p.klast = (rem >= 1 && rem <= kTileK) ? ceil_div(rem, 16) : kTileK / 16;
+    }
     p.taps = 9;
     p.kpad = kpad;
     p.H = H;
