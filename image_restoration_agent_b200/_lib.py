@@ -8,8 +8,11 @@ from __future__ import annotations
 import ctypes as C
 from pathlib import Path
 
+import os
+
 PKG = Path(__file__).resolve().parent
-LIB_PATH = PKG / "libirb200.so"
+# IRB_LIB selects another build of the same ABI (the -DIRB_DIAG library of tools/gpu_ab.sh); default = the product
+LIB_PATH = Path(os.environ["IRB_LIB"]).resolve() if os.environ.get("IRB_LIB") else PKG / "libirb200.so"
 
 ARCH_RESTORMER, ARCH_SWINIR = 1, 2
 F32, BF16 = 0, 1
@@ -41,6 +44,7 @@ PROTOTYPES = {
     "irb_destroy": (None, [_vp]),
     "irb_set_option": (_i, [_vp, C.c_char_p, _ll]),
     "irb_scale": (_i, [_vp]),
+    "irb_tile_batch": (_i, [_vp, _i, _i, _i, _ip]),
     "irb_workspace_bytes": (_i, [_vp, _i, _i, _i, C.POINTER(_sz)]),
     "irb_forward_tiles": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "irb_restore_workspace_bytes": (_i, [_vp, _i, _i, _i, _i, C.POINTER(_sz)]),
@@ -58,6 +62,7 @@ PROTOTYPES = {
     "irb_mdta_gram": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "irb_mdta_attn": (_i, [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp]),
     "irb_stitch": (_i, [_vp, _i, _i, _i, _i, _ip, _ip, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "irb_stitch_rows": (_i, [_vp, _i, _i, _i, _i, _ip, _ip, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "irb_profile_begin": (_i, [_vp]),
     "irb_profile_end": (_i, [_vp]),
     "irb_profile_count": (_i, []),

@@ -39,12 +39,21 @@ def _digest(paths) -> str:
     return h.hexdigest()
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
+def build(force: bool = False, verbose: bool = False, diag: bool = False) -> Path:
+    """diag=True builds libirb200_diag.so with -DIRB_DIAG: the A/B environment switches of DESIGN.md §5 exist only
+    there (IRB_LIB=<path> makes _lib.load() pick it up); the shipped library has them compiled out."""
+    if diag:
+        return _build(force, verbose, PKG / "libirb200_diag.so", PKG / "_build_diag", ["-DIRB_DIAG"])
+    return _build(force, verbose, LIB, BUILD, [])
+
+
+def _build(force: bool, verbose: bool, LIB: Path, BUILD: Path, extra) -> Path:
+    NVCC_FLAGS = globals()["NVCC_FLAGS"] + list(extra)
     sources = sorted(CSRC.glob("*.cu"))
     headers = sorted(CSRC.glob("*.cuh")) + sorted(CSRC.glob("*.h")) + [PKG.parent / "include" / "irb200.h"]
     BUILD.mkdir(exist_ok=True)
     stamp = BUILD / "stamp"
-    dig = _digest(sources + headers)
+    dig = _digest(sources + headers) + " ".join(extra)
     if not force and LIB.exists() and stamp.exists() and stamp.read_text() == dig:
         return LIB
     nvcc = _nvcc()
@@ -72,4 +81,4 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, diag="--diag" in sys.argv))

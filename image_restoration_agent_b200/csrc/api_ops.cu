@@ -4,6 +4,8 @@
 #include "kernels.h"
 #include <stdlib.h>
 #include <string.h>
+#include <mutex>
+#include <set>
 #include <vector>
 
 namespace irb {
@@ -16,10 +18,29 @@ bool g_prof_on = false;
 bool pdl_enabled() {
     static int on = -1;
     if (on < 0) {
-        const char* e = getenv("IRB_PDL");
-        on = e ? atoi(e) : 1;
+        on = IRB_DIAG_ENV("IRB_PDL", 1);
     }
     return on != 0;
+}
+
+#ifdef IRB_DIAG
+int diag_env(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+#endif
+
+cudaError_t smem_optin(const void* fn, int bytes) {
+    static std::mutex mu;
+    static std::set<std::pair<const void*, int>> done;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lk(mu);
+    if (done.count({fn, dev})) return cudaSuccess;
+    e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) done.insert({fn, dev});
+    return e;
 }
 struct ProfRec {
     char name[56];
@@ -251,6 +272,14 @@ int irb_stitch(const float* d_tiles, int c, int th, int tw, int sf, const int* y
     IRB_TRY(require_device());
     return tiles_stitch(d_tiles, c, th, tw, sf, ys, xs, ny, nx, h, w, crop_h, crop_w, d_out_f32, d_out_u8,
                         reverse_channels, (cudaStream_t)stream);
+}
+
+int irb_stitch_rows(const float* d_tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx,
+                    int h, int w, int crop_h, int crop_w, int row0, int rows, float* d_out_f32, uint8_t* d_out_u8,
+                    int reverse_channels, void* stream) {
+    IRB_TRY(require_device());
+    return tiles_stitch_rows(d_tiles, c, th, tw, sf, ys, xs, ny, nx, h, w, crop_h, crop_w, row0, rows, d_out_f32,
+                             d_out_u8, reverse_channels, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -38,6 +38,22 @@ void set_error(const std::string& msg);
         if (_rc != 0) return _rc; \
     } while (0)
 
+// ---- diagnosis switches -------------------------------------------------------------------------
+// The A/B switches of DESIGN.md §5 (IRB_GEMM_DBG, IRB_GEMM_SPEC, ...) exist only in a library built with -DIRB_DIAG
+// (build.py --diag -> libirb200_diag.so). The shipped library evaluates every switch to its default at compile
+// time: no environment variable can skip stores, MMAs or epilogues, or change numerics, at run time.
+#ifdef IRB_DIAG
+int diag_env(const char* name, int dflt);
+#define IRB_DIAG_ENV(name, dflt) ::irb::diag_env(name, dflt)
+#else
+#define IRB_DIAG_ENV(name, dflt) (dflt)
+#endif
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE attribute: the opt-in is remembered per
+// (function, current device), so a second GPU driven from the same process gets it too. Returns a cudaError_t.
+cudaError_t smem_optin(const void* fn, int bytes);
+#define IRB_SMEM_OPTIN(fn, bytes) IRB_CHECK_CUDA(::irb::smem_optin(reinterpret_cast<const void*>(fn), bytes))
+
 // ---- optional per-launch profiling (irb_profile_begin/end; bench.py's live roofline) ---------------
 // Every launch wrapper calls prof_mark() right after its kernel launch. When profiling is off this is one
 // predictable branch; when on, a CUDA event is recorded on the launching stream, so the device time between

@@ -159,11 +159,7 @@ bool conv3x3_small_n_ok(int C, int N, const Epi& e) {
 
 template <int PX, int NOUT>
 static int launch_cs(const ConvSmallParams& p, size_t smem, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_small_n_kernel<PX, NOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
-    }
+    IRB_SMEM_OPTIN((conv3x3_small_n_kernel<PX, NOUT>), 200 * 1024);
     dim3 grid(p.tiles_x, p.tiles_y, p.Nimg);
     conv3x3_small_n_kernel<PX, NOUT><<<grid, kCsThreads, smem, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
@@ -218,8 +214,7 @@ int conv3x3_bf16(const bf16* x, long long ldx, int Nimg, int H, int W, int C, co
                  int w_rows_total, const Epi& epi, cudaStream_t stream) {
     static int on = -1;
     if (on < 0) {
-        const char* e = getenv("IRB_CONV_SMALLN");
-        on = e ? atoi(e) : 1;
+        on = IRB_DIAG_ENV("IRB_CONV_SMALLN", 1);
     }
     if (on && conv3x3_small_n_ok(C, N, epi) && ldx % 8 == 0 && Nimg <= 65535)
         return conv3x3_small_n(x, ldx, Nimg, H, W, C, Wt, kpad, N, epi, stream);

@@ -207,19 +207,14 @@ static int dw_tma_launch(bool gate, const bf16* x, long long ldx, int Ctot, bf16
     const int grid = groups * p.chunks;
     const int nst = gate ? kDwStagesGate : kDwStagesPlain;
     const size_t smem = size_t(nst) * (gate ? 2 : 1) * kDwStreamBytes + 128 + nst * 32;
-    static bool attr_set = false;
-    if (!attr_set) {
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
-    }
+    IRB_SMEM_OPTIN((dw3x3_tma_kernel<2>), 200 * 1024);
+    IRB_SMEM_OPTIN((dw3x3_tma_kernel<1>), 200 * 1024);
+    IRB_SMEM_OPTIN((dw3x3_tma_kernel<0>), 200 * 1024);
     static int gelu_tanh = -1;
     if (gelu_tanh < 0) {
         // measured equal to the sigmoid form here (6.07 vs 6.06 ms on cfg2: this kernel is not SFU-bound), so the
         // default stays the more accurate sigmoid form
-        const char* e = getenv("IRB_DW_GELU_TANH");
-        gelu_tanh = e ? atoi(e) : 0;
+        gelu_tanh = IRB_DIAG_ENV("IRB_DW_GELU_TANH", 0);
     }
     if (gate && gelu_tanh)
         IRB_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<2>, dim3(grid), dim3(kDwThreads), smem, stream, p));

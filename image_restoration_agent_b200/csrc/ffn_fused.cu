@@ -442,8 +442,7 @@ bool gdfn_fused_shape_ok(int C, int hp) {
 bool gdfn_fused_supported(int C, int hp) {
     static int enabled = -1;
     if (enabled < 0) {
-        const char* e = getenv("IRB_FUSED_FFN");
-        enabled = e ? atoi(e) : 0;  // opt-in: at parity with the three-kernel path, see DESIGN.md
+        enabled = IRB_DIAG_ENV("IRB_FUSED_FFN", 0);  // opt-in: at parity with the three-kernel path, see DESIGN.md
     }
     return enabled && gdfn_fused_shape_ok(C, hp);
 }
@@ -504,11 +503,7 @@ int gdfn_fused_bf16(const bf16* xmid, long long ldm, const float2* stats_in, bf1
     const size_t smem = 1024 + size_t(p.KS) * kFfA1Slab + size_t(2) * p.KS * kFfWinSlab + 2 * kFfA2Bytes +
                         3 * size_t(p.wout_bytes) + 2 * kFfHidBytes + size_t(4) * hp * 4 + sizeof(FfnBars) + 64;
     IRB_REQUIRE(smem <= 227 * 1024, "gdfn_fused: shared memory budget exceeded");
-    static bool attr_set = false;
-    if (!attr_set) {
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(gdfn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set = true;
-    }
+    IRB_SMEM_OPTIN((gdfn_fused_kernel), 227 * 1024);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

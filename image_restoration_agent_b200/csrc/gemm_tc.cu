@@ -1077,8 +1077,7 @@ int make_tmap_bf16_sw(CUtensorMap* m, const void* base, int rank, const uint64_t
     // IRB_TMA_PROMO=0..3 forces none/64/128/256 (diagnosis).
     static int promo_env = -2;
     if (promo_env == -2) {
-        const char* e = getenv("IRB_TMA_PROMO");
-        promo_env = e ? atoi(e) : -1;
+        promo_env = IRB_DIAG_ENV("IRB_TMA_PROMO", -1);
     }
     const int promo = promo_env >= 0 ? promo_env : 2;
     const CUtensorMapL2promotion pr = promo == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE
@@ -1109,8 +1108,7 @@ static int pick_bn(int N) {
     if (n16 <= 256) return n16;
     static int force = -1;  // IRB_GEMM_BN: tile width for N > 256 (diagnosis)
     if (force < 0) {
-        const char* e = getenv("IRB_GEMM_BN");
-        force = e ? atoi(e) : 0;
+        force = IRB_DIAG_ENV("IRB_GEMM_BN", 0);
     }
     if (force >= 16 && force <= 256 && force % 16 == 0) return force;
     int best = 256, best_pad = ceil_div(N, 256) * 256;
@@ -1158,8 +1156,7 @@ typedef void (*GemmKernelFn)(const TcGemmParams);
 static int gemm_spec_on() {  // IRB_GEMM_SPEC=0: generic kernel only (diagnosis)
     static int on = -1;
     if (on < 0) {
-        const char* e = getenv("IRB_GEMM_SPEC");
-        on = e ? atoi(e) : 1;
+        on = IRB_DIAG_ENV("IRB_GEMM_SPEC", 1);
     }
     return on;
 }
@@ -1211,13 +1208,11 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     // the same N x K weights from L2 for each of its tiles (3x the A traffic at K = 96, all SMs on the same lines)
     static int bres_on = -1;
     if (bres_on < 0) {
-        const char* e = getenv("IRB_GEMM_BRES");
-        bres_on = e ? atoi(e) : 1;
+        bres_on = IRB_DIAG_ENV("IRB_GEMM_BRES", 1);
     }
     static int dbg = -1;
     if (dbg < 0) {
-        const char* e = getenv("IRB_GEMM_DBG");
-        dbg = e ? atoi(e) : 0;
+        dbg = IRB_DIAG_ENV("IRB_GEMM_DBG", 0);
     }
     p.dbg = dbg;
     p.b_resident = 0;
@@ -1246,8 +1241,7 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
         const int res = p.epi.res == nullptr ? 0 : (p.res_tma ? 2 : 1);
         static int gelu_tanh = -1;
         if (gelu_tanh < 0) {
-            const char* e = getenv("IRB_GELU_TANH");
-            gelu_tanh = e ? atoi(e) : 1;
+            gelu_tanh = IRB_DIAG_ENV("IRB_GELU_TANH", 1);
         }
         const int act = (p.epi.act == ACT_GELU && gelu_tanh && p.epi.out_dt == DT_BF16) ? kActGeluTanh : p.epi.act;
         var = act | (ln << 2) | (res << 4) | (p.epi.stats_out ? 64 : 0);
@@ -1255,18 +1249,13 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     int slot = 0;
     GemmKernelFn fn = pick_gemm_kernel(var, &slot);
     IRB_REQUIRE(var >= 0 || (!p.res_tma && p.blk_cols == 64), "tc_gemm: internal: res_tma / 48-column blocks need a specialised variant");
-    static bool attr_set[64] = {false};
-    if (!attr_set[slot]) {
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set[slot] = true;
-    }
+    IRB_SMEM_OPTIN((fn), 227 * 1024);
     // Order 1 (a CTA walks all n-tiles of an m-tile) re-reads A from L2 back to back, but hands out whole m-tiles: with
     // few m-tiles per CTA (the deep Restormer levels: 192 m-tiles on 148 SMs) a third of the SMs idle in the second
     // wave. Then the (m, n) items are dealt round-robin instead (order 0). IRB_GEMM_ORDER=0/1 forces one.
     static int order = -2;
     if (order == -2) {
-        const char* e = getenv("IRB_GEMM_ORDER");
-        order = e ? atoi(e) : -1;
+        order = IRB_DIAG_ENV("IRB_GEMM_ORDER", -1);
     }
     const long long m_units = (long long)batch * p.tiles_m;
     p.m_outer = order >= 0 ? order : ((p.tiles_n > 1 && m_units < 8ll * sm_count()) ? 0 : 1);
@@ -1317,8 +1306,7 @@ int tc_gemm(const bf16* A, long long lda, int M, int K, int batch, long long a_b
         IRB_TRY(make_tmap_bf16(&p.tmC, epi.out, 3, dims, str, box));
         static int restma_on = -1;
         if (restma_on < 0) {
-            const char* e = getenv("IRB_GEMM_RESTMA");
-            restma_on = e ? atoi(e) : 1;
+            restma_on = IRB_DIAG_ENV("IRB_GEMM_RESTMA", 1);
         }
         if (restma_on && epi.res != nullptr && epi.res_dt == DT_BF16 && gemm_variant_exists(epi)) {
             uint64_t rstr[2] = {uint64_t(epi.ldr) * 2, uint64_t(epi.ldr) * 2 * M};

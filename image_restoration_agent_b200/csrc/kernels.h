@@ -92,6 +92,9 @@ int window_attention(const void* qkv, int dt, long long ld, void* out, long long
 int tiles_gather(const float* img, int c, int h, int w, const int* ys, const int* xs, int ny, int nx, int th, int tw,
                  float* tiles, const float* mean, float scale, cudaStream_t stream);
 // Overlap blend (reference order h-major, w-minor), divide by the analytic count, crop, clamp, round-half-even.
+int tiles_stitch_rows(const float* tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx,
+                      int h, int w, int crop_h, int crop_w, int row0, int rows, float* out_f32, uint8_t* out_u8,
+                      int u8_reverse_channels, cudaStream_t stream);
 int tiles_stitch(const float* tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx, int h,
                  int w, int crop_h, int crop_w, float* out_f32 /*[c][crop_h][crop_w] or null*/,
                  uint8_t* out_u8 /*[crop_h][crop_w][c] or null*/, int u8_reverse_channels, cudaStream_t stream);

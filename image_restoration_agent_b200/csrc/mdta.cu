@@ -192,19 +192,14 @@ int mdta_gram_tc(const bf16* qkv, long long ld, int Nimg, int P, int C, int head
     IRB_REQUIRE((P + p.chunk_px - 1) / p.chunk_px == nchunks, "mdta_gram_tc: nchunks must come from mdta_nchunks()");
     static int nbox1 = -1;
     if (nbox1 < 0) {
-        const char* e = getenv("IRB_GRAM_NBOX1");
-        nbox1 = e ? atoi(e) : 1;
+        nbox1 = IRB_DIAG_ENV("IRB_GRAM_NBOX1", 1);
     }
     p.nbox = (c <= 64 && nbox1) ? 1 : 2;
     p.stages = 4;
     p.Gpart = Gpart;
     p.ssq_part = ssq_part;
     const size_t smem = size_t(p.stages) * 2 * p.nbox * kGramBox + 1024 + 256;
-    static bool attr_set = false;
-    if (!attr_set) {
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(mdta_gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
-    }
+    IRB_SMEM_OPTIN((mdta_gram_tc_kernel), 200 * 1024);
     dim3 grid(nchunks, heads, Nimg);
     mdta_gram_tc_kernel<<<grid, 192, smem, stream>>>(p);
     IRB_CHECK_CUDA(cudaGetLastError());
@@ -414,13 +409,9 @@ int mdta_softmax_weff(const float* Gpart, const float* ssq_part, int nchunks, co
         const long long per = (long long)heads * Nimg;
         const int rpt = ceil_div(C, 64) * per >= 296 ? 4 : (ceil_div(C, 32) * per >= 296 ? 2 : 1);
         const size_t smem = (size_t(c) * c + size_t(16 * rpt) * (c + 1)) * sizeof(float);
-        static bool attr_set = false;
-        if (!attr_set) {
-            IRB_CHECK_CUDA(cudaFuncSetAttribute(mdta_weff_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-            IRB_CHECK_CUDA(cudaFuncSetAttribute(mdta_weff_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-            IRB_CHECK_CUDA(cudaFuncSetAttribute(mdta_weff_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-            attr_set = true;
-        }
+        IRB_SMEM_OPTIN((mdta_weff_kernel<1>), 100 * 1024);
+        IRB_SMEM_OPTIN((mdta_weff_kernel<2>), 100 * 1024);
+        IRB_SMEM_OPTIN((mdta_weff_kernel<4>), 100 * 1024);
         dim3 grid(ceil_div(C, 16 * rpt), heads, Nimg);
         if (rpt == 4)
             mdta_weff_kernel<4><<<grid, 256, smem, stream>>>(attn, Wp, C, heads, Weff, w_dt);

@@ -263,6 +263,24 @@ static int make_plan(Model* m, int img_h, int img_w, int tile, int overlap, void
     return 0;
 }
 
+// Every model entry point runs on the model's device whatever device the calling thread has current (a Flask worker
+// thread defaults to device 0); the caller's current device is restored on return.
+struct DeviceGuard {
+    int prev = -1;
+    cudaError_t err = cudaSuccess;
+    explicit DeviceGuard(int dev) {
+        err = cudaGetDevice(&prev);
+        if (err == cudaSuccess && prev != dev) err = cudaSetDevice(dev);
+        else if (err == cudaSuccess) prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+#define IRB_ON_DEVICE(m)            \
+    DeviceGuard _dg((m)->device);   \
+    IRB_CHECK_CUDA(_dg.err)
+
 extern "C" {
 
 int irb_create(const irb_model_desc* desc, const void* weights_blob, size_t nbytes, int device, irb_handle** out) {
@@ -273,7 +291,8 @@ int irb_create(const irb_model_desc* desc, const void* weights_blob, size_t nbyt
         return 2;
     }
     IRB_REQUIRE(device >= 0 && device < ndev, "irb_create: bad device index");
-    IRB_CHECK_CUDA(cudaSetDevice(device));
+    DeviceGuard _dg(device);
+    IRB_CHECK_CUDA(_dg.err);
     cudaDeviceProp prop;
     IRB_CHECK_CUDA(cudaGetDeviceProperties(&prop, device));
     if (prop.major != 10) {
@@ -322,6 +341,12 @@ int irb_set_option(irb_handle* h, const char* key, long long value) {
 
 int irb_scale(const irb_handle* h) { return h ? h->model->scale : 0; }
 
+int irb_tile_batch(irb_handle* h, int n_tiles, int tile_h, int tile_w, int* out_batch) {
+    IRB_REQUIRE(h && out_batch && n_tiles > 0 && tile_h > 0 && tile_w > 0, "irb_tile_batch: bad arguments");
+    *out_batch = pick_batch(h->model, n_tiles, tile_h, tile_w);
+    return 0;
+}
+
 int irb_workspace_bytes(irb_handle* h, int n_tiles, int tile_h, int tile_w, size_t* out_bytes) {
     IRB_REQUIRE(h && out_bytes && n_tiles > 0 && tile_h > 0 && tile_w > 0, "irb_workspace_bytes: bad arguments");
     Model* m = h->model;
@@ -334,6 +359,7 @@ int irb_forward_tiles(irb_handle* h, const float* d_in, float* d_out, int n_tile
                       void* d_workspace, size_t workspace_bytes, void* stream) {
     IRB_REQUIRE(h && d_in && d_out && d_workspace, "irb_forward_tiles: NULL argument");
     Model* m = h->model;
+    IRB_ON_DEVICE(m);
     size_t need;
     IRB_TRY(irb_workspace_bytes(h, n_tiles, tile_h, tile_w, &need));
     IRB_REQUIRE(workspace_bytes >= need, "irb_forward_tiles: workspace too small");
@@ -365,6 +391,7 @@ int irb_restore_image(irb_handle* h, const void* d_in, int in_fmt, int reverse_c
     IRB_REQUIRE(d_out_u8 || d_out_f32, "irb_restore_image: no output requested");
     IRB_REQUIRE(in_fmt == 0 || in_fmt == 1, "irb_restore_image: in_fmt must be 0 (u8 HWC) or 1 (f32 planar)");
     Model* m = h->model;
+    IRB_ON_DEVICE(m);
     RestorePlan P;
     IRB_TRY(make_plan(m, img_h, img_w, tile, overlap, d_workspace, P));
     IRB_REQUIRE(workspace_bytes >= P.total, "irb_restore_image: workspace too small");
@@ -410,6 +437,7 @@ int irb_tiles_prepare(irb_handle* h, const void* d_in, int in_fmt, int reverse_c
                       int tile, int overlap, float* d_padded, float* d_tiles, void* stream) {
     IRB_REQUIRE(h && d_in && d_padded && d_tiles, "irb_tiles_prepare: NULL argument");
     Model* m = h->model;
+    IRB_ON_DEVICE(m);
     RestorePlan P;
     IRB_TRY(make_plan(m, img_h, img_w, tile, overlap, nullptr, P));
     cudaStream_t s = (cudaStream_t)stream;
@@ -426,6 +454,7 @@ int irb_forward_tiles_cl(irb_handle* h, const float* d_in, float* d_out, int n_t
                          void* d_workspace, size_t workspace_bytes, void* stream) {
     IRB_REQUIRE(h && d_in && d_out && d_workspace && n_tiles > 0, "irb_forward_tiles_cl: bad argument");
     Model* m = h->model;
+    IRB_ON_DEVICE(m);
     const size_t need = m->forward_workspace(n_tiles, tile_h, tile_w);
     IRB_REQUIRE(workspace_bytes >= need, "irb_forward_tiles_cl: workspace too small");
     return m->forward(d_in, d_out, n_tiles, tile_h, tile_w, d_workspace, workspace_bytes, (cudaStream_t)stream);

@@ -459,13 +459,9 @@ int window_attention_tc(const bf16* qkv, long long ld, bf16* out, long long ldo,
     const int grid = p.units < sms ? p.units : sms;
     const size_t smem = 1024 + size_t(kWaStages) * kWaStage + 2 * kWaPBytes + 8 * 32 * 17 * 4 +
                         ((heads * kWaTabSize + 3) & ~3) * 4 + WB_COUNT * 8 + 64;
-    static bool attr_set = false;
-    if (!attr_set) {
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(window_attention_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(window_attention_tc_kernel<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        IRB_CHECK_CUDA(cudaFuncSetAttribute(window_attention_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set = true;
-    }
+    IRB_SMEM_OPTIN((window_attention_tc_kernel<0>), 227 * 1024);
+    IRB_SMEM_OPTIN((window_attention_tc_kernel<15>), 227 * 1024);
+    IRB_SMEM_OPTIN((window_attention_tc_kernel<16>), 227 * 1024);
     if (p.d == 30)
         window_attention_tc_kernel<15><<<grid, kWaThreads, smem, stream>>>(p);
     else if (p.d == 32)

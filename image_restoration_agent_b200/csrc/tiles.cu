@@ -118,13 +118,15 @@ int tiles_gather(const float* img, int c, int h, int w, const int* ys, const int
 // E/W of inference.py:309-320 / demo.py:142-153 as a gather: every output pixel sums the tiles that cover it in
 // the reference's loop order (h_idx outer, w_idx inner; fp32, starting from 0), and divides by their count.
 __global__ void tiles_stitch_kernel(const float* __restrict__ tiles, int c, int th, int tw, int sf, IdxLists L, int h,
-                                    int w, int crop_h, int crop_w, float* __restrict__ out_f32,
+                                    int w, int row0, int rows, int crop_w, float* __restrict__ out_f32,
                                     uint8_t* __restrict__ out_u8, int rev) {
+    // the launch covers output rows [row0, row0 + rows) (a rank's strip; the whole crop on one GPU); the outputs are
+    // strip-local: out_u8 [rows][crop_w][c], out_f32 [c][rows][crop_w]
     const int TH = th * sf, TW = tw * sf;
-    const long long total = (long long)crop_h * crop_w;
+    const long long total = (long long)rows * crop_w;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
-        const int oy = int(i / crop_w), ox = int(i % crop_w);
+        const int oy = row0 + int(i / crop_w), ox = int(i % crop_w);
         float e[3] = {0.f, 0.f, 0.f};
         float cnt = 0.f;
         for (int iy = 0; iy < L.ny; ++iy) {
@@ -150,21 +152,33 @@ __global__ void tiles_stitch_kernel(const float* __restrict__ tiles, int c, int 
     }
 }
 
-int tiles_stitch(const float* tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx, int h,
-                 int w, int crop_h, int crop_w, float* out_f32, uint8_t* out_u8, int u8_reverse_channels,
-                 cudaStream_t stream) {
+int tiles_stitch_rows(const float* tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx,
+                      int h, int w, int crop_h, int crop_w, int row0, int rows, float* out_f32, uint8_t* out_u8,
+                      int u8_reverse_channels, cudaStream_t stream) {
     IdxLists L;
     IRB_TRY(fill_idx(L, ys, xs, ny, nx));
     IRB_REQUIRE(c >= 1 && c <= 3 && sf >= 1, "tiles_stitch: 1..3 channels, sf >= 1");
     IRB_REQUIRE(crop_h <= h * sf && crop_w <= w * sf && crop_h > 0 && crop_w > 0, "tiles_stitch: crop outside the image");
-    const long long total = (long long)crop_h * crop_w;
+    IRB_REQUIRE(row0 >= 0 && rows >= 0 && row0 + rows <= crop_h, "tiles_stitch: row range outside the crop");
+    if (rows == 0) return 0;
+    const long long total = (long long)rows * crop_w;
     const int blocks = int(ceil_div_ll(total, 256) > 148 * 16 ? 148 * 16 : ceil_div_ll(total, 256));
-    tiles_stitch_kernel<<<blocks, 256, 0, stream>>>(tiles, c, th, tw, sf, L, h, w, crop_h, crop_w, out_f32, out_u8,
+    tiles_stitch_kernel<<<blocks, 256, 0, stream>>>(tiles, c, th, tw, sf, L, h, w, row0, rows, crop_w, out_f32, out_u8,
                                                     u8_reverse_channels);
     IRB_CHECK_CUDA(cudaGetLastError());
+    // algorithmic bytes: the tile rows that cover the strip, read once, + the strip written once
+    const double frac = double(rows) / crop_h;
     prof_mark("tiles_stitch", c, ny * nx, 0.0,
-              4.0 * ny * nx * th * tw * sf * sf * c + double(total) * c * ((out_f32 ? 4 : 0) + (out_u8 ? 1 : 0)), stream);
+              frac * 4.0 * ny * nx * th * tw * sf * sf * c + double(total) * c * ((out_f32 ? 4 : 0) + (out_u8 ? 1 : 0)),
+              stream);
     return 0;
+}
+
+int tiles_stitch(const float* tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx, int h,
+                 int w, int crop_h, int crop_w, float* out_f32, uint8_t* out_u8, int u8_reverse_channels,
+                 cudaStream_t stream) {
+    return tiles_stitch_rows(tiles, c, th, tw, sf, ys, xs, ny, nx, h, w, crop_h, crop_w, 0, crop_h, out_f32, out_u8,
+                             u8_reverse_channels, stream);
 }
 
 }  // namespace irb

@@ -166,6 +166,21 @@ def stitch(tiles, ys, xs, sf, h, w, crop_h, crop_w, want_u8=True, reverse_channe
     return out, u8
 
 
+def stitch_rows(tiles, ys, xs, sf, h, w, crop_h, crop_w, row0, rows, want_u8=True, want_f32=False,
+                reverse_channels=False, out_u8=None):
+    """Blend of output rows [row0, row0+rows) only (a rank's strip). `tiles` holds ALL tile slots [ny*nx, TH, TW, c];
+    only the tile rows covering the strip are read. -> (f32 [c, rows, crop_w] | None, u8 [rows, crop_w, c] | None)."""
+    nt, TH, TW, c = tiles.shape
+    th, tw = TH // sf, TW // sf
+    out = torch.empty((c, rows, crop_w), device=tiles.device, dtype=torch.float32) if want_f32 else None
+    u8 = out_u8 if out_u8 is not None else (
+        torch.empty((rows, crop_w, c), device=tiles.device, dtype=torch.uint8) if want_u8 else None)
+    check(_lib.load().irb_stitch_rows(tiles.data_ptr(), c, th, tw, sf, _lib.int_array(ys), _lib.int_array(xs),
+                                      len(ys), len(xs), h, w, crop_h, crop_w, row0, rows, _ptr(out), _ptr(u8),
+                                      int(reverse_channels), torch.cuda.current_stream(tiles.device).cuda_stream))
+    return out, u8
+
+
 def window_attention(qkv, C, heads, window, shift, bias_table):
     """qkv [n, H, W, 3*heads*dstride] (q pre-scaled) -> [n, H, W, C]."""
     n, H, W, C3 = qkv.shape

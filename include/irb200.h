@@ -85,6 +85,10 @@ void irb_destroy(irb_handle* h);
 /* options: "tile_batch" (max tiles per forward batch inside irb_restore_image; 0 = automatic) */
 int irb_set_option(irb_handle* h, const char* key, long long value);
 int irb_scale(const irb_handle* h); /* upscale factor (1 for Restormer / denoise) */
+/* Tiles per forward batch that irb_restore_image would use for n_tiles tiles of tile_h x tile_w (the "tile_batch"
+ * option, else the largest batch whose workspace stays under 40 GiB). Callers that drive irb_forward_tiles_cl
+ * themselves (multi-rank sharding) chunk their tile range by it. */
+int irb_tile_batch(irb_handle* h, int n_tiles, int tile_h, int tile_w, int* out_batch);
 
 /* model(x): x is [n, c, th, tw] fp32 NCHW (device), y is [n, c, th*s, tw*s] fp32 NCHW (device).
  * Restormer needs th, tw multiples of 8; SwinIR reflect-pads to the window internally like the reference. */
@@ -161,6 +165,14 @@ int irb_mdta_attn(const float* d_Gpart, const float* d_ssq_part, int nchunks, co
 int irb_stitch(const float* d_tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx,
                int h, int w, int crop_h, int crop_w, float* d_out_f32, uint8_t* d_out_u8, int reverse_channels,
                void* stream);
+/* The same blend restricted to output rows [row0, row0 + rows) of the crop — the strip one rank owns when the tiles
+ * of an image are sharded. d_tiles is still indexed by the GLOBAL tile number iy*nx+ix; only the tile
+ * rows that cover the strip are read, so a rank needs its own tiles plus its neighbours' seam rows in place.
+ * Outputs are strip-local: d_out_u8 [rows][crop_w][c], d_out_f32 [c][rows][crop_w]. Per pixel the tiles are summed
+ * in the reference's (h_idx, w_idx) order, so the strips concatenate to irb_stitch()'s result bit for bit. */
+int irb_stitch_rows(const float* d_tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx,
+                    int h, int w, int crop_h, int crop_w, int row0, int rows, float* d_out_f32, uint8_t* d_out_u8,
+                    int reverse_channels, void* stream);
 /* SwinIR (shifted-)window attention on a channels-last qkv tensor [n, H, W, 3*heads*dstride] (sections q | k | v,
  * head-major, dstride >= C/heads channels per head, q pre-multiplied by head_dim^-0.5):
  * out[n,H,W,C] = window_reverse(softmax(q k^T + rel_pos_bias + shift_mask) v), with the cyclic shift folded into

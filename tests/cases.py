@@ -6,6 +6,9 @@ R_CASES = {
     "restormer_small_biasfree_gray": lambda: configs.small_restormer_config("BiasFree", 1),
     "restormer_full_motion_deblur": lambda: configs.restormer_config("Motion_Deblurring"),
     "restormer_full_real_denoise": lambda: configs.restormer_config("Real_Denoising"),
+    # round 2: one tile of the benchmarked configurations (MDTA Gram K = 65 536 / 262 144), tools/make_golden_full.py
+    "restormer_cfg2_tile256": lambda: configs.restormer_config("Motion_Deblurring"),
+    "restormer_cfg5_tile512": lambda: configs.restormer_config("Real_Denoising"),
 }
 S_CASES = {
     "swinir_small_color_dn": lambda: configs.small_swinir_config("color_dn"),
@@ -17,6 +20,10 @@ S_CASES = {
     "swinir_small_realsr_x4": lambda: configs.small_swinir_config("real_sr", scale=4),
     "swinir_small_realsr_large_x4": lambda: configs.small_swinir_config("real_sr", scale=4, large_model=True),
     "swinir_full_gray_dn": lambda: configs.swinir_config("gray_dn"),
+    # round 2: full depth (36 / 54 STL) colour and SR models on 64x64 image-like inputs
+    "swinir_full_color_dn": lambda: configs.swinir_config("color_dn"),
+    "swinir_full_classical_x4": lambda: configs.swinir_config("classical_sr", scale=4),
+    "swinir_full_realsr_large_x4": lambda: configs.swinir_config("real_sr", scale=4, large_model=True),
 }
 
 
@@ -24,9 +31,11 @@ def tool_case(name, g):
     """-> (arch, cfg, state_dict, tile, overlap, scale) of a *_tool_* fixture."""
     tile = None if int(g["tile"]) < 0 else int(g["tile"])
     if name.startswith("restormer"):
-        cfg = configs.small_restormer_config("WithBias", 3)
+        cfg = (configs.restormer_config("Motion_Deblurring") if "cfg2crop" in name
+               else configs.small_restormer_config("WithBias", 3))
         return "restormer", cfg, synth.restormer_state_dict(cfg, seed=int(g["seed"])), tile, int(g["overlap"]), 1
     task = "classical_sr" if "classical_sr" in name else "color_dn"
     scale = int(g["scale"])
-    cfg = configs.small_swinir_config(task, scale=scale)
+    full = "full" in g.files and int(g["full"]) == 1
+    cfg = configs.swinir_config(task, scale=scale) if full else configs.small_swinir_config(task, scale=scale)
     return "swinir", cfg, synth.swinir_state_dict(cfg, seed=int(g["seed"])), tile, int(g["overlap"]), scale

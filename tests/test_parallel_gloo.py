@@ -96,3 +96,110 @@ def test_two_rank_tiled_restore_matches_reference_loop(tmp_path):
     mp.spawn(_tiled_worker, args=(2, _free_port(), out), nprocs=2, join=True)
     r = torch.load(out)
     assert (r["got"] - r["want"]).abs().max() <= 1e-6
+
+
+# ------------------------------------------------------------------------------------------------------------
+# strip path: local blend of owned rows + seam exchange + uint8 strip gather (parallel.restore_strips)
+# ------------------------------------------------------------------------------------------------------------
+class _CpuEngine:
+    """CPU stand-in with the Engine methods restore_strips() uses. The 'model' is a fixed per-tile function with an
+    upscale factor, the blend is the reference's E/W accumulation restricted to a row range."""
+
+    def __init__(self, scale=1, c=3):
+        self.scale, self.channels = scale, c
+
+    def plan(self, h, w, tile, overlap):
+        from oracle import tiling
+        t = min(tile, h, w)
+        return dict(hp=h, wp=w, th=t, tw=t, ys=tiling.tile_indices(h, t, overlap), xs=tiling.tile_indices(w, t, overlap),
+                    scale=self.scale, c=self.channels, h=h, w=w)
+
+    def prepare_tiles(self, img, plan, tile, overlap, bgr=False):
+        x = img.float() / 255.0
+        t = plan["th"]
+        return torch.stack([x[y:y + t, xx:xx + t] for y in plan["ys"] for xx in plan["xs"]]).contiguous()
+
+    def forward_cl(self, tiles, out=None):
+        s = self.scale
+        y = (tiles * 0.75 + tiles.flip(1) * 0.5 - 0.1 * tiles.mean(dim=(1, 2, 3), keepdim=True))
+        y = y.repeat_interleave(s, 1).repeat_interleave(s, 2)
+        if out is None:
+            return y
+        out.copy_(y)
+        return out
+
+    def stitch_rows(self, slots, plan, row0, rows, bgr=False, want_f32=False, out_u8=None):
+        s, t = plan["scale"], plan["th"] * plan["scale"]
+        H, W, c = plan["h"] * s, plan["w"] * s, plan["c"]
+        E = torch.zeros(rows, W, c)
+        cnt = torch.zeros(rows, W, 1)
+        k = 0
+        for y in plan["ys"]:
+            for xx in plan["xs"]:
+                a, b = max(row0, y * s), min(row0 + rows, y * s + t)
+                if b > a:
+                    E[a - row0:b - row0, xx * s:xx * s + t] += slots[k, a - y * s:b - y * s]
+                    cnt[a - row0:b - row0, xx * s:xx * s + t] += 1
+                k += 1
+        f = E / cnt
+        u8 = torch.round(f.clamp(0, 1) * 255.0).to(torch.uint8)
+        if bgr:
+            u8 = u8.flip(2)
+        if out_u8 is not None:
+            out_u8.copy_(u8)
+            u8 = out_u8
+        return u8, (f if want_f32 else None)
+
+
+def _strip_worker(rank, world, port, h, w, tile, ov, scale, out_path):
+    sys.path.insert(0, ROOT)
+    from image_restoration_agent_b200 import parallel, synth
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    eng = _CpuEngine(scale=scale)
+    img = torch.from_numpy(synth.synthetic_image_u8(h, w, 3, seed=4))
+    got, stats = parallel.restore_strips(eng, img, tile, ov, bgr=True)
+    if rank == 0:
+        # single-process result: every tile computed here, the whole image blended at once
+        plan = eng.plan(h, w, tile, ov)
+        slots = eng.forward_cl(eng.prepare_tiles(img, plan, tile, ov))
+        want, _ = eng.stitch_rows(slots, plan, 0, h * scale, bgr=True)
+        torch.save({"got": got, "want": want, "stats": stats}, out_path)
+    else:
+        assert got is None
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,h,w,tile,ov,scale", [(2, 40, 56, 24, 8, 1), (2, 33, 47, 16, 4, 2), (3, 64, 40, 24, 8, 1),
+                                                     (2, 24, 24, 24, 8, 1)])
+def test_strip_path_bit_identical_to_single_process(tmp_path, world, h, w, tile, ov, scale):
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_strip_worker, args=(world, _free_port(), h, w, tile, ov, scale, out), nprocs=world, join=True)
+    r = torch.load(out)
+    assert r["got"].shape == (h * scale, w * scale, 3) and torch.equal(r["got"], r["want"])
+    if h > tile:
+        assert r["stats"]["gather_bytes"] > 0
+
+
+def test_seam_messages_cover_exactly_the_foreign_rows():
+    """Every (output row, covering tile) pair is either local to the row's owner or delivered by exactly one message."""
+    from image_restoration_agent_b200.parallel import partition, seam_messages, strip_rows
+    plan = dict(scale=1, th=512, tw=512, ys=[0, 448, 896, 1344, 1648],
+                xs=[0, 448, 896, 1344, 1792, 2240, 2688, 3136, 3328], h=2160, w=3840, c=3)   # cfg5 (SURVEY §8a T4)
+    for world in (2, 4, 8):
+        nt = 45
+        owner = [r for r, (lo, hi) in enumerate(partition(nt, world)) for _ in range(lo, hi)]
+        have = {}
+        for src, q, t, a, b in seam_messages(plan, world):
+            assert owner[t] == src and src != q and 0 <= a < b <= 512
+            for row in (a, b - 1):
+                assert (q, t, row) not in have
+                have[(q, t, row)] = 1
+        for q, (r0, r1) in enumerate(strip_rows(2160, world)):
+            for t in range(nt):
+                top = plan["ys"][t // 9]
+                a, b = max(r0, top), min(r1, top + 512)
+                if b > a and owner[t] != q:
+                    assert (q, t, a - top) in have and (q, t, b - 1 - top) in have

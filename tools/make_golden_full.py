@@ -1,0 +1,151 @@
+"""Round-2 golden fixtures: the UNMODIFIED reference at the sizes and depths that bench.py measures.
+
+Runs only in the build container (needs /root/reference); `python tools/make_golden_full.py [group ...]`.
+Groups:
+  restormer_tiles : Restormer Motion_Deblurring on the first 256x256 tile of the cfg2 image (Gram K = 65 536) and
+                    Real_Denoising (BiasFree) on the first 512x512 tile of the cfg5 image (K = 262 144)
+  swinir_full     : full-depth SwinIR-M color_dn, SwinIR-M classical_sr x4 (cfg3's model) and SwinIR-L real_sr x4
+                    (9 RSTB, C = 240, 3conv) on 64x64 image-like inputs
+  tool_cfg2       : tool-level crop of cfg2 (480x480, tile 256 / overlap 32 -> 2x2 tiles), full Restormer
+  swinir_test     : the SwinIR tool fixtures with the tile loop run by the reference's OWN test()
+                    (SwinIR/inference.py:294-322, imported with the timm shim), pad / crop / quantise of
+                    inference.py:76-90 around it; oracle/tiling.py must reproduce them bit for bit
+Every case asserts oracle == reference before the fixture is written.
+"""
+import os
+import sys
+import time
+import types
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import make_golden as mg  # noqa: E402  (sets sys.path, REF paths, shim)
+
+from image_restoration_agent_b200 import configs, synth  # noqa: E402
+from oracle import restormer_ref, swinir_ref, tiling  # noqa: E402
+
+
+def image_like(h, w, c, seed):
+    """[1, c, h, w] fp32 in [0,1] from the bench's synthetic uint8 image (same generator, same seed)."""
+    img = synth.synthetic_image_u8(h, w, c, seed=seed)
+    return torch.from_numpy(img).float().div(255.0).permute(2, 0, 1).unsqueeze(0).contiguous()
+
+
+def restormer_tiles():
+    for name, task, full, t in (("restormer_cfg2_tile256", "Motion_Deblurring", (720, 1280), 256),
+                                ("restormer_cfg5_tile512", "Real_Denoising", (2160, 3840), 512)):
+        print(name)
+        cfg = configs.restormer_config(task)
+        sd = synth.restormer_state_dict(cfg, seed=0)
+        ref = mg.ref_restormer(cfg, sd)
+        x = image_like(full[0], full[1], 3, seed=0)[..., :t, :t].contiguous()
+        t0 = time.time()
+        with torch.no_grad():
+            y_ref = ref(x)
+        print(f"  reference forward {time.time() - t0:.1f} s")
+        y_or = restormer_ref.Model(sd, cfg)(x)
+        mg.check(name, y_or, y_ref)
+        mg.save(name, x=x.numpy(), y=y_ref.numpy(), seed=np.int64(0))
+
+
+def swinir_full():
+    cases = [
+        ("swinir_full_color_dn", configs.swinir_config("color_dn"), 0),
+        ("swinir_full_classical_x4", configs.swinir_config("classical_sr", scale=4), 0),
+        ("swinir_full_realsr_large_x4", configs.swinir_config("real_sr", scale=4, large_model=True), 0),
+    ]
+    for name, cfg, seed in cases:
+        print(name)
+        sd = synth.swinir_state_dict(cfg, seed=seed)
+        ref = mg.ref_swinir(cfg, sd)
+        x = image_like(512, 512, 3, seed=0)[..., 100:164, 200:264].contiguous()
+        t0 = time.time()
+        with torch.no_grad():
+            y_ref = ref(x)
+        print(f"  reference forward {time.time() - t0:.1f} s, out {tuple(y_ref.shape)}")
+        y_or = swinir_ref.Model(sd, cfg)(x)
+        mg.check(name, y_or, y_ref, tol=5e-5)
+        mg.save(name, x=x.numpy(), y=y_ref.numpy(), seed=np.int64(seed))
+
+
+def tool_cfg2():
+    name = "restormer_tool_cfg2crop_t256_o32"
+    print(name)
+    cfg = configs.restormer_config("Motion_Deblurring")
+    sd = synth.restormer_state_dict(cfg, seed=0)
+    ref = mg.ref_restormer(cfg, sd)
+    img = np.ascontiguousarray(synth.synthetic_image_u8(720, 1280, 3, seed=0)[:480, :480])
+    u8_ref = tiling.restormer_restore_image(img, ref, 256, 32)
+    f_ref = tiling.restormer_restore_image(img, ref, 256, 32, return_float=True)
+    u8_or = tiling.restormer_restore_image(img, restormer_ref.Model(sd, cfg), 256, 32)
+    d = np.abs(u8_or.astype(int) - u8_ref.astype(int)).max()
+    print(f"  uint8 oracle vs reference: max LSB diff = {d}")
+    assert d <= 1
+    mg.save(name, img=img, out_u8=u8_ref, out_f32=f_ref.numpy(), seed=np.int64(0), tile=np.int64(256),
+            overlap=np.int64(32))
+
+
+def reference_swinir_tool(img_bgr_u8, model, scale, window_size, tile, overlap, ref_test):
+    """inference.py:69-90 around the reference's own test(): returns (uint8 HWC BGR, float CHW RGB un-clamped)."""
+    args = types.SimpleNamespace(tile=tile, tile_overlap=overlap, scale=scale)
+    img_lq = img_bgr_u8.astype(np.float32) / 255.0                                            # :240
+    img_lq = np.transpose(img_lq if img_lq.shape[2] == 1 else img_lq[:, :, [2, 1, 0]], (2, 0, 1))  # :70
+    img_lq = torch.from_numpy(np.ascontiguousarray(img_lq)).float().unsqueeze(0)                # :71
+    with torch.no_grad():
+        _, _, h_old, w_old = img_lq.size()
+        h_pad = (h_old // window_size + 1) * window_size - h_old
+        w_pad = (w_old // window_size + 1) * window_size - w_old
+        img_lq = torch.cat([img_lq, torch.flip(img_lq, [2])], 2)[:, :, :h_old + h_pad, :]
+        img_lq = torch.cat([img_lq, torch.flip(img_lq, [3])], 3)[:, :, :, :w_old + w_pad]
+        output = ref_test(img_lq, model, args, window_size)                                    # :81 the reference's
+        output = output[..., :h_old * scale, :w_old * scale]
+    f = output[0].clone()
+    o = output.data.squeeze().float().cpu().clamp_(0, 1).numpy()
+    if o.ndim == 3:
+        o = np.transpose(o[[2, 1, 0], :, :], (1, 2, 0))
+    return (o * 255.0).round().astype(np.uint8), f
+
+
+def swinir_test():
+    mg.install_timm_shim()
+    sys.path.insert(0, mg.SW)
+    import inference as ref_inference  # the reference script; main() is behind a __main__ guard
+
+    for task, scale, tile, ov, full in (("color_dn", 1, None, 32, False), ("color_dn", 1, 16, 8, False),
+                                        ("classical_sr", 4, 16, 8, False), ("color_dn", 1, 64, 32, True)):
+        if full:  # full-depth SwinIR-M, 104x88 image -> 112x96 padded, tile 64 / overlap 32 -> 3x2 tiles
+            cfg = configs.swinir_config(task, scale=scale)
+            img = np.ascontiguousarray(synth.synthetic_image_u8(512, 512, 3, seed=0)[40:144, 60:148])
+            name = f"swinir_tool_full_{task}_x{scale}_t{tile}_o{ov}"
+        else:
+            cfg = configs.small_swinir_config(task, scale=scale)
+            img = synth.synthetic_image_u8(30, 27, 3, seed=5)
+            name = f"swinir_tool_small_{task}_x{scale}_t{tile}_o{ov}"
+        print(name)
+        sd = synth.swinir_state_dict(cfg, seed=7)
+        ref = mg.ref_swinir(cfg, sd)
+        u8_ref, f_ref = reference_swinir_tool(img, ref, scale, cfg["window_size"], tile, ov, ref_inference.test)
+        # the restated tile loop must be the same function
+        u8_t = tiling.swinir_process_image(img, ref, scale, cfg["window_size"], tile, ov)
+        f_t = tiling.swinir_process_image(img, ref, scale, cfg["window_size"], tile, ov, return_float=True)
+        assert np.array_equal(u8_t, u8_ref) and torch.equal(f_t, f_ref), "oracle/tiling.py != inference.test()"
+        u8_or = tiling.swinir_process_image(img, swinir_ref.Model(sd, cfg), scale, cfg["window_size"], tile, ov)
+        d = np.abs(u8_or.astype(int) - u8_ref.astype(int)).max()
+        print(f"  tiling.py == inference.test() bit-exact; uint8 oracle model vs reference: max LSB diff = {d}")
+        assert d <= 1
+        mg.save(name, img=img, out_u8=u8_ref, out_f32=f_ref.numpy(), seed=np.int64(7),
+                tile=np.int64(-1 if tile is None else tile), overlap=np.int64(ov), scale=np.int64(scale),
+                full=np.int64(int(full)))
+
+
+GROUPS = {"restormer_tiles": restormer_tiles, "swinir_full": swinir_full, "tool_cfg2": tool_cfg2,
+          "swinir_test": swinir_test}
+
+if __name__ == "__main__":
+    torch.manual_seed(0)
+    torch.set_num_threads(os.cpu_count() or 8)
+    for g in (sys.argv[1:] or list(GROUPS)):
+        GROUPS[g]()
+    print("done")
