@@ -47,6 +47,9 @@ struct Model {
     int cin = 3;
     int scale = 1;
     long long tile_batch = 0;
+    // 1: tile % window_size == 0 is required like the SwinIR script (inference.py:302); 0: the SwinIR service path
+    // (model_serving.py:146-166 has no such assert: the model reflect-pads ragged tiles itself). Restormer always checks.
+    int strict_tile = 1;
     std::vector<void*> dev_allocs;
     virtual ~Model();
     // model(x) on channels-last fp32 tiles: in [n,H,W,cin] -> out [n,H*s,W*s,cin]

@@ -243,7 +243,8 @@ static int make_plan(Model* m, int img_h, int img_w, int tile, int overlap, void
         int t = tile < P.hp ? tile : P.hp;
         t = t < P.wp ? t : P.wp;
         // inference.py:302 / demo.py:136
-        IRB_REQUIRE(t % m->tile_multiple() == 0, "tile size should be a multiple of window_size (SwinIR) / 8 (Restormer)");
+        IRB_REQUIRE((m->desc.arch == IRB_ARCH_SWINIR && !m->strict_tile) || t % m->tile_multiple() == 0,
+                    "tile size should be a multiple of window_size (SwinIR) / 8 (Restormer)");
         IRB_REQUIRE(overlap >= 0 && overlap < t, "tile_overlap must be smaller than the tile");
         P.th = P.tw = t;
         IRB_REQUIRE((P.hp - t) / (t - overlap) + 2 <= 128 && (P.wp - t) / (t - overlap) + 2 <= 128,
@@ -333,6 +334,10 @@ int irb_set_option(irb_handle* h, const char* key, long long value) {
     if (strcmp(key, "tile_batch") == 0) {
         IRB_REQUIRE(value >= 0, "tile_batch must be >= 0");
         h->model->tile_batch = value;
+        return 0;
+    }
+    if (strcmp(key, "strict_tile") == 0) {
+        h->model->strict_tile = value != 0;
         return 0;
     }
     set_error(std::string("irb_set_option: unknown key ") + key);

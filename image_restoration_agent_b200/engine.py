@@ -73,6 +73,7 @@ class Engine:
         self._h = h
         self.scale = self.lib.irb_scale(h)
         self.channels = desc.in_chans
+        self.strict_tile = True   # False: the Flask service's process_image semantics (ragged SwinIR tiles allowed)
         self._ws = None
         self._ws_gen = 0          # bumped when the workspace is re-allocated: captured graphs hold its address
         self._graphs: dict = {}
@@ -130,6 +131,7 @@ class Engine:
     # ---- the whole tool body for one image ----
     def _restore_call(self, img, fmt, bgr, h, w, t, tile_overlap, u8, f32):
         need = C.c_size_t()
+        check(self.lib.irb_set_option(self._h, b"strict_tile", int(self.strict_tile)))
         check(self.lib.irb_restore_workspace_bytes(self._h, h, w, t, tile_overlap, C.byref(need)))
         ws = self._workspace(need.value)
         check(self.lib.irb_restore_image(self._h, img.data_ptr(), fmt, int(bgr), h, w, t, tile_overlap,

@@ -128,12 +128,13 @@ def seam_messages(plan: dict, world: int) -> List[Tuple[int, int, int, int, int]
 
 
 def restore_strips(engine, img: torch.Tensor, tile=None, tile_overlap: int = 32, bgr: bool = False, dst: int = 0,
-                   group=None):
+                   group=None, solo: bool = False):
     """One image over all ranks. `engine` needs plan / prepare_tiles / forward_cl(tiles, out=) / stitch_rows
     (Engine, or a CPU stand-in in the gloo tests). Returns the uint8 image [H*s, W*s, c] on dst, None elsewhere,
-    plus a dict of the bytes that crossed the wire."""
-    world = dist.get_world_size(group) if dist.is_initialized() else 1
-    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    plus a dict of the bytes that crossed the wire. solo=True runs the same code as a single rank even inside an
+    initialised process group (bench.py's N = 1 leg of the strong-scaling pair)."""
+    world = dist.get_world_size(group) if dist.is_initialized() and not solo else 1
+    rank = dist.get_rank(group) if dist.is_initialized() and not solo else 0
     if img.dtype == torch.uint8:
         h, w, _ = img.shape
     else:

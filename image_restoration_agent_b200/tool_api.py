@@ -13,7 +13,10 @@ INTEGRATION.md shows the three-line change that registers these classes in the r
 """
 from __future__ import annotations
 
+import hashlib
+import json
 import os
+import threading
 import time
 from pathlib import Path
 from typing import Optional
@@ -25,28 +28,45 @@ from .engine import Engine
 from .weights import load_checkpoint
 
 _ENGINES: dict = {}
+_ENGINES_LOCK = threading.Lock()
 
 
-def get_engine(arch: str, key: str, cfg: dict, state_dict_fn, precision: str = "bf16", device: int = 0) -> Engine:
-    k = (arch, key, precision, device)
-    if k not in _ENGINES:
-        _ENGINES[k] = Engine(arch, cfg, state_dict_fn(), precision=precision, device=device)
-    return _ENGINES[k]
+def _cfg_digest(cfg: dict) -> str:
+    return hashlib.sha1(json.dumps(cfg, sort_keys=True, default=str).encode()).hexdigest()[:16]
+
+
+def get_engine(arch: str, source, cfg: dict, state_dict_fn, precision: str = "bf16", device: int = 0) -> Engine:
+    """Resident engines, one per (arch, weights source, config, precision, device). `source` is the resolved
+    checkpoint path (str) or the caller's in-memory state_dict object; for the latter the cache entry keeps a
+    reference to it, so its id() cannot be recycled for other weights while the entry lives. Thread-safe: Flask
+    worker threads racing on a cold cache build one engine."""
+    src_key = ("path", os.path.abspath(source)) if isinstance(source, (str, os.PathLike)) else ("obj", id(source))
+    k = (arch, src_key, _cfg_digest(cfg), precision, int(device))
+    with _ENGINES_LOCK:
+        hit = _ENGINES.get(k)
+        if hit is None:
+            hit = (Engine(arch, cfg, state_dict_fn(), precision=precision, device=device), source)
+            _ENGINES[k] = hit
+        return hit[0]
 
 
 def clear_engines():
-    for e in _ENGINES.values():
-        e.close()
-    _ENGINES.clear()
+    with _ENGINES_LOCK:
+        for e, _ in _ENGINES.values():
+            e.close()
+        _ENGINES.clear()
 
 
-class Tool:
-    """Pre/post-conditions of the reference Tool (tool.py:33-62): `input_dir` holds exactly one file, `output_dir`
-    is empty before and holds exactly `output.png` after."""
+class _LocalTool:
+    """Mirror of the reference Tool's pre/post-conditions (tool.py:33-62), used only when the reference package is
+    not importable: `input_dir` holds exactly one file, `output_dir` is empty before and holds exactly `output.png`
+    after."""
 
-    def __init__(self, tool_name: str, subtask: str):
+    def __init__(self, tool_name: str, subtask: str, work_dir=None, script_rel_path=None):
         self.tool_name = tool_name
         self.subtask = subtask
+        self.work_dir = None
+        self.script_path = None
 
     def __call__(self, input_dir: Path, output_dir: Path, silent: bool = False, *args) -> None:
         input_dir, output_dir = Path(input_dir), Path(output_dir)
@@ -76,6 +96,19 @@ class Tool:
 
     def _invoke(self, *args) -> None:
         raise NotImplementedError
+
+
+def _reference_tool_base():
+    """Inside the reference process (AgenticIR/ on sys.path) the B200 tools subclass the reference's own
+    executor.tool.Tool, so isinstance checks and the toolbox lists (`list[Tool]`) accept them unchanged."""
+    try:
+        from executor.tool import Tool as RefTool  # noqa: PLC0415
+        return RefTool
+    except Exception:  # noqa: BLE001  (package absent, or its heavy imports unavailable)
+        return None
+
+
+Tool = _reference_tool_base() or _LocalTool
 
 
 def _imread(path, flags):
@@ -115,16 +148,24 @@ class SwinIRB200(Tool):
         def sd():
             if self.state_dict is not None:
                 return self.state_dict
-            return load_checkpoint(os.path.join(self.model_zoo, self.model_name), ("params", "params_ema"))
-        return get_engine("swinir", self.tool_name + str(id(self.state_dict)), self.cfg, sd, self.precision, self.device)
+            # define_model(): 'params_ema' for real_sr, 'params' otherwise, bare dict if absent (inference.py:165,197-198)
+            keys = ("params_ema",) if self.opt_task == "real_sr" else ("params",)
+            return load_checkpoint(os.path.join(self.model_zoo, self.model_name), keys)
+        src = self.state_dict if self.state_dict is not None else os.path.join(self.model_zoo, self.model_name)
+        return get_engine("swinir", src, self.cfg, sd, self.precision, self.device)
+
+    def restore_u8_device(self, img_bgr, graph: bool = False):
+        """uint8 [H,W,3] BGR on the GPU (what cv2.imread of input.png holds) -> uint8 [sH,sW,3] BGR on the GPU (what
+        output.png would hold): the tool body without the file system (Chain keeps the hand-off in HBM)."""
+        return self._engine().restore_device(img_bgr, self.tile, self.tile_overlap, bgr=True, graph=graph)[0]
 
     def _invoke(self) -> None:
         import cv2
 
-        path = sorted(self.input_dir.glob("*"))[0]
+        path = sorted(Path(self.input_dir).glob("*"))[0]
         img = _imread(path, cv2.IMREAD_COLOR)  # uint8 HWC BGR; /255 happens on the device (inference.py:240)
         out = self._engine().restore(img, self.tile, self.tile_overlap, bgr=True)
-        cv2.imwrite(str(self.output_dir / "output.png"), out)
+        cv2.imwrite(str(Path(self.output_dir) / "output.png"), out)
 
 
 class RestormerB200(Tool):
@@ -155,18 +196,84 @@ class RestormerB200(Tool):
             if self.state_dict is not None:
                 return self.state_dict
             return load_checkpoint(os.path.join(self.weights_root, self.WEIGHTS[self.opt_task]), ("params",))
-        return get_engine("restormer", self.opt_task + str(id(self.state_dict)), self.cfg, sd, self.precision,
-                          self.device)
+        src = (self.state_dict if self.state_dict is not None
+               else os.path.join(self.weights_root, self.WEIGHTS[self.opt_task]))
+        return get_engine("restormer", src, self.cfg, sd, self.precision, self.device)
+
+    def restore_u8_device(self, img_bgr, graph: bool = False):
+        """uint8 [H,W,3] BGR (or [H,W,1] gray) on the GPU -> restored uint8 of the same layout on the GPU."""
+        gray = self.cfg["inp_channels"] == 1
+        return self._engine().restore_device(img_bgr, self.tile, self.tile_overlap, bgr=not gray, graph=graph)[0]
 
     def _invoke(self) -> None:
         import cv2
 
-        path = sorted(self.input_dir.glob("*"))[0]
+        path = sorted(Path(self.input_dir).glob("*"))[0]
         gray = self.cfg["inp_channels"] == 1
         img = _imread(path, cv2.IMREAD_GRAYSCALE if gray else cv2.IMREAD_COLOR)  # demo.py:40-47
         # the reference converts BGR->RGB, restores, converts back: same as running on BGR with channel reversal
         out = self._engine().restore(img, self.tile, self.tile_overlap, bgr=not gray)
-        cv2.imwrite(str(self.output_dir / "output.png"), out)
+        cv2.imwrite(str(Path(self.output_dir) / "output.png"), out)
+
+
+class Chain:
+    """A plan of several tools run back to back on one image (BASELINE config 4: derain -> denoise -> x4 SR) with the
+    inter-stage hand-off kept in HBM.
+
+    The reference chains tools through files: every tool writes a uint8 `output.png`, which is copied to the next
+    tool's `input.png` (AgenticIR/executor/tool.py:56-62, AgentApp/agentic_api.py:200-210), so the image is QUANTISED
+    to uint8 between stages. PNG is lossless, hence the next stage sees exactly the uint8 array the
+    previous one produced: here that array simply stays on the GPU. Decode once, H2D once, D2H once, encode once;
+    the bytes equal the file-based chain's."""
+
+    def __init__(self, tools):
+        self.tools = list(tools)
+        assert self.tools, "empty chain"
+
+    def run_device(self, img_bgr_u8, graph: bool = False):
+        x = img_bgr_u8
+        for k, tool in enumerate(self.tools):
+            x = tool.restore_u8_device(x, graph=graph)
+            if graph and k + 1 < len(self.tools):
+                # a graph's output buffer is static: the next call of the SAME tool would overwrite it in place
+                # only when one tool appears twice in a chain
+                if any(t is tool for t in self.tools[k + 1:]):
+                    x = x.clone()
+        return x
+
+    def run(self, img_bgr_u8: np.ndarray, graph: bool = False) -> np.ndarray:
+        import torch
+
+        dev = f"cuda:{self.tools[0].device}"
+        d = torch.from_numpy(np.ascontiguousarray(img_bgr_u8)).to(dev, non_blocking=True)
+        return self.run_device(d, graph=graph).cpu().numpy()
+
+    def __call__(self, input_dir: Path, output_dir: Path, silent: bool = False) -> None:
+        """Same contract as Tool.__call__ (one file in, `output.png` out) for the whole chain."""
+        import cv2
+
+        input_dir, output_dir = Path(input_dir), Path(output_dir)
+        assert len(os.listdir(input_dir)) == 1, "The input directory should contain the input only."
+        assert os.listdir(output_dir) == [], "The output directory should be empty."
+        start = time.time()
+        img = _imread(sorted(input_dir.glob("*"))[0], cv2.IMREAD_COLOR)
+        out = self.run(img)
+        cv2.imwrite(str(output_dir / "output.png"), out)
+        if not silent:
+            print(f"Chain\t: {' -> '.join(t.tool_name for t in self.tools)}")
+            print(f"Output\t: {output_dir / 'output.png'}")
+            print(f"Time\t: {round(time.time() - start, 3)}s")
+
+
+class _strict_tile:
+    def __init__(self, eng: Engine, value: bool):
+        self.eng, self.value = eng, value
+
+    def __enter__(self):
+        self.prev, self.eng.strict_tile = self.eng.strict_tile, self.value
+
+    def __exit__(self, *exc):
+        self.eng.strict_tile = self.prev
 
 
 def process_image(img_lq: np.ndarray, model: Engine, scale: int, window_size: int, tile=None, tile_overlap=32):
@@ -177,7 +284,8 @@ def process_image(img_lq: np.ndarray, model: Engine, scale: int, window_size: in
     assert model.scale == scale and model.cfg["window_size"] == window_size
     x = np.transpose(img_lq if img_lq.shape[2] == 1 else img_lq[:, :, [2, 1, 0]], (2, 0, 1))
     d = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).to(f"cuda:{model.device}")
-    u8, _ = model.restore_device(d, tile, tile_overlap, bgr=(img_lq.shape[2] == 3))
+    with _strict_tile(model, False):  # model_serving.py:146-166 has no tile % window_size assert
+        u8, _ = model.restore_device(d, tile, tile_overlap, bgr=(img_lq.shape[2] == 3))
     out = u8.cpu().numpy()
     return out[:, :, 0] if out.shape[2] == 1 else out
 
@@ -202,8 +310,9 @@ class RestormerService:
                 return self.state_dict
             name = os.path.basename(RestormerB200.WEIGHTS[task])
             return load_checkpoint(os.path.join(self.weights_dir, name), ("params",))
-        return get_engine("restormer", "svc_" + task + str(id(self.state_dict)), self.cfg, sd, self.precision,
-                          self.device)
+        src = (self.state_dict if self.state_dict is not None
+               else os.path.join(self.weights_dir, os.path.basename(RestormerB200.WEIGHTS[task])))
+        return get_engine("restormer", src, self.cfg, sd, self.precision, self.device)
 
     def restore_image(self, img_bytes: bytes, task: str, tile=None, tile_overlap=32) -> bytes:
         import cv2

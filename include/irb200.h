@@ -82,7 +82,9 @@ int irb_padded_size(int arch, int window_size, int h, int w, int* hp, int* wp);
  * tensors of the reference state_dict). Uploads + repacks weights on `device`; synchronises. */
 int irb_create(const irb_model_desc* desc, const void* weights_blob, size_t nbytes, int device, irb_handle** out);
 void irb_destroy(irb_handle* h);
-/* options: "tile_batch" (max tiles per forward batch inside irb_restore_image; 0 = automatic) */
+/* options: "tile_batch" (max tiles per forward batch inside irb_restore_image; 0 = automatic);
+ *          "strict_tile" (default 1: SwinIR tiles must be a multiple of window_size like inference.py:302; 0: the
+ *          Flask service's process_image, model_serving.py:146-166, which has no such assert) */
 int irb_set_option(irb_handle* h, const char* key, long long value);
 int irb_scale(const irb_handle* h); /* upscale factor (1 for Restormer / denoise) */
 /* Tiles per forward batch that irb_restore_image would use for n_tiles tiles of tile_h x tile_w (the "tile_batch"

@@ -1,8 +1,10 @@
 """GPU (-m gpu): the CUDA path behind the C ABI against the reference outputs in tests/golden/ and against the oracle.
 
 Tolerances (north_star): fp32 mode <= 1e-4 max-abs on the [0,1] scale; bf16 mode <= 2e-2 max-abs and PSNR >= 45 dB;
-tile indexing / blend weights bit-exact; uint8 within 1 LSB of the reference in fp32 mode, and within
-1 + ceil(255 * max_abs_float_error) LSB in bf16 mode (a 2e-2 float budget cannot guarantee 1 LSB after quantisation).
+tile indexing / blend weights bit-exact; uint8 within 1 LSB of the reference in fp32 mode. In bf16 mode the north_star
+asks for 1 LSB as well, which its own 2e-2 float budget cannot guarantee: two floats e apart quantise at most
+floor(255 e) + 1 levels apart, so the tests assert exactly that bound with the MEASURED e, plus >= 97 % of the pixels
+within 1 LSB, and print the LSB histogram (DESIGN.md §2 records the measured distributions at the BASELINE sizes).
 """
 import glob
 import math
@@ -39,6 +41,7 @@ def test_restormer_forward_matches_reference(name, prec, golden_dir):
     eng = _engine("restormer", cfg, synth.restormer_state_dict(cfg, seed=int(g["seed"])), prec)
     y = eng(torch.from_numpy(g["x"]).cuda()).cpu().numpy()
     assert np.isfinite(y).all()
+    print(f"\n[parity] {name} {prec}: max-abs {np.abs(y - g['y']).max():.2e}, PSNR {psnr(y, g['y']):.1f} dB")
     assert np.abs(y - g["y"]).max() <= TOL[prec]
     if prec == "bf16":
         assert psnr(y, g["y"]) >= 45.0
@@ -53,6 +56,7 @@ def test_swinir_forward_matches_reference(name, prec, golden_dir):
     eng = _engine("swinir", cfg, synth.swinir_state_dict(cfg, seed=int(g["seed"])), prec)
     y = eng(torch.from_numpy(g["x"]).cuda()).cpu().numpy()
     assert y.shape == g["y"].shape and np.isfinite(y).all()
+    print(f"\n[parity] {name} {prec}: max-abs {np.abs(y - g['y']).max():.2e}, PSNR {psnr(y, g['y']):.1f} dB")
     assert np.abs(y - g["y"]).max() <= TOL[prec]
     if prec == "bf16":
         assert psnr(y, g["y"]) >= 45.0
@@ -75,8 +79,13 @@ def test_tool_body_matches_reference(name, prec, golden_dir):
     f = f32.cpu().numpy()
     err = float(np.abs(f - g["out_f32"]).max())
     assert err <= TOL[prec]
-    lsb = int(np.abs(u8.cpu().numpy().astype(int) - g["out_u8"].astype(int)).max())
-    assert lsb <= (1 if prec == "fp32" else 1 + math.ceil(255 * err))
+    d = np.abs(u8.cpu().numpy().astype(int) - g["out_u8"].astype(int))
+    lsb = int(d.max())
+    hist = np.bincount(d.ravel(), minlength=4)[:8].tolist()
+    print(f"\n[parity] {name} {prec}: max-abs {err:.2e}, PSNR {psnr(f, g['out_f32']):.1f} dB, uint8 LSB histogram {hist}")
+    assert lsb <= (1 if prec == "fp32" else 1 + math.floor(255 * err))
+    if prec == "bf16":
+        assert (d <= 1).mean() >= 0.97 and psnr(f, g["out_f32"]) >= 45.0
     # host API (H2D + D2H inside) gives the same bytes
     assert np.array_equal(eng.restore(g["img"], tile, overlap, bgr=(arch == "swinir")), u8.cpu().numpy())
     eng.close()
@@ -117,7 +126,7 @@ def test_restormer_cfg2_full_size_properties():
     # (1) determinism / idempotence of the pipeline
     u8b, f32b = eng.restore_device(img, 256, 32, want_f32=True)
     assert torch.equal(u8, u8b)
-    # (2) tile_batch does not change the result beyond split-K atomics order
+    # (2) tile_batch changes the Gram's split-K chunking (fp32 sum order), nothing else
     eng.set_tile_batch(5)
     _, f32c = eng.restore_device(img, 256, 32, want_f32=True)
     assert (f32c - f32).abs().max().item() <= 2e-3
