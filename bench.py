@@ -354,7 +354,8 @@ class Job:
     """The engines of a workload's stages and one step over a list of device images (the chain keeps the uint8
     hand-off between stages in HBM, T7 semantics)."""
 
-    def __init__(self, name, device, tile_batch=0, graph=False):
+    def __init__(self, name, device, tile_batch=0, graph=False, options=()):
+        from image_restoration_agent_b200._lib import check
         from image_restoration_agent_b200.engine import Engine
         self.wl = WORKLOADS[name]
         self.graph = graph
@@ -364,6 +365,9 @@ class Job:
             e = Engine(arch, cfg, sd, precision=self.wl["prec"], device=device)
             if tile_batch:
                 e.set_tile_batch(tile_batch)
+            for kv in options:   # library options (include/irb200.h: irb_set_option), e.g. fuse_pwdw=0 for an A/B
+                k, v = kv.split("=")
+                check(e.lib.irb_set_option(e._h, k.encode(), int(v)))
             self.engines.append(e)
         self.out_scale = 1
         for e in self.engines:
@@ -400,7 +404,7 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     wl = WORKLOADS[args.workload]
     h, w, c = wl["shape"]
-    job = Job(args.workload, local, args.tile_batch, graph=args.graph)
+    job = Job(args.workload, local, args.tile_batch, graph=args.graph, options=args.opt)
     s = job.out_scale
     batch_mode = wl["multi"] == "batch"
     # images this rank restores per step: its share of the fixed batch (strong), or one own image (weak)
@@ -481,7 +485,9 @@ def run_b200(args):
     torch.cuda.synchronize()
     job_prof = job
     if args.graph:   # launches inside a replayed graph cannot be bracketed: profile the eager path of the same code
-        job_prof = Job(args.workload, local, args.tile_batch, graph=False)
+        job_prof = Job(args.workload, local, args.tile_batch, graph=False, options=args.opt)
+        job_prof.restore(imgs_dev[0])   # sizes its workspace outside the profiled call
+        torch.cuda.synchronize()
     with KernelProfile() as prof:
         job_prof.restore(imgs_dev[0] if imgs_dev else torch.from_numpy(synth.synthetic_image_u8(h, w, c, 0)).to(dev))
     launches_per_image = prof.launches
@@ -539,6 +545,7 @@ def run_b200(args):
             "config": config_dict(args.workload),
             "run": {"images_per_step": images_per_step, "images_per_step_this_rank": n_loc,
                     "tile_batch": args.tile_batch or "auto", "cuda_graph_replay": bool(args.graph),
+                    "library_options": list(args.opt),
                     "workspace_gib": round(sum(e._ws.numel() for e in job.engines if e._ws is not None) / 2**30, 2),
                     "gathered_bytes_per_step": gathered_bytes,
                     "gather": "async NCCL gather of the uint8 results to rank 0, overlapped with the next step, flushed "
@@ -659,6 +666,7 @@ def main():
     ap.add_argument("--graph", type=int, default=-1,
                     help="1: replay a CUDA graph of the whole tool body per image (Engine.restore_device(graph=True)); "
                          "0: issue the launches from host code every step; default: per workload")
+    ap.add_argument("--opt", action="append", default=[], help="library option key=value (irb_set_option), repeatable")
     ap.add_argument("--cpu-steps", type=int, default=3, help="timed oracle tile forwards of the cpu_baseline leg")
     ap.add_argument("--strong4k", type=int, default=1,
                     help="N > 1: append the strong_4k object (one 4K image over the N ranks); 0 skips it; 2 also runs "

@@ -248,6 +248,14 @@ int irb_gdfn_fused(const void* d_x, long long ldx, void* d_y, long long ldy, int
                            d_t, d_dw, (const bf16*)d_wout, (cudaStream_t)stream);
 }
 
+int irb_pwdw_fused(int gate, const void* d_x, long long ldx, const float* d_stats, const void* d_w1, int nrows, int hp,
+                   const float* d_colsum, const float* d_t, const float* d_dw, int dw_ld, void* d_y, long long ldy, int n,
+                   int H, int W, int C, void* stream) {
+    IRB_TRY(require_device());
+    return pwdw_fused_bf16(gate != 0, (const bf16*)d_x, ldx, reinterpret_cast<const float2*>(d_stats), (const bf16*)d_w1,
+                           nrows, hp, d_colsum, d_t, d_dw, dw_ld, (bf16*)d_y, ldy, n, H, W, C, (cudaStream_t)stream);
+}
+
 int irb_mdta_nchunks(int P, int heads, int n) { return mdta_nchunks(P, heads, n); }
 
 int irb_mdta_gram(const void* d_qkv, int dtype, long long ld, int n, int P, int C, int heads, int nchunks,

@@ -53,6 +53,12 @@ int dwconv3x3_bf16_tma(const bf16* x, long long ldx, bf16* y, long long ldy, int
                        const float* wt, cudaStream_t stream);
 int dwconv3x3_gate_bf16_tma(const bf16* x, long long ldx, bf16* y, long long ldy, int Nimg, int H, int W, int hp,
                             const float* wt, cudaStream_t stream);
+// ---- pwdw_fused.cu : 1x1 convolution (folded LayerNorm) -> depthwise 3x3 [-> GELU gate] without the HBM round trip ----
+bool pwdw_fused_shape_ok(int C, int nrows, bool gate, int hp);
+int pwdw_fused_bf16(bool gate, const bf16* x, long long ldx, const float2* stats, const bf16* w1, int nrows, int hp,
+                    const float* cs, const float* tb, const float* dww, int dw_ld, bf16* y, long long ldy, int Nimg,
+                    int H, int W, int C, cudaStream_t stream);
+
 // ---- ffn_fused.cu : the whole GDFN (LayerNorm fold -> project_in -> dw3x3 -> GELU gate -> project_out -> + x) ----
 // x_out = x_mid + Wout . (gelu(dw(h1)) * dw(h2)), [h1 | h2] = Win' . LN(x_mid); Win' is [2*hp][C] with the LayerNorm
 // gain folded in (rows [0,hp) = h1, [hp,2hp) = h2), cs / t as in Epi::ln_colsum / bias (nullptr for BiasFree),

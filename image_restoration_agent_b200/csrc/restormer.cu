@@ -251,7 +251,7 @@ void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
     w.x4 = b.take(P4 * 8 * d * E);
     // scratch sized by the worst level: per-pixel channel counts shrink 2x while pixels shrink 4x, so the
     // full-resolution decoder level (C = 2d) dominates; take the max explicitly.
-    size_t ln = 0, qkv = 0, hid = 0, gat = 0, weff = 0, gs = 0, at = 0;
+    size_t ln = 0, qkv = 0, qkv_pre = 0, hid = 0, gat = 0, weff = 0, gs = 0, at = 0;
     const size_t Ps[4] = {P1, P2, P3, P4};
     for (int l = 0; l < 4; ++l) {
         const int Cs[2] = {d << l, l == 0 ? 2 * d : d << l};
@@ -261,7 +261,11 @@ void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
             const int hp = (int(C * desc.ffn_expansion_factor) + 63) / 64 * 64;
             ln = std::max(ln, Ps[l] * C * E);
             qkv = std::max(qkv, Ps[l] * 3 * C * E);
-            hid = std::max(hid, Ps[l] * 2 * hp * E);
+            // the tensors between the 1x1 and the depthwise convolutions exist only where the pair is not fused
+            const bool fq = dt == DT_BF16 && fuse_pwdw && pwdw_fused_shape_ok(C, 3 * C, false, 0);
+            const bool fg = dt == DT_BF16 && fuse_pwdw && pwdw_fused_shape_ok(C, 2 * hp, true, hp);
+            if (!fq) qkv_pre = std::max(qkv_pre, Ps[l] * 3 * C * E);
+            if (!fg) hid = std::max(hid, Ps[l] * 2 * hp * E);
             gat = std::max(gat, Ps[l] * hp * E);
             weff = std::max(weff, size_t(n) * C * C * E);
             at = std::max(at, size_t(n) * C * (C / heads) * 4);
@@ -270,7 +274,7 @@ void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
         }
     }
     w.ln = b.take(ln);
-    w.qkv_pre = b.take(qkv);
+    w.qkv_pre = b.take(qkv_pre);
     w.qkv = b.take(qkv);
     w.hidden = b.take(hid);
     w.gated = b.take(gat);
@@ -313,13 +317,21 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
     const long long P = (long long)n * H * W;
     const int mode = desc.ln_bias_free ? 1 : 0;
     // --- x = x + project_out(attn(norm1(x))) ---
+    // bf16, C <= 128: each "1x1 -> depthwise 3x3" pair is one kernel (pwdw_fused.cu): qkv_pre / hidden stay on the SM
+    const bool fuse_qkv = dt == DT_BF16 && fuse_pwdw && pwdw_fused_shape_ok(C, 3 * C, false, 0);
+    const bool fuse_gate = dt == DT_BF16 && fuse_pwdw && pwdw_fused_shape_ok(C, 2 * w.hp, true, w.hp);
     if (dt == DT_BF16) {  // norm1 folded into the qkv GEMM
         if (!ws.stats_valid) IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
-        Epi e = make_epi(ws.qkv_pre, 3 * C, dt);
-        e.ln_stats = ws.stats;
-        e.ln_colsum = w.qkv_cs;
-        e.bias = w.qkv_t;
-        IRB_TRY(run_gemm(x, ldx, P, C, w.qkv_w, C, 3 * C, 3 * C, e, s));
+        if (fuse_qkv) {
+            IRB_TRY(pwdw_fused_bf16(false, (const bf16*)x, ldx, ws.stats, (const bf16*)w.qkv_w, 3 * C, 0, w.qkv_cs,
+                                    w.qkv_t, w.qkv_dw, 3 * C, (bf16*)ws.qkv, 3 * C, n, H, W, C, s));
+        } else {
+            Epi e = make_epi(ws.qkv_pre, 3 * C, dt);
+            e.ln_stats = ws.stats;
+            e.ln_colsum = w.qkv_cs;
+            e.bias = w.qkv_t;
+            IRB_TRY(run_gemm(x, ldx, P, C, w.qkv_w, C, 3 * C, 3 * C, e, s));
+        }
     } else {
         IRB_TRY(layernorm(x, dt, ldx, ws.ln, dt, C, P, C, w.n1w, w.n1b, mode, 1e-5f, s));
         IRB_TRY(run_gemm(ws.ln, C, P, C, w.qkv_w, C, 3 * C, 3 * C, make_epi(ws.qkv_pre, 3 * C, dt), s));
@@ -327,7 +339,7 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
     const int nch = mdta_nchunks(H * W, heads, n);
     float* G = ws.G;                                       // [n][heads][nch][c][c]
     float* ssq = ws.G + size_t(n) * heads * nch * c * c;   // [n][heads][nch][2][c]
-    IRB_TRY(dwconv3x3(ws.qkv_pre, dt, 3 * C, ws.qkv, 3 * C, n, H, W, 3 * C, w.qkv_dw, nullptr, 0, s));
+    if (!fuse_qkv) IRB_TRY(dwconv3x3(ws.qkv_pre, dt, 3 * C, ws.qkv, 3 * C, n, H, W, 3 * C, w.qkv_dw, nullptr, 0, s));
     if (dt == DT_BF16)
         IRB_TRY(mdta_gram_tc((const bf16*)ws.qkv, 3 * C, n, H * W, C, heads, nch, G, ssq, s));
     else
@@ -364,16 +376,21 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
     // --- x = x + project_out(gelu(dw(x1)) * dw(x2)) ---
     if (dt == DT_BF16) {  // norm2 folded into project_in
         if (!ws.stats_valid) IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
-        Epi e = make_epi(ws.hidden, 2 * w.hp, dt);
-        e.ln_stats = ws.stats;
-        e.ln_colsum = w.pin_cs;
-        e.bias = w.pin_t;
-        IRB_TRY(run_gemm(x, ldx, P, C, w.pin_w, C, 2 * w.hp, 2 * w.hp, e, s));
+        if (fuse_gate) {
+            IRB_TRY(pwdw_fused_bf16(true, (const bf16*)x, ldx, ws.stats, (const bf16*)w.pin_w, 2 * w.hp, w.hp, w.pin_cs,
+                                    w.pin_t, w.ffn_dw, 2 * w.hp, (bf16*)ws.gated, w.hp, n, H, W, C, s));
+        } else {
+            Epi e = make_epi(ws.hidden, 2 * w.hp, dt);
+            e.ln_stats = ws.stats;
+            e.ln_colsum = w.pin_cs;
+            e.bias = w.pin_t;
+            IRB_TRY(run_gemm(x, ldx, P, C, w.pin_w, C, 2 * w.hp, 2 * w.hp, e, s));
+        }
     } else {
         IRB_TRY(layernorm(x, dt, ldx, ws.ln, dt, C, P, C, w.n2w, w.n2b, mode, 1e-5f, s));
         IRB_TRY(run_gemm(ws.ln, C, P, C, w.pin_w, C, 2 * w.hp, 2 * w.hp, make_epi(ws.hidden, 2 * w.hp, dt), s));
     }
-    IRB_TRY(dwconv3x3_gate(ws.hidden, dt, 2 * w.hp, ws.gated, w.hp, n, H, W, w.hp, w.ffn_dw, s));
+    if (!fuse_gate) IRB_TRY(dwconv3x3_gate(ws.hidden, dt, 2 * w.hp, ws.gated, w.hp, n, H, W, w.hp, w.ffn_dw, s));
     {
         Epi e = make_epi(x, ldx, dt);
         e.res = x;

@@ -189,3 +189,16 @@ def window_attention(qkv, C, heads, window, shift, bias_table):
     check(_lib.load().irb_window_attention(qkv.data_ptr(), _dt(qkv), C3, y.data_ptr(), C, n, H, W, C, heads, dstride,
                                            window, shift, bias_table.data_ptr(), _stream()))
     return y
+
+
+def pwdw_fused(x, stats, w1, dww, colsum=None, t=None, gate=False):
+    """x bf16 [n,H,W,C]; stats fp32 [n*H*W, 2] (mu, rstd); w1 bf16 [rows, C] (LayerNorm gain folded); dww fp32
+    [9, rows]; colsum / t fp32 [rows] or None (BiasFree). -> bf16 [n,H,W,rows] (plain) or [n,H,W,rows/2] (gate)."""
+    n, H, W, C = x.shape
+    rows = w1.shape[0]
+    hp = rows // 2 if gate else 0
+    y = torch.zeros((n, H, W, hp if gate else rows), device=x.device, dtype=torch.bfloat16)
+    check(_lib.load().irb_pwdw_fused(int(gate), x.data_ptr(), x.stride(2), stats.data_ptr(), w1.data_ptr(), rows, hp,
+                                     _ptr(colsum), _ptr(t), dww.data_ptr(), dww.shape[1], y.data_ptr(), y.shape[3],
+                                     n, H, W, C, torch.cuda.current_stream(x.device).cuda_stream))
+    return y

@@ -83,6 +83,8 @@ int irb_padded_size(int arch, int window_size, int h, int w, int* hp, int* wp);
 int irb_create(const irb_model_desc* desc, const void* weights_blob, size_t nbytes, int device, irb_handle** out);
 void irb_destroy(irb_handle* h);
 /* options: "tile_batch" (max tiles per forward batch inside irb_restore_image; 0 = automatic);
+ *          "fuse_pwdw" (default 1: Restormer blocks with C <= 128 run each 1x1 -> depthwise pair as one kernel,
+ *          irb_pwdw_fused; 0: the separate GEMM + depthwise kernels);
  *          "strict_tile" (default 1: SwinIR tiles must be a multiple of window_size like inference.py:302; 0: the
  *          Flask service's process_image, model_serving.py:146-166, which has no such assert) */
 int irb_set_option(irb_handle* h, const char* key, long long value);
@@ -150,6 +152,17 @@ int irb_gdfn_dw_gate(const void* d_x, int dtype, long long ldx, void* d_y, long 
 int irb_gdfn_fused(const void* d_x, long long ldx, void* d_y, long long ldy, int n, int H, int W, int C, int hp,
                    const void* d_win, const float* d_colsum, const float* d_t, const float* d_dw, const void* d_wout,
                    float* d_stats_in, float* d_stats_out, float eps, void* stream);
+/* A Restormer "1x1 convolution -> depthwise 3x3" pair as ONE bf16 kernel: the tensor between the two convolutions
+ * stays in shared memory (restormer_arch.py:115-116 qkv -> qkv_dwconv; :88-93 project_in -> dwconv -> gelu gate).
+ *   gate 0: y[n,H,W,:nrows] = dw3x3(h),                      h = W1' . LN(x)   (nrows % 8 == 0)
+ *   gate 1: y[n,H,W,:hp]    = gelu(dw3x3(h)[:hp]) * dw3x3(h)[hp:2hp]           (nrows == 2*hp, hp % 32 == 0)
+ * d_x bf16 [n,H,W,C] (row stride ldx), C in {16..128} multiple of 16; d_stats fp32 [n*H*W][2] = (mu, rstd) of the
+ * rows of x; d_w1 bf16 [nrows][C] = the 1x1 weights with the LayerNorm gain folded in; d_colsum / d_t fp32 [nrows]
+ * (row sums of the rounded folded weights / W1 . ln_bias; both NULL for BiasFree: h = rstd * (W1' . x));
+ * d_dw fp32 [9][dw_ld] tap-major. h is zero outside the image (the depthwise convolution's zero padding). */
+int irb_pwdw_fused(int gate, const void* d_x, long long ldx, const float* d_stats, const void* d_w1, int nrows, int hp,
+                   const float* d_colsum, const float* d_t, const float* d_dw, int dw_ld, void* d_y, long long ldy, int n,
+                   int H, int W, int C, void* stream);
 /* MDTA Gram over a channels-last qkv tensor (q | k | v): the P pixels are split into nchunks =
  * irb_mdta_nchunks(P, heads, n) chunks and every chunk writes its own slot (no atomics -> bit-reproducible):
  *   d_Gpart   [n][heads][nchunks][c][c]   partial sum_p q k^T

@@ -252,3 +252,39 @@ def test_stitch_is_bit_exact_with_the_reference_accumulation(h, w, tile, ov, sf,
     assert torch.equal(out, ref[:, :ch, :cw])
     ref8 = (ref[:, :ch, :cw].clamp(0, 1).permute(1, 2, 0).cpu().numpy() * 255.0).round().astype(np.uint8)
     assert np.array_equal(u8.cpu().numpy(), ref8)
+
+
+@pytest.mark.parametrize("gate", [False, True])
+@pytest.mark.parametrize("with_bias", [True, False])
+@pytest.mark.parametrize("n,H,W,C,rows", [(2, 16, 32, 48, 144), (1, 24, 40, 96, 288), (3, 8, 72, 96, 512),
+                                          (1, 40, 24, 48, 256), (2, 9, 33, 96, 288)])
+def test_pwdw_fused_matches_separate_ops(gate, with_bias, n, H, W, C, rows):
+    """1x1 (folded LayerNorm) -> depthwise 3x3 [-> gelu gate] in one kernel vs the torch fp32 restatement of
+    restormer_arch.py:115-116 / :88-93 on the same bf16-rounded operands (incl. ragged tiles: H % 8, W % 32 != 0)."""
+    from image_restoration_agent_b200 import ops
+    if gate:
+        rows = 256 if C == 48 else 512
+    x = (torch.randn(n, H, W, C, device="cuda") * 1.5 + 0.3).bfloat16()
+    xf = x.float()
+    mu = xf.mean(-1)
+    rstd = 1.0 / torch.sqrt(xf.var(-1, unbiased=False) + 1e-5)
+    stats = torch.stack([mu, rstd], -1).reshape(-1, 2).contiguous()
+    gain = torch.randn(C, device="cuda") * 0.1 + 1.0
+    ln_b = torch.randn(C, device="cuda") * 0.05
+    w = torch.randn(rows, C, device="cuda") / C ** 0.5
+    w1 = (w * gain).bfloat16()
+    colsum = w1.float().sum(1).contiguous() if with_bias else None
+    t = (w @ ln_b).contiguous() if with_bias else None
+    dww = (torch.randn(9, rows, device="cuda") / 3.0).contiguous()
+    y = ops.pwdw_fused(x, stats, w1, dww, colsum, t, gate=gate)
+    # reference: hidden rounded to bf16 (as the unfused path stores it), zero padding of the hidden tensor
+    acc = xf @ w1.float().t()
+    if with_bias:
+        hid = rstd[..., None] * (acc - mu[..., None] * colsum) + t
+    else:
+        hid = rstd[..., None] * acc
+    hid = hid.bfloat16().float().permute(0, 3, 1, 2)
+    dw = F.conv2d(hid, dww.t().reshape(rows, 1, 3, 3), padding=1, groups=rows).permute(0, 2, 3, 1)
+    ref = F.gelu(dw[..., :rows // 2]) * dw[..., rows // 2:] if gate else dw
+    assert y.shape == ref.shape
+    close(y, ref, 1.6e-2)
