@@ -57,7 +57,6 @@ PROTOTYPES = {
     "irb_conv3x3": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _i, _i, _i, _vp, _vp, _ll, _i, _f, _i, _vp, _ll, _vp]),
     "irb_dwconv3x3": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "irb_gdfn_dw_gate": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _vp, _vp]),
-    "irb_gdfn_fused": (_i, [_vp, _ll, _vp, _ll, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _vp]),
     "irb_pwdw_fused": (_i, [_i, _vp, _ll, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _vp, _ll, _i, _i, _i, _i, _vp]),
     "irb_mdta_nchunks": (_i, [_i, _i, _i]),
     "irb_mdta_gram": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _i, _vp, _vp, _vp]),

@@ -236,18 +236,6 @@ int irb_gdfn_dw_gate(const void* d_x, int dtype, long long ldx, void* d_y, long 
     return dwconv3x3_gate(d_x, dtype, ldx, d_y, ldy, n, H, W, hp, d_w, (cudaStream_t)stream);
 }
 
-int irb_gdfn_fused(const void* d_x, long long ldx, void* d_y, long long ldy, int n, int H, int W, int C, int hp,
-                   const void* d_win, const float* d_colsum, const float* d_t, const float* d_dw, const void* d_wout,
-                   float* d_stats_in, float* d_stats_out, float eps, void* stream) {
-    IRB_TRY(require_device());
-    IRB_REQUIRE(gdfn_fused_shape_ok(C, hp), "irb_gdfn_fused: unsupported (C, hp)");
-    const long long P = (long long)n * H * W;
-    IRB_TRY(row_stats(d_x, DT_BF16, ldx, reinterpret_cast<float2*>(d_stats_in), P, C, eps, (cudaStream_t)stream));
-    return gdfn_fused_bf16((const bf16*)d_x, ldx, reinterpret_cast<const float2*>(d_stats_in), (bf16*)d_y, ldy,
-                           reinterpret_cast<float2*>(d_stats_out), eps, n, H, W, C, hp, (const bf16*)d_win, d_colsum,
-                           d_t, d_dw, (const bf16*)d_wout, (cudaStream_t)stream);
-}
-
 int irb_pwdw_fused(int gate, const void* d_x, long long ldx, const float* d_stats, const void* d_w1, int nrows, int hp,
                    const float* d_colsum, const float* d_t, const float* d_dw, int dw_ld, void* d_y, long long ldy, int n,
                    int H, int W, int C, void* stream) {

@@ -59,15 +59,6 @@ int pwdw_fused_bf16(bool gate, const bf16* x, long long ldx, const float2* stats
                     const float* cs, const float* tb, const float* dww, int dw_ld, bf16* y, long long ldy, int Nimg,
                     int H, int W, int C, cudaStream_t stream);
 
-// ---- ffn_fused.cu : the whole GDFN (LayerNorm fold -> project_in -> dw3x3 -> GELU gate -> project_out -> + x) ----
-// x_out = x_mid + Wout . (gelu(dw(h1)) * dw(h2)), [h1 | h2] = Win' . LN(x_mid); Win' is [2*hp][C] with the LayerNorm
-// gain folded in (rows [0,hp) = h1, [hp,2hp) = h2), cs / t as in Epi::ln_colsum / bias (nullptr for BiasFree),
-// stats_in = (mu, rstd) per pixel of x_mid, stats_out = the same for x_out. x_out must not alias x_mid.
-bool gdfn_fused_supported(int C, int hp);  // shape supported AND the model runners use it (IRB_FUSED_FFN=1)
-bool gdfn_fused_shape_ok(int C, int hp);
-int gdfn_fused_bf16(const bf16* xmid, long long ldm, const float2* stats_in, bf16* xout, long long ldx,
-                    float2* stats_out, float stats_eps, int Nimg, int H, int W, int C, int hp, const bf16* win,
-                    const float* cs, const float* t, const float* dww, const bf16* wout, cudaStream_t stream);
 // fp32 [rows][cin] (cin <= 4) -> bf16 [rows][8]: channel c = bf16(x), channel cin + c = bf16(x - hi), rest zero
 int split_hi_lo_bf16(const float* x, int cin, bf16* y, long long rows, cudaStream_t stream);
 int nearest_up2(const void* x, int dt, long long ldx, void* y, long long ldy, int Nimg, int H, int W, int C,

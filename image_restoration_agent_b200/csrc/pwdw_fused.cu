@@ -8,20 +8,22 @@
 // pixels, 1.33x the tile: the tensor pipe idles at ~13 % in the unfused model, so the recompute is free) and handed to
 // the depthwise warps through shared memory.
 //
-// Work item = (image, 32x8 tile); persistent CTAs, one per SM, 22 warps:
-//   warp 20 (TMA)      : x halo tile {C, 34, 10} -> A (K-major, 128B swizzle, 3 M-blocks of 128 rows; rows / columns
+// Work item = (image, 32x8 tile); persistent CTAs, one per SM, 18 warps:
+//   warp 16 (TMA)      : x halo tile {C, 34, 10} -> A (K-major, 128B swizzle, 3 M-blocks of 128 rows; rows / columns
 //                        outside the image are zero-filled) once per item; per 64-column chunk j of W1' -> B ring (2)
-//   warp 21 (MMA)      : D[j & 1] (TMEM, 3 x [128 x 64] fp32) = A . B_j^T                         tcgen05.mma
-//   warps 16-19 (cvt)  : D -> registers -> folded LayerNorm (rstd * acc + (-mu rstd) * colsum + t), ZERO outside the
+//   warp 17 (MMA)      : D[j & 1] (TMEM, 3 x [128 x 64] fp32) = A . B_j^T                         tcgen05.mma
+//   warps 0-15, per chunk, two phases (conversion runs one chunk ahead of the stencil; hand-over by mbarriers):
+//     convert          : warp w drains TMEM lane quarter w & 3, columns 16 (w >> 2) .. +15 of the three M-blocks:
+//                        D -> registers -> folded LayerNorm (rstd * acc + (-mu rstd) * colsum + t), ZERO outside the
 //                        image (the depthwise convolution's zero padding applies to the 1x1's OUTPUT) -> bf16 ->
-//                        hidden halo tile [340 px][64 ch] in shared memory (ring of 2, 16-byte chunks XOR-swizzled by
-//                        the row so that both these row-per-thread stores and the pixel-per-warp loads below are
-//                        conflict-free)
-//   warps 0-15 (dw)    : the depthwise stencil of dw_tma.cu on that tile: warp = 2 output columns, lane = channel pair,
+//                        hidden halo tile [340 px][64 ch] in shared memory (2 buffers, 16-byte chunks XOR-swizzled by
+//                        the row so that these row-per-thread stores and the pixel-per-warp loads are conflict-free)
+//     stencil          : the depthwise code of dw_tma.cu on that tile: warp = 2 output columns, lane = channel pair,
 //                        input-stationary rows, packed fma.rn.f32x2; plain: bf16 stores; gate: lanes 0-15 hold the
 //                        gelu half, lanes 16-31 the linear half of the SAME 32 gated channels, the half-warps swap one
 //                        pixel each and every lane stores one gelu(h1) * h2 pair
-// TMEM accumulators and the hidden tile are double-buffered, so TMA, MMA, conversion and the stencil overlap.
+//   (a first version with 4 dedicated converter warps left the 16 stencil warps waiting on them 46 % of the time,
+//   profiles/r02_s02_ncu_pwdw_v1.txt; here every warp does both, the TMEM double buffer keeps the MMA a chunk ahead).
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
@@ -34,8 +36,8 @@ static constexpr int kPwRows = kPwHW * kPwHH;        // 340 halo pixels = rows o
 static constexpr int kPwASlab = 384 * 128;           // one 64-channel K slab of the halo tile (3 M-blocks)
 static constexpr int kPwBSlab = 64 * 128;            // 64 output columns x 64 K
 static constexpr int kPwHid = kPwRows * 128;         // 43 520 B: hidden halo tile, 64 channels
-static constexpr int kPwDwWarps = 16, kPwCvWarps = 4;
-static constexpr int kPwThreads = (kPwDwWarps + kPwCvWarps + 2) * 32;  // 704
+static constexpr int kPwDwWarps = 16, kPwCvWarps = 0;
+static constexpr int kPwThreads = (kPwDwWarps + kPwCvWarps + 2) * 32;  // 576
 static constexpr int kPwAccStride = 192;             // TMEM columns per accumulator buffer (3 M-blocks x 64)
 
 struct alignas(64) PwDwParams {
@@ -44,10 +46,10 @@ struct alignas(64) PwDwParams {
     const float2* stats;  // [N*H*W] (mu, rstd) of the rows of x
     const float* cs;      // [rows] column sums of the folded weights (WithBias LayerNorm) or nullptr
     const float* tb;      // [rows] W1 . ln_bias or nullptr
-    const float* dww;     // [9][dw_ld] depthwise taps, fp32
+    const float* dww;     // [rows / 2][9][2] depthwise taps, fp32: the 9 taps of a channel pair are contiguous
     bf16* y;
     long long ldy;
-    int dw_ld, H, W, KS, klast, nchunks, nout, nrows, hp;
+    int H, W, KS, klast, nchunks, nout, nrows, hp;
     int tiles_x, tiles_y, total;
 };
 
@@ -75,8 +77,8 @@ __global__ void __launch_bounds__(kPwThreads, 1) pwdw_fused_kernel(const __grid_
             mbar_init(&bars->b_full[i], 1);
             mbar_init(&bars->b_empty[i], 1);
             mbar_init(&bars->d_full[i], 1);
-            mbar_init(&bars->d_empty[i], kPwCvWarps);
-            mbar_init(&bars->h_full[i], kPwCvWarps);
+            mbar_init(&bars->d_empty[i], kPwDwWarps);
+            mbar_init(&bars->h_full[i], kPwDwWarps);
             mbar_init(&bars->h_empty[i], kPwDwWarps);
         }
         fence_mbar_init();
@@ -155,202 +157,223 @@ __global__ void __launch_bounds__(kPwThreads, 1) pwdw_fused_kernel(const __grid_
                 umma_commit(&bars->a_empty);  // every MMA of this item has read the halo tile
             }
         }
-    } else if (warp >= kPwDwWarps) {
-        // ================= converter: TMEM -> folded LayerNorm -> bf16 hidden halo tile =================
-        const int q = warp & 3;  // TMEM lane quarter of this warp (warps 16..19 -> 0..3)
+    } else {
+        // ================= warps 0..15: convert chunk t (TMEM -> hidden tile), then the stencil of chunk t - 1 =================
+        // A software pipeline over this CTA's flat chunk sequence t = 0, 1, ...: conversion runs ONE chunk ahead of the
+        // stencil, and the two hidden buffers are handed over with mbarriers (h_full: all 16 warps converted their part;
+        // h_empty: all 16 warps finished the stencil), so warps drift up to a chunk apart: while some wait for TMEM loads
+        // others issue stencil math (a CTA-wide barrier per chunk left the SM at IPC 1.3).
+        const int q = warp & 3;    // TMEM lane quarter this warp may read
+        const int cg = warp >> 2;  // its 16-column group of the chunk
+        const int col0 = warp * 2; // its two output columns in the stencil phase
         const uint32_t hid0 = smem_u32(sH);
-        int cj = 0;
-        for (int item = blockIdx.x; item < p.total; item += gridDim.x) {
-            const int img = item / per_img;
-            const int rr = item - img * per_img;
-            const int ty = rr / p.tiles_x, tx = rr - ty * p.tiles_x;
-            f32x2 a2[3], b2[3];
-            bool ok[3];
+        const long long row_step = (long long)p.W * p.ldy;
+        const int my_items = blockIdx.x < p.total ? (p.total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+        const int T = my_items * NCH;
+        // conversion stage state
+        int itemC = blockIdx.x, jC = 0;
+        float ar[3], br[3];
+        uint32_t okm[3];
+        // stencil stage state
+        int itemS = blockIdx.x, jS = 0;
+        int imgS = 0, tyS = 0, txS = 0;
+        for (int t = 0; t <= T; ++t) {
+            if (t < T) {
+                // ---------------- convert chunk t: columns cg*16 .. +15, rows q*32 + lane of every M-block ----------------
+                const int s = t & 1;
+                const uint32_t ph = (t >> 1) & 1;
+                if (jC == 0) {  // new item: LayerNorm statistics of this thread's three halo rows; mask = 0 outside the image
+                    const int img = itemC / per_img;
+                    const int rr = itemC - img * per_img;
+                    const int ty = rr / p.tiles_x, tx = rr - ty * p.tiles_x;
 #pragma unroll
-            for (int mb = 0; mb < 3; ++mb) {
-                const int r = mb * 128 + q * 32 + lane;
-                const int hy = r / kPwHW, hx = r - hy * kPwHW;
-                const int y = ty * kPwTH - 1 + hy, x = tx * kPwTW - 1 + hx;
-                ok[mb] = r < kPwRows && y >= 0 && y < p.H && x >= 0 && x < p.W;
-                float2 st = make_float2(0.f, 0.f);
-                if (ok[mb]) st = __ldg(p.stats + ((long long)img * p.H + y) * p.W + x);
-                a2[mb] = splat2(st.y);
-                b2[mb] = splat2(-st.x * st.y);
-            }
-            for (int j = 0; j < NCH; ++j, ++cj) {
-                const int s = cj & 1;
-                const uint32_t ph = (cj >> 1) & 1;
-                // column vectors (colsum, t) of the two 32-column halves of this chunk, and how many columns exist
-                int nA = 32, nB = 32;
-                long long offA, offB;
-                if (GATE == 0) {
-                    offA = (long long)j * 64;
-                    offB = offA + 32;
-                    nA = min(32, max(0, p.nrows - j * 64));
-                    nB = min(32, max(0, p.nrows - j * 64 - 32));
-                } else {
-                    offA = (long long)j * 32;
-                    offB = (long long)p.hp + j * 32;
+                    for (int mb = 0; mb < 3; ++mb) {
+                        const int r = mb * 128 + q * 32 + lane;
+                        const int hy = r / kPwHW, hx = r - hy * kPwHW;
+                        const int y = ty * kPwTH - 1 + hy, x = tx * kPwTW - 1 + hx;
+                        const bool ok = r < kPwRows && y >= 0 && y < p.H && x >= 0 && x < p.W;
+                        float2 st = make_float2(0.f, 0.f);
+                        if (ok) st = __ldg(p.stats + ((long long)img * p.H + y) * p.W + x);
+                        ar[mb] = st.y;
+                        br[mb] = -st.x * st.y;
+                        okm[mb] = ok ? 0xFFFFFFFFu : 0u;
+                    }
                 }
+                const int j = jC;
+                int off;      // index of the chunk's column cg*16 in the colsum / t vectors
+                int nv = 16;  // how many of the 16 columns exist (plain: the last chunk may be ragged)
+                if (GATE == 0) {
+                    off = j * 64 + cg * 16;
+                    nv = min(16, max(0, p.nrows - off));
+                } else {
+                    off = (cg < 2 ? j * 32 + cg * 16 : p.hp + j * 32 + (cg - 2) * 16);
+                }
+                f32x2 csv[8], tbv[8];
+                if (p.cs != nullptr) {
+                    const float4* cp = reinterpret_cast<const float4*>(p.cs + off);
+                    const float4* tp = reinterpret_cast<const float4*>(p.tb + off);
+#pragma unroll
+                    for (int g4 = 0; g4 < 4; ++g4) {
+                        float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f), t4 = c4;
+                        if (g4 * 4 < nv) {
+                            c4 = __ldg(cp + g4);
+                            t4 = __ldg(tp + g4);
+                        }
+                        csv[2 * g4] = pack2(c4.x, c4.y);
+                        csv[2 * g4 + 1] = pack2(c4.z, c4.w);
+                        tbv[2 * g4] = pack2(t4.x, t4.y);
+                        tbv[2 * g4 + 1] = pack2(t4.z, t4.w);
+                    }
+                }
+                mbar_wait(&bars->h_empty[s], ph ^ 1);  // every warp finished the stencil of chunk t - 2 on this buffer
                 mbar_wait(&bars->d_full[s], ph);
                 tc_fence_after();
-                mbar_wait(&bars->h_empty[s], ph ^ 1);
                 const uint32_t hid = hid0 + s * kPwHid;
+                const uint32_t tq = tmem_base + s * kPwAccStride + cg * 16 + (uint32_t(q * 32) << 16);
+                uint32_t acc[2][16];  // ping-pong: the load of M-block mb + 1 flies while mb is converted
+                tmem_ld16_nowait(tq, acc[0]);
 #pragma unroll
                 for (int mb = 0; mb < 3; ++mb) {
-                    if (mb * 128 + q * 32 >= kPwRows) continue;  // warp-uniform: this quarter has no halo rows
+                    if (mb * 128 + q * 32 >= kPwRows) continue;  // warp-uniform: quarter 3 of the last M-block is empty
+                    tmem_ld_wait();
+                    if (mb + 1 < 3 && (mb + 1) * 128 + q * 32 < kPwRows) tmem_ld16_nowait(tq + (mb + 1) * 64, acc[(mb + 1) & 1]);
                     const int r = mb * 128 + q * 32 + lane;
-                    const uint32_t taddr = tmem_base + s * kPwAccStride + mb * 64 + (uint32_t(q * 32) << 16);
-                    const uint32_t row = hid + r * 128;
-                    const uint32_t rx = uint32_t(r & 7);
+                    const f32x2 a2 = splat2(ar[mb]), b2 = splat2(br[mb]);
+                    uint32_t pk[8];
 #pragma unroll
-                    for (int half = 0; half < 2; ++half) {
-                        uint32_t acc[32];
-                        tmem_ld32_nowait(taddr + half * 32, acc);
-                        tmem_ld_wait();
-                        const long long off = half ? offB : offA;
-                        const int nv = half ? nB : nA;
-#pragma unroll
-                        for (int c8 = 0; c8 < 4; ++c8) {
-                            uint32_t pk[4];
-#pragma unroll
-                            for (int h4 = 0; h4 < 2; ++h4) {
-                                f32x2 x0 = pack2(__uint_as_float(acc[c8 * 8 + h4 * 4 + 0]), __uint_as_float(acc[c8 * 8 + h4 * 4 + 1]));
-                                f32x2 x1 = pack2(__uint_as_float(acc[c8 * 8 + h4 * 4 + 2]), __uint_as_float(acc[c8 * 8 + h4 * 4 + 3]));
-                                if (p.cs != nullptr) {  // WithBias: rstd * acc + ((-mu rstd) * colsum + t)
-                                    float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f), t4 = c4;
-                                    if (c8 * 8 + h4 * 4 < nv) {
-                                        c4 = __ldg(reinterpret_cast<const float4*>(p.cs + off + c8 * 8 + h4 * 4));
-                                        t4 = __ldg(reinterpret_cast<const float4*>(p.tb + off + c8 * 8 + h4 * 4));
-                                    }
-                                    x0 = fma2(x0, a2[mb], fma2(b2[mb], pack2(c4.x, c4.y), pack2(t4.x, t4.y)));
-                                    x1 = fma2(x1, a2[mb], fma2(b2[mb], pack2(c4.z, c4.w), pack2(t4.z, t4.w)));
-                                } else {                // BiasFree: rstd * acc
-                                    x0 = mul2(x0, a2[mb]);
-                                    x1 = mul2(x1, a2[mb]);
-                                }
-                                pk[h4 * 2 + 0] = ok[mb] ? f32x2_to_bf16x2(x0) : 0u;  // zero padding of the 1x1's OUTPUT
-                                pk[h4 * 2 + 1] = ok[mb] ? f32x2_to_bf16x2(x1) : 0u;
-                            }
-                            if (r < kPwRows) sts_v4(row + ((uint32_t(half * 4 + c8) ^ rx) << 4), pk[0], pk[1], pk[2], pk[3]);
-                        }
+                    for (int i = 0; i < 8; ++i) {
+                        f32x2 x = pack2(__uint_as_float(acc[mb & 1][2 * i]), __uint_as_float(acc[mb & 1][2 * i + 1]));
+                        if (p.cs != nullptr)   // WithBias: rstd * acc + ((-mu rstd) * colsum + t)
+                            x = fma2(x, a2, fma2(b2, csv[i], tbv[i]));
+                        else                   // BiasFree: rstd * acc
+                            x = mul2(x, a2);
+                        pk[i] = f32x2_to_bf16x2(x) & okm[mb];  // zero padding of the 1x1's OUTPUT
+                    }
+                    if (r < kPwRows) {
+                        const uint32_t row = hid + r * 128;
+                        const uint32_t rx = uint32_t(r & 7);
+                        sts_v4(row + ((uint32_t(cg * 2) ^ rx) << 4), pk[0], pk[1], pk[2], pk[3]);
+                        sts_v4(row + ((uint32_t(cg * 2 + 1) ^ rx) << 4), pk[4], pk[5], pk[6], pk[7]);
                     }
                 }
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
-                    mbar_arrive(&bars->d_empty[s]);
-                    mbar_arrive(&bars->h_full[s]);
+                    mbar_arrive(&bars->d_empty[s]);  // this warp's share of the accumulator is drained
+                    mbar_arrive(&bars->h_full[s]);   // and its part of the hidden tile is written
+                }
+                if (++jC == NCH) {
+                    jC = 0;
+                    itemC += gridDim.x;
                 }
             }
-        }
-    } else {
-        // ================= depthwise 3x3 (+ GELU gate): warp = output columns (2*warp, 2*warp + 1) =================
-        const int col0 = warp * 2;
-        // the 16-byte chunk (lane >> 2) of halo row r sits at ((lane >> 2) ^ (r & 7)) << 4; r = col0 + K with a
-        // compile-time K below, and (col0 + K) & 7 == (col0 + (K & 7)) & 7: eight per-lane offsets cover every row
-        uint32_t sw[8];
+            if (t == 0) continue;
+            // ---------------- stencil of chunk t - 1 ----------------
+            const int s = (t - 1) & 1;
+            const uint32_t ph = ((t - 1) >> 1) & 1;
+            if (jS == 0) {
+                imgS = itemS / per_img;
+                const int rr = itemS - imgS * per_img;
+                tyS = rr / p.tiles_x;
+                txS = rr - tyS * p.tiles_x;
+            }
+            const int j = jS;
+            const int gx = txS * kPwTW + col0;
+            const int nrows = min(kPwTH, p.H - tyS * kPwTH);
+            int c0, oc;
+            bool cvalid;
+            if (GATE == 0) {
+                c0 = j * 64 + lane * 2;
+                oc = c0;
+                cvalid = c0 < p.nout;
+            } else {
+                oc = j * 32 + (lane & 15) * 2;
+                c0 = (lane < 16 ? 0 : p.hp) + oc;
+                cvalid = oc < p.nout;
+            }
+            f32x2 wr[9];  // this lane's channel pair: 9 taps x 2 channels, contiguous in the packed weights
+            {
+                const float2* wp = reinterpret_cast<const float2*>(p.dww) + (cvalid ? (c0 >> 1) * 9 : 0);
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-            sw[k] = col0 * 128 + ((uint32_t(lane >> 2) ^ uint32_t((col0 + k) & 7)) << 4) + (lane & 3) * 4;
-        const uint32_t hid0 = smem_u32(sH);
-        const long long row_step = (long long)p.W * p.ldy;
-        int cj = 0;
-        for (int item = blockIdx.x; item < p.total; item += gridDim.x) {
-            const int img = item / per_img;
-            const int rr = item - img * per_img;
-            const int ty = rr / p.tiles_x, tx = rr - ty * p.tiles_x;
-            const int gx = tx * kPwTW + col0;
-            const int nrows = min(kPwTH, p.H - ty * kPwTH);
-            for (int j = 0; j < NCH; ++j, ++cj) {
-                const int s = cj & 1;
-                const uint32_t ph = (cj >> 1) & 1;
-                int c0, oc;
-                bool cvalid;
-                if (GATE == 0) {
-                    c0 = j * 64 + lane * 2;
-                    oc = c0;
-                    cvalid = c0 < p.nout;
-                } else {
-                    oc = j * 32 + (lane & 15) * 2;
-                    c0 = (lane < 16 ? 0 : p.hp) + oc;
-                    cvalid = oc < p.nout;
+                for (int tt = 0; tt < 9; ++tt) {
+                    const float2 w2 = __ldg(wp + tt);
+                    wr[tt] = cvalid ? pack2(w2.x, w2.y) : pack2(0.f, 0.f);
                 }
-                f32x2 wr[9];
+            }
+            // stencil loads: the 16-byte chunk (lane >> 2) of halo row r sits at ((lane >> 2) ^ (r & 7)) << 4; r = col0 + K
+            // with a compile-time K, and (col0 + K) & 7 == (col0 + (K & 7)) & 7: eight per-lane bases cover every row
+            uint32_t a[8];
 #pragma unroll
-                for (int t = 0; t < 9; ++t) {
-                    float2 w2 = make_float2(0.f, 0.f);
-                    if (cvalid) w2 = __ldg(reinterpret_cast<const float2*>(p.dww + (long long)t * p.dw_ld + c0));
-                    wr[t] = pack2(w2.x, w2.y);
+            for (int k = 0; k < 8; ++k)
+                a[k] = hid0 + s * kPwHid + col0 * 128 + ((uint32_t(lane >> 2) ^ uint32_t((col0 + k) & 7)) << 4) + (lane & 3) * 4;
+            bf16* yp0;
+            bool ok0, ok1;
+            if (GATE == 0) {
+                yp0 = p.y + (((long long)imgS * p.H + tyS * kPwTH) * p.W + gx) * p.ldy + oc;
+                ok0 = cvalid && gx < p.W;
+                ok1 = cvalid && gx + 1 < p.W;
+            } else {  // this lane stores pixel gx + (lane >> 4)
+                yp0 = p.y + (((long long)imgS * p.H + tyS * kPwTH) * p.W + gx + (lane >> 4)) * p.ldy + oc;
+                ok0 = ok1 = cvalid && gx + (lane >> 4) < p.W;
+            }
+            mbar_wait(&bars->h_full[s], ph);
+            f32x2 acc[3][2];  // [output row mod 3][pixel]
+#pragma unroll
+            for (int hr = 0; hr < kPwHH; ++hr) {
+                f32x2 in[4];
+#pragma unroll
+                for (int d = 0; d < 4; ++d) {
+                    const int K = hr * kPwHW + d;
+                    in[d] = bf16x2_to_f32x2_alu(lds_u32(a[K & 7] + K * 128));
                 }
-                uint32_t a[8];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) a[k] = hid0 + s * kPwHid + sw[k];
-                bf16* yp0;
-                bool ok0, ok1;
-                if (GATE == 0) {
-                    yp0 = p.y + (((long long)img * p.H + ty * kPwTH) * p.W + gx) * p.ldy + oc;
-                    ok0 = cvalid && gx < p.W;
-                    ok1 = cvalid && gx + 1 < p.W;
-                } else {  // this lane stores pixel gx + (lane >> 4)
-                    yp0 = p.y + (((long long)img * p.H + ty * kPwTH) * p.W + gx + (lane >> 4)) * p.ldy + oc;
-                    ok0 = ok1 = cvalid && gx + (lane >> 4) < p.W;
-                }
-                mbar_wait(&bars->h_full[s], ph);
-                f32x2 acc[3][2];  // [output row mod 3][pixel]
+                for (int dr = 0; dr < 3; ++dr) {  // halo row hr is tap row dr of output row hr - dr
+                    const int orow = hr - dr;
+                    if (orow < 0 || orow >= kPwTH) continue;
+                    const int sl = orow % 3;
 #pragma unroll
-                for (int hr = 0; hr < kPwHH; ++hr) {
-                    f32x2 in[4];
-#pragma unroll
-                    for (int d = 0; d < 4; ++d) {
-                        const int K = hr * kPwHW + d;
-                        in[d] = bf16x2_to_f32x2_alu(lds_u32(a[K & 7] + K * 128));
+                    for (int px = 0; px < 2; ++px) {
+                        if (dr == 0)
+                            acc[sl][px] = mul2(in[px], wr[0]);
+                        else
+                            ffma2(acc[sl][px], in[px], wr[dr * 3]);
+                        ffma2(acc[sl][px], in[px + 1], wr[dr * 3 + 1]);
+                        ffma2(acc[sl][px], in[px + 2], wr[dr * 3 + 2]);
                     }
-#pragma unroll
-                    for (int dr = 0; dr < 3; ++dr) {  // halo row hr is tap row dr of output row hr - dr
-                        const int orow = hr - dr;
-                        if (orow < 0 || orow >= kPwTH) continue;
-                        const int sl = orow % 3;
-#pragma unroll
-                        for (int px = 0; px < 2; ++px) {
-                            if (dr == 0)
-                                acc[sl][px] = mul2(in[px], wr[0]);
-                            else
-                                ffma2(acc[sl][px], in[px], wr[dr * 3]);
-                            ffma2(acc[sl][px], in[px + 1], wr[dr * 3 + 1]);
-                            ffma2(acc[sl][px], in[px + 2], wr[dr * 3 + 2]);
+                }
+                const int done = hr - 2;  // this output row is complete
+                if (done >= 0) {
+                    const int sl = done % 3;
+                    if (GATE == 0) {
+                        float o0, o1;
+                        unpack2(acc[sl][0], o0, o1);
+                        const uint32_t pk0 = pack_bf16x2(o0, o1);
+                        unpack2(acc[sl][1], o0, o1);
+                        const uint32_t pk1 = pack_bf16x2(o0, o1);
+                        if (done < nrows) {
+                            if (ok0) *reinterpret_cast<uint32_t*>(yp0) = pk0;
+                            if (ok1) *reinterpret_cast<uint32_t*>(yp0 + p.ldy) = pk1;
                         }
+                    } else {
+                        // lanes 0-15 hold dw(h1), lanes 16-31 dw(h2) of the same channel pair: the lower half gates
+                        // pixel 0, the upper half pixel 1
+                        const f32x2 send = lane < 16 ? acc[sl][1] : acc[sl][0];
+                        const f32x2 recv = __shfl_xor_sync(0xffffffffu, send, 16);
+                        const f32x2 h1 = lane < 16 ? acc[sl][0] : recv;
+                        const f32x2 h2 = lane < 16 ? recv : acc[sl][1];
+                        const f32x2 g = mul2(gelu2_fast(h1), h2);
+                        float o0, o1;
+                        unpack2(g, o0, o1);
+                        if (done < nrows && ok0) *reinterpret_cast<uint32_t*>(yp0) = pack_bf16x2(o0, o1);
                     }
-                    const int done = hr - 2;  // this output row is complete
-                    if (done >= 0) {
-                        const int sl = done % 3;
-                        if (GATE == 0) {
-                            float o0, o1;
-                            unpack2(acc[sl][0], o0, o1);
-                            const uint32_t pk0 = pack_bf16x2(o0, o1);
-                            unpack2(acc[sl][1], o0, o1);
-                            const uint32_t pk1 = pack_bf16x2(o0, o1);
-                            if (done < nrows) {
-                                if (ok0) *reinterpret_cast<uint32_t*>(yp0) = pk0;
-                                if (ok1) *reinterpret_cast<uint32_t*>(yp0 + p.ldy) = pk1;
-                            }
-                        } else {
-                            // lanes 0-15 hold dw(h1), lanes 16-31 dw(h2) of the same channel pair: the lower half gates
-                            // pixel 0, the upper half pixel 1
-                            const f32x2 send = lane < 16 ? acc[sl][1] : acc[sl][0];
-                            const f32x2 recv = __shfl_xor_sync(0xffffffffu, send, 16);
-                            const f32x2 h1 = lane < 16 ? acc[sl][0] : recv;
-                            const f32x2 h2 = lane < 16 ? recv : acc[sl][1];
-                            const f32x2 g = mul2(gelu2_fast(h1), h2);
-                            float o0, o1;
-                            unpack2(g, o0, o1);
-                            if (done < nrows && ok0) *reinterpret_cast<uint32_t*>(yp0) = pack_bf16x2(o0, o1);
-                        }
-                        yp0 += row_step;
-                    }
+                    yp0 += row_step;
                 }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&bars->h_empty[s]);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->h_empty[s]);
+            if (++jS == NCH) {
+                jS = 0;
+                itemS += gridDim.x;
             }
         }
     }
@@ -390,7 +413,7 @@ int pwdw_fused_bf16(bool gate, const bf16* x, long long ldx, const float2* stats
     p.cs = cs;
     p.tb = tb;
     p.dww = dww;
-    p.dw_ld = dw_ld;
+    (void)dw_ld;
     p.y = y;
     p.ldy = ldy;
     p.H = H;

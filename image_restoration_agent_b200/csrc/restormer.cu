@@ -19,6 +19,7 @@ struct RBlockW {
     float *n1w, *n1b, *n2w, *n2b;
     void* qkv_w;     // [3C][C]
     float* qkv_dw;   // [9][3C]
+    float *qkv_dwp, *ffn_dwp;  // the same taps as [ch/2][9][2] (pwdw_fused.cu: a channel pair's 9 taps contiguous)
     float* temp;     // [heads]
     float* proj_w;   // [C][C] fp32 (folded with the attention matrix per image)
     void* pin_w;     // [2hp][C]   rows [0,h) = x1, [hp,hp+h) = x2, others zero
@@ -47,6 +48,14 @@ static void fold_ln(std::vector<float>& w, int N, int K, int ldw, const float* g
     }
 }
 
+// [9][n] tap-major -> [n/2][9][2]
+static std::vector<float> pair_major(const std::vector<float>& w, int n) {
+    std::vector<float> o(size_t(9) * n);
+    for (int c = 0; c < n; ++c)
+        for (int k = 0; k < 9; ++k) o[(size_t(c >> 1) * 9 + k) * 2 + (c & 1)] = w[size_t(k) * n + c];
+    return o;
+}
+
 struct ConvW {
     void* w;       // storage dtype, [npad][9*kpad]
     float* wf32;   // fp32 copy (SIMT path for tiny channel counts)
@@ -71,7 +80,6 @@ struct Restormer : Model {
         float *G, *sumsq, *attn;
         bf16* in8;      // [P1][8] hi/lo split of the fp32 input (bf16 mode)
         float2* stats;  // [P] (mu, rstd) of the LayerNorm folded into the next GEMM (bf16 mode)
-        float2* stats2; // [P] norm2 statistics of the attention output when the GDFN runs as one fused kernel
         size_t gs_bytes;
         bool stats_valid;  // ws.stats already holds the LayerNorm statistics of the current stream (written by the producing GEMM)
     };
@@ -129,6 +137,8 @@ int Restormer::load_block(const Blob& blob, const std::string& p, int C, int hea
     {
         std::vector<float> d = pack_dw(t);
         IRB_TRY(upload_f32(d.data(), d.size(), &o.qkv_dw));
+        std::vector<float> dp = pair_major(d, 3 * C);
+        IRB_TRY(upload_f32(dp.data(), dp.size(), &o.qkv_dwp));
     }
     IRB_TRY(blob.get(p + ".attn.project_out.weight", t, C, C, 1, 1));
     IRB_TRY(upload_f32(t.data, size_t(C) * C, &o.proj_w));
@@ -158,6 +168,8 @@ int Restormer::load_block(const Blob& blob, const std::string& p, int C, int hea
             for (int k = 0; k < 9; ++k) w[size_t(k) * 2 * hp + dst] = t.data[size_t(r) * 9 + k];
         }
         IRB_TRY(upload_f32(w.data(), w.size(), &o.ffn_dw));
+        std::vector<float> wp = pair_major(w, 2 * hp);
+        IRB_TRY(upload_f32(wp.data(), wp.size(), &o.ffn_dwp));
     }
     IRB_TRY(blob.get(p + ".ffn.project_out.weight", t, C, h, 1, 1));
     {
@@ -280,7 +292,6 @@ void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
     w.gated = b.take(gat);
     w.weff = b.take(weff);
     w.stats = b.take<float2>(P1 * sizeof(float2));
-    w.stats2 = b.take<float2>(P1 * sizeof(float2));
     w.in8 = b.take<bf16>(P1 * 8 * sizeof(bf16));
     w.G = b.take<float>(gs);
     w.gs_bytes = gs;
@@ -324,7 +335,7 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
         if (!ws.stats_valid) IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
         if (fuse_qkv) {
             IRB_TRY(pwdw_fused_bf16(false, (const bf16*)x, ldx, ws.stats, (const bf16*)w.qkv_w, 3 * C, 0, w.qkv_cs,
-                                    w.qkv_t, w.qkv_dw, 3 * C, (bf16*)ws.qkv, 3 * C, n, H, W, C, s));
+                                    w.qkv_t, w.qkv_dwp, 3 * C, (bf16*)ws.qkv, 3 * C, n, H, W, C, s));
         } else {
             Epi e = make_epi(ws.qkv_pre, 3 * C, dt);
             e.ln_stats = ws.stats;
@@ -345,19 +356,15 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
     else
         IRB_TRY(mdta_gram_simt(ws.qkv, DT_F32, 3 * C, n, H * W, C, heads, nch, G, ssq, s));
     IRB_TRY(mdta_softmax_weff(G, ssq, nch, w.temp, w.proj_w, n, C, heads, ws.weff, dt, ws.attn, s));
-    // bf16, C <= 96: the whole GDFN is one kernel that recomputes the hidden tensor with a halo, so it cannot run in
-    // place: the attention output goes to the scratch stream ws.ln and the GDFN writes x.
-    const bool fused_ffn = dt == DT_BF16 && gdfn_fused_supported(C, w.hp);
     {
-        Epi e = fused_ffn ? make_epi(ws.ln, C, dt) : make_epi(x, ldx, dt);
+        Epi e = make_epi(x, ldx, dt);
         e.res = x;
         e.ldr = ldx;
         e.res_dt = dt;
         const void* v = at(ws.qkv, 2 * C);
         ws.stats_valid = false;
-        float2* st = fused_ffn ? ws.stats2 : ws.stats;
         if (dt == DT_BF16 && tc_can_fuse_stats(C, e)) {  // norm2's statistics come out of this GEMM's epilogue
-            e.stats_out = st;
+            e.stats_out = ws.stats;
             e.stats_eps = 1e-5f;
             ws.stats_valid = true;
         }
@@ -366,19 +373,12 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
         else
             IRB_TRY(simt_gemm(v, DT_F32, 3 * C, H * W, C, n, 0, (const float*)ws.weff, C, C, C, e, s));
     }
-    if (fused_ffn) {
-        if (!ws.stats_valid) IRB_TRY(row_stats(ws.ln, dt, C, ws.stats2, P, C, 1e-5f, s));
-        IRB_TRY(gdfn_fused_bf16((const bf16*)ws.ln, C, ws.stats2, (bf16*)x, ldx, ws.stats, 1e-5f, n, H, W, C, w.hp,
-                                (const bf16*)w.pin_w, w.pin_cs, w.pin_t, w.ffn_dw, (const bf16*)w.pout_w, s));
-        ws.stats_valid = true;
-        return 0;
-    }
     // --- x = x + project_out(gelu(dw(x1)) * dw(x2)) ---
     if (dt == DT_BF16) {  // norm2 folded into project_in
         if (!ws.stats_valid) IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
         if (fuse_gate) {
             IRB_TRY(pwdw_fused_bf16(true, (const bf16*)x, ldx, ws.stats, (const bf16*)w.pin_w, 2 * w.hp, w.hp, w.pin_cs,
-                                    w.pin_t, w.ffn_dw, 2 * w.hp, (bf16*)ws.gated, w.hp, n, H, W, C, s));
+                                    w.pin_t, w.ffn_dwp, 2 * w.hp, (bf16*)ws.gated, w.hp, n, H, W, C, s));
         } else {
             Epi e = make_epi(ws.hidden, 2 * w.hp, dt);
             e.ln_stats = ws.stats;

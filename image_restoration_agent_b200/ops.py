@@ -95,41 +95,6 @@ def gdfn_dw_gate(x, w9c):
     return y
 
 
-def pack_gdfn(ln_w, ln_b, w_in, w_dw, w_out):
-    """Reference GDFN weights (restormer_arch.py:80-86: project_in [2h, C, 1, 1], dwconv [2h, 1, 3, 3], project_out
-    [C, h, 1, 1]) + the block's norm2 -> the operands of irb_gdfn_fused: hidden padded to hp = 64-multiple, LayerNorm
-    gain folded into project_in, colsum of the bf16-rounded folded weights, t = Win . ln_bias."""
-    h2, C = w_in.shape[0], w_in.shape[1]
-    h = h2 // 2
-    hp = (h + 63) // 64 * 64
-    dev = w_in.device
-    win = torch.zeros((2 * hp, C), device=dev, dtype=torch.float32)
-    win[:h] = w_in.reshape(h2, C)[:h].float()
-    win[hp:hp + h] = w_in.reshape(h2, C)[h:].float()
-    t = (win @ ln_b.float()).contiguous() if ln_b is not None else None
-    win = (win * ln_w.float()[None, :]).bfloat16().contiguous()
-    cs = win.float().sum(1).contiguous() if ln_b is not None else None
-    dw = torch.zeros((9, 2 * hp), device=dev, dtype=torch.float32)
-    dw[:, :h] = w_dw.reshape(h2, 9)[:h].float().t()
-    dw[:, hp:hp + h] = w_dw.reshape(h2, 9)[h:].float().t()
-    wout = torch.zeros((C, hp), device=dev, dtype=torch.float32)
-    wout[:, :h] = w_out.reshape(C, h).float()
-    return dict(hp=hp, win=win, cs=cs, t=t, dw=dw.contiguous(), wout=wout.bfloat16().contiguous())
-
-
-def gdfn_fused(x, packed, eps=1e-5):
-    """x [n, H, W, C] bf16 (a channel slice with a larger row stride is fine) -> (x + GDFN(LN(x)), stats [n*H*W, 2])."""
-    n, H, W, C = x.shape
-    y = torch.empty((n, H, W, C), device=x.device, dtype=torch.bfloat16)
-    st_in = torch.empty((n * H * W, 2), device=x.device, dtype=torch.float32)
-    st_out = torch.full((n * H * W, 2), float("nan"), device=x.device, dtype=torch.float32)
-    check(_lib.load().irb_gdfn_fused(x.data_ptr(), x.stride(-2), y.data_ptr(), C, n, H, W, C, packed["hp"],
-                                     packed["win"].data_ptr(), _ptr(packed["cs"]), _ptr(packed["t"]),
-                                     packed["dw"].data_ptr(), packed["wout"].data_ptr(), st_in.data_ptr(),
-                                     st_out.data_ptr(), eps, _stream()))
-    return y, st_out
-
-
 def mdta_gram(qkv, heads):
     """-> (Gpart [n, heads, nchunks, c, c], ssq_part [n, heads, nchunks, 2, c]): per-chunk partial sums."""
     n, H, W, C3 = qkv.shape
@@ -198,7 +163,9 @@ def pwdw_fused(x, stats, w1, dww, colsum=None, t=None, gate=False):
     rows = w1.shape[0]
     hp = rows // 2 if gate else 0
     y = torch.zeros((n, H, W, hp if gate else rows), device=x.device, dtype=torch.bfloat16)
+    # [9, rows] tap-major -> [rows/2, 9, 2]: the 9 taps of a channel pair contiguous (the kernel's layout)
+    dwp = dww.t().reshape(rows // 2, 2, 9).permute(0, 2, 1).contiguous()
     check(_lib.load().irb_pwdw_fused(int(gate), x.data_ptr(), x.stride(2), stats.data_ptr(), w1.data_ptr(), rows, hp,
-                                     _ptr(colsum), _ptr(t), dww.data_ptr(), dww.shape[1], y.data_ptr(), y.shape[3],
+                                     _ptr(colsum), _ptr(t), dwp.data_ptr(), rows, y.data_ptr(), y.shape[3],
                                      n, H, W, C, torch.cuda.current_stream(x.device).cuda_stream))
     return y

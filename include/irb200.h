@@ -83,8 +83,8 @@ int irb_padded_size(int arch, int window_size, int h, int w, int* hp, int* wp);
 int irb_create(const irb_model_desc* desc, const void* weights_blob, size_t nbytes, int device, irb_handle** out);
 void irb_destroy(irb_handle* h);
 /* options: "tile_batch" (max tiles per forward batch inside irb_restore_image; 0 = automatic);
- *          "fuse_pwdw" (default 1: Restormer blocks with C <= 128 run each 1x1 -> depthwise pair as one kernel,
- *          irb_pwdw_fused; 0: the separate GEMM + depthwise kernels);
+ *          "fuse_pwdw" (default 0; 1: Restormer blocks with C <= 128 run each 1x1 -> depthwise pair as one kernel,
+ *          irb_pwdw_fused — parity-equal but measured slower than the separate kernels);
  *          "strict_tile" (default 1: SwinIR tiles must be a multiple of window_size like inference.py:302; 0: the
  *          Flask service's process_image, model_serving.py:146-166, which has no such assert) */
 int irb_set_option(irb_handle* h, const char* key, long long value);
@@ -143,15 +143,6 @@ int irb_dwconv3x3(const void* d_x, int dtype, long long ldx, void* d_y, long lon
 /* GDFN: y[.,c] = gelu(dw(x)[.,c]) * dw(x)[.,hp+c], c < hp; d_w fp32 [9][2*hp] */
 int irb_gdfn_dw_gate(const void* d_x, int dtype, long long ldx, void* d_y, long long ldy, int n, int H, int W, int hp,
                      const float* d_w, void* stream);
-/* The whole GDFN of a Restormer block (restormer_arch.py:88-93 with the block's norm2 and residual,
- * :149-150) as ONE bf16 kernel: y = x + Wout . (gelu(dw(h1)) * dw(h2)), [h1 | h2] = Win' . LN(x).
- * d_win bf16 [2*hp][C] = project_in with the LayerNorm gain folded in (rows [0,hp) = h1, [hp,2hp) = h2, zero padded),
- * d_colsum / d_t fp32 [2*hp] = row sums of the (rounded) folded weights / Win . ln_bias (both NULL for BiasFree),
- * d_dw fp32 [9][2*hp], d_wout bf16 [C][hp]. d_stats_in / d_stats_out: fp32 [n*H*W][2] scratch / output (mu, rstd) of
- * the rows of x / y. C in {16..96} multiple of 16, hp in {64,128,192,256}; y must not alias x. */
-int irb_gdfn_fused(const void* d_x, long long ldx, void* d_y, long long ldy, int n, int H, int W, int C, int hp,
-                   const void* d_win, const float* d_colsum, const float* d_t, const float* d_dw, const void* d_wout,
-                   float* d_stats_in, float* d_stats_out, float eps, void* stream);
 /* A Restormer "1x1 convolution -> depthwise 3x3" pair as ONE bf16 kernel: the tensor between the two convolutions
  * stays in shared memory (restormer_arch.py:115-116 qkv -> qkv_dwconv; :88-93 project_in -> dwconv -> gelu gate).
  *   gate 0: y[n,H,W,:nrows] = dw3x3(h),                      h = W1' . LN(x)   (nrows % 8 == 0)
@@ -159,7 +150,8 @@ int irb_gdfn_fused(const void* d_x, long long ldx, void* d_y, long long ldy, int
  * d_x bf16 [n,H,W,C] (row stride ldx), C in {16..128} multiple of 16; d_stats fp32 [n*H*W][2] = (mu, rstd) of the
  * rows of x; d_w1 bf16 [nrows][C] = the 1x1 weights with the LayerNorm gain folded in; d_colsum / d_t fp32 [nrows]
  * (row sums of the rounded folded weights / W1 . ln_bias; both NULL for BiasFree: h = rstd * (W1' . x));
- * d_dw fp32 [9][dw_ld] tap-major. h is zero outside the image (the depthwise convolution's zero padding). */
+ * d_dw fp32 [nrows/2][9][2]: the 9 taps (ky*3+kx) of each channel PAIR contiguous (dw_ld is ignored).
+ * h is zero outside the image (the depthwise convolution's zero padding). */
 int irb_pwdw_fused(int gate, const void* d_x, long long ldx, const float* d_stats, const void* d_w1, int nrows, int hp,
                    const float* d_colsum, const float* d_t, const float* d_dw, int dw_ld, void* d_y, long long ldy, int n,
                    int H, int W, int C, void* stream);

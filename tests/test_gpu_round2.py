@@ -234,16 +234,16 @@ def test_engine_on_its_own_device_from_a_thread_whose_current_device_differs():
 
 @pytest.mark.parametrize("ln", ["WithBias", "BiasFree"])
 def test_fused_pwdw_model_equals_unfused_within_bf16_rounding(ln):
-    """The fused 1x1 -> depthwise kernels are the default; the separate GEMM + depthwise kernels (option
-    fuse_pwdw = 0) must give the same model output up to bf16 rounding of single elements."""
+    """The fused 1x1 -> depthwise kernels (option fuse_pwdw = 1; opt-in) and the default separate
+    GEMM + depthwise kernels must give the same model output up to bf16 rounding of single elements."""
     from image_restoration_agent_b200._lib import check
     from image_restoration_agent_b200.engine import Engine
     cfg = configs.restormer_config("Motion_Deblurring" if ln == "WithBias" else "Real_Denoising")
     eng = Engine("restormer", cfg, synth.restormer_state_dict(cfg, 0), precision="bf16")
     x = torch.from_numpy(synth.synthetic_image_u8(96, 160, 3, seed=2)).cuda().float().div(255).permute(2, 0, 1)[None]
-    y1 = eng(x.contiguous())
-    check(eng.lib.irb_set_option(eng._h, b"fuse_pwdw", 0))
     y0 = eng(x.contiguous())
     check(eng.lib.irb_set_option(eng._h, b"fuse_pwdw", 1))
+    y1 = eng(x.contiguous())
+    check(eng.lib.irb_set_option(eng._h, b"fuse_pwdw", 0))
     assert torch.isfinite(y1).all() and (y1 - y0).abs().max().item() <= 5e-3
     eng.close()
