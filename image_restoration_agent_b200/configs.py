@@ -31,6 +31,26 @@ def restormer_config(task: str) -> dict:
     return p
 
 
+XRESTORMER_BASE = {  # executor/{dehazing,denoising,deraining,motion_deblurring}/configs/xrestormer.yml: network_g
+    "inp_channels": 3, "out_channels": 3, "dim": 48, "num_blocks": [2, 4, 4, 4], "num_refinement_blocks": 4,
+    "channel_heads": [1, 2, 4, 8], "spatial_heads": [1, 2, 4, 8], "overlap_ratio": [0.5, 0.5, 0.5, 0.5],
+    "window_size": 8, "spatial_dim_head": 16, "ffn_expansion_factor": 2.66, "bias": False,
+    "LayerNorm_type": "WithBias", "dual_pixel_task": False, "scale": 1,
+}
+XRESTORMER_SUBTASKS = ("dehazing", "denoising", "deraining", "motion_deblurring")  # scale 1; SR (scale 4) not served
+
+
+def xrestormer_config() -> dict:
+    """The one architecture all four scale-1 X-Restormer tools share (padding_size 64 in every yml)."""
+    return copy.deepcopy(XRESTORMER_BASE)
+
+
+def small_xrestormer_config(ln_type="WithBias") -> dict:
+    p = copy.deepcopy(XRESTORMER_BASE)
+    p.update(num_blocks=[1, 1, 1, 1], num_refinement_blocks=1, LayerNorm_type=ln_type)
+    return p
+
+
 SWINIR_TASKS = ("classical_sr", "lightweight_sr", "real_sr", "gray_dn", "color_dn", "jpeg_car", "color_jpeg_car")
 
 

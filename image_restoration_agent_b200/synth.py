@@ -86,6 +86,72 @@ def restormer_state_dict(cfg: dict, seed: int = 0) -> "OrderedDict[str, torch.Te
     return sd
 
 
+def xrestormer_state_dict(cfg: dict, seed: int = 0) -> "OrderedDict[str, torch.Tensor]":
+    """Keys / shapes of xrestormer_arch.py:324-380 (TransformerBlock :239-260: channel_attn, channel_ffn,
+    spatial_attn (OCAB with rel_pos_emb), spatial_ffn, norm1..4)."""
+    g = _Gen(seed)
+    sd: OrderedDict[str, torch.Tensor] = OrderedDict()
+    dim = cfg["dim"]
+    with_bias = cfg["LayerNorm_type"] != "BiasFree"
+    assert not cfg.get("bias", False) and not cfg.get("dual_pixel_task", False)
+    ws, dh = cfg["window_size"], cfg["spatial_dim_head"]
+
+    def ffn(prefix, C):
+        hidden = int(C * cfg["ffn_expansion_factor"])
+        sd[f"{prefix}.project_in.weight"] = g.conv(2 * hidden, C, 1)
+        sd[f"{prefix}.dwconv.weight"] = g.conv(2 * hidden, 1, 3)
+        sd[f"{prefix}.project_out.weight"] = g.conv(C, hidden, 1)
+
+    def block(prefix, C, level):
+        ch, sh = cfg["channel_heads"][level], cfg["spatial_heads"][level]
+        inner = dh * sh
+        rel = 2 * (ws + int(ws * cfg["overlap_ratio"][level])) - 1
+        # registration order of the reference module (spatial_attn, channel_attn, norm1..4, channel_ffn, spatial_ffn)
+        sd[f"{prefix}.spatial_attn.qkv.weight"] = g.conv(3 * inner, C, 1)
+        sd[f"{prefix}.spatial_attn.project_out.weight"] = g.conv(C, inner, 1)
+        sd[f"{prefix}.spatial_attn.rel_pos_emb.rel_height"] = g.normal((rel, dh), dh ** -0.5)
+        sd[f"{prefix}.spatial_attn.rel_pos_emb.rel_width"] = g.normal((rel, dh), dh ** -0.5)
+        sd[f"{prefix}.channel_attn.temperature"] = g.uniform((ch, 1, 1), 1.75) + 2.25
+        sd[f"{prefix}.channel_attn.qkv.weight"] = g.conv(3 * C, C, 1)
+        sd[f"{prefix}.channel_attn.qkv_dwconv.weight"] = g.conv(3 * C, 1, 3)
+        sd[f"{prefix}.channel_attn.project_out.weight"] = g.conv(C, C, 1)
+        for nrm in ("norm1", "norm2", "norm3", "norm4"):
+            sd[f"{prefix}.{nrm}.body.weight"] = g.normal((C,), 0.1, 1.0)
+            if with_bias:
+                sd[f"{prefix}.{nrm}.body.bias"] = g.normal((C,), 0.05)
+        ffn(f"{prefix}.channel_ffn", C)
+        ffn(f"{prefix}.spatial_ffn", C)
+
+    nb = cfg["num_blocks"]
+    sd["patch_embed.proj.weight"] = g.conv(dim, cfg["inp_channels"], 3)
+    for i in range(nb[0]):
+        block(f"encoder_level1.{i}", dim, 0)
+    sd["down1_2.body.0.weight"] = g.conv(dim // 2, dim, 3)
+    for i in range(nb[1]):
+        block(f"encoder_level2.{i}", dim * 2, 1)
+    sd["down2_3.body.0.weight"] = g.conv(dim, dim * 2, 3)
+    for i in range(nb[2]):
+        block(f"encoder_level3.{i}", dim * 4, 2)
+    sd["down3_4.body.0.weight"] = g.conv(dim * 2, dim * 4, 3)
+    for i in range(nb[3]):
+        block(f"latent.{i}", dim * 8, 3)
+    sd["up4_3.body.0.weight"] = g.conv(dim * 16, dim * 8, 3)
+    sd["reduce_chan_level3.weight"] = g.conv(dim * 4, dim * 8, 1)
+    for i in range(nb[2]):
+        block(f"decoder_level3.{i}", dim * 4, 2)
+    sd["up3_2.body.0.weight"] = g.conv(dim * 8, dim * 4, 3)
+    sd["reduce_chan_level2.weight"] = g.conv(dim * 2, dim * 4, 1)
+    for i in range(nb[1]):
+        block(f"decoder_level2.{i}", dim * 2, 1)
+    sd["up2_1.body.0.weight"] = g.conv(dim * 4, dim * 2, 3)
+    for i in range(nb[0]):
+        block(f"decoder_level1.{i}", dim * 2, 0)
+    for i in range(cfg["num_refinement_blocks"]):
+        block(f"refinement.{i}", dim * 2, 0)
+    sd["output.weight"] = g.conv(cfg["out_channels"], dim * 2, 3)
+    return sd
+
+
 def swinir_state_dict(cfg: dict, seed: int = 0) -> "OrderedDict[str, torch.Tensor]":
     """Parameters only; the buffers relative_position_index / attn_mask are recomputed analytically."""
     g = _Gen(seed)

@@ -88,3 +88,23 @@ def restormer_restore_image(img_rgb_u8: np.ndarray, model, tile=None, tile_overl
     restored = torch.clamp(restored, 0, 1)[:, :, :height, :width]
     r = restored.permute(0, 2, 3, 1).numpy()[0]
     return np.rint(r * np.float32(255.0)).astype(np.uint8)
+
+
+def xrestormer_restore_image(img_bgr_u8: np.ndarray, model, return_float=False, padding_size: int = 64):
+    """The BasicSR test path of the X-Restormer tool (executor/*/configs/xrestormer.yml: no tile, padding_size 64):
+    cv2.imread BGR -> RGB float/255 (basicsr img2tensor, bgr2rgb) -> reflect pad bottom/right to a multiple of
+    padding_size only when needed (xrestormer_model.py:56-66 pre_process) -> model -> crop (:139-142 post_process) ->
+    tensor2img: clamp(0,1), RGB -> BGR, (x * 255).round() -> uint8. img_bgr_u8: uint8 [H, W, 3] BGR; returns BGR."""
+    x = torch.from_numpy(np.ascontiguousarray(img_bgr_u8[:, :, ::-1])).float().div(255.0).permute(2, 0, 1).unsqueeze(0)
+    _, _, h, w = x.shape
+    ph = (padding_size - h % padding_size) % padding_size
+    pw = (padding_size - w % padding_size) % padding_size
+    x = F.pad(x, (0, pw, 0, ph), "reflect")
+    with torch.no_grad():
+        y = model(x)
+    y = y[:, :, :h, :w]
+    if return_float:
+        return y[0].clone()
+    o = y[0].float().clamp_(0, 1).numpy()
+    o = np.transpose(o[[2, 1, 0], :, :], (1, 2, 0))
+    return (o * 255.0).round().astype(np.uint8)

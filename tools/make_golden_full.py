@@ -143,6 +143,72 @@ def swinir_test():
 GROUPS = {"restormer_tiles": restormer_tiles, "swinir_full": swinir_full, "tool_cfg2": tool_cfg2,
           "swinir_test": swinir_test}
 
+
+
+# ---------------- X-Restormer ----------------
+XR = f"{mg.REF}/AgenticIR/executor/dehazing/tools/X-Restormer"
+
+
+def ref_xrestormer(cfg, sd):
+    """The reference XRestormer class, imported from its file with stand-ins for the two imports that are absent here
+    (basicsr's ARCH_REGISTRY decorator and torchstat, neither touches the arithmetic)."""
+    import importlib.util
+    basicsr = types.ModuleType("basicsr")
+    utils = types.ModuleType("basicsr.utils")
+    registry = types.ModuleType("basicsr.utils.registry")
+
+    class _Reg:
+        def register(self, *a, **k):
+            return lambda cls: cls
+
+    registry.ARCH_REGISTRY = _Reg()
+    torchstat = types.ModuleType("torchstat")
+    torchstat.stat = lambda *a, **k: None
+    sys.modules.update({"basicsr": basicsr, "basicsr.utils": utils, "basicsr.utils.registry": registry,
+                        "torchstat": torchstat})
+    spec = importlib.util.spec_from_file_location("xrestormer_arch_ref", f"{XR}/xrestormer/archs/xrestormer_arch.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    m = mod.XRestormer(**cfg)
+    m.load_state_dict(sd, strict=True)
+    return m.eval()
+
+
+def xrestormer():
+    from oracle import xrestormer_ref
+    cases = [("xrestormer_small_withbias", configs.small_xrestormer_config("WithBias"), (1, 3, 64, 128), 1),
+             ("xrestormer_small_biasfree", configs.small_xrestormer_config("BiasFree"), (2, 3, 64, 64), 2),
+             ("xrestormer_full", configs.xrestormer_config(), (1, 3, 128, 64), 0)]
+    for name, cfg, shape, seed in cases:
+        print(name)
+        sd = synth.xrestormer_state_dict(cfg, seed=seed)
+        ref = ref_xrestormer(cfg, sd)
+        x = image_like(512, 512, 3, seed=seed)[..., 30:30 + shape[2], 70:70 + shape[3]].repeat(shape[0], 1, 1, 1).contiguous()
+        if shape[0] > 1:
+            x[1] = x[1].flip(-1)
+        with torch.no_grad():
+            y_ref = ref(x)
+        y_or = xrestormer_ref.Model(sd, cfg)(x)
+        mg.check(name, y_or, y_ref, tol=2e-5)
+        mg.save(name, x=x.numpy(), y=y_ref.numpy(), seed=np.int64(seed))
+    # tool level: reflect pad to a multiple of 64, whole image, crop, tensor2img (xrestormer_model.py:56-66, :139-142)
+    name = "xrestormer_tool_small"
+    print(name)
+    cfg = configs.small_xrestormer_config("WithBias")
+    sd = synth.xrestormer_state_dict(cfg, seed=3)
+    ref = ref_xrestormer(cfg, sd)
+    img = synth.synthetic_image_u8(70, 100, 3, seed=4)
+    u8_ref = tiling.xrestormer_restore_image(img, ref)
+    f_ref = tiling.xrestormer_restore_image(img, ref, return_float=True)
+    u8_or = tiling.xrestormer_restore_image(img, xrestormer_ref.Model(sd, cfg))
+    d = np.abs(u8_or.astype(int) - u8_ref.astype(int)).max()
+    print(f"  uint8 oracle vs reference: max LSB diff = {d}")
+    assert d <= 1
+    mg.save(name, img=img, out_u8=u8_ref, out_f32=f_ref.numpy(), seed=np.int64(3), tile=np.int64(-1), overlap=np.int64(0))
+
+
+GROUPS["xrestormer"] = xrestormer
+
 if __name__ == "__main__":
     torch.manual_seed(0)
     torch.set_num_threads(os.cpu_count() or 8)
