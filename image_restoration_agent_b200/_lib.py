@@ -14,7 +14,7 @@ PKG = Path(__file__).resolve().parent
 # IRB_LIB selects another build of the same ABI (the -DIRB_DIAG library of tools/gpu_ab.sh); default = the product
 LIB_PATH = Path(os.environ["IRB_LIB"]).resolve() if os.environ.get("IRB_LIB") else PKG / "libirb200.so"
 
-ARCH_RESTORMER, ARCH_SWINIR = 1, 2
+ARCH_RESTORMER, ARCH_SWINIR, ARCH_XRESTORMER = 1, 2, 3
 F32, BF16 = 0, 1
 UPSAMPLER_NONE, UPSAMPLER_PIXELSHUFFLE, UPSAMPLER_NEAREST_CONV = 0, 1, 2
 ACT_NONE, ACT_GELU, ACT_LRELU = 0, 1, 2
@@ -28,6 +28,7 @@ class ModelDesc(C.Structure):
         ("img_size", C.c_int), ("window_size", C.c_int), ("embed_dim", C.c_int), ("num_layers", C.c_int),
         ("depths", C.c_int * 16), ("num_heads", C.c_int * 16), ("mlp_ratio", C.c_int), ("upscale", C.c_int),
         ("img_range", C.c_float), ("upsampler", C.c_int), ("resi_3conv", C.c_int),
+        ("spatial_heads", C.c_int * 4), ("spatial_dim_head", C.c_int), ("overlap_ratio", C.c_float),
     ]
 
 
@@ -58,6 +59,7 @@ PROTOTYPES = {
     "irb_dwconv3x3": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "irb_gdfn_dw_gate": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _vp, _vp]),
     "irb_pwdw_fused": (_i, [_i, _vp, _ll, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _vp, _ll, _i, _i, _i, _i, _vp]),
+    "irb_ocab": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "irb_mdta_nchunks": (_i, [_i, _i, _i]),
     "irb_mdta_gram": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "irb_mdta_attn": (_i, [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp]),

@@ -111,6 +111,9 @@ int irb_padded_size(int arch, int window_size, int h, int w, int* hp, int* wp) {
     } else if (arch == IRB_ARCH_RESTORMER) {
         *hp = (h % 8) ? ((h + 8) / 8) * 8 : h;  // demo.py:122-126
         *wp = (w % 8) ? ((w + 8) / 8) * 8 : w;
+    } else if (arch == IRB_ARCH_XRESTORMER) {
+        *hp = (h % 64) ? (h / 64 + 1) * 64 : h;  // xrestormer_model.py:56-66, padding_size 64
+        *wp = (w % 64) ? (w / 64 + 1) * 64 : w;
     } else {
         set_error("irb_padded_size: unknown arch");
         return 1;
@@ -242,6 +245,13 @@ int irb_pwdw_fused(int gate, const void* d_x, long long ldx, const float* d_stat
     IRB_TRY(require_device());
     return pwdw_fused_bf16(gate != 0, (const bf16*)d_x, ldx, reinterpret_cast<const float2*>(d_stats), (const bf16*)d_w1,
                            nrows, hp, d_colsum, d_t, d_dw, dw_ld, (bf16*)d_y, ldy, n, H, W, C, (cudaStream_t)stream);
+}
+
+int irb_ocab(const void* d_qkv, int dtype, long long ld, void* d_out, long long ldo, int n, int H, int W, int heads,
+             int dim_head, int window, int overlap_window, const float* d_rel_h, const float* d_rel_w, void* stream) {
+    IRB_TRY(require_device());
+    return ocab_attention(d_qkv, dtype == IRB_BF16 ? DT_BF16 : DT_F32, ld, d_out, ldo, n, H, W, heads, dim_head, window,
+                          overlap_window, d_rel_h, d_rel_w, (cudaStream_t)stream);
 }
 
 int irb_mdta_nchunks(int P, int heads, int n) { return mdta_nchunks(P, heads, n); }

@@ -53,6 +53,10 @@ int dwconv3x3_bf16_tma(const bf16* x, long long ldx, bf16* y, long long ldy, int
                        const float* wt, cudaStream_t stream);
 int dwconv3x3_gate_bf16_tma(const bf16* x, long long ldx, bf16* y, long long ldy, int Nimg, int H, int W, int hp,
                             const float* wt, cudaStream_t stream);
+// ---- ocab.cu : X-Restormer overlapping cross-attention (xrestormer_arch.py:190-237) ----
+int ocab_attention(const void* qkv, int dt, long long ld, void* out, long long ldo, int Nimg, int H, int W, int heads,
+                   int dim_head, int ws, int ows, const float* rel_h, const float* rel_w, cudaStream_t stream);
+
 // ---- pwdw_fused.cu : 1x1 convolution (folded LayerNorm) -> depthwise 3x3 [-> GELU gate] without the HBM round trip ----
 bool pwdw_fused_shape_ok(int C, int nrows, bool gate, int hp);
 int pwdw_fused_bf16(bool gate, const bf16* x, long long ldx, const float2* stats, const bf16* w1, int nrows, int hp,

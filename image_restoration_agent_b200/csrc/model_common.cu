@@ -306,7 +306,7 @@ int irb_create(const irb_model_desc* desc, const void* weights_blob, size_t nbyt
     IRB_TRY(blob.parse(weights_blob, nbytes));
     Model* m = nullptr;
     int rc;
-    if (desc->arch == IRB_ARCH_RESTORMER)
+    if (desc->arch == IRB_ARCH_RESTORMER || desc->arch == IRB_ARCH_XRESTORMER)
         rc = build_restormer(*desc, blob, device, &m);
     else if (desc->arch == IRB_ARCH_SWINIR)
         rc = build_swinir(*desc, blob, device, &m);

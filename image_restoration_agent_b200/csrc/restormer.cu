@@ -28,6 +28,21 @@ struct RBlockW {
     // bf16 mode: norm1 / norm2 are folded into qkv_w / pin_w (W' = W diag(gain)); the GEMM epilogue applies
     // rstd * (acc - mu * colsum) + t with colsum[n] = sum_k W'[n,k], t[n] = sum_k W[n,k] * ln_bias[k]
     float *qkv_cs, *qkv_t, *pin_cs, *pin_t;
+    // X-Restormer (xrestormer_arch.py:239-260): the block continues with x += OCAB(norm3(x)); x += GDFN(norm4(x))
+    bool has_spatial = false;
+    int sheads = 0, inner = 0, ows = 0;  // spatial heads, sheads * dim_head, overlapping window size
+    float *n3w = nullptr, *n3b = nullptr;
+    void* oc_qkv_w = nullptr;    // [3*inner][C] (norm3 folded in bf16 mode)
+    float *oc_cs = nullptr, *oc_t = nullptr;
+    void* oc_proj_w = nullptr;   // [C][inner]
+    float *rel_h = nullptr, *rel_w = nullptr;  // [2*ows-1][dim_head]
+    RBlockW* sp = nullptr;       // the second GDFN (norm4 + spatial_ffn), stored in the ffn fields of another RBlockW
+};
+
+// state_dict names of the pieces of a block: Restormer {norm1, attn, norm2, ffn}; X-Restormer's first half
+// {norm1, channel_attn, norm2, channel_ffn} and its second GDFN {-, -, norm4, spatial_ffn}
+struct BlockNames {
+    const char *norm_a, *attn, *norm_f, *ffn;
 };
 
 // W [N][K] (row stride ldw) -> W' = W * diag(gain) in place; colsum of the bf16-ROUNDED W'; t = W . ln_bias
@@ -70,7 +85,7 @@ struct Restormer : Model {
     ConvW patch, down12, down23, down34, up43, up32, up21, outc;
     void *reduce3, *reduce2;
 
-    int tile_multiple() const override { return 8; }
+    int tile_multiple() const override { return desc.arch == IRB_ARCH_XRESTORMER ? 64 : 8; }
     size_t forward_workspace(int n, int H, int W) override;
     int forward(const float* in, float* out, int n, int H, int W, void* ws, size_t ws_bytes,
                 cudaStream_t stream) override;
@@ -84,7 +99,12 @@ struct Restormer : Model {
         bool stats_valid;  // ws.stats already holds the LayerNorm statistics of the current stream (written by the producing GEMM)
     };
     void layout(Bump& b, int n, int H, int W, WS& w);
-    int load_block(const Blob& blob, const std::string& p, int C, int heads, RBlockW& o);
+    int load_block(const Blob& blob, const std::string& p, int C, int heads, RBlockW& o,
+                   BlockNames nm = {"norm1", "attn", "norm2", "ffn"});
+    int load_spatial(const Blob& blob, const std::string& p, int C, int level, RBlockW& o);
+    int run_attn(const RBlockW& w, void* x, long long ldx, int n, int H, int W, WS& ws, cudaStream_t s);
+    int run_ffn(const RBlockW& w, void* x, long long ldx, int n, int H, int W, WS& ws, cudaStream_t s);
+    int run_ocab(const RBlockW& w, void* x, long long ldx, int n, int H, int W, WS& ws, cudaStream_t s);
     int load_conv(const Blob& blob, const std::string& name, int N, int C, ConvW& o, bool pixelshuffle = false);
     int run_block(const RBlockW& w, void* x, long long ldx, int n, int H, int W, WS& ws, cudaStream_t s);
     int run_conv(const ConvW& c, const void* x, int x_dt, long long ldx, int n, int H, int W, Epi e, cudaStream_t s);
@@ -93,35 +113,44 @@ struct Restormer : Model {
     char* at(void* p, long long elems) { return reinterpret_cast<char*>(p) + elems * (long long)esize(); }
 };
 
-int Restormer::load_block(const Blob& blob, const std::string& p, int C, int heads, RBlockW& o) {
+int Restormer::load_block(const Blob& blob, const std::string& p, int C, int heads, RBlockW& o, BlockNames nm) {
+    const bool has_attn = nm.attn != nullptr;
+    const std::string NA = p + "." + (has_attn ? nm.norm_a : nm.norm_f), NF = p + "." + nm.norm_f;
+    const std::string AT = p + "." + (has_attn ? nm.attn : ""), FF = p + "." + nm.ffn;
     o.C = C;
     o.heads = heads;
     o.h = int(C * desc.ffn_expansion_factor);  // restormer_arch.py:80 int(dim*ffn_expansion_factor)
     o.hp = (o.h + 63) / 64 * 64;
     BlobTensor t;
-    IRB_TRY(blob.get(p + ".norm1.body.weight", t, C));
+    IRB_TRY(blob.get(NA + ".body.weight", t, C));
     IRB_TRY(upload_f32(t.data, C, &o.n1w));
-    IRB_TRY(blob.get(p + ".norm2.body.weight", t, C));
+    IRB_TRY(blob.get(NF + ".body.weight", t, C));
     IRB_TRY(upload_f32(t.data, C, &o.n2w));
     o.n1b = o.n2b = nullptr;
     if (!desc.ln_bias_free) {
-        IRB_TRY(blob.get(p + ".norm1.body.bias", t, C));
+        IRB_TRY(blob.get(NA + ".body.bias", t, C));
         IRB_TRY(upload_f32(t.data, C, &o.n1b));
-        IRB_TRY(blob.get(p + ".norm2.body.bias", t, C));
+        IRB_TRY(blob.get(NF + ".body.bias", t, C));
         IRB_TRY(upload_f32(t.data, C, &o.n2b));
     }
-    IRB_TRY(blob.get(p + ".attn.temperature", t, heads, 1, 1));
-    IRB_TRY(upload_f32(t.data, heads, &o.temp));
+    o.temp = nullptr;
+    if (has_attn) {
+        IRB_TRY(blob.get(AT + ".temperature", t, heads, 1, 1));
+        IRB_TRY(upload_f32(t.data, heads, &o.temp));
+    }
     const bool fold = dt == DT_BF16;
     BlobTensor g1, b1, g2, b2;
-    IRB_TRY(blob.get(p + ".norm1.body.weight", g1, C));
-    IRB_TRY(blob.get(p + ".norm2.body.weight", g2, C));
+    IRB_TRY(blob.get(NA + ".body.weight", g1, C));
+    IRB_TRY(blob.get(NF + ".body.weight", g2, C));
     if (!desc.ln_bias_free) {
-        IRB_TRY(blob.get(p + ".norm1.body.bias", b1, C));
-        IRB_TRY(blob.get(p + ".norm2.body.bias", b2, C));
+        IRB_TRY(blob.get(NA + ".body.bias", b1, C));
+        IRB_TRY(blob.get(NF + ".body.bias", b2, C));
     }
     o.qkv_cs = o.qkv_t = o.pin_cs = o.pin_t = nullptr;
-    IRB_TRY(blob.get(p + ".attn.qkv.weight", t, 3 * C, C, 1, 1));
+    o.qkv_w = nullptr;
+    o.qkv_dw = o.qkv_dwp = o.proj_w = nullptr;
+    if (has_attn) {
+    IRB_TRY(blob.get(AT + ".qkv.weight", t, 3 * C, C, 1, 1));
     {
         std::vector<float> w(t.data, t.data + size_t(3) * C * C), cs, tt;
         if (fold) {
@@ -133,17 +162,18 @@ int Restormer::load_block(const Blob& blob, const std::string& p, int C, int hea
         }
         IRB_TRY(upload_act(w.data(), w.size(), &o.qkv_w));
     }
-    IRB_TRY(blob.get(p + ".attn.qkv_dwconv.weight", t, 3 * C, 1, 3, 3));
+    IRB_TRY(blob.get(AT + ".qkv_dwconv.weight", t, 3 * C, 1, 3, 3));
     {
         std::vector<float> d = pack_dw(t);
         IRB_TRY(upload_f32(d.data(), d.size(), &o.qkv_dw));
         std::vector<float> dp = pair_major(d, 3 * C);
         IRB_TRY(upload_f32(dp.data(), dp.size(), &o.qkv_dwp));
     }
-    IRB_TRY(blob.get(p + ".attn.project_out.weight", t, C, C, 1, 1));
+    IRB_TRY(blob.get(AT + ".project_out.weight", t, C, C, 1, 1));
     IRB_TRY(upload_f32(t.data, size_t(C) * C, &o.proj_w));
+    }
     const int h = o.h, hp = o.hp;
-    IRB_TRY(blob.get(p + ".ffn.project_in.weight", t, 2 * h, C, 1, 1));
+    IRB_TRY(blob.get(FF + ".project_in.weight", t, 2 * h, C, 1, 1));
     {
         std::vector<float> w(size_t(2) * hp * C, 0.f);
         for (int r = 0; r < 2 * h; ++r) {
@@ -160,7 +190,7 @@ int Restormer::load_block(const Blob& blob, const std::string& p, int C, int hea
         }
         IRB_TRY(upload_act(w.data(), w.size(), &o.pin_w));
     }
-    IRB_TRY(blob.get(p + ".ffn.dwconv.weight", t, 2 * h, 1, 3, 3));
+    IRB_TRY(blob.get(FF + ".dwconv.weight", t, 2 * h, 1, 3, 3));
     {
         std::vector<float> w(size_t(9) * 2 * hp, 0.f);
         for (int r = 0; r < 2 * h; ++r) {
@@ -171,13 +201,50 @@ int Restormer::load_block(const Blob& blob, const std::string& p, int C, int hea
         std::vector<float> wp = pair_major(w, 2 * hp);
         IRB_TRY(upload_f32(wp.data(), wp.size(), &o.ffn_dwp));
     }
-    IRB_TRY(blob.get(p + ".ffn.project_out.weight", t, C, h, 1, 1));
+    IRB_TRY(blob.get(FF + ".project_out.weight", t, C, h, 1, 1));
     {
         std::vector<float> w(size_t(C) * hp, 0.f);
         for (int r = 0; r < C; ++r) memcpy(&w[size_t(r) * hp], t.data + size_t(r) * h, size_t(h) * 4);
         IRB_TRY(upload_act(w.data(), w.size(), &o.pout_w));
     }
     return 0;
+}
+
+// OCAB + norm3 + the second GDFN of an X-Restormer block (xrestormer_arch.py:190-260)
+int Restormer::load_spatial(const Blob& blob, const std::string& p, int C, int level, RBlockW& o) {
+    const int dh = desc.spatial_dim_head;
+    o.has_spatial = true;
+    o.sheads = desc.spatial_heads[level];
+    o.inner = dh * o.sheads;
+    o.ows = int(desc.window_size * desc.overlap_ratio) + desc.window_size;  // :196
+    const int inner = o.inner, rel = 2 * o.ows - 1;
+    BlobTensor t, g3, b3;
+    IRB_TRY(blob.get(p + ".norm3.body.weight", g3, C));
+    IRB_TRY(upload_f32(g3.data, C, &o.n3w));
+    if (!desc.ln_bias_free) {
+        IRB_TRY(blob.get(p + ".norm3.body.bias", b3, C));
+        IRB_TRY(upload_f32(b3.data, C, &o.n3b));
+    }
+    IRB_TRY(blob.get(p + ".spatial_attn.qkv.weight", t, 3 * inner, C, 1, 1));
+    {
+        std::vector<float> w(t.data, t.data + size_t(3) * inner * C), cs, tt;
+        if (dt == DT_BF16) {
+            fold_ln(w, 3 * inner, C, C, g3.data, desc.ln_bias_free ? nullptr : b3.data, cs, tt);
+            if (!desc.ln_bias_free) {
+                IRB_TRY(upload_f32(cs.data(), cs.size(), &o.oc_cs));
+                IRB_TRY(upload_f32(tt.data(), tt.size(), &o.oc_t));
+            }
+        }
+        IRB_TRY(upload_act(w.data(), w.size(), &o.oc_qkv_w));
+    }
+    IRB_TRY(blob.get(p + ".spatial_attn.project_out.weight", t, C, inner, 1, 1));
+    IRB_TRY(upload_act(t.data, size_t(C) * inner, &o.oc_proj_w));
+    IRB_TRY(blob.get(p + ".spatial_attn.rel_pos_emb.rel_height", t, rel, dh));
+    IRB_TRY(upload_f32(t.data, size_t(rel) * dh, &o.rel_h));
+    IRB_TRY(blob.get(p + ".spatial_attn.rel_pos_emb.rel_width", t, rel, dh));
+    IRB_TRY(upload_f32(t.data, size_t(rel) * dh, &o.rel_w));
+    o.sp = new RBlockW();
+    return load_block(blob, p, C, 1, *o.sp, BlockNames{nullptr, nullptr, "norm4", "spatial_ffn"});
 }
 
 int Restormer::load_conv(const Blob& blob, const std::string& name, int N, int C, ConvW& o, bool pixelshuffle) {
@@ -222,9 +289,31 @@ int build_restormer(const irb_model_desc& d, const Blob& blob, int device, Model
                     "Restormer: channels per head must divide and be <= 96");
     IRB_REQUIRE((2 * d.dim) % d.heads[0] == 0 && (2 * d.dim) / d.heads[0] <= 96, "Restormer: decoder-1 head size");
     const int dim = d.dim;
+    const bool xr = d.arch == IRB_ARCH_XRESTORMER;
+    if (xr) {
+        IRB_REQUIRE(d.spatial_dim_head == 16 && d.window_size >= 2 && d.window_size <= 8, "XRestormer: spatial_dim_head 16, window <= 8");
+        IRB_REQUIRE(d.overlap_ratio >= 0.f && int(d.window_size * d.overlap_ratio) % 2 == 0 &&
+                        int(d.window_size * d.overlap_ratio) + d.window_size <= 16,
+                    "XRestormer: overlapping window must be <= 16 and symmetric");
+        for (int l = 0; l < 4; ++l)
+            IRB_REQUIRE(d.spatial_heads[l] >= 1 && 3 * 16 * d.spatial_heads[l] <= 3 * (d.dim << l),
+                        "XRestormer: spatial heads x 16 must not exceed the level's channel count");
+    }
     auto stage = [&](std::vector<RBlockW>& v, const char* name, int nblk, int C, int heads) -> int {
         v.resize(nblk);
-        for (int i = 0; i < nblk; ++i) IRB_TRY(m->load_block(blob, std::string(name) + "." + std::to_string(i), C, heads, v[i]));
+        for (int i = 0; i < nblk; ++i) {
+            const std::string p = std::string(name) + "." + std::to_string(i);
+            if (!xr) {
+                IRB_TRY(m->load_block(blob, p, C, heads, v[i]));
+            } else {  // level of this stage: 0 for C = dim and for the 2*dim decoder-1 / refinement stages
+                const bool lvl0 = strcmp(name, "encoder_level1") == 0 || strcmp(name, "decoder_level1") == 0 ||
+                                  strcmp(name, "refinement") == 0;
+                int level = 0;
+                if (!lvl0) level = C == dim * 2 ? 1 : (C == dim * 4 ? 2 : 3);
+                IRB_TRY(m->load_block(blob, p, C, heads, v[i], BlockNames{"norm1", "channel_attn", "norm2", "channel_ffn"}));
+                IRB_TRY(m->load_spatial(blob, p, C, level, v[i]));
+            }
+        }
         return 0;
     };
     IRB_TRY(m->load_conv(blob, "patch_embed.proj.weight", dim, d.in_chans, m->patch));
@@ -324,13 +413,23 @@ int Restormer::run_conv(const ConvW& c, const void* x, int x_dt, long long ldx, 
 
 // TransformerBlock.forward (restormer_arch.py:146-150) on the stream x [n*H*W, C] (row stride ldx), in place.
 int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H, int W, WS& ws, cudaStream_t s) {
+    IRB_TRY(run_attn(w, x, ldx, n, H, W, ws, s));
+    IRB_TRY(run_ffn(w, x, ldx, n, H, W, ws, s));
+    if (w.has_spatial) {  // xrestormer_arch.py:259-260
+        IRB_TRY(run_ocab(w, x, ldx, n, H, W, ws, s));
+        IRB_TRY(run_ffn(*w.sp, x, ldx, n, H, W, ws, s));
+    }
+    return 0;
+}
+
+// x = x + project_out(attn(norm1(x)))   (restormer_arch.py:148)
+int Restormer::run_attn(const RBlockW& w, void* x, long long ldx, int n, int H, int W, WS& ws, cudaStream_t s) {
     const int C = w.C, heads = w.heads, c = C / heads;
     const long long P = (long long)n * H * W;
     const int mode = desc.ln_bias_free ? 1 : 0;
     // --- x = x + project_out(attn(norm1(x))) ---
     // bf16, C <= 128: each "1x1 -> depthwise 3x3" pair is one kernel (pwdw_fused.cu): qkv_pre / hidden stay on the SM
     const bool fuse_qkv = dt == DT_BF16 && fuse_pwdw && pwdw_fused_shape_ok(C, 3 * C, false, 0);
-    const bool fuse_gate = dt == DT_BF16 && fuse_pwdw && pwdw_fused_shape_ok(C, 2 * w.hp, true, w.hp);
     if (dt == DT_BF16) {  // norm1 folded into the qkv GEMM
         if (!ws.stats_valid) IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
         if (fuse_qkv) {
@@ -373,6 +472,15 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
         else
             IRB_TRY(simt_gemm(v, DT_F32, 3 * C, H * W, C, n, 0, (const float*)ws.weff, C, C, C, e, s));
     }
+    return 0;
+}
+
+// x = x + project_out(gelu(dw(x1)) * dw(x2)), [x1 | x2] = project_in(norm2(x))   (restormer_arch.py:149, :88-93)
+int Restormer::run_ffn(const RBlockW& w, void* x, long long ldx, int n, int H, int W, WS& ws, cudaStream_t s) {
+    const int C = w.C;
+    const long long P = (long long)n * H * W;
+    const int mode = desc.ln_bias_free ? 1 : 0;
+    const bool fuse_gate = dt == DT_BF16 && fuse_pwdw && pwdw_fused_shape_ok(C, 2 * w.hp, true, w.hp);
     // --- x = x + project_out(gelu(dw(x1)) * dw(x2)) ---
     if (dt == DT_BF16) {  // norm2 folded into project_in
         if (!ws.stats_valid) IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
@@ -405,6 +513,37 @@ int Restormer::run_block(const RBlockW& w, void* x, long long ldx, int n, int H,
         IRB_TRY(run_gemm(ws.gated, w.hp, P, w.hp, w.pout_w, w.hp, C, C, e, s));
     }
     return 0;
+}
+
+// x = x + project_out(OCA(qkv(norm3(x))))   (xrestormer_arch.py:259, :190-237)
+int Restormer::run_ocab(const RBlockW& w, void* x, long long ldx, int n, int H, int W, WS& ws, cudaStream_t s) {
+    const int C = w.C, inner = w.inner;
+    const long long P = (long long)n * H * W;
+    const int mode = desc.ln_bias_free ? 1 : 0;
+    if (dt == DT_BF16) {  // norm3 folded into the qkv GEMM
+        if (!ws.stats_valid) IRB_TRY(row_stats(x, dt, ldx, ws.stats, P, C, 1e-5f, s));
+        Epi e = make_epi(ws.qkv, 3 * inner, dt);
+        e.ln_stats = ws.stats;
+        e.ln_colsum = w.oc_cs;
+        e.bias = w.oc_t;
+        IRB_TRY(run_gemm(x, ldx, P, C, w.oc_qkv_w, C, 3 * inner, 3 * inner, e, s));
+    } else {
+        IRB_TRY(layernorm(x, dt, ldx, ws.ln, dt, C, P, C, w.n3w, w.n3b, mode, 1e-5f, s));
+        IRB_TRY(run_gemm(ws.ln, C, P, C, w.oc_qkv_w, C, 3 * inner, 3 * inner, make_epi(ws.qkv, 3 * inner, dt), s));
+    }
+    IRB_TRY(ocab_attention(ws.qkv, dt, 3 * inner, ws.ln, inner, n, H, W, w.sheads, desc.spatial_dim_head,
+                           desc.window_size, w.ows, w.rel_h, w.rel_w, s));
+    Epi e = make_epi(x, ldx, dt);
+    e.res = x;
+    e.ldr = ldx;
+    e.res_dt = dt;
+    ws.stats_valid = false;
+    if (dt == DT_BF16 && tc_can_fuse_stats(C, e)) {  // norm4's statistics
+        e.stats_out = ws.stats;
+        e.stats_eps = 1e-5f;
+        ws.stats_valid = true;
+    }
+    return run_gemm(ws.ln, inner, P, inner, w.oc_proj_w, inner, C, C, e, s);
 }
 
 int Restormer::forward(const float* in, float* out, int n, int H, int W, void* wsp, size_t ws_bytes,

@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import ARCH_RESTORMER, ARCH_SWINIR, BF16, F32, ModelDesc, check
+from ._lib import ARCH_RESTORMER, ARCH_SWINIR, ARCH_XRESTORMER, BF16, F32, ModelDesc, check
 from .weights import state_dict_to_blob
 
 _UPSAMPLER = {"": 0, None: 0, "pixelshuffle": 1, "nearest+conv": 2}
@@ -30,6 +30,27 @@ def restormer_desc(cfg: dict, precision: int) -> ModelDesc:
     d.heads[:] = cfg["heads"]
     d.ffn_expansion_factor = cfg["ffn_expansion_factor"]
     d.ln_bias_free = int(cfg["LayerNorm_type"] == "BiasFree")
+    return d
+
+
+def xrestormer_desc(cfg: dict, precision: int) -> ModelDesc:
+    """XRestormer(...) of xrestormer_arch.py:324-341 with the agent's configs (executor/*/configs/xrestormer.yml)."""
+    if cfg.get("bias", False) or cfg.get("dual_pixel_task", False) or cfg.get("scale", 1) != 1:
+        raise ValueError("irb200 X-Restormer supports bias=False, dual_pixel_task=False, scale=1")
+    if len(set(cfg["overlap_ratio"])) != 1:
+        raise ValueError("irb200 X-Restormer needs one overlap_ratio for all levels")
+    d = ModelDesc()
+    d.arch, d.precision, d.in_chans = ARCH_XRESTORMER, precision, cfg["inp_channels"]
+    d.dim = cfg["dim"]
+    d.num_blocks[:] = cfg["num_blocks"]
+    d.num_refinement_blocks = cfg["num_refinement_blocks"]
+    d.heads[:] = cfg["channel_heads"]
+    d.ffn_expansion_factor = cfg["ffn_expansion_factor"]
+    d.ln_bias_free = int(cfg["LayerNorm_type"] == "BiasFree")
+    d.window_size = cfg["window_size"]
+    d.spatial_heads[:] = cfg["spatial_heads"]
+    d.spatial_dim_head = cfg["spatial_dim_head"]
+    d.overlap_ratio = cfg["overlap_ratio"][0]
     return d
 
 
@@ -63,7 +84,7 @@ class Engine:
         self.dev = torch.device("cuda", self.device)
         prec = {"bf16": BF16, "fp32": F32, "f32": F32}[precision]
         self.precision = precision
-        desc = restormer_desc(cfg, prec) if arch == "restormer" else swinir_desc(cfg, prec)
+        desc = {"restormer": restormer_desc, "swinir": swinir_desc, "xrestormer": xrestormer_desc}[arch](cfg, prec)
         blob = state_dict_to_blob(state_dict)
         h = C.c_void_p()
         # irb_create uploads on `device` and restores the caller's current device; the calling thread's device is

@@ -216,6 +216,45 @@ class RestormerB200(Tool):
         cv2.imwrite(str(Path(self.output_dir) / "output.png"), out)
 
 
+class XRestormerB200(Tool):
+    """In-process replacement of multitask_tools.XRestormer (tool_name 'xrestormer', a BasicSRModel tool:
+    multitask_tools.py:67-78) for the four scale-1 subtasks. The reference runs BasicSR's test pipeline on the yml of
+    executor/<subtask>/configs/xrestormer.yml: reflect pad to a multiple of 64, whole image, crop, tensor2img."""
+
+    SUBTASKS = configs.XRESTORMER_SUBTASKS
+    WEIGHTS = {"dehazing": "dehaze_300k.pth", "denoising": "denoise_300k.pth", "deraining": "derain_155k.pth",
+               "motion_deblurring": "deblur_300k.pth"}  # path.pretrain_network_g of the four ymls
+
+    def __init__(self, subtask: str, weights_root: Optional[str] = None, state_dict=None, precision: str = "bf16",
+                 device: int = 0, cfg: Optional[dict] = None):
+        if subtask not in self.SUBTASKS:
+            raise ValueError(f"irb200 X-Restormer serves {self.SUBTASKS} (scale 1); got {subtask!r}")
+        super().__init__(tool_name="xrestormer", subtask=subtask)
+        self.cfg = cfg or configs.xrestormer_config()
+        self.weights_root, self.state_dict = weights_root, state_dict
+        self.precision, self.device = precision, device
+
+    def _engine(self) -> Engine:
+        def sd():
+            if self.state_dict is not None:
+                return self.state_dict
+            return load_checkpoint(os.path.join(self.weights_root, self.WEIGHTS[self.subtask]), ("params_ema", "params"))
+        src = (self.state_dict if self.state_dict is not None
+               else os.path.join(self.weights_root, self.WEIGHTS[self.subtask]))
+        return get_engine("xrestormer", src, self.cfg, sd, self.precision, self.device)
+
+    def restore_u8_device(self, img_bgr, graph: bool = False):
+        return self._engine().restore_device(img_bgr, None, 0, bgr=True, graph=graph)[0]
+
+    def _invoke(self) -> None:
+        import cv2
+
+        path = sorted(Path(self.input_dir).glob("*"))[0]
+        img = _imread(path, cv2.IMREAD_COLOR)
+        out = self._engine().restore(img, None, 0, bgr=True)
+        cv2.imwrite(str(Path(self.output_dir) / "output.png"), out)
+
+
 class Chain:
     """A plan of several tools run back to back on one image (BASELINE config 4: derain -> denoise -> x4 SR) with the
     inter-stage hand-off kept in HBM.

@@ -30,6 +30,7 @@ extern "C" {
 
 #define IRB_ARCH_RESTORMER 1
 #define IRB_ARCH_SWINIR 2
+#define IRB_ARCH_XRESTORMER 3 /* X-Restormer: Restormer blocks + overlapping cross-attention */
 
 #define IRB_F32 0  /* fp32 storage + fp32 FMA arithmetic (verification mode, <=1e-4 of the reference) */
 #define IRB_BF16 1 /* bf16 storage, tcgen05 tensor-core contractions with fp32 accumulation */
@@ -64,6 +65,11 @@ typedef struct irb_model_desc {
     float img_range;
     int upsampler;  /* IRB_UPSAMPLER_* */
     int resi_3conv; /* 1: resi_connection='3conv', 0: '1conv' */
+    /* XRestormer(...)  xrestormer_arch.py:324-341: dim, num_blocks, num_refinement_blocks, heads (= channel_heads),
+     * ffn_expansion_factor, ln_bias_free as above, window_size as above, plus: */
+    int spatial_heads[4];
+    int spatial_dim_head;
+    float overlap_ratio; /* the same for every level in all agent configs */
 } irb_model_desc;
 
 const char* irb_last_error(void);
@@ -75,7 +81,8 @@ int irb_version(void);
 int irb_plan_tiles(int n, int tile, int overlap, int* idx, int* count);
 
 /* Padded size the reference scripts feed to the model: SwinIR (h / ws + 1) * ws (always pads,
- * inference.py:76-78); Restormer next multiple of 8 only when needed (demo.py:122-126). Host-only. */
+ * inference.py:76-78); Restormer next multiple of 8 only when needed (demo.py:122-126); X-Restormer next multiple of
+ * 64 only when needed (xrestormer_model.py:56-66, padding_size 64). Host-only. */
 int irb_padded_size(int arch, int window_size, int h, int w, int* hp, int* wp);
 
 /* weights_blob: host memory, format documented in image_restoration_agent_b200/weights.py (IRBW v1: named fp32
@@ -155,6 +162,12 @@ int irb_gdfn_dw_gate(const void* d_x, int dtype, long long ldx, void* d_y, long 
 int irb_pwdw_fused(int gate, const void* d_x, long long ldx, const float* d_stats, const void* d_w1, int nrows, int hp,
                    const float* d_colsum, const float* d_t, const float* d_dw, int dw_ld, void* d_y, long long ldy, int n,
                    int H, int W, int C, void* stream);
+/* X-Restormer overlapping cross-attention (xrestormer_arch.py:190-237) on a channels-last qkv tensor
+ * [n, H, W, 3*heads*dim_head] (q | k | v, head-major): queries = the window x window blocks, keys / values = the
+ * overlap_window-wide zero-padded neighbourhoods, logits += q . rel_width[dj] + q . rel_height[di] with q pre-scaled by
+ * dim_head^-0.5 inside the kernel. d_rel_h / d_rel_w fp32 [2*overlap_window-1][dim_head]. dim_head must be 16. */
+int irb_ocab(const void* d_qkv, int dtype, long long ld, void* d_out, long long ldo, int n, int H, int W, int heads,
+             int dim_head, int window, int overlap_window, const float* d_rel_h, const float* d_rel_w, void* stream);
 /* MDTA Gram over a channels-last qkv tensor (q | k | v): the P pixels are split into nchunks =
  * irb_mdta_nchunks(P, heads, n) chunks and every chunk writes its own slot (no atomics -> bit-reproducible):
  *   d_Gpart   [n][heads][nchunks][c][c]   partial sum_p q k^T

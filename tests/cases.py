@@ -10,6 +10,11 @@ R_CASES = {
     "restormer_cfg2_tile256": lambda: configs.restormer_config("Motion_Deblurring"),
     "restormer_cfg5_tile512": lambda: configs.restormer_config("Real_Denoising"),
 }
+X_CASES = {  # X-Restormer, tools/make_golden_full.py xrestormer
+    "xrestormer_small_withbias": lambda: configs.small_xrestormer_config("WithBias"),
+    "xrestormer_small_biasfree": lambda: configs.small_xrestormer_config("BiasFree"),
+    "xrestormer_full": lambda: configs.xrestormer_config(),
+}
 S_CASES = {
     "swinir_small_color_dn": lambda: configs.small_swinir_config("color_dn"),
     "swinir_small_color_dn_ragged": lambda: configs.small_swinir_config("color_dn"),

@@ -247,3 +247,66 @@ def test_fused_pwdw_model_equals_unfused_within_bf16_rounding(ln):
     check(eng.lib.irb_set_option(eng._h, b"fuse_pwdw", 0))
     assert torch.isfinite(y1).all() and (y1 - y0).abs().max().item() <= 5e-3
     eng.close()
+
+
+# ---------------- X-Restormer ----------------
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", ["xrestormer_small_withbias", "xrestormer_small_biasfree", "xrestormer_full"])
+def test_xrestormer_forward_matches_reference(name, prec, golden_dir):
+    from cases import X_CASES
+    from image_restoration_agent_b200.engine import Engine
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    cfg = X_CASES[name]()
+    eng = Engine("xrestormer", cfg, synth.xrestormer_state_dict(cfg, seed=int(g["seed"])), precision=prec)
+    y = eng(torch.from_numpy(g["x"]).cuda()).cpu().numpy()
+    err = float(np.abs(y - g["y"]).max())
+    mse = float(((y.astype(np.float64) - g["y"]) ** 2).mean())
+    ps = 200.0 if mse == 0 else 10 * math.log10(1.0 / mse)
+    print(f"\n[parity] {name} {prec}: max-abs {err:.2e}, PSNR {ps:.1f} dB")
+    assert np.isfinite(y).all() and err <= (1e-4 if prec == "fp32" else 2e-2)
+    if prec == "bf16":
+        assert ps >= 45.0
+    eng.close()
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_xrestormer_tool_matches_reference(tmp_path, prec, golden_dir):
+    """Tool(input_dir, output_dir) -> output.png: reflect pad to 64, whole image, crop, tensor2img."""
+    import cv2
+    from image_restoration_agent_b200.tool_api import XRestormerB200, clear_engines
+    g = np.load(os.path.join(golden_dir, "xrestormer_pipeline_small.npz"))
+    cfg = configs.small_xrestormer_config("WithBias")
+    sd = synth.xrestormer_state_dict(cfg, seed=int(g["seed"]))
+    i, o = _dirs(tmp_path, g["img"])
+    tool = XRestormerB200("dehazing", state_dict=sd, cfg=cfg, precision=prec)
+    assert tool.tool_name == "xrestormer"
+    tool(i, o, silent=True)
+    got = cv2.imread(str(o / "output.png"), cv2.IMREAD_COLOR)
+    d = _lsb(got, g["out_u8"])
+    assert got.shape == g["out_u8"].shape
+    assert d.max() <= (1 if prec == "fp32" else math.ceil(255 * 2e-2)) and (d <= 1).mean() >= 0.90
+    eng = tool._engine()
+    _, f32 = eng.restore_device(torch.from_numpy(g["img"]).cuda(), None, 0, bgr=True, want_f32=True)
+    assert np.abs(f32.cpu().numpy() - g["out_f32"]).max() <= (1e-4 if prec == "fp32" else 2e-2)
+    clear_engines()
+
+
+def test_ocab_kernel_matches_oracle():
+    """The overlapping cross-attention op alone against oracle/xrestormer_ref.ocab (same weights, fp32)."""
+    from image_restoration_agent_b200 import _lib
+    from oracle import xrestormer_ref
+    torch.manual_seed(0)
+    n, H, W, heads, dh, ws, ows = 2, 16, 24, 2, 16, 8, 12
+    inner = heads * dh
+    qkv = torch.randn(n, 3 * inner, H, W)
+    rel_h, rel_w = torch.randn(2 * ows - 1, dh) * 0.25, torch.randn(2 * ows - 1, dh) * 0.25
+    sd = {"p.qkv.weight": torch.eye(3 * inner).reshape(3 * inner, 3 * inner, 1, 1),
+          "p.project_out.weight": torch.eye(inner).reshape(inner, inner, 1, 1),
+          "p.rel_pos_emb.rel_height": rel_h, "p.rel_pos_emb.rel_width": rel_w}
+    want = xrestormer_ref.ocab(qkv, sd, "p", heads, ws, 0.5, dh).permute(0, 2, 3, 1)
+    x = qkv.permute(0, 2, 3, 1).contiguous().cuda()
+    out = torch.zeros(n, H, W, inner, device="cuda")
+    lib = _lib.load()
+    _lib.check(lib.irb_ocab(x.data_ptr(), _lib.F32, 3 * inner, out.data_ptr(), inner, n, H, W, heads, dh, ws, ows,
+                            rel_h.cuda().data_ptr(), rel_w.cuda().data_ptr(), torch.cuda.current_stream().cuda_stream))
+    assert (out.cpu() - want).abs().max().item() <= 2e-5

@@ -49,3 +49,24 @@ def test_tool_oracle_matches_reference(name, golden_dir):
     assert np.abs(f.numpy() - g["out_f32"]).max() <= 2e-5
     assert np.abs(u8.astype(int) - g["out_u8"].astype(int)).max() <= 1
     assert u8.shape == g["out_u8"].shape and u8.dtype == np.uint8
+
+
+from cases import X_CASES  # noqa: E402
+from oracle import xrestormer_ref  # noqa: E402
+
+
+@pytest.mark.parametrize("name", sorted(X_CASES))
+def test_xrestormer_oracle_matches_reference(name, golden_dir):
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    cfg = X_CASES[name]()
+    sd = synth.xrestormer_state_dict(cfg, seed=int(g["seed"]))
+    y = xrestormer_ref.Model(sd, cfg)(torch.from_numpy(g["x"])).numpy()
+    assert np.abs(y - g["y"]).max() <= 2e-5
+
+
+def test_xrestormer_tool_oracle_matches_reference(golden_dir):
+    g = np.load(os.path.join(golden_dir, "xrestormer_pipeline_small.npz"))
+    cfg = configs.small_xrestormer_config("WithBias")
+    m = xrestormer_ref.Model(synth.xrestormer_state_dict(cfg, seed=int(g["seed"])), cfg)
+    assert np.abs(tiling.xrestormer_restore_image(g["img"], m, return_float=True).numpy() - g["out_f32"]).max() <= 2e-5
+    assert np.abs(tiling.xrestormer_restore_image(g["img"], m).astype(int) - g["out_u8"].astype(int)).max() <= 1

@@ -192,7 +192,7 @@ def xrestormer():
         mg.check(name, y_or, y_ref, tol=2e-5)
         mg.save(name, x=x.numpy(), y=y_ref.numpy(), seed=np.int64(seed))
     # tool level: reflect pad to a multiple of 64, whole image, crop, tensor2img (xrestormer_model.py:56-66, :139-142)
-    name = "xrestormer_tool_small"
+    name = "xrestormer_pipeline_small"
     print(name)
     cfg = configs.small_xrestormer_config("WithBias")
     sd = synth.xrestormer_state_dict(cfg, seed=3)
