@@ -307,6 +307,7 @@ def test_ocab_kernel_matches_oracle():
     x = qkv.permute(0, 2, 3, 1).contiguous().cuda()
     out = torch.zeros(n, H, W, inner, device="cuda")
     lib = _lib.load()
+    rh, rw = rel_h.cuda(), rel_w.cuda()   # keep the device copies alive across the call
     _lib.check(lib.irb_ocab(x.data_ptr(), _lib.F32, 3 * inner, out.data_ptr(), inner, n, H, W, heads, dh, ws, ows,
-                            rel_h.cuda().data_ptr(), rel_w.cuda().data_ptr(), torch.cuda.current_stream().cuda_stream))
+                            rh.data_ptr(), rw.data_ptr(), torch.cuda.current_stream().cuda_stream))
     assert (out.cpu() - want).abs().max().item() <= 2e-5

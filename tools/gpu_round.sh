@@ -30,7 +30,7 @@ for st in $STEPS; do
         timeout 600 python bench.py --workload $wl --warmup 3 --no-cpu --opt $a=$v --top 40 > gpurun_out/${TAG}_opt_${a}${v}_${wl}_$rep.json 2>> gpurun_out/${TAG}_optab.err; echo "opt $a=$v $wl rc=$?"
       done; done; done;;
     pytest)  # pytest:<k-expression>
-      timeout 1200 python -m pytest tests -m gpu -x -q -rP -k "$a" > gpurun_out/${TAG}_pytest_k.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${TAG}_pytest_k.log; tail -15 gpurun_out/${TAG}_pytest_k.log;;
+      timeout 1200 python -m pytest tests -m gpu -x -q -rP -k "$a" > gpurun_out/${TAG}_pytest_$a.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${TAG}_pytest_$a.log; tail -15 gpurun_out/${TAG}_pytest_$a.log;;
     graph_ab)
       for wl in $(echo ${a:-cfg2,swinir_dn} | tr , ' '); do for g in 0 1; do
         timeout 600 python bench.py --workload $wl --warmup 3 --no-cpu --graph $g --top 5 > gpurun_out/${TAG}_graph${g}_$wl.json 2> gpurun_out/${TAG}_graph${g}_$wl.err; echo "graph$g $wl rc=$?"
