@@ -69,6 +69,10 @@ WORKLOADS = {
                  desc="cfg4: chain Restormer Deraining -> uint8 -> SwinIR-M color_dn -> uint8 -> SwinIR-L real_sr x4 on "
                       "512x512, batch 32, whole-image calls (the executor never passes --tile), uint8 hand-off in HBM, "
                       "bf16"),
+    "swinir_dn_256": dict(stages=[("swinir", "color_dn", None, 32, 1, False)], shape=(256, 256, 3), batch=1,
+                          prec="bf16", multi="weak",
+                          desc="SwinIR-M color_dn 256x256 synthetic, whole image (the executor's untiled small-image "
+                               "call, multitask_tools.py:120-133), bf16"),
     "swinir_dn": dict(stages=[("swinir", "color_dn", None, 32, 1, False)], shape=(512, 512, 3), batch=1, prec="bf16",
                       multi="weak", desc="SwinIR-M color_dn 512x512 synthetic, whole image, bf16"),
 }
