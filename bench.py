@@ -69,6 +69,10 @@ WORKLOADS = {
                  desc="cfg4: chain Restormer Deraining -> uint8 -> SwinIR-M color_dn -> uint8 -> SwinIR-L real_sr x4 on "
                       "512x512, batch 32, whole-image calls (the executor never passes --tile), uint8 hand-off in HBM, "
                       "bf16"),
+    "xrestormer_512": dict(stages=[("xrestormer", "dehazing", None, 0, 1, False)], shape=(512, 512, 3), batch=1,
+                           prec="bf16", multi="weak",
+                           desc="X-Restormer (dehazing config) 512x512 synthetic, whole image (the BasicSR tool path: no "
+                                "tile, pad to 64), bf16"),
     "swinir_dn_256": dict(stages=[("swinir", "color_dn", None, 32, 1, False)], shape=(256, 256, 3), batch=1,
                           prec="bf16", multi="weak",
                           desc="SwinIR-M color_dn 256x256 synthetic, whole image (the executor's untiled small-image "
@@ -101,6 +105,9 @@ def stage_model(stage):
     if arch == "restormer":
         cfg = configs.restormer_config(task)
         return arch, cfg, synth.restormer_state_dict(cfg, seed=0)
+    if arch == "xrestormer":
+        cfg = configs.xrestormer_config()
+        return arch, cfg, synth.xrestormer_state_dict(cfg, seed=0)
     cfg = configs.swinir_config(task, scale=scale, large_model=large)
     return arch, cfg, synth.swinir_state_dict(cfg, seed=0)
 
@@ -115,6 +122,8 @@ def executed_px_per_image(stage, h, w):
     if arch == "swinir":
         ws = 7 if "jpeg" in task else 8
         hp, wp = (h // ws + 1) * ws, (w // ws + 1) * ws                      # inference.py:76-78
+    elif arch == "xrestormer":
+        hp, wp = (h + 63) // 64 * 64, (w + 63) // 64 * 64                    # xrestormer_model.py:56-66
     else:
         hp, wp = (h + 7) // 8 * 8, (w + 7) // 8 * 8                          # demo.py:122-126
     if tile is None:
@@ -132,6 +141,8 @@ def model_level(wl, ms_step, images_per_step, step_bytes, peaks):
     for st in wl["stages"]:
         arch, task, tile, ov, scale, large = st
         key = ("restormer", c) if arch == "restormer" else ("swinir", "real_sr_large" if large else task)
+        if arch == "xrestormer" or key not in MODEL_FLOPS_PER_PX:
+            return {"note": "no model-level ceiling: BASELINE.md section 2 has no FLOP count for this model"}
         px = executed_px_per_image(st, hh, ww)
         px_exec += px
         flops += MODEL_FLOPS_PER_PX[key] * px
@@ -222,9 +233,10 @@ def config_dict(name):
 
 
 def oracle_model(stage):
-    from oracle import restormer_ref, swinir_ref
+    from oracle import restormer_ref, swinir_ref, xrestormer_ref
     arch, cfg, sd = stage_model(stage)
-    return (restormer_ref.Model if arch == "restormer" else swinir_ref.Model)(sd, cfg), cfg
+    cls = {"restormer": restormer_ref.Model, "swinir": swinir_ref.Model, "xrestormer": xrestormer_ref.Model}[arch]
+    return cls(sd, cfg), cfg
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -331,6 +343,8 @@ def parity_report(eng, stage, shape, prec):
     if arch == "swinir":
         x = tiling.swinir_pad(x, cfg["window_size"])
     t = min(tile or (256 if arch == "restormer" else 128), x.shape[2], x.shape[3])
+    if arch == "xrestormer":
+        t = 128
     if arch == "swinir" and tile is None:
         t = min(t, 128)                                   # 128^2 tokens at full depth: ~3 s of oracle time
     x = x[..., :t, :t].contiguous()

@@ -44,8 +44,8 @@ for st in $STEPS; do
     ncu)   # ncu:<kernel regex>:<launch-skip>[:workload]
       CMD="python bench.py --workload ${c:-cfg2} --steps 1 --warmup 0 --no-cpu --graph 0"
       timeout 600 $CMD > gpurun_out/plain2.log 2>&1 &&
-      timeout 900 ncu --set full --import-source on --clock-control none -k regex:$a --launch-skip ${b:-0} --launch-count 1 -f -o gpurun_out/${TAG}_ncu_$a $CMD > gpurun_out/ncu_full.log 2>&1
-      ncu -i gpurun_out/${TAG}_ncu_$a.ncu-rep --page details > gpurun_out/${TAG}_ncu_full_$a.txt 2>&1;;
+      timeout 900 ncu --set full --import-source on --clock-control none -k regex:$a --launch-skip ${b:-0} --launch-count 1 -f -o gpurun_out/${TAG}_ncu_${a}_${b:-0} $CMD > gpurun_out/ncu_full.log 2>&1
+      ncu -i gpurun_out/${TAG}_ncu_${a}_${b:-0}.ncu-rep --page details > gpurun_out/${TAG}_ncu_full_${a}_${b:-0}.txt 2>&1;;
     ab)    # ab:<lib a>:<lib b>[:workload]  two builds of the library on one box, interleaved
       for rep in 1 2; do for lib in $a $b; do
         IRB_LIB=$lib timeout 600 python bench.py --workload ${c:-cfg2} --warmup 3 --no-cpu --top 40 > gpurun_out/${TAG}_ab_$(basename $lib .so)_${c:-cfg2}_$rep.json 2>> gpurun_out/${TAG}_ab.err
