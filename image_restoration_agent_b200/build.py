@@ -81,4 +81,11 @@ def _build(force: bool, verbose: bool, LIB: Path, BUILD: Path, extra) -> Path:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, diag="--diag" in sys.argv))
+    # --variant NAME -DFOO=1 ...  builds libirb200_NAME.so with extra defines (same-box A/B of two kernel variants:
+    # tools/gpu_round.sh TAG ab:<lib_a>:<lib_b>:<workload>)
+    if "--variant" in sys.argv:
+        name = sys.argv[sys.argv.index("--variant") + 1]
+        defs = [a for a in sys.argv if a.startswith("-D")]
+        print(_build("--force" in sys.argv, "-v" in sys.argv, PKG / f"libirb200_{name}.so", PKG / f"_build_{name}", defs))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, diag="--diag" in sys.argv))

@@ -16,13 +16,26 @@
 #include "kernels.h"
 #include <stdlib.h>
 
+#ifndef IRB_DW_GATE_TH
+#define IRB_DW_GATE_TH 8
+#endif
+
 namespace irb {
 
-static constexpr int kDwTW = 32, kDwTH = 8;                    // output tile (pixels)
-static constexpr int kDwHW = kDwTW + 2, kDwHH = kDwTH + 2;     // halo'd tile
+static constexpr int kDwTW = 32;                               // output tile width (pixels)
+static constexpr int kDwHW = kDwTW + 2;                        // halo'd tile width
 static constexpr int kDwCh = 64;                               // channels per chunk = one 128-byte row
-static constexpr int kDwStreamBytes = kDwHH * kDwHW * kDwCh * 2;  // 43 520
-static constexpr int kDwStagesGate = 2, kDwStagesPlain = 4;  // 2 x 87 KB / 4 x 43.5 KB of shared memory
+// Output tile height and ring depth. plain: 32x8 tiles, 4 stages of 43.5 KB. gate (two streams per stage): 32x8 tiles,
+// 2 stages of 87 KB. ncu (profiles/r02_s08_ncu_dw_gate.txt) shows 15 % of the gate kernel's stall samples on the
+// TMA-full barrier, so 32x6 tiles with 3 stages of 69.6 KB were tried (-DIRB_DW_GATE_TH=6): 6.49-6.64 ms against
+// 6.34-6.40 ms per 20 launches in a same-box A/B (profiles/r02_s09_ab_*): the extra halo rows (8/6 instead of 10/8 per
+// output row) cost more than the third stage gains. The default stays 8.
+template <int GATE> struct DwGeom {
+    static constexpr int TH = GATE != 0 ? IRB_DW_GATE_TH : 8;
+    static constexpr int HH = TH + 2;
+    static constexpr int kStream = HH * kDwHW * kDwCh * 2;    // bytes of one stream of one stage
+    static constexpr int kStages = GATE != 0 ? (IRB_DW_GATE_TH == 8 ? 2 : 3) : 4;
+};
 static constexpr int kDwConsumerWarps = kDwTW / 2;             // 16
 static constexpr int kDwThreads = (kDwConsumerWarps + 1) * 32; // + producer warp
 
@@ -44,8 +57,10 @@ struct alignas(64) DwParams {
 template <int GATE>  // 0: plain; 1: GELU gate, sigmoid form (ex2 + rcp); 2: GELU gate, tanh form (MUFU.TANH)
 __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_constant__ DwParams p) {
     constexpr int NS = GATE != 0 ? 2 : 1;
+    constexpr int kDwTH = DwGeom<GATE>::TH, kDwHH = DwGeom<GATE>::HH;
+    constexpr int kDwStreamBytes = DwGeom<GATE>::kStream;
     constexpr int stage_bytes = NS * kDwStreamBytes;
-    constexpr int kDwStages = GATE != 0 ? kDwStagesGate : kDwStagesPlain;
+    constexpr int kDwStages = DwGeom<GATE>::kStages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + kDwStages * stage_bytes);
@@ -182,7 +197,9 @@ static int dw_tma_launch(bool gate, const bf16* x, long long ldx, int Ctot, bf16
     DwParams p{};
     uint64_t dims[4] = {uint64_t(Ctot), uint64_t(W), uint64_t(H), uint64_t(Nimg)};
     uint64_t str[3] = {uint64_t(ldx) * 2, uint64_t(ldx) * 2 * W, uint64_t(ldx) * 2 * W * H};
-    uint32_t box[4] = {kDwCh, kDwHW, kDwHH, 1};
+    const int kDwTH = gate ? DwGeom<1>::TH : DwGeom<0>::TH;
+    const int kDwStreamBytes = gate ? DwGeom<1>::kStream : DwGeom<0>::kStream;
+    uint32_t box[4] = {kDwCh, kDwHW, uint32_t(kDwTH + 2), 1};
     IRB_TRY(make_tmap_bf16_sw(&p.tm, x, 4, dims, str, box, 0));
     p.y = y;
     p.ldy = ldy;
@@ -205,11 +222,11 @@ static int dw_tma_launch(bool gate, const bf16* x, long long ldx, int Ctot, bf16
     const int spatial = p.total / p.chunks;
     const int groups = spatial < sms / p.chunks ? spatial : sms / p.chunks;  // CTAs per chunk
     const int grid = groups * p.chunks;
-    const int nst = gate ? kDwStagesGate : kDwStagesPlain;
+    const int nst = gate ? DwGeom<1>::kStages : DwGeom<0>::kStages;
     const size_t smem = size_t(nst) * (gate ? 2 : 1) * kDwStreamBytes + 128 + nst * 32;
-    IRB_SMEM_OPTIN((dw3x3_tma_kernel<2>), 200 * 1024);
-    IRB_SMEM_OPTIN((dw3x3_tma_kernel<1>), 200 * 1024);
-    IRB_SMEM_OPTIN((dw3x3_tma_kernel<0>), 200 * 1024);
+    IRB_SMEM_OPTIN((dw3x3_tma_kernel<2>), 227 * 1024);
+    IRB_SMEM_OPTIN((dw3x3_tma_kernel<1>), 227 * 1024);
+    IRB_SMEM_OPTIN((dw3x3_tma_kernel<0>), 227 * 1024);
     static int gelu_tanh = -1;
     if (gelu_tanh < 0) {
         // measured equal to the sigmoid form here (6.07 vs 6.06 ms on cfg2: this kernel is not SFU-bound), so the
