@@ -329,6 +329,24 @@ def process_image(img_lq: np.ndarray, model: Engine, scale: int, window_size: in
     return out[:, :, 0] if out.shape[2] == 1 else out
 
 
+def process_images(imgs_lq, model: Engine, scale: int, window_size: int, tile=None, tile_overlap=32):
+    """The `/predict_batch` loop of the SwinIR service (model_serving.py:285-306: process_image per uploaded file) on a
+    list of float32 BGR images; the engine stays resident and same-shaped images reuse one workspace (and one CUDA
+    graph when the caller passes graph-enabled engines). Under an initialised torch.distributed group the list is
+    sharded over the ranks (parallel.partition) and rank 0 receives every result."""
+    import torch.distributed as dist
+
+    from . import parallel
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return [process_image(im, model, scale, window_size, tile, tile_overlap) for im in imgs_lq]
+    rank, world = dist.get_rank(), dist.get_world_size()
+    lo, hi = parallel.partition(len(imgs_lq), world)[rank]
+    mine = [process_image(imgs_lq[i], model, scale, window_size, tile, tile_overlap) for i in range(lo, hi)]
+    gathered = [None] * world if rank == 0 else None
+    dist.gather_object(mine, gathered, dst=0)
+    return [o for part in gathered for o in part] if rank == 0 else None
+
+
 class RestormerService:
     """Drop-in for the Flask wrapper's service object (model_serving.py:55-208): load_model + restore_image."""
 

@@ -311,3 +311,33 @@ def test_ocab_kernel_matches_oracle():
     _lib.check(lib.irb_ocab(x.data_ptr(), _lib.F32, 3 * inner, out.data_ptr(), inner, n, H, W, heads, dh, ws, ows,
                             rh.data_ptr(), rw.data_ptr(), torch.cuda.current_stream().cuda_stream))
     assert (out.cpu() - want).abs().max().item() <= 2e-5
+
+
+def test_engine_serialises_concurrent_flask_style_threads():
+    """The reference shares one model object across Flask worker threads with no lock (model_serving.py:39,105-128);
+    Engine serialises them: concurrent calls from 4 threads give exactly the single-threaded results."""
+    import threading
+    from image_restoration_agent_b200.engine import Engine
+    from image_restoration_agent_b200.tool_api import process_images
+    cfg = configs.small_swinir_config("color_dn")
+    eng = Engine("swinir", cfg, synth.swinir_state_dict(cfg, 2), precision="bf16")
+    imgs = [synth.synthetic_image_u8(40 + 8 * k, 48, 3, seed=k) for k in range(4)]
+    want = [eng.restore(im, 16, 8, bgr=True) for im in imgs]
+    got = [None] * 4
+    errs = []
+
+    def work(k):
+        try:
+            for _ in range(5):
+                got[k] = eng.restore(imgs[k], 16, 8, bgr=True)
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    ts = [threading.Thread(target=work, args=(k,)) for k in range(4)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errs, errs
+    assert all(np.array_equal(g, w) for g, w in zip(got, want))
+    batch = process_images([im.astype(np.float32) / 255.0 for im in imgs], eng, 1, 8, tile=16, tile_overlap=8)
+    assert all(np.array_equal(b, w) for b, w in zip(batch, want))   # /predict_batch loop == per-image calls
+    eng.close()
