@@ -60,6 +60,11 @@ WORKLOADS = {
                  multi="batch",
                  desc="cfg3: SwinIR-M classical_sr x4 512x512 -> 2048x2048, batch 64, tile 256 overlap 32 "
                       "(9 tiles per image), bf16"),
+    "cfg3_whole": dict(stages=[("swinir", "classical_sr", None, 32, 4, False)], shape=(512, 512, 3), batch=64,
+                       prec="bf16", multi="batch",
+                       desc="cfg3 without tiling (the executor never passes --tile; SURVEY 8d: 'also report whole-image "
+                            "mode'): SwinIR-M classical_sr x4 512x512 -> 2048x2048, batch 64, whole 520x520 padded image "
+                            "per forward, bf16"),
     "cfg3_1img": dict(stages=[("swinir", "classical_sr", 256, 32, 4, False)], shape=(512, 512, 3), batch=1,
                       prec="bf16", multi="weak",
                       desc="one image of cfg3: SwinIR-M classical_sr x4 512x512 -> 2048x2048, tile 256 overlap 32, bf16"),
