@@ -59,6 +59,7 @@ PROTOTYPES = {
     "irb_dwconv3x3": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "irb_gdfn_dw_gate": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _vp, _vp]),
     "irb_pwdw_fused": (_i, [_i, _vp, _ll, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _vp, _ll, _i, _i, _i, _i, _vp]),
+    "irb_mlp_fused": (_i, [_vp, _ll, _ll, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _f, _vp]),
     "irb_ocab": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "irb_mdta_nchunks": (_i, [_i, _i, _i]),
     "irb_mdta_gram": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _i, _vp, _vp, _vp]),

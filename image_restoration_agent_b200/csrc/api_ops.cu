@@ -247,6 +247,15 @@ int irb_pwdw_fused(int gate, const void* d_x, long long ldx, const float* d_stat
                            nrows, hp, d_colsum, d_t, d_dw, dw_ld, (bf16*)d_y, ldy, n, H, W, C, (cudaStream_t)stream);
 }
 
+int irb_mlp_fused(void* d_x, long long ldx, long long rows, int C, int hid, const float* d_stats_in, const void* d_w1,
+                  int ldw1, const float* d_colsum1, const float* d_b1, const void* d_w2, int ldw2, const float* d_b2,
+                  float* d_stats_out, float eps, void* stream) {
+    IRB_TRY(require_device());
+    return mlp_fused_bf16((bf16*)d_x, ldx, rows, C, hid, reinterpret_cast<const float2*>(d_stats_in), (const bf16*)d_w1,
+                          ldw1, d_colsum1, d_b1, (const bf16*)d_w2, ldw2, d_b2, reinterpret_cast<float2*>(d_stats_out), eps,
+                          (cudaStream_t)stream);
+}
+
 int irb_ocab(const void* d_qkv, int dtype, long long ld, void* d_out, long long ldo, int n, int H, int W, int heads,
              int dim_head, int window, int overlap_window, const float* d_rel_h, const float* d_rel_w, void* stream) {
     IRB_TRY(require_device());

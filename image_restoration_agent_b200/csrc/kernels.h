@@ -53,6 +53,12 @@ int dwconv3x3_bf16_tma(const bf16* x, long long ldx, bf16* y, long long ldy, int
                        const float* wt, cudaStream_t stream);
 int dwconv3x3_gate_bf16_tma(const bf16* x, long long ldx, bf16* y, long long ldy, int Nimg, int H, int W, int hp,
                             const float* wt, cudaStream_t stream);
+// ---- mlp_fused.cu : SwinIR fc1 -> GELU -> fc2 -> + x (norm2 folded, in place) as one kernel ----
+bool mlp_fused_shape_ok(int C, int hid);
+int mlp_fused_bf16(bf16* x, long long ldx, long long P, int C, int hid, const float2* stats_in, const bf16* w1,
+                   int ldw1, const float* cs1, const float* b1, const bf16* w2, int ldw2, const float* b2,
+                   float2* stats_out, float eps, cudaStream_t stream);
+
 // ---- ocab.cu : X-Restormer overlapping cross-attention (xrestormer_arch.py:190-237) ----
 int ocab_attention(const void* qkv, int dt, long long ld, void* out, long long ldo, int Nimg, int H, int W, int heads,
                    int dim_head, int ws, int ows, const float* rel_h, const float* rel_w, cudaStream_t stream);

@@ -1,0 +1,395 @@
+// SwinIR's MLP half-block as ONE kernel, bf16 storage, sm_100a (network_swinir.py:24-30 Mlp.forward with the block's
+// norm2 and residual, :277):
+//
+//     x[p, :] <- x[p, :] + W2 . gelu(W1' . LN(x[p, :]) + b1') + b2        in place, plus (mu, rstd) of the new row
+//
+// The `hidden` tensor (2C = 360 channels, 720 B per token written and read back by the two-GEMM path: 46 % of the two
+// GEMMs' HBM bytes) never leaves the SM. Unlike Restormer's depthwise pairs (pwdw_fused.cu) there is no CUDA-core
+// stencil between the two contractions, only the GELU, so the fusion removes bytes without loading the issue slots.
+//
+// Work item = 128 tokens (one UMMA M); persistent CTAs, one per SM, 11 warps:
+//   warp 8 (TMA)   : x tile [128][C] -> A (K-major, 128B swizzle, 2 buffers); per 64-column group g of the hidden
+//                    layer: W1' rows [64g, 64g+64) -> ring (2), W2 columns [64g, 64g+64) -> ring (2). Weights stream
+//                    from L2 for every tile (276 KB per 128 tokens at C = 180; they do not fit next to the tiles).
+//   warp 9 (MMA)   : D1[g & 1] (TMEM [128 x 64]) = A . W1'_g^T ; D2[tile & 1] (TMEM [128 x Npad]) += A2_g . W2_g^T, issued
+//                    one group behind D1 so that the conversion of group g overlaps the first GEMM of group g + 1
+//   warps 0-7      : convert: D1 -> folded LayerNorm (rstd * acc + (-mu rstd) * colsum + b1') -> tanh-form GELU -> bf16
+//                    -> A2[g & 1] (K-major swizzled UMMA operand in shared memory); warp w: TMEM lane quarter w & 3,
+//                    columns 32 (w >> 2) .. +31.
+//                    epilogue: D2 -> + b2 + residual (read from the A tile that is still in shared memory: the residual
+//                    IS the GEMM input) -> LayerNorm statistics of the new row -> bf16 written IN PLACE into the A tile
+//   warp 10 (store): TMA-stores the A tile back to x (same tensor map as the load), then frees the A buffer
+#include "common.cuh"
+#include "ptx.cuh"
+#include "kernels.h"
+
+namespace irb {
+
+static constexpr int kMfWarps = 8;
+static constexpr int kMfThreads = (kMfWarps + 3) * 32;  // 352
+static constexpr int kMfATile = 128 * 128;               // one 64-channel K chunk of a 128-token tile (16 KB)
+static constexpr int kMfW1Slab = 64 * 128;               // 64 hidden rows x 64 K (8 KB)
+static constexpr int kMfA2 = 128 * 128;                  // 128 tokens x 64 hidden columns (16 KB)
+
+struct alignas(64) MlpParams {
+    CUtensorMap tmX;   // x {C, P, 1}, box {64, 128, 1}: load and in-place store
+    CUtensorMap tmW1;  // W1' {C, hid, 1}, box {64, 64, 1}
+    CUtensorMap tmW2;  // W2 {hid, C, 1}, box {64, NB, 1}
+    const float2* stats_in;  // [P] (mu, rstd) of the rows of x (norm2)
+    float2* stats_out;       // [P] (mu, rstd) of the new rows, or nullptr
+    const float* cs1;        // [hid] colsum of the folded W1'
+    const float* b1;         // [hid] fc1 bias + W1 . ln_bias
+    const float* b2;         // [C]
+    int P, C, hid, KS, klast, NG, NB;  // KS = K chunks of 64 in C; NG = hidden groups of 64; NB = C rounded up to 16
+    int tiles;
+    float eps;
+};
+
+struct MfBars {
+    uint64_t a_full[2], a_empty[2], w1_full[2], w1_empty[2], w2_full[2], w2_empty[2], d1_full[2], d1_empty[2],
+        a2_full[2], a2_empty[2], d2_full[2], d2_empty[2], out_ready[2];
+    uint32_t tmem_slot;
+};
+
+__global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_constant__ MlpParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const int KS = p.KS, NG = p.NG;
+    uint8_t* sA = smem;                                   // 2 x KS x 16 KB
+    uint8_t* sW1 = sA + 2 * KS * kMfATile;                // 2 x KS x 8 KB
+    uint8_t* sA2 = sW1 + 2 * KS * kMfW1Slab;              // 2 x 16 KB
+    uint8_t* sW2 = sA2 + 2 * kMfA2;                       // 2 x NB x 128 B
+    const int w2_bytes = p.NB * 128;
+    uint8_t* sRed = sW2 + 2 * w2_bytes;                   // [128][2] float2 partial LayerNorm sums of the upper column half
+    MfBars* bars = reinterpret_cast<MfBars*>(sRed + 128 * sizeof(float2));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&bars->a_full[i], 1);
+            mbar_init(&bars->a_empty[i], 1);
+            mbar_init(&bars->w1_full[i], 1);
+            mbar_init(&bars->w1_empty[i], 1);
+            mbar_init(&bars->w2_full[i], 1);
+            mbar_init(&bars->w2_empty[i], 1);
+            mbar_init(&bars->d1_full[i], 1);
+            mbar_init(&bars->d1_empty[i], kMfWarps);
+            mbar_init(&bars->a2_full[i], kMfWarps);
+            mbar_init(&bars->a2_empty[i], 1);
+            mbar_init(&bars->d2_full[i], 1);
+            mbar_init(&bars->d2_empty[i], kMfWarps);
+            mbar_init(&bars->out_ready[i], kMfWarps);
+        }
+        fence_mbar_init();
+    }
+    if (warp == kMfWarps + 1) {
+        tmem_alloc(&bars->tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_slot;
+    const uint32_t d2_col0 = 128;  // D1 buffers at columns 0 / 64, D2 buffers at 128 / 128 + 192 (NB <= 192)
+    griddep_wait();
+    griddep_launch();
+
+    if (warp == kMfWarps) {
+        // ================= TMA loader =================
+        if (elect_one()) {
+            tma_prefetch_desc(&p.tmX);
+            tma_prefetch_desc(&p.tmW1);
+            tma_prefetch_desc(&p.tmW2);
+            int it = 0, G = 0;
+            for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+                const int ab = it & 1;
+                mbar_wait(&bars->a_empty[ab], ((it >> 1) & 1) ^ 1);
+                mbar_arrive_expect_tx(&bars->a_full[ab], uint32_t(KS) * kMfATile);
+                for (int ks = 0; ks < KS; ++ks)
+                    tma_load_3d(sA + (ab * KS + ks) * kMfATile, &p.tmX, &bars->a_full[ab], ks * 64, tile * 128, 0);
+                for (int g = 0; g < NG; ++g, ++G) {
+                    const int s = G & 1;
+                    const uint32_t ph = ((G >> 1) & 1) ^ 1;
+                    mbar_wait(&bars->w1_empty[s], ph);
+                    mbar_arrive_expect_tx(&bars->w1_full[s], uint32_t(KS) * kMfW1Slab);
+                    for (int ks = 0; ks < KS; ++ks)
+                        tma_load_3d(sW1 + (s * KS + ks) * kMfW1Slab, &p.tmW1, &bars->w1_full[s], ks * 64, g * 64, 0);
+                    mbar_wait(&bars->w2_empty[s], ph);
+                    mbar_arrive_expect_tx(&bars->w2_full[s], uint32_t(w2_bytes));
+                    tma_load_3d(sW2 + s * w2_bytes, &p.tmW2, &bars->w2_full[s], g * 64, 0, 0);
+                }
+            }
+        }
+    } else if (warp == kMfWarps + 1) {
+        // ================= MMA issuer =================
+        if (elect_one()) {
+            const uint32_t idesc1 = make_idesc_bf16(128, 64, 0, 0);
+            const uint32_t idesc2 = make_idesc_bf16(128, p.NB, 0, 0);
+            const uint32_t a_base = smem_u32(sA), w1_base = smem_u32(sW1), a2_base = smem_u32(sA2), w2_base = smem_u32(sW2);
+            int it = 0, G = 0;
+            auto mma2 = [&](int Gp, int gp, uint32_t d2) {  // D2 += A2[Gp & 1] . W2[Gp & 1]^T  (K = 64)
+                const int s = Gp & 1;
+                const uint32_t ph = (Gp >> 1) & 1;
+                mbar_wait(&bars->a2_full[s], ph);
+                mbar_wait(&bars->w2_full[s], ph);
+                tc_fence_after();
+                const uint64_t ad = make_sdesc_sw128(a2_base + s * kMfA2, 16, 1024);
+                const uint64_t bd = make_sdesc_sw128(w2_base + s * w2_bytes, 16, 1024);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16(d2, ad + uint64_t(k * 2), bd + uint64_t(k * 2), idesc2, (gp | k) != 0 ? 1u : 0u);
+                umma_commit(&bars->a2_empty[s]);
+                umma_commit(&bars->w2_empty[s]);
+            };
+            for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+                const int ab = it & 1;
+                const uint32_t d2 = tmem_base + d2_col0 + ab * 192;
+                mbar_wait(&bars->a_full[ab], (it >> 1) & 1);
+                mbar_wait(&bars->d2_empty[ab], ((it >> 1) & 1) ^ 1);
+                tc_fence_after();
+                for (int g = 0; g < NG; ++g, ++G) {
+                    const int s = G & 1;
+                    const uint32_t ph = (G >> 1) & 1;
+                    mbar_wait(&bars->w1_full[s], ph);
+                    mbar_wait(&bars->d1_empty[s], ph ^ 1);
+                    tc_fence_after();
+                    const uint32_t d1 = tmem_base + s * 64;
+                    for (int ks = 0; ks < KS; ++ks) {
+                        const int nk = ks == KS - 1 ? p.klast : 4;
+                        const uint64_t ad = make_sdesc_sw128(a_base + (ab * KS + ks) * kMfATile, 16, 1024);
+                        const uint64_t bd = make_sdesc_sw128(w1_base + (s * KS + ks) * kMfW1Slab, 16, 1024);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (k < nk) umma_bf16(d1, ad + uint64_t(k * 2), bd + uint64_t(k * 2), idesc1, (ks | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&bars->w1_empty[s]);
+                    umma_commit(&bars->d1_full[s]);
+                    if (g > 0) mma2(G - 1, g - 1, d2);
+                }
+                mma2(G - 1, NG - 1, d2);
+                umma_commit(&bars->d2_full[ab]);
+            }
+        }
+    } else if (warp == kMfWarps + 2) {
+        // ================= store warp: the finished tile goes back to x, then the A buffer is free =================
+        if (elect_one()) {
+            int it = 0;
+            for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+                const int ab = it & 1;
+                mbar_wait(&bars->out_ready[ab], (it >> 1) & 1);
+                for (int ks = 0; ks < KS; ++ks)
+                    tma_store_3d(&p.tmX, sA + (ab * KS + ks) * kMfATile, ks * 64, tile * 128, 0);
+                bulk_commit();
+                bulk_wait_read0();  // shared memory has been read: the loader may refill this buffer
+                mbar_arrive(&bars->a_empty[ab]);
+            }
+            bulk_wait0();  // all stores have landed before the CTA exits
+        }
+    } else {
+        // ================= warps 0..7: GELU conversion of every hidden group, then the tile's epilogue =================
+        const int q = warp & 3;    // TMEM lane quarter
+        const int ch = warp >> 2;  // column half: conversion columns 32 ch .. +31 of a group; epilogue columns NB/2 ch ..
+        const int r = q * 32 + lane;           // row of the tile
+        const uint32_t rx = uint32_t(r & 7);   // swizzle term of this row
+        const uint32_t lane_t = uint32_t(q * 32) << 16;
+        float2* red = reinterpret_cast<float2*>(sRed);
+        int it = 0, G = 0;
+        for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+            const int ab = it & 1;
+            const long long grow = (long long)tile * 128 + r;
+            const bool valid = grow < p.P;
+            float2 st = make_float2(0.f, 1.f);
+            if (valid) st = __ldg(p.stats_in + grow);
+            const f32x2 a2v = splat2(st.y), b2v = splat2(-st.x * st.y);
+            for (int g = 0; g < NG; ++g, ++G) {
+                const int s = G & 1;
+                const uint32_t ph = (G >> 1) & 1;
+                const int col0 = g * 64 + ch * 32;  // first hidden column of this thread's 32
+                mbar_wait(&bars->d1_full[s], ph);
+                tc_fence_after();
+                uint32_t acc[32];
+                tmem_ld32_nowait(tmem_base + s * 64 + ch * 32 + lane_t, acc);
+                mbar_wait(&bars->a2_empty[s], ph ^ 1);  // the second GEMM of group G - 2 has read this A2 buffer
+                tmem_ld_wait();
+                tc_fence_before();
+                const uint32_t row = smem_u32(sA2) + s * kMfA2 + r * 128;
+#pragma unroll
+                for (int c8 = 0; c8 < 4; ++c8) {
+                    uint32_t pk[4];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int col = col0 + c8 * 8 + h * 4;
+                        float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f), t4 = c4;
+                        if (col < p.hid) {  // hid % 4 == 0
+                            c4 = __ldg(reinterpret_cast<const float4*>(p.cs1 + col));
+                            t4 = __ldg(reinterpret_cast<const float4*>(p.b1 + col));
+                        }
+                        f32x2 x0 = pack2(__uint_as_float(acc[c8 * 8 + h * 4 + 0]), __uint_as_float(acc[c8 * 8 + h * 4 + 1]));
+                        f32x2 x1 = pack2(__uint_as_float(acc[c8 * 8 + h * 4 + 2]), __uint_as_float(acc[c8 * 8 + h * 4 + 3]));
+                        x0 = fma2(x0, a2v, fma2(b2v, pack2(c4.x, c4.y), pack2(t4.x, t4.y)));
+                        x1 = fma2(x1, a2v, fma2(b2v, pack2(c4.z, c4.w), pack2(t4.z, t4.w)));
+                        pk[h * 2 + 0] = f32x2_to_bf16x2(gelu2_tanh(x0));
+                        pk[h * 2 + 1] = f32x2_to_bf16x2(gelu2_tanh(x1));
+                    }
+                    sts_v4(row + ((uint32_t(ch * 4 + c8) ^ rx) << 4), pk[0], pk[1], pk[2], pk[3]);
+                }
+                fence_proxy_async();  // the UMMA (async proxy) reads what this thread just wrote
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(&bars->d1_empty[s]);
+                    mbar_arrive(&bars->a2_full[s]);
+                }
+            }
+            // ---- epilogue: columns [ch * NB/2, (ch + 1) * NB/2) of this row ----
+            mbar_wait(&bars->d2_full[ab], (it >> 1) & 1);
+            tc_fence_after();
+            const int half = p.NB >> 1;            // multiple of 8 (NB % 16 == 0)
+            const int ecol0 = ch * half;
+            const uint32_t d2 = tmem_base + d2_col0 + ab * 192 + lane_t;
+            const uint32_t a_tile = smem_u32(sA) + ab * KS * kMfATile;
+            // shift of the LayerNorm sums: the OLD row's mean (both column halves of a row must use the same value, and
+            // x[row, 0] itself may already have been overwritten in place by the other half's thread)
+            const float shift = st.x;
+            const f32x2 nshift = splat2(-shift);
+            f32x2 s1 = pack2(0.f, 0.f), s2 = s1;
+            for (int c8 = 0; c8 < half / 8; ++c8) {
+                const int col = ecol0 + c8 * 8;
+                float v[8];
+                {
+                    uint32_t a8[8];
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                 : "=r"(a8[0]), "=r"(a8[1]), "=r"(a8[2]), "=r"(a8[3]), "=r"(a8[4]), "=r"(a8[5]), "=r"(a8[6]),
+                                   "=r"(a8[7])
+                                 : "r"(d2 + col)
+                                 : "memory");
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(a8[i]);
+                }
+                // residual chunk: K chunk col / 64 of the A tile, 16-byte chunk (col % 64) / 8 of the row
+                const uint32_t addr = a_tile + (col >> 6) * kMfATile + r * 128 + ((uint32_t((col & 63) >> 3) ^ rx) << 4);
+                const uint4 res = lds_v4(addr);
+                float4 bb0 = make_float4(0.f, 0.f, 0.f, 0.f), bb1 = bb0;
+                if (col < p.C) {  // C % 4 == 0
+                    bb0 = __ldg(reinterpret_cast<const float4*>(p.b2 + col));
+                    if (col + 4 < p.C) bb1 = __ldg(reinterpret_cast<const float4*>(p.b2 + col + 4));
+                }
+                const f32x2 y0 = add2(add2(pack2(v[0], v[1]), pack2(bb0.x, bb0.y)), bf16x2_to_f32x2(res.x));
+                const f32x2 y1 = add2(add2(pack2(v[2], v[3]), pack2(bb0.z, bb0.w)), bf16x2_to_f32x2(res.y));
+                const f32x2 y2 = add2(add2(pack2(v[4], v[5]), pack2(bb1.x, bb1.y)), bf16x2_to_f32x2(res.z));
+                const f32x2 y3 = add2(add2(pack2(v[6], v[7]), pack2(bb1.z, bb1.w)), bf16x2_to_f32x2(res.w));
+                if (col + 8 <= p.C) {
+                    const f32x2 d0 = add2(y0, nshift), d1 = add2(y1, nshift), d2v = add2(y2, nshift), d3 = add2(y3, nshift);
+                    s1 = add2(s1, add2(add2(d0, d1), add2(d2v, d3)));
+                    s2 = fma2(d0, d0, s2);
+                    s2 = fma2(d1, d1, s2);
+                    s2 = fma2(d2v, d2v, s2);
+                    s2 = fma2(d3, d3, s2);
+                } else if (col < p.C) {  // the ragged last chunk (C = 180: columns 176..179)
+                    float yy[8];
+                    unpack2(y0, yy[0], yy[1]);
+                    unpack2(y1, yy[2], yy[3]);
+                    unpack2(y2, yy[4], yy[5]);
+                    unpack2(y3, yy[6], yy[7]);
+                    float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        if (col + i < p.C) {
+                            const float d = yy[i] - shift;
+                            t1 += d;
+                            t2 = fmaf(d, d, t2);
+                        }
+                    s1 = add2(s1, pack2(t1, 0.f));
+                    s2 = add2(s2, pack2(t2, 0.f));
+                }
+                sts_v4(addr, f32x2_to_bf16x2(y0), f32x2_to_bf16x2(y1), f32x2_to_bf16x2(y2), f32x2_to_bf16x2(y3));
+            }
+            tc_fence_before();
+            fence_proxy_async();  // the TMA store (async proxy) reads the tile
+            // LayerNorm statistics of the new row: the two column halves meet through shared memory
+            float a0, a1, q0, q1;
+            unpack2(s1, a0, a1);
+            unpack2(s2, q0, q1);
+            if (ch == 1) red[r] = make_float2(a0 + a1, q0 + q1);
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (ch == 0 && valid && p.stats_out != nullptr) {
+                const float2 o = red[r];
+                const float invn = 1.0f / float(p.C);
+                const float m = (a0 + a1 + o.x) * invn;
+                const float var = fmaxf((q0 + q1 + o.y) * invn - m * m, 0.f);
+                p.stats_out[grow] = make_float2(shift + m, rsqrtf(var + p.eps));
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");  // red[] is free again; every warp's part of the tile is written
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&bars->d2_empty[ab]);
+                mbar_arrive(&bars->out_ready[ab]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kMfWarps + 1) tmem_dealloc(tmem_base, 512);
+}
+
+bool mlp_fused_shape_ok(int C, int hid) {
+    // K = C in <= 3 chunks of 64 and two D2 buffers of <= 192 TMEM columns next to the two D1 buffers
+    return C >= 16 && C <= 192 && C % 4 == 0 && hid % 4 == 0 && hid >= 64 && hid <= 1024;
+}
+
+// x [P][ldx] bf16 (in place); w1 bf16 [hid][ldw1] = fc1 with norm2's gain folded in; w2 bf16 [C][ldw2]
+int mlp_fused_bf16(bf16* x, long long ldx, long long P, int C, int hid, const float2* stats_in, const bf16* w1,
+                   int ldw1, const float* cs1, const float* b1, const bf16* w2, int ldw2, const float* b2,
+                   float2* stats_out, float eps, cudaStream_t stream) {
+    IRB_REQUIRE(mlp_fused_shape_ok(C, hid), "mlp_fused: unsupported shape");
+    IRB_REQUIRE(ldx % 8 == 0 && ldw1 % 8 == 0 && ldw2 % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
+                "mlp_fused: rows must be 16-byte aligned");
+    IRB_REQUIRE(stats_in && cs1 && b1 && b2 && P > 0 && P < (1ll << 31), "mlp_fused: missing operand");
+    MlpParams p{};
+    p.P = int(P);
+    p.C = C;
+    p.hid = hid;
+    p.KS = ceil_div(C, 64);
+    p.klast = ceil_div(C - (p.KS - 1) * 64, 16);
+    p.NG = ceil_div(hid, 64);
+    p.NB = (C + 15) / 16 * 16;
+    p.tiles = int(ceil_div_ll(P, 128));
+    p.stats_in = stats_in;
+    p.stats_out = stats_out;
+    p.cs1 = cs1;
+    p.b1 = b1;
+    p.b2 = b2;
+    p.eps = eps;
+    {
+        uint64_t dims[3] = {uint64_t(C), uint64_t(P), 1};
+        uint64_t str[2] = {uint64_t(ldx) * 2, uint64_t(ldx) * 2 * uint64_t(P)};
+        uint32_t box[3] = {64, 128, 1};
+        IRB_TRY(make_tmap_bf16(&p.tmX, x, 3, dims, str, box));
+    }
+    {
+        uint64_t dims[3] = {uint64_t(C), uint64_t(hid), 1};
+        uint64_t str[2] = {uint64_t(ldw1) * 2, uint64_t(ldw1) * 2 * uint64_t(hid)};
+        uint32_t box[3] = {64, 64, 1};
+        IRB_TRY(make_tmap_bf16(&p.tmW1, w1, 3, dims, str, box));
+    }
+    {
+        uint64_t dims[3] = {uint64_t(hid), uint64_t(C), 1};
+        uint64_t str[2] = {uint64_t(ldw2) * 2, uint64_t(ldw2) * 2 * uint64_t(C)};
+        uint32_t box[3] = {64, uint32_t(p.NB), 1};
+        IRB_TRY(make_tmap_bf16(&p.tmW2, w2, 3, dims, str, box));
+    }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int grid = p.tiles < sms ? p.tiles : sms;
+    const size_t smem = 1024 + size_t(2) * p.KS * kMfATile + size_t(2) * p.KS * kMfW1Slab + 2 * kMfA2 +
+                        size_t(2) * p.NB * 128 + 128 * sizeof(float2) + sizeof(MfBars) + 64;
+    IRB_REQUIRE(smem <= 227 * 1024, "mlp_fused: shared memory budget exceeded");
+    IRB_SMEM_OPTIN((mlp_fused_kernel), 227 * 1024);
+    IRB_CHECK_CUDA(launch_pdl(mlp_fused_kernel, dim3(grid), dim3(kMfThreads), smem, stream, p));
+    // algorithmic work: x read once and written once, weights once; both contractions
+    prof_mark("mlp_fused", C, hid, 4.0 * double(P) * C * hid, double(P) * C * 2 * 2 + 2.0 * C * hid * 2 + double(P) * 16,
+              stream);
+    return 0;
+}
+
+}  // namespace irb

@@ -50,6 +50,7 @@ struct Model {
     // 1: tile % window_size == 0 is required like the SwinIR script (inference.py:302); 0: the SwinIR service path
     // (model_serving.py:146-166 has no such assert: the model reflect-pads ragged tiles itself). Restormer always checks.
     int strict_tile = 1;
+    int fuse_mlp = 1;   // SwinIR: fc1 -> GELU -> fc2 -> + x as one kernel (mlp_fused.cu) where the shape allows
     int fuse_pwdw = 0;  // Restormer: 1x1 -> depthwise pairs as one kernel (pwdw_fused.cu); opt-in, see DESIGN.md section 8
     std::vector<void*> dev_allocs;
     virtual ~Model();

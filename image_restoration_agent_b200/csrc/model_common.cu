@@ -336,6 +336,10 @@ int irb_set_option(irb_handle* h, const char* key, long long value) {
         h->model->tile_batch = value;
         return 0;
     }
+    if (strcmp(key, "fuse_mlp") == 0) {
+        h->model->fuse_mlp = value != 0;
+        return 0;
+    }
     if (strcmp(key, "fuse_pwdw") == 0) {
         h->model->fuse_pwdw = value != 0;
         return 0;

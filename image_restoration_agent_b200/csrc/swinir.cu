@@ -413,6 +413,15 @@ int SwinIR::stl(const STLW& L, const void* xin, void* xout, int n, int H, int W,
         }
         IRB_TRY(gemm(w.attn, ldC, P, L.proj, e, s));
     }
+    if (dt == DT_BF16 && fuse_mlp && mlp_fused_shape_ok(C, hid)) {
+        // fc1 -> GELU -> fc2 -> + x in one kernel (mlp_fused.cu): the hidden tensor stays on the SM; the kernel also
+        // writes the next block's norm1 statistics (it reads norm2's from w.stats and overwrites them row by row)
+        if (!w.stats_valid) IRB_TRY(row_stats(xout, dt, ldC, w.stats, P, C, 1e-5f, s));
+        IRB_TRY(mlp_fused_bf16((bf16*)xout, ldC, P, C, hid, w.stats, (const bf16*)L.fc1.w, L.fc1.kpad, L.fc1.cs, L.fc1.b,
+                               (const bf16*)L.fc2.w, L.fc2.kpad, L.fc2.b, w.stats, 1e-5f, s));
+        w.stats_valid = true;
+        return 0;
+    }
     if (dt == DT_BF16) {  // norm2 folded into fc1
         if (!w.stats_valid) IRB_TRY(row_stats(xout, dt, ldC, w.stats, P, C, 1e-5f, s));
         Epi e = make_epi(w.hidden, hid, dt);

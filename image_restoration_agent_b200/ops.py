@@ -169,3 +169,15 @@ def pwdw_fused(x, stats, w1, dww, colsum=None, t=None, gate=False):
                                      _ptr(colsum), _ptr(t), dwp.data_ptr(), rows, y.data_ptr(), y.shape[3],
                                      n, H, W, C, torch.cuda.current_stream(x.device).cuda_stream))
     return y
+
+
+def mlp_fused(x, stats, w1, colsum1, b1, w2, b2, C, eps=1e-5):
+    """In place on x bf16 [rows, ldx] (C valid columns): x += W2 . gelu(W1' . LN(x) + b1') + b2; -> (x, stats_out)."""
+    rows = x.shape[0]
+    hid = w1.shape[0]
+    st_out = torch.full((rows, 2), float("nan"), device=x.device, dtype=torch.float32)
+    check(_lib.load().irb_mlp_fused(x.data_ptr(), x.stride(0), rows, C, hid, stats.data_ptr(), w1.data_ptr(),
+                                    w1.stride(0), colsum1.data_ptr(), b1.data_ptr(), w2.data_ptr(), w2.stride(0),
+                                    b2.data_ptr(), st_out.data_ptr(), eps,
+                                    torch.cuda.current_stream(x.device).cuda_stream))
+    return x, st_out

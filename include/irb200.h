@@ -92,6 +92,7 @@ void irb_destroy(irb_handle* h);
 /* options: "tile_batch" (max tiles per forward batch inside irb_restore_image; 0 = automatic);
  *          "fuse_pwdw" (default 0; 1: Restormer blocks with C <= 128 run each 1x1 -> depthwise pair as one kernel,
  *          irb_pwdw_fused — parity-equal but measured slower than the separate kernels);
+ *          "fuse_mlp" (SwinIR: fc1 -> GELU -> fc2 -> + x as one kernel, irb_mlp_fused, where the shape allows);
  *          "strict_tile" (default 1: SwinIR tiles must be a multiple of window_size like inference.py:302; 0: the
  *          Flask service's process_image, model_serving.py:146-166, which has no such assert) */
 int irb_set_option(irb_handle* h, const char* key, long long value);
@@ -162,6 +163,14 @@ int irb_gdfn_dw_gate(const void* d_x, int dtype, long long ldx, void* d_y, long 
 int irb_pwdw_fused(int gate, const void* d_x, long long ldx, const float* d_stats, const void* d_w1, int nrows, int hp,
                    const float* d_colsum, const float* d_t, const float* d_dw, int dw_ld, void* d_y, long long ldy, int n,
                    int H, int W, int C, void* stream);
+/* SwinIR's MLP half-block in place, bf16 (network_swinir.py:24-30 with the block's norm2 and residual, :277):
+ *   x[p,:] <- x[p,:] + W2 . gelu(W1' . LN(x[p,:]) + b1') + b2, and (mu, rstd) of the new rows into d_stats_out.
+ * d_x bf16 [rows][ldx] (C valid columns, C <= 192, C % 4 == 0); d_stats_in fp32 [rows][2] = (mu, rstd) of the rows of
+ * x; d_w1 bf16 [hid][ldw1] = fc1 with norm2's gain folded in, d_colsum1 / d_b1 fp32 [hid] (row sums of the rounded
+ * folded weights / fc1 bias + W1 . ln_bias); d_w2 bf16 [C][ldw2], d_b2 fp32 [C]. The hidden tensor stays on the SM. */
+int irb_mlp_fused(void* d_x, long long ldx, long long rows, int C, int hid, const float* d_stats_in, const void* d_w1,
+                  int ldw1, const float* d_colsum1, const float* d_b1, const void* d_w2, int ldw2, const float* d_b2,
+                  float* d_stats_out, float eps, void* stream);
 /* X-Restormer overlapping cross-attention (xrestormer_arch.py:190-237) on a channels-last qkv tensor
  * [n, H, W, 3*heads*dim_head] (q | k | v, head-major): queries = the window x window blocks, keys / values = the
  * overlap_window-wide zero-padded neighbourhoods, logits += q . rel_width[dj] + q . rel_height[di] with q pre-scaled by

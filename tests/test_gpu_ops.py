@@ -259,3 +259,40 @@ def test_pwdw_fused_matches_separate_ops(gate, with_bias, n, H, W, C, rows):
     ref = F.gelu(dw[..., :rows // 2]) * dw[..., rows // 2:] if gate else dw
     assert y.shape == ref.shape
     close(y, ref, 1.6e-2)
+
+
+@pytest.mark.parametrize("rows,C,hid", [(1000, 180, 360), (128, 180, 360), (129, 64, 128), (4097, 96, 192), (300, 48, 96)])
+def test_mlp_fused_matches_torch(rows, C, hid):
+    """fc1 (norm2 folded) -> GELU -> fc2 -> + x in place (network_swinir.py:24-30, :277) as one kernel vs fp32 torch on the
+    same bf16-rounded operands, and the LayerNorm statistics of the new rows."""
+    from image_restoration_agent_b200 import ops
+    ld = (C + 15) // 16 * 16
+    xb = torch.zeros(rows, ld, device="cuda", dtype=torch.bfloat16)
+    xb[:, :C] = (torch.randn(rows, C, device="cuda") * 1.2 + 0.2).bfloat16()
+    x0 = xb[:, :C].float()
+    mu = x0.mean(-1)
+    rstd = 1.0 / torch.sqrt(x0.var(-1, unbiased=False) + 1e-5)
+    stats = torch.stack([mu, rstd], -1).contiguous()
+    gain = torch.randn(C, device="cuda") * 0.1 + 1.0
+    ln_b = torch.randn(C, device="cuda") * 0.05
+    W1 = torch.randn(hid, C, device="cuda") / C ** 0.5
+    b1 = torch.randn(hid, device="cuda") * 0.1
+    W2 = torch.randn(C, hid, device="cuda") / hid ** 0.5
+    b2 = torch.randn(C, device="cuda") * 0.1
+    k1 = (C + 7) // 8 * 8
+    w1 = torch.zeros(hid, k1, device="cuda", dtype=torch.bfloat16)
+    w1[:, :C] = (W1 * gain).bfloat16()
+    cs1 = w1.float().sum(1).contiguous()
+    b1f = (b1 + W1 @ ln_b).contiguous()
+    k2 = (hid + 7) // 8 * 8
+    w2 = torch.zeros(C, k2, device="cuda", dtype=torch.bfloat16)
+    w2[:, :hid] = W2.bfloat16()
+    # reference: the two-GEMM path's arithmetic (hidden rounded to bf16 between the GEMMs, tanh-form GELU)
+    h = rstd[:, None] * (x0 @ w1[:, :C].float().t() - mu[:, None] * cs1) + b1f
+    h = F.gelu(h, approximate="tanh").bfloat16().float()
+    ref = x0 + h @ w2[:, :hid].float().t() + b2
+    y, st = ops.mlp_fused(xb, stats, w1, cs1, b1f, w2, b2.contiguous(), C)
+    close(y[:, :C], ref, 1.6e-2)
+    assert (st[:, 0] - ref.mean(1)).abs().max().item() <= 2e-2 * max(ref.abs().max().item(), 1.0)
+    r2 = 1.0 / torch.sqrt(ref.var(1, unbiased=False) + 1e-5)
+    assert ((st[:, 1] - r2).abs() / r2).max().item() <= 3e-2

@@ -341,3 +341,19 @@ def test_engine_serialises_concurrent_flask_style_threads():
     batch = process_images([im.astype(np.float32) / 255.0 for im in imgs], eng, 1, 8, tile=16, tile_overlap=8)
     assert all(np.array_equal(b, w) for b, w in zip(batch, want))   # /predict_batch loop == per-image calls
     eng.close()
+
+
+def test_fused_mlp_model_equals_two_gemm_path_within_bf16_rounding():
+    """SwinIR with the fused MLP kernel (option fuse_mlp) vs the two-GEMM path: same output up to bf16 rounding."""
+    from image_restoration_agent_b200._lib import check
+    from image_restoration_agent_b200.engine import Engine
+    cfg = configs.swinir_config("color_dn")
+    eng = Engine("swinir", cfg, synth.swinir_state_dict(cfg, 0), precision="bf16")
+    x = torch.from_numpy(synth.synthetic_image_u8(72, 96, 3, seed=2)).cuda().float().div(255).permute(2, 0, 1)[None]
+    check(eng.lib.irb_set_option(eng._h, b"fuse_mlp", 1))
+    y1 = eng(x.contiguous())
+    check(eng.lib.irb_set_option(eng._h, b"fuse_mlp", 0))
+    y0 = eng(x.contiguous())
+    check(eng.lib.irb_set_option(eng._h, b"fuse_mlp", 1))
+    assert torch.isfinite(y1).all() and (y1 - y0).abs().max().item() <= 1e-2
+    eng.close()
