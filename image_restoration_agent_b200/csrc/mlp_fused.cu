@@ -7,26 +7,27 @@
 // GEMMs' HBM bytes) never leaves the SM. Unlike Restormer's depthwise pairs (pwdw_fused.cu) there is no CUDA-core
 // stencil between the two contractions, only the GELU, so the fusion removes bytes without loading the issue slots.
 //
-// Work item = 128 tokens (one UMMA M); persistent CTAs, one per SM, 11 warps:
-//   warp 8 (TMA)   : x tile [128][C] -> A (K-major, 128B swizzle, 2 buffers); per 64-column group g of the hidden
+// Work item = 128 tokens (one UMMA M); persistent CTAs, one per SM, 19 warps:
+//   warp 16 (TMA)  : x tile [128][C] -> A (K-major, 128B swizzle, 2 buffers); per 64-column group g of the hidden
 //                    layer: W1' rows [64g, 64g+64) -> ring (2), W2 columns [64g, 64g+64) -> ring (2). Weights stream
 //                    from L2 for every tile (276 KB per 128 tokens at C = 180; they do not fit next to the tiles).
-//   warp 9 (MMA)   : D1[g & 1] (TMEM [128 x 64]) = A . W1'_g^T ; D2[tile & 1] (TMEM [128 x Npad]) += A2_g . W2_g^T, issued
+//   warp 17 (MMA)  : D1[g & 1] (TMEM [128 x 64]) = A . W1'_g^T ; D2[tile & 1] (TMEM [128 x Npad]) += A2_g . W2_g^T, issued
 //                    one group behind D1 so that the conversion of group g overlaps the first GEMM of group g + 1
-//   warps 0-7      : convert: D1 -> folded LayerNorm (rstd * acc + (-mu rstd) * colsum + b1') -> tanh-form GELU -> bf16
+//   warps 0-15     : convert: D1 -> folded LayerNorm (rstd * acc + (-mu rstd) * colsum + b1') -> tanh-form GELU -> bf16
 //                    -> A2[g & 1] (K-major swizzled UMMA operand in shared memory); warp w: TMEM lane quarter w & 3,
-//                    columns 32 (w >> 2) .. +31.
+//                    columns 16 (w >> 2) .. +15 (8 warps left the SM at IPC 1.5: the GELU chains need more warps in flight).
 //                    epilogue: D2 -> + b2 + residual (read from the A tile that is still in shared memory: the residual
 //                    IS the GEMM input) -> LayerNorm statistics of the new row -> bf16 written IN PLACE into the A tile
-//   warp 10 (store): TMA-stores the A tile back to x (same tensor map as the load), then frees the A buffer
+//   warp 18 (store): TMA-stores the A tile back to x (same tensor map as the load), then frees the A buffer
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
 
 namespace irb {
 
-static constexpr int kMfWarps = 8;
-static constexpr int kMfThreads = (kMfWarps + 3) * 32;  // 352
+static constexpr int kMfWarps = 16;                      // conversion / epilogue warps: 4 TMEM lane quarters x 4 column groups
+static constexpr int kMfCG = kMfWarps / 4;               // column groups
+static constexpr int kMfThreads = (kMfWarps + 3) * 32;  // 608
 static constexpr int kMfATile = 128 * 128;               // one 64-channel K chunk of a 128-token tile (16 KB)
 static constexpr int kMfW1Slab = 64 * 128;               // 64 hidden rows x 64 K (8 KB)
 static constexpr int kMfA2 = 128 * 128;                  // 128 tokens x 64 hidden columns (16 KB)
@@ -60,8 +61,8 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
     uint8_t* sA2 = sW1 + 2 * KS * kMfW1Slab;              // 2 x 16 KB
     uint8_t* sW2 = sA2 + 2 * kMfA2;                       // 2 x NB x 128 B
     const int w2_bytes = p.NB * 128;
-    uint8_t* sRed = sW2 + 2 * w2_bytes;                   // [128][2] float2 partial LayerNorm sums of the upper column half
-    MfBars* bars = reinterpret_cast<MfBars*>(sRed + 128 * sizeof(float2));
+    uint8_t* sRed = sA2;  // [kMfCG - 1][128] float2 partial LayerNorm sums; aliases A2, which is idle during an epilogue
+    MfBars* bars = reinterpret_cast<MfBars*>(sW2 + 2 * w2_bytes);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
@@ -187,7 +188,8 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
     } else {
         // ================= warps 0..7: GELU conversion of every hidden group, then the tile's epilogue =================
         const int q = warp & 3;    // TMEM lane quarter
-        const int ch = warp >> 2;  // column half: conversion columns 32 ch .. +31 of a group; epilogue columns NB/2 ch ..
+        const int ch = warp >> 2;  // column group: conversion columns CW ch .. +CW-1 of a hidden group; epilogue columns NB/kMfCG ch ..
+        constexpr int CW = 64 / kMfCG;         // 16 conversion columns per thread and group
         const int r = q * 32 + lane;           // row of the tile
         const uint32_t rx = uint32_t(r & 7);   // swizzle term of this row
         const uint32_t lane_t = uint32_t(q * 32) << 16;
@@ -203,46 +205,49 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
             for (int g = 0; g < NG; ++g, ++G) {
                 const int s = G & 1;
                 const uint32_t ph = (G >> 1) & 1;
-                const int col0 = g * 64 + ch * 32;  // first hidden column of this thread's 32
+                const int col0 = g * 64 + ch * CW;  // first hidden column of this thread's CW
+                // column vectors first: they do not depend on the accumulator, so their latency hides behind the wait
+                f32x2 tbv[CW / 2];
+#pragma unroll
+                for (int i = 0; i < CW / 4; ++i) {
+                    const int col = col0 + i * 4;
+                    float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f), t4 = c4;
+                    if (col < p.hid) {  // hid % 4 == 0
+                        c4 = __ldg(reinterpret_cast<const float4*>(p.cs1 + col));
+                        t4 = __ldg(reinterpret_cast<const float4*>(p.b1 + col));
+                    }
+                    tbv[2 * i] = fma2(b2v, pack2(c4.x, c4.y), pack2(t4.x, t4.y));      // (-mu rstd) * colsum + b1'
+                    tbv[2 * i + 1] = fma2(b2v, pack2(c4.z, c4.w), pack2(t4.z, t4.w));
+                }
                 mbar_wait(&bars->d1_full[s], ph);
                 tc_fence_after();
-                uint32_t acc[32];
-                tmem_ld32_nowait(tmem_base + s * 64 + ch * 32 + lane_t, acc);
+                uint32_t acc[CW];
+                tmem_ld16_nowait(tmem_base + s * 64 + ch * CW + lane_t, acc);
                 mbar_wait(&bars->a2_empty[s], ph ^ 1);  // the second GEMM of group G - 2 has read this A2 buffer
                 tmem_ld_wait();
                 tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bars->d1_empty[s]);  // the accumulator is in registers: D1[s] is free
                 const uint32_t row = smem_u32(sA2) + s * kMfA2 + r * 128;
 #pragma unroll
-                for (int c8 = 0; c8 < 4; ++c8) {
+                for (int c8 = 0; c8 < CW / 8; ++c8) {
                     uint32_t pk[4];
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const int col = col0 + c8 * 8 + h * 4;
-                        float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f), t4 = c4;
-                        if (col < p.hid) {  // hid % 4 == 0
-                            c4 = __ldg(reinterpret_cast<const float4*>(p.cs1 + col));
-                            t4 = __ldg(reinterpret_cast<const float4*>(p.b1 + col));
-                        }
-                        f32x2 x0 = pack2(__uint_as_float(acc[c8 * 8 + h * 4 + 0]), __uint_as_float(acc[c8 * 8 + h * 4 + 1]));
-                        f32x2 x1 = pack2(__uint_as_float(acc[c8 * 8 + h * 4 + 2]), __uint_as_float(acc[c8 * 8 + h * 4 + 3]));
-                        x0 = fma2(x0, a2v, fma2(b2v, pack2(c4.x, c4.y), pack2(t4.x, t4.y)));
-                        x1 = fma2(x1, a2v, fma2(b2v, pack2(c4.z, c4.w), pack2(t4.z, t4.w)));
-                        pk[h * 2 + 0] = f32x2_to_bf16x2(gelu2_tanh(x0));
-                        pk[h * 2 + 1] = f32x2_to_bf16x2(gelu2_tanh(x1));
+                    for (int h = 0; h < 4; ++h) {
+                        f32x2 x = pack2(__uint_as_float(acc[c8 * 8 + h * 2]), __uint_as_float(acc[c8 * 8 + h * 2 + 1]));
+                        x = fma2(x, a2v, tbv[c8 * 4 + h]);
+                        pk[h] = f32x2_to_bf16x2(gelu2_tanh(x));
                     }
-                    sts_v4(row + ((uint32_t(ch * 4 + c8) ^ rx) << 4), pk[0], pk[1], pk[2], pk[3]);
+                    sts_v4(row + ((uint32_t(ch * (CW / 8) + c8) ^ rx) << 4), pk[0], pk[1], pk[2], pk[3]);
                 }
                 fence_proxy_async();  // the UMMA (async proxy) reads what this thread just wrote
                 __syncwarp();
-                if (lane == 0) {
-                    mbar_arrive(&bars->d1_empty[s]);
-                    mbar_arrive(&bars->a2_full[s]);
-                }
+                if (lane == 0) mbar_arrive(&bars->a2_full[s]);
             }
-            // ---- epilogue: columns [ch * NB/2, (ch + 1) * NB/2) of this row ----
+            // ---- epilogue: columns [ch * NB/kMfCG, (ch + 1) * NB/kMfCG) of this row ----
             mbar_wait(&bars->d2_full[ab], (it >> 1) & 1);
             tc_fence_after();
-            const int half = p.NB >> 1;            // multiple of 8 (NB % 16 == 0)
+            const int half = p.NB / kMfCG;         // columns per thread: a multiple of 8 (NB % 32 == 0)
             const int ecol0 = ch * half;
             const uint32_t d2 = tmem_base + d2_col0 + ab * 192 + lane_t;
             const uint32_t a_tile = smem_u32(sA) + ab * KS * kMfATile;
@@ -251,57 +256,66 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
             const float shift = st.x;
             const f32x2 nshift = splat2(-shift);
             f32x2 s1 = pack2(0.f, 0.f), s2 = s1;
-            for (int c8 = 0; c8 < half / 8; ++c8) {
-                const int col = ecol0 + c8 * 8;
-                float v[8];
-                {
-                    uint32_t a8[8];
-                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                                 : "=r"(a8[0]), "=r"(a8[1]), "=r"(a8[2]), "=r"(a8[3]), "=r"(a8[4]), "=r"(a8[5]), "=r"(a8[6]),
-                                   "=r"(a8[7])
-                                 : "r"(d2 + col)
-                                 : "memory");
-                    tmem_ld_wait();
+            for (int c32 = 0; c32 < half; c32 += 32) {
+                // up to 32 columns per TMEM load (half = 96 at C = 180: three loads per row instead of twelve)
+                uint32_t a32[32];
+                const int ncol = min(32, half - c32);
+                if (ncol == 32) {
+                    tmem_ld32_nowait(d2 + ecol0 + c32, a32);
+                } else {
+                    for (int c8 = 0; c8 < ncol; c8 += 8)
+                        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                     : "=r"(a32[c8 + 0]), "=r"(a32[c8 + 1]), "=r"(a32[c8 + 2]), "=r"(a32[c8 + 3]),
+                                       "=r"(a32[c8 + 4]), "=r"(a32[c8 + 5]), "=r"(a32[c8 + 6]), "=r"(a32[c8 + 7])
+                                     : "r"(d2 + ecol0 + c32 + c8)
+                                     : "memory");
+                }
+                tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(a8[i]);
-                }
-                // residual chunk: K chunk col / 64 of the A tile, 16-byte chunk (col % 64) / 8 of the row
-                const uint32_t addr = a_tile + (col >> 6) * kMfATile + r * 128 + ((uint32_t((col & 63) >> 3) ^ rx) << 4);
-                const uint4 res = lds_v4(addr);
-                float4 bb0 = make_float4(0.f, 0.f, 0.f, 0.f), bb1 = bb0;
-                if (col < p.C) {  // C % 4 == 0
-                    bb0 = __ldg(reinterpret_cast<const float4*>(p.b2 + col));
-                    if (col + 4 < p.C) bb1 = __ldg(reinterpret_cast<const float4*>(p.b2 + col + 4));
-                }
-                const f32x2 y0 = add2(add2(pack2(v[0], v[1]), pack2(bb0.x, bb0.y)), bf16x2_to_f32x2(res.x));
-                const f32x2 y1 = add2(add2(pack2(v[2], v[3]), pack2(bb0.z, bb0.w)), bf16x2_to_f32x2(res.y));
-                const f32x2 y2 = add2(add2(pack2(v[4], v[5]), pack2(bb1.x, bb1.y)), bf16x2_to_f32x2(res.z));
-                const f32x2 y3 = add2(add2(pack2(v[6], v[7]), pack2(bb1.z, bb1.w)), bf16x2_to_f32x2(res.w));
-                if (col + 8 <= p.C) {
-                    const f32x2 d0 = add2(y0, nshift), d1 = add2(y1, nshift), d2v = add2(y2, nshift), d3 = add2(y3, nshift);
-                    s1 = add2(s1, add2(add2(d0, d1), add2(d2v, d3)));
-                    s2 = fma2(d0, d0, s2);
-                    s2 = fma2(d1, d1, s2);
-                    s2 = fma2(d2v, d2v, s2);
-                    s2 = fma2(d3, d3, s2);
-                } else if (col < p.C) {  // the ragged last chunk (C = 180: columns 176..179)
-                    float yy[8];
-                    unpack2(y0, yy[0], yy[1]);
-                    unpack2(y1, yy[2], yy[3]);
-                    unpack2(y2, yy[4], yy[5]);
-                    unpack2(y3, yy[6], yy[7]);
-                    float t1 = 0.f, t2 = 0.f;
+                for (int c8 = 0; c8 < 4; ++c8) {
+                    if (c8 * 8 >= ncol) break;
+                    const int col = ecol0 + c32 + c8 * 8;
+                    float v[8];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        if (col + i < p.C) {
-                            const float d = yy[i] - shift;
-                            t1 += d;
-                            t2 = fmaf(d, d, t2);
-                        }
-                    s1 = add2(s1, pack2(t1, 0.f));
-                    s2 = add2(s2, pack2(t2, 0.f));
+                    for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(a32[c8 * 8 + i]);
+                    // residual chunk: K chunk col / 64 of the A tile, 16-byte chunk (col % 64) / 8 of the row
+                    const uint32_t addr = a_tile + (col >> 6) * kMfATile + r * 128 + ((uint32_t((col & 63) >> 3) ^ rx) << 4);
+                    const uint4 res = lds_v4(addr);
+                    float4 bb0 = make_float4(0.f, 0.f, 0.f, 0.f), bb1 = bb0;
+                    if (col < p.C) {  // C % 4 == 0
+                        bb0 = __ldg(reinterpret_cast<const float4*>(p.b2 + col));
+                        if (col + 4 < p.C) bb1 = __ldg(reinterpret_cast<const float4*>(p.b2 + col + 4));
+                    }
+                    const f32x2 y0 = add2(add2(pack2(v[0], v[1]), pack2(bb0.x, bb0.y)), bf16x2_to_f32x2(res.x));
+                    const f32x2 y1 = add2(add2(pack2(v[2], v[3]), pack2(bb0.z, bb0.w)), bf16x2_to_f32x2(res.y));
+                    const f32x2 y2 = add2(add2(pack2(v[4], v[5]), pack2(bb1.x, bb1.y)), bf16x2_to_f32x2(res.z));
+                    const f32x2 y3 = add2(add2(pack2(v[6], v[7]), pack2(bb1.z, bb1.w)), bf16x2_to_f32x2(res.w));
+                    if (col + 8 <= p.C) {
+                        const f32x2 d0 = add2(y0, nshift), d1 = add2(y1, nshift), d2v = add2(y2, nshift), d3 = add2(y3, nshift);
+                        s1 = add2(s1, add2(add2(d0, d1), add2(d2v, d3)));
+                        s2 = fma2(d0, d0, s2);
+                        s2 = fma2(d1, d1, s2);
+                        s2 = fma2(d2v, d2v, s2);
+                        s2 = fma2(d3, d3, s2);
+                    } else if (col < p.C) {  // the ragged last chunk (C = 180: columns 176..179)
+                        float yy[8];
+                        unpack2(y0, yy[0], yy[1]);
+                        unpack2(y1, yy[2], yy[3]);
+                        unpack2(y2, yy[4], yy[5]);
+                        unpack2(y3, yy[6], yy[7]);
+                        float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            if (col + i < p.C) {
+                                const float d = yy[i] - shift;
+                                t1 += d;
+                                t2 = fmaf(d, d, t2);
+                            }
+                        s1 = add2(s1, pack2(t1, 0.f));
+                        s2 = add2(s2, pack2(t2, 0.f));
+                    }
+                    sts_v4(addr, f32x2_to_bf16x2(y0), f32x2_to_bf16x2(y1), f32x2_to_bf16x2(y2), f32x2_to_bf16x2(y3));
                 }
-                sts_v4(addr, f32x2_to_bf16x2(y0), f32x2_to_bf16x2(y1), f32x2_to_bf16x2(y2), f32x2_to_bf16x2(y3));
             }
             tc_fence_before();
             fence_proxy_async();  // the TMA store (async proxy) reads the tile
@@ -309,16 +323,22 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
             float a0, a1, q0, q1;
             unpack2(s1, a0, a1);
             unpack2(s2, q0, q1);
-            if (ch == 1) red[r] = make_float2(a0 + a1, q0 + q1);
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (ch > 0) red[(ch - 1) * 128 + r] = make_float2(a0 + a1, q0 + q1);
+            asm volatile("bar.sync 1, %0;" ::"n"(kMfWarps * 32) : "memory");
             if (ch == 0 && valid && p.stats_out != nullptr) {
-                const float2 o = red[r];
+                float t1 = a0 + a1, t2 = q0 + q1;
+#pragma unroll
+                for (int k = 0; k < kMfCG - 1; ++k) {
+                    const float2 o = red[k * 128 + r];
+                    t1 += o.x;
+                    t2 += o.y;
+                }
                 const float invn = 1.0f / float(p.C);
-                const float m = (a0 + a1 + o.x) * invn;
-                const float var = fmaxf((q0 + q1 + o.y) * invn - m * m, 0.f);
+                const float m = t1 * invn;
+                const float var = fmaxf(t2 * invn - m * m, 0.f);
                 p.stats_out[grow] = make_float2(shift + m, rsqrtf(var + p.eps));
             }
-            asm volatile("bar.sync 1, 256;" ::: "memory");  // red[] is free again; every warp's part of the tile is written
+            asm volatile("bar.sync 1, %0;" ::"n"(kMfWarps * 32) : "memory");  // red[] (= A2) is free again; the tile is written
             __syncwarp();
             if (lane == 0) {
                 mbar_arrive(&bars->d2_empty[ab]);
@@ -333,7 +353,8 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
 
 bool mlp_fused_shape_ok(int C, int hid) {
     // K = C in <= 3 chunks of 64 and two D2 buffers of <= 192 TMEM columns next to the two D1 buffers
-    return C >= 16 && C <= 192 && C % 4 == 0 && hid % 4 == 0 && hid >= 64 && hid <= 1024;
+    return C >= 32 && C <= 192 && C % 4 == 0 && ((C + 15) / 16 * 16) % (8 * kMfCG) == 0 && hid % 4 == 0 && hid >= 64 &&
+           hid <= 1024;
 }
 
 // x [P][ldx] bf16 (in place); w1 bf16 [hid][ldw1] = fc1 with norm2's gain folded in; w2 bf16 [C][ldw2]
@@ -382,7 +403,7 @@ int mlp_fused_bf16(bf16* x, long long ldx, long long P, int C, int hid, const fl
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int grid = p.tiles < sms ? p.tiles : sms;
     const size_t smem = 1024 + size_t(2) * p.KS * kMfATile + size_t(2) * p.KS * kMfW1Slab + 2 * kMfA2 +
-                        size_t(2) * p.NB * 128 + 128 * sizeof(float2) + sizeof(MfBars) + 64;
+                        size_t(2) * p.NB * 128 + sizeof(MfBars) + 64;
     IRB_REQUIRE(smem <= 227 * 1024, "mlp_fused: shared memory budget exceeded");
     IRB_SMEM_OPTIN((mlp_fused_kernel), 227 * 1024);
     IRB_CHECK_CUDA(launch_pdl(mlp_fused_kernel, dim3(grid), dim3(kMfThreads), smem, stream, p));
