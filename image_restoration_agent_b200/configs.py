@@ -37,17 +37,21 @@ XRESTORMER_BASE = {  # executor/{dehazing,denoising,deraining,motion_deblurring}
     "window_size": 8, "spatial_dim_head": 16, "ffn_expansion_factor": 2.66, "bias": False,
     "LayerNorm_type": "WithBias", "dual_pixel_task": False, "scale": 1,
 }
-XRESTORMER_SUBTASKS = ("dehazing", "denoising", "deraining", "motion_deblurring")  # scale 1; SR (scale 4) not served
+XRESTORMER_SUBTASKS = ("dehazing", "denoising", "deraining", "motion_deblurring", "super_resolution")
 
 
-def xrestormer_config() -> dict:
-    """The one architecture all four scale-1 X-Restormer tools share (padding_size 64 in every yml)."""
-    return copy.deepcopy(XRESTORMER_BASE)
-
-
-def small_xrestormer_config(ln_type="WithBias") -> dict:
+def xrestormer_config(subtask: str = "dehazing") -> dict:
+    """The one architecture all X-Restormer tools share; scale 1 / padding_size 64 in four ymls, scale 4 / padding_size
+    16 in executor/super_resolution/configs/xrestormer.yml (the input is bilinearly up-sampled x4 first)."""
     p = copy.deepcopy(XRESTORMER_BASE)
-    p.update(num_blocks=[1, 1, 1, 1], num_refinement_blocks=1, LayerNorm_type=ln_type)
+    if subtask == "super_resolution":
+        p["scale"] = 4
+    return p
+
+
+def small_xrestormer_config(ln_type="WithBias", scale=1) -> dict:
+    p = copy.deepcopy(XRESTORMER_BASE)
+    p.update(num_blocks=[1, 1, 1, 1], num_refinement_blocks=1, LayerNorm_type=ln_type, scale=scale)
     return p
 
 

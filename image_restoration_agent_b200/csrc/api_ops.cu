@@ -112,8 +112,11 @@ int irb_padded_size(int arch, int window_size, int h, int w, int* hp, int* wp) {
         *hp = (h % 8) ? ((h + 8) / 8) * 8 : h;  // demo.py:122-126
         *wp = (w % 8) ? ((w + 8) / 8) * 8 : w;
     } else if (arch == IRB_ARCH_XRESTORMER) {
-        *hp = (h % 64) ? (h / 64 + 1) * 64 : h;  // xrestormer_model.py:56-66, padding_size 64
-        *wp = (w % 64) ? (w / 64 + 1) * 64 : w;
+        // xrestormer_model.py:56-66: padding_size 64 (scale-1 configs) / 16 (the scale-4 SR config); the caller passes it
+        // in `window_size` (0 = 64)
+        const int m = window_size > 0 ? window_size : 64;
+        *hp = (h % m) ? (h / m + 1) * m : h;
+        *wp = (w % m) ? (w / m + 1) * m : w;
     } else {
         set_error("irb_padded_size: unknown arch");
         return 1;

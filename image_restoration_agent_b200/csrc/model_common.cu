@@ -231,7 +231,8 @@ struct RestorePlan {
 
 static int make_plan(Model* m, int img_h, int img_w, int tile, int overlap, void* ws, RestorePlan& P) {
     IRB_REQUIRE(img_h > 0 && img_w > 0, "restore: empty image");
-    IRB_TRY(irb_padded_size(m->desc.arch, m->desc.window_size, img_h, img_w, &P.hp, &P.wp));
+    IRB_TRY(irb_padded_size(m->desc.arch, m->desc.arch == IRB_ARCH_XRESTORMER ? m->tile_multiple() : m->desc.window_size,
+                            img_h, img_w, &P.hp, &P.wp));
     P.sf = m->scale;
     P.c = m->cin;
     if (tile <= 0) {

@@ -85,10 +85,11 @@ struct Restormer : Model {
     ConvW patch, down12, down23, down34, up43, up32, up21, outc;
     void *reduce3, *reduce2;
 
-    int tile_multiple() const override { return desc.arch == IRB_ARCH_XRESTORMER ? 64 : 8; }
+    int tile_multiple() const override { return desc.arch == IRB_ARCH_XRESTORMER ? 64 / scale : 8; }
     size_t forward_workspace(int n, int H, int W) override;
     int forward(const float* in, float* out, int n, int H, int W, void* ws, size_t ws_bytes,
                 cudaStream_t stream) override;
+    int forward_core(const float* in, float* out, int n, int H, int W, void* ws, size_t ws_bytes, cudaStream_t stream);
 
     struct WS {
         void *cat1, *cat2, *cat3, *x2, *x3, *x4, *ln, *qkv_pre, *qkv, *hidden, *gated, *weff;
@@ -281,6 +282,10 @@ int build_restormer(const irb_model_desc& d, const Blob& blob, int device, Model
     m->device = device;
     m->cin = d.in_chans;
     m->scale = 1;
+    if (d.arch == IRB_ARCH_XRESTORMER && d.upscale > 1) {  // the SR config: scale 4 (executor/super_resolution/configs/xrestormer.yml)
+        IRB_REQUIRE(d.upscale == 2 || d.upscale == 4, "XRestormer: scale must be 1, 2 or 4");
+        m->scale = d.upscale;
+    }
     m->dim = d.dim;
     IRB_REQUIRE(d.dim > 0 && d.dim % 16 == 0, "Restormer: dim must be a positive multiple of 16");
     IRB_REQUIRE(d.in_chans == 1 || d.in_chans == 3, "Restormer: in_chans must be 1 or 3");
@@ -391,8 +396,9 @@ void Restormer::layout(Bump& b, int n, int H, int W, WS& w) {
 size_t Restormer::forward_workspace(int n, int H, int W) {
     Bump b(nullptr);
     WS w;
-    layout(b, n, H, W, w);
-    return b.off + 256;
+    layout(b, n, H * scale, W * scale, w);
+    const size_t up = scale == 1 ? 0 : ((size_t(n) * H * scale * W * scale * cin * 4 + 255) & ~size_t(255));
+    return b.off + 256 + up;
 }
 
 int Restormer::run_gemm(const void* A, long long lda, long long M, int K, const void* Wt, int ldw, int N, int wrows,
@@ -546,14 +552,52 @@ int Restormer::run_ocab(const RBlockW& w, void* x, long long ldx, int n, int H, 
     return run_gemm(ws.ln, inner, P, inner, w.oc_proj_w, inner, C, C, e, s);
 }
 
-int Restormer::forward(const float* in, float* out, int n, int H, int W, void* wsp, size_t ws_bytes,
-                       cudaStream_t s) {
+// F.interpolate(x, scale_factor=S, mode='bilinear', align_corners=False) on channels-last fp32 (xrestormer_arch.py:383-384,
+// the scale-4 SR variant of X-Restormer up-samples its INPUT and then runs the scale-1 network on it)
+__global__ void bilinear_up_kernel(const float* __restrict__ in, float* __restrict__ out, int n, int H, int W, int c, int S) {
+    const int Ho = H * S, Wo = W * S;
+    const long long total = (long long)n * Ho * Wo;
+    const float inv = 1.0f / float(S);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int ox = int(i % Wo), oy = int((i / Wo) % Ho);
+        const long long b = i / ((long long)Wo * Ho);
+        // ATen area_pixel_compute_source_index (align_corners=False): src = max((dst + 0.5) * scale - 0.5, 0)
+        const float sy = fmaxf((oy + 0.5f) * inv - 0.5f, 0.f), sx = fmaxf((ox + 0.5f) * inv - 0.5f, 0.f);
+        const int y0 = int(sy), x0 = int(sx);
+        const int y1 = y0 + (y0 < H - 1 ? 1 : 0), x1 = x0 + (x0 < W - 1 ? 1 : 0);
+        const float ly = sy - y0, lx = sx - x0, hy = 1.f - ly, hx = 1.f - lx;
+        const float* p00 = in + ((b * H + y0) * W + x0) * c;
+        const float* p01 = in + ((b * H + y0) * W + x1) * c;
+        const float* p10 = in + ((b * H + y1) * W + x0) * c;
+        const float* p11 = in + ((b * H + y1) * W + x1) * c;
+        for (int ch = 0; ch < c; ++ch)
+            out[i * c + ch] = hy * (hx * p00[ch] + lx * p01[ch]) + ly * (hx * p10[ch] + lx * p11[ch]);
+    }
+}
+
+int Restormer::forward(const float* in, float* out, int n, int H, int W, void* wsp, size_t ws_bytes, cudaStream_t s) {
+    if (scale == 1) return forward_core(in, out, n, H, W, wsp, ws_bytes, s);
+    // X-Restormer SR: bilinear x`scale` of the input, then the network at the up-sampled size (:383-412)
+    IRB_REQUIRE(ws_bytes >= forward_workspace(n, H, W), "XRestormer: workspace too small");
+    const size_t up_bytes = (size_t(n) * H * scale * W * scale * cin * 4 + 255) & ~size_t(255);
+    float* up = reinterpret_cast<float*>(wsp);
+    const long long total = (long long)n * H * scale * W * scale;
+    const int blocks = int(ceil_div_ll(total, 256) > 148 * 16 ? 148 * 16 : ceil_div_ll(total, 256));
+    bilinear_up_kernel<<<blocks, 256, 0, s>>>(in, up, n, H, W, cin, scale);
+    IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("bilinear_up", cin, scale, 0.0, double(total) * cin * 4.0 * (1.0 + 1.0 / (scale * scale)), s);
+    return forward_core(up, out, n, H * scale, W * scale, reinterpret_cast<char*>(wsp) + up_bytes, ws_bytes - up_bytes, s);
+}
+
+int Restormer::forward_core(const float* in, float* out, int n, int H, int W, void* wsp, size_t ws_bytes,
+                            cudaStream_t s) {
     IRB_REQUIRE(H % 8 == 0 && W % 8 == 0, "Restormer: tile height/width must be multiples of 8");
-    IRB_REQUIRE(ws_bytes >= forward_workspace(n, H, W), "Restormer: workspace too small");
     IRB_REQUIRE((long long)H * W < (1ll << 31) / 8, "Restormer: tile too large");
     Bump b(wsp);
     WS ws;
     layout(b, n, H, W, ws);
+    IRB_REQUIRE(ws_bytes >= b.off, "Restormer: workspace too small");
     const int d = dim;
     auto blocks = [&](std::vector<RBlockW>& v, void* x, long long ldx, int h, int w) -> int {
         ws.stats_valid = false;  // the stream was just written by a convolution

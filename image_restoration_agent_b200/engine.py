@@ -35,8 +35,8 @@ def restormer_desc(cfg: dict, precision: int) -> ModelDesc:
 
 def xrestormer_desc(cfg: dict, precision: int) -> ModelDesc:
     """XRestormer(...) of xrestormer_arch.py:324-341 with the agent's configs (executor/*/configs/xrestormer.yml)."""
-    if cfg.get("bias", False) or cfg.get("dual_pixel_task", False) or cfg.get("scale", 1) != 1:
-        raise ValueError("irb200 X-Restormer supports bias=False, dual_pixel_task=False, scale=1")
+    if cfg.get("bias", False) or cfg.get("dual_pixel_task", False) or cfg.get("scale", 1) not in (1, 2, 4):
+        raise ValueError("irb200 X-Restormer supports bias=False, dual_pixel_task=False, scale in (1, 2, 4)")
     if len(set(cfg["overlap_ratio"])) != 1:
         raise ValueError("irb200 X-Restormer needs one overlap_ratio for all levels")
     d = ModelDesc()
@@ -51,6 +51,7 @@ def xrestormer_desc(cfg: dict, precision: int) -> ModelDesc:
     d.spatial_heads[:] = cfg["spatial_heads"]
     d.spatial_dim_head = cfg["spatial_dim_head"]
     d.overlap_ratio = cfg["overlap_ratio"][0]
+    d.upscale = cfg.get("scale", 1)
     return d
 
 

@@ -218,19 +218,20 @@ class RestormerB200(Tool):
 
 class XRestormerB200(Tool):
     """In-process replacement of multitask_tools.XRestormer (tool_name 'xrestormer', a BasicSRModel tool:
-    multitask_tools.py:67-78) for the four scale-1 subtasks. The reference runs BasicSR's test pipeline on the yml of
-    executor/<subtask>/configs/xrestormer.yml: reflect pad to a multiple of 64, whole image, crop, tensor2img."""
+    multitask_tools.py:67-78) for its five subtasks. The reference runs BasicSR's test pipeline on the yml of
+    executor/<subtask>/configs/xrestormer.yml: reflect pad to a multiple of 64 (16 for the scale-4 SR config, whose
+    network first up-samples the input bilinearly), whole image, crop, tensor2img."""
 
     SUBTASKS = configs.XRESTORMER_SUBTASKS
     WEIGHTS = {"dehazing": "dehaze_300k.pth", "denoising": "denoise_300k.pth", "deraining": "derain_155k.pth",
-               "motion_deblurring": "deblur_300k.pth"}  # path.pretrain_network_g of the four ymls
+               "motion_deblurring": "deblur_300k.pth", "super_resolution": "sr_300k.pth"}  # path.pretrain_network_g
 
     def __init__(self, subtask: str, weights_root: Optional[str] = None, state_dict=None, precision: str = "bf16",
                  device: int = 0, cfg: Optional[dict] = None):
         if subtask not in self.SUBTASKS:
-            raise ValueError(f"irb200 X-Restormer serves {self.SUBTASKS} (scale 1); got {subtask!r}")
+            raise ValueError(f"irb200 X-Restormer serves {self.SUBTASKS}; got {subtask!r}")
         super().__init__(tool_name="xrestormer", subtask=subtask)
-        self.cfg = cfg or configs.xrestormer_config()
+        self.cfg = cfg or configs.xrestormer_config(subtask)
         self.weights_root, self.state_dict = weights_root, state_dict
         self.precision, self.device = precision, device
 

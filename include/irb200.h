@@ -66,7 +66,8 @@ typedef struct irb_model_desc {
     int upsampler;  /* IRB_UPSAMPLER_* */
     int resi_3conv; /* 1: resi_connection='3conv', 0: '1conv' */
     /* XRestormer(...)  xrestormer_arch.py:324-341: dim, num_blocks, num_refinement_blocks, heads (= channel_heads),
-     * ffn_expansion_factor, ln_bias_free as above, window_size as above, plus: */
+     * ffn_expansion_factor, ln_bias_free as above, window_size as above, upscale = scale (1; 4 = the SR config: the input
+     * is bilinearly up-sampled first, :383-384), plus: */
     int spatial_heads[4];
     int spatial_dim_head;
     float overlap_ratio; /* the same for every level in all agent configs */
@@ -82,7 +83,8 @@ int irb_plan_tiles(int n, int tile, int overlap, int* idx, int* count);
 
 /* Padded size the reference scripts feed to the model: SwinIR (h / ws + 1) * ws (always pads,
  * inference.py:76-78); Restormer next multiple of 8 only when needed (demo.py:122-126); X-Restormer next multiple of
- * 64 only when needed (xrestormer_model.py:56-66, padding_size 64). Host-only. */
+ * `window_size` (64 for the scale-1 configs, 16 for the scale-4 SR config; 0 = 64) only when needed
+ * (xrestormer_model.py:56-66). Host-only. */
 int irb_padded_size(int arch, int window_size, int h, int w, int* hp, int* wp);
 
 /* weights_blob: host memory, format documented in image_restoration_agent_b200/weights.py (IRBW v1: named fp32

@@ -90,7 +90,7 @@ def restormer_restore_image(img_rgb_u8: np.ndarray, model, tile=None, tile_overl
     return np.rint(r * np.float32(255.0)).astype(np.uint8)
 
 
-def xrestormer_restore_image(img_bgr_u8: np.ndarray, model, return_float=False, padding_size: int = 64):
+def xrestormer_restore_image(img_bgr_u8: np.ndarray, model, return_float=False, padding_size: int = 64, scale: int = 1):
     """The BasicSR test path of the X-Restormer tool (executor/*/configs/xrestormer.yml: no tile, padding_size 64):
     cv2.imread BGR -> RGB float/255 (basicsr img2tensor, bgr2rgb) -> reflect pad bottom/right to a multiple of
     padding_size only when needed (xrestormer_model.py:56-66 pre_process) -> model -> crop (:139-142 post_process) ->
@@ -102,7 +102,7 @@ def xrestormer_restore_image(img_bgr_u8: np.ndarray, model, return_float=False, 
     x = F.pad(x, (0, pw, 0, ph), "reflect")
     with torch.no_grad():
         y = model(x)
-    y = y[:, :, :h, :w]
+    y = y[:, :, :h * scale, :w * scale]   # post_process: 0 : h - mod_pad_h * scale
     if return_float:
         return y[0].clone()
     o = y[0].float().clamp_(0, 1).numpy()

@@ -85,8 +85,9 @@ def _stage(x, sd, name, n, cfg, level):
 
 
 def forward(sd, cfg, inp_img):
-    """XRestormer.forward, xrestormer_arch.py:382-412 (scale = 1)."""
-    assert cfg.get("scale", 1) == 1, "the agent's configs use scale 1 (executor/*/configs/xrestormer.yml)"
+    """XRestormer.forward, xrestormer_arch.py:382-412."""
+    if cfg.get("scale", 1) > 1:  # :383-384
+        inp_img = F.interpolate(inp_img, scale_factor=cfg["scale"], mode="bilinear", align_corners=False)
     nb = cfg["num_blocks"]
     down = lambda t, n: F.pixel_unshuffle(F.conv2d(t, sd[f"{n}.body.0.weight"], padding=1), 2)
     up = lambda t, n: F.pixel_shuffle(F.conv2d(t, sd[f"{n}.body.0.weight"], padding=1), 2)

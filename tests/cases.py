@@ -14,6 +14,7 @@ X_CASES = {  # X-Restormer, tools/make_golden_full.py xrestorm
     "xrestormer_small_withbias": lambda: configs.small_xrestormer_config("WithBias"),
     "xrestormer_small_biasfree": lambda: configs.small_xrestormer_config("BiasFree"),
     "xrestormer_full": lambda: configs.xrestormer_config(),
+    "xrestormer_small_sr_x4": lambda: configs.small_xrestormer_config("WithBias", scale=4),
 }
 S_CASES = {
     "swinir_small_color_dn": lambda: configs.small_swinir_config("color_dn"),

@@ -251,7 +251,8 @@ def test_fused_pwdw_model_equals_unfused_within_bf16_rounding(ln):
 
 # ---------------- X-Restormer ----------------
 @pytest.mark.parametrize("prec", ["fp32", "bf16"])
-@pytest.mark.parametrize("name", ["xrestormer_small_withbias", "xrestormer_small_biasfree", "xrestormer_full"])
+@pytest.mark.parametrize("name", ["xrestormer_small_withbias", "xrestormer_small_biasfree", "xrestormer_full",
+                                  "xrestormer_small_sr_x4"])
 def test_xrestormer_forward_matches_reference(name, prec, golden_dir):
     from cases import X_CASES
     from image_restoration_agent_b200.engine import Engine
@@ -287,6 +288,26 @@ def test_xrestormer_tool_matches_reference(tmp_path, prec, golden_dir):
     assert d.max() <= (1 if prec == "fp32" else math.ceil(255 * 2e-2)) and (d <= 1).mean() >= 0.90
     eng = tool._engine()
     _, f32 = eng.restore_device(torch.from_numpy(g["img"]).cuda(), None, 0, bgr=True, want_f32=True)
+    assert np.abs(f32.cpu().numpy() - g["out_f32"]).max() <= (1e-4 if prec == "fp32" else 2e-2)
+    clear_engines()
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_xrestormer_sr_tool_matches_reference(tmp_path, prec, golden_dir):
+    """The scale-4 SR tool (executor/super_resolution/configs/xrestormer.yml): pad to 16, bilinear x4 inside the model."""
+    import cv2
+    from image_restoration_agent_b200.tool_api import XRestormerB200, clear_engines
+    g = np.load(os.path.join(golden_dir, "xrestormer_pipeline_small_sr_x4.npz"))
+    cfg = configs.small_xrestormer_config("WithBias", scale=4)
+    sd = synth.xrestormer_state_dict(cfg, seed=int(g["seed"]))
+    i, o = _dirs(tmp_path, g["img"])
+    tool = XRestormerB200("super_resolution", state_dict=sd, cfg=cfg, precision=prec)
+    tool(i, o, silent=True)
+    got = cv2.imread(str(o / "output.png"), cv2.IMREAD_COLOR)
+    assert got.shape == g["out_u8"].shape == (120, 164, 3)
+    d = _lsb(got, g["out_u8"])
+    assert d.max() <= (1 if prec == "fp32" else math.ceil(255 * 2e-2)) and (d <= 1).mean() >= 0.90
+    _, f32 = tool._engine().restore_device(torch.from_numpy(g["img"]).cuda(), None, 0, bgr=True, want_f32=True)
     assert np.abs(f32.cpu().numpy() - g["out_f32"]).max() <= (1e-4 if prec == "fp32" else 2e-2)
     clear_engines()
 

@@ -209,6 +209,33 @@ def xrestormer():
 
 GROUPS["xrestormer"] = xrestormer
 
+
+def xrestormer_sr():
+    """The scale-4 SR config (executor/super_resolution/configs/xrestormer.yml: scale 4, padding_size 16)."""
+    from oracle import xrestormer_ref
+    name = "xrestormer_small_sr_x4"
+    print(name)
+    cfg = configs.small_xrestormer_config("WithBias", scale=4)
+    sd = synth.xrestormer_state_dict(cfg, seed=5)
+    ref = ref_xrestormer(cfg, sd)
+    x = image_like(512, 512, 3, seed=5)[..., 10:42, 20:68].contiguous()      # 32 x 48 -> 128 x 192
+    with torch.no_grad():
+        y_ref = ref(x)
+    y_or = xrestormer_ref.Model(sd, cfg)(x)
+    mg.check(name, y_or, y_ref, tol=2e-5)
+    mg.save(name, x=x.numpy(), y=y_ref.numpy(), seed=np.int64(5))
+    name = "xrestormer_pipeline_small_sr_x4"
+    print(name)
+    img = synth.synthetic_image_u8(30, 41, 3, seed=6)                          # pad 16 -> 32 x 48, out 120 x 164
+    u8_ref = tiling.xrestormer_restore_image(img, ref, padding_size=16, scale=4)
+    f_ref = tiling.xrestormer_restore_image(img, ref, return_float=True, padding_size=16, scale=4)
+    u8_or = tiling.xrestormer_restore_image(img, xrestormer_ref.Model(sd, cfg), padding_size=16, scale=4)
+    assert np.abs(u8_or.astype(int) - u8_ref.astype(int)).max() <= 1
+    mg.save(name, img=img, out_u8=u8_ref, out_f32=f_ref.numpy(), seed=np.int64(5), tile=np.int64(-1), overlap=np.int64(0))
+
+
+GROUPS["xrestormer_sr"] = xrestormer_sr
+
 if __name__ == "__main__":
     torch.manual_seed(0)
     torch.set_num_threads(os.cpu_count() or 8)
