@@ -29,6 +29,7 @@ class ModelDesc(C.Structure):
         ("depths", C.c_int * 16), ("num_heads", C.c_int * 16), ("mlp_ratio", C.c_int), ("upscale", C.c_int),
         ("img_range", C.c_float), ("upsampler", C.c_int), ("resi_3conv", C.c_int),
         ("spatial_heads", C.c_int * 4), ("spatial_dim_head", C.c_int), ("overlap_ratio", C.c_float),
+        ("unshuffle_scale", C.c_int),
     ]
 
 

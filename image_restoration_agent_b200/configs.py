@@ -86,6 +86,20 @@ def swinir_config(task: str, scale: int = 1, large_model: bool = False, training
     raise ValueError(f"Unknown task: {task}")
 
 
+def diffbir_swinir_config() -> dict:
+    """DiffBIR's stage-1 degradation-removal SwinIR (executor/super_resolution/configs/diffbir.yml:92-107,
+    DiffBIR/model/swinir.py:629-800): PixelUnshuffle(8) head, 8 RSTB, nearest+conv x8 tail; output size == input size."""
+    return dict(upscale=8, in_chans=3, img_size=64, window_size=8, img_range=1.0, depths=[6] * 8, embed_dim=180,
+                num_heads=[6] * 8, mlp_ratio=2, upsampler="nearest+conv", resi_connection="1conv", unshuffle=True,
+                unshuffle_scale=8)
+
+
+def small_diffbir_swinir_config() -> dict:
+    p = diffbir_swinir_config()
+    p["depths"], p["num_heads"] = [2, 2], [6, 6]
+    return p
+
+
 def small_restormer_config(ln_type="WithBias", inp_channels=3) -> dict:
     """A shrunken Restormer (same code paths, every level present) for fast parity tests."""
     p = copy.deepcopy(RESTORMER_BASE)

@@ -67,6 +67,30 @@ __global__ void swin_prep_kernel(const float* __restrict__ in, float* __restrict
         }
     }
 }
+// DiffBIR stage 1 (DiffBIR/model/swinir.py:716-724): (x - mean) * img_range, then PixelUnshuffle(us):
+// out[b, y, x, c * us^2 + i * us + j] = in[b, y * us + i, x * us + j, c]
+template <typename T>
+__global__ void swin_prep_unshuffle_kernel(const float* __restrict__ in, T* __restrict__ out, int n, int H, int W, int c,
+                                           int us, float m0, float m1, float m2, float range) {
+    const int co = c * us * us;
+    const long long total = (long long)n * H * W * co;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int oc = int(i % co);
+        long long px = i / co;
+        const int x = int(px % W);
+        px /= W;
+        const int y = int(px % H);
+        const long long b = px / H;
+        const int ch = oc / (us * us), sub = oc - ch * us * us, si = sub / us, sj = sub - si * us;
+        const float mean = ch == 0 ? m0 : (ch == 1 ? m1 : m2);
+        const float v = (in[((b * (H * us) + y * us + si) * (long long)(W * us) + x * us + sj) * c + ch] - mean) * range;
+        if (sizeof(T) == 4)
+            reinterpret_cast<float*>(out)[i] = v;
+        else
+            reinterpret_cast<bf16*>(out)[i] = __float2bfloat16_rn(v);
+    }
+}
 __global__ void crop_nhwc_kernel(const float* __restrict__ in, float* __restrict__ out, int n, int H, int W, int Hc,
                                  int Wc, int c) {
     const long long total = (long long)n * Hc * Wc * c;
@@ -88,6 +112,9 @@ static int grid_for(long long total) {
 
 struct SwinIR : Model {
     int C, ldC, ws, ws_eff, can_shift, hid, dp, Cq;
+    int us = 1;   // PixelUnshuffle factor of conv_first (DiffBIR stage 1: 8), 1 = none
+    int tsc = 1;  // scale of the reconstruction tail (desc.upscale); the model's in -> out scale is tsc / us
+    Conv3W conv_up3;
     float mean[3];
     Conv3W conv_first, conv_before_up, conv_up1, conv_up2, conv_hr, conv_last;
     std::vector<Conv3W> upsample;
@@ -96,7 +123,7 @@ struct SwinIR : Model {
     std::vector<ResiW> layer_conv;
     ResiW conv_after_body;
 
-    int tile_multiple() const override { return desc.window_size; }
+    int tile_multiple() const override { return desc.window_size * us; }
     size_t forward_workspace(int n, int H, int W) override;
     int forward(const float* in, float* out, int n, int H, int W, void* ws, size_t ws_bytes,
                 cudaStream_t stream) override;
@@ -236,7 +263,12 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
     m->dt = d.precision == IRB_BF16 ? DT_BF16 : DT_F32;
     m->device = device;
     m->cin = d.in_chans;
-    m->scale = d.upscale;
+    m->tsc = d.upscale;
+    m->us = d.unshuffle_scale > 1 ? d.unshuffle_scale : 1;
+    if (m->us > 1)  // DiffBIR/model/swinir.py:716-724: the tail undoes the head's PixelUnshuffle
+        IRB_REQUIRE(d.upsampler == IRB_UPSAMPLER_NEAREST_CONV && d.upscale == m->us && (m->us == 2 || m->us == 4 || m->us == 8),
+                    "SwinIR: unshuffle needs the nearest+conv tail with upscale == unshuffle_scale in {2, 4, 8}");
+    m->scale = d.upscale / m->us;
     IRB_REQUIRE(d.in_chans == 1 || d.in_chans == 3, "SwinIR: in_chans must be 1 or 3");
     IRB_REQUIRE(d.embed_dim > 0 && d.embed_dim % 4 == 0 && d.embed_dim <= 512, "SwinIR: embed_dim must be %4, <= 512");
     IRB_REQUIRE(d.window_size >= 1 && d.window_size <= 8, "SwinIR: window_size must be <= 8");
@@ -246,7 +278,8 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
                     d.upsampler == IRB_UPSAMPLER_NEAREST_CONV, "SwinIR: bad upsampler");
     if (d.upsampler == IRB_UPSAMPLER_NONE) IRB_REQUIRE(d.upscale == 1, "SwinIR: upsampler '' needs upscale 1");
     if (d.upsampler == IRB_UPSAMPLER_NEAREST_CONV)
-        IRB_REQUIRE(d.upscale == 2 || d.upscale == 4, "SwinIR: nearest+conv supports x2 / x4");
+        IRB_REQUIRE(d.upscale == 2 || d.upscale == 4 || (d.upscale == 8 && m->us == 8),
+                    "SwinIR: nearest+conv supports x2 / x4 (x8 with the unshuffle head)");
     const int C = m->C = d.embed_dim;
     m->ldC = (C + 15) / 16 * 16;
     m->ws = d.window_size;
@@ -267,7 +300,10 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
         m->mean[2] = 0.4040f;
     }
     IRB_TRY(m->upload_f32(m->mean, 3, &m->d_mean));
-    IRB_TRY(m->load_conv(blob, "conv_first", C, d.in_chans, m->conv_first));
+    if (m->us > 1)  // Sequential(PixelUnshuffle, Conv2d): the convolution is entry 1
+        IRB_TRY(m->load_conv(blob, "conv_first.1", C, d.in_chans * m->us * m->us, m->conv_first));
+    else
+        IRB_TRY(m->load_conv(blob, "conv_first", C, d.in_chans, m->conv_first));
     IRB_TRY(m->load_norm(blob, "patch_embed.norm", &m->pen_w, &m->pen_b));
     m->layers.resize(d.num_layers);
     m->layer_conv.resize(d.num_layers);
@@ -304,7 +340,8 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
     } else if (d.upsampler == IRB_UPSAMPLER_NEAREST_CONV) {
         IRB_TRY(m->load_conv(blob, "conv_before_upsample.0", 64, C, m->conv_before_up));
         IRB_TRY(m->load_conv(blob, "conv_up1", 64, 64, m->conv_up1));
-        if (d.upscale == 4) IRB_TRY(m->load_conv(blob, "conv_up2", 64, 64, m->conv_up2));
+        if (d.upscale >= 4) IRB_TRY(m->load_conv(blob, "conv_up2", 64, 64, m->conv_up2));
+        if (d.upscale == 8) IRB_TRY(m->load_conv(blob, "conv_up3", 64, 64, m->conv_up3));
         IRB_TRY(m->load_conv(blob, "conv_hr", 64, 64, m->conv_hr));
         IRB_TRY(m->load_conv(blob, "conv_last", d.in_chans, 64, m->conv_last));
     } else {
@@ -313,13 +350,14 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
     return 0;
 }
 
-void SwinIR::layout(Bump& b, int n, int H0, int W0, WS& w) {
+void SwinIR::layout(Bump& b, int n, int Hin, int Win, WS& w) {
+    const int H0 = Hin / us, W0 = Win / us;  // the body runs at 1 / us of the input resolution (us = 1 except DiffBIR)
     int H, W;
     padded(H0, W0, H, W);
     const size_t E = esize();
     const size_t P = size_t(n) * H * W;
-    const int s = scale;
-    w.xin = b.take<float>(P * cin * 4);
+    const int s = tsc;
+    w.xin = b.take<float>(P * cin * us * us * 4);
     w.out_tmp = (H != H0 || W != W0) ? b.take<float>(P * s * s * cin * 4) : nullptr;
     w.xa = b.take(P * ldC * E);
     w.xb = b.take(P * ldC * E);
@@ -452,8 +490,13 @@ int SwinIR::stl(const STLW& L, const void* xin, void* xout, int n, int H, int W,
     return 0;
 }
 
-int SwinIR::forward(const float* in, float* out, int n, int H0, int W0, void* wsp, size_t ws_bytes, cudaStream_t s) {
-    IRB_REQUIRE(ws_bytes >= forward_workspace(n, H0, W0), "SwinIR: workspace too small");
+int SwinIR::forward(const float* in, float* out, int n, int Hin, int Win, void* wsp, size_t ws_bytes, cudaStream_t s) {
+    IRB_REQUIRE(ws_bytes >= forward_workspace(n, Hin, Win), "SwinIR: workspace too small");
+    // DiffBIR stage 1: the body runs on the PixelUnshuffle'd input; the reference pads only to the window at full
+    // resolution (:844-849), so inputs that are not multiples of us * window fail there too
+    IRB_REQUIRE(us == 1 || (Hin % (us * desc.window_size) == 0 && Win % (us * desc.window_size) == 0),
+                "SwinIR (unshuffle head): height / width must be multiples of unshuffle_scale * window_size");
+    const int H0 = Hin / us, W0 = Win / us;
     int H, W;
     padded(H0, W0, H, W);
     IRB_REQUIRE(H - H0 < H0 && W - W0 < W0, "SwinIR: image smaller than the reflect padding");
@@ -461,15 +504,32 @@ int SwinIR::forward(const float* in, float* out, int n, int H0, int W0, void* ws
     if (desc.resi_3conv) IRB_REQUIRE(C / 4 <= 64, "SwinIR: 3conv supports embed_dim <= 256");
     Bump b(wsp);
     WS w;
-    layout(b, n, H0, W0, w);
+    layout(b, n, Hin, Win, w);
     const long long P = (long long)n * H * W;
-    const int sc = scale;
+    const int sc = tsc;
+    if (us > 1) {
+        const int co = cin * us * us;
+        void* xu = dt == DT_BF16 ? w.hidden : (void*)w.xin;  // w.hidden is free here (P * hid >= P * co elements)
+        IRB_REQUIRE(dt != DT_BF16 || hid >= co, "SwinIR (unshuffle head): hidden buffer too small for the unshuffled input");
+        if (dt == DT_BF16)
+            swin_prep_unshuffle_kernel<bf16><<<grid_for(P * co), 256, 0, s>>>(in, (bf16*)xu, n, H, W, cin, us, mean[0],
+                                                                              mean[1], mean[2], desc.img_range);
+        else
+            swin_prep_unshuffle_kernel<float><<<grid_for(P * co), 256, 0, s>>>(in, (float*)xu, n, H, W, cin, us, mean[0],
+                                                                               mean[1], mean[2], desc.img_range);
+        IRB_CHECK_CUDA(cudaGetLastError());
+        prof_mark("swin_prep_unshuffle", cin, us, 0.0, double(P) * co * (4.0 + esize()), s);
+        IRB_TRY(conv(conv_first, xu, dt, co, n, H, W, make_epi(w.ffirst, ldC, dt), s));
+    } else {
     // (x - mean) * img_range on the reflect-padded tile (:806-810)
     swin_prep_kernel<<<grid_for(P), 256, 0, s>>>(in, w.xin, n, H0, W0, H, W, cin, mean[0], mean[1], mean[2],
                                                  desc.img_range);
     IRB_CHECK_CUDA(cudaGetLastError());
     prof_mark("swin_prep", cin, 0, 0.0, 8.0 * P * cin, s);
-    if (conv_first.wsplit) {  // :813 / :833 on the tensor core: x = hi + lo in bf16 (w.hidden is free here)
+    }
+    if (us > 1) {
+        // conv_first already ran on the unshuffled input
+    } else if (conv_first.wsplit) {  // :813 / :833 on the tensor core: x = hi + lo in bf16 (w.hidden is free here)
         IRB_TRY(split_hi_lo_bf16(w.xin, cin, (bf16*)w.hidden, P, s));
         Epi e = make_epi(w.ffirst, ldC, dt);
         e.bias = conv_first.b;
@@ -557,11 +617,17 @@ int SwinIR::forward(const float* in, float* out, int n, int H0, int W0, void* ws
         int h = 2 * H, wd = 2 * W;
         void* cur = w.u2;
         void* other = w.u1;
-        if (sc == 4) {
+        if (sc >= 4) {
             IRB_TRY(nearest_up2(w.u2, dt, 64, w.u1, 64, n, h, wd, 64, s));
             h *= 2;
             wd *= 2;
             IRB_TRY(conv(conv_up2, w.u1, dt, 64, n, h, wd, lrelu_epi(w.u2, 0.2f), s));
+        }
+        if (sc == 8) {  // DiffBIR stage 1 (:891)
+            IRB_TRY(nearest_up2(w.u2, dt, 64, w.u1, 64, n, h, wd, 64, s));
+            h *= 2;
+            wd *= 2;
+            IRB_TRY(conv(conv_up3, w.u1, dt, 64, n, h, wd, lrelu_epi(w.u2, 0.2f), s));
         }
         IRB_TRY(conv(conv_hr, cur, dt, 64, n, h, wd, lrelu_epi(other, 0.2f), s));
         IRB_TRY(conv(conv_last, other, dt, 64, n, h, wd, last_epi(), s));

@@ -70,6 +70,7 @@ def swinir_desc(cfg: dict, precision: int) -> ModelDesc:
     d.img_range = cfg["img_range"]
     d.upsampler = _UPSAMPLER[cfg["upsampler"]]
     d.resi_3conv = int(cfg["resi_connection"] == "3conv")
+    d.unshuffle_scale = int(cfg["unshuffle_scale"]) if cfg.get("unshuffle") else 0
     return d
 
 
@@ -95,7 +96,7 @@ class Engine:
         self._h = h
         self.scale = self.lib.irb_scale(h)
         self.channels = desc.in_chans
-        self.strict_tile = True   # False: the Flask service's process_image semantics (ragged SwinIR tiles allowed)
+        self.strict_tile = True   # default of restore_device(strict_tile=None); False = process_image semantics
         self._ws = None
         self._ws_gen = 0          # bumped when the workspace is re-allocated: captured graphs hold its address
         self._graphs: dict = {}
@@ -151,9 +152,9 @@ class Engine:
     __call__ = forward
 
     # ---- the whole tool body for one image ----
-    def _restore_call(self, img, fmt, bgr, h, w, t, tile_overlap, u8, f32):
+    def _restore_call(self, img, fmt, bgr, h, w, t, tile_overlap, u8, f32, strict=None):
         need = C.c_size_t()
-        check(self.lib.irb_set_option(self._h, b"strict_tile", int(self.strict_tile)))
+        check(self.lib.irb_set_option(self._h, b"strict_tile", int(self.strict_tile if strict is None else strict)))
         check(self.lib.irb_restore_workspace_bytes(self._h, h, w, t, tile_overlap, C.byref(need)))
         ws = self._workspace(need.value)
         check(self.lib.irb_restore_image(self._h, img.data_ptr(), fmt, int(bgr), h, w, t, tile_overlap,
@@ -162,7 +163,7 @@ class Engine:
                                          self._stream()))
 
     def restore_device(self, img: torch.Tensor, tile=None, tile_overlap: int = 32, bgr: bool = False,
-                       want_u8: bool = True, want_f32: bool = False, graph: bool = False):
+                       want_u8: bool = True, want_f32: bool = False, graph: bool = False, strict_tile=None):
         """img: CUDA uint8 [H,W,c] or CUDA fp32 planar [c,H,W] in [0,1]. Returns (u8 [sH,sW,c] | None, f32 | None).
 
         graph=True replays a CUDA graph captured once per (image shape, tile, overlap, flags): the ~300-450 kernel
@@ -183,9 +184,10 @@ class Engine:
             if not graph:
                 u8 = torch.empty((h * s, w * s, c), dtype=torch.uint8, device=self.dev) if want_u8 else None
                 f32 = torch.empty((c, h * s, w * s), dtype=torch.float32, device=self.dev) if want_f32 else None
-                self._restore_call(img, fmt, bgr, h, w, t, tile_overlap, u8, f32)
+                self._restore_call(img, fmt, bgr, h, w, t, tile_overlap, u8, f32, strict_tile)
                 return u8, f32
-            key = (fmt, h, w, t, int(tile_overlap), bool(bgr), bool(want_u8), bool(want_f32))
+            key = (fmt, h, w, t, int(tile_overlap), bool(bgr), bool(want_u8), bool(want_f32),
+                   bool(self.strict_tile if strict_tile is None else strict_tile))
             g = self._graphs.get(key)
             if g is None or g["gen"] != self._ws_gen:
                 g = self._capture(key, img)
@@ -194,7 +196,7 @@ class Engine:
             return g["u8"], g["f32"]
 
     def _capture(self, key, img):
-        fmt, h, w, t, ov, bgr, want_u8, want_f32 = key
+        fmt, h, w, t, ov, bgr, want_u8, want_f32, strict = key
         s, c = self.scale, self.channels
         st_in = torch.empty_like(img)
         u8 = torch.empty((h * s, w * s, c), dtype=torch.uint8, device=self.dev) if want_u8 else None
@@ -202,11 +204,11 @@ class Engine:
         st_in.copy_(img)
         # one eager call first: sizes the workspace (which bumps _ws_gen) and performs the per-device
         # cudaFuncSetAttribute opt-ins, neither of which may happen during capture
-        self._restore_call(st_in, fmt, bgr, h, w, t, ov, u8, f32)
+        self._restore_call(st_in, fmt, bgr, h, w, t, ov, u8, f32, strict)
         torch.cuda.current_stream(self.dev).synchronize()
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph):  # the capture stream is the current stream inside this block
-            self._restore_call(st_in, fmt, bgr, h, w, t, ov, u8, f32)
+            self._restore_call(st_in, fmt, bgr, h, w, t, ov, u8, f32, strict)
         g = {"graph": graph, "in": st_in, "u8": u8, "f32": f32, "gen": self._ws_gen}
         self._graphs[key] = g
         return g

@@ -180,7 +180,10 @@ def swinir_state_dict(cfg: dict, seed: int = 0) -> "OrderedDict[str, torch.Tenso
             conv(f"{name}.2", C // 4, C // 4, 1)
             conv(f"{name}.4", C, C // 4)
 
-    conv("conv_first", C, cin)
+    if cfg.get("unshuffle"):  # DiffBIR stage 1: Sequential(PixelUnshuffle(sf), Conv2d(cin * sf^2, C)) -> key conv_first.1
+        conv("conv_first.1", C, cin * cfg["unshuffle_scale"] ** 2)
+    else:
+        conv("conv_first", C, cin)
     norm("patch_embed.norm")
     for r, depth in enumerate(cfg["depths"]):
         nh = cfg["num_heads"][r]
@@ -213,8 +216,10 @@ def swinir_state_dict(cfg: dict, seed: int = 0) -> "OrderedDict[str, torch.Tenso
     elif up == "nearest+conv":
         conv("conv_before_upsample.0", 64, C)
         conv("conv_up1", 64, 64)
-        if cfg["upscale"] == 4:
+        if cfg["upscale"] >= 4:
             conv("conv_up2", 64, 64)
+        if cfg["upscale"] == 8:
+            conv("conv_up3", 64, 64)
         conv("conv_hr", 64, 64)
         conv("conv_last", cin, 64)
     else:

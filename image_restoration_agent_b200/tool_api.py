@@ -305,17 +305,6 @@ class Chain:
             print(f"Time\t: {round(time.time() - start, 3)}s")
 
 
-class _strict_tile:
-    def __init__(self, eng: Engine, value: bool):
-        self.eng, self.value = eng, value
-
-    def __enter__(self):
-        self.prev, self.eng.strict_tile = self.eng.strict_tile, self.value
-
-    def __exit__(self, *exc):
-        self.eng.strict_tile = self.prev
-
-
 def process_image(img_lq: np.ndarray, model: Engine, scale: int, window_size: int, tile=None, tile_overlap=32):
     """Drop-in for model_serving.py:131-175. img_lq: float32 [H, W, 3] BGR in [0,1] (cv2.imread(...)/255) or
     [H, W, 1]; returns uint8 [H*s, W*s, 3] BGR (or [H*s, W*s]). `model` is an irb200 Engine."""
@@ -324,8 +313,8 @@ def process_image(img_lq: np.ndarray, model: Engine, scale: int, window_size: in
     assert model.scale == scale and model.cfg["window_size"] == window_size
     x = np.transpose(img_lq if img_lq.shape[2] == 1 else img_lq[:, :, [2, 1, 0]], (2, 0, 1))
     d = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).to(f"cuda:{model.device}")
-    with _strict_tile(model, False):  # model_serving.py:146-166 has no tile % window_size assert
-        u8, _ = model.restore_device(d, tile, tile_overlap, bgr=(img_lq.shape[2] == 3))
+    # model_serving.py:146-166 has no `tile % window_size` assert (the option is applied under the engine's lock)
+    u8, _ = model.restore_device(d, tile, tile_overlap, bgr=(img_lq.shape[2] == 3), strict_tile=False)
     out = u8.cpu().numpy()
     return out[:, :, 0] if out.shape[2] == 1 else out
 

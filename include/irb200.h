@@ -71,6 +71,10 @@ typedef struct irb_model_desc {
     int spatial_heads[4];
     int spatial_dim_head;
     float overlap_ratio; /* the same for every level in all agent configs */
+    /* SwinIR, DiffBIR stage 1 (DiffBIR/model/swinir.py:716-724): 0 = plain conv_first; s > 1: conv_first =
+     * PixelUnshuffle(s) + conv(in_chans * s^2 -> embed_dim), upscale must equal s (nearest+conv tail, x2 per stage), so
+     * the model's output has the size of its input (irb_scale() = 1) */
+    int unshuffle_scale;
 } irb_model_desc;
 
 const char* irb_last_error(void);

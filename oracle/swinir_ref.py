@@ -135,17 +135,24 @@ def forward(sd, cfg, x):
         x = body(conv(x, "conv_first"))
         x = F.pixel_shuffle(conv(x, "upsample.0"), cfg["upscale"])
     elif up == "nearest+conv":
-        x = body(conv(x, "conv_first"))
+        if cfg.get("unshuffle"):
+            # DiffBIR's stage-1 SwinIR (DiffBIR/model/swinir.py:716-724, :868-893): conv_first = Sequential(
+            # PixelUnshuffle(sf), Conv2d(in_chans * sf^2, C)); the tail up-samples by the same sf (three nearest x2 stages)
+            x = body(conv(F.pixel_unshuffle(x, cfg["unshuffle_scale"]), "conv_first.1"))
+        else:
+            x = body(conv(x, "conv_first"))
         x = F.leaky_relu(conv(x, "conv_before_upsample.0"), 0.01)
         x = F.leaky_relu(conv(F.interpolate(x, scale_factor=2, mode="nearest"), "conv_up1"), 0.2)
-        if cfg["upscale"] == 4:
+        if cfg["upscale"] >= 4:
             x = F.leaky_relu(conv(F.interpolate(x, scale_factor=2, mode="nearest"), "conv_up2"), 0.2)
+        if cfg["upscale"] == 8:
+            x = F.leaky_relu(conv(F.interpolate(x, scale_factor=2, mode="nearest"), "conv_up3"), 0.2)
         x = conv(F.leaky_relu(conv(x, "conv_hr"), 0.2), "conv_last")
     else:
         x_first = conv(x, "conv_first")
         x = x + conv(body(x_first), "conv_last")
     x = x / rng + mean
-    return x[:, :, :H * cfg["upscale"], :W * cfg["upscale"]]
+    return x[:, :, :H * cfg["upscale"], :W * cfg["upscale"]]  # DiffBIR: H * 8 exceeds the tensor, i.e. no crop (:895)
 
 
 class Model:

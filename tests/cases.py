@@ -30,6 +30,10 @@ S_CASES = {
     "swinir_full_color_dn": lambda: configs.swinir_config("color_dn"),
     "swinir_full_classical_x4": lambda: configs.swinir_config("classical_sr", scale=4),
     "swinir_full_realsr_large_x4": lambda: configs.swinir_config("real_sr", scale=4, large_model=True),
+    # DiffBIR's stage-1 SwinIR: PixelUnshuffle(8) head, nearest+conv x8 tail; from the imported
+    # DiffBIR/model/swinir.py (tools/make_golden_full.py diffbir)
+    "diffbir_swinir_small": lambda: configs.small_diffbir_swinir_config(),
+    "diffbir_swinir_full": lambda: configs.diffbir_swinir_config(),
 }
 
 

@@ -236,6 +236,72 @@ def xrestormer_sr():
 
 GROUPS["xrestormer_sr"] = xrestormer_sr
 
+
+# ---------------- DiffBIR stage-1 SwinIR ----------------
+DB = f"{mg.REF}/AgenticIR/executor/super_resolution/tools/DiffBIR"
+
+
+def ref_diffbir_swinir(cfg, sd):
+    """DiffBIR/model/swinir.py's SwinIR, imported from its file with stand-ins for what is absent here and touches no
+    arithmetic: pytorch_lightning (LightningModule -> nn.Module), utils.metrics (LPIPS / PSNR, training-time logging
+    only), the logging mixin, timm's three layer helpers."""
+    import importlib.util
+    mg.install_timm_shim()
+    pl = types.ModuleType("pytorch_lightning")
+    pl.LightningModule = torch.nn.Module
+    plu = types.ModuleType("pytorch_lightning.utilities")
+    plt = types.ModuleType("pytorch_lightning.utilities.types")
+    plt.STEP_OUTPUT = object
+    utils = types.ModuleType("utils")
+    metrics = types.ModuleType("utils.metrics")
+    metrics.calculate_psnr_pt = lambda *a, **k: None
+
+    class LPIPS(torch.nn.Module):
+        def __init__(self, *a, **k):
+            super().__init__()
+
+    metrics.LPIPS = LPIPS
+    pkg = types.ModuleType("model")
+    pkg.__path__ = [f"{DB}/model"]
+    mixins = types.ModuleType("model.mixins")
+
+    class ImageLoggerMixin:
+        pass
+
+    mixins.ImageLoggerMixin = ImageLoggerMixin
+    sys.modules.update({"pytorch_lightning": pl, "pytorch_lightning.utilities": plu,
+                        "pytorch_lightning.utilities.types": plt, "utils": utils, "utils.metrics": metrics,
+                        "model": pkg, "model.mixins": mixins})
+    spec = importlib.util.spec_from_file_location("model.swinir", f"{DB}/model/swinir.py")
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["model.swinir"] = mod
+    spec.loader.exec_module(mod)
+    kw = dict(cfg)
+    kw["sf"] = kw.pop("upscale")
+    kw["patch_size"] = 1
+    m = mod.SwinIR(**kw)
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected, unexpected
+    assert all(k.endswith("relative_position_index") or k.endswith("attn_mask") for k in missing), missing
+    return m.eval()
+
+
+def diffbir():
+    for name, cfg, shape, seed in (("diffbir_swinir_small", configs.small_diffbir_swinir_config(), (1, 3, 64, 128), 1),
+                                   ("diffbir_swinir_full", configs.diffbir_swinir_config(), (1, 3, 128, 128), 0)):
+        print(name)
+        sd = synth.swinir_state_dict(cfg, seed=seed)
+        ref = ref_diffbir_swinir(cfg, sd)
+        x = image_like(512, 512, 3, seed=seed)[..., 64:64 + shape[2], 128:128 + shape[3]].contiguous()
+        with torch.no_grad():
+            y_ref = ref(x)
+        y_or = swinir_ref.Model(sd, cfg)(x)
+        mg.check(name, y_or, y_ref, tol=5e-5)
+        mg.save(name, x=x.numpy(), y=y_ref.numpy(), seed=np.int64(seed))
+
+
+GROUPS["diffbir"] = diffbir
+
 if __name__ == "__main__":
     torch.manual_seed(0)
     torch.set_num_threads(os.cpu_count() or 8)
