@@ -78,6 +78,8 @@ class Engine:
     """One model resident on one GPU. Thread-safe: concurrent Flask requests serialise on a lock
     (the reference shares one model object across threads with no lock, model_serving.py:39,105-128)."""
 
+    MAX_GRAPHS = 8  # captured (shape, tile, overlap, flags) combinations kept per engine, oldest dropped first
+
     def __init__(self, arch: str, cfg: dict, state_dict, precision: str = "bf16", device: int = 0):
         self.lib = _lib.load()
         if not torch.cuda.is_available():
@@ -210,6 +212,8 @@ class Engine:
         with torch.cuda.graph(graph):  # the capture stream is the current stream inside this block
             self._restore_call(st_in, fmt, bgr, h, w, t, ov, u8, f32, strict)
         g = {"graph": graph, "in": st_in, "u8": u8, "f32": f32, "gen": self._ws_gen}
+        while len(self._graphs) >= self.MAX_GRAPHS:  # bounded: every entry pins its static input / output buffers
+            self._graphs.pop(next(iter(self._graphs)))
         self._graphs[key] = g
         return g
 
