@@ -14,7 +14,7 @@ PKG = Path(__file__).resolve().parent
 # IRB_LIB selects another build of the same ABI (the -DIRB_DIAG library of tools/gpu_ab.sh); default = the product
 LIB_PATH = Path(os.environ["IRB_LIB"]).resolve() if os.environ.get("IRB_LIB") else PKG / "libirb200.so"
 
-ARCH_RESTORMER, ARCH_SWINIR, ARCH_XRESTORMER = 1, 2, 3
+ARCH_RESTORMER, ARCH_SWINIR, ARCH_XRESTORMER, ARCH_HAT = 1, 2, 3, 4
 F32, BF16 = 0, 1
 UPSAMPLER_NONE, UPSAMPLER_PIXELSHUFFLE, UPSAMPLER_NEAREST_CONV = 0, 1, 2
 ACT_NONE, ACT_GELU, ACT_LRELU = 0, 1, 2
@@ -30,6 +30,7 @@ class ModelDesc(C.Structure):
         ("img_range", C.c_float), ("upsampler", C.c_int), ("resi_3conv", C.c_int),
         ("spatial_heads", C.c_int * 4), ("spatial_dim_head", C.c_int), ("overlap_ratio", C.c_float),
         ("unshuffle_scale", C.c_int),
+        ("compress_ratio", C.c_int), ("squeeze_factor", C.c_int), ("conv_scale", C.c_float),
     ]
 
 
@@ -61,6 +62,9 @@ PROTOTYPES = {
     "irb_gdfn_dw_gate": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _vp, _vp]),
     "irb_pwdw_fused": (_i, [_i, _vp, _ll, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _vp, _ll, _i, _i, _i, _i, _vp]),
     "irb_mlp_fused": (_i, [_vp, _ll, _ll, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _f, _vp]),
+    "irb_hat_attention": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "irb_restore_crop_workspace_bytes": (_i, [_vp, _i, _i, _i, _i, C.POINTER(_sz)]),
+    "irb_restore_image_crop": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "irb_ocab": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "irb_mdta_nchunks": (_i, [_i, _i, _i]),
     "irb_mdta_gram": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _i, _vp, _vp, _vp]),

@@ -100,6 +100,24 @@ def small_diffbir_swinir_config() -> dict:
     return p
 
 
+def hat_config() -> dict:
+    """HAT (Real_HAT_GAN_SRx4): executor/super_resolution/configs/hat.yml:21-37 (network_g) with the tile settings of
+    :7-9 (tile_size 512, tile_pad 32) under "tile"."""
+    return dict(upscale=4, in_chans=3, img_size=64, window_size=16, compress_ratio=3, squeeze_factor=30, conv_scale=0.01,
+                overlap_ratio=0.5, img_range=1.0, depths=[6] * 6, embed_dim=180, num_heads=[6] * 6, mlp_ratio=2,
+                upsampler="pixelshuffle", resi_connection="1conv")
+
+
+HAT_TILE = dict(tile_size=512, tile_pad=32)  # hat.yml:7-9
+
+
+def small_hat_config(window_size=16, upscale=4) -> dict:
+    """Shallow HAT of the same structure (2 RHAGs x 2 HABs + OCAB, C = 60, 6 heads -> head_dim 10) for CPU-speed tests."""
+    return dict(upscale=upscale, in_chans=3, img_size=64, window_size=window_size, compress_ratio=3, squeeze_factor=30,
+                conv_scale=0.01, overlap_ratio=0.5, img_range=1.0, depths=[2, 2], embed_dim=60, num_heads=[6, 6],
+                mlp_ratio=2, upsampler="pixelshuffle", resi_connection="1conv")
+
+
 def small_restormer_config(ln_type="WithBias", inp_channels=3) -> dict:
     """A shrunken Restormer (same code paths, every level present) for fast parity tests."""
     p = copy.deepcopy(RESTORMER_BASE)

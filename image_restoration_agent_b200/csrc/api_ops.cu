@@ -117,6 +117,10 @@ int irb_padded_size(int arch, int window_size, int h, int w, int* hp, int* wp) {
         const int m = window_size > 0 ? window_size : 64;
         *hp = (h % m) ? (h / m + 1) * m : h;
         *wp = (w % m) ? (w / m + 1) * m : w;
+    } else if (arch == IRB_ARCH_HAT) {
+        IRB_REQUIRE(window_size > 0, "irb_padded_size: window_size");
+        *hp = (h % window_size) ? h + window_size - h % window_size : h;  // hat_model.py:16-26 pre_process
+        *wp = (w % window_size) ? w + window_size - w % window_size : w;
     } else {
         set_error("irb_padded_size: unknown arch");
         return 1;

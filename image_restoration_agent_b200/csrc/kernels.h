@@ -63,6 +63,17 @@ int mlp_fused_bf16(bf16* x, long long ldx, long long P, int C, int hid, const fl
 int ocab_attention(const void* qkv, int dt, long long ld, void* out, long long ldo, int Nimg, int H, int W, int heads,
                    int dim_head, int ws, int ows, const float* rel_h, const float* rel_w, cudaStream_t stream);
 
+// ---- hat.cu : HAT's window-16 self-attention / overlapping cross-attention and CAB channel attention ----
+// ows == ws: (shifted-)window self-attention; ows > ws: OCAB (keys from the zero-padded ows x ows window, no shift)
+int hat_attention(const void* qkv, int dt, long long ld, void* out, long long ldo, int n, int H, int W, int heads, int d,
+                  int dstride, int ws, int ows, int shift, const float* table, cudaStream_t stream);
+int channel_attention_slabs(int n, long long hw);
+int channel_attention_scale(const void* y, int dt, long long ldy, int n, long long hw, int C, int Cs, const float* w1,
+                            const float* b1, const float* w2, const float* b2, float out_scale, float* sums,
+                            float* scale, cudaStream_t stream);
+int add_scaled(const void* x, long long ldx, const void* y, long long ldy, void* out, long long ldo, int dt, long long rows,
+               long long hw, int C, const float* scale, cudaStream_t stream);
+
 // ---- pwdw_fused.cu : 1x1 convolution (folded LayerNorm) -> depthwise 3x3 [-> GELU gate] without the HBM round trip ----
 bool pwdw_fused_shape_ok(int C, int nrows, bool gate, int hp);
 int pwdw_fused_bf16(bool gate, const bf16* x, long long ldx, const float2* stats, const bf16* w1, int nrows, int hp,
@@ -105,6 +116,9 @@ int tiles_stitch_rows(const float* tiles, int c, int th, int tw, int sf, const i
 int tiles_stitch(const float* tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx, int h,
                  int w, int crop_h, int crop_w, float* out_f32 /*[c][crop_h][crop_w] or null*/,
                  uint8_t* out_u8 /*[crop_h][crop_w][c] or null*/, int u8_reverse_channels, cudaStream_t stream);
+// crop-with-pad tiling (HAT): paste the [ph][pw] rectangle at (oy, ox) of a channels-last tile to (Y0, X0) of the outputs
+int tile_paste(const float* tile, int c, int TH, int TW, int oy, int ox, int ph, int pw, int Y0, int X0, int out_h,
+               int out_w, float* out_f32, uint8_t* out_u8, int u8_reverse_channels, cudaStream_t stream);
 // uint8 HWC (optionally BGR) -> planar float [c][h'][w'] in [0,1] with the reference's padding rule.
 // pad_mode 0: reflect (Restormer / F.pad 'reflect'), 1: symmetric flip-and-concat (SwinIR scripts).
 int image_prepare(const uint8_t* src, int h, int w, int c, int reverse_channels, float* dst, int hp, int wp,

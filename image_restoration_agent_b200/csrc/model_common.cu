@@ -309,7 +309,7 @@ int irb_create(const irb_model_desc* desc, const void* weights_blob, size_t nbyt
     int rc;
     if (desc->arch == IRB_ARCH_RESTORMER || desc->arch == IRB_ARCH_XRESTORMER)
         rc = build_restormer(*desc, blob, device, &m);
-    else if (desc->arch == IRB_ARCH_SWINIR)
+    else if (desc->arch == IRB_ARCH_SWINIR || desc->arch == IRB_ARCH_HAT)
         rc = build_swinir(*desc, blob, device, &m);
     else {
         set_error("irb_create: unknown arch");
@@ -427,6 +427,86 @@ int irb_restore_image(irb_handle* h, const void* d_in, int in_fmt, int reverse_c
     }
     IRB_TRY(tiles_stitch(P.tiles_out, P.c, P.th, P.tw, P.sf, P.ys, P.xs, P.ny, P.nx, P.hp, P.wp, img_h * P.sf,
                          img_w * P.sf, d_out_f32, d_out_u8, reverse_channels, s));
+    return 0;
+}
+
+// ---- HATModel's tile mode (hat_model.py:16-109): crop-with-pad tiles, no blending -------------------------------
+struct CropPlan {
+    int hp, wp, ny, nx, ts, tp, mth, mtw, sf, c;
+    float *padded, *tile_in, *tile_out;
+    void* model_ws;
+    size_t model_ws_bytes, total;
+};
+static int make_crop_plan(Model* m, int img_h, int img_w, int tile_size, int tile_pad, void* ws, CropPlan& P) {
+    IRB_REQUIRE(img_h > 0 && img_w > 0, "restore: empty image");
+    IRB_TRY(irb_padded_size(m->desc.arch, m->desc.arch == IRB_ARCH_XRESTORMER ? m->tile_multiple() : m->desc.window_size,
+                            img_h, img_w, &P.hp, &P.wp));
+    P.sf = m->scale;
+    P.c = m->cin;
+    if (tile_size <= 0) {  // HATModel.process: the whole padded image
+        P.ts = P.hp > P.wp ? P.hp : P.wp;
+        P.tp = 0;
+    } else {
+        // hat.yml:7-9: both must be integer multiples of the window size (the network does not pad)
+        IRB_REQUIRE(tile_size % m->tile_multiple() == 0 && tile_pad >= 0 && tile_pad % m->tile_multiple() == 0,
+                    "tile_size and tile_pad must be integer multiples of the window size");
+        P.ts = tile_size;
+        P.tp = tile_pad;
+    }
+    P.ny = (P.hp + P.ts - 1) / P.ts;
+    P.nx = (P.wp + P.ts - 1) / P.ts;
+    P.mth = P.ts + 2 * P.tp < P.hp ? P.ts + 2 * P.tp : P.hp;
+    P.mtw = P.ts + 2 * P.tp < P.wp ? P.ts + 2 * P.tp : P.wp;
+    Bump b(ws);
+    P.padded = b.take<float>(size_t(P.c) * P.hp * P.wp * 4);
+    P.tile_in = b.take<float>(size_t(P.mth) * P.mtw * P.c * 4);
+    P.tile_out = b.take<float>(size_t(P.mth) * P.mtw * P.sf * P.sf * P.c * 4);
+    P.model_ws_bytes = m->forward_workspace(1, P.mth, P.mtw);
+    P.model_ws = b.take<void>(P.model_ws_bytes);
+    P.total = b.off + 256;
+    return 0;
+}
+
+int irb_restore_crop_workspace_bytes(irb_handle* h, int img_h, int img_w, int tile_size, int tile_pad, size_t* out_bytes) {
+    IRB_REQUIRE(h && out_bytes, "irb_restore_crop_workspace_bytes: NULL argument");
+    CropPlan P;
+    IRB_TRY(make_crop_plan(h->model, img_h, img_w, tile_size, tile_pad, nullptr, P));
+    *out_bytes = P.total;
+    return 0;
+}
+
+int irb_restore_image_crop(irb_handle* h, const void* d_in, int in_fmt, int reverse_channels, int img_h, int img_w,
+                           int tile_size, int tile_pad, uint8_t* d_out_u8, float* d_out_f32, void* d_workspace,
+                           size_t workspace_bytes, void* stream) {
+    IRB_REQUIRE(h && d_in && d_workspace, "irb_restore_image_crop: NULL argument");
+    IRB_REQUIRE(d_out_u8 || d_out_f32, "irb_restore_image_crop: no output requested");
+    IRB_REQUIRE(in_fmt == 0 || in_fmt == 1, "irb_restore_image_crop: in_fmt must be 0 (u8 HWC) or 1 (f32 planar)");
+    Model* m = h->model;
+    IRB_ON_DEVICE(m);
+    CropPlan P;
+    IRB_TRY(make_crop_plan(m, img_h, img_w, tile_size, tile_pad, d_workspace, P));
+    IRB_REQUIRE(workspace_bytes >= P.total, "irb_restore_image_crop: workspace too small");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int pad_mode = m->desc.arch == IRB_ARCH_SWINIR ? 1 : 0;
+    if (in_fmt == 0)
+        IRB_TRY(image_prepare(reinterpret_cast<const uint8_t*>(d_in), img_h, img_w, P.c, reverse_channels, P.padded,
+                              P.hp, P.wp, pad_mode, s));
+    else
+        IRB_TRY(image_pad_f32(reinterpret_cast<const float*>(d_in), P.c, img_h, img_w, P.padded, P.hp, P.wp, pad_mode, s));
+    const int sf = P.sf;
+    for (int ty = 0; ty < P.ny; ++ty)
+        for (int tx = 0; tx < P.nx; ++tx) {
+            const int y0 = ty * P.ts, x0 = tx * P.ts;
+            const int y1 = y0 + P.ts < P.hp ? y0 + P.ts : P.hp, x1 = x0 + P.ts < P.wp ? x0 + P.ts : P.wp;
+            const int y0p = y0 - P.tp > 0 ? y0 - P.tp : 0, x0p = x0 - P.tp > 0 ? x0 - P.tp : 0;
+            const int y1p = y1 + P.tp < P.hp ? y1 + P.tp : P.hp, x1p = x1 + P.tp < P.wp ? x1 + P.tp : P.wp;
+            const int th = y1p - y0p, tw = x1p - x0p;
+            IRB_TRY(tiles_gather(P.padded, P.c, P.hp, P.wp, &y0p, &x0p, 1, 1, th, tw, P.tile_in, nullptr, 1.0f, s));
+            IRB_TRY(m->forward(P.tile_in, P.tile_out, 1, th, tw, P.model_ws, P.model_ws_bytes, s));
+            IRB_TRY(tile_paste(P.tile_out, P.c, th * sf, tw * sf, (y0 - y0p) * sf, (x0 - x0p) * sf, (y1 - y0) * sf,
+                               (x1 - x0) * sf, y0 * sf, x0 * sf, img_h * sf, img_w * sf, d_out_f32, d_out_u8,
+                               reverse_channels, s));
+        }
     return 0;
 }
 

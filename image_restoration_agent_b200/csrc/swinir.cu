@@ -49,6 +49,9 @@ struct STLW {
     float *n1w, *n1b, *n2w, *n2b, *bias_table;
     LinW qkv, proj, fc1, fc2;
     int shift, heads;
+    // HAT only (hat_arch.py:61-74 CAB): conv3x3 C -> C/r, GELU, conv3x3 C/r -> C, channel attention (two 1x1 convolutions)
+    Conv3W cab0, cab2;
+    float *ca_w1, *ca_b1, *ca_w2, *ca_b2;
 };
 
 // reflect pad (network_swinir.py:783-788) + (x - mean) * img_range (:809-810) on channels-last fp32
@@ -112,6 +115,9 @@ static int grid_for(long long total) {
 
 struct SwinIR : Model {
     int C, ldC, ws, ws_eff, can_shift, hid, dp, Cq;
+    bool hat = false;  // HAT (hat_arch.py): HAB = STL + CAB branch, one OCAB per residual group, windows up to 16
+    int ows = 0, c_cab = 0, ld_cab = 0, c_sq = 0;  // HAT: overlapping window, C / compress_ratio (+ row stride), C / squeeze_factor
+    std::vector<STLW> ocab;                         // HAT: layers[r].residual_group.overlap_attn
     int us = 1;   // PixelUnshuffle factor of conv_first (DiffBIR stage 1: 8), 1 = none
     int tsc = 1;  // scale of the reconstruction tail (desc.upscale); the model's in -> out scale is tsc / us
     Conv3W conv_up3;
@@ -123,7 +129,7 @@ struct SwinIR : Model {
     std::vector<ResiW> layer_conv;
     ResiW conv_after_body;
 
-    int tile_multiple() const override { return desc.window_size * us; }
+    int tile_multiple() const override { return desc.window_size * us; }  // HAT: the network does not pad
     size_t forward_workspace(int n, int H, int W) override;
     int forward(const float* in, float* out, int n, int H, int W, void* ws, size_t ws_bytes,
                 cudaStream_t stream) override;
@@ -131,6 +137,8 @@ struct SwinIR : Model {
     struct WS {
         float *xin, *out_tmp;
         void *xa, *xb, *ffirst, *ln, *qkv, *attn, *hidden, *q4a, *q4b, *t64, *u1, *u2, *u3;
+        void *cab1, *cab;          // HAT: the two CAB convolution outputs
+        float *ca_sums, *ca_scale; // HAT: per-slab channel sums, per-image channel scale
         float2* stats;
         bool stats_valid;  // stats already describe the stream the next block normalises (written by the producing GEMM)
     };
@@ -149,6 +157,11 @@ struct SwinIR : Model {
     int conv(const Conv3W& c, const void* x, int x_dt, long long ldx, int n, int H, int W, Epi e, cudaStream_t s);
     int resi(const ResiW& r, const void* x, long long ldx, int n, int H, int W, Epi e, WS& w, cudaStream_t s);
     int stl(const STLW& L, const void* xin, void* xout, int n, int H, int W, WS& w, cudaStream_t s);
+    int mlp(const STLW& L, void* x, long long P, WS& w, cudaStream_t s);
+    int hab(const STLW& L, const void* xin, void* xout, int n, int H, int W, WS& w, cudaStream_t s);
+    int ocab_block(const STLW& L, void* x, int n, int H, int W, WS& w, cudaStream_t s);
+    int load_block(const Blob& blob, const std::string& p, const std::string& attn, int heads, int table_rows, bool fold1,
+                   STLW& L);
 };
 
 int SwinIR::load_norm(const Blob& blob, const std::string& name, float** w, float** b) {
@@ -203,7 +216,7 @@ int SwinIR::load_qkv(const Blob& blob, const std::string& name, int heads, LinW&
                 b[dst] = tb.data[src] * s;
             }
     o.cs = nullptr;
-    if (dt == DT_BF16) {
+    if (dt == DT_BF16 && !fold_norm.empty()) {
         BlobTensor g, lb;
         IRB_TRY(blob.get(fold_norm + ".weight", g, C));
         IRB_TRY(blob.get(fold_norm + ".bias", lb, C));
@@ -256,6 +269,23 @@ int SwinIR::load_resi(const Blob& blob, const std::string& name, ResiW& o) {
     return 0;
 }
 
+// norm1, attention (qkv / bias table / proj under `attn`), norm2, mlp of one block. fold1: LayerNorm 1 folded into the
+// qkv GEMM (SwinIR, bf16); HAT materialises norm1(x) because its convolution branch reads it too.
+int SwinIR::load_block(const Blob& blob, const std::string& p, const std::string& attn, int heads, int table_rows,
+                       bool fold1, STLW& L) {
+    L.heads = heads;
+    IRB_TRY(load_norm(blob, p + ".norm1", &L.n1w, &L.n1b));
+    IRB_TRY(load_norm(blob, p + ".norm2", &L.n2w, &L.n2b));
+    BlobTensor t;
+    IRB_TRY(blob.get(attn + "relative_position_bias_table", t, table_rows, heads));
+    IRB_TRY(upload_f32(t.data, size_t(table_rows) * heads, &L.bias_table));
+    IRB_TRY(load_qkv(blob, attn + "qkv", heads, L.qkv, fold1 ? p + ".norm1" : std::string()));
+    IRB_TRY(load_lin(blob, attn + "proj", C, C, L.proj));
+    IRB_TRY(load_lin(blob, p + ".mlp.fc1", hid, C, L.fc1, p + ".norm2"));
+    IRB_TRY(load_lin(blob, p + ".mlp.fc2", C, hid, L.fc2));
+    return 0;
+}
+
 int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** out) {
     SwinIR* m = new SwinIR();
     *out = m;
@@ -271,7 +301,22 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
     m->scale = d.upscale / m->us;
     IRB_REQUIRE(d.in_chans == 1 || d.in_chans == 3, "SwinIR: in_chans must be 1 or 3");
     IRB_REQUIRE(d.embed_dim > 0 && d.embed_dim % 4 == 0 && d.embed_dim <= 512, "SwinIR: embed_dim must be %4, <= 512");
-    IRB_REQUIRE(d.window_size >= 1 && d.window_size <= 8, "SwinIR: window_size must be <= 8");
+    m->hat = d.arch == IRB_ARCH_HAT;
+    if (m->hat) {
+        IRB_REQUIRE(d.window_size >= 2 && d.window_size <= 16 && d.window_size % 2 == 0, "HAT: window_size must be even, <= 16");
+        IRB_REQUIRE(d.img_size > d.window_size, "HAT: img_size must exceed window_size");
+        IRB_REQUIRE(d.upsampler == IRB_UPSAMPLER_PIXELSHUFFLE && !d.resi_3conv && m->us == 1,
+                    "HAT: only upsampler 'pixelshuffle' with resi_connection '1conv' (hat.yml)");
+        IRB_REQUIRE(d.compress_ratio >= 1 && d.squeeze_factor >= 1 && d.embed_dim / d.compress_ratio >= 1 &&
+                        d.embed_dim / d.squeeze_factor >= 1, "HAT: bad compress_ratio / squeeze_factor");
+        m->ows = int(d.window_size * d.overlap_ratio) + d.window_size;  // hat_arch.py:373
+        IRB_REQUIRE((m->ows - d.window_size) % 2 == 0 && m->ows <= 64, "HAT: bad overlap_ratio");
+        m->c_cab = d.embed_dim / d.compress_ratio;
+        m->ld_cab = (m->c_cab + 15) / 16 * 16;
+        m->c_sq = d.embed_dim / d.squeeze_factor;
+    } else {
+        IRB_REQUIRE(d.window_size >= 1 && d.window_size <= 8, "SwinIR: window_size must be <= 8");
+    }
     IRB_REQUIRE(d.num_layers >= 1 && d.num_layers <= 16, "SwinIR: 1..16 RSTB layers");
     IRB_REQUIRE(d.upscale >= 1 && (d.upscale & (d.upscale - 1)) == 0, "SwinIR: upscale must be a power of two");
     IRB_REQUIRE(d.upsampler == IRB_UPSAMPLER_NONE || d.upscale > 1 || d.upsampler == IRB_UPSAMPLER_PIXELSHUFFLE ||
@@ -312,18 +357,29 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
         for (int b = 0; b < d.depths[r]; ++b) {
             STLW& L = m->layers[r][b];
             const std::string p = "layers." + std::to_string(r) + ".residual_group.blocks." + std::to_string(b);
-            L.heads = d.num_heads[r];
-            L.shift = (b % 2 == 1 && m->can_shift) ? m->ws / 2 : 0;  // :383
-            IRB_TRY(m->load_norm(blob, p + ".norm1", &L.n1w, &L.n1b));
-            IRB_TRY(m->load_norm(blob, p + ".norm2", &L.n2w, &L.n2b));
-            BlobTensor t;
+            L.shift = (b % 2 == 1 && m->can_shift) ? m->ws / 2 : 0;  // :383 (hat_arch.py:495)
             const int nb = (2 * m->ws_eff - 1) * (2 * m->ws_eff - 1);
-            IRB_TRY(blob.get(p + ".attn.relative_position_bias_table", t, nb, L.heads));
-            IRB_TRY(m->upload_f32(t.data, size_t(nb) * L.heads, &L.bias_table));
-            IRB_TRY(m->load_qkv(blob, p + ".attn.qkv", L.heads, L.qkv, p + ".norm1"));
-            IRB_TRY(m->load_lin(blob, p + ".attn.proj", C, C, L.proj));
-            IRB_TRY(m->load_lin(blob, p + ".mlp.fc1", m->hid, C, L.fc1, p + ".norm2"));
-            IRB_TRY(m->load_lin(blob, p + ".mlp.fc2", C, m->hid, L.fc2));
+            IRB_TRY(m->load_block(blob, p, p + ".attn.", d.num_heads[r], nb, !m->hat, L));
+            if (m->hat) {  // conv_block = CAB (hat_arch.py:61-74)
+                IRB_TRY(m->load_conv(blob, p + ".conv_block.cab.0", m->c_cab, C, L.cab0));
+                IRB_TRY(m->load_conv(blob, p + ".conv_block.cab.2", C, m->c_cab, L.cab2));
+                BlobTensor t;
+                IRB_TRY(blob.get(p + ".conv_block.cab.3.attention.1.weight", t, m->c_sq, C, 1, 1));
+                IRB_TRY(m->upload_f32(t.data, size_t(m->c_sq) * C, &L.ca_w1));
+                IRB_TRY(blob.get(p + ".conv_block.cab.3.attention.1.bias", t, m->c_sq));
+                IRB_TRY(m->upload_f32(t.data, m->c_sq, &L.ca_b1));
+                IRB_TRY(blob.get(p + ".conv_block.cab.3.attention.3.weight", t, C, m->c_sq, 1, 1));
+                IRB_TRY(m->upload_f32(t.data, size_t(C) * m->c_sq, &L.ca_w2));
+                IRB_TRY(blob.get(p + ".conv_block.cab.3.attention.3.bias", t, C));
+                IRB_TRY(m->upload_f32(t.data, C, &L.ca_b2));
+            }
+        }
+        if (m->hat) {  // overlap_attn = OCAB (hat_arch.py:352-438); table (ws + ows - 1)^2 x heads
+            if (m->ocab.empty()) m->ocab.resize(d.num_layers);
+            const std::string p = "layers." + std::to_string(r) + ".residual_group.overlap_attn";
+            const int nb = (m->ws + m->ows - 1) * (m->ws + m->ows - 1);
+            m->ocab[r].shift = 0;
+            IRB_TRY(m->load_block(blob, p, p + ".", d.num_heads[r], nb, false, m->ocab[r]));
         }
         IRB_TRY(m->load_resi(blob, "layers." + std::to_string(r) + ".conv", m->layer_conv[r]));
     }
@@ -367,6 +423,14 @@ void SwinIR::layout(Bump& b, int n, int Hin, int Win, WS& w) {
     w.qkv = b.take(P * 3 * Cq * E);
     w.attn = b.take(P * ldC * E);
     w.hidden = b.take(P * hid * E);
+    w.cab1 = w.cab = nullptr;
+    w.ca_sums = w.ca_scale = nullptr;
+    if (hat) {
+        w.cab1 = b.take(P * ld_cab * E);
+        w.cab = b.take(P * ldC * E);
+        w.ca_sums = b.take<float>(size_t(n) * channel_attention_slabs(n, (long long)H * W) * C * 4);
+        w.ca_scale = b.take<float>(size_t(n) * C * 4);
+    }
     w.q4a = w.q4b = nullptr;
     if (desc.resi_3conv) {
         w.q4a = b.take(P * 64 * E);
@@ -451,6 +515,11 @@ int SwinIR::stl(const STLW& L, const void* xin, void* xout, int n, int H, int W,
         }
         IRB_TRY(gemm(w.attn, ldC, P, L.proj, e, s));
     }
+    return mlp(L, xout, P, w, s);
+}
+
+// x += mlp(norm2(x)) (:276 / hat_arch.py:307, :437); norm2's statistics are in w.stats when w.stats_valid
+int SwinIR::mlp(const STLW& L, void* xout, long long P, WS& w, cudaStream_t s) {
     if (dt == DT_BF16 && fuse_mlp && mlp_fused_shape_ok(C, hid)) {
         // fc1 -> GELU -> fc2 -> + x in one kernel (mlp_fused.cu): the hidden tensor stays on the SM; the kernel also
         // writes the next block's norm1 statistics (it reads norm2's from w.stats and overwrites them row by row)
@@ -490,6 +559,61 @@ int SwinIR::stl(const STLW& L, const void* xin, void* xout, int n, int H, int W,
     return 0;
 }
 
+// HAB.forward (hat_arch.py:266-309): x = shortcut + attn(norm1(x)) + conv_scale * CAB(norm1(x)); x += mlp(norm2(x)).
+// norm1(x) is materialised (w.ln) because two consumers read it; the channel-attention scale and conv_scale are
+// applied when the convolution branch is added to the shortcut, before the projection GEMM adds the attention branch.
+int SwinIR::hab(const STLW& L, const void* xin, void* xout, int n, int H, int W, WS& w, cudaStream_t s) {
+    const long long P = (long long)n * H * W;
+    IRB_TRY(layernorm(xin, dt, ldC, w.ln, dt, ldC, P, C, L.n1w, L.n1b, 0, 1e-5f, s));
+    IRB_TRY(gemm(w.ln, ldC, P, L.qkv, make_epi(w.qkv, 3 * Cq, dt), s));
+    IRB_TRY(hat_attention(w.qkv, dt, 3 * Cq, w.attn, ldC, n, H, W, L.heads, C / L.heads, dp, ws, ws, L.shift, L.bias_table, s));
+    {
+        Epi e = make_epi(w.cab1, ld_cab, dt);
+        e.act = ACT_GELU;
+        IRB_TRY(conv(L.cab0, w.ln, dt, ldC, n, H, W, e, s));
+        IRB_TRY(conv(L.cab2, w.cab1, dt, ld_cab, n, H, W, make_epi(w.cab, ldC, dt), s));
+    }
+    IRB_TRY(channel_attention_scale(w.cab, dt, ldC, n, (long long)H * W, C, c_sq, L.ca_w1, L.ca_b1, L.ca_w2, L.ca_b2,
+                                    desc.conv_scale, w.ca_sums, w.ca_scale, s));
+    IRB_TRY(add_scaled(xin, ldC, w.cab, ldC, xout, ldC, dt, P, (long long)H * W, C, w.ca_scale, s));
+    {
+        Epi e = make_epi(xout, ldC, dt);
+        e.res = xout;
+        e.ldr = ldC;
+        e.res_dt = dt;
+        w.stats_valid = false;
+        if (dt == DT_BF16 && tc_can_fuse_stats(C, e)) {
+            e.stats_out = w.stats;
+            e.stats_eps = 1e-5f;
+            w.stats_valid = true;
+        }
+        IRB_TRY(gemm(w.attn, ldC, P, L.proj, e, s));
+    }
+    return mlp(L, xout, P, w, s);
+}
+
+// OCAB.forward (hat_arch.py:392-438), in place on x
+int SwinIR::ocab_block(const STLW& L, void* x, int n, int H, int W, WS& w, cudaStream_t s) {
+    const long long P = (long long)n * H * W;
+    IRB_TRY(layernorm(x, dt, ldC, w.ln, dt, ldC, P, C, L.n1w, L.n1b, 0, 1e-5f, s));
+    IRB_TRY(gemm(w.ln, ldC, P, L.qkv, make_epi(w.qkv, 3 * Cq, dt), s));
+    IRB_TRY(hat_attention(w.qkv, dt, 3 * Cq, w.attn, ldC, n, H, W, L.heads, C / L.heads, dp, ws, ows, 0, L.bias_table, s));
+    {
+        Epi e = make_epi(x, ldC, dt);
+        e.res = x;
+        e.ldr = ldC;
+        e.res_dt = dt;
+        w.stats_valid = false;
+        if (dt == DT_BF16 && tc_can_fuse_stats(C, e)) {
+            e.stats_out = w.stats;
+            e.stats_eps = 1e-5f;
+            w.stats_valid = true;
+        }
+        IRB_TRY(gemm(w.attn, ldC, P, L.proj, e, s));
+    }
+    return mlp(L, x, P, w, s);
+}
+
 int SwinIR::forward(const float* in, float* out, int n, int Hin, int Win, void* wsp, size_t ws_bytes, cudaStream_t s) {
     IRB_REQUIRE(ws_bytes >= forward_workspace(n, Hin, Win), "SwinIR: workspace too small");
     // DiffBIR stage 1: the body runs on the PixelUnshuffle'd input; the reference pads only to the window at full
@@ -499,6 +623,7 @@ int SwinIR::forward(const float* in, float* out, int n, int Hin, int Win, void* 
     const int H0 = Hin / us, W0 = Win / us;
     int H, W;
     padded(H0, W0, H, W);
+    IRB_REQUIRE(!hat || (H == H0 && W == W0), "HAT: height / width must be multiples of window_size (HATModel.pre_process pads)");
     IRB_REQUIRE(H - H0 < H0 && W - W0 < W0, "SwinIR: image smaller than the reflect padding");
     IRB_REQUIRE(H % ws_eff == 0 && W % ws_eff == 0, "SwinIR: padded size must be a multiple of the window");
     if (desc.resi_3conv) IRB_REQUIRE(C / 4 <= 64, "SwinIR: 3conv supports embed_dim <= 256");
@@ -545,9 +670,10 @@ int SwinIR::forward(const float* in, float* out, int n, int Hin, int Win, void* 
         // RSTB (:481-482): xa = conv(blocks(xa)) + xa ; the blocks run in xb
         const void* src = w.xa;
         for (auto& L : layers[r]) {
-            IRB_TRY(stl(L, src, w.xb, n, H, W, w, s));
+            IRB_TRY(hat ? hab(L, src, w.xb, n, H, W, w, s) : stl(L, src, w.xb, n, H, W, w, s));
             src = w.xb;
         }
+        if (hat) IRB_TRY(ocab_block(ocab[r], w.xb, n, H, W, w, s));  // AttenBlocks.forward, hat_arch.py:526-534
         Epi e = make_epi(w.xa, ldC, dt);
         e.res = w.xa;
         e.ldr = ldC;

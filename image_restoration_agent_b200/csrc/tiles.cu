@@ -174,6 +174,46 @@ int tiles_stitch_rows(const float* tiles, int c, int th, int tw, int sf, const i
     return 0;
 }
 
+// HATModel.tile_process, hat_model.py:92-105: the tile's own area (its output minus the tile_pad border) replaces the
+// output rectangle; no blending. tile: channels-last [TH][TW][c]; the rectangle [ph][pw] read at (oy, ox) of the tile is
+// written at (Y0, X0) of the outputs out_f32 [c][out_h][out_w] / out_u8 [out_h][out_w][c], clipped to them
+// (post_process :107-109 crops the window padding).
+__global__ void tile_paste_kernel(const float* __restrict__ tile, int c, int TW, int oy, int ox, int ph, int pw, int Y0,
+                                  int X0, int out_h, int out_w, float* __restrict__ out_f32,
+                                  uint8_t* __restrict__ out_u8, int rev) {
+    const long long total = (long long)ph * pw;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int y = int(i / pw), x = int(i % pw);
+        const float* t = tile + ((long long)(oy + y) * TW + ox + x) * c;
+        const long long o = (long long)(Y0 + y) * out_w + X0 + x;
+        for (int ch = 0; ch < c; ++ch) {
+            const float v = t[ch];
+            if (out_f32) out_f32[(long long)ch * out_h * out_w + o] = v;
+            if (out_u8) {
+                const float cl = fminf(fmaxf(v, 0.f), 1.f);
+                out_u8[o * c + (rev ? (c - 1 - ch) : ch)] = (uint8_t)rintf(cl * 255.0f);
+            }
+        }
+    }
+}
+
+int tile_paste(const float* tile, int c, int TH, int TW, int oy, int ox, int ph, int pw, int Y0, int X0, int out_h,
+               int out_w, float* out_f32, uint8_t* out_u8, int u8_reverse_channels, cudaStream_t stream) {
+    IRB_REQUIRE(c >= 1 && c <= 3, "tile_paste: 1..3 channels");
+    IRB_REQUIRE(oy >= 0 && ox >= 0 && oy + ph <= TH && ox + pw <= TW, "tile_paste: rectangle outside the tile");
+    if (Y0 + ph > out_h) ph = out_h - Y0;
+    if (X0 + pw > out_w) pw = out_w - X0;
+    if (ph <= 0 || pw <= 0) return 0;  // the rectangle lies entirely in the cropped padding
+    const long long total = (long long)ph * pw;
+    const int blocks = int(ceil_div_ll(total, 256) > 148 * 16 ? 148 * 16 : ceil_div_ll(total, 256));
+    tile_paste_kernel<<<blocks, 256, 0, stream>>>(tile, c, TW, oy, ox, ph, pw, Y0, X0, out_h, out_w, out_f32, out_u8,
+                                                  u8_reverse_channels);
+    IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("tile_paste", c, 0, 0.0, double(total) * c * (4 + (out_f32 ? 4 : 0) + (out_u8 ? 1 : 0)), stream);
+    return 0;
+}
+
 int tiles_stitch(const float* tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx, int h,
                  int w, int crop_h, int crop_w, float* out_f32, uint8_t* out_u8, int u8_reverse_channels,
                  cudaStream_t stream) {

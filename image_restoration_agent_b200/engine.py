@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import ARCH_RESTORMER, ARCH_SWINIR, ARCH_XRESTORMER, BF16, F32, ModelDesc, check
+from ._lib import ARCH_HAT, ARCH_RESTORMER, ARCH_SWINIR, ARCH_XRESTORMER, BF16, F32, ModelDesc, check
 from .weights import state_dict_to_blob
 
 _UPSAMPLER = {"": 0, None: 0, "pixelshuffle": 1, "nearest+conv": 2}
@@ -74,6 +74,18 @@ def swinir_desc(cfg: dict, precision: int) -> ModelDesc:
     return d
 
 
+def hat_desc(cfg: dict, precision: int) -> ModelDesc:
+    """HAT(...) of hat_arch.py:738-766 with executor/super_resolution/configs/hat.yml:21-37."""
+    if cfg["upsampler"] != "pixelshuffle" or cfg["resi_connection"] != "1conv":
+        raise ValueError("irb200 serves HAT with upsampler 'pixelshuffle' and resi_connection '1conv' (hat.yml)")
+    d = swinir_desc(cfg, precision)
+    d.arch = ARCH_HAT
+    d.overlap_ratio = float(cfg["overlap_ratio"])
+    d.compress_ratio, d.squeeze_factor = int(cfg["compress_ratio"]), int(cfg["squeeze_factor"])
+    d.conv_scale = float(cfg["conv_scale"])
+    return d
+
+
 class Engine:
     """One model resident on one GPU. Thread-safe: concurrent Flask requests serialise on a lock
     (the reference shares one model object across threads with no lock, model_serving.py:39,105-128)."""
@@ -88,7 +100,8 @@ class Engine:
         self.dev = torch.device("cuda", self.device)
         prec = {"bf16": BF16, "fp32": F32, "f32": F32}[precision]
         self.precision = precision
-        desc = {"restormer": restormer_desc, "swinir": swinir_desc, "xrestormer": xrestormer_desc}[arch](cfg, prec)
+        desc = {"restormer": restormer_desc, "swinir": swinir_desc, "xrestormer": xrestormer_desc,
+                "hat": hat_desc}[arch](cfg, prec)
         blob = state_dict_to_blob(state_dict)
         h = C.c_void_p()
         # irb_create uploads on `device` and restores the caller's current device; the calling thread's device is
@@ -196,6 +209,39 @@ class Engine:
             g["in"].copy_(img, non_blocking=True)
             g["graph"].replay()
             return g["u8"], g["f32"]
+
+    def restore_crop_device(self, img: torch.Tensor, tile_size=None, tile_pad: int = 32, bgr: bool = False,
+                            want_u8: bool = True, want_f32: bool = False):
+        """HATModel's tool body (hat_model.py:16-109): window padding, crop-with-pad tiles (tile_size None = the whole
+        image), each tile's own area pasted without blending, crop. Tensors as in restore_device."""
+        if img.dtype == torch.uint8:
+            h, w, c = img.shape
+            fmt = 0
+        else:
+            c, h, w = img.shape
+            fmt = 1
+        assert c == self.channels, f"model has {self.channels} channel(s), image has {c}"
+        self._on_device(img)
+        img = img.contiguous()
+        s = self.scale
+        t = 0 if tile_size is None else int(tile_size)
+        need = C.c_size_t()
+        with self._lock, torch.cuda.device(self.dev):
+            u8 = torch.empty((h * s, w * s, c), dtype=torch.uint8, device=self.dev) if want_u8 else None
+            f32 = torch.empty((c, h * s, w * s), dtype=torch.float32, device=self.dev) if want_f32 else None
+            check(self.lib.irb_restore_crop_workspace_bytes(self._h, h, w, t, int(tile_pad), C.byref(need)))
+            ws = self._workspace(need.value)
+            check(self.lib.irb_restore_image_crop(self._h, img.data_ptr(), fmt, int(bgr), h, w, t, int(tile_pad),
+                                                  None if u8 is None else u8.data_ptr(),
+                                                  None if f32 is None else f32.data_ptr(), ws.data_ptr(), ws.numel(),
+                                                  self._stream()))
+        return u8, f32
+
+    def restore_crop(self, img_u8: np.ndarray, tile_size=None, tile_pad: int = 32, bgr: bool = False) -> np.ndarray:
+        """Host uint8 [H,W,c] in -> host uint8 [sH,sW,c] out through restore_crop_device; H2D and D2H included."""
+        d = torch.from_numpy(np.ascontiguousarray(img_u8)).to(self.dev, non_blocking=True)
+        u8, _ = self.restore_crop_device(d, tile_size, tile_pad, bgr)
+        return u8.cpu().numpy()
 
     def _capture(self, key, img):
         fmt, h, w, t, ov, bgr, want_u8, want_f32, strict = key

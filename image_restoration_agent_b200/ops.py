@@ -156,6 +156,18 @@ def window_attention(qkv, C, heads, window, shift, bias_table):
     return y
 
 
+def hat_attention(qkv, heads, head_dim, window, overlap_window, shift, bias_table):
+    """HAT window attention (irb_hat_attention): qkv [n, H, W, 3*heads*dstride] (q pre-scaled, fp32 or bf16) ->
+    [n, H, W, heads*head_dim]. overlap_window == window: (shifted-)window self-attention; larger: OCAB."""
+    n, H, W, C3 = qkv.shape
+    dstride = C3 // (3 * heads)
+    C = heads * head_dim
+    y = torch.zeros((n, H, W, C), device=qkv.device, dtype=qkv.dtype)
+    check(_lib.load().irb_hat_attention(qkv.data_ptr(), _dt(qkv), C3, y.data_ptr(), C, n, H, W, heads, head_dim, dstride,
+                                        window, overlap_window, shift, bias_table.data_ptr(), _stream()))
+    return y
+
+
 def pwdw_fused(x, stats, w1, dww, colsum=None, t=None, gate=False):
     """x bf16 [n,H,W,C]; stats fp32 [n*H*W, 2] (mu, rstd); w1 bf16 [rows, C] (LayerNorm gain folded); dww fp32
     [9, rows]; colsum / t fp32 [rows] or None (BiasFree). -> bf16 [n,H,W,rows] (plain) or [n,H,W,rows/2] (gate)."""

@@ -227,6 +227,63 @@ def swinir_state_dict(cfg: dict, seed: int = 0) -> "OrderedDict[str, torch.Tenso
     return sd
 
 
+def hat_state_dict(cfg: dict, seed: int = 0) -> "OrderedDict[str, torch.Tensor]":
+    """Parameters of hat_arch.HAT (upsampler 'pixelshuffle', '1conv'); the registered buffers
+    relative_position_index_SA / _OCA are included because the reference loads with strict=True."""
+    g = _Gen(seed)
+    sd: OrderedDict[str, torch.Tensor] = OrderedDict()
+    C, ws, cin = cfg["embed_dim"], cfg["window_size"], cfg["in_chans"]
+    ows = ws + int(cfg["overlap_ratio"] * ws)
+    hidden = int(C * cfg["mlp_ratio"])
+
+    def conv(name, cout, cin_, k=3):
+        sd[f"{name}.weight"] = g.conv(cout, cin_, k)
+        sd[f"{name}.bias"] = g.uniform((cout,), 1.0 / math.sqrt(cin_ * k * k))
+
+    def lin(name, cout, cin_):
+        sd[f"{name}.weight"] = g.linear(cout, cin_)
+        sd[f"{name}.bias"] = g.uniform((cout,), 1.0 / math.sqrt(cin_))
+
+    def norm(name):
+        sd[f"{name}.weight"] = g.normal((C,), 0.1, 1.0)
+        sd[f"{name}.bias"] = g.normal((C,), 0.05)
+
+    conv("conv_first", C, cin)
+    norm("patch_embed.norm")
+    for r, depth in enumerate(cfg["depths"]):
+        nh = cfg["num_heads"][r]
+        grp = f"layers.{r}.residual_group"
+        for b in range(depth):
+            p = f"{grp}.blocks.{b}"
+            norm(f"{p}.norm1")
+            sd[f"{p}.attn.relative_position_bias_table"] = g.normal(((2 * ws - 1) ** 2, nh), 0.5)
+            lin(f"{p}.attn.qkv", 3 * C, C)
+            lin(f"{p}.attn.proj", C, C)
+            conv(f"{p}.conv_block.cab.0", C // cfg["compress_ratio"], C)
+            conv(f"{p}.conv_block.cab.2", C, C // cfg["compress_ratio"])
+            conv(f"{p}.conv_block.cab.3.attention.1", C // cfg["squeeze_factor"], C, 1)
+            conv(f"{p}.conv_block.cab.3.attention.3", C, C // cfg["squeeze_factor"], 1)
+            norm(f"{p}.norm2")
+            lin(f"{p}.mlp.fc1", hidden, C)
+            lin(f"{p}.mlp.fc2", C, hidden)
+        p = f"{grp}.overlap_attn"
+        norm(f"{p}.norm1")
+        lin(f"{p}.qkv", 3 * C, C)
+        sd[f"{p}.relative_position_bias_table"] = g.normal(((ws + ows - 1) ** 2, nh), 0.5)
+        lin(f"{p}.proj", C, C)
+        norm(f"{p}.norm2")
+        lin(f"{p}.mlp.fc1", hidden, C)
+        lin(f"{p}.mlp.fc2", C, hidden)
+        conv(f"layers.{r}.conv", C, C)
+    norm("norm")
+    conv("conv_after_body", C, C)
+    conv("conv_before_upsample.0", 64, C)
+    for i in range(int(math.log2(cfg["upscale"]))):
+        conv(f"upsample.{2 * i}", 256, 64)
+    conv("conv_last", cin, 64)
+    return sd
+
+
 def synthetic_image_u8(h: int, w: int, c: int = 3, seed: int = 0) -> np.ndarray:
     """uint8 HWC image with image-like statistics: uniform noise, 5x5 box-blurred twice, contrast stretched
     (SURVEY.md §8d)."""

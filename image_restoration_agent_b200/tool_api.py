@@ -256,6 +256,44 @@ class XRestormerB200(Tool):
         cv2.imwrite(str(Path(self.output_dir) / "output.png"), out)
 
 
+class HATB200(Tool):
+    """In-process replacement of the agent's HAT tool (executor/super_resolution/__init__.py:12-20: tool_name 'hat', a
+    BasicSRModel tool running hat/test.py on executor/super_resolution/configs/hat.yml). BasicSR's test pipeline with
+    model_type HATModel (hat/models/hat_model.py:16-109): cv2.imread BGR -> RGB / 255, reflect pad to the window (16),
+    tile_size 512 / tile_pad 32 crop-with-pad tiles pasted without blending, crop, tensor2img -> output.png.
+    Checkpoint key 'params_ema' (hat.yml path.param_key_g)."""
+
+    WEIGHTS = "Real_HAT_GAN_SRx4.pth"  # hat.yml path.pretrain_network_g
+
+    def __init__(self, weights_root: Optional[str] = None, state_dict=None, precision: str = "bf16", device: int = 0,
+                 cfg: Optional[dict] = None, tile: Optional[dict] = None):
+        super().__init__(tool_name="hat", subtask="super_resolution")
+        self.cfg = cfg or configs.hat_config()
+        self.tile = dict(configs.HAT_TILE if tile is None else tile)   # {} = HATModel.process (no 'tile' key in the yml)
+        self.weights_root, self.state_dict = weights_root, state_dict
+        self.precision, self.device = precision, device
+
+    def _engine(self) -> Engine:
+        def sd():
+            if self.state_dict is not None:
+                return self.state_dict
+            return load_checkpoint(os.path.join(self.weights_root, self.WEIGHTS), ("params_ema", "params"))
+        src = self.state_dict if self.state_dict is not None else os.path.join(self.weights_root, self.WEIGHTS)
+        return get_engine("hat", src, self.cfg, sd, self.precision, self.device)
+
+    def restore_u8_device(self, img_bgr, graph: bool = False):
+        return self._engine().restore_crop_device(img_bgr, self.tile.get("tile_size"), self.tile.get("tile_pad", 0),
+                                                  bgr=True)[0]
+
+    def _invoke(self) -> None:
+        import cv2
+
+        path = sorted(Path(self.input_dir).glob("*"))[0]
+        img = _imread(path, cv2.IMREAD_COLOR)
+        out = self._engine().restore_crop(img, self.tile.get("tile_size"), self.tile.get("tile_pad", 0), bgr=True)
+        cv2.imwrite(str(Path(self.output_dir) / "output.png"), out)
+
+
 class Chain:
     """A plan of several tools run back to back on one image (BASELINE config 4: derain -> denoise -> x4 SR) with the
     inter-stage hand-off kept in HBM.

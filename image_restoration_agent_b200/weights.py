@@ -15,7 +15,8 @@ import struct
 
 import numpy as np
 
-_SKIP_SUFFIXES = ("relative_position_index", "attn_mask")
+_SKIP_SUFFIXES = ("relative_position_index", "attn_mask",
+                  "relative_position_index_SA", "relative_position_index_OCA")  # HAT's two index buffers
 _ENTRY = struct.Struct("<96sI4IQQ")
 
 

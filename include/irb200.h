@@ -31,6 +31,7 @@ extern "C" {
 #define IRB_ARCH_RESTORMER 1
 #define IRB_ARCH_SWINIR 2
 #define IRB_ARCH_XRESTORMER 3 /* X-Restormer: Restormer blocks + overlapping cross-attention */
+#define IRB_ARCH_HAT 4         /* HAT: SwinIR skeleton + CAB branch + OCAB per group, window 16 */
 
 #define IRB_F32 0  /* fp32 storage + fp32 FMA arithmetic (verification mode, <=1e-4 of the reference) */
 #define IRB_BF16 1 /* bf16 storage, tcgen05 tensor-core contractions with fp32 accumulation */
@@ -75,6 +76,12 @@ typedef struct irb_model_desc {
      * PixelUnshuffle(s) + conv(in_chans * s^2 -> embed_dim), upscale must equal s (nearest+conv tail, x2 per stage), so
      * the model's output has the size of its input (irb_scale() = 1) */
     int unshuffle_scale;
+    /* HAT(...)  hat_arch.py:738-766 (configs/hat.yml:21-37): the SwinIR fields above (img_size, window_size <= 16,
+     * embed_dim, depths, num_heads, mlp_ratio, upscale, img_range, upsampler = pixelshuffle, resi_3conv = 0) and
+     * overlap_ratio, plus: */
+    int compress_ratio;  /* CAB: conv3x3 C -> C / compress_ratio -> C */
+    int squeeze_factor;  /* ChannelAttention: C -> C / squeeze_factor -> C */
+    float conv_scale;    /* weight of the CAB branch in HAB.forward (:306) */
 } irb_model_desc;
 
 const char* irb_last_error(void);
@@ -88,7 +95,7 @@ int irb_plan_tiles(int n, int tile, int overlap, int* idx, int* count);
 /* Padded size the reference scripts feed to the model: SwinIR (h / ws + 1) * ws (always pads,
  * inference.py:76-78); Restormer next multiple of 8 only when needed (demo.py:122-126); X-Restormer next multiple of
  * `window_size` (64 for the scale-1 configs, 16 for the scale-4 SR config; 0 = 64) only when needed
- * (xrestormer_model.py:56-66). Host-only. */
+ * (xrestormer_model.py:56-66); HAT next multiple of window_size only when needed (hat_model.py:16-26). Host-only. */
 int irb_padded_size(int arch, int window_size, int h, int w, int* hp, int* wp);
 
 /* weights_blob: host memory, format documented in image_restoration_agent_b200/weights.py (IRBW v1: named fp32
@@ -124,6 +131,16 @@ int irb_restore_workspace_bytes(irb_handle* h, int img_h, int img_w, int tile, i
 int irb_restore_image(irb_handle* h, const void* d_in, int in_fmt, int reverse_channels, int img_h, int img_w,
                       int tile, int overlap, uint8_t* d_out_u8, float* d_out_f32, void* d_workspace,
                       size_t workspace_bytes, void* stream);
+
+/* HATModel's tool body (hat/models/hat_model.py:16-109): reflect pad bottom / right to the window (pre_process), cut
+ * tile_size tiles with a tile_pad border clipped to the image (tile_process; tile_size = 0: the whole image, process),
+ * run each through the model, paste each tile's own area (no blending), crop (post_process). tile_size and tile_pad
+ * must be multiples of the model's window. Formats as irb_restore_image. Works for every arch; the padded size follows
+ * the arch's own rule (irb_padded_size). */
+int irb_restore_crop_workspace_bytes(irb_handle* h, int img_h, int img_w, int tile_size, int tile_pad, size_t* out_bytes);
+int irb_restore_image_crop(irb_handle* h, const void* d_in, int in_fmt, int reverse_channels, int img_h, int img_w,
+                           int tile_size, int tile_pad, uint8_t* d_out_u8, float* d_out_f32, void* d_workspace,
+                           size_t workspace_bytes, void* stream);
 
 /* ---- the stages of irb_restore_image, exposed so that tiles can be sharded across ranks (one process per GPU):
  * plan (host) -> tiles_prepare -> forward_tiles_cl on this rank's tile range -> [NCCL gather] -> irb_stitch. ------
@@ -183,6 +200,16 @@ int irb_mlp_fused(void* d_x, long long ldx, long long rows, int C, int hid, cons
  * dim_head^-0.5 inside the kernel. d_rel_h / d_rel_w fp32 [2*overlap_window-1][dim_head]. dim_head must be 16. */
 int irb_ocab(const void* d_qkv, int dtype, long long ld, void* d_out, long long ldo, int n, int H, int W, int heads,
              int dim_head, int window, int overlap_window, const float* d_rel_h, const float* d_rel_w, void* stream);
+/* HAT window attention (hat_arch.py:165-197 WindowAttention with window <= 16 and the shift mask of :921-941 when
+ * overlap_window == window; :392-432 OCAB when overlap_window > window: keys / values from the zero-padded
+ * overlap_window-wide neighbourhood, shift must be 0) on a channels-last qkv tensor [n, H, W, ld] with sections q | k | v
+ * of heads * dstride channels each (head-major, the first head_dim of every dstride real, q pre-scaled).
+ * d_bias_table fp32 [(2*window-1)^2][heads] resp. [(window+overlap_window-1)^2][heads], indexed like
+ * calculate_rpi_sa / calculate_rpi_oca (:882-919), negative OCA indices wrapping like PyTorch indexing.
+ * out [n, H, W, ldo], channel head * head_dim + dd. */
+int irb_hat_attention(const void* d_qkv, int dtype, long long ld, void* d_out, long long ldo, int n, int H, int W,
+                      int heads, int head_dim, int dstride, int window, int overlap_window, int shift,
+                      const float* d_bias_table, void* stream);
 /* MDTA Gram over a channels-last qkv tensor (q | k | v): the P pixels are split into nchunks =
  * irb_mdta_nchunks(P, heads, n) chunks and every chunk writes its own slot (no atomics -> bit-reproducible):
  *   d_Gpart   [n][heads][nchunks][c][c]   partial sum_p q k^T

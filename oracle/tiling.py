@@ -6,6 +6,8 @@ Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl refere
 """
 from __future__ import annotations
 
+import math
+
 import numpy as np
 import torch
 import torch.nn.functional as F
@@ -103,6 +105,51 @@ def xrestormer_restore_image(img_bgr_u8: np.ndarray, model, return_float=False, 
     with torch.no_grad():
         y = model(x)
     y = y[:, :, :h * scale, :w * scale]   # post_process: 0 : h - mod_pad_h * scale
+    if return_float:
+        return y[0].clone()
+    o = y[0].float().clamp_(0, 1).numpy()
+    o = np.transpose(o[[2, 1, 0], :, :], (1, 2, 0))
+    return (o * 255.0).round().astype(np.uint8)
+
+
+def hat_tile_plan(height: int, width: int, tile_size: int, tile_pad: int) -> list[tuple[int, ...]]:
+    """The tile rectangles of HATModel.tile_process (hat/models/hat_model.py:40-75) on the window-padded image, one
+    tuple per tile in the reference's y-major order:
+    (y0, y1, x0, x1, y0_pad, y1_pad, x0_pad, x1_pad) = the tile's own area and the area fed to the network."""
+    plan = []
+    for y in range(math.ceil(height / tile_size)):
+        for x in range(math.ceil(width / tile_size)):
+            x0, y0 = x * tile_size, y * tile_size
+            x1, y1 = min(x0 + tile_size, width), min(y0 + tile_size, height)
+            plan.append((y0, y1, x0, x1, max(y0 - tile_pad, 0), min(y1 + tile_pad, height), max(x0 - tile_pad, 0),
+                         min(x1 + tile_pad, width)))
+    return plan
+
+
+def hat_restore_image(img_bgr_u8: np.ndarray, model, scale: int = 4, window_size: int = 16, tile_size=512, tile_pad=32,
+                      return_float=False):
+    """The BasicSR test path of the HAT tool (executor/super_resolution/configs/hat.yml): cv2.imread BGR -> RGB
+    float/255 (basicsr img2tensor) -> HATModel.pre_process (hat_model.py:16-26: reflect pad bottom/right to a multiple
+    of window_size) -> tile_process (:40-105: crop-with-pad tiles, each tile's own area pasted, NO blending;
+    tile_size None = process() on the whole image, :28-38) -> post_process (:107-109) -> tensor2img.
+    img_bgr_u8: uint8 [H, W, 3] BGR; returns BGR uint8 [H*scale, W*scale, 3]."""
+    x = torch.from_numpy(np.ascontiguousarray(img_bgr_u8[:, :, ::-1])).float().div(255.0).permute(2, 0, 1).unsqueeze(0)
+    _, c, h, w = x.shape
+    ph = (window_size - h % window_size) % window_size
+    pw = (window_size - w % window_size) % window_size
+    x = F.pad(x, (0, pw, 0, ph), "reflect")
+    H, W = x.shape[2:]
+    with torch.no_grad():
+        if tile_size is None:
+            y = model(x)
+        else:
+            y = x.new_zeros((1, c, H * scale, W * scale))
+            for (y0, y1, x0, x1, y0p, y1p, x0p, x1p) in hat_tile_plan(H, W, tile_size, tile_pad):
+                o = model(x[:, :, y0p:y1p, x0p:x1p])
+                oy, ox = (y0 - y0p) * scale, (x0 - x0p) * scale
+                y[:, :, y0 * scale:y1 * scale, x0 * scale:x1 * scale] = o[:, :, oy:oy + (y1 - y0) * scale,
+                                                                          ox:ox + (x1 - x0) * scale]
+    y = y[:, :, :h * scale, :w * scale]
     if return_float:
         return y[0].clone()
     o = y[0].float().clamp_(0, 1).numpy()

@@ -16,6 +16,11 @@ X_CASES = {  # X-Restormer, tools/make_golden_full.py xrestorm
     "xrestormer_full": lambda: configs.xrestormer_config(),
     "xrestormer_small_sr_x4": lambda: configs.small_xrestormer_config("WithBias", scale=4),
 }
+H_CASES = {  # HAT, tools/make_golden_full.py hat
+    "hat_small": lambda: configs.small_hat_config(),
+    "hat_small_w8_x2": lambda: configs.small_hat_config(window_size=8, upscale=2),
+    "hat_full": lambda: configs.hat_config(),
+}
 S_CASES = {
     "swinir_small_color_dn": lambda: configs.small_swinir_config("color_dn"),
     "swinir_small_color_dn_ragged": lambda: configs.small_swinir_config("color_dn"),

@@ -302,6 +302,120 @@ def diffbir():
 
 GROUPS["diffbir"] = diffbir
 
+
+
+# ---------------- HAT ----------------
+HATDIR = f"{mg.REF}/AgenticIR/executor/super_resolution/tools/HAT"
+
+
+def _hat_shims():
+    """Stand-ins for the basicsr imports of hat_arch.py / hat_model.py (registry decorators, to_2tuple, trunc_normal_,
+    the SRModel base class, metric / image helpers): none of them touches the arithmetic of forward / tile_process."""
+    def mod(name, **attrs):
+        m = types.ModuleType(name)
+        for k, v in attrs.items():
+            setattr(m, k, v)
+        sys.modules[name] = m
+        return m
+
+    class _Reg:
+        def register(self, *a, **k):
+            return lambda cls: cls
+
+    mod("basicsr")
+    mod("basicsr.utils", imwrite=None, tensor2img=None)
+    mod("basicsr.utils.registry", ARCH_REGISTRY=_Reg(), MODEL_REGISTRY=_Reg())
+    mod("basicsr.archs")
+    mod("basicsr.archs.arch_util", to_2tuple=lambda x: (x, x) if not isinstance(x, tuple) else x,
+        trunc_normal_=lambda t, std=1.0, **k: torch.nn.init.trunc_normal_(t, std=std))
+    mod("basicsr.models")
+    mod("basicsr.models.sr_model", SRModel=type("SRModel", (), {}))
+    mod("basicsr.metrics", calculate_metric=None)
+
+
+def ref_hat(cfg, sd):
+    import importlib.util
+    _hat_shims()
+    spec = importlib.util.spec_from_file_location("hat_arch_ref", f"{HATDIR}/hat/archs/hat_arch.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    m = mod.HAT(**cfg)
+    missing, unexpected = m.load_state_dict(sd, strict=False)  # the two rpi buffers are not parameters
+    assert not unexpected and all("relative_position_index" in k for k in missing), (missing, unexpected)
+    return m.eval()
+
+
+def ref_hat_tool(img_bgr_u8, net, scale, window_size, tile_size, tile_pad, return_float=False):
+    """The reference's OWN HATModel.pre_process / tile_process / process / post_process (hat_model.py:16-109), run as
+    unbound functions on a stand-in object; img2tensor / tensor2img of basicsr around them."""
+    import importlib.util
+    _hat_shims()
+    spec = importlib.util.spec_from_file_location("hat_model_ref", f"{HATDIR}/hat/models/hat_model.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    M = mod.HATModel
+    o = types.SimpleNamespace()
+    o.opt = {"network_g": {"window_size": window_size}, "scale": scale}
+    if tile_size is not None:
+        o.opt["tile"] = {"tile_size": tile_size, "tile_pad": tile_pad}
+    o.net_g = net
+    o.lq = torch.from_numpy(np.ascontiguousarray(img_bgr_u8[:, :, ::-1])).float().div(255.0).permute(2, 0, 1).unsqueeze(0)
+    M.pre_process(o)
+    if tile_size is not None:
+        M.tile_process(o)
+    else:
+        M.process(o)
+    M.post_process(o)
+    y = o.output
+    if return_float:
+        return y[0].clone()
+    a = y[0].float().clamp_(0, 1).numpy()
+    a = np.transpose(a[[2, 1, 0], :, :], (1, 2, 0))
+    return (a * 255.0).round().astype(np.uint8)
+
+
+def hat():
+    from oracle import hat_ref
+    cases = [("hat_small", configs.small_hat_config(), (1, 3, 32, 48), 1),
+             ("hat_small_w8_x2", configs.small_hat_config(window_size=8, upscale=2), (2, 3, 32, 24), 2),
+             ("hat_full", configs.hat_config(), (1, 3, 32, 48), 0)]
+    for name, cfg, shape, seed in cases:
+        print(name)
+        sd = synth.hat_state_dict(cfg, seed=seed)
+        ref = ref_hat(cfg, sd)
+        x = image_like(512, 512, 3, seed=seed)[..., 30:30 + shape[2], 70:70 + shape[3]].repeat(shape[0], 1, 1, 1).contiguous()
+        if shape[0] > 1:
+            x[1] = x[1].flip(-1)
+        t0 = time.time()
+        with torch.no_grad():
+            y_ref = ref(x)
+        print(f"  reference forward {time.time() - t0:.1f} s")
+        y_or = hat_ref.Model(sd, cfg)(x)
+        mg.check(name, y_or, y_ref, tol=2e-5)
+        mg.save(name, x=x.numpy(), y=y_ref.numpy(), seed=np.int64(seed))
+    # tool level: reflect pad to the window, crop-with-pad tiles (ragged last row / column), paste, crop, tensor2img
+    cfg = configs.small_hat_config()
+    sd = synth.hat_state_dict(cfg, seed=3)
+    ref = ref_hat(cfg, sd)
+    orc = hat_ref.Model(sd, cfg)
+    for name, shape, ts, tp in (("hat_pipeline_small_t32_p16", (70, 100), 32, 16), ("hat_pipeline_small_whole", (40, 52), None, 0)):
+        print(name)
+        img = synth.synthetic_image_u8(shape[0], shape[1], 3, seed=4)
+        u8_ref = ref_hat_tool(img, ref, 4, 16, ts, tp)
+        f_ref = ref_hat_tool(img, ref, 4, 16, ts, tp, return_float=True)
+        u8_same = tiling.hat_restore_image(img, ref, 4, 16, ts, tp)      # oracle tile loop around the reference network
+        assert np.array_equal(u8_same, u8_ref), "oracle tile loop differs from HATModel.tile_process"
+        u8_or = tiling.hat_restore_image(img, orc, 4, 16, ts, tp)
+        d = np.abs(u8_or.astype(int) - u8_ref.astype(int)).max()
+        print(f"  uint8 oracle vs reference: max LSB diff = {d}")
+        assert d <= 1
+        mg.save(name, img=img, out_u8=u8_ref, out_f32=f_ref.numpy(), seed=np.int64(3), tile=np.int64(ts or -1),
+                overlap=np.int64(tp))
+
+
+GROUPS["hat"] = hat
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
     torch.set_num_threads(os.cpu_count() or 8)
