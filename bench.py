@@ -78,6 +78,11 @@ WORKLOADS = {
                            prec="bf16", multi="weak",
                            desc="X-Restormer (dehazing config) 512x512 synthetic, whole image (the BasicSR tool path: no "
                                 "tile, pad to 64), bf16"),
+    "hat_x4": dict(stages=[("hat", "real_sr_x4", 512, 32, 4, False)], shape=(1024, 1024, 3), batch=1, prec="bf16",
+                   multi="weak",
+                   desc="HAT (Real_HAT_GAN_SRx4, executor/super_resolution/configs/hat.yml) x4 1024x1024 -> 4096x4096 "
+                        "synthetic, HATModel tile mode: tile_size 512 / tile_pad 32 (4 tiles of 544x544, pasted without "
+                        "blending), bf16"),
     "swinir_dn_256": dict(stages=[("swinir", "color_dn", None, 32, 1, False)], shape=(256, 256, 3), batch=1,
                           prec="bf16", multi="weak",
                           desc="SwinIR-M color_dn 256x256 synthetic, whole image (the executor's untiled small-image "
@@ -113,6 +118,9 @@ def stage_model(stage):
     if arch == "xrestormer":
         cfg = configs.xrestormer_config()
         return arch, cfg, synth.xrestormer_state_dict(cfg, seed=0)
+    if arch == "hat":
+        cfg = configs.hat_config()
+        return arch, cfg, synth.hat_state_dict(cfg, seed=0)
     cfg = configs.swinir_config(task, scale=scale, large_model=large)
     return arch, cfg, synth.swinir_state_dict(cfg, seed=0)
 
@@ -124,6 +132,12 @@ def _tile_idx(n, tile, ov):
 def executed_px_per_image(stage, h, w):
     """Pixels the model actually runs on for one h x w input image (script pad + tile over-compute)."""
     arch, task, tile, ov, scale, large = stage
+    if arch == "hat":                                                        # hat_model.py:16-75
+        hp, wp = (h + 15) // 16 * 16, (w + 15) // 16 * 16
+        if tile is None:
+            return hp * wp
+        span = lambda n: [min(a + tile + ov, n) - max(a - ov, 0) for a in range(0, n, tile)]
+        return sum(th * tw for th in span(hp) for tw in span(wp))
     if arch == "swinir":
         ws = 7 if "jpeg" in task else 8
         hp, wp = (h // ws + 1) * ws, (w // ws + 1) * ws                      # inference.py:76-78
@@ -146,7 +160,7 @@ def model_level(wl, ms_step, images_per_step, step_bytes, peaks):
     for st in wl["stages"]:
         arch, task, tile, ov, scale, large = st
         key = ("restormer", c) if arch == "restormer" else ("swinir", "real_sr_large" if large else task)
-        if arch == "xrestormer" or key not in MODEL_FLOPS_PER_PX:
+        if arch in ("xrestormer", "hat") or key not in MODEL_FLOPS_PER_PX:
             return {"note": "no model-level ceiling: BASELINE.md section 2 has no FLOP count for this model"}
         px = executed_px_per_image(st, hh, ww)
         px_exec += px
@@ -238,9 +252,10 @@ def config_dict(name):
 
 
 def oracle_model(stage):
-    from oracle import restormer_ref, swinir_ref, xrestormer_ref
+    from oracle import hat_ref, restormer_ref, swinir_ref, xrestormer_ref
     arch, cfg, sd = stage_model(stage)
-    cls = {"restormer": restormer_ref.Model, "swinir": swinir_ref.Model, "xrestormer": xrestormer_ref.Model}[arch]
+    cls = {"restormer": restormer_ref.Model, "swinir": swinir_ref.Model, "xrestormer": xrestormer_ref.Model,
+           "hat": hat_ref.Model}[arch]
     return cls(sd, cfg), cfg
 
 
@@ -274,7 +289,10 @@ def cpu_sample_mps(name: str, steps: int, warmup: int, threads: int | None = Non
         if arch == "swinir":
             x = tiling.swinir_pad(x, cfg["window_size"])
         hp, wp = x.shape[2:]
-        if tile is None:
+        if arch == "hat":   # crop-with-pad tiles of several shapes: time a 128x128 crop, scale by the executed pixels
+            th, tw, ntiles = 128, 128, 1
+            factor = executed_px_per_image(st, hh, ww) / float(th * tw)
+        elif tile is None:
             th, tw, ntiles = min(hp, 256), min(wp, 256), 1
             factor = (hp * wp) / float(th * tw)
         else:
@@ -299,7 +317,7 @@ def cpu_sample_mps(name: str, steps: int, warmup: int, threads: int | None = Non
         first_ms = first_ms if first_ms is not None else sec_tile * 1e3
         sec_img += sec_tile * factor
         notes.append(f"{arch}:{task} {len(times)} timed forward(s) of one {th}x{tw} "
-                     f"{'tile' if tile else 'crop'} ({sec_tile:.3f} s each) x {factor:.2f}")
+                     f"{'tile' if tile and arch != 'hat' else 'crop'} ({sec_tile:.3f} s each) x {factor:.2f}")
         hh, ww = hh * scale, ww * scale
     mps = (h * w / 1e6) / sec_img
     sample = (f"oracle fp32 on {torch.get_num_threads()} threads; " + "; ".join(notes) +
@@ -348,7 +366,7 @@ def parity_report(eng, stage, shape, prec):
     if arch == "swinir":
         x = tiling.swinir_pad(x, cfg["window_size"])
     t = min(tile or (256 if arch == "restormer" else 128), x.shape[2], x.shape[3])
-    if arch == "xrestormer":
+    if arch in ("xrestormer", "hat"):
         t = 128
     if arch == "swinir" and tile is None:
         t = min(t, 128)                                   # 128^2 tokens at full depth: ~3 s of oracle time
@@ -399,7 +417,10 @@ class Job:
     def restore(self, img_dev):
         x = img_dev
         for e, st in zip(self.engines, self.wl["stages"]):
-            x, _ = e.restore_device(x, st[2], st[3], bgr=(x.shape[2] == 3), graph=self.graph)
+            if st[0] == "hat":   # HATModel's crop-with-pad tile mode: st[2] = tile_size, st[3] = tile_pad
+                x, _ = e.restore_crop_device(x, st[2], st[3], bgr=True)
+            else:
+                x, _ = e.restore_device(x, st[2], st[3], bgr=(x.shape[2] == 3), graph=self.graph)
         return x
 
     def close(self):
