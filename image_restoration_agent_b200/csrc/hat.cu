@@ -163,6 +163,12 @@ __global__ void __launch_bounds__(256, 2) hat_attention_kernel(const HatAttnPara
     }
 }
 
+// hat_attn_tc.cu
+bool hat_attention_tc_ok(int dt, long long ld, long long ldo, int H, int W, int heads, int d, int dstride, int ws, int ows,
+                         int shift);
+int hat_attention_tc(const bf16* qkv, long long ld, bf16* out, long long ldo, int n, int H, int W, int heads, int d,
+                     int ows, int shift, const float* table, cudaStream_t stream);
+
 // mode 0: self-attention (ows = ws; bias index (q - k + ws - 1), shift mask); mode 1: overlapping cross-attention
 int hat_attention(const void* qkv, int dt, long long ld, void* out, long long ldo, int n, int H, int W, int heads, int d,
                   int dstride, int ws, int ows, int shift, const float* table, cudaStream_t stream) {
@@ -171,6 +177,10 @@ int hat_attention(const void* qkv, int dt, long long ld, void* out, long long ld
     IRB_REQUIRE(H % ws == 0 && W % ws == 0, "hat_attention: H, W must be multiples of the window");
     IRB_REQUIRE(d >= 1 && d <= kHatDP && dstride >= d, "hat_attention: head_dim must be <= 32");
     IRB_REQUIRE(shift >= 0 && shift < ws && (shift == 0 || ows == ws), "hat_attention: bad shift");
+    // bf16, window 16 (overlapping window 24), head_dim <= 32 in a stride-32 layout: tcgen05 kernel; everything else
+    // (fp32 mode, other windows): the FMA kernel below
+    if (IRB_DIAG_ENV("IRB_HAT_ATTN_TC", 1) && hat_attention_tc_ok(dt, ld, ldo, H, W, heads, d, dstride, ws, ows, shift))
+        return hat_attention_tc((const bf16*)qkv, ld, (bf16*)out, ldo, n, H, W, heads, d, ows, shift, table, stream);
     HatAttnParams p{};
     p.qkv = qkv;
     p.dt = dt;

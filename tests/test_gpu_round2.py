@@ -390,7 +390,7 @@ def test_hat_self_attention_kernel_matches_oracle(ws, shift):
     from image_restoration_agent_b200 import ops
     from oracle import hat_ref, swinir_ref
     torch.manual_seed(ws + shift)
-    n, heads, d, H, W = 2, 3, 30 if ws == 16 else 10, 2 * ws, 3 * ws
+    n, heads, d, H, W = 2, 4 if ws == 16 else 3, 30 if ws == 16 else 10, 2 * ws, 3 * ws  # window 16, bf16: tcgen05 kernel
     C = heads * d
     x = torch.randn(n, H, W, 3 * C)                      # q | k | v, [3][heads][d] like the qkv Linear output
     table = torch.randn((2 * ws - 1) ** 2, heads) * 0.5
@@ -417,7 +417,9 @@ def test_hat_self_attention_kernel_matches_oracle(ws, shift):
     got = ops.hat_attention(dev.reshape(n, H, W, 3 * heads * ds).cuda(), heads, d, ws, ws, shift, table.cuda())
     assert (got.cpu() - want).abs().max().item() <= 2e-5
     got16 = ops.hat_attention(dev.reshape(n, H, W, 3 * heads * ds).cuda().bfloat16(), heads, d, ws, ws, shift, table.cuda())
-    assert (got16.float().cpu() - want).abs().max().item() <= 6e-2
+    e16 = (got16.float().cpu() - want).abs()
+    print(f"\n[parity] hat self-attention ws {ws} shift {shift} bf16: max-abs {e16.max().item():.2e}, mean {e16.mean().item():.2e}")
+    assert e16.max().item() <= 6e-2 and e16.mean().item() <= 6e-3
 
 
 def test_hat_overlap_attention_kernel_matches_oracle():
@@ -448,6 +450,10 @@ def test_hat_overlap_attention_kernel_matches_oracle():
     dev[:, :, :, 0] *= d ** -0.5
     got = ops.hat_attention(dev.reshape(n, H, W, 3 * heads * ds).cuda(), heads, d, ws, ows, 0, table.cuda())
     assert (got.cpu() - want).abs().max().item() <= 2e-5
+    got16 = ops.hat_attention(dev.reshape(n, H, W, 3 * heads * ds).cuda().bfloat16(), heads, d, ws, ows, 0, table.cuda())
+    e16 = (got16.float().cpu() - want).abs()   # bf16: the tcgen05 kernel (streaming softmax over 12 chunks of 48 keys)
+    print(f"\n[parity] hat overlapping attention bf16: max-abs {e16.max().item():.2e}, mean {e16.mean().item():.2e}")
+    assert e16.max().item() <= 6e-2 and e16.mean().item() <= 6e-3
 
 
 @pytest.mark.parametrize("prec", ["fp32", "bf16"])
