@@ -22,6 +22,16 @@
 #include "ptx.cuh"
 #include "kernels.h"
 
+// The MMA thread polls its barriers with the non-blocking mbarrier.test_wait: try_wait suspends for a few hundred
+// cycles per not-ready barrier, and a polling round over six of them reacted to events ~1 us late.
+#ifdef IRB_OLD_POLL  // A/B switch (build.py --variant): the blocking poll of the first version
+#define IRB_MMA_POLL mbar_try_wait
+#define IRB_MMA_POLL_SLEEP 64
+#else
+#define IRB_MMA_POLL mbar_test_wait
+#define IRB_MMA_POLL_SLEEP 20
+#endif
+
 namespace irb {
 
 static constexpr int kHtWarps = 12;              // warp 0: MMA, 1..8: softmax groups, 9..11: loaders
@@ -151,43 +161,77 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
             __syncwarp();
             const uint32_t q_dst = smem_u32(stage_base + lw * kHtStage);
             const bf16* base = p.qkv + it.hp * 64 + c8 * 8;
-            // Q: token t = m * 128 + row of the window, at shifted-frame (wy*16 + t/16, wx*16 + t%16)
+            // Q: token t = m * 128 + row of the window, at shifted-frame (wy*16 + t/16, wx*16 + t%16). Only the last
+            // window row / column of a shifted frame wraps around the image; everywhere else the 16 x 16 tokens are an
+            // affine grid and the addresses are plain increments.
+            const bool wrap = p.shift > 0 && (wy == p.nwy - 1 || wx == p.nwx - 1);
+            const long long rowstep = (long long)p.W * p.ld;
+            const bf16* wbase = base + (((long long)img * p.H + wy * 16 + p.shift) * p.W + wx * 16 + p.shift + sub) * p.ld;
+            if (!wrap) {
+                const bf16* src = wbase + (long long)(it.m * 8) * rowstep;
+#pragma unroll
+                for (int ty = 0; ty < 8; ++ty) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int row = ty * 16 + k * 4 + sub;
+                        cp_async16(q_dst + row * 128 + ((c8 ^ (row & 7)) << 4), src + (long long)(k * 4) * p.ld);
+                    }
+                    src += rowstep;
+                }
+            } else {
 #pragma unroll 4
-            for (int i = 0; i < 32; ++i) {
-                const int row = i * 4 + sub;
-                const int t = it.m * 128 + row;
-                int oy = wy * 16 + (t >> 4) + p.shift, ox = wx * 16 + (t & 15) + p.shift;
-                if (oy >= p.H) oy -= p.H;
-                if (ox >= p.W) ox -= p.W;
-                const long long pix = ((long long)img * p.H + oy) * p.W + ox;
-                cp_async16(q_dst + row * 128 + ((c8 ^ (row & 7)) << 4), base + pix * p.ld);
-            }
-            const uint32_t k_dst = q_dst + kHtQBytes, v_dst = k_dst + kHtKBytes;
-#pragma unroll 4
-            for (int i = 0; i < KC / 4; ++i) {
-                const int row = i * 4 + sub;
-                int oy, ox;
-                bool inside = true;
-                if (MODE == 0) {
-                    const int j = it.c * KC + row;
-                    oy = wy * 16 + (j >> 4) + p.shift;
-                    ox = wx * 16 + (j & 15) + p.shift;
+                for (int i = 0; i < 32; ++i) {
+                    const int row = i * 4 + sub;
+                    const int t = it.m * 128 + row;
+                    int oy = wy * 16 + (t >> 4) + p.shift, ox = wx * 16 + (t & 15) + p.shift;
                     if (oy >= p.H) oy -= p.H;
                     if (ox >= p.W) ox -= p.W;
-                } else {
-                    const int kr = row / KW;
-                    oy = wy * 16 - 4 + it.c * KR + kr;
-                    ox = wx * 16 - 4 + (row - kr * KW);
-                    inside = oy >= 0 && oy < p.H && ox >= 0 && ox < p.W;
+                    const long long pix = ((long long)img * p.H + oy) * p.W + ox;
+                    cp_async16(q_dst + row * 128 + ((c8 ^ (row & 7)) << 4), base + pix * p.ld);
                 }
-                const uint32_t off = row * 128 + ((c8 ^ (row & 7)) << 4);
-                if (inside) {
-                    const bf16* src = base + (((long long)img * p.H + oy) * p.W + ox) * p.ld;
-                    cp_async16(k_dst + off, src + p.Cq);
-                    cp_async16(v_dst + off, src + 2 * p.Cq);
-                } else {  // nn.Unfold's zero padding: exact zero key / value vectors
-                    sts_v4(k_dst + off, 0u, 0u, 0u, 0u);
-                    sts_v4(v_dst + off, 0u, 0u, 0u, 0u);
+            }
+            const uint32_t k_dst = q_dst + kHtQBytes, v_dst = k_dst + kHtKBytes;
+            if (MODE == 0 && !wrap) {
+                const bf16* src = wbase + (long long)(it.c * KR) * rowstep;
+#pragma unroll
+                for (int ty = 0; ty < KR; ++ty) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int row = ty * 16 + k * 4 + sub;
+                        const uint32_t off = row * 128 + ((c8 ^ (row & 7)) << 4);
+                        const bf16* sp = src + (long long)(k * 4) * p.ld;
+                        cp_async16(k_dst + off, sp + p.Cq);
+                        cp_async16(v_dst + off, sp + 2 * p.Cq);
+                    }
+                    src += rowstep;
+                }
+            } else {
+#pragma unroll 4
+                for (int i = 0; i < KC / 4; ++i) {
+                    const int row = i * 4 + sub;
+                    int oy, ox;
+                    bool inside = true;
+                    if (MODE == 0) {
+                        const int j = it.c * KC + row;
+                        oy = wy * 16 + (j >> 4) + p.shift;
+                        ox = wx * 16 + (j & 15) + p.shift;
+                        if (oy >= p.H) oy -= p.H;
+                        if (ox >= p.W) ox -= p.W;
+                    } else {
+                        const int kr = row / KW;
+                        oy = wy * 16 - 4 + it.c * KR + kr;
+                        ox = wx * 16 - 4 + (row - kr * KW);
+                        inside = oy >= 0 && oy < p.H && ox >= 0 && ox < p.W;
+                    }
+                    const uint32_t off = row * 128 + ((c8 ^ (row & 7)) << 4);
+                    if (inside) {
+                        const bf16* src = base + (((long long)img * p.H + oy) * p.W + ox) * p.ld;
+                        cp_async16(k_dst + off, src + p.Cq);
+                        cp_async16(v_dst + off, src + 2 * p.Cq);
+                    } else {  // nn.Unfold's zero padding: exact zero key / value vectors
+                        sts_v4(k_dst + off, 0u, 0u, 0u, 0u);
+                        sts_v4(v_dst + off, 0u, 0u, 0u, 0u);
+                    }
                 }
             }
             cp_async_commit();
@@ -213,12 +257,12 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
                 bool progress = false;
                 if (s_next < my_steps) {
                     const int st = s_next % kHtStages;
-                    if (!s_loaded && mbar_try_wait(&bar[HB_FULL + st], (s_next / kHtStages) & 1)) s_loaded = true;
+                    if (!s_loaded && IRB_MMA_POLL(&bar[HB_FULL + st], (s_next / kHtStages) & 1)) s_loaded = true;
                     if (s_loaded) {
                         const uint32_t q_addr = smem_u32(stage_base + st * kHtStage);
                         const uint32_t k_addr = q_addr + kHtQBytes;
                         for (int g = 0; g < 2; ++g) {
-                            if (s_done[g] || !mbar_try_wait(&bar[HB_SEMPTY + g], (s_next & 1) ^ 1)) continue;
+                            if (s_done[g] || !IRB_MMA_POLL(&bar[HB_SEMPTY + g], (s_next & 1) ^ 1)) continue;
                             tc_fence_after();
 #pragma unroll
                             for (int ks = 0; ks < 2; ++ks) {
@@ -241,8 +285,8 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
                     const int st = pv_next % kHtStages;
                     const uint32_t v_addr = smem_u32(stage_base + st * kHtStage) + kHtQBytes + kHtKBytes;
                     for (int g = 0; g < 2; ++g) {
-                        if (pv_done[g] || !mbar_try_wait(&bar[HB_PFULL + g], pv_next & 1) ||
-                            !mbar_try_wait(&bar[HB_OEMPTY + g], (pv_next & 1) ^ 1))
+                        if (pv_done[g] || !IRB_MMA_POLL(&bar[HB_PFULL + g], pv_next & 1) ||
+                            !IRB_MMA_POLL(&bar[HB_OEMPTY + g], (pv_next & 1) ^ 1))
                             continue;
                         tc_fence_after();
                         const uint32_t pa = smem_u32(p_base + g * kHtPBytes);
@@ -265,7 +309,7 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
                 if (progress) {
                     spins = 0;
                 } else {
-                    __nanosleep(64);
+                    __nanosleep(IRB_MMA_POLL_SLEEP);
                     if (++spins > (1u << 24)) __trap();  // protocol bug: fail the launch instead of hanging
                 }
             }

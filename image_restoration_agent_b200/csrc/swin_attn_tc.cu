@@ -18,6 +18,16 @@
 #include "ptx.cuh"
 #include "kernels.h"
 
+// The MMA thread polls its barriers with the non-blocking mbarrier.test_wait: try_wait suspends for a few hundred
+// cycles per not-ready barrier, and a polling round over six of them reacted to events ~1 us late.
+#ifdef IRB_OLD_POLL  // A/B switch (build.py --variant): the blocking poll of the first version
+#define IRB_MMA_POLL mbar_try_wait
+#define IRB_MMA_POLL_SLEEP 64
+#else
+#define IRB_MMA_POLL mbar_test_wait
+#define IRB_MMA_POLL_SLEEP 20
+#endif
+
 namespace irb {
 
 static constexpr int kWaThreads = 13 * 32;      // warp 0: MMA, 1..8: softmax groups A/B, 9..12: loaders
@@ -216,12 +226,12 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                 bool progress = false;
                 if (s_next < my_pairs) {
                     const int st = s_next & 1;
-                    if (!s_loaded && mbar_try_wait(&bar[WB_FULL + st], (s_next >> 1) & 1)) s_loaded = true;
+                    if (!s_loaded && IRB_MMA_POLL(&bar[WB_FULL + st], (s_next >> 1) & 1)) s_loaded = true;
                     if (s_loaded) {
                         const uint32_t q_addr = smem_u32(stage_base + st * kWaStage);
                         const uint32_t k_addr = q_addr + kWaTile;
                         for (int g = 0; g < 2; ++g) {
-                            if (s_done[g] || !mbar_try_wait(&bar[WB_SEMPTY + g], (s_next & 1) ^ 1)) continue;
+                            if (s_done[g] || !IRB_MMA_POLL(&bar[WB_SEMPTY + g], (s_next & 1) ^ 1)) continue;
                             tc_fence_after();
 #pragma unroll
                             for (int ks = 0; ks < 2; ++ks) {
@@ -244,8 +254,8 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                     const int st = pv_next & 1;
                     const uint32_t v_addr = smem_u32(stage_base + st * kWaStage) + 2 * kWaTile;
                     for (int g = 0; g < 2; ++g) {
-                        if (pv_done[g] || !mbar_try_wait(&bar[WB_PFULL + g], pv_next & 1) ||
-                            !mbar_try_wait(&bar[WB_OEMPTY + g], (pv_next & 1) ^ 1))
+                        if (pv_done[g] || !IRB_MMA_POLL(&bar[WB_PFULL + g], pv_next & 1) ||
+                            !IRB_MMA_POLL(&bar[WB_OEMPTY + g], (pv_next & 1) ^ 1))
                             continue;
                         tc_fence_after();
                         const uint32_t pa = smem_u32(p_base + g * kWaPBytes);
@@ -270,7 +280,7 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                 } else {
                     // back off: this thread shares its scheduler with softmax and loader warps, and the kernel is
                     // sensitive to issue pressure
-                    __nanosleep(64);
+                    __nanosleep(IRB_MMA_POLL_SLEEP);
                     if (++spins > (1u << 24)) __trap();  // protocol bug: fail the launch instead of hanging
                 }
             }
