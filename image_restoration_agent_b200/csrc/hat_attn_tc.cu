@@ -6,9 +6,14 @@
 // 16 = 64 keys, MODE 1: 2 rows of 24 = 48 keys) so that the relative-position bias of key jj of a chunk sits at a
 // compile-time offset from a per-(token, chunk) base pointer. One STEP = (window, head pair, M block, key chunk):
 //   loaders (3 warps, one per ring stage)
-//                     : cp.async gather of Q (128 tokens), K and V (the chunk's keys) of the head pair (64 channels = one
-//                       128-byte swizzled row) into the UMMA layout; the cyclic shift and the overlapping window's zero
-//                       padding are address arithmetic (out-of-image keys are written as zeros)
+//                     : Q (128 tokens), K and V (the chunk's keys) of the head pair (64 channels = one 128-byte swizzled
+//                       row) into the UMMA layout. A window that does not wrap around the image is an axis-aligned box of
+//                       the qkv tensor: three TMA loads by one lane ({64 ch, 16, 8} for Q, {64, 16, 4} / {64, 24, 2} for a key
+//                       chunk), and the out-of-image keys of the overlapping window arrive as zeros (TMA out-of-bounds
+//                       fill = nn.Unfold's padding). The last window row / column of a shifted frame wraps around the
+//                       image and is gathered row by row with cp.async (~6 % of the windows of a 544 x 544 tile).
+//                       ncu (profiles/r02_s21) showed the all-cp.async loader's issue time on the critical path: the
+//                       softmax warps sat on the S barrier for 22 % of the samples; TMA took 0.52 -> 0.34 ms per launch.
 //   MMA (1 thread)    : S_h = Q_h K_h^T (M 128, N = chunk, K 32) per head of the pair; O_h = P_h V (M 128, N 64, K = chunk)
 //   softmax (2 x 4 warps, one group per head of the pair, thread = query row):
 //                       S row from TMEM -> * log2(e) + bias (+ shift mask) -> chunk max / exp2 / sum -> unnormalised P
@@ -81,8 +86,13 @@ struct HtIter {
     }
 };
 
+// tm_q / tm_kv: 4-D tensor maps {channel, x, y, image} over the qkv tensor with boxes {64, 16, 8, 1} (a Q block: half a
+// window) and {64, KW, KR, 1} (a key chunk), 128-byte swizzle: the box lands in shared memory exactly in the UMMA
+// layout, and out-of-image key positions of the overlapping window arrive as zeros (nn.Unfold's padding).
 template <int MODE, int D2T>
-__global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const HtParams p) {
+__global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const HtParams p,
+                                                                         const __grid_constant__ CUtensorMap tm_q,
+                                                                         const __grid_constant__ CUtensorMap tm_kv) {
     using Cfg = HtCfg<MODE>;
     constexpr int KC = Cfg::KC, NC = Cfg::NC, KW = Cfg::KW, KR = Cfg::KR, TR = Cfg::TR;
     constexpr int kTabSize = TR * kHtTabStride;
@@ -162,76 +172,59 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
             const uint32_t q_dst = smem_u32(stage_base + lw * kHtStage);
             const bf16* base = p.qkv + it.hp * 64 + c8 * 8;
             // Q: token t = m * 128 + row of the window, at shifted-frame (wy*16 + t/16, wx*16 + t%16). Only the last
-            // window row / column of a shifted frame wraps around the image; everywhere else the 16 x 16 tokens are an
-            // affine grid and the addresses are plain increments.
+            // window row / column of a shifted frame wraps around the image.
             const bool wrap = p.shift > 0 && (wy == p.nwy - 1 || wx == p.nwx - 1);
-            const long long rowstep = (long long)p.W * p.ld;
-            const bf16* wbase = base + (((long long)img * p.H + wy * 16 + p.shift) * p.W + wx * 16 + p.shift + sub) * p.ld;
             if (!wrap) {
-                const bf16* src = wbase + (long long)(it.m * 8) * rowstep;
-#pragma unroll
-                for (int ty = 0; ty < 8; ++ty) {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const int row = ty * 16 + k * 4 + sub;
-                        cp_async16(q_dst + row * 128 + ((c8 ^ (row & 7)) << 4), src + (long long)(k * 4) * p.ld);
-                    }
-                    src += rowstep;
+                // the 16 x 16 tokens are an axis-aligned box of the image: three TMA loads by one lane
+                if (lane == 0) {
+                    uint8_t* st = stage_base + lw * kHtStage;
+                    mbar_arrive_expect_tx(&bar[HB_FULL + lw], kHtQBytes + 2 * KC * 128);
+                    const int x0 = wx * 16 + p.shift, y0 = wy * 16 + p.shift;
+                    const int kx0 = MODE == 0 ? x0 : x0 - 4, ky0 = MODE == 0 ? y0 + it.c * KR : y0 - 4 + it.c * KR;
+                    tma_load_4d(st, &tm_q, &bar[HB_FULL + lw], it.hp * 64, x0, y0 + it.m * 8, img);
+                    tma_load_4d(st + kHtQBytes, &tm_kv, &bar[HB_FULL + lw], p.Cq + it.hp * 64, kx0, ky0, img);
+                    tma_load_4d(st + kHtQBytes + kHtKBytes, &tm_kv, &bar[HB_FULL + lw], 2 * p.Cq + it.hp * 64, kx0, ky0, img);
                 }
-            } else {
+                __syncwarp();
+                continue;
+            }
+            // the last window row / column of a shifted frame wraps around the image: gather with cp.async
 #pragma unroll 4
-                for (int i = 0; i < 32; ++i) {
-                    const int row = i * 4 + sub;
-                    const int t = it.m * 128 + row;
-                    int oy = wy * 16 + (t >> 4) + p.shift, ox = wx * 16 + (t & 15) + p.shift;
-                    if (oy >= p.H) oy -= p.H;
-                    if (ox >= p.W) ox -= p.W;
-                    const long long pix = ((long long)img * p.H + oy) * p.W + ox;
-                    cp_async16(q_dst + row * 128 + ((c8 ^ (row & 7)) << 4), base + pix * p.ld);
-                }
+            for (int i = 0; i < 32; ++i) {
+                const int row = i * 4 + sub;
+                const int t = it.m * 128 + row;
+                int oy = wy * 16 + (t >> 4) + p.shift, ox = wx * 16 + (t & 15) + p.shift;
+                if (oy >= p.H) oy -= p.H;
+                if (ox >= p.W) ox -= p.W;
+                const long long pix = ((long long)img * p.H + oy) * p.W + ox;
+                cp_async16(q_dst + row * 128 + ((c8 ^ (row & 7)) << 4), base + pix * p.ld);
             }
             const uint32_t k_dst = q_dst + kHtQBytes, v_dst = k_dst + kHtKBytes;
-            if (MODE == 0 && !wrap) {
-                const bf16* src = wbase + (long long)(it.c * KR) * rowstep;
-#pragma unroll
-                for (int ty = 0; ty < KR; ++ty) {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const int row = ty * 16 + k * 4 + sub;
-                        const uint32_t off = row * 128 + ((c8 ^ (row & 7)) << 4);
-                        const bf16* sp = src + (long long)(k * 4) * p.ld;
-                        cp_async16(k_dst + off, sp + p.Cq);
-                        cp_async16(v_dst + off, sp + 2 * p.Cq);
-                    }
-                    src += rowstep;
-                }
-            } else {
 #pragma unroll 4
-                for (int i = 0; i < KC / 4; ++i) {
-                    const int row = i * 4 + sub;
-                    int oy, ox;
-                    bool inside = true;
-                    if (MODE == 0) {
-                        const int j = it.c * KC + row;
-                        oy = wy * 16 + (j >> 4) + p.shift;
-                        ox = wx * 16 + (j & 15) + p.shift;
-                        if (oy >= p.H) oy -= p.H;
-                        if (ox >= p.W) ox -= p.W;
-                    } else {
-                        const int kr = row / KW;
-                        oy = wy * 16 - 4 + it.c * KR + kr;
-                        ox = wx * 16 - 4 + (row - kr * KW);
-                        inside = oy >= 0 && oy < p.H && ox >= 0 && ox < p.W;
-                    }
-                    const uint32_t off = row * 128 + ((c8 ^ (row & 7)) << 4);
-                    if (inside) {
-                        const bf16* src = base + (((long long)img * p.H + oy) * p.W + ox) * p.ld;
-                        cp_async16(k_dst + off, src + p.Cq);
-                        cp_async16(v_dst + off, src + 2 * p.Cq);
-                    } else {  // nn.Unfold's zero padding: exact zero key / value vectors
-                        sts_v4(k_dst + off, 0u, 0u, 0u, 0u);
-                        sts_v4(v_dst + off, 0u, 0u, 0u, 0u);
-                    }
+            for (int i = 0; i < KC / 4; ++i) {
+                const int row = i * 4 + sub;
+                int oy, ox;
+                bool inside = true;
+                if (MODE == 0) {
+                    const int j = it.c * KC + row;
+                    oy = wy * 16 + (j >> 4) + p.shift;
+                    ox = wx * 16 + (j & 15) + p.shift;
+                    if (oy >= p.H) oy -= p.H;
+                    if (ox >= p.W) ox -= p.W;
+                } else {
+                    const int kr = row / KW;
+                    oy = wy * 16 - 4 + it.c * KR + kr;
+                    ox = wx * 16 - 4 + (row - kr * KW);
+                    inside = oy >= 0 && oy < p.H && ox >= 0 && ox < p.W;
+                }
+                const uint32_t off = row * 128 + ((c8 ^ (row & 7)) << 4);
+                if (inside) {
+                    const bf16* src = base + (((long long)img * p.H + oy) * p.W + ox) * p.ld;
+                    cp_async16(k_dst + off, src + p.Cq);
+                    cp_async16(v_dst + off, src + 2 * p.Cq);
+                } else {  // nn.Unfold's zero padding: exact zero key / value vectors
+                    sts_v4(k_dst + off, 0u, 0u, 0u, 0u);
+                    sts_v4(v_dst + off, 0u, 0u, 0u, 0u);
                 }
             }
             cp_async_commit();
@@ -486,11 +479,19 @@ bool hat_attention_tc_ok(int dt, long long ld, long long ldo, int H, int W, int 
 template <int MODE, int D2T>
 static int hat_attention_tc_launch(const HtParams& p, int grid, cudaStream_t stream) {
     using Cfg = HtCfg<MODE>;
+    CUtensorMap tm_q, tm_kv;
+    {
+        const uint64_t dims[4] = {uint64_t(3 * p.Cq), uint64_t(p.W), uint64_t(p.H), uint64_t(p.n)};
+        const uint64_t strides[3] = {uint64_t(p.ld) * 2, uint64_t(p.W) * p.ld * 2, uint64_t(p.H) * p.W * p.ld * 2};
+        const uint32_t box_q[4] = {64, 16, 8, 1}, box_kv[4] = {64, uint32_t(Cfg::KW), uint32_t(Cfg::KR), 1};
+        IRB_TRY(make_tmap_bf16_sw(&tm_q, p.qkv, 4, dims, strides, box_q, 128));
+        IRB_TRY(make_tmap_bf16_sw(&tm_kv, p.qkv, 4, dims, strides, box_kv, 128));
+    }
     const size_t smem = 1024 + size_t(kHtStages) * kHtStage + 2 * kHtPBytes + 8 * 32 * 17 * 4 +
                         ((p.heads * Cfg::TR * kHtTabStride + 3) & ~3) * 4 + HB_COUNT * 8 + 64;
     IRB_REQUIRE(smem <= 227 * 1024, "hat_attention_tc: shared memory");
     IRB_SMEM_OPTIN((hat_attention_tc_kernel<MODE, D2T>), 227 * 1024);
-    hat_attention_tc_kernel<MODE, D2T><<<grid, kHtThreads, smem, stream>>>(p);
+    hat_attention_tc_kernel<MODE, D2T><<<grid, kHtThreads, smem, stream>>>(p, tm_q, tm_kv);
     IRB_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
