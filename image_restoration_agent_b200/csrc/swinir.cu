@@ -94,6 +94,25 @@ __global__ void swin_prep_unshuffle_kernel(const float* __restrict__ in, T* __re
             reinterpret_cast<bf16*>(out)[i] = __float2bfloat16_rn(v);
     }
 }
+// UpsampleOneStep's PixelShuffle(s) (network_swinir.py:594-612) + x / img_range + mean (:838):
+// out[b, y*s + i, x*s + j, c] = t[b, y, x, c*s*s + i*s + j] / range + mean[c]
+__global__ void pixel_shuffle_out_kernel(const float* __restrict__ t, float* __restrict__ out, int n, int H, int W, int c,
+                                         int s, float m0, float m1, float m2, float inv_range) {
+    const int Ho = H * s, Wo = W * s;
+    const long long total = (long long)n * Ho * Wo * c;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int ch = int(i % c);
+        long long px = i / c;
+        const int xo = int(px % Wo);
+        px /= Wo;
+        const int yo = int(px % Ho);
+        const long long b = px / Ho;
+        const int y = yo / s, si = yo - y * s, x = xo / s, sj = xo - x * s;
+        const float mean = ch == 0 ? m0 : (ch == 1 ? m1 : m2);
+        out[i] = t[((b * H + y) * W + x) * (long long)(c * s * s) + ch * s * s + si * s + sj] * inv_range + mean;
+    }
+}
 __global__ void crop_nhwc_kernel(const float* __restrict__ in, float* __restrict__ out, int n, int H, int W, int Hc,
                                  int Wc, int c) {
     const long long total = (long long)n * Hc * Wc * c;
@@ -318,9 +337,11 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
         IRB_REQUIRE(d.window_size >= 1 && d.window_size <= 8, "SwinIR: window_size must be <= 8");
     }
     IRB_REQUIRE(d.num_layers >= 1 && d.num_layers <= 16, "SwinIR: 1..16 RSTB layers");
-    IRB_REQUIRE(d.upscale >= 1 && (d.upscale & (d.upscale - 1)) == 0, "SwinIR: upscale must be a power of two");
-    IRB_REQUIRE(d.upsampler == IRB_UPSAMPLER_NONE || d.upscale > 1 || d.upsampler == IRB_UPSAMPLER_PIXELSHUFFLE ||
-                    d.upsampler == IRB_UPSAMPLER_NEAREST_CONV, "SwinIR: bad upsampler");
+    if (d.upsampler == IRB_UPSAMPLER_PIXELSHUFFLE_DIRECT)
+        IRB_REQUIRE(d.upscale >= 2 && d.upscale <= 4 && m->us == 1 && !m->hat, "SwinIR: pixelshuffledirect supports x2 / x3 / x4");
+    else
+        IRB_REQUIRE(d.upscale >= 1 && (d.upscale & (d.upscale - 1)) == 0, "SwinIR: upscale must be a power of two");
+    IRB_REQUIRE(d.upsampler >= IRB_UPSAMPLER_NONE && d.upsampler <= IRB_UPSAMPLER_PIXELSHUFFLE_DIRECT, "SwinIR: bad upsampler");
     if (d.upsampler == IRB_UPSAMPLER_NONE) IRB_REQUIRE(d.upscale == 1, "SwinIR: upsampler '' needs upscale 1");
     if (d.upsampler == IRB_UPSAMPLER_NEAREST_CONV)
         IRB_REQUIRE(d.upscale == 2 || d.upscale == 4 || (d.upscale == 8 && m->us == 8),
@@ -400,6 +421,8 @@ int build_swinir(const irb_model_desc& d, const Blob& blob, int device, Model** 
         if (d.upscale == 8) IRB_TRY(m->load_conv(blob, "conv_up3", 64, 64, m->conv_up3));
         IRB_TRY(m->load_conv(blob, "conv_hr", 64, 64, m->conv_hr));
         IRB_TRY(m->load_conv(blob, "conv_last", d.in_chans, 64, m->conv_last));
+    } else if (d.upsampler == IRB_UPSAMPLER_PIXELSHUFFLE_DIRECT) {
+        IRB_TRY(m->load_conv(blob, "upsample.0", d.upscale * d.upscale * d.in_chans, C, m->conv_last));  // UpsampleOneStep :594-612
     } else {
         IRB_TRY(m->load_conv(blob, "conv_last", d.in_chans, C, m->conv_last));
     }
@@ -446,6 +469,8 @@ void SwinIR::layout(Bump& b, int n, int Hin, int Win, WS& w) {
         w.t64 = b.take(P * 64 * E);
         w.u1 = b.take(P * s * s * 64 * E);
         w.u2 = b.take(P * s * s * 64 * E);
+    } else if (desc.upsampler == IRB_UPSAMPLER_PIXELSHUFFLE_DIRECT) {
+        w.u1 = b.take(P * s * s * cin * 4);  // fp32 [P][s*s*cin] before the shuffle
     }
 }
 
@@ -716,6 +741,14 @@ int SwinIR::forward(const float* in, float* out, int n, int Hin, int Win, void* 
         e.ldr = cin;
         e.res_dt = DT_F32;
         IRB_TRY(conv(conv_last, w.xb, dt, ldC, n, H, W, e, s));
+    } else if (desc.upsampler == IRB_UPSAMPLER_PIXELSHUFFLE_DIRECT) {
+        // x = upsample(x): conv C -> s*s*cin, PixelShuffle(s) (:818-822); the shuffle kernel also applies / img_range + mean
+        IRB_TRY(conv(conv_last, w.xb, dt, ldC, n, H, W, make_epi(w.u1, sc * sc * cin, DT_F32), s));
+        const long long total = P * sc * sc * cin;
+        pixel_shuffle_out_kernel<<<grid_for(total), 256, 0, s>>>(reinterpret_cast<const float*>(w.u1), dst, n, H, W, cin, sc,
+                                                                 mean[0], mean[1], mean[2], 1.0f / desc.img_range);
+        IRB_CHECK_CUDA(cudaGetLastError());
+        prof_mark("pixel_shuffle_out", cin, sc, 0.0, 8.0 * total, s);
     } else if (desc.upsampler == IRB_UPSAMPLER_PIXELSHUFFLE) {
         IRB_TRY(conv(conv_before_up, w.xb, dt, ldC, n, H, W, lrelu_epi(w.t64, 0.01f), s));  // nn.LeakyReLU() :742-743
         const void* cur = w.t64;

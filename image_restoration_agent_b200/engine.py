@@ -14,7 +14,7 @@ from . import _lib
 from ._lib import ARCH_HAT, ARCH_RESTORMER, ARCH_SWINIR, ARCH_XRESTORMER, BF16, F32, ModelDesc, check
 from .weights import state_dict_to_blob
 
-_UPSAMPLER = {"": 0, None: 0, "pixelshuffle": 1, "nearest+conv": 2}
+_UPSAMPLER = {"": 0, None: 0, "pixelshuffle": 1, "nearest+conv": 2, "pixelshuffledirect": 3}
 
 
 def restormer_desc(cfg: dict, precision: int) -> ModelDesc:
@@ -57,8 +57,7 @@ def xrestormer_desc(cfg: dict, precision: int) -> ModelDesc:
 
 def swinir_desc(cfg: dict, precision: int) -> ModelDesc:
     if cfg["upsampler"] not in _UPSAMPLER:
-        raise ValueError(f"upsampler {cfg['upsampler']!r} is not served by irb200 (agent tools use '', "
-                         "'pixelshuffle', 'nearest+conv')")
+        raise ValueError(f"unknown SwinIR upsampler {cfg['upsampler']!r}")
     d = ModelDesc()
     d.arch, d.precision, d.in_chans = ARCH_SWINIR, precision, cfg["in_chans"]
     d.img_size, d.window_size, d.embed_dim = cfg["img_size"], cfg["window_size"], cfg["embed_dim"]

@@ -39,6 +39,7 @@ extern "C" {
 #define IRB_UPSAMPLER_NONE 0         /* denoise / JPEG-CAR tail: x + conv_last(res)   network_swinir.py:832-836 */
 #define IRB_UPSAMPLER_PIXELSHUFFLE 1 /* classical SR                                   network_swinir.py:812-817 */
 #define IRB_UPSAMPLER_NEAREST_CONV 2 /* real-world SR                                  network_swinir.py:823-831 */
+#define IRB_UPSAMPLER_PIXELSHUFFLE_DIRECT 3 /* lightweight SR: one conv + PixelShuffle(s), s in {2, 3, 4}   :818-822 */
 
 typedef struct irb_handle irb_handle;
 

@@ -35,6 +35,10 @@ S_CASES = {
     "swinir_full_color_dn": lambda: configs.swinir_config("color_dn"),
     "swinir_full_classical_x4": lambda: configs.swinir_config("classical_sr", scale=4),
     "swinir_full_realsr_large_x4": lambda: configs.swinir_config("real_sr", scale=4, large_model=True),
+    # lightweight SR: the 'pixelshuffledirect' upsampler (x2, x3 with a ragged 21x30 input, full depth x4)
+    "swinir_small_lightweight_x2": lambda: configs.small_swinir_config("lightweight_sr", scale=2),
+    "swinir_small_lightweight_x3": lambda: configs.small_swinir_config("lightweight_sr", scale=3),
+    "swinir_full_lightweight_x4": lambda: configs.swinir_config("lightweight_sr", scale=4),
     # DiffBIR's stage-1 SwinIR: PixelUnshuffle(8) head, nearest+conv x8 tail; from the imported
     # DiffBIR/model/swinir.py (tools/make_golden_full.py diffbir)
     "diffbir_swinir_small": lambda: configs.small_diffbir_swinir_config(),

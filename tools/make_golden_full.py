@@ -416,6 +416,28 @@ def hat():
 GROUPS["hat"] = hat
 
 
+# ---------------- SwinIR lightweight SR: the 'pixelshuffledirect' upsampler (inference.py:144-150) ----------------
+def lightweight():
+    cases = [("swinir_small_lightweight_x2", configs.small_swinir_config("lightweight_sr", scale=2), (1, 3, 24, 40), 1),
+             ("swinir_small_lightweight_x3", configs.small_swinir_config("lightweight_sr", scale=3), (2, 3, 21, 30), 2),
+             ("swinir_full_lightweight_x4", configs.swinir_config("lightweight_sr", scale=4), (1, 3, 48, 64), 0)]
+    for name, cfg, shape, seed in cases:
+        print(name)
+        sd = synth.swinir_state_dict(cfg, seed=seed)
+        ref = mg.ref_swinir(cfg, sd)
+        x = image_like(512, 512, 3, seed=seed)[..., 30:30 + shape[2], 70:70 + shape[3]].repeat(shape[0], 1, 1, 1).contiguous()
+        if shape[0] > 1:
+            x[1] = x[1].flip(-1)
+        with torch.no_grad():
+            y_ref = ref(x)
+        y_or = swinir_ref.Model(sd, cfg)(x)
+        mg.check(name, y_or, y_ref)
+        mg.save(name, x=x.numpy(), y=y_ref.numpy(), seed=np.int64(seed))
+
+
+GROUPS["lightweight"] = lightweight
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
     torch.set_num_threads(os.cpu_count() or 8)
