@@ -82,6 +82,8 @@ int pwdw_fused_bf16(bool gate, const bf16* x, long long ldx, const float2* stats
 
 // fp32 [rows][cin] (cin <= 4) -> bf16 [rows][8]: channel c = bf16(x), channel cin + c = bf16(x - hi), rest zero
 int split_hi_lo_bf16(const float* x, int cin, bf16* y, long long rows, cudaStream_t stream);
+// fp32 [rows][K] -> bf16 [rows][6K] (h | h | h | m | m | l, x = h + m + l): the A operand of the fp32-mode tensor-core GEMMs
+int split3_bf16(const float* x, long long ldx, bf16* y, long long ldy, long long rows, int K, cudaStream_t stream);
 int nearest_up2(const void* x, int dt, long long ldx, void* y, long long ldy, int Nimg, int H, int W, int C,
                 cudaStream_t stream);
 

@@ -51,7 +51,10 @@ struct Model {
     // (model_serving.py:146-166 has no such assert: the model reflect-pads ragged tiles itself). Restormer always checks.
     int strict_tile = 1;
     int fuse_mlp = 1;   // SwinIR: fc1 -> GELU -> fc2 -> + x as one kernel (mlp_fused.cu) where the shape allows
-    int fuse_pwdw = 0;  // Restormer: 1x1 -> depthwise pairs as one kernel (pwdw_fused.cu); opt-in, see DESIGN.md section 8
+    int fuse_pwdw = 0;
+    // fp32 mode, SwinIR / HAT: linear layers and 3x3 convolutions on the tensor cores with the operands split into three
+    // bf16 terms each (six bf16 products per fp32 product, fp32 accumulation); 0 = fp32 FMA kernels
+    int fp32_tc = 1;  // Restormer: 1x1 -> depthwise pairs as one kernel (pwdw_fused.cu); opt-in, see DESIGN.md section 8
     std::vector<void*> dev_allocs;
     virtual ~Model();
     // model(x) on channels-last fp32 tiles: in [n,H,W,cin] -> out [n,H*s,W*s,cin]
@@ -64,6 +67,7 @@ struct Model {
     // uploads (tracked, freed by the destructor)
     int upload_f32(const float* host, size_t n, float** out);
     int upload_act(const float* host, size_t n, void** out);  // converted to the storage dtype
+    int upload_bf16(const float* host, size_t n, void** out); // always bf16
     int dev_alloc(size_t bytes, void** out);
 };
 

@@ -111,6 +111,16 @@ int Model::upload_act(const float* host, size_t n, void** out) {
     return 0;
 }
 
+int Model::upload_bf16(const float* host, size_t n, void** out) {
+    std::vector<bf16> tmp(n);
+    for (size_t i = 0; i < n; ++i) tmp[i] = __float2bfloat16_rn(host[i]);
+    void* p;
+    IRB_TRY(dev_alloc(n * 2, &p));
+    IRB_CHECK_CUDA(cudaMemcpy(p, tmp.data(), n * 2, cudaMemcpyHostToDevice));
+    *out = p;
+    return 0;
+}
+
 std::vector<float> pack_conv3x3(const BlobTensor& w, int& kpad, int& npad) {
     const int N = int(w.dims[0]), C = int(w.dims[1]);
     kpad = (C + 63) / 64 * 64;
@@ -343,6 +353,10 @@ int irb_set_option(irb_handle* h, const char* key, long long value) {
     }
     if (strcmp(key, "fuse_pwdw") == 0) {
         h->model->fuse_pwdw = value != 0;
+        return 0;
+    }
+    if (strcmp(key, "fp32_tc") == 0) {
+        h->model->fp32_tc = value != 0;
         return 0;
     }
     if (strcmp(key, "strict_tile") == 0) {

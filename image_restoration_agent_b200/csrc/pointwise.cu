@@ -418,6 +418,45 @@ __global__ void __launch_bounds__(256) split_hi_lo_kernel(const float* __restric
     *reinterpret_cast<uint4*>(y + r * 8) = u;
 }
 
+// fp32 [rows][K] -> bf16 [rows][6K] = h | h | h | m | m | l with x = h + m + l (three bf16 terms carry the 24 mantissa
+// bits of x): against weights laid out Wh | Wm | Wl | Wh | Wm | Wh one bf16 GEMM over 6K computes
+// h.Wh + h.Wm + h.Wl + m.Wh + m.Wm + l.Wh, i.e. x.W up to terms of relative size 2^-24 (fp32 accumulation in TMEM).
+__global__ void split3_kernel(const float* __restrict__ x, long long ldx, bf16* __restrict__ y, long long ldy,
+                              long long rows, int K) {
+    const int K2 = K >> 1;
+    const long long total = rows * K2;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / K2;
+        const int c = int(i - r * K2) * 2;
+        const float2 v = *reinterpret_cast<const float2*>(x + r * ldx + c);
+        const bf16 h0 = __float2bfloat16_rn(v.x), h1 = __float2bfloat16_rn(v.y);
+        const float r0 = v.x - __bfloat162float(h0), r1 = v.y - __bfloat162float(h1);   // exact in fp32
+        const bf16 m0 = __float2bfloat16_rn(r0), m1 = __float2bfloat16_rn(r1);
+        const bf16 l0 = __float2bfloat16_rn(r0 - __bfloat162float(m0)), l1 = __float2bfloat16_rn(r1 - __bfloat162float(m1));
+        __nv_bfloat162 h, m, l;
+        h.x = h0; h.y = h1; m.x = m0; m.y = m1; l.x = l0; l.y = l1;
+        __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(y + r * ldy + c);
+        o[0] = h;
+        o[K2] = h;
+        o[2 * K2] = h;
+        o[3 * K2] = m;
+        o[4 * K2] = m;
+        o[5 * K2] = l;
+    }
+}
+
+int split3_bf16(const float* x, long long ldx, bf16* y, long long ldy, long long rows, int K, cudaStream_t stream) {
+    IRB_REQUIRE(K % 2 == 0 && ldx % 2 == 0 && ldy % 2 == 0 && ldy >= 6ll * K, "split3_bf16: K and the row strides must be even");
+    if (rows <= 0) return 0;
+    const long long total = rows * (K / 2);
+    const long long b = ceil_div_ll(total, 256);
+    split3_kernel<<<int(b > 148 * 32 ? 148 * 32 : b), 256, 0, stream>>>(x, ldx, y, ldy, rows, K);
+    IRB_CHECK_CUDA(cudaGetLastError());
+    prof_mark("split3", K, 0, 0.0, double(rows) * K * (4 + 12), stream);
+    return 0;
+}
+
 int split_hi_lo_bf16(const float* x, int cin, bf16* y, long long rows, cudaStream_t stream) {
     IRB_REQUIRE(cin >= 1 && cin <= 4, "split_hi_lo_bf16: cin must be <= 4");
     if (rows <= 0) return 0;

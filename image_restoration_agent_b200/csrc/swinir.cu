@@ -15,7 +15,31 @@ struct LinW {
     float* b;    // [N] fp32 (nullptr = no bias)
     float* cs;   // bf16 mode, LayerNorm folded in: colsum[n] = sum_k bf16(W[n,k] * gain[k]); b then holds b + W.ln_bias
     int N, K, kpad, npad;
+    void* w3 = nullptr;  // fp32 mode: bf16 [npad][k3pad] = Wh | Wm | Wl | Wh | Wm | Wh (W = Wh + Wm + Wl), see split3_bf16
+    int k3pad = 0;
 };
+
+// the three bf16 terms of an fp32 value
+static inline void split3_host(float v, float* t) {
+    t[0] = __bfloat162float(__float2bfloat16_rn(v));
+    const float r1 = v - t[0];
+    t[1] = __bfloat162float(__float2bfloat16_rn(r1));
+    t[2] = __bfloat162float(__float2bfloat16_rn(r1 - t[1]));
+}
+// W [N][K] (row stride ldw) -> [npad][k3pad] with segments Wh | Wm | Wl | Wh | Wm | Wh: pairs with the A segments
+// h | h | h | m | m | l into h.Wh + h.Wm + h.Wl + m.Wh + m.Wm + l.Wh
+static std::vector<float> pack_split3(const float* w, int N, int K, int ldw, int npad, int& k3pad) {
+    static const int term[6] = {0, 1, 2, 0, 1, 0};
+    k3pad = (6 * K + 7) / 8 * 8;
+    std::vector<float> o(size_t(npad) * k3pad, 0.f);
+    for (int n = 0; n < N; ++n)
+        for (int k = 0; k < K; ++k) {
+            float t[3];
+            split3_host(w[size_t(n) * ldw + k], t);
+            for (int sg = 0; sg < 6; ++sg) o[size_t(n) * k3pad + sg * K + k] = t[term[sg]];
+        }
+    return o;
+}
 
 // W [N][K] -> W * diag(gain) in place; colsum of the bf16-rounded result; bias += W . ln_bias
 static void fold_ln(std::vector<float>& w, std::vector<float>& bias, int N, int K, const float* gain,
@@ -40,6 +64,8 @@ struct Conv3W {
     float* b;
     int N, C, kpad, npad;
     int ps;        // PixelShuffle epilogue mode for this conv: 0 none, 1 reference row order, 3 sub-pixel-major rows
+    void* w3 = nullptr;  // fp32 mode: bf16 [npad][9 * kpad3], per tap the six split segments of 6 * C input channels
+    int kpad3 = 0;
 };
 struct ResiW {  // '1conv' (c0 only) or '3conv' (c0 -> lrelu -> lin -> lrelu -> c2)
     Conv3W c0, c2;
@@ -156,11 +182,14 @@ struct SwinIR : Model {
     struct WS {
         float *xin, *out_tmp;
         void *xa, *xb, *ffirst, *ln, *qkv, *attn, *hidden, *q4a, *q4b, *t64, *u1, *u2, *u3;
+        void* a3;                  // fp32 mode: the split A operand of the tensor-core GEMM / convolution in flight
+        size_t a3_bytes;
         void *cab1, *cab;          // HAT: the two CAB convolution outputs
         float *ca_sums, *ca_scale; // HAT: per-slab channel sums, per-image channel scale
         float2* stats;
         bool stats_valid;  // stats already describe the stream the next block normalises (written by the producing GEMM)
     };
+    WS* cur_ws = nullptr;  // the workspace of the forward in flight (fp32 mode: its split buffer)
     void layout(Bump& b, int n, int H0, int W0, WS& w);
     void padded(int H0, int W0, int& H, int& W) const {
         const int m = desc.window_size;
@@ -215,6 +244,10 @@ int SwinIR::load_lin(const Blob& blob, const std::string& name, int N, int K, Li
     IRB_TRY(upload_f32(b0.data(), N, &o.b));
     o.N = N;
     o.K = K;
+    if (dt == DT_F32 && K % 4 == 0) {
+        std::vector<float> w3 = pack_split3(w0.data(), N, K, K, o.npad, o.k3pad);
+        IRB_TRY(upload_bf16(w3.data(), w3.size(), &o.w3));
+    }
     return 0;
 }
 
@@ -248,6 +281,10 @@ int SwinIR::load_qkv(const Blob& blob, const std::string& name, int heads, LinW&
     IRB_TRY(upload_f32(b.data(), b.size(), &o.b));
     o.N = 3 * Cq;
     o.K = C;
+    if (dt == DT_F32 && C % 4 == 0) {
+        std::vector<float> w3 = pack_split3(w.data(), 3 * Cq, C, C, o.npad, o.k3pad);
+        IRB_TRY(upload_bf16(w3.data(), w3.size(), &o.w3));
+    }
     return 0;
 }
 
@@ -277,6 +314,20 @@ int SwinIR::load_conv(const Blob& blob, const std::string& name, int N, int Cin,
         IRB_TRY(upload_act(wsp.data(), wsp.size(), &o.wsplit));
     }
     IRB_TRY(upload_f32(bias.data(), N, &o.b));
+    if (dt == DT_F32 && Cin >= 16 && Cin % 4 == 0) {
+        // w holds [npad][9][kpad] (rows possibly permuted for the PixelShuffle store): split every tap's Cin weights
+        static const int term[6] = {0, 1, 2, 0, 1, 0};
+        o.kpad3 = (6 * Cin + 63) / 64 * 64;
+        std::vector<float> w3(size_t(o.npad) * 9 * o.kpad3, 0.f);
+        for (int n = 0; n < o.npad; ++n)
+            for (int tp = 0; tp < 9; ++tp)
+                for (int c = 0; c < Cin; ++c) {
+                    float t3[3];
+                    split3_host(w[(size_t(n) * 9 + tp) * o.kpad + c], t3);
+                    for (int sg = 0; sg < 6; ++sg) w3[(size_t(n) * 9 + tp) * o.kpad3 + sg * Cin + c] = t3[term[sg]];
+                }
+        IRB_TRY(upload_bf16(w3.data(), w3.size(), &o.w3));
+    }
     return 0;
 }
 
@@ -446,6 +497,22 @@ void SwinIR::layout(Bump& b, int n, int Hin, int Win, WS& w) {
     w.qkv = b.take(P * 3 * Cq * E);
     w.attn = b.take(P * ldC * E);
     w.hidden = b.take(P * hid * E);
+    w.a3 = nullptr;
+    w.a3_bytes = 0;
+    if (dt == DT_F32) {
+        // widest split operand: 6 * hidden per token in the body, 6 * 64 per up-sampled pixel in the tails
+        size_t cols = size_t(6) * (hid > C ? hid : C);
+        size_t rows = P;
+        if (desc.upsampler == IRB_UPSAMPLER_PIXELSHUFFLE || desc.upsampler == IRB_UPSAMPLER_NEAREST_CONV) {
+            const size_t tail = P * s * s * 6 * 64;
+            if (tail > rows * cols) {
+                rows = P * s * s;
+                cols = 6 * 64;
+            }
+        }
+        w.a3_bytes = rows * cols * 2;
+        w.a3 = b.take(w.a3_bytes);
+    }
     w.cab1 = w.cab = nullptr;
     w.ca_sums = w.ca_scale = nullptr;
     if (hat) {
@@ -486,6 +553,12 @@ int SwinIR::gemm(const void* A, long long lda, long long M, const LinW& L, Epi e
     e.bias = L.b;
     if (dt == DT_BF16)
         return tc_gemm((const bf16*)A, lda, int(M), L.K, 1, 0, (const bf16*)L.w, L.kpad, L.N, L.npad, 0, e, s);
+    if (fp32_tc && L.w3 && cur_ws && size_t(M) * 6 * L.K * 2 <= cur_ws->a3_bytes) {
+        // fp32 mode on the tensor cores: x = h + m + l in bf16, six bf16 products per fp32 product (split3_bf16)
+        IRB_TRY(split3_bf16((const float*)A, lda, (bf16*)cur_ws->a3, 6ll * L.K, M, L.K, s));
+        return tc_gemm((const bf16*)cur_ws->a3, 6ll * L.K, int(M), 6 * L.K, 1, 0, (const bf16*)L.w3, L.k3pad, L.N, L.npad, 0,
+                       e, s);
+    }
     return simt_gemm(A, DT_F32, lda, int(M), L.K, 1, 0, (const float*)L.w, L.kpad, L.N, 0, e, s);
 }
 
@@ -494,6 +567,11 @@ int SwinIR::conv(const Conv3W& c, const void* x, int x_dt, long long ldx, int n,
     e.bias = c.b;
     if (dt == DT_BF16 && x_dt == DT_BF16 && c.C >= 16)
         return conv3x3_bf16((const bf16*)x, ldx, n, H, W, c.C, (const bf16*)c.w, c.kpad, c.N, c.npad, e, s);
+    const long long Px = (long long)n * H * W;
+    if (dt == DT_F32 && x_dt == DT_F32 && fp32_tc && c.w3 && cur_ws && size_t(Px) * 6 * c.C * 2 <= cur_ws->a3_bytes) {
+        IRB_TRY(split3_bf16((const float*)x, ldx, (bf16*)cur_ws->a3, 6ll * c.C, Px, c.C, s));
+        return tc_conv3x3((const bf16*)cur_ws->a3, 6ll * c.C, n, H, W, 6 * c.C, (const bf16*)c.w3, c.kpad3, c.N, c.npad, e, s);
+    }
     IRB_REQUIRE(c.wf32 != nullptr, "SwinIR: missing fp32 conv weights");
     return simt_conv3x3(x, x_dt, ldx, n, H, W, c.C, c.wf32, c.kpad, c.N, e, s);
 }
@@ -655,6 +733,7 @@ int SwinIR::forward(const float* in, float* out, int n, int Hin, int Win, void* 
     Bump b(wsp);
     WS w;
     layout(b, n, Hin, Win, w);
+    cur_ws = &w;   // calls on one model are serialised by the caller (Engine's lock): the pointer is per forward
     const long long P = (long long)n * H * W;
     const int sc = tsc;
     if (us > 1) {

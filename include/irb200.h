@@ -107,6 +107,9 @@ void irb_destroy(irb_handle* h);
  *          "fuse_pwdw" (default 0; 1: Restormer blocks with C <= 128 run each 1x1 -> depthwise pair as one kernel,
  *          irb_pwdw_fused — parity-equal but measured slower than the separate kernels);
  *          "fuse_mlp" (SwinIR: fc1 -> GELU -> fc2 -> + x as one kernel, irb_mlp_fused, where the shape allows);
+ *          "fp32_tc" (default 1; SwinIR / HAT in IRB_F32 mode: linear layers and 3x3 convolutions run on the tensor cores
+ *          with both operands split into three bf16 terms, six bf16 products per fp32 product, fp32 accumulation; 0: the
+ *          fp32 FMA kernels);
  *          "strict_tile" (default 1: SwinIR tiles must be a multiple of window_size like inference.py:302; 0: the
  *          Flask service's process_image, model_serving.py:146-166, which has no such assert) */
 int irb_set_option(irb_handle* h, const char* key, long long value);
