@@ -68,6 +68,8 @@ PROTOTYPES = {
     "irb_ocab": (_i, [_vp, _i, _ll, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "irb_mdta_nchunks": (_i, [_i, _i, _i]),
     "irb_mdta_gram": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "irb_mdta_attn_static_max_bytes": (_sz, []),
+    "irb_mdta_attn_static": (_i, [_vp, _i, _ll, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "irb_mdta_attn": (_i, [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp]),
     "irb_stitch": (_i, [_vp, _i, _i, _i, _i, _ip, _ip, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "irb_stitch_rows": (_i, [_vp, _i, _i, _i, _i, _ip, _ip, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),

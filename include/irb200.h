@@ -227,6 +227,20 @@ int irb_mdta_gram(const void* d_qkv, int dtype, long long ld, int n, int P, int 
 int irb_mdta_attn(const float* d_Gpart, const float* d_ssq_part, int nchunks, const float* d_temperature,
                   const float* d_wproj, int n, int C, int heads, void* d_weff, int dtype, float* d_attn,
                   void* stream);
+/* irb_mdta_gram + irb_mdta_attn as ONE call that allocates nothing (no cudaMalloc / cudaFree / allocating library
+ * routine): the per-chunk partial sums live in a file-scope static __device__ array of
+ * irb_mdta_attn_static_max_bytes() = 4 MiB, held by every GPU that loads the library until the process exits.
+ * No counterpart in the reference: added for callers that cannot allocate
+ * (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). The caller still passes the input
+ * (d_qkv, channels-last q | k | v, row stride ld, n images of P pixels) and the outputs (d_weff [n][C][C] in `dtype`,
+ * d_attn fp32 [n][heads][c][c]); results are bit-identical to the existing pair (same kernels).
+ * Limit: n * heads * irb_mdta_nchunks(P, heads, n) * (c*c + 2*c) floats (c = C / heads) must fit in the array; larger
+ * shapes are rejected with an error that names both sizes. Every call shares the array and overwrites it (nothing needs
+ * to start at zero: the Gram kernel writes every slot it later reads): calls that OVERLAP on the GPU (two streams, or
+ * graph branches without a dependency) race on it; serialise them on one stream or with events. */
+size_t irb_mdta_attn_static_max_bytes(void);
+int irb_mdta_attn_static(const void* d_qkv, int dtype, long long ld, int n, int P, int C, int heads,
+                         const float* d_temperature, const float* d_wproj, void* d_weff, float* d_attn, void* stream);
 /* overlap-blend stitch of channels-last fp32 tiles [ny*nx][th*sf][tw*sf][c] (host index lists) */
 int irb_stitch(const float* d_tiles, int c, int th, int tw, int sf, const int* ys, const int* xs, int ny, int nx,
                int h, int w, int crop_h, int crop_w, float* d_out_f32, uint8_t* d_out_u8, int reverse_channels,
