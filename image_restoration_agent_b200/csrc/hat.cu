@@ -270,6 +270,7 @@ __global__ void __launch_bounds__(kPoolThreads) chan_pool4_kernel(const T* __res
     const int t = threadIdx.x;
     if (t < phases * C4) {
         const int ph = t / C4, c = (t - ph * C4) * 4;
+        constexpr int U = 8;  // independent loads in flight per thread
         float4 a[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -282,16 +283,16 @@ __global__ void __launch_bounds__(kPoolThreads) chan_pool4_kernel(const T* __res
             return r;
         };
         long long px = p0 + ph;
-        for (; px + 3 * phases < p1; px += 4 * phases) {
-            float4 v[4];
+        for (; px + (U - 1) * phases < p1; px += U * phases) {
+            float4 v[U];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) v[u] = ld4(px + u * phases);
+            for (int u = 0; u < U; ++u) v[u] = ld4(px + u * phases);
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                a[u].x += v[u].x;
-                a[u].y += v[u].y;
-                a[u].z += v[u].z;
-                a[u].w += v[u].w;
+            for (int u = 0; u < U; ++u) {
+                a[u & 3].x += v[u].x;
+                a[u & 3].y += v[u].y;
+                a[u & 3].z += v[u].z;
+                a[u & 3].w += v[u].w;
             }
         }
         for (; px < p1; px += phases) {
@@ -360,35 +361,45 @@ __global__ void ca_scale_kernel(const float* __restrict__ sums, int slabs, float
     }
 }
 
-// out[p, c] = x[p, c] + y[p, c] * scale[img(p), c]
+// out[p, c] = x[p, c] + y[p, c] * scale[img(p), c]; four channels per thread (8-byte bf16 / 16-byte fp32 accesses)
 template <typename T>
 __global__ void add_scaled_kernel(const T* __restrict__ x, long long ldx, const T* __restrict__ y, long long ldy,
                                   T* __restrict__ out, long long ldo, long long rows, long long hw, int C,
                                   const float* __restrict__ scale) {
-    const int c2 = C >> 1;  // C is even: two channels per thread
-    const long long total = rows * c2;
+    const int c4 = C >> 2;
+    const long long total = rows * c4;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
-        const long long r = i / c2;
-        const int c = int(i - r * c2) * 2;
-        const float* sc = scale + (r / hw) * C + c;
+        const long long r = i / c4;
+        const int c = int(i - r * c4) * 4;
+        const float4 sc = *reinterpret_cast<const float4*>(scale + (r / hw) * C + c);
+        float4 a, b;
         if (sizeof(T) == 4) {
-            const float2 a = *reinterpret_cast<const float2*>(reinterpret_cast<const float*>(x) + r * ldx + c);
-            const float2 b = *reinterpret_cast<const float2*>(reinterpret_cast<const float*>(y) + r * ldy + c);
-            *reinterpret_cast<float2*>(reinterpret_cast<float*>(out) + r * ldo + c) =
-                make_float2(fmaf(b.x, sc[0], a.x), fmaf(b.y, sc[1], a.y));
+            a = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(x) + r * ldx + c);
+            b = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(y) + r * ldy + c);
         } else {
-            const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(reinterpret_cast<const bf16*>(x) + r * ldx + c));
-            const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(reinterpret_cast<const bf16*>(y) + r * ldy + c));
-            *reinterpret_cast<__nv_bfloat162*>(reinterpret_cast<bf16*>(out) + r * ldo + c) =
-                __floats2bfloat162_rn(fmaf(b.x, sc[0], a.x), fmaf(b.y, sc[1], a.y));
+            const uint2 ua = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(x) + r * ldx + c);
+            const uint2 ub = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(y) + r * ldy + c);
+            unpack_bf16x2(ua.x, a.x, a.y);
+            unpack_bf16x2(ua.y, a.z, a.w);
+            unpack_bf16x2(ub.x, b.x, b.y);
+            unpack_bf16x2(ub.y, b.z, b.w);
+        }
+        const float4 o = make_float4(fmaf(b.x, sc.x, a.x), fmaf(b.y, sc.y, a.y), fmaf(b.z, sc.z, a.z), fmaf(b.w, sc.w, a.w));
+        if (sizeof(T) == 4) {
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + r * ldo + c) = o;
+        } else {
+            uint2 uo;
+            uo.x = pack_bf16x2(o.x, o.y);
+            uo.y = pack_bf16x2(o.z, o.w);
+            *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(out) + r * ldo + c) = uo;
         }
     }
 }
 
 int channel_attention_slabs(int n, long long hw) {
     int slabs = int(hw / 256 > 0 ? hw / 256 : 1);
-    const int cap = 148 * 2 / (n > 0 ? n : 1);
+    const int cap = 148 * 4 / (n > 0 ? n : 1);
     if (slabs > cap) slabs = cap > 0 ? cap : 1;
     return slabs;
 }
@@ -428,8 +439,8 @@ int channel_attention_scale(const void* y, int dt, long long ldy, int n, long lo
 
 int add_scaled(const void* x, long long ldx, const void* y, long long ldy, void* out, long long ldo, int dt, long long rows,
                long long hw, int C, const float* scale, cudaStream_t stream) {
-    IRB_REQUIRE(C % 2 == 0 && ldx % 2 == 0 && ldy % 2 == 0 && ldo % 2 == 0, "add_scaled: channel counts must be even");
-    const long long total = rows * (C / 2);
+    IRB_REQUIRE(C % 4 == 0 && ldx % 4 == 0 && ldy % 4 == 0 && ldo % 4 == 0, "add_scaled: channel counts must be multiples of 4");
+    const long long total = rows * (C / 4);
     const long long b = ceil_div_ll(total, 256);
     const int blocks = int(b > 148 * 16 ? 148 * 16 : b);
     if (dt == DT_F32)

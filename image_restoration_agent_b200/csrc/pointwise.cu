@@ -102,7 +102,17 @@ template <typename TI, typename TO>
 static int layernorm_launch(const void* x, long long ldx, void* y, long long ldy, long long rows, int C, const float* w,
                             const float* b, int mode, float eps, cudaStream_t stream) {
     const int nch = C / 4;
-    const int lpp = nch <= 8 ? 8 : (nch <= 16 ? 16 : 32);
+    // lanes per pixel: the group size in {8, 16, 32} (each lane owns up to 4 chunks of 4 channels) that leaves the fewest
+    // idle lane slots: C = 180 -> 45 chunks: 16 lanes x 3 passes (48 slots) instead of 32 x 2 (64 slots, 30 % idle)
+    int lpp = 32, best = 1 << 30;
+    for (int cand = 8; cand <= 32; cand <<= 1) {
+        if (nch > 4 * cand) continue;
+        const int slots = (nch + cand - 1) / cand * cand;
+        if (slots < best) {
+            best = slots;
+            lpp = cand;
+        }
+    }
     const long long threads = rows * lpp;
     const int blocks = int(ceil_div_ll(threads, 256));
     const TI* xi = reinterpret_cast<const TI*>(x);
