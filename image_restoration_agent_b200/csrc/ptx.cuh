@@ -297,6 +297,12 @@ __device__ __forceinline__ void sts_v4(uint32_t addr, uint32_t a, uint32_t b, ui
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 // two packed pairs (4 consecutive floats) from shared memory
+// one f32x2 (two adjacent fp32 words, 8-byte aligned); volatile: the issue order of a batch of these is the program's
+__device__ __forceinline__ f32x2 lds_f32x2(uint32_t addr) {
+    f32x2 v;
+    asm volatile("ld.shared.b64 %0, [%1];" : "=l"(v) : "r"(addr));
+    return v;
+}
 __device__ __forceinline__ void lds_f32x4(uint32_t addr, f32x2& a, f32x2& b) {
     asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "r"(addr));
 }

@@ -30,18 +30,23 @@
 
 namespace irb {
 
-static constexpr int kWaThreads = 13 * 32;      // warp 0: MMA, 1..8: softmax groups A/B, 9..12: loaders
+static constexpr int kWaThreads = 11 * 32;      // warp 0: MMA, 1..8: softmax groups A/B, 9..10: loaders (352 threads: 168 registers each)
 static constexpr int kWaTile = 128 * 128;       // one [128 tokens][64 ch] bf16 operand tile (16 KB)
 static constexpr int kWaStage = 3 * kWaTile;    // Q | K | V
 static constexpr int kWaStages = 2;
 static constexpr int kWaPBytes = 2 * kWaTile;   // P of one head: 2 k-tiles of [128 rows][64 keys]
 static constexpr float kLog2e = 1.4426950408889634f;
-// The (2w-1)^2 = 15 x 15 bias table sits in shared memory with a row stride of 24 words: a warp's 32 tokens are 4
-// rows x 8 columns of a window, their lookups for one key are 4 runs of 8 consecutive words whose starts are then
-// 0 / 24 / 16 / 8 mod 32: conflict-free (with the natural stride 15 every lookup was a 2-way bank conflict, and the
-// kernel is shared-memory-bandwidth bound: 64 lookups per token row and head).
-static constexpr int kWaTabStride = 24;
-static constexpr int kWaTabSize = 15 * kWaTabStride;
+// The (2w-1)^2 = 15 x 15 bias table sits in shared memory MIRRORED in x (column = xj - xi + 7, so the biases of keys
+// xj, xj + 1 of one key row are adjacent words in ascending order) and TWICE per head, the second copy shifted by one
+// word: a token with odd xi reads its (even, odd) key pairs from copy 0, a token with even xi from copy 1, and either
+// way every pair is one aligned LDS.64 with an immediate offset (-yj * 16 + xj) from a per-(token, head) pointer. Row
+// stride 16 and copy offset 246 words make the 16 lanes of a half-warp (2 token rows x 8 columns) hit 32 distinct banks
+// for every key pair (brute-forced; the kernel is sensitive to shared-memory wavefronts: 32 lookups per token and head).
+// Two keys per instruction everywhere else too: packed fma.rn.f32x2 / add.rn.f32x2 (the softmax warps' instruction
+// count, not memory, was what bounded the kernel).
+static constexpr int kWaTabStride = 16;
+static constexpr int kWaTabCopy = 246;
+static constexpr int kWaTabSize = 488;           // words per head (both copies)
 
 struct WaParams {
     const bf16* qkv;
@@ -54,7 +59,11 @@ struct WaParams {
 };
 
 // bar[] layout (uint64 each)
-enum { WB_FULL = 0, WB_EMPTY = 2, WB_SFULL = 4, WB_SEMPTY = 6, WB_PFULL = 8, WB_OFULL = 10, WB_OEMPTY = 12, WB_COUNT = 14 };
+// WB_FULL / WB_EMPTY guard the Q | K halves of a stage (free again as soon as the S MMAs that read them are done),
+// WB_VFULL / WB_VEMPTY its V third (free after the P V MMAs): Q and K of step n + 2 are loaded a whole step earlier than
+// if the stage were released as one
+enum { WB_FULL = 0, WB_EMPTY = 2, WB_SFULL = 4, WB_SEMPTY = 6, WB_PFULL = 8, WB_OFULL = 10, WB_OEMPTY = 12, WB_VFULL = 14,
+       WB_VEMPTY = 16, WB_COUNT = 18 };
 
 __device__ __forceinline__ long long wa_token_pixel(const WaParams& p, int unit, int r, bool& valid, int& masky, int& maskx) {
     // row r of the unit -> window, token, original-frame pixel; masky / maskx: 0 none, 1: token in the first
@@ -100,8 +109,15 @@ __device__ __forceinline__ long long wa_window_pixel(const WaParams& p, const Wa
     return w.valid ? ((long long)w.img * p.H + oy) * p.W + ox : 0;
 }
 
+// tm: 4-D tensor map {channel, x, y, image} over the qkv tensor, box {64, 8, 8, 1} (one window of one head pair), 128-byte
+// swizzle: a window that does not wrap around the image (all but the last window row / column of a shifted frame) is an
+// axis-aligned box and lands in shared memory in the UMMA layout with one TMA load per operand. tm4: the same tensor with
+// box {64, 4, 1, 1} = half a token row: a wrapping window (shift 4) is 16 such boxes, none of which straddles the wrap;
+// TMA derives the swizzle from the destination address, so each lands at its rows of the 1024-byte-aligned tile.
 template <int D2T>
-__global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(const WaParams p) {
+__global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(const WaParams p,
+                                                                            const __grid_constant__ CUtensorMap tm,
+                                                                            const __grid_constant__ CUtensorMap tm4) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* stage_base = smem;                                   // [stages][Q|K|V]
@@ -120,20 +136,23 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
         for (int i = threadIdx.x; i < n16; i += kWaThreads) z[i] = make_uint4(0u, 0u, 0u, 0u);
         for (int i = threadIdx.x; i < p.heads * kWaTabSize; i += kWaThreads) {
             const int h = i / kWaTabSize, e2 = i - h * kWaTabSize;
-            const int ey = e2 / kWaTabStride, ex = e2 - ey * kWaTabStride;
-            if (ex >= 15) {
-                s_table[i] = 0.f;
-                continue;
+            const int copy = e2 >= kWaTabCopy ? 1 : 0;
+            const int w = e2 - copy * (kWaTabCopy + 1);          // copy 1 holds the same words one position later
+            float v = 0.f;
+            if (w >= 0) {
+                const int row = w / kWaTabStride, col = w - row * kWaTabStride;  // row = yi - yj + 7, col = xj - xi + 7
+                if (row < 15 && col < 15) v = __ldg(p.bias_table + (row * 15 + (14 - col)) * p.heads + h) * kLog2e;
             }
-            const int e = ey * 15 + ex;
-            s_table[i] = __ldg(p.bias_table + e * p.heads + h) * kLog2e;
+            s_table[i] = v;
         }
     }
     if (warp == 0) {
         if (lane == 0) {
             for (int s = 0; s < 2; ++s) {
-                mbar_init(&bar[WB_FULL + s], 4);
+                mbar_init(&bar[WB_FULL + s], 1);
                 mbar_init(&bar[WB_EMPTY + s], 1);
+                mbar_init(&bar[WB_VFULL + s], 1);
+                mbar_init(&bar[WB_VEMPTY + s], 1);
                 mbar_init(&bar[WB_SFULL + s], 1);
                 mbar_init(&bar[WB_SEMPTY + s], 4);
                 mbar_init(&bar[WB_PFULL + s], 4);
@@ -155,54 +174,43 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
     // TMEM columns: S of group g at g*128, O of group g at 256 + g*64
 
     if (warp >= 9) {
-        // ===================== loaders: warp lw owns token rows lw*32 .. +31 =====================
-        // 8 consecutive lanes fetch the 8 16-byte chunks of ONE row's 128-byte line (4 rows per instruction), so a
-        // warp-wide cp.async touches 4 cache lines instead of 32: the L1 tag stage handles one line per cycle, and
-        // with lane = row it was the bottleneck of the kernel (3072 tag cycles per stage).
-        const int lw = warp - 9;
-        const int c = lane & 7;
-        const int sub = lane >> 3;
-        int cnt = 0;
-        for (int u = blockIdx.x; u < p.units; u += gridDim.x) {
-            long long poff[8];
-            const WaWindow win = wa_window(p, u * 2 + (lw >> 1));  // the warp's 32 rows are half a window
-            const uint32_t vmask = win.valid ? 0xffu : 0u;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) poff[i] = wa_window_pixel(p, win, lw * 32 + i * 4 + sub) * p.ld + c * 8;
-            // The two-stage ring covers one head pair of look-ahead, less than the DRAM latency under load: pull the
-            // rows of this CTA's NEXT unit (all heads: 3 * Cq bf16 = whole 128-byte lines) into L2 now, a full unit
-            // (3 head pairs) ahead, so the cp.async gathers below only ever see L2 latency.
-            if (u + (int)gridDim.x < p.units) {
-                const int nlines = (3 * p.Cq) >> 6;
-                const WaWindow wnx = wa_window(p, (u + (int)gridDim.x) * 2 + (lw >> 1));
-                if (wnx.valid) {
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const long long pix = wa_window_pixel(p, wnx, lw * 32 + i * 4 + sub);
-                        for (int l = c; l < nlines; l += 8) prefetch_l2(p.qkv + pix * p.ld + l * 64);
+        // ===================== loaders: warp 9 streams Q | K, warp 10 streams V =====================
+        // One lane per stream issues TMA loads: one box per window and operand, or 16 half-row boxes for a window in the
+        // last window row / column of a shifted frame, which wraps around the image (the cyclic shift of :243-247).
+        const int lw = warp - 9;             // 0: Q | K, 1: V
+        const int nt = lw == 0 ? 2 : 1;      // operand tiles of this warp's stream
+        const int t0 = lw == 0 ? 0 : 2;
+        uint64_t* full = &bar[lw == 0 ? WB_FULL : WB_VFULL];
+        uint64_t* empty = &bar[lw == 0 ? WB_EMPTY : WB_VEMPTY];
+        if (lane == 0) {
+            int cnt = 0;
+            for (int u = blockIdx.x; u < p.units; u += gridDim.x) {
+                const WaWindow w0 = wa_window(p, u * 2), w1 = wa_window(p, u * 2 + 1);
+                for (int hp = 0; hp < npairs; ++hp, ++cnt) {
+                    const int s = cnt & 1;
+                    mbar_wait(&empty[s], ((cnt >> 1) & 1) ^ 1);
+                    uint8_t* st = stage_base + s * kWaStage;
+                    mbar_arrive_expect_tx(&full[s], (w1.valid ? 2 : 1) * nt * 8192);
+                    for (int wi = 0; wi < 2; ++wi) {
+                        const WaWindow& w = wi ? w1 : w0;
+                        if (!w.valid) continue;
+                        const bool wrap = p.shift > 0 && (w.wy == p.nwy - 1 || w.wx == p.nwx - 1);
+                        for (int t = t0; t < t0 + nt; ++t) {
+                            uint8_t* dst = st + t * kWaTile + wi * 8192;
+                            const int ch = t * p.Cq + hp * 64;
+                            if (!wrap) {
+                                tma_load_4d(dst, &tm, &full[s], ch, w.wx * 8 + p.shift, w.wy * 8 + p.shift, w.img);
+                            } else {
+                                for (int hr = 0; hr < 16; ++hr) {  // token row ty = hr >> 1, tokens tx = 4 * (hr & 1) .. + 3
+                                    int oy = w.wy * 8 + (hr >> 1) + p.shift, ox = w.wx * 8 + (hr & 1) * 4 + p.shift;
+                                    if (oy >= p.H) oy -= p.H;
+                                    if (ox >= p.W) ox -= p.W;
+                                    tma_load_4d(dst + hr * 512, &tm4, &full[s], ch, ox, oy, w.img);
+                                }
+                            }
+                        }
                     }
                 }
-            }
-            for (int hp = 0; hp < npairs; ++hp, ++cnt) {
-                const int s = cnt & 1;
-                if (lane == 0) mbar_wait(&bar[WB_EMPTY + s], ((cnt >> 1) & 1) ^ 1);
-                __syncwarp();
-                const uint32_t dst0 = smem_u32(stage_base + s * kWaStage) + lw * 32 * 128;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    if (vmask & (1u << i)) {
-                        const int rl = i * 4 + sub;  // row inside the warp's 32
-                        const uint32_t dst = dst0 + rl * 128 + ((c ^ (rl & 7)) << 4);
-                        const bf16* src = p.qkv + poff[i] + hp * 64;
-#pragma unroll
-                        for (int t = 0; t < 3; ++t) cp_async16(dst + t * kWaTile, src + t * p.Cq);
-                    }
-                }
-                cp_async_commit();
-                cp_async_wait<0>();   // the other stage is being consumed meanwhile: the ring hides this latency
-                fence_proxy_async();  // generic-proxy writes -> visible to the tensor core's async-proxy reads
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&bar[WB_FULL + s]);
             }
         }
     } else if (warp == 0) {
@@ -220,7 +228,7 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
             // so every head pair paid a full gather latency.
             int s_next = 0, pv_next = 0;
             bool s_done[2] = {false, false}, pv_done[2] = {false, false};
-            bool s_loaded = false;
+            bool s_loaded = false, v_loaded = false;
             uint32_t spins = 0;
             while (pv_next < my_pairs) {
                 bool progress = false;
@@ -244,13 +252,16 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                             progress = true;
                         }
                         if (s_done[0] && s_done[1]) {
+                            umma_commit(&bar[WB_EMPTY + st]);  // Q, K of this stage are no longer read
                             s_done[0] = s_done[1] = false;
                             s_loaded = false;
                             ++s_next;
                         }
                     }
                 }
-                if (pv_next < s_next) {
+                if (pv_next < s_next && !v_loaded && IRB_MMA_POLL(&bar[WB_VFULL + (pv_next & 1)], (pv_next >> 1) & 1))
+                    v_loaded = true;
+                if (pv_next < s_next && v_loaded) {
                     const int st = pv_next & 1;
                     const uint32_t v_addr = smem_u32(stage_base + st * kWaStage) + 2 * kWaTile;
                     for (int g = 0; g < 2; ++g) {
@@ -270,8 +281,9 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                         progress = true;
                     }
                     if (pv_done[0] && pv_done[1]) {
-                        umma_commit(&bar[WB_EMPTY + st]);  // Q, K, V of this stage are no longer read
+                        umma_commit(&bar[WB_VEMPTY + st]);  // V of this stage is no longer read
                         pv_done[0] = pv_done[1] = false;
+                        v_loaded = false;
                         ++pv_next;
                     }
                 }
@@ -326,7 +338,14 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
         float inv_s = 0.f;
         // S(cnt) row from TMEM -> unnormalised probabilities (bf16 pairs) in pk, 1 / sum in inv_s
         auto softmax_phase = [&](int cnt, int h) {
-            const float* tab = s_table + h * kWaTabSize + (yi + 7) * kWaTabStride + xi + 7;
+            const int copy = (xi & 1) ^ 1;
+            const uint32_t tab = smem_u32(s_table + h * kWaTabSize + copy * (kWaTabCopy + 1) + (yi + 7) * kWaTabStride + (7 - xi));
+            // the bias pairs do not depend on S: the first half is in flight while this warp waits for the S barrier, the
+            // second half while the first is consumed (left to the compiler, every LDS fed the next FFMA2 through ONE
+            // register pair: 32 shared-memory round trips in series, ncu r02_s33)
+            f32x2 bq[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) bq[k] = lds_f32x2(tab + 4 * (((k & 3) * 2) - (k >> 2) * kWaTabStride));
             mbar_wait(&bar[WB_SFULL + g], cnt & 1);
             tc_fence_after();
             uint32_t sr[64];
@@ -336,28 +355,50 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&bar[WB_SEMPTY + g]);
-            float t[64];
-            float mx_ = -INFINITY;
+            f32x2 t2[32];
+            const f32x2 l2e = splat2(kLog2e);
 #pragma unroll
-            for (int j = 0; j < 64; ++j) {
-                const int yj = j >> 3, xj = j & 7;
-                t[j] = fmaf(__uint_as_float(sr[j]), kLog2e, tab[-(yj * kWaTabStride + xj)]);
-            }
+            for (int k = 0; k < 16; ++k)
+                t2[k] = fma2(pack2(__uint_as_float(sr[2 * k]), __uint_as_float(sr[2 * k + 1])), l2e, bq[k]);
+#pragma unroll
+            for (int k = 16; k < 32; ++k) bq[k - 16] = lds_f32x2(tab + 4 * (((k & 3) * 2) - (k >> 2) * kWaTabStride));
+#pragma unroll
+            for (int k = 16; k < 32; ++k)
+                t2[k] = fma2(pack2(__uint_as_float(sr[2 * k]), __uint_as_float(sr[2 * k + 1])), l2e, bq[k - 16]);
             if (any_mask) {
+                const f32x2 q00 = splat2(m00), q01 = splat2(m01), q10 = splat2(m10), q11 = splat2(m11);
 #pragma unroll
-                for (int j = 0; j < 64; ++j) {
-                    const int yj = j >> 3, xj = j & 7;
-                    t[j] += (yj >= 4) ? ((xj >= 4) ? m11 : m10) : ((xj >= 4) ? m01 : m00);
+                for (int k = 0; k < 32; ++k) {
+                    const int yj = k >> 2, xj = (k & 3) * 2;
+                    t2[k] = add2(t2[k], (yj >= 4) ? ((xj >= 4) ? q11 : q10) : ((xj >= 4) ? q01 : q00));
                 }
             }
+            float mxs[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four independent chains
 #pragma unroll
-            for (int j = 0; j < 64; ++j) mx_ = fmaxf(mx_, t[j]);
-            float sum = 0.f;
+            for (int k = 0; k < 32; ++k) {
+                float a, b;
+                unpack2(t2[k], a, b);
+                mxs[k & 3] = fmaxf(mxs[k & 3], fmaxf(a, b));
+            }
+            const float mx_ = fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3]));
+            const f32x2 nmx = splat2(-mx_);
+            f32x2 s2a = pack2(0.f, 0.f), s2b = pack2(0.f, 0.f);
 #pragma unroll
-            for (int j = 0; j < 64; j += 2) {
-                const float e0 = ex2_approx(t[j] - mx_), e1 = ex2_approx(t[j + 1] - mx_);
-                sum += e0 + e1;
-                pk[j >> 1] = pack_bf16x2(e0, e1);
+            for (int k = 0; k < 32; ++k) {
+                float a, b;
+                unpack2(add2(t2[k], nmx), a, b);
+                const float e0 = ex2_approx(a), e1 = ex2_approx(b);
+                if (k & 1)
+                    s2b = add2(s2b, pack2(e0, e1));
+                else
+                    s2a = add2(s2a, pack2(e0, e1));
+                pk[k] = pack_bf16x2(e0, e1);
+            }
+            float sum;
+            {
+                float a, b;
+                unpack2(add2(s2a, s2b), a, b);
+                sum = a + b;
             }
             inv_s = 1.0f / sum;
         };
@@ -472,12 +513,20 @@ int window_attention_tc(const bf16* qkv, long long ld, bf16* out, long long ldo,
     IRB_SMEM_OPTIN((window_attention_tc_kernel<0>), 227 * 1024);
     IRB_SMEM_OPTIN((window_attention_tc_kernel<15>), 227 * 1024);
     IRB_SMEM_OPTIN((window_attention_tc_kernel<16>), 227 * 1024);
+    CUtensorMap tm, tm4;
+    {
+        const uint64_t dims[4] = {uint64_t(3 * p.Cq), uint64_t(W), uint64_t(H), uint64_t(n)};
+        const uint64_t strides[3] = {uint64_t(ld) * 2, uint64_t(W) * ld * 2, uint64_t(H) * W * ld * 2};
+        const uint32_t box[4] = {64, 8, 8, 1}, box4[4] = {64, 4, 1, 1};
+        IRB_TRY(make_tmap_bf16_sw(&tm, qkv, 4, dims, strides, box, 128));
+        IRB_TRY(make_tmap_bf16_sw(&tm4, qkv, 4, dims, strides, box4, 128));
+    }
     if (p.d == 30)
-        window_attention_tc_kernel<15><<<grid, kWaThreads, smem, stream>>>(p);
+        window_attention_tc_kernel<15><<<grid, kWaThreads, smem, stream>>>(p, tm, tm4);
     else if (p.d == 32)
-        window_attention_tc_kernel<16><<<grid, kWaThreads, smem, stream>>>(p);
+        window_attention_tc_kernel<16><<<grid, kWaThreads, smem, stream>>>(p, tm, tm4);
     else
-        window_attention_tc_kernel<0><<<grid, kWaThreads, smem, stream>>>(p);
+        window_attention_tc_kernel<0><<<grid, kWaThreads, smem, stream>>>(p, tm, tm4);
     IRB_CHECK_CUDA(cudaGetLastError());
     const double px = double(n) * H * W;
     prof_mark("window_attention_tc", C, shift, 4.0 * px * 64 * C, px * (3.0 * p.Cq + C) * 2, stream);
