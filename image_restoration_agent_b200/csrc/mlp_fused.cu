@@ -11,17 +11,29 @@
 //   warp 16 (TMA)  : x tile [128][C] -> A (K-major, 128B swizzle, 2 buffers); per 64-column group g of the hidden
 //                    layer: W1' rows [64g, 64g+64) -> ring (2), W2 columns [64g, 64g+64) -> ring (2). Weights stream
 //                    from L2 for every tile (276 KB per 128 tokens at C = 180; they do not fit next to the tiles).
-//   warp 17 (MMA)  : D1[g & 1] (TMEM [128 x 64]) = A . W1'_g^T ; D2[tile & 1] (TMEM [128 x Npad]) += A2_g . W2_g^T, issued
-//                    one group behind D1 so that the conversion of group g overlaps the first GEMM of group g + 1
+//   warp 17 (MMA)  : D1[g & 1] (TMEM [128 x 64]) = A . W1'_g^T ; D2[tile & 1] (TMEM [128 x Npad]) += A2_g . W2_g^T with
+//                    A2_g read FROM TENSOR MEMORY (tcgen05.mma with a TMEM A operand); a polling issue loop over two
+//                    cursors, the first GEMM at most one group ahead of the second (A2 sits in D1's columns)
 //   warps 0-15     : convert: D1 -> folded LayerNorm (rstd * acc + (-mu rstd) * colsum + b1') -> tanh-form GELU -> bf16
-//                    -> A2[g & 1] (K-major swizzled UMMA operand in shared memory); warp w: TMEM lane quarter w & 3,
-//                    columns 16 (w >> 2) .. +15 (8 warps left the SM at IPC 1.5: the GELU chains need more warps in flight).
+//                    pairs written back IN PLACE over the first 8 of the thread's 16 accumulator columns (tcgen05.st):
+//                    the GELU output never touches shared memory. Warp w: TMEM lane quarter w & 3, columns
+//                    16 (w >> 2) .. +15 = one K = 16 step of the second GEMM.
 //                    epilogue: D2 -> + b2 + residual (read from the A tile that is still in shared memory: the residual
 //                    IS the GEMM input) -> LayerNorm statistics of the new row -> bf16 written IN PLACE into the A tile
 //   warp 18 (store): TMA-stores the A tile back to x (same tensor map as the load), then frees the A buffer
+// Measured per tile with the clock trace (-DIRB_MLP_DBG=5): six groups of ~1 450 cycles (D1 wait 240, TMEM load 240,
+// GELU + TMEM store 650, the rest barriers) and an epilogue of ~4 800 (D2 wait 1 100, 98 KB of TMEM reads + residual +
+// statistics 3 000, barriers 600).
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
+
+#if defined(IRB_MLP_DBG) && IRB_MLP_DBG == 5  // timing experiment: clock() trace of warp 0 / lane 0 of CTA 0, printed at exit
+#include <cstdio>
+#define IRB_TS(i) do { if (trace && nts < 160) { tsv[nts] = clock64(); tsi[nts++] = (i); } } while (0)
+#else
+#define IRB_TS(i) do { } while (0)
+#endif
 
 namespace irb {
 
@@ -30,7 +42,7 @@ static constexpr int kMfCG = kMfWarps / 4;               // column groups
 static constexpr int kMfThreads = (kMfWarps + 3) * 32;  // 608
 static constexpr int kMfATile = 128 * 128;               // one 64-channel K chunk of a 128-token tile (16 KB)
 static constexpr int kMfW1Slab = 64 * 128;               // 64 hidden rows x 64 K (8 KB)
-static constexpr int kMfA2 = 128 * 128;                  // 128 tokens x 64 hidden columns (16 KB)
+static constexpr int kMfAux = 16 * 1024;                 // per-column vectors + LayerNorm partial sums
 
 struct alignas(64) MlpParams {
     CUtensorMap tmX;   // x {C, P, 1}, box {64, 128, 1}: load and in-place store
@@ -58,10 +70,22 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
     const int KS = p.KS, NG = p.NG;
     uint8_t* sA = smem;                                   // 2 x KS x 16 KB
     uint8_t* sW1 = sA + 2 * KS * kMfATile;                // 2 x KS x 8 KB
-    uint8_t* sA2 = sW1 + 2 * KS * kMfW1Slab;              // 2 x 16 KB
-    uint8_t* sW2 = sA2 + 2 * kMfA2;                       // 2 x NB x 128 B
+    uint8_t* sAux = sW1 + 2 * KS * kMfW1Slab;             // 16 KB
+    uint8_t* sW2 = sAux + kMfAux;                         // 2 x NB x 128 B
     const int w2_bytes = p.NB * 128;
-    uint8_t* sRed = sA2;  // [kMfCG - 1][128] float2 partial LayerNorm sums; aliases A2, which is idle during an epilogue
+    uint8_t* sRed = sAux;  // [kMfCG - 1][128] float2 partial LayerNorm sums (3 KB)
+    // The per-column vectors (colsum | b1' padded to NG * 64, then b2 padded to NB) live in shared memory. Read through
+    // __ldg they cost 1 000 - 1 500 cycles per group and 3 500 - 5 000 per epilogue (clock trace of a conversion warp,
+    // DESIGN.md section 5): with 231 KB of shared memory carved out almost no L1 is left, every such load went to L2, and
+    // its latency sat on the conversion chain. The room is what the GELU output used to occupy: it now stays in tensor memory.
+    float* sVec = reinterpret_cast<float*>(sAux + 4096);
+    float* sVecB1 = sVec + NG * 64;
+    float* sVecB2 = sVec + 2 * NG * 64;
+    for (int i = threadIdx.x; i < NG * 64; i += kMfThreads) {
+        sVec[i] = i < p.hid ? __ldg(p.cs1 + i) : 0.f;
+        sVecB1[i] = i < p.hid ? __ldg(p.b1 + i) : 0.f;
+    }
+    for (int i = threadIdx.x; i < p.NB; i += kMfThreads) sVecB2[i] = i < p.C ? __ldg(p.b2 + i) : 0.f;
     MfBars* bars = reinterpret_cast<MfBars*>(sW2 + 2 * w2_bytes);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -123,51 +147,89 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
         }
     } else if (warp == kMfWarps + 1) {
         // ================= MMA issuer =================
+        // One thread, a polling issue loop over two independent cursors: G1 = next first-GEMM group, G2 = next second-GEMM
+        // group (G2 < G1). With blocking waits in program order (MMA1(G), then MMA2(G - 1)) the thread sat in MMA2(G - 1)'s
+        // wait for the conversion of G - 1 and could not issue MMA1(G + 1), whose accumulator buffer had been free since
+        // that conversion STARTED: the conversion warps then waited for D1 (ncu r02_s38: 10 % of their samples on d1_full,
+        // 30 % of the issuer's on a2_full). Descriptors are built once; inside the loop a descriptor is a 32-bit add.
         if (elect_one()) {
             const uint32_t idesc1 = make_idesc_bf16(128, 64, 0, 0);
             const uint32_t idesc2 = make_idesc_bf16(128, p.NB, 0, 0);
-            const uint32_t a_base = smem_u32(sA), w1_base = smem_u32(sW1), a2_base = smem_u32(sA2), w2_base = smem_u32(sW2);
-            int it = 0, G = 0;
-            auto mma2 = [&](int Gp, int gp, uint32_t d2) {  // D2 += A2[Gp & 1] . W2[Gp & 1]^T  (K = 64)
-                const int s = Gp & 1;
-                const uint32_t ph = (Gp >> 1) & 1;
-                mbar_wait(&bars->a2_full[s], ph);
-                mbar_wait(&bars->w2_full[s], ph);
-                tc_fence_after();
-                const uint64_t ad = make_sdesc_sw128(a2_base + s * kMfA2, 16, 1024);
-                const uint64_t bd = make_sdesc_sw128(w2_base + s * w2_bytes, 16, 1024);
-#pragma unroll
-                for (int k = 0; k < 4; ++k) umma_bf16(d2, ad + uint64_t(k * 2), bd + uint64_t(k * 2), idesc2, (gp | k) != 0 ? 1u : 0u);
-                umma_commit(&bars->a2_empty[s]);
-                umma_commit(&bars->w2_empty[s]);
-            };
-            for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
-                const int ab = it & 1;
-                const uint32_t d2 = tmem_base + d2_col0 + ab * 192;
-                mbar_wait(&bars->a_full[ab], (it >> 1) & 1);
-                mbar_wait(&bars->d2_empty[ab], ((it >> 1) & 1) ^ 1);
-                tc_fence_after();
-                for (int g = 0; g < NG; ++g, ++G) {
-                    const int s = G & 1;
-                    const uint32_t ph = (G >> 1) & 1;
-                    mbar_wait(&bars->w1_full[s], ph);
-                    mbar_wait(&bars->d1_empty[s], ph ^ 1);
-                    tc_fence_after();
-                    const uint32_t d1 = tmem_base + s * 64;
-                    for (int ks = 0; ks < KS; ++ks) {
-                        const int nk = ks == KS - 1 ? p.klast : 4;
-                        const uint64_t ad = make_sdesc_sw128(a_base + (ab * KS + ks) * kMfATile, 16, 1024);
-                        const uint64_t bd = make_sdesc_sw128(w1_base + (s * KS + ks) * kMfW1Slab, 16, 1024);
+            const uint64_t a_desc0 = make_sdesc_sw128(smem_u32(sA), 16, 1024);
+            const uint64_t w1_desc0 = make_sdesc_sw128(smem_u32(sW1), 16, 1024);
+            const uint64_t w2_desc0 = make_sdesc_sw128(smem_u32(sW2), 16, 1024);
+            const uint32_t w2_step = uint32_t(w2_bytes) >> 4;
+            int my_tiles = 0;
+            for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) ++my_tiles;
+            const int total = my_tiles * NG;
+            int G1 = 0, it1 = 0, g1 = 0;   // first GEMM: global group counter, tile iteration, group inside the tile
+            int G2 = 0, it2 = 0, g2 = 0;   // second GEMM
+            bool a_ok = false, w1_ok = false, d1_ok = false, a2_ok = false, w2_ok = false, d2_ok = false;
+            uint32_t spins = 0;
+            while (G2 < total) {
+                bool progress = false;
+                if (G2 < G1) {  // ---- D2 += A2[G2 & 1] . W2[G2 & 1]^T  (K = 64) ----
+                    const int s = G2 & 1, ab = it2 & 1;
+                    const uint32_t ph = (G2 >> 1) & 1;
+                    if (!a2_ok && mbar_test_wait(&bars->a2_full[s], ph)) a2_ok = true;
+                    if (!w2_ok && mbar_test_wait(&bars->w2_full[s], ph)) w2_ok = true;
+                    if (!d2_ok && (g2 != 0 || mbar_test_wait(&bars->d2_empty[ab], ((it2 >> 1) & 1) ^ 1))) d2_ok = true;
+                    if (a2_ok && w2_ok && d2_ok) {
+                        tc_fence_after();
+                        const uint32_t d2 = tmem_base + d2_col0 + ab * 192;
+                        const uint64_t bd = w2_desc0 + uint64_t(uint32_t(s) * w2_step);
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            if (k < nk) umma_bf16(d1, ad + uint64_t(k * 2), bd + uint64_t(k * 2), idesc1, (ks | k) != 0 ? 1u : 0u);
+                            umma_bf16_ts(d2, tmem_base + s * 64 + k * 16, bd + uint64_t(k * 2), idesc2, (g2 | k) != 0 ? 1u : 0u);
+                        umma_commit(&bars->a2_empty[s]);
+                        umma_commit(&bars->w2_empty[s]);
+                        if (g2 == NG - 1) umma_commit(&bars->d2_full[ab]);
+                        a2_ok = w2_ok = d2_ok = false;
+                        ++G2;
+                        if (++g2 == NG) {
+                            g2 = 0;
+                            ++it2;
+                        }
+                        progress = true;
                     }
-                    umma_commit(&bars->w1_empty[s]);
-                    umma_commit(&bars->d1_full[s]);
-                    if (g > 0) mma2(G - 1, g - 1, d2);
                 }
-                mma2(G - 1, NG - 1, d2);
-                umma_commit(&bars->d2_full[ab]);
+                if (G1 < total && G1 - G2 <= 1) {
+                    const int s = G1 & 1, ab = it1 & 1;
+                    const uint32_t ph = (G1 >> 1) & 1;
+                    if (!a_ok && (g1 != 0 || mbar_test_wait(&bars->a_full[ab], (it1 >> 1) & 1))) a_ok = true;
+                    if (!w1_ok && mbar_test_wait(&bars->w1_full[s], ph)) w1_ok = true;
+                    if (!d1_ok && mbar_test_wait(&bars->d1_empty[s], ph ^ 1)) d1_ok = true;
+                    if (a_ok && w1_ok && d1_ok) {
+                        tc_fence_after();
+                        const uint32_t d1 = tmem_base + s * 64;
+                        uint64_t ad = a_desc0 + uint64_t(uint32_t(ab * KS) * (kMfATile >> 4));
+                        uint64_t bd = w1_desc0 + uint64_t(uint32_t(s * KS) * (kMfW1Slab >> 4));
+                        for (int ks = 0; ks < KS; ++ks) {
+                            const int nk = ks == KS - 1 ? p.klast : 4;
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                if (k < nk) umma_bf16(d1, ad + uint64_t(k * 2), bd + uint64_t(k * 2), idesc1, (ks | k) != 0 ? 1u : 0u);
+                            ad += kMfATile >> 4;
+                            bd += kMfW1Slab >> 4;
+                        }
+                        umma_commit(&bars->w1_empty[s]);
+                        umma_commit(&bars->d1_full[s]);
+                        w1_ok = d1_ok = false;
+                        ++G1;
+                        if (++g1 == NG) {
+                            g1 = 0;
+                            ++it1;
+                            a_ok = false;
+                        }
+                        progress = true;
+                    }
+                }
+                if (progress) {
+                    spins = 0;
+                } else {
+                    __nanosleep(20);
+                    if (++spins > (1u << 24)) __trap();  // protocol bug: fail the launch instead of hanging
+                }
             }
         }
     } else if (warp == kMfWarps + 2) {
@@ -194,13 +256,26 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
         const uint32_t rx = uint32_t(r & 7);   // swizzle term of this row
         const uint32_t lane_t = uint32_t(q * 32) << 16;
         float2* red = reinterpret_cast<float2*>(sRed);
+#if defined(IRB_MLP_DBG) && IRB_MLP_DBG == 5
+        const bool trace = blockIdx.x == 0 && threadIdx.x == 0;
+        long long tsv[160];
+        int tsi[160];
+        int nts = 0;
+#endif
         int it = 0, G = 0;
+        // (mu, rstd) of this thread's row, fetched one tile ahead
+        float2 st_next = make_float2(0.f, 1.f);
+        if ((long long)blockIdx.x * 128 + r < p.P) st_next = __ldg(p.stats_in + (long long)blockIdx.x * 128 + r);
         for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
             const int ab = it & 1;
             const long long grow = (long long)tile * 128 + r;
             const bool valid = grow < p.P;
-            float2 st = make_float2(0.f, 1.f);
-            if (valid) st = __ldg(p.stats_in + grow);
+            const float2 st = st_next;
+            {
+                const long long gnext = grow + (long long)gridDim.x * 128;
+                st_next = make_float2(0.f, 1.f);
+                if (tile + (int)gridDim.x < p.tiles && gnext < p.P) st_next = __ldg(p.stats_in + gnext);
+            }
             const f32x2 a2v = splat2(st.y), b2v = splat2(-st.x * st.y);
             for (int g = 0; g < NG; ++g, ++G) {
                 const int s = G & 1;
@@ -211,41 +286,44 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
 #pragma unroll
                 for (int i = 0; i < CW / 4; ++i) {
                     const int col = col0 + i * 4;
-                    float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f), t4 = c4;
-                    if (col < p.hid) {  // hid % 4 == 0
-                        c4 = __ldg(reinterpret_cast<const float4*>(p.cs1 + col));
-                        t4 = __ldg(reinterpret_cast<const float4*>(p.b1 + col));
-                    }
+                    const float4 c4 = *reinterpret_cast<const float4*>(sVec + col);
+                    const float4 t4 = *reinterpret_cast<const float4*>(sVecB1 + col);
                     tbv[2 * i] = fma2(b2v, pack2(c4.x, c4.y), pack2(t4.x, t4.y));      // (-mu rstd) * colsum + b1'
                     tbv[2 * i + 1] = fma2(b2v, pack2(c4.z, c4.w), pack2(t4.z, t4.w));
                 }
+                IRB_TS(0);
                 mbar_wait(&bars->d1_full[s], ph);
+                IRB_TS(1);
                 tc_fence_after();
                 uint32_t acc[CW];
                 tmem_ld16_nowait(tmem_base + s * 64 + ch * CW + lane_t, acc);
                 mbar_wait(&bars->a2_empty[s], ph ^ 1);  // the second GEMM of group G - 2 has read this A2 buffer
+                IRB_TS(2);
                 tmem_ld_wait();
+                IRB_TS(3);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bars->d1_empty[s]);  // the accumulator is in registers: D1[s] is free
-                const uint32_t row = smem_u32(sA2) + s * kMfA2 + r * 128;
+                uint32_t pk[CW / 2];
 #pragma unroll
-                for (int c8 = 0; c8 < CW / 8; ++c8) {
-                    uint32_t pk[4];
-#pragma unroll
-                    for (int h = 0; h < 4; ++h) {
-                        f32x2 x = pack2(__uint_as_float(acc[c8 * 8 + h * 2]), __uint_as_float(acc[c8 * 8 + h * 2 + 1]));
-                        x = fma2(x, a2v, tbv[c8 * 4 + h]);
-                        pk[h] = f32x2_to_bf16x2(gelu2_tanh(x));
-                    }
-                    sts_v4(row + ((uint32_t(ch * (CW / 8) + c8) ^ rx) << 4), pk[0], pk[1], pk[2], pk[3]);
+                for (int h = 0; h < CW / 2; ++h) {
+                    f32x2 x = pack2(__uint_as_float(acc[h * 2]), __uint_as_float(acc[h * 2 + 1]));
+                    x = fma2(x, a2v, tbv[h]);
+                    pk[h] = f32x2_to_bf16x2(gelu2_tanh(x));
                 }
-                fence_proxy_async();  // the UMMA (async proxy) reads what this thread just wrote
+                // in place: the packed bf16 pairs of this thread's 16 columns overwrite the first 8 of those columns
+                tmem_st8(tmem_base + s * 64 + ch * CW + lane_t, pk);
+                tmem_st_wait();
+                tc_fence_before();
+                IRB_TS(4);
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bars->a2_full[s]);
+                IRB_TS(5);
             }
+            IRB_TS(6);
             // ---- epilogue: columns [ch * NB/kMfCG, (ch + 1) * NB/kMfCG) of this row ----
             mbar_wait(&bars->d2_full[ab], (it >> 1) & 1);
+            IRB_TS(7);
             tc_fence_after();
             const int half = p.NB / kMfCG;         // columns per thread: a multiple of 8 (NB % 32 == 0)
             const int ecol0 = ch * half;
@@ -281,11 +359,8 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
                     // residual chunk: K chunk col / 64 of the A tile, 16-byte chunk (col % 64) / 8 of the row
                     const uint32_t addr = a_tile + (col >> 6) * kMfATile + r * 128 + ((uint32_t((col & 63) >> 3) ^ rx) << 4);
                     const uint4 res = lds_v4(addr);
-                    float4 bb0 = make_float4(0.f, 0.f, 0.f, 0.f), bb1 = bb0;
-                    if (col < p.C) {  // C % 4 == 0
-                        bb0 = __ldg(reinterpret_cast<const float4*>(p.b2 + col));
-                        if (col + 4 < p.C) bb1 = __ldg(reinterpret_cast<const float4*>(p.b2 + col + 4));
-                    }
+                    const float4 bb0 = *reinterpret_cast<const float4*>(sVecB2 + col);
+                    const float4 bb1 = *reinterpret_cast<const float4*>(sVecB2 + col + 4);
                     const f32x2 y0 = add2(add2(pack2(v[0], v[1]), pack2(bb0.x, bb0.y)), bf16x2_to_f32x2(res.x));
                     const f32x2 y1 = add2(add2(pack2(v[2], v[3]), pack2(bb0.z, bb0.w)), bf16x2_to_f32x2(res.y));
                     const f32x2 y2 = add2(add2(pack2(v[4], v[5]), pack2(bb1.x, bb1.y)), bf16x2_to_f32x2(res.z));
@@ -317,8 +392,10 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
                     sts_v4(addr, f32x2_to_bf16x2(y0), f32x2_to_bf16x2(y1), f32x2_to_bf16x2(y2), f32x2_to_bf16x2(y3));
                 }
             }
+            IRB_TS(8);
             tc_fence_before();
             fence_proxy_async();  // the TMA store (async proxy) reads the tile
+            IRB_TS(9);
             // LayerNorm statistics of the new row: the two column halves meet through shared memory
             float a0, a1, q0, q1;
             unpack2(s1, a0, a1);
@@ -344,7 +421,15 @@ __global__ void __launch_bounds__(kMfThreads, 1) mlp_fused_kernel(const __grid_c
                 mbar_arrive(&bars->d2_empty[ab]);
                 mbar_arrive(&bars->out_ready[ab]);
             }
+            IRB_TS(10);
         }
+#if defined(IRB_MLP_DBG) && IRB_MLP_DBG == 5
+        if (trace) {
+            static __device__ int printed;
+            if (atomicAdd(&printed, 1) == 0)
+                for (int i = 1; i < nts; ++i) printf("TS %d %d %lld\n", i, tsi[i], tsv[i] - tsv[i - 1]);
+        }
+#endif
     }
     tc_fence_before();
     __syncthreads();
@@ -402,7 +487,7 @@ int mlp_fused_bf16(bf16* x, long long ldx, long long P, int C, int hid, const fl
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int grid = p.tiles < sms ? p.tiles : sms;
-    const size_t smem = 1024 + size_t(2) * p.KS * kMfATile + size_t(2) * p.KS * kMfW1Slab + 2 * kMfA2 +
+    const size_t smem = 1024 + size_t(2) * p.KS * kMfATile + size_t(2) * p.KS * kMfW1Slab + kMfAux +
                         size_t(2) * p.NB * 128 + sizeof(MfBars) + 64;
     IRB_REQUIRE(smem <= 227 * 1024, "mlp_fused: shared memory budget exceeded");
     IRB_SMEM_OPTIN((mlp_fused_kernel), 227 * 1024);

@@ -733,7 +733,13 @@ int SwinIR::forward(const float* in, float* out, int n, int Hin, int Win, void* 
     Bump b(wsp);
     WS w;
     layout(b, n, Hin, Win, w);
-    cur_ws = &w;   // calls on one model are serialised by the caller (Engine's lock): the pointer is per forward
+    // calls on one model are serialised by the caller (Engine's lock): the pointer is per forward and cleared on every
+    // return path
+    struct WsScope {
+        WS*& slot;
+        WsScope(WS*& s_, WS* v) : slot(s_) { slot = v; }
+        ~WsScope() { slot = nullptr; }
+    } ws_scope(cur_ws, &w);
     const long long P = (long long)n * H * W;
     const int sc = tsc;
     if (us > 1) {

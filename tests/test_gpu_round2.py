@@ -514,3 +514,26 @@ def test_hat_crop_mode_rejects_bad_tiles():
     with pytest.raises(ValueError, match="multiples of window_size"):
         eng(torch.zeros(1, 3, 40, 32, device="cuda"))
     eng.close()
+
+
+def test_device_chain_ending_in_hat_equals_file_chain(tmp_path):
+    """A plan that ends in the HAT SR tool (derain -> denoise -> HAT x4): the device-resident chain gives exactly the
+    bytes of the file-based chain; HAT's crop-with-pad tile mode sits behind the same restore_u8_device hook."""
+    import cv2
+    from image_restoration_agent_b200.tool_api import Chain, HATB200, clear_engines
+    hcfg = configs.small_hat_config()
+    tools = _chain_tools("bf16")[:2] + [HATB200(state_dict=synth.hat_state_dict(hcfg, 6), cfg=hcfg, precision="bf16",
+                                                tile={"tile_size": 32, "tile_pad": 16})]
+    img = synth.synthetic_image_u8(40, 56, 3, seed=12)
+    src = tmp_path / "s0"
+    src.mkdir()
+    cv2.imwrite(str(src / "input.png"), img)
+    for k, tool in enumerate(tools):
+        dst = tmp_path / f"s{k + 1}"
+        dst.mkdir()
+        tool(src, dst, silent=True)
+        src = dst
+    want = cv2.imread(str(src / "output.png"), cv2.IMREAD_COLOR)
+    got = Chain(tools).run(img)
+    assert got.shape == (160, 224, 3) and np.array_equal(got, want)
+    clear_engines()
