@@ -50,6 +50,8 @@ struct alignas(64) TcGemmParams {
     int m_outer;                  // 1: a CTA walks all n-tiles of its m-tile back to back
     int b_resident;               // 1 (mode 0): the whole weight matrix stays in shared memory, the ring carries A only
     int bres_bytes;
+    int a_hold;                   // mode 0, weights not resident: 1 / 2 buffers that keep an m-tile's A slabs while the
+                                  // CTA walks its n-tiles (the ring then carries B only); 0 = A travels with B
     int blk_cols;                 // columns per epilogue block: 64, or 48 (PixelShuffle with 48 | N/4, specialised kernels only)
     int res_tma;                  // 1: tmR is valid and the residual is TMA-staged (RES 2)
     int stg_per_warp;             // 4 KB staging blocks per epilogue warp: 2, or 3 when the residual is TMA-staged
@@ -646,8 +648,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
     extern __shared__ uint8_t smem_raw[];
     // pointer arithmetic on the __shared__ symbol (not an integer round trip) keeps the address space known: LDS/STS
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    // b_resident: [weights: tiles_n x ktiles slabs of BN x 128 B][ring of A tiles]; otherwise ring of (A, B) stages
-    const int stage_bytes = p.b_resident ? kABytes : kABytes + p.BN * 128;
+    // b_resident: [weights: tiles_n x ktiles slabs of BN x 128 B][ring of A tiles]; a_hold: [a_hold x ktiles A slabs][ring
+    // of B slabs]; otherwise ring of (A, B) stages
+    const int stage_bytes = p.b_resident ? kABytes : (p.a_hold ? p.BN * 128 : kABytes + p.BN * 128);
     uint8_t* ring = smem + p.bres_bytes;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + p.stages * stage_bytes);
     uint64_t* empty_bar = full_bar + p.stages;
@@ -656,7 +659,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
     uint64_t* bres_full = tempty_bar + 2;         // resident weights loaded (TMA -> MMA)
     uint64_t* bres_empty = bres_full + 1;         // all MMAs that read the resident weights are done (MMA -> TMA)
     uint64_t* res_bar = bres_empty + 1;           // [8][3] residual blocks landed (TMA -> epilogue warp)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 24);
+    uint64_t* ah_full = res_bar + 24;             // [2] held A tile loaded (TMA -> MMA)
+    uint64_t* ah_empty = ah_full + 2;             // [2] all n-tiles of the held A tile are done (MMA -> TMA)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(ah_empty + 2);
     const int ncolv = p.tiles_n * p.BN;                        // padded column count
     float* colvec = reinterpret_cast<float*>(tmem_slot + 4);  // [bias | colsum][ncolv], 16-byte aligned, staged once
     // 8 epilogue warps x stg_per_warp x 4 KB staging blocks for TMA stores ([32 rows][64 bf16], 128B-swizzled), 1024-aligned;
@@ -683,6 +688,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
             mbar_init(bres_full, 1);
             mbar_init(bres_empty, 1);
             for (int i = 0; i < 24; ++i) mbar_init(&res_bar[i], 1);
+            for (int i = 0; i < 2; ++i) {
+                mbar_init(&ah_full[i], 1);
+                mbar_init(&ah_empty[i], 1);
+            }
             if (VAR >= 0 && ((VAR >> 4) & 3) == 2) tma_prefetch_desc(&p.tmR);
             fence_mbar_init();
         }
@@ -703,7 +712,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
         // ===== TMA producer: the whole warp walks the tiles, the elected lane issues (ptxas then knows the issue
         // is single-threaded and drops its per-instruction election loops) =====
         const bool leader = elect_one() != 0;
-        int nb = 0, cur_z = -1;
+        int nb = 0, cur_z = -1, nhold = 0;
         int s = 0;         // ring slot and its phase, carried instead of it % stages, (it / stages) & 1
         uint32_t ph = 0;
         TileIter ti;
@@ -726,6 +735,19 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 cur_z = z;
                 ++nb;
             }
+            if (p.a_hold && nt == 0) {
+                // first n-tile of an m-tile (a CTA walks them in order): its A slabs go into a hold buffer once; the
+                // other n-tiles re-use them instead of pulling them through the L2 fabric again
+                const int hb = nhold % p.a_hold;
+                GEMM_WAIT(&ah_empty[hb], ((nhold / p.a_hold) & 1) ^ 1);
+                if (leader) {
+                    mbar_arrive_expect_tx(&ah_full[hb], p.ktiles * kABytes);
+                    for (int kc = 0; kc < p.ktiles; ++kc)
+                        tma_load_3d(smem + (hb * p.ktiles + kc) * kABytes, &p.tmA, &ah_full[hb], kc * kTileK, mt * kTileM, z);
+                }
+                __syncwarp();
+                ++nhold;
+            }
             int x0 = 0, y0 = 0;
             if (p.mode == 1) {
                 x0 = (mt % p.tiles_x) * p.BW;
@@ -743,12 +765,16 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                             mbar_arrive(&full_bar[s]);
                         } else {
                             mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
-                            if (p.mode == 0)
-                                tma_load_3d(sa, &p.tmA, &full_bar[s], kc * kTileK, mt * kTileM, z);
-                            else
-                                tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx, y0 + dy, z);
-                            if (!p.b_resident)
-                                tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK, z * p.b_rows_per_batch + n0);
+                            if (p.a_hold) {  // the stage is a B slab only
+                                tma_load_2d(sa, &p.tmB, &full_bar[s], kc * kTileK, z * p.b_rows_per_batch + n0);
+                            } else {
+                                if (p.mode == 0)
+                                    tma_load_3d(sa, &p.tmA, &full_bar[s], kc * kTileK, mt * kTileM, z);
+                                else
+                                    tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx, y0 + dy, z);
+                                if (!p.b_resident)
+                                    tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK, z * p.b_rows_per_batch + n0);
+                            }
                         }
                     }
                     __syncwarp();
@@ -764,12 +790,17 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
         // descriptors stay warp-uniform), lane 0 alone issues the tcgen05 instructions =====
         const bool leader = elect_one() != 0;  // elect.sync is deterministic for the full mask: always the same lane
         const uint32_t idesc = make_idesc_bf16(kTileM, p.BN, 0, 0);
-        int t = 0, nb = 0, cur_z = -1;
+        int t = 0, nb = 0, cur_z = -1, nhold = 0, cur_hb = 0;
         int s = 0;
         uint32_t ph = 0;
         TileIter ti;
         for (tile_first(p, ti); ti.w < p.total; tile_next(p, ti), ++t) {
             const int a = t & 1;
+            if (p.a_hold && ti.nt == 0) {
+                cur_hb = nhold % p.a_hold;
+                GEMM_WAIT(&ah_full[cur_hb], (nhold / p.a_hold) & 1);
+                ++nhold;
+            }
             if (p.b_resident) {
                 const int z = ti.z;
                 if (cur_z < 0 || (p.b_rows_per_batch != 0 && z != cur_z)) {
@@ -790,8 +821,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 if (++kc == p.ktiles) kc = 0;
                 GEMM_WAIT(&full_bar[s], ph);
                 tc_fence_after();
-                const uint32_t a_addr = smem_u32(ring + s * stage_bytes);
-                const uint32_t b_addr = p.b_resident ? bres_tile + i * p.BN * 128 : a_addr + kABytes;
+                const uint32_t st_addr = smem_u32(ring + s * stage_bytes);
+                const uint32_t a_addr = p.a_hold ? smem_u32(smem) + (cur_hb * p.ktiles + i) * kABytes : st_addr;
+                const uint32_t b_addr = p.b_resident ? bres_tile + i * p.BN * 128 : (p.a_hold ? st_addr : st_addr + kABytes);
                 // one descriptor per operand and stage; the 32-byte K steps only move the 16-byte-unit address field
                 const uint64_t adesc0 = make_sdesc_sw128(a_addr, 16, 1024);
                 const uint64_t bdesc0 = make_sdesc_sw128(b_addr, 16, 1024);
@@ -809,7 +841,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                     ph ^= 1;
                 }
             }
-            if (leader) umma_commit(&tfull_bar[a]);  // accumulator complete
+            if (leader) {
+                umma_commit(&tfull_bar[a]);  // accumulator complete
+                if (p.a_hold && ti.nt == p.tiles_n - 1) umma_commit(&ah_empty[cur_hb]);  // the held A tile is done
+            }
             __syncwarp();
         }
     } else if (warp >= 2) {
@@ -1192,6 +1227,48 @@ static bool gemm_variant_exists(const Epi& e) {
     return var >= 0;
 }
 
+// shared-memory bytes of everything but the operand buffers
+static size_t gemm_fixed_smem(int tiles_n, int BN, int stg_per_warp) {
+    return 1024 /*align*/ + 512 /*barriers*/ + size_t(2) * tiles_n * BN * 4 /*column vectors*/ + 1024 +
+           8 * size_t(stg_per_warp) * 4096 /*TMA-store staging*/;
+}
+static bool gemm_m_outer(long long m_units, int tiles_n) {
+    static int order = -2;
+    if (order == -2) {
+        order = IRB_DIAG_ENV("IRB_GEMM_ORDER", -1);
+    }
+    return order >= 0 ? order != 0 : !(tiles_n > 1 && m_units < 8ll * sm_count());
+}
+// A-hold plan of a 1x1 GEMM whose weights do not fit in shared memory (SwinIR's qkv / fc layers: K = 180 / 240, N = 576 /
+// 768): with (A, B) stages every (m, n) tile pulls its A slabs AND its B slabs through the L2 fabric, 885 MB per launch of
+// the [180 -> 576] GEMM against 94 MB of unique A (ncu l1tex__m_xbar2l1tex_read_bytes, profiles/r02_s52), at 7.6 TB/s
+// the binding resource; holding the m-tile's A for all its n-tiles removes the A re-reads. Returns the number of hold
+// buffers (0 = none).
+static int plan_a_hold(int M, int K, int N, int batch, int stg_per_warp, int* BN) {
+    static int on = -1;
+    if (on < 0) on = IRB_DIAG_ENV("IRB_GEMM_AHOLD", 1);
+    if (!on) return 0;
+    const int ktiles = ceil_div(K, kTileK);
+    const int bn0 = *BN;
+    if (ceil_div(N, bn0) < 2) return 0;
+    if (!gemm_m_outer((long long)batch * ceil_div(M, kTileM), ceil_div(N, bn0))) return 0;
+    {   // weights resident? then the ring carries A only anyway
+        const size_t bres = size_t(ceil_div(N, bn0)) * ktiles * bn0 * 128;
+        if (gemm_fixed_smem(ceil_div(N, bn0), bn0, stg_per_warp) + bres + 3 * size_t(kABytes) <= 227 * 1024) return 0;
+    }
+    // Measured (same-box A/B, profiles/r02_s54 / r02_s55): the [180 -> 576] GEMM of SwinIR-M / HAT with ONE hold buffer and
+    // the planned BN = 192: 4.60 -> 4.25 ms per 36 launches (cfg3 tile: all GEMMs 14.35 -> 13.45 ms). Narrowing BN to make
+    // room loses more than the hold gains (BN = 128, two buffers: 5.07 ms; SwinIR-L's [240 -> 768] at BN = 128: cfg4 GEMMs
+    // 36.1 -> 40.1 ms), and with K <= 128 (Restormer: two K slabs, little A to re-read) the hold is a small loss
+    // (cfg2 GEMMs 17.9 -> 18.3 ms). So: the planned width only, three or more K slabs.
+    if (ktiles < 3 || bn0 % 64 != 0) return 0;
+    for (int nh : {2, 1}) {
+        const size_t need = gemm_fixed_smem(ceil_div(N, bn0), bn0, stg_per_warp) + size_t(nh) * ktiles * kABytes + 3 * size_t(bn0) * 128;
+        if (need <= 227 * 1024) return nh;
+    }
+    return 0;
+}
+
 static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     const int stage_bytes = kABytes + p.BN * 128;
     p.acc_stride = (p.BN + 31) / 32 * 32;
@@ -1199,8 +1276,7 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     p.tiles_n = ceil_div(p.N, p.BN);
     p.stg_per_warp = p.res_tma ? 3 : 2;
     if (p.blk_cols == 0) p.blk_cols = 64;
-    const size_t fixed = 1024 /*align*/ + 512 /*barriers*/ + size_t(2) * p.tiles_n * p.BN * 4 /*column vectors*/ +
-                         1024 + 8 * size_t(p.stg_per_warp) * 4096 /*TMA-store staging*/;
+    const size_t fixed = gemm_fixed_smem(p.tiles_n, p.BN, p.stg_per_warp);
     IRB_REQUIRE(fixed + 2 * size_t(stage_bytes) <= 227 * 1024, "tc_gemm: N too large for the shared-memory column vectors");
     int stages = int((227 * 1024 - fixed) / stage_bytes);
     if (stages > 8) stages = 8;
@@ -1228,6 +1304,19 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
             if (stages > 8) stages = 8;
         }
     }
+    const long long m_units = (long long)batch * p.tiles_m;
+    p.m_outer = gemm_m_outer(m_units, p.tiles_n) ? 1 : 0;
+    if (p.a_hold) {  // planned by tc_gemm (plan_a_hold): re-checked against the final layout
+        const size_t hold = size_t(p.a_hold) * p.ktiles * kABytes, bst = size_t(p.BN) * 128;
+        if (p.mode == 0 && !p.b_resident && p.m_outer && p.tiles_n >= 2 && fixed + hold + 3 * bst <= 227 * 1024) {
+            p.bres_bytes = int(hold);
+            ring_stage = bst;
+            stages = int((227 * 1024 - fixed - hold) / bst);
+            if (stages > 8) stages = 8;
+        } else {
+            p.a_hold = 0;
+        }
+    }
     p.stages = stages;
     const long long total = (long long)batch * p.tiles_m * p.tiles_n;
     IRB_REQUIRE(total < (1ll << 31), "tc_gemm: too many tiles");
@@ -1252,13 +1341,7 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
     IRB_SMEM_OPTIN((fn), 227 * 1024);
     // Order 1 (a CTA walks all n-tiles of an m-tile) re-reads A from L2 back to back, but hands out whole m-tiles: with
     // few m-tiles per CTA (the deep Restormer levels: 192 m-tiles on 148 SMs) a third of the SMs idle in the second
-    // wave. Then the (m, n) items are dealt round-robin instead (order 0). IRB_GEMM_ORDER=0/1 forces one.
-    static int order = -2;
-    if (order == -2) {
-        order = IRB_DIAG_ENV("IRB_GEMM_ORDER", -1);
-    }
-    const long long m_units = (long long)batch * p.tiles_m;
-    p.m_outer = order >= 0 ? order : ((p.tiles_n > 1 && m_units < 8ll * sm_count()) ? 0 : 1);
+    // wave. Then the (m, n) items are dealt round-robin instead (order 0, gemm_m_outer()). IRB_GEMM_ORDER=0/1 forces one.
     const long long units = p.m_outer ? m_units : total;
     const int grid = int(units < sm_count() ? units : sm_count());
     p.step_nt = grid % p.tiles_n;
@@ -1285,6 +1368,7 @@ int tc_gemm(const bf16* A, long long lda, int M, int K, int batch, long long a_b
     p.M = M;
     p.N = N;
     p.BN = pick_bn(N);
+    p.a_hold = plan_a_hold(M, K, N, batch, epi.res != nullptr ? 3 : 2, &p.BN);
     p.ktiles = ceil_div(K, kTileK);
     p.klast = ceil_div(K - (p.ktiles - 1) * kTileK, 16);
     p.taps = 1;
