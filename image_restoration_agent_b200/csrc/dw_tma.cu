@@ -11,6 +11,7 @@
 // touches (input-stationary, 3 live accumulator rows), so each element costs one LDS.32 + two ALU ops per 2 output
 // columns. Arithmetic is fp32 with packed fma.rn.f32x2 (both channels of the pair in one instruction); the GELU is
 // evaluated packed as well, in its sigmoid form (gelu2_fast: the kernel is bound by the FP32 pipe, 2 MUFU per element).
+#include <cstdio>
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
@@ -121,10 +122,21 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_c
             wr[st][t] = pack2(w2.x, w2.y);
         }
     int it = 0;
+#ifdef IRB_DW_TRACE  // timing experiment: clock() trace of consumer warp 0 of CTA 0 (gate kernel, Cout == IRB_DW_TRACE)
+    const bool trace = GATE != 0 && blockIdx.x == 0 && threadIdx.x == 0 && p.Cout == IRB_DW_TRACE;
+    long long tsv[120];
+    int tsi[120];
+    int nts = 0;
+#define IRB_TS(i) do { if (trace && nts < 120) { tsv[nts] = clock64(); tsi[nts++] = (i); } } while (0)
+#else
+#define IRB_TS(i) do { } while (0)
+#endif
     for (int sp = sp0; sp < per_chunk; sp += sp_step, ++it) {
         const int s = it % kDwStages;
         const uint32_t ph = (it / kDwStages) & 1;
+        IRB_TS(0);
         mbar_wait(&full[s], ph);
+        IRB_TS(1);
         const int4 id = item[s];
         const int img = id.x, ty = id.y, tx = id.z;
         const uint32_t tile = lane_off + s * stage_bytes;
@@ -185,9 +197,18 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw3x3_tma_kernel(const __grid_c
                 yp1 += row_step;
             }
         }
+        IRB_TS(2);
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[s]);
+        IRB_TS(3);
     }
+#ifdef IRB_DW_TRACE
+    if (trace) {
+        static __device__ int printed;
+        if (atomicAdd(&printed, 1) == 0)
+            for (int i = 1; i < nts; ++i) printf("TS %d %d %lld\n", i, tsi[i], tsv[i] - tsv[i - 1]);
+    }
+#endif
 }
 
 static int dw_tma_launch(bool gate, const bf16* x, long long ldx, int Ctot, bf16* y, long long ldy, int Nimg, int H,
