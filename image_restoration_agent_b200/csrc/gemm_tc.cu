@@ -16,6 +16,7 @@
 // residual -> swizzled smem -> TMA store). A ring of `stages` shared-memory slots with full/empty mbarriers
 // decouples TMA from the tensor core; tfull/tempty mbarriers hand accumulators between MMA and epilogue.
 #include "common.cuh"
+#include <cstdio>
 #include "ptx.cuh"
 #include "kernels.h"
 #include <stdlib.h>
@@ -481,7 +482,17 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
     }
 
     uint32_t nb = 0;  // blocks consumed by this warp
+#ifdef IRB_GEMM_TRACE  // timing experiment: clock() trace of the first epilogue warp of CTA 0, launches with N == IRB_GEMM_TRACE
+    const bool trace = blockIdx.x == 0 && warp == 2 && lane == 0 && p.N == IRB_GEMM_TRACE;
+    long long tsv[160];
+    int tsi[160];
+    int nts = 0;
+#define IRB_TS(i) do { if (trace && nts < 160) { tsv[nts] = clock64(); tsi[nts++] = (i); } } while (0)
+#else
+#define IRB_TS(i) do { } while (0)
+#endif
     for (; ti.w < p.total; t += 2) {
+        IRB_TS(0);
         const int nt = ti.nt;
         const int mt = ti.mt;
         const int z = ti.z;
@@ -518,7 +529,9 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
         f32x2 st_s1 = 0ull, st_s2 = 0ull;
         float st_shift = 0.f;
         const bf16* rrow = reinterpret_cast<const bf16*>(p.epi.res) + (valid ? grow : 0) * p.epi.ldr + n0;
+        IRB_TS(1);
         GEMM_WAIT(&c.tfull_bar[set], (t >> 1) & 1);
+        IRB_TS(2);
         tc_fence_after();
         const uint32_t taddr = c.tmem_base + set * p.acc_stride + (uint32_t(q * 32) << 16);
         if (p.dbg & 32) {  // diagnosis: no epilogue work at all (results are wrong on purpose)
@@ -596,6 +609,7 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
                 epi_block<ACT, LN, RES != 0, STATS>(acc, rr, ng, nvalid, s_bias + cb, s_cs + cb, fa, fb, slope, rrag,
                                                     stg_warp_p + bsel * 4096 + lane * 128, lane, st_s1, st_s2, st_shift);
             }
+            IRB_TS(3);
             const bool last = cb + bcols >= ncols;
             if (last) {  // the accumulator is in registers / staged: hand it back to the MMA warp
                 tc_fence_before();
@@ -622,6 +636,7 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
                 }
                 bulk_commit();
             }
+            IRB_TS(4);
             ++nb;
             if (RES == 2) {
                 // block nb+1 goes into the staging block of block nb-2: its store must have finished reading
@@ -639,7 +654,15 @@ __device__ __forceinline__ void epilogue_fast(const TcGemmParams& p, const EpiCt
             const float var = fmaxf((q0 + q1) * invn - m * m, 0.f);
             p.epi.stats_out[grow] = make_float2(st_shift + m, rsqrtf(var + p.epi.stats_eps));
         }
+        IRB_TS(5);
     }
+#ifdef IRB_GEMM_TRACE
+    if (trace) {
+        static __device__ int printed;
+        if (atomicAdd(&printed, 1) == 0)
+            for (int i = 1; i < nts; ++i) printf("TS %d %d %lld\n", i, tsi[i], tsv[i] - tsv[i - 1]);
+    }
+#endif
     bulk_wait0();  // all bulk stores of this warp have landed before the CTA exits
 }
 
