@@ -14,6 +14,7 @@
 // The relative-position bias is looked up from a shared-memory copy of the (2w-1)^2 x heads table with the index
 // (yi-yj+7)*15 + (xi-xj+7) folded into immediate offsets; the -100 mask is derived from the token coordinates of the
 // windows in the last window row / column of the shifted frame. Nothing is materialised in HBM.
+#include <cstdio>
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
@@ -337,6 +338,15 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
         uint32_t pk[32];
         float inv_s = 0.f;
         // S(cnt) row from TMEM -> unnormalised probabilities (bf16 pairs) in pk, 1 / sum in inv_s
+#ifdef IRB_WA_TRACE  // timing experiment: clock() trace of softmax warp 1 / lane 0 of CTA 0, printed at exit
+        const bool trace = blockIdx.x == 0 && threadIdx.x == 32;
+        long long tsv[150];
+        int tsi[150];
+        int nts = 0;
+#define IRB_TS(i) do { if (trace && nts < 150) { tsv[nts] = clock64(); tsi[nts++] = (i); } } while (0)
+#else
+#define IRB_TS(i) do { } while (0)
+#endif
         auto softmax_phase = [&](int cnt, int h) {
             const int copy = (xi & 1) ^ 1;
             const uint32_t tab = smem_u32(s_table + h * kWaTabSize + copy * (kWaTabCopy + 1) + (yi + 7) * kWaTabStride + (7 - xi));
@@ -346,7 +356,9 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
             f32x2 bq[16];
 #pragma unroll
             for (int k = 0; k < 16; ++k) bq[k] = lds_f32x2(tab + 4 * (((k & 3) * 2) - (k >> 2) * kWaTabStride));
+            IRB_TS(1);
             mbar_wait(&bar[WB_SFULL + g], cnt & 1);
+            IRB_TS(2);
             tc_fence_after();
             uint32_t sr[64];
             tmem_ld32_nowait(tmem_base + lane_addr + g * 128 + win * 64, sr);
@@ -402,12 +414,15 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
             }
             inv_s = 1.0f / sum;
         };
+        long long o_base = -1;                 // output pointers of the store pattern, per unit (see the O phase)
+        int o_off[D2T > 0 ? D2T : 1] = {};
         int u_s = blockIdx.x, hp_s = 0;
         if (u_s < p.units) {
             unit_info(u_s);
             softmax_phase(0, g);
         }
         for (int cnt = 0; u_s < p.units; ++cnt) {
+            IRB_TS(3);
             // ---- P(cnt) -> shared memory (UMMA A layout) -> tensor core ----
 #pragma unroll
             for (int c = 0; c < 8; ++c)
@@ -416,6 +431,7 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
             fence_proxy_async();
             __syncwarp();
             if (lane == 0) mbar_arrive(&bar[WB_PFULL + g]);
+            IRB_TS(4);
             const long long orow = orow_s;
             const float inv = inv_s;
             const int h = hp_s * 2 + g;
@@ -427,11 +443,14 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
             }
             if (u_s < p.units) softmax_phase(cnt + 1, hp_s * 2 + g);
             // ---- O(cnt) = P V / sum ----
+            IRB_TS(5);
             mbar_wait(&bar[WB_OFULL + g], cnt & 1);
+            IRB_TS(6);
             tc_fence_after();
             uint32_t orr[32];
             tmem_ld32_nowait(tmem_base + lane_addr + 256 + g * 64 + g * 32, orr);
             tmem_ld_wait();
+            IRB_TS(8);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&bar[WB_OEMPTY + g]);
@@ -441,21 +460,35 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                     tb[lane * tstride + k] =
                         pack_bf16x2(__uint_as_float(orr[2 * k]) * inv, __uint_as_float(orr[2 * k + 1]) * inv);
             __syncwarp();
+            IRB_TS(9);
             // coalesced: consecutive lanes write consecutive words of a token's head slice
             if (D2T > 0) {
-                uint32_t v[D2T > 0 ? D2T : 1];
-                int rows[D2T > 0 ? D2T : 1];
+                // The store pattern (word wi = lane + 32 * it of the warp's 32 x D2T output words -> token row wi / D2T)
+                // needs the row pointer of ANOTHER lane's token. Fetching it with two shuffles per word cost ~100
+                // cycles per word in series (clock trace r02_s59: 1 500 of the step's 4 200 cycles): the pointers only
+                // change with the unit, so they are gathered once per unit (first head pair) as 32-bit offsets from the
+                // warp's first token and kept in registers for its other head pairs.
+                if ((h >> 1) == 0) {
+                    o_base = __shfl_sync(0xffffffffu, orow, 0);
+                    const int rel = int(orow - o_base);
 #pragma unroll
-                for (int it = 0; it < D2T; ++it) {
-                    const int wi = lane + 32 * it;
-                    rows[it] = wi / D2T;
-                    v[it] = tb[rows[it] * tstride + (wi - rows[it] * D2T)];
+                    for (int it = 0; it < D2T; ++it) {
+                        const int wi = lane + 32 * it;
+                        const int row = wi / D2T;
+                        o_off[it] = __shfl_sync(0xffffffffu, rel, row) + (wi - row * D2T);
+                    }
                 }
+                if (o_base >= 0) {  // warp-uniform: the 32 rows of a warp belong to one window
+                    uint32_t v[D2T > 0 ? D2T : 1];
 #pragma unroll
-                for (int it = 0; it < D2T; ++it) {
-                    const int wi = lane + 32 * it;
-                    const long long ob = __shfl_sync(0xffffffffu, orow, rows[it]);
-                    if (ob >= 0) out32[ob + h * D2T + (wi - rows[it] * D2T)] = v[it];
+                    for (int it = 0; it < D2T; ++it) {
+                        const int wi = lane + 32 * it;
+                        const int row = wi / D2T;
+                        v[it] = tb[row * tstride + (wi - row * D2T)];
+                    }
+                    uint32_t* ob = out32 + o_base + h * D2T;
+#pragma unroll
+                    for (int it = 0; it < D2T; ++it) ob[o_off[it]] = v[it];
                 }
             } else {
                 const int nwords = 32 * d2;
@@ -467,7 +500,15 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                 }
             }
             __syncwarp();
+            IRB_TS(7);
         }
+#ifdef IRB_WA_TRACE
+        if (trace) {
+            static __device__ int printed;
+            if (atomicAdd(&printed, 1) == 0)
+                for (int i = 1; i < nts; ++i) printf("TS %d %d %lld\n", i, tsi[i], tsv[i] - tsv[i - 1]);
+        }
+#endif
     }
     tc_fence_before();
     __syncthreads();
