@@ -11,7 +11,7 @@
 //                       the qkv tensor: three TMA loads by one lane ({64 ch, 16, 8} for Q, {64, 16, 4} / {64, 24, 2} for a key
 //                       chunk), and the out-of-image keys of the overlapping window arrive as zeros (TMA out-of-bounds
 //                       fill = nn.Unfold's padding). The last window row / column of a shifted frame wraps around the
-//                       image and is gathered row by row with cp.async (~6 % of the windows of a 544 x 544 tile).
+//                       image (~6 % of the windows of a 544 x 544 tile): its tiles are loaded as half-row boxes {64, 8, 1}.
 //                       ncu (profiles/r02_s21) showed the all-cp.async loader's issue time on the critical path: the
 //                       softmax warps sat on the S barrier for 22 % of the samples; TMA took 0.52 -> 0.34 ms per launch.
 //   MMA (1 thread)    : S_h = Q_h K_h^T (M 128, N = chunk, K 32) per head of the pair; O_h = P_h V (M 128, N 64, K = chunk)
@@ -92,7 +92,8 @@ struct HtIter {
 template <int MODE, int D2T>
 __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const HtParams p,
                                                                          const __grid_constant__ CUtensorMap tm_q,
-                                                                         const __grid_constant__ CUtensorMap tm_kv) {
+                                                                         const __grid_constant__ CUtensorMap tm_kv,
+                                                                         const __grid_constant__ CUtensorMap tm_h) {
     using Cfg = HtCfg<MODE>;
     constexpr int KC = Cfg::KC, NC = Cfg::NC, KW = Cfg::KW, KR = Cfg::KR, TR = Cfg::TR;
     constexpr int kTabSize = TR * kHtTabStride;
@@ -159,9 +160,7 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
 
     if (warp >= 9) {
         // ===================== loaders: warp lw fills ring stage lw (steps lw, lw + 3, ...) =====================
-        // 8 consecutive lanes fetch the 8 16-byte chunks of one row's 128-byte line, 4 rows per instruction
         const int lw = warp - 9;
-        const int c8 = lane & 7, sub = lane >> 3;
         HtIter<NC> it{(int)blockIdx.x, 0, 0, 0};
         for (int cnt = 0; it.u < p.windows; ++cnt, it.advance(npairs, gridDim.x)) {
             if (cnt % kHtStages != lw) continue;
@@ -169,8 +168,6 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
             const int wy = wi / p.nwx, wx = wi - wy * p.nwx;
             if (lane == 0) mbar_wait(&bar[HB_EMPTY + lw], ((cnt / kHtStages) & 1) ^ 1);
             __syncwarp();
-            const uint32_t q_dst = smem_u32(stage_base + lw * kHtStage);
-            const bf16* base = p.qkv + it.hp * 64 + c8 * 8;
             // Q: token t = m * 128 + row of the window, at shifted-frame (wy*16 + t/16, wx*16 + t%16). Only the last
             // window row / column of a shifted frame wraps around the image.
             const bool wrap = p.shift > 0 && (wy == p.nwy - 1 || wx == p.nwx - 1);
@@ -188,50 +185,27 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
                 __syncwarp();
                 continue;
             }
-            // the last window row / column of a shifted frame wraps around the image: gather with cp.async
-#pragma unroll 4
-            for (int i = 0; i < 32; ++i) {
-                const int row = i * 4 + sub;
-                const int t = it.m * 128 + row;
-                int oy = wy * 16 + (t >> 4) + p.shift, ox = wx * 16 + (t & 15) + p.shift;
-                if (oy >= p.H) oy -= p.H;
-                if (ox >= p.W) ox -= p.W;
-                const long long pix = ((long long)img * p.H + oy) * p.W + ox;
-                cp_async16(q_dst + row * 128 + ((c8 ^ (row & 7)) << 4), base + pix * p.ld);
-            }
-            const uint32_t k_dst = q_dst + kHtQBytes, v_dst = k_dst + kHtKBytes;
-#pragma unroll 4
-            for (int i = 0; i < KC / 4; ++i) {
-                const int row = i * 4 + sub;
-                int oy, ox;
-                bool inside = true;
-                if (MODE == 0) {
-                    const int j = it.c * KC + row;
-                    oy = wy * 16 + (j >> 4) + p.shift;
-                    ox = wx * 16 + (j & 15) + p.shift;
+            // the last window row / column of a shifted frame (shift 8) wraps around the image: half token rows (8 tokens) never
+            // straddle the wrap, so the same tiles are 16 (Q) + 8 + 8 (K, V) half-row boxes; TMA derives the swizzle from
+            // the destination address, so every piece lands at its rows of the 1024-byte-aligned tile
+            if (lane == 0) {
+                uint8_t* st = stage_base + lw * kHtStage;
+                mbar_arrive_expect_tx(&bar[HB_FULL + lw], kHtQBytes + 2 * KC * 128);
+                for (int hr = 0; hr < 16; ++hr) {  // Q: token row it.m * 8 + (hr >> 1), tokens 8 * (hr & 1) .. + 7
+                    int oy = wy * 16 + it.m * 8 + (hr >> 1) + p.shift, ox = wx * 16 + (hr & 1) * 8 + p.shift;
                     if (oy >= p.H) oy -= p.H;
                     if (ox >= p.W) ox -= p.W;
-                } else {
-                    const int kr = row / KW;
-                    oy = wy * 16 - 4 + it.c * KR + kr;
-                    ox = wx * 16 - 4 + (row - kr * KW);
-                    inside = oy >= 0 && oy < p.H && ox >= 0 && ox < p.W;
+                    tma_load_4d(st + hr * 1024, &tm_h, &bar[HB_FULL + lw], it.hp * 64, ox, oy, img);
                 }
-                const uint32_t off = row * 128 + ((c8 ^ (row & 7)) << 4);
-                if (inside) {
-                    const bf16* src = base + (((long long)img * p.H + oy) * p.W + ox) * p.ld;
-                    cp_async16(k_dst + off, src + p.Cq);
-                    cp_async16(v_dst + off, src + 2 * p.Cq);
-                } else {  // nn.Unfold's zero padding: exact zero key / value vectors
-                    sts_v4(k_dst + off, 0u, 0u, 0u, 0u);
-                    sts_v4(v_dst + off, 0u, 0u, 0u, 0u);
+                for (int hr = 0; hr < 2 * KR; ++hr) {  // K, V: key row it.c * KR + (hr >> 1)
+                    int oy = wy * 16 + it.c * KR + (hr >> 1) + p.shift, ox = wx * 16 + (hr & 1) * 8 + p.shift;
+                    if (oy >= p.H) oy -= p.H;
+                    if (ox >= p.W) ox -= p.W;
+                    tma_load_4d(st + kHtQBytes + hr * 1024, &tm_h, &bar[HB_FULL + lw], p.Cq + it.hp * 64, ox, oy, img);
+                    tma_load_4d(st + kHtQBytes + kHtKBytes + hr * 1024, &tm_h, &bar[HB_FULL + lw], 2 * p.Cq + it.hp * 64, ox, oy, img);
                 }
             }
-            cp_async_commit();
-            cp_async_wait<0>();   // the other two stages are in flight on the other loader warps meanwhile
-            fence_proxy_async();  // generic-proxy writes -> visible to the tensor core's async-proxy reads
             __syncwarp();
-            if (lane == 0) mbar_arrive(&bar[HB_FULL + lw]);
         }
     } else if (warp == 0) {
         // ===================== MMA issuer =====================
@@ -444,14 +418,22 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
             __syncwarp();
             // coalesced: consecutive lanes write consecutive words of a token's head slice
             if (D2T > 0) {
+                // row pointers of the store pattern as 32-bit offsets from the warp's first token, all gathered before the
+                // first store (a 64-bit shuffle + store per word ran in series: ~100 cycles per word in swin_attn_tc.cu)
+                const long long o_base = __shfl_sync(0xffffffffu, orow, 0);
+                const int rel = int(orow - o_base);
+                int o_off[D2T > 0 ? D2T : 1];
+                uint32_t v[D2T > 0 ? D2T : 1];
 #pragma unroll
                 for (int it2 = 0; it2 < D2T; ++it2) {
                     const int wi = lane + 32 * it2;
                     const int row = wi / D2T;
-                    const uint32_t v = tb[row * tstride + (wi - row * D2T)];
-                    const long long ob = __shfl_sync(0xffffffffu, orow, row);
-                    out32[ob + h * D2T + (wi - row * D2T)] = v;
+                    o_off[it2] = __shfl_sync(0xffffffffu, rel, row) + (wi - row * D2T);
+                    v[it2] = tb[row * tstride + (wi - row * D2T)];
                 }
+                uint32_t* ob = out32 + o_base + h * D2T;
+#pragma unroll
+                for (int it2 = 0; it2 < D2T; ++it2) ob[o_off[it2]] = v[it2];
             } else {
                 const int nwords = 32 * d2;
                 for (int wi = lane; wi < nwords; wi += 32) {
@@ -479,19 +461,21 @@ bool hat_attention_tc_ok(int dt, long long ld, long long ldo, int H, int W, int 
 template <int MODE, int D2T>
 static int hat_attention_tc_launch(const HtParams& p, int grid, cudaStream_t stream) {
     using Cfg = HtCfg<MODE>;
-    CUtensorMap tm_q, tm_kv;
+    CUtensorMap tm_q, tm_kv, tm_h;
     {
         const uint64_t dims[4] = {uint64_t(3 * p.Cq), uint64_t(p.W), uint64_t(p.H), uint64_t(p.n)};
         const uint64_t strides[3] = {uint64_t(p.ld) * 2, uint64_t(p.W) * p.ld * 2, uint64_t(p.H) * p.W * p.ld * 2};
         const uint32_t box_q[4] = {64, 16, 8, 1}, box_kv[4] = {64, uint32_t(Cfg::KW), uint32_t(Cfg::KR), 1};
         IRB_TRY(make_tmap_bf16_sw(&tm_q, p.qkv, 4, dims, strides, box_q, 128));
         IRB_TRY(make_tmap_bf16_sw(&tm_kv, p.qkv, 4, dims, strides, box_kv, 128));
+        const uint32_t box_h[4] = {64, 8, 1, 1};  // half a token row: the pieces of a window that wraps around the image
+        IRB_TRY(make_tmap_bf16_sw(&tm_h, p.qkv, 4, dims, strides, box_h, 128));
     }
     const size_t smem = 1024 + size_t(kHtStages) * kHtStage + 2 * kHtPBytes + 8 * 32 * 17 * 4 +
                         ((p.heads * Cfg::TR * kHtTabStride + 3) & ~3) * 4 + HB_COUNT * 8 + 64;
     IRB_REQUIRE(smem <= 227 * 1024, "hat_attention_tc: shared memory");
     IRB_SMEM_OPTIN((hat_attention_tc_kernel<MODE, D2T>), 227 * 1024);
-    hat_attention_tc_kernel<MODE, D2T><<<grid, kHtThreads, smem, stream>>>(p, tm_q, tm_kv);
+    hat_attention_tc_kernel<MODE, D2T><<<grid, kHtThreads, smem, stream>>>(p, tm_q, tm_kv, tm_h);
     IRB_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

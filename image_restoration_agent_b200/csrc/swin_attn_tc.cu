@@ -364,6 +364,7 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
             tmem_ld32_nowait(tmem_base + lane_addr + g * 128 + win * 64, sr);
             tmem_ld32_nowait(tmem_base + lane_addr + g * 128 + win * 64 + 32, sr + 32);
             tmem_ld_wait();
+            IRB_TS(10);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&bar[WB_SEMPTY + g]);
@@ -385,6 +386,7 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                     t2[k] = add2(t2[k], (yj >= 4) ? ((xj >= 4) ? q11 : q10) : ((xj >= 4) ? q01 : q00));
                 }
             }
+            IRB_TS(11);
             float mxs[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four independent chains
 #pragma unroll
             for (int k = 0; k < 32; ++k) {
@@ -393,6 +395,7 @@ __global__ void __launch_bounds__(kWaThreads, 1) window_attention_tc_kernel(cons
                 mxs[k & 3] = fmaxf(mxs[k & 3], fmaxf(a, b));
             }
             const float mx_ = fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3]));
+            IRB_TS(12);
             const f32x2 nmx = splat2(-mx_);
             f32x2 s2a = pack2(0.f, 0.f), s2b = pack2(0.f, 0.f);
 #pragma unroll
