@@ -23,6 +23,7 @@
 //                       transpose buffer as coalesced stores.
 // The softmax of step n + 1 runs while the P V product of step n is in flight (same software pipeline as
 // swin_attn_tc.cu). Nothing is materialised in HBM: neither the logits nor the unfolded 24 x 24 key windows.
+#include <cstdio>
 #include "common.cuh"
 #include "ptx.cuh"
 #include "kernels.h"
@@ -315,6 +316,15 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
         uint32_t pk[KC / 2];
         float mloc = 0.f, lloc = 0.f;
         // S(cnt) row from TMEM -> unnormalised chunk probabilities (bf16 pairs) in pk, chunk max in mloc, chunk sum in lloc
+#ifdef IRB_HT_TRACE  // timing experiment: clock() trace of softmax warp 1 / lane 0 of CTA 0 (MODE == IRB_HT_TRACE - 1)
+        const bool trace = blockIdx.x == 0 && threadIdx.x == 32 && MODE == IRB_HT_TRACE - 1;
+        long long tsv[150];
+        int tsi[150];
+        int nts = 0;
+#define IRB_TS(i) do { if (trace && nts < 150) { tsv[nts] = clock64(); tsi[nts++] = (i); } } while (0)
+#else
+#define IRB_TS(i) do { } while (0)
+#endif
         auto softmax_phase = [&](int cnt, const HtIter<NC>& it) {
             const int h = it.hp * 2 + g;
             const float* tab;
@@ -322,7 +332,9 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
                 tab = s_table + h * kTabSize + (yi + 15 - it.c * KR) * kHtTabStride + xi + 15;
             else             // (ky - yi + 15) * 48 + (kx - xi + 15), ky = 2 c + jj / 24, kx = jj % 24
                 tab = s_table + h * kTabSize + (it.c * KR - yi + 15) * kHtTabStride + 15 - xi;
+            IRB_TS(1);
             mbar_wait(&bar[HB_SFULL + g], cnt & 1);
+            IRB_TS(2);
             tc_fence_after();
             uint32_t sr[64];
             tmem_ld32_nowait(tmem_base + lane_addr + g * 64, sr);
@@ -371,6 +383,7 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
             softmax_phase(0, it);
         }
         for (int cnt = 0; it.u < p.windows; ++cnt) {
+            IRB_TS(3);
             // ---- P(cnt) -> shared memory (UMMA A layout) -> tensor core ----
 #pragma unroll
             for (int c = 0; c < KC / 8; ++c)
@@ -379,6 +392,7 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
             fence_proxy_async();
             __syncwarp();
             if (lane == 0) mbar_arrive(&bar[HB_PFULL + g]);
+            IRB_TS(4);
             const long long orow = orow_s;
             const float mc = mloc, lc = lloc;
             const int h = it.hp * 2 + g;
@@ -390,7 +404,9 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
                 softmax_phase(cnt + 1, it);
             }
             // ---- O(cnt) = P V: merge the chunk into the running state ----
+            IRB_TS(5);
             mbar_wait(&bar[HB_OFULL + g], cnt & 1);
+            IRB_TS(6);
             tc_fence_after();
             uint32_t orr[32];
             tmem_ld32_nowait(tmem_base + lane_addr + 128 + g * 64 + g * 32, orr);
@@ -406,6 +422,7 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
 #pragma unroll
                 for (int k = 0; k < 32; ++k) o[k] = fmaf(o[k], a, __uint_as_float(orr[k]) * b);
             }
+            IRB_TS(7);
             if (!last_chunk) continue;
             const float inv = 1.0f / L;
 #pragma unroll
@@ -444,7 +461,15 @@ __global__ void __launch_bounds__(kHtThreads, 1) hat_attention_tc_kernel(const H
                 }
             }
             __syncwarp();
+            IRB_TS(8);
         }
+#ifdef IRB_HT_TRACE
+        if (trace) {
+            static __device__ int printed;
+            if (atomicAdd(&printed, 1) == 0)
+                for (int i = 1; i < nts; ++i) printf("TS %d %d %lld\n", i, tsi[i], tsv[i] - tsv[i - 1]);
+        }
+#endif
     }
     tc_fence_before();
     __syncthreads();
