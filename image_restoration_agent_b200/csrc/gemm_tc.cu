@@ -44,6 +44,8 @@ struct alignas(64) TcGemmParams {
     int H, W, BW, BH, tiles_x;
     int b_rows_per_batch;
     int stages;
+    int dyr;          // mode 1, narrow tiles: one A halo box {64, BW, BH + 2} per (dx, K slab) serves the three dy taps
+    int kg;           // K slabs (A | B pairs) per ring stage: 1, or more for narrow tiles (see launch_tc)
     int tmem_cols;    // 2 accumulators of acc_stride columns
     int acc_stride;
     int tiles_m, tiles_n, total;  // work items: total = batch * tiles_m * tiles_n, n fastest
@@ -673,7 +675,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     // b_resident: [weights: tiles_n x ktiles slabs of BN x 128 B][ring of A tiles]; a_hold: [a_hold x ktiles A slabs][ring
     // of B slabs]; otherwise ring of (A, B) stages
-    const int stage_bytes = p.b_resident ? kABytes : (p.a_hold ? p.BN * 128 : kABytes + p.BN * 128);
+    const int slab_bytes = kABytes + p.BN * 128;   // one (A, B) slab pair of the plain ring
+    const int halo_bytes = (p.BH + 2) * p.BW * 128;   // dyr: A box of BH + 2 pixel rows
+    const int stage_bytes = p.dyr ? halo_bytes + 3 * p.BN * 128
+                                  : (p.b_resident ? kABytes : (p.a_hold ? p.BN * 128 : p.kg * slab_bytes));
     uint8_t* ring = smem + p.bres_bytes;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + p.stages * stage_bytes);
     uint64_t* empty_bar = full_bar + p.stages;
@@ -726,7 +731,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const int total_it = p.taps * p.ktiles;
+    const int total_it = p.dyr ? 3 * p.ktiles : p.taps * p.ktiles / p.kg;   // ring stages per tile
     // PDL: everything above overlapped the previous kernel's tail; its results are visible from here on
     griddep_wait();
     griddep_launch();
@@ -776,27 +781,53 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                 x0 = (mt % p.tiles_x) * p.BW;
                 y0 = (mt / p.tiles_x) * p.BH;
             }
+            if (p.dyr) {
+                // stage (dx, kc): the A box covers pixel rows y0 - 1 .. y0 + BH of the dx-shifted columns; tap (dy, dx)
+                // reads it from row dy * BW on (a 1024-byte multiple: plain descriptors), with its own weight slab
+                for (int dx = 0; dx < 3; ++dx) {
+                    for (int kc = 0; kc < p.ktiles; ++kc) {
+                        GEMM_WAIT(&empty_bar[s], ph ^ 1);
+                        if (leader) {
+                            uint8_t* sa = ring + s * stage_bytes;
+                            mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
+                            tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx - 1, y0 - 1, z);
+                            for (int dy = 0; dy < 3; ++dy)
+                                tma_load_2d(sa + halo_bytes + dy * p.BN * 128, &p.tmB, &full_bar[s],
+                                            (dy * 3 + dx) * p.kpad + kc * kTileK, n0);
+                        }
+                        __syncwarp();
+                        if (++s == p.stages) {
+                            s = 0;
+                            ph ^= 1;
+                        }
+                    }
+                }
+                continue;
+            }
             for (int tap = 0; tap < p.taps; ++tap) {
                 const int dy = (p.taps == 9) ? tap / 3 - 1 : 0;
                 const int dx = (p.taps == 9) ? tap % 3 - 1 : 0;
-                for (int kc = 0; kc < p.ktiles; ++kc) {
+                for (int kc0 = 0; kc0 < p.ktiles; kc0 += p.kg) {
                     GEMM_WAIT(&empty_bar[s], ph ^ 1);
-                    uint8_t* sa = ring + s * stage_bytes;
-                    uint8_t* sb = sa + kABytes;
                     if (leader) {
                         if (p.dbg & 128) {  // diagnosis: no operand loads
                             mbar_arrive(&full_bar[s]);
                         } else {
                             mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
-                            if (p.a_hold) {  // the stage is a B slab only
-                                tma_load_2d(sa, &p.tmB, &full_bar[s], kc * kTileK, z * p.b_rows_per_batch + n0);
-                            } else {
-                                if (p.mode == 0)
-                                    tma_load_3d(sa, &p.tmA, &full_bar[s], kc * kTileK, mt * kTileM, z);
-                                else
-                                    tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx, y0 + dy, z);
-                                if (!p.b_resident)
-                                    tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK, z * p.b_rows_per_batch + n0);
+                            for (int j = 0; j < p.kg; ++j) {  // kg > 1 only in the plain (A, B) ring
+                                const int kc = kc0 + j;
+                                uint8_t* sa = ring + s * stage_bytes + j * slab_bytes;
+                                uint8_t* sb = sa + kABytes;
+                                if (p.a_hold) {  // the stage is a B slab only
+                                    tma_load_2d(sa, &p.tmB, &full_bar[s], kc * kTileK, z * p.b_rows_per_batch + n0);
+                                } else {
+                                    if (p.mode == 0)
+                                        tma_load_3d(sa, &p.tmA, &full_bar[s], kc * kTileK, mt * kTileM, z);
+                                    else
+                                        tma_load_4d(sa, &p.tmA, &full_bar[s], kc * kTileK, x0 + dx, y0 + dy, z);
+                                    if (!p.b_resident)
+                                        tma_load_2d(sb, &p.tmB, &full_bar[s], tap * p.kpad + kc * kTileK, z * p.b_rows_per_batch + n0);
+                                }
                             }
                         }
                     }
@@ -813,9 +844,22 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
         // descriptors stay warp-uniform), lane 0 alone issues the tcgen05 instructions =====
         const bool leader = elect_one() != 0;  // elect.sync is deterministic for the full mask: always the same lane
         const uint32_t idesc = make_idesc_bf16(kTileM, p.BN, 0, 0);
+#ifdef IRB_GEMM_TRACE  // timing experiment: clock() trace of the MMA issuer of CTA 0 (lines "TM")
+        const bool mtrace = blockIdx.x == 0 && lane == 0 && p.N == IRB_GEMM_TRACE;
+        long long mtv[200];
+        int mti[200];
+        int nmt = 0;
+#define IRB_TM(i) do { if (mtrace && nmt < 200) { mtv[nmt] = clock64(); mti[nmt++] = (i); } } while (0)
+#else
+#define IRB_TM(i) do { } while (0)
+#endif
         int t = 0, nb = 0, cur_z = -1, nhold = 0, cur_hb = 0;
         int s = 0;
         uint32_t ph = 0;
+        // loop invariants of the issue loops, read from the constant bank once
+        const int g_kg = p.kg, g_ktiles = p.ktiles, g_klast = p.klast, g_nst = p.stages;
+        const bool g_hold = p.a_hold != 0, g_bres = p.b_resident != 0, g_nomma = (p.dbg & 64) != 0;
+        const uint32_t g_bn128 = uint32_t(p.BN) * 128, ring_u32 = smem_u32(ring), hold_base = smem_u32(smem);
         TileIter ti;
         for (tile_first(p, ti); ti.w < p.total; tile_next(p, ti), ++t) {
             const int a = t & 1;
@@ -834,42 +878,101 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tc_gemm_kernel(const __grid_c
                     ++nb;
                 }
             }
+            IRB_TM(10);
             GEMM_WAIT(&tempty_bar[a], ((t >> 1) & 1) ^ 1);
+            IRB_TM(11);
             tc_fence_after();
             const uint32_t tacc = tmem_base + a * p.acc_stride;
             const uint32_t bres_tile = smem_u32(smem) + ti.nt * p.ktiles * p.BN * 128;
             int kc = 0;  // chunk within the tap
-            for (int i = 0; i < total_it; ++i) {
-                const int ksteps = (kc == p.ktiles - 1) ? p.klast : kTileK / 16;
-                if (++kc == p.ktiles) kc = 0;
-                GEMM_WAIT(&full_bar[s], ph);
-                tc_fence_after();
-                const uint32_t st_addr = smem_u32(ring + s * stage_bytes);
-                const uint32_t a_addr = p.a_hold ? smem_u32(smem) + (cur_hb * p.ktiles + i) * kABytes : st_addr;
-                const uint32_t b_addr = p.b_resident ? bres_tile + i * p.BN * 128 : (p.a_hold ? st_addr : st_addr + kABytes);
-                // one descriptor per operand and stage; the 32-byte K steps only move the 16-byte-unit address field
-                const uint64_t adesc0 = make_sdesc_sw128(a_addr, 16, 1024);
-                const uint64_t bdesc0 = make_sdesc_sw128(b_addr, 16, 1024);
-                if (leader) {
+            if (p.dyr) {
+                // lean issue loop: everything but the slot address is loop-invariant (the generic loop below spends
+                // ~310 cycles per slab on constant-bank loads and register -> uniform moves, profiles/r02_s75)
+                const uint32_t dstep = uint32_t(p.BW * 128) >> 4, bstep = uint32_t(p.BN * 128) >> 4;
+                for (int i = 0; i < total_it; ++i) {
+                    const int ksteps = (kc == g_ktiles - 1) ? g_klast : kTileK / 16;
+                    if (++kc == g_ktiles) kc = 0;
+                    IRB_TM(12);
+                    GEMM_WAIT(&full_bar[s], ph);
+                    IRB_TM(13);
+                    tc_fence_after();
+                    const uint32_t st_addr = ring_u32 + s * stage_bytes;
+                    const uint64_t adesc0 = make_sdesc_sw128(st_addr, 16, 1024);
+                    const uint64_t bdesc0 = make_sdesc_sw128(st_addr + halo_bytes, 16, 1024);
+                    if (leader) {
 #pragma unroll
-                    for (int k = 0; k < kTileK / 16; ++k) {
-                        if (k < ksteps && !(p.dbg & 64))  // K steps past the data are zeros on both sides: skipped
-                            umma_bf16(tacc, adesc0 + uint64_t(k * 2), bdesc0 + uint64_t(k * 2), idesc, (i | k) != 0 ? 1u : 0u);
+                        for (int dy = 0; dy < 3; ++dy) {
+#pragma unroll
+                            for (int k = 0; k < kTileK / 16; ++k) {
+                                if (k < ksteps)
+                                    umma_bf16(tacc, adesc0 + uint64_t(dy * dstep + k * 2), bdesc0 + uint64_t(dy * bstep + k * 2),
+                                              idesc, (i | dy | k) != 0 ? 1u : 0u);
+                            }
+                        }
+                        umma_commit(&empty_bar[s]);
                     }
-                    umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
+                    IRB_TM(15);
+                    __syncwarp();
+                    if (++s == g_nst) {
+                        s = 0;
+                        ph ^= 1;
+                    }
                 }
-                __syncwarp();
-                if (++s == p.stages) {
-                    s = 0;
-                    ph ^= 1;
+            } else {
+                // same idea for the generic ring: the loop-invariant parameters live in registers (hoisted above the tile
+                // loop), the operand addresses are one select per mode
+                const uint32_t hold_a = hold_base + uint32_t(cur_hb * g_ktiles) * kABytes;
+                for (int i = 0; i < total_it; ++i) {
+                    IRB_TM(12);
+                    GEMM_WAIT(&full_bar[s], ph);
+                    IRB_TM(13);
+                    tc_fence_after();
+                    const uint32_t st_addr = ring_u32 + s * stage_bytes;
+                    for (int j = 0; j < g_kg; ++j) {  // slabs of this stage (kg > 1 only in the plain (A, B) ring)
+                        const int ksteps = (kc == g_ktiles - 1) ? g_klast : kTileK / 16;
+                        if (++kc == g_ktiles) kc = 0;
+                        const int gi = i * g_kg + j;
+                        const uint32_t sl_addr = st_addr + j * slab_bytes;
+                        const uint32_t a_addr = g_hold ? hold_a + gi * kABytes : sl_addr;
+                        const uint32_t b_addr = g_bres ? bres_tile + gi * g_bn128 : (g_hold ? sl_addr : sl_addr + kABytes);
+                        // one descriptor per operand and slab; the 32-byte K steps only move the 16-byte-unit address field
+                        const uint64_t adesc0 = make_sdesc_sw128(a_addr, 16, 1024);
+                        const uint64_t bdesc0 = make_sdesc_sw128(b_addr, 16, 1024);
+                        if (leader) {
+#pragma unroll
+                            for (int k = 0; k < kTileK / 16; ++k) {
+                                if (k < ksteps && !g_nomma)  // K steps past the data are zeros on both sides: skipped
+                                    umma_bf16(tacc, adesc0 + uint64_t(k * 2), bdesc0 + uint64_t(k * 2), idesc, (gi | k) != 0 ? 1u : 0u);
+                            }
+                        }
+                        IRB_TM(14);
+                    }
+                    if (leader) umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
+                    IRB_TM(15);
+                    __syncwarp();
+                    IRB_TM(16);
+                    if (++s == g_nst) {
+                        s = 0;
+                        ph ^= 1;
+                    }
                 }
             }
+            IRB_TM(17);
             if (leader) {
                 umma_commit(&tfull_bar[a]);  // accumulator complete
                 if (p.a_hold && ti.nt == p.tiles_n - 1) umma_commit(&ah_empty[cur_hb]);  // the held A tile is done
             }
+            IRB_TM(18);
             __syncwarp();
+            IRB_TM(19);
         }
+#ifdef IRB_GEMM_TRACE
+        if (mtrace) {
+            static __device__ int mprinted;
+            if (atomicAdd(&mprinted, 1) == 0)
+                for (int i = 1; i < nmt; ++i) printf("TM %d %d %lld\n", i, mti[i], mtv[i] - mtv[i - 1]);
+        }
+#endif
     } else if (warp >= 2) {
         // ===== epilogue: TMEM -> registers -> global. Two sets of 4 warps: set s drains accumulator s, i.e. the
         // tiles t of this CTA with (t & 1) == s, so two tiles are in the epilogue at once and the sets never wait
@@ -1340,6 +1443,31 @@ static int launch_tc(TcGemmParams& p, int batch, cudaStream_t stream) {
             p.a_hold = 0;
         }
     }
+    // Narrow tiles: one ring handshake of the MMA issuer (full wait, descriptors, commit, empty wait on the producer side)
+    // costs 150 - 200 cycles, a 64-column slab is only 4 x 32 = 128 cycles of tensor-core time: HAT's [180 -> 60] CAB
+    // convolution ran at the SAME speed without its operand loads and without its MMAs (IRB_GEMM_DBG 128 / 64,
+    // profiles/r02_s72): 27 handshakes per tile bound it. Such tiles put kg K slabs into one stage (the smallest divisor
+    // of ktiles that gives a stage >= 384 tensor-core cycles and still leaves two stages).
+    if (p.dyr) {  // planned by tc_conv3x3 (narrow tiles only): A halo box + three weight slabs per stage
+        ring_stage = size_t(p.BH + 2) * p.BW * 128 + 3 * size_t(p.BN) * 128;
+        stages = int((227 * 1024 - fixed) / ring_stage);
+        IRB_REQUIRE(stages >= 2, "tc_conv3x3: dy-reuse stage does not fit");
+        if (stages > 8) stages = 8;
+    }
+    p.kg = 1;
+    static int kg_on = -1;
+    if (kg_on < 0) kg_on = IRB_DIAG_ENV("IRB_GEMM_KG", 1);
+    if (kg_on && !p.dyr && !p.b_resident && !p.a_hold && p.ktiles > 1 && p.BN <= (kg_on >= 2 ? 128 : 64)) {
+        for (int kg = 2; kg <= p.ktiles; ++kg) {
+            if (p.ktiles % kg) continue;
+            const int st = int((227 * 1024 - fixed) / (size_t(kg) * stage_bytes));
+            if (st < 2) break;
+            p.kg = kg;
+            stages = st > 8 ? 8 : st;
+            ring_stage = size_t(kg) * stage_bytes;
+            if (2 * p.BN * kg >= 384) break;
+        }
+    }
     p.stages = stages;
     const long long total = (long long)batch * p.tiles_m * p.tiles_n;
     IRB_REQUIRE(total < (1ll << 31), "tc_gemm: too many tiles");
@@ -1439,15 +1567,22 @@ int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, cons
                 "tc_conv3x3: operands must be 16-byte aligned");
     IRB_REQUIRE(kpad >= C, "tc_conv3x3: kpad < C");
     TcGemmParams p{};
-    // pixel box: as wide as the row allows, 128 pixels in total
+    // pixel box of 128 pixels: as wide as the row allows
     int BW = 128;
     while (BW > 8 && BW > W) BW >>= 1;
     if (BW > W) BW = 8;
+    // Narrow outputs (BN <= 64: HAT's / SwinIR's C -> C / 3 compress convolutions): a 16 x 8 pixel box, and ONE A box of
+    // 16 x 10 pixels per (dx, K slab) that serves the three dy taps (p.dyr): 396 KB instead of 648 KB through the L2
+    // fabric per tile at K = 180, which at 10 TB/s was one of the two bounds of that convolution (profiles/r02_s72-s76)
+    static int dyr_on = -1;
+    if (dyr_on < 0) dyr_on = IRB_DIAG_ENV("IRB_CONV_DYR", 1);
+    p.dyr = (dyr_on && pick_bn(N) <= 64 && W >= 16 && H >= 8 && epi.ps == 0) ? 1 : 0;
+    if (p.dyr) BW = 16;
     const int BH = 128 / BW;
     {
         uint64_t dims[4] = {uint64_t(C), uint64_t(W), uint64_t(H), uint64_t(Nimg)};
         uint64_t str[3] = {uint64_t(lda) * 2, uint64_t(lda) * 2 * W, uint64_t(lda) * 2 * W * H};
-        uint32_t box[4] = {kTileK, uint32_t(BW), uint32_t(BH), 1};
+        uint32_t box[4] = {kTileK, uint32_t(BW), uint32_t(p.dyr ? BH + 2 : BH), 1};
         IRB_TRY(make_tmap_bf16(&p.tmA, A, 4, dims, str, box));
     }
     p.mode = 1;
