@@ -1567,10 +1567,24 @@ int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, cons
                 "tc_conv3x3: operands must be 16-byte aligned");
     IRB_REQUIRE(kpad >= C, "tc_conv3x3: kpad < C");
     TcGemmParams p{};
-    // pixel box of 128 pixels: as wide as the row allows
+    // pixel box of 128 pixels: the shape that covers the image with the fewest boxes (a 544-wide HAT tile takes five
+    // 128 x 1 boxes per row, 15 % of them padding, but exactly 17 x 136 boxes of 32 x 4), the widest one on a tie
     int BW = 128;
     while (BW > 8 && BW > W) BW >>= 1;
     if (BW > W) BW = 8;
+    static int shape_on = -1;
+    if (shape_on < 0) shape_on = IRB_DIAG_ENV("IRB_CONV_SHAPE", 1);
+    if (shape_on) {
+        long long best = (long long)ceil_div(W, BW) * ceil_div(H, 128 / BW);
+        const int bw_min = epi.ps == 3 ? 32 : 8;   // the PixelShuffle TMA store wants >= 32 pixels of one row
+        for (int bw = BW >> 1; bw >= bw_min; bw >>= 1) {
+            const long long n = (long long)ceil_div(W, bw) * ceil_div(H, 128 / bw);
+            if (n < best) {
+                best = n;
+                BW = bw;
+            }
+        }
+    }
     // Narrow outputs (BN <= 64: HAT's / SwinIR's C -> C / 3 compress convolutions): a 16 x 8 pixel box, and ONE A box of
     // 16 x 10 pixels per (dx, K slab) that serves the three dy taps (p.dyr): 396 KB instead of 648 KB through the L2
     // fabric per tile at K = 180, which at 10 TB/s was one of the two bounds of that convolution (profiles/r02_s72-s76)
