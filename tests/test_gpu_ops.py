@@ -71,6 +71,11 @@ def test_gemm_batched_per_image_weights_on_a_channel_slice(dt, tol):
 @pytest.mark.parametrize("n,H,W,Cin,N", [(2, 32, 32, 48, 24), (1, 24, 40, 96, 192), (2, 16, 16, 384, 768),
                                          (1, 40, 24, 180, 180), (1, 64, 64, 96, 3), (1, 33, 20, 64, 64),
                                          (1, 8, 8, 60, 240), (1, 136, 8, 64, 256),
+                                         # outputs <= 64 wide: the dy-reuse path (16 x 10 pixel A box per dx), three K
+                                         # slabs with a partial last one, ragged in both directions, several images
+                                         (1, 21, 50, 180, 60), (2, 16, 48, 240, 60), (1, 9, 17, 64, 16),
+                                         # box shape by fewest boxes: 544 wide -> 32 x 4 boxes, ragged rows
+                                         (1, 6, 544, 60, 180),
                                          # N <= 4: the shared-memory stencil kernel (conv_small.cu), ragged tiles / chunks
                                          (2, 37, 45, 180, 3), (1, 9, 70, 64, 1), (1, 20, 33, 64, 4), (3, 16, 32, 96, 2)])
 def test_conv3x3_implicit_gemm(dt, tol, n, H, W, Cin, N):
