@@ -14,6 +14,8 @@
 #include "../../include/irb200.h"
 #include "common.cuh"
 #include "kernels.h"
+#include <type_traits>
+#include <cstring>
 
 namespace irb {
 
@@ -257,50 +259,54 @@ __global__ void __launch_bounds__(kPoolThreads) chan_pool_kernel(const void* __r
 }
 
 // The same with 4 channels per thread (8-byte bf16 / 16-byte fp32 loads): C % 4 == 0, rows 8 / 16-byte aligned.
+// 512-thread blocks at <= 64 registers so that two are resident per SM (the first version's 1024-thread block at 63
+// registers was alone on its SM, 64 KB of loads in flight, 4 waves of blocks: 0.34 of the DRAM peak, ncu
+// profiles/r02_s82); every pass is a batch of U raw loads (bf16: 16 x 8 bytes, 128 KB in flight per SM), the last one
+// predicated instead of a one-load-at-a-time remainder loop.
+static constexpr int kPool4Threads = 512;
 template <typename T>
-__global__ void __launch_bounds__(kPoolThreads) chan_pool4_kernel(const T* __restrict__ x, long long ldx, long long hw, int C,
-                                                                  int slabs, float* __restrict__ sums) {
+__global__ void __launch_bounds__(kPool4Threads, 2) chan_pool4_kernel(const T* __restrict__ x, long long ldx, long long hw,
+                                                                      int C, int slabs, float* __restrict__ sums) {
     extern __shared__ float pool_sm[];  // [phases][C]
     const int img = blockIdx.y, slab = blockIdx.x;
     const int C4 = C >> 2;
-    const int phases = kPoolThreads / C4;
+    const int phases = kPool4Threads / C4;
     const long long per = (hw + slabs - 1) / slabs;
     const long long p0 = slab * per, p1 = p0 + per < hw ? p0 + per : hw;
-    const T* xb = x + (long long)img * hw * ldx;
     const int t = threadIdx.x;
     if (t < phases * C4) {
         const int ph = t / C4, c = (t - ph * C4) * 4;
-        constexpr int U = 8;  // independent loads in flight per thread
+        const T* xb = x + (long long)img * hw * ldx + c;
+        constexpr int U = sizeof(T) == 4 ? 8 : 16;  // independent loads in flight per thread
+        typedef typename std::conditional<sizeof(T) == 4, float4, uint2>::type Raw;
         float4 a[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-        auto ld4 = [&](long long px) -> float4 {
-            if (sizeof(T) == 4) return *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xb) + px * ldx + c);
-            const uint2 v = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(xb) + px * ldx + c);
-            float4 r;
-            unpack_bf16x2(v.x, r.x, r.y);
-            unpack_bf16x2(v.y, r.z, r.w);
-            return r;
-        };
-        long long px = p0 + ph;
-        for (; px + (U - 1) * phases < p1; px += U * phases) {
-            float4 v[U];
-#pragma unroll
-            for (int u = 0; u < U; ++u) v[u] = ld4(px + u * phases);
+        const long long step = (long long)phases * ldx;
+        for (long long px = p0 + ph; px < p1; px += U * phases) {
+            Raw v[U];
+            const T* q = xb + px * ldx;
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                a[u & 3].x += v[u].x;
-                a[u & 3].y += v[u].y;
-                a[u & 3].z += v[u].z;
-                a[u & 3].w += v[u].w;
+                if (px + u * phases < p1)
+                    v[u] = *reinterpret_cast<const Raw*>(q + u * step);
+                else
+                    memset(&v[u], 0, sizeof(Raw));   // +0.0 in both formats
             }
-        }
-        for (; px < p1; px += phases) {
-            const float4 v = ld4(px);
-            a[0].x += v.x;
-            a[0].y += v.y;
-            a[0].z += v.z;
-            a[0].w += v.w;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                float4 f;
+                if constexpr (sizeof(T) == 4) {
+                    f = v[u];
+                } else {
+                    unpack_bf16x2(v[u].x, f.x, f.y);
+                    unpack_bf16x2(v[u].y, f.z, f.w);
+                }
+                a[u & 3].x += f.x;
+                a[u & 3].y += f.y;
+                a[u & 3].z += f.z;
+                a[u & 3].w += f.w;
+            }
         }
         float* o = pool_sm + ph * C + c;
         o[0] = (a[0].x + a[1].x) + (a[2].x + a[3].x);
@@ -309,7 +315,7 @@ __global__ void __launch_bounds__(kPoolThreads) chan_pool4_kernel(const T* __res
         o[3] = (a[0].w + a[1].w) + (a[2].w + a[3].w);
     }
     __syncthreads();
-    for (int c = threadIdx.x; c < C; c += kPoolThreads) {
+    for (int c = threadIdx.x; c < C; c += kPool4Threads) {
         float acc = 0.f;
         for (int ph = 0; ph < phases; ++ph) acc += pool_sm[ph * C + c];
         sums[((long long)img * slabs + slab) * C + c] = acc;
@@ -317,6 +323,11 @@ __global__ void __launch_bounds__(kPoolThreads) chan_pool4_kernel(const T* __res
 }
 
 // scale[img][c] = out_scale * sigmoid(W2 . relu(W1 . mean + b1) + b2)   (ChannelAttention.forward, hat_arch.py:47-58)
+// slab groups of the first phase: one group per (C / 4)-thread slice of the block when C % 4 == 0, per C threads otherwise
+__host__ __device__ inline int ca_groups(int threads, int C) {
+    const int per = (C % 4 == 0) ? C / 4 : C;
+    return threads / per > 0 ? threads / per : 1;
+}
 __global__ void ca_scale_kernel(const float* __restrict__ sums, int slabs, float inv_hw, int C, int Cs, const float* __restrict__ w1,
                                 const float* __restrict__ b1, const float* __restrict__ w2, const float* __restrict__ b2,
                                 float out_scale, float* __restrict__ scale) {
@@ -325,19 +336,50 @@ __global__ void ca_scale_kernel(const float* __restrict__ sums, int slabs, float
     float* hid = ca_sm + C;          // [Cs]
     float* part = ca_sm + C + Cs;    // [groups][C]
     const int img = blockIdx.x;
-    const int groups = blockDim.x / C > 0 ? blockDim.x / C : 1;
-    for (int t = threadIdx.x; t < groups * C; t += blockDim.x) {
-        const int gq = t / C, c = t - gq * C;
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;   // fixed association: the result does not depend on scheduling
-        int sl = gq;
-        for (; sl + 3 * groups < slabs; sl += 4 * groups) {
-            a0 += sums[((long long)img * slabs + sl) * C + c];
-            a1 += sums[((long long)img * slabs + sl + groups) * C + c];
-            a2 += sums[((long long)img * slabs + sl + 2 * groups) * C + c];
-            a3 += sums[((long long)img * slabs + sl + 3 * groups) * C + c];
+    const int groups = ca_groups(blockDim.x, C);
+    if (C % 4 == 0) {
+        // thread = (slab group, 4 channels): 16-byte loads, blockDim / (C / 4) groups (22 at C = 180: a few hundred slabs
+        // are 4 batches of 4 independent loads per thread, not 30 rounds of scalar ones)
+        const int C4 = C >> 2;
+        const float4* s4 = reinterpret_cast<const float4*>(sums + (long long)img * slabs * C);
+        for (int t = threadIdx.x; t < groups * C4; t += blockDim.x) {
+            const int gq = t / C4, c4 = t - gq * C4;
+            float4 a[4];   // fixed association: the result does not depend on scheduling
+#pragma unroll
+            for (int u = 0; u < 4; ++u) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int sl = gq; sl < slabs; sl += 4 * groups) {
+                float4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    v[u] = sl + u * groups < slabs ? s4[(long long)(sl + u * groups) * C4 + c4] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    a[u].x += v[u].x;
+                    a[u].y += v[u].y;
+                    a[u].z += v[u].z;
+                    a[u].w += v[u].w;
+                }
+            }
+            float* o = part + gq * C + c4 * 4;
+            o[0] = (a[0].x + a[1].x) + (a[2].x + a[3].x);
+            o[1] = (a[0].y + a[1].y) + (a[2].y + a[3].y);
+            o[2] = (a[0].z + a[1].z) + (a[2].z + a[3].z);
+            o[3] = (a[0].w + a[1].w) + (a[2].w + a[3].w);
         }
-        for (; sl < slabs; sl += groups) a0 += sums[((long long)img * slabs + sl) * C + c];
-        part[t] = (a0 + a1) + (a2 + a3);
+    } else {
+        for (int t = threadIdx.x; t < groups * C; t += blockDim.x) {
+            const int gq = t / C, c = t - gq * C;
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+            int sl = gq;
+            for (; sl + 3 * groups < slabs; sl += 4 * groups) {
+                a0 += sums[((long long)img * slabs + sl) * C + c];
+                a1 += sums[((long long)img * slabs + sl + groups) * C + c];
+                a2 += sums[((long long)img * slabs + sl + 2 * groups) * C + c];
+                a3 += sums[((long long)img * slabs + sl + 3 * groups) * C + c];
+            }
+            for (; sl < slabs; sl += groups) a0 += sums[((long long)img * slabs + sl) * C + c];
+            part[t] = (a0 + a1) + (a2 + a3);
+        }
     }
     __syncthreads();
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
@@ -412,13 +454,14 @@ int channel_attention_scale(const void* y, int dt, long long ldy, int n, long lo
     IRB_REQUIRE(C >= 1 && C <= 1024 && Cs >= 1 && Cs <= 256, "channel_attention: bad channel counts");
     const int slabs = channel_attention_slabs(n, hw);
     const size_t esz = dt == DT_F32 ? 4 : 2;
-    if (C % 4 == 0 && (ldy * esz) % (4 * esz) == 0 && (reinterpret_cast<uintptr_t>(y) & (4 * esz - 1)) == 0) {
-        const int phases = kPoolThreads / (C / 4);
+    if (C % 4 == 0 && C / 4 <= kPool4Threads && (ldy * esz) % (4 * esz) == 0 &&
+        (reinterpret_cast<uintptr_t>(y) & (4 * esz - 1)) == 0) {
+        const int phases = kPool4Threads / (C / 4);
         const size_t sm = size_t(phases) * C * sizeof(float);
         if (dt == DT_F32)
-            chan_pool4_kernel<float><<<dim3(slabs, n), kPoolThreads, sm, stream>>>((const float*)y, ldy, hw, C, slabs, sums);
+            chan_pool4_kernel<float><<<dim3(slabs, n), kPool4Threads, sm, stream>>>((const float*)y, ldy, hw, C, slabs, sums);
         else
-            chan_pool4_kernel<bf16><<<dim3(slabs, n), kPoolThreads, sm, stream>>>((const bf16*)y, ldy, hw, C, slabs, sums);
+            chan_pool4_kernel<bf16><<<dim3(slabs, n), kPool4Threads, sm, stream>>>((const bf16*)y, ldy, hw, C, slabs, sums);
     } else {
         const int phases = kPoolThreads / C > 0 ? kPoolThreads / C : 1;
         chan_pool_kernel<<<dim3(slabs, n), kPoolThreads, size_t(phases) * C * sizeof(float), stream>>>(y, dt, ldy, hw, C,
@@ -427,7 +470,7 @@ int channel_attention_scale(const void* y, int dt, long long ldy, int n, long lo
     IRB_CHECK_CUDA(cudaGetLastError());
     prof_mark("chan_pool", C, 0, 0.0, double(n) * hw * C * (dt == DT_F32 ? 4 : 2), stream);
     {
-        const int groups = 1024 / C > 0 ? 1024 / C : 1;
+        const int groups = ca_groups(1024, C);
         ca_scale_kernel<<<n, 1024, size_t(C + Cs + groups * C) * sizeof(float), stream>>>(sums, slabs, 1.0f / float(hw), C,
                                                                                          Cs, w1, b1, w2, b2, out_scale,
                                                                                          scale);

@@ -48,6 +48,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const TI* __restrict__ x
     const long long row = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / LPP;
     const bool active = row < rows;
     const int nch = C >> 2;
+    const bool vec_wb = ((reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(bias)) & 15) == 0;
     float v[MAXCH][4];
     float s = 0.f;
 #pragma unroll
@@ -83,15 +84,27 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const TI* __restrict__ x
     for (int j = 0; j < MAXCH; ++j) {
         const int ch = lane + j * LPP;
         if (ch < nch) {
-            float o4[4];
+            float o4[4], g4[4], b4[4] = {0.f, 0.f, 0.f, 0.f};
+            if (vec_wb) {  // one 16-byte load per vector and chunk instead of four (eight) scalar ones
+                const float4 g = __ldg(reinterpret_cast<const float4*>(w) + ch);
+                g4[0] = g.x, g4[1] = g.y, g4[2] = g.z, g4[3] = g.w;
+                if (mode == 0 && bias) {
+                    const float4 b = __ldg(reinterpret_cast<const float4*>(bias) + ch);
+                    b4[0] = b.x, b4[1] = b.y, b4[2] = b.z, b4[3] = b.w;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    g4[i] = __ldg(w + ch * 4 + i);
+                    if (mode == 0 && bias) b4[i] = __ldg(bias + ch * 4 + i);
+                }
+            }
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const int c = ch * 4 + i;
-                const float g = __ldg(w + c);
                 if (mode == 0)
-                    o4[i] = (v[j][i] - mu) * rstd * g + (bias ? __ldg(bias + c) : 0.f);
+                    o4[i] = (v[j][i] - mu) * rstd * g4[i] + b4[i];
                 else
-                    o4[i] = v[j][i] * rstd * g;
+                    o4[i] = v[j][i] * rstd * g4[i];
             }
             Vec4<TO>::store(y + row * ldy + ch * 4, o4);
         }
