@@ -72,19 +72,14 @@ __global__ void __launch_bounds__(kCsThreads) conv3x3_small_n_kernel(const ConvS
         const int hy = px / hw, hx = px - hy * hw;
         const int gy = y0 + hy - 1, gx = x0 + hx - 1;
         const bool inside = gy >= 0 && gy < p.H && gx >= 0 && gx < p.W;
-        const bf16* src = p.x + (((long long)img * p.H + gy) * p.W + gx) * p.ldx + ck * 8;
-        if (inside && ck * 8 + 8 <= p.C) {
-            cp_async16(halo_s0 + (px * p.pstride + ck) * 16, src);
-        } else {
-            uint4 v = make_uint4(0u, 0u, 0u, 0u);
-            if (inside) {  // ragged last chunk (C % 8 != 0): element-wise, the rest stays zero
-                bf16 t[8];
-#pragma unroll
-                for (int k = 0; k < 8; ++k) t[k] = (ck * 8 + k < p.C) ? src[k] : __float2bfloat16(0.f);
-                v = *reinterpret_cast<const uint4*>(t);
-            }
-            halo[px * p.pstride + ck] = v;
-        }
+        // one zero-filling cp.async for every item: whole chunks copy 16 bytes, the ragged last chunk (C % 8 != 0) its
+        // valid channels, out-of-image pixels nothing (src_bytes 0 reads no memory). The first version took a
+        // load -> pack -> store path for ragged chunks: with C = 180 every warp holds one (23 chunks per pixel), so
+        // every pass of every warp waited a DRAM round trip: 44 % of the kernel's stall samples on that one
+        // instruction, 0.037 of the HBM peak (ncu profiles/r02_s85).
+        const int valid = inside ? min(8, p.C - ck * 8) * 2 : 0;
+        const bf16* src = inside ? p.x + (((long long)img * p.H + gy) * p.W + gx) * p.ldx + ck * 8 : p.x;
+        cp_async16_zfill(halo_s0 + (px * p.pstride + ck) * 16, src, valid);
     }
     cp_async_commit();
     cp_async_wait<0>();
@@ -216,7 +211,11 @@ int conv3x3_bf16(const bf16* x, long long ldx, int Nimg, int H, int W, int C, co
     if (on < 0) {
         on = IRB_DIAG_ENV("IRB_CONV_SMALLN", 1);
     }
-    if (on && conv3x3_small_n_ok(C, N, epi) && ldx % 8 == 0 && Nimg <= 65535)
+    // With two or more 64-channel K slabs the implicit GEMM's dy-reuse path (gemm_tc.cu, one 16 x 10 pixel A box per
+    // (dx, K slab), N padded to 16) now beats the stencil: [180 -> 3] 0.09 vs 0.19 ms, [96 -> 3] 0.35 vs 0.37 ms; with one
+    // slab ([64 -> 3] at HR resolution) the stencil wins, 1.32 vs 1.63 ms (profiles/r02_s87, same box).
+    const bool stencil = C <= 64 || W < 16 || H < 8;
+    if (on && stencil && conv3x3_small_n_ok(C, N, epi) && ldx % 8 == 0 && Nimg <= 65535)
         return conv3x3_small_n(x, ldx, Nimg, H, W, C, Wt, kpad, N, epi, stream);
     return tc_conv3x3(x, ldx, Nimg, H, W, C, Wt, kpad, N, w_rows_total, epi, stream);
 }
