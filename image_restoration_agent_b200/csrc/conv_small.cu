@@ -17,7 +17,11 @@
 namespace irb {
 
 static constexpr int kCsTW = 32;       // tile width  (= lanes of a warp)
-static constexpr int kCsWarps = 4;     // rows of threads
+#ifndef IRB_CS_WARPS
+#define IRB_CS_WARPS 8
+#endif
+static constexpr int kCsWarps = IRB_CS_WARPS;     // rows of threads (8: sixteen warps per SM at two CTAs, PX = 2 / 1)
+static constexpr int kCsPxBig = 16 / kCsWarps, kCsPxSmall = 8 / kCsWarps;   // pixels per thread of the 16- / 8-row tile
 static constexpr int kCsThreads = kCsTW * kCsWarps;
 
 struct ConvSmallParams {
@@ -148,7 +152,7 @@ bool conv3x3_small_n_ok(int C, int N, const Epi& e) {
     if (!(N >= 1 && N <= 4 && C >= 16 && C <= 256 && e.ps == 0 && e.ln_stats == nullptr && e.stats_out == nullptr))
         return false;
     const int nchunk = (C + 7) / 8, pstride = nchunk | 1;
-    const size_t smem = size_t(2 * kCsWarps + 2) * (kCsTW + 2) * pstride * 16 + size_t(9) * nchunk * 4 * 32;
+    const size_t smem = size_t(8 + 2) * (kCsTW + 2) * pstride * 16 + size_t(9) * nchunk * 4 * 32;
     return smem <= 200 * 1024;
 }
 
@@ -181,10 +185,11 @@ int conv3x3_small_n(const bf16* x, long long ldx, int Nimg, int H, int W, int C,
     p.pstride = p.nchunk | 1;
     p.nchunk_magic = uint32_t(((1ull << 32) + p.nchunk - 1) / p.nchunk);
     p.epi = epi;
-    // 4 pixels per thread (16-row tiles) when two CTAs of that size still fit an SM, else 2 (8-row tiles)
+    // 16-row tiles (kCsPxBig pixels per thread) when two CTAs of that size still fit an SM, else 8-row tiles. Eight warps
+    // per CTA instead of four (same tiles, half the pixels per thread): [64 -> 3] 2.58 -> 2.26 ms (profiles/r02_s92)
     const size_t wbytes = size_t(9) * p.nchunk * (N <= 1 ? 1 : (N <= 3 ? 3 : 4)) * 32;
-    const size_t smem4 = size_t(4 * kCsWarps + 2) * (kCsTW + 2) * p.pstride * 16 + wbytes;
-    const size_t smem2 = size_t(2 * kCsWarps + 2) * (kCsTW + 2) * p.pstride * 16 + wbytes;
+    const size_t smem4 = size_t(16 + 2) * (kCsTW + 2) * p.pstride * 16 + wbytes;
+    const size_t smem2 = size_t(8 + 2) * (kCsTW + 2) * p.pstride * 16 + wbytes;
     const bool px4 = smem4 <= 100 * 1024 && H >= 16;
     const int TH = px4 ? 16 : 8;
     p.tiles_x = ceil_div(W, kCsTW);
@@ -192,11 +197,11 @@ int conv3x3_small_n(const bf16* x, long long ldx, int Nimg, int H, int W, int C,
     const size_t smem = px4 ? smem4 : smem2;
     int rc;
     if (N <= 1)
-        rc = px4 ? launch_cs<4, 1>(p, smem, stream) : launch_cs<2, 1>(p, smem, stream);
+        rc = px4 ? launch_cs<kCsPxBig, 1>(p, smem, stream) : launch_cs<kCsPxSmall, 1>(p, smem, stream);
     else if (N <= 3)
-        rc = px4 ? launch_cs<4, 3>(p, smem, stream) : launch_cs<2, 3>(p, smem, stream);
+        rc = px4 ? launch_cs<kCsPxBig, 3>(p, smem, stream) : launch_cs<kCsPxSmall, 3>(p, smem, stream);
     else
-        rc = px4 ? launch_cs<4, 4>(p, smem, stream) : launch_cs<2, 4>(p, smem, stream);
+        rc = px4 ? launch_cs<kCsPxBig, 4>(p, smem, stream) : launch_cs<kCsPxSmall, 4>(p, smem, stream);
     IRB_TRY(rc);
     const double rows = double(H) * W * Nimg;
     prof_mark("conv3x3_small_n", C, N, 18.0 * rows * C * N, rows * C * 2 + 9.0 * N * C * 2 + epi_bytes(epi, rows, N), stream);
