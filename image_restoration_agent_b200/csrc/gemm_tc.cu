@@ -1590,7 +1590,7 @@ int tc_conv3x3(const bf16* A, long long lda, int Nimg, int H, int W, int C, cons
     // fabric per tile at K = 180, which at 10 TB/s was one of the two bounds of that convolution (profiles/r02_s72-s76)
     static int dyr_on = -1;
     if (dyr_on < 0) dyr_on = IRB_DIAG_ENV("IRB_CONV_DYR", 1);
-    p.dyr = (dyr_on && pick_bn(N) <= 64 && W >= 16 && H >= 8 && epi.ps == 0) ? 1 : 0;
+    p.dyr = (dyr_on && pick_bn(N) <= 64 && W >= 16 && H >= 8 && epi.ps != 3) ? 1 : 0;   // not with the 5-D PixelShuffle TMA store (needs >= 32 pixels of a row)
     if (p.dyr) BW = 16;
     const int BH = 128 / BW;
     {
