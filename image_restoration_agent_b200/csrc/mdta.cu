@@ -358,37 +358,55 @@ __global__ void __launch_bounds__(256) mdta_softmax_kernel(const float* __restri
 template <int RPT>
 __global__ void __launch_bounds__(256) mdta_weff_kernel(const float* __restrict__ attn, const float* __restrict__ Wp,
                                                         int C, int heads, void* __restrict__ Weff, int w_dt) {
-    extern __shared__ float sm[];  // attn [c][c] then Wp rows [64][c + 1]
+    extern __shared__ __align__(16) float sm[];  // attn [c][cs] then Wp rows [16 * RPT][c + 1]
     const int c = C / heads;
     const int head = blockIdx.y, img = blockIdx.z;
     constexpr int kWeffRows = 16 * RPT;
     const int o0 = blockIdx.x * kWeffRows;
     float* s_attn = sm;
-    float* s_w = sm + c * c;
     const int wld = c + 1;  // odd-ish stride: the 4 rows of a thread and the row groups of a warp spread over banks
+    const int cs = (c + 3) & ~3;  // attn row stride in shared memory (16-byte rows; the pad columns are zero)
+    float* s_w2 = sm + c * cs;
     const float* a = attn + ((long long)img * heads + head) * c * c;
-    for (int e = threadIdx.x; e < c * c; e += 256) s_attn[e] = a[e];
+    for (int e = threadIdx.x; e < c * cs; e += 256) {
+        const int i = e / cs, j = e - i * cs;
+        s_attn[e] = j < c ? a[i * c + j] : 0.f;
+    }
     for (int e = threadIdx.x; e < kWeffRows * c; e += 256) {
         const int r = e / c, i = e - r * c;
-        s_w[r * wld + i] = (o0 + r < C) ? __ldg(Wp + (long long)(o0 + r) * C + head * c + i) : 0.f;
+        s_w2[r * wld + i] = (o0 + r < C) ? __ldg(Wp + (long long)(o0 + r) * C + head * c + i) : 0.f;
     }
     __syncthreads();
-    for (int e = threadIdx.x; e < 16 * c; e += 256) {
-        const int rq = e / c, j = e - rq * c;
-        float acc[RPT];
+    // thread = RPT rows x 4 columns: per i one 16-byte attn load and RPT weight loads feed 4 * RPT FMAs (the first version's
+    // RPT rows x 1 column issued 5 shared-memory loads per 4 FMAs and was bound by them: 45 us for 0.64 GFLOP at level 4)
+    const int c4 = cs >> 2;
+    for (int e = threadIdx.x; e < 16 * c4; e += 256) {
+        const int rq = e / c4, j = (e - rq * c4) * 4;
+        float acc[RPT][4];
 #pragma unroll
-        for (int k = 0; k < RPT; ++k) acc[k] = 0.f;
-        const float* w0 = s_w + rq * wld;
+        for (int k = 0; k < RPT; ++k) acc[k][0] = acc[k][1] = acc[k][2] = acc[k][3] = 0.f;
+        const float* w0 = s_w2 + rq * wld;
 #pragma unroll 4
         for (int i = 0; i < c; ++i) {
-            const float av = s_attn[i * c + j];
+            const float4 av = *reinterpret_cast<const float4*>(s_attn + i * cs + j);
 #pragma unroll
-            for (int k = 0; k < RPT; ++k) acc[k] = fmaf(w0[k * 16 * wld + i], av, acc[k]);
+            for (int k = 0; k < RPT; ++k) {
+                const float w = w0[k * 16 * wld + i];
+                acc[k][0] = fmaf(w, av.x, acc[k][0]);
+                acc[k][1] = fmaf(w, av.y, acc[k][1]);
+                acc[k][2] = fmaf(w, av.z, acc[k][2]);
+                acc[k][3] = fmaf(w, av.w, acc[k][3]);
+            }
         }
         const long long ob = ((long long)img * C + o0 + rq) * C + head * c + j;
 #pragma unroll
-        for (int k = 0; k < RPT; ++k)
-            if (o0 + rq + 16 * k < C) st_from_float(Weff, ob + (long long)(16 * k) * C, w_dt, acc[k]);
+        for (int k = 0; k < RPT; ++k) {
+            if (o0 + rq + 16 * k < C) {
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj)
+                    if (j + jj < c) st_from_float(Weff, ob + (long long)(16 * k) * C + jj, w_dt, acc[k][jj]);
+            }
+        }
     }
 }
 
@@ -408,7 +426,7 @@ int mdta_softmax_weff(const float* Gpart, const float* ssq_part, int nchunks, co
     {
         const long long per = (long long)heads * Nimg;
         const int rpt = ceil_div(C, 64) * per >= 296 ? 4 : (ceil_div(C, 32) * per >= 296 ? 2 : 1);
-        const size_t smem = (size_t(c) * c + size_t(16 * rpt) * (c + 1)) * sizeof(float);
+        const size_t smem = (size_t(c) * ((c + 3) & ~3) + size_t(16 * rpt) * (c + 1)) * sizeof(float);
         IRB_SMEM_OPTIN((mdta_weff_kernel<1>), 100 * 1024);
         IRB_SMEM_OPTIN((mdta_weff_kernel<2>), 100 * 1024);
         IRB_SMEM_OPTIN((mdta_weff_kernel<4>), 100 * 1024);
