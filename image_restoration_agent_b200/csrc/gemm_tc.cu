@@ -7,6 +7,9 @@
 // mode 1 (3x3 conv, zero pad 1): A is a [N, H, W, C] channels-last activation, loaded by a 4-D TMA map
 //   {C, W, H, N} with a {64, BW, BH, 1} box (BW*BH = 128 pixels); the 9 taps are 9 shifted boxes and the
 //   out-of-bounds halo is zero-filled by TMA, which is exactly the convolution's zero padding.
+//   Narrow outputs (BN <= 64, `dyr`): a 16 x 8 pixel tile, and per (dx, K slab) ONE A box {64, 16, 10} whose rows
+//   dy * 16 .. dy * 16 + 127 are the A operand of tap (dy, dx) (a 2 KB offset: plain descriptors), next to the three
+//   weight slabs of that dx. Other narrow plain rings put `kg` K slabs into one stage (fewer barrier handshakes).
 // Weights Wt are [Nrows, Ktot] bf16, K contiguous (the layout nn.Conv2d / nn.Linear already use), loaded by a
 //   2-D TMA map with a {64, BN} box. Both operands land in shared memory in the 128B-swizzled K-major layout
 //   that the UMMA descriptors below describe.
